@@ -1,0 +1,527 @@
+#!/usr/bin/env python
+"""Benchmark of the two hot paths (contract: see the task statement / DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload both|ntxent|syncbn]
+
+Prints ONE JSON line (rank 0).  Primary metric: NT-Xent fwd+bwd pairs/s at global 2N=8192, D=128
+(BASELINE.json configs[3], run on N GPUs with rows sharded); the `syncbn` object carries the second
+metric (SyncBN fwd+bwd HBM GB/s on [256,256,8,8] NHWC bf16 per GPU, configs[1]).
+
+A "step" = one forward + backward of the loss on one batch of synthetic embeddings (or of the
+batch-norm layer on one activation tensor).  `value` is timed with inputs resident in HBM, `e2e`
+through the public module API from pinned host buffers (H2D of the inputs and D2H of the results
+inside the timed region).  Timed with CUDA events on the launching stream, max over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = 'NT-Xent fwd+bwd pairs/s at global 2N=8192 D=128'
+B_GLOBAL, N_VIEWS, DIM, TEMP = 4096, 2, 128, 0.5            # BASELINE.json configs[3]; T as main_supcon.py:214
+BN_SHAPE = (256, 256, 8, 8)                                   # BASELINE.json configs[1], per GPU
+
+
+def peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(hbm=p['hbm_gbs'], tf=p['bf16_tflops'], tf_sus=p.get('bf16_tflops_sustained'), src='measured')
+    return dict(hbm=6650.0, tf=1590.0, tf_sus=1400.0, src='fallback')
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the GPU is under the bench's load."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.samples, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'note': 'nvidia-smi unavailable'}
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for ts, line in self.samples:
+            if ts < t0 or ts > t1 + 0.15:
+                continue
+            parts = [p.strip() for p in line.split(',')]
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+# ----------------------------------------------------------------------------- helpers
+def dist_setup(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        os.environ.setdefault('MASTER_PORT', '29533')
+        torch.cuda.set_device(local)
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    else:
+        torch.cuda.set_device(0)
+    return world, rank, local
+
+
+def max_over_ranks(ms, world):
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return ms
+    t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier(world):
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def time_steps(step_fn, steps, warmup, world):
+    """W untimed steps, then exactly K steps between barrier+synchronize, CUDA events, max over ranks."""
+    import torch
+    for i in range(warmup):
+        step_fn(i)
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step_fn(warmup + i)
+    e1.record()
+    barrier(world)
+    return max_over_ranks(e0.elapsed_time(e1), world)
+
+
+# ----------------------------------------------------------------------------- NT-Xent (ours)
+def make_loss_runner(world, rank, engine, pool):
+    """Returns step functions for the loss on this rank's shard of the 2N=8192 global batch."""
+    import torch
+    import torch.nn.functional as F
+    from simclr_pytorch_distributed_b200 import SupConLoss
+    b_local = B_GLOBAL // world
+    dtype = torch.bfloat16 if engine == 'bf16' else torch.float32
+    g = torch.Generator().manual_seed(1234 + rank)
+    host = [F.normalize(torch.randn(b_local, N_VIEWS, DIM, generator=g), dim=-1).to(dtype).pin_memory()
+            for _ in range(pool)]
+    dev = [h.cuda().requires_grad_(True) for h in host]
+    if world == 1:
+        crit = SupConLoss(temperature=TEMP, engine=engine)
+        fwd = lambda f: crit(f)                                                     # noqa: E731
+    else:
+        from simclr_pytorch_distributed_b200.gather import DistributedSupConLoss
+        crit = DistributedSupConLoss(temperature=TEMP, engine=engine, normalize=False)
+        fwd = lambda f: crit(f)                                                     # noqa: E731
+
+    def step_resident(i):
+        f = dev[i % pool]
+        f.grad = None
+        fwd(f).backward()
+
+    grad_host = torch.empty(b_local, N_VIEWS, DIM, dtype=dtype).pin_memory()
+    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def step_e2e(i):
+        f = host[i % pool].cuda(non_blocking=True).requires_grad_(True)
+        loss = fwd(f)
+        loss.backward()
+        grad_host.copy_(f.grad, non_blocking=True)
+        loss_host.copy_(loss.detach().float(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()     # the caller reads loss and gradient every step
+
+    nbytes = b_local * N_VIEWS * DIM * host[0].element_size()
+    return step_resident, step_e2e, nbytes, nbytes + 4, b_local
+
+
+def loss_kernel_breakdown(engine, steps):
+    """Per-kernel CUDA-event times of one fwd+bwd through the C ABI (N=1 shapes), for the roofline."""
+    import torch
+    import torch.nn.functional as F
+    from simclr_pytorch_distributed_b200 import losses as L, _lib
+    lib = _lib.load()
+    dev = torch.device('cuda')
+    dtype = torch.bfloat16 if engine == 'bf16' else torch.float32
+    z = F.normalize(torch.randn(B_GLOBAL, N_VIEWS, DIM, device=dev), dim=-1).to(dtype)
+    plan = L.LossPlan(B_GLOBAL, N_VIEWS, DIM, engine=L._ENGINES[engine])
+    k = torch.empty((plan.n_k, plan.ldk), dtype=plan.k_torch, device=dev)
+    k_lo = torch.empty_like(k) if engine == 'bf16x3' else None
+    stats = torch.empty((4, plan.n_k), dtype=torch.float32, device=dev)
+    loss = torch.empty((), dtype=torch.float32, device=dev)
+    gout = torch.ones((), dtype=torch.float32, device=dev)
+    dk = torch.empty((plan.rows_local, DIM), dtype=torch.float32, device=dev)
+    dz = torch.empty_like(z)
+    prob = L._problem(plan, k, k_lo, None, None, TEMP, 0.07)
+    names = ['prep', 'forward(+finalize)', 'backward', 'finish']
+    tot = [0.0] * 4
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    for it in range(steps + 3):
+        ev[0].record()
+        L.launch_prep(lib, z, plan, False, k, k_lo, None)
+        ev[1].record()
+        L.launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
+        ev[2].record()
+        L.launch_backward(lib, prob, plan, stats[0], stats[2], gout, dk, dev)
+        ev[3].record()
+        L.launch_finish(lib, dk, z, plan, False, None, dz)
+        ev[4].record()
+        torch.cuda.synchronize()
+        if it >= 3:
+            for j in range(4):
+                tot[j] += ev[j].elapsed_time(ev[j + 1])
+    return {n: t / steps * 1e3 for n, t in zip(names, tot)}     # microseconds
+
+
+# ----------------------------------------------------------------------------- SyncBN (ours)
+def make_bn_runner(world, rank, pool):
+    import torch
+    from simclr_pytorch_distributed_b200 import SyncBatchNorm
+    N, C, H, W_ = BN_SHAPE
+    g = torch.Generator().manual_seed(4321 + rank)
+    mu = (torch.rand(1, C, 1, 1, generator=g) * 4 - 2)
+    sg = (torch.rand(1, C, 1, 1, generator=g) * 1.5 + 0.5)
+    mk = lambda: (torch.randn(N, C, H, W_, generator=g) * sg + mu).to(torch.bfloat16).contiguous(   # noqa: E731
+        memory_format=torch.channels_last)
+    host_x = [mk().pin_memory() for _ in range(pool)]
+    host_dy = [torch.randn(N, C, H, W_, generator=g).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last).pin_memory() for _ in range(pool)]
+    dev_x = [h.cuda().requires_grad_(True) for h in host_x]
+    dev_dy = [h.cuda() for h in host_dy]
+    bn = SyncBatchNorm(C).cuda()
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.normal_(0, 0.1)
+
+    def step_resident(i):
+        x = dev_x[i % pool]
+        x.grad = None
+        bn(x).backward(dev_dy[i % pool])
+
+    y_host = torch.empty_like(host_x[0]).pin_memory()
+    dx_host = torch.empty_like(host_x[0]).pin_memory()
+
+    def step_e2e(i):
+        x = host_x[i % pool].cuda(non_blocking=True).requires_grad_(True)
+        dy = host_dy[i % pool].cuda(non_blocking=True)
+        y = bn(x)
+        y.backward(dy)
+        y_host.copy_(y.detach(), non_blocking=True)
+        dx_host.copy_(x.grad, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    S = N * C * H * W_ * 2
+    return step_resident, step_e2e, S, bn
+
+
+def bn_kernel_breakdown(steps, pool=8):
+    import torch
+    from simclr_pytorch_distributed_b200.sync_batchnorm import _Kernels as K, _layout
+    N, C, H, W_ = BN_SHAPE
+    dev = torch.device('cuda')
+    xs = [(torch.randn(N, C, H, W_, device=dev) * 1.5 + 0.5).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last) for _ in range(pool)]
+    dys = [torch.randn(N, C, H, W_, device=dev).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last) for _ in range(pool)]
+    ys = [torch.empty_like(x) for x in xs]
+    dxs = [torch.empty_like(x) for x in xs]
+    w = torch.rand(C, device=dev) + 0.5
+    b = torch.randn(C, device=dev) * 0.1
+    rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    st = torch.empty(2 * C + 1, device=dev)
+    saved = torch.empty(2 * C + 1, device=dev)
+    out = torch.empty(4 * C, device=dev)
+    _, geom = _layout(xs[0])
+    names = ['stats', 'apply', 'backward_reduce', 'backward_apply']
+    tot = [0.0] * 4
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    for it in range(steps + 3):
+        x, dy, y, dx = xs[it % pool], dys[it % pool], ys[it % pool], dxs[it % pool]
+        ev[0].record()
+        K.stats(x, geom, st)
+        ev[1].record()
+        K.apply(x, y, geom, st, 1, w, b, rm, rv, 0.1, 1e-5, saved, 0)
+        ev[2].record()
+        K.backward_reduce(dy, x, geom, saved, w, b, out[:2 * C], out[2 * C:3 * C], out[3 * C:], 0)
+        ev[3].record()
+        K.backward_apply(dy, x, dx, geom, saved, w, b, out[:2 * C], 0)
+        ev[4].record()
+        torch.cuda.synchronize()
+        if it >= 3:
+            for j in range(4):
+                tot[j] += ev[j].elapsed_time(ev[j + 1])
+    return {n: t / steps * 1e3 for n, t in zip(names, tot)}
+
+
+# ----------------------------------------------------------------------------- CPU baselines
+def cpu_loss_baseline(budget_s=15.0, max_steps=20):
+    """The reference's dense CPU algorithm (oracle/dense_port.py, a port: /root/reference does not
+    travel to the GPU box) on the same [4096, 2, 128] fp32 workload, all host threads."""
+    import torch
+    import torch.nn.functional as F
+    from oracle.dense_port import dense_supcon_fwd_bwd
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    z = F.normalize(torch.randn(B_GLOBAL, N_VIEWS, DIM, generator=torch.Generator().manual_seed(1234)), dim=-1)
+    dense_supcon_fwd_bwd(z, temperature=TEMP)          # warm-up
+    times, t_start = [], time.time()
+    while len(times) < max_steps and (time.time() - t_start < budget_s or len(times) < 2):
+        t0 = time.perf_counter()
+        dense_supcon_fwd_bwd(z, temperature=TEMP)
+        times.append(time.perf_counter() - t0)
+    times.sort()
+    med = times[len(times) // 2]
+    return med, len(times), cores
+
+
+def cpu_bn_baseline(budget_s=8.0, max_steps=50):
+    import torch
+    from oracle.dense_port import bn_train_fwd_bwd
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    N, C, H, W_ = BN_SHAPE
+    x = (torch.randn(N, C, H, W_) * 1.5 + 0.5).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(N, C, H, W_).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w, b = torch.ones(C), torch.zeros(C)
+    rm, rv = torch.zeros(C), torch.ones(C)
+    bn_train_fwd_bwd(x, dy, w, b, rm, rv)
+    times, t_start = [], time.time()
+    while len(times) < max_steps and (time.time() - t_start < budget_s or len(times) < 2):
+        t0 = time.perf_counter()
+        bn_train_fwd_bwd(x, dy, w, b, rm, rv)
+        times.append(time.perf_counter() - t0)
+    times.sort()
+    return times[len(times) // 2], len(times), cores
+
+
+# ----------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """`--impl reference`: the reference's CPU path on this box's host cores (port, see above)."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    steps, warmup = args.steps, args.warmup
+    import torch
+    import torch.nn.functional as F
+    from oracle.dense_port import dense_supcon_fwd_bwd
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    z = F.normalize(torch.randn(B_GLOBAL, N_VIEWS, DIM, generator=torch.Generator().manual_seed(1234)), dim=-1)
+    t0 = time.perf_counter()
+    dense_supcon_fwd_bwd(z, temperature=TEMP)
+    first = time.perf_counter() - t0
+    # keep the whole run within a few minutes: cap the number of executed steps, not the workload
+    budget = 150.0
+    w_run = max(1, min(warmup, int(0.2 * budget / max(first, 1e-3))))
+    k_run = max(2, min(steps, int(0.8 * budget / max(first, 1e-3))))
+    for _ in range(w_run - 1):
+        dense_supcon_fwd_bwd(z, temperature=TEMP)
+    t0 = time.perf_counter()
+    for _ in range(k_run):
+        dense_supcon_fwd_bwd(z, temperature=TEMP)
+    per = (time.perf_counter() - t0) / k_run
+    val = B_GLOBAL / per
+    bn_t, bn_n, _ = cpu_bn_baseline(budget_s=10.0)
+    S = BN_SHAPE[0] * BN_SHAPE[1] * BN_SHAPE[2] * BN_SHAPE[3] * 2
+    sample = ('full workload [4096,2,128] fp32 fwd+bwd per step; %d of the requested %d timed steps '
+              'executed (after %d warm-ups)' % (k_run, steps, w_run))
+    out = {
+        'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'pairs/s', 'n_gpus': args.gpus,
+        'steps': steps, 'warmup': warmup, 'ms_per_step': per * 1e3, 'higher_is_better': True,
+        'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': 'NT-Xent SimCLR loss fwd+bwd, global 2N=8192 (B=4096 pairs, 2 views), D=128, '
+                               'T=0.5, base_T=0.07', 'device': 'host CPU'},
+        'cpu_baseline': {'value': val, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': val, 'unit': 'pairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+        'syncbn': {'metric': 'SyncBN fwd+bwd HBM GB/s', 'value': 8 * S / bn_t / 1e9, 'unit': 'GB/s',
+                   'ms_per_step': bn_t * 1e3,
+                   'config': {'workload': 'F.batch_norm train fwd+bwd [256,256,8,8] NHWC bf16 on host CPU'},
+                   'cpu_baseline': {'value': 8 * S / bn_t / 1e9, 'unit': 'GB/s', 'cores': cores, 'kind': 'port',
+                                    'sample': '%d fwd+bwd steps' % bn_n}},
+    }
+    print(json.dumps(out), flush=True)
+
+
+# ----------------------------------------------------------------------------- main (ours)
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=20)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--workload', default='both', choices=['both', 'ntxent', 'syncbn'])
+    ap.add_argument('--engine', default=os.environ.get('SIMCLR_B200_BENCH_ENGINE', 'bf16'))
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == 'reference':
+        run_reference(args)
+        return
+
+    import torch
+    from simclr_pytorch_distributed_b200 import _lib
+    world, rank, local = dist_setup(args)
+    lib = _lib.load()
+    pk = peaks()
+    engine = args.engine
+    if engine != 'fp32':
+        try:     # the tensor-core engine may not exist yet in an early round: say so, do not hide it
+            from simclr_pytorch_distributed_b200 import SupConLoss
+            SupConLoss(engine=engine)(torch.nn.functional.normalize(torch.randn(8, 2, 128, device='cuda'), dim=-1))
+        except RuntimeError as e:
+            if 'not built yet' not in str(e):
+                raise
+            engine = 'fp32'
+    sampler = ClockSampler(local) if rank == 0 else None
+    t_load0 = time.time()
+    out = {}
+
+    # ------------------------------------------------ NT-Xent
+    if args.workload in ('both', 'ntxent'):
+        pool = 64                                    # 64 x 2 MiB (bf16) of embeddings + grads > L2
+        step_res, step_e2e, h2d, d2h, b_local = make_loss_runner(world, rank, engine, pool)
+        c0 = lib.scb_launch_count()
+        ms = time_steps(step_res, args.steps, args.warmup, world)
+        launches = (lib.scb_launch_count() - c0) // (args.steps + args.warmup)
+        ms_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
+        per = ms / args.steps
+        A = C = N_VIEWS * B_GLOBAL
+        flops_step = 6.0 * A * C * DIM
+        out.update({
+            'metric': METRIC, 'value': B_GLOBAL / (per * 1e-3), 'unit': 'pairs/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': per, 'higher_is_better': True,
+            'scaling': 'strong', 'vs_baseline': None,
+            'dtype': {'bf16': 'bf16', 'bf16x3': 'bf16x3 (split bf16, fp32 accumulate)', 'fp32': 'f32'}[engine],
+            'data': 'synthetic',
+            'config': {'workload': 'NT-Xent SimCLR loss fwd+bwd, global 2N=8192 (B=4096 pairs, 2 views), D=128, '
+                                   'T=0.5, base_T=0.07; rows sharded over %d GPU(s), %d pairs per GPU' % (world, b_local),
+                       'engine': engine, 'l2': 'inputs rotate through a pool of %d embedding/gradient sets '
+                                               '(> L2 in total); the 2 MiB working set of one step is L2-resident '
+                                               'by construction' % pool,
+                       'launch': 'eager, public module API (SupConLoss.forward + autograd backward)'},
+            'e2e': {'value': B_GLOBAL / (ms_e2e / args.steps * 1e-3), 'unit': 'pairs/s',
+                    'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
+            'gpu_launches': int(launches),
+            'step_tensor_frac_of_measured_peak': flops_step / world / (per * 1e-3) / (pk['tf'] * 1e12),
+        })
+        if rank == 0 and world == 1:
+            kb = loss_kernel_breakdown(engine, min(args.steps, 100))
+            t_bwd = kb['backward']
+            achieved = 4.0 * A * C * DIM / (t_bwd * 1e-6) / 1e12
+            out['roofline'] = {'bound': 'tensor', 'achieved': achieved, 'peak': pk['tf'], 'unit': 'TFLOP/s',
+                               'frac': achieved / pk['tf'], 'traffic': None,
+                               'kernel': 'supcon backward (%s engine)' % engine, 'peak_source': pk['src'] + ' burst',
+                               'algorithmic_flops_per_launch': 4.0 * A * C * DIM,
+                               'kernel_us': kb}
+    # ------------------------------------------------ SyncBN
+    if args.workload in ('both', 'syncbn'):
+        pool = 12                                    # 12 x (x, dy, y, dx) of 8 MiB each = 400 MB > L2
+        step_res, step_e2e, S, bn = make_bn_runner(world, rank, pool)
+        c0 = lib.scb_launch_count()
+        ms = time_steps(step_res, args.steps, args.warmup, world)
+        launches = (lib.scb_launch_count() - c0) // (args.steps + args.warmup)
+        ms_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
+        per = ms / args.steps
+        gbs = 8.0 * S / (per * 1e-3) / 1e9           # per GPU; algorithmic bytes of SURVEY 8(d)
+        sb = {'metric': 'SyncBN fwd+bwd HBM GB/s', 'value': gbs * world, 'per_gpu': gbs, 'unit': 'GB/s',
+              'ms_per_step': per, 'scaling': 'weak', 'dtype': 'bf16 I/O, f32 statistics',
+              'config': {'workload': 'SyncBatchNorm fwd+bwd on [256,256,8,8] NHWC bf16 per GPU, %d GPU(s)' % world,
+                         'l2': 'x/dy/y/dx rotate through %d buffer sets (> L2)' % pool,
+                         'launch': 'eager, public module API'},
+              'e2e': {'value': 8.0 * S * world / (ms_e2e / args.steps * 1e-3) / 1e9, 'unit': 'GB/s',
+                      'h2d_bytes_per_step': 2 * S, 'd2h_bytes_per_step': 2 * S},
+              'gpu_launches': int(launches)}
+        if rank == 0 and world == 1:
+            kb = bn_kernel_breakdown(min(args.steps, 100))
+            tot_us = sum(kb.values())
+            ach = 8.0 * S / (tot_us * 1e-6) / 1e9
+            dom = max(kb, key=kb.get)
+            passes = {'stats': 1, 'apply': 2, 'backward_reduce': 2, 'backward_apply': 3}
+            ach_dom = passes[dom] * S / (kb[dom] * 1e-6) / 1e9
+            sb['roofline'] = {'bound': 'hbm', 'achieved': ach_dom, 'peak': pk['hbm'], 'unit': 'GB/s',
+                              'frac': ach_dom / pk['hbm'], 'traffic': None, 'kernel': 'bn_' + dom,
+                              'peak_source': pk['src'], 'algorithmic_bytes_per_launch': passes[dom] * S,
+                              'four_kernels_sum': {'achieved': ach, 'frac': ach / pk['hbm'], 'us': tot_us},
+                              'kernel_us': kb}
+        if 'metric' in out:
+            out['syncbn'] = sb
+        else:
+            out.update(sb)
+            out.update({'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'higher_is_better': True,
+                        'vs_baseline': None, 'data': 'synthetic'})
+
+    # keep the GPU under the same load until the clock sampler has a few readings
+    if rank == 0:
+        t_end = time.time()
+        extra_t0 = time.time()
+        i = 0
+        while time.time() - extra_t0 < 1.2:
+            step_res(i)
+            i += 1
+            if i % 50 == 0:
+                torch.cuda.synchronize()
+        torch.cuda.synchronize()
+        out['clocks'] = sampler.stop(t_load0, time.time())
+        out['clocks']['note'] = ('sampled every 100 ms from the first warm-up step to 1.2 s of the same steps '
+                                 'run right after the timed regions (the timed regions alone are shorter than '
+                                 'one sampling period)')
+    barrier(world)
+
+    # ------------------------------------------------ CPU baseline (rank 0, N=1)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        t, n, cores = cpu_loss_baseline()
+        out['cpu_baseline'] = {'value': B_GLOBAL / t, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port',
+                               'sample': 'median of %d fwd+bwd of the full [4096,2,128] fp32 workload '
+                                         '(oracle/dense_port.py, torch CPU)' % n}
+        if 'syncbn' in out:
+            tb, nb, _ = cpu_bn_baseline()
+            S = BN_SHAPE[0] * BN_SHAPE[1] * BN_SHAPE[2] * BN_SHAPE[3] * 2
+            out['syncbn']['cpu_baseline'] = {'value': 8 * S / tb / 1e9, 'unit': 'GB/s', 'cores': cores,
+                                             'kind': 'port', 'sample': 'median of %d fwd+bwd, F.batch_norm '
+                                                                       'train mode, NHWC bf16, torch CPU' % nb}
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,194 @@
+/* simclr_b200.h -- C ABI of libsimclr_b200.so: the sm_100a (B200) implementation of the two
+ * data-parallel hot paths of Dyfine/SimCLR_pytorch_distributed.
+ *
+ *   path 1  SupConLoss.forward / autograd backward      /root/reference/losses.py:17-93
+ *           + the gather / normalise glue that feeds it  /root/reference/main_supcon.py:266-286
+ *   path 2  the nn.SyncBatchNorm layers of --syncBN      /root/reference/main_supcon.py:222-224
+ *           (arithmetic: torch/nn/modules/_functions.py:10-209, ATen Normalization.cuh)
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in `_host`; the library never
+ *     allocates, frees or keeps caller memory; scratch ("workspace") is passed in by the caller,
+ *     sized by the matching *_workspace_bytes() query, and must be zero-filled ONCE when it is
+ *     created (kernels leave it zeroed again when they finish);
+ *   - every launch goes to the `stream` argument (a cudaStream_t passed as void*); nothing here
+ *     synchronises the device or the host;
+ *   - functions return SCB_OK (0) or a negative code; scb_last_error() gives the message of the
+ *     last failure on the calling thread;
+ *   - dtypes are the SCB_* codes below; all statistics / accumulators are float32.
+ *
+ * There is no CPU fallback: with no CUDA device the compute entry points fail with SCB_ERR_CUDA.
+ */
+#ifndef SIMCLR_B200_H_
+#define SIMCLR_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SCB_OK 0
+#define SCB_ERR_ARG (-1)
+#define SCB_ERR_CUDA (-2)
+#define SCB_ERR_UNSUPPORTED (-3)
+
+/* element types */
+#define SCB_F32 0
+#define SCB_BF16 1
+#define SCB_F16 2
+
+/* positive-pair rule (losses.py:39-50) */
+#define SCB_MASK_SIMCLR 0   /* labels=None, mask=None: eye(B)                 losses.py:42-43 */
+#define SCB_MASK_LABELS 1   /* eq(labels, labels.T)                           losses.py:44-48 */
+#define SCB_MASK_EXPLICIT 2 /* user [B,B] float mask, may be asymmetric       losses.py:49-50 */
+
+/* contrast_mode (losses.py:54-61) */
+#define SCB_MODE_ALL 0
+#define SCB_MODE_ONE 1
+
+/* arithmetic engines of the loss */
+#define SCB_ENGINE_FP32 0   /* SIMT fp32 tiles: any D, any mask; the exact-mode path            */
+#define SCB_ENGINE_BF16 1   /* tcgen05.mma kind::f16 (bf16 operands, fp32 TMEM accumulators)    */
+#define SCB_ENGINE_BF16X3 2 /* same kernels, operands split hi+lo (3 MMAs): ~fp32-accurate      */
+
+/* flags of the batch-norm apply kernels */
+#define SCB_BN_RELU 1       /* y = max(y, 0) fused into the apply      */
+
+const char* scb_last_error(void);
+int scb_version(void);
+/* compute capability of the current device as major*10+minor (100 on B200), negative on error */
+int scb_device_cc(void);
+/* number of kernels this library has launched in this process so far (bench bookkeeping) */
+int64_t scb_launch_count(void);
+
+/* ======================================================================== path 1: the loss
+ *
+ * Row order.  The contrast matrix K holds one embedding per row.  Rows are grouped in
+ * `n_seg` segments (one per rank; 1 on a single GPU), each segment view-major:
+ *      row = q*(n_views*seg) + v*seg + b        sample id = q*seg + b
+ * With n_seg == 1 this is exactly the reference's `cat(unbind(features, 1))` (losses.py:53).
+ * Anchors are all rows (`all`) or the v == 0 rows (`one`), losses.py:54-59.
+ */
+typedef struct scb_supcon_problem {
+    const void* k;          /* [n_k, ldk] contrast matrix, dtype k_dtype (F32 for ENGINE_FP32, BF16 else) */
+    const void* k_lo;       /* ENGINE_BF16X3 only: low-order halves, same shape (k ~= k + k_lo)   */
+    const int64_t* labels;  /* [n_seg*seg] class id per sample id, or NULL                        */
+    const float* mask;      /* [n_seg*seg, n_seg*seg] explicit mask, or NULL                      */
+    int32_t k_dtype;
+    int32_t n_k;            /* rows of k = n_seg * n_views * seg                                  */
+    int32_t dim;            /* D, logical feature length                                          */
+    int32_t ldk;            /* row stride of k in elements (>= dim; zero padded up to ldk)        */
+    int32_t n_views;        /* V                                                                  */
+    int32_t seg;            /* samples per segment                                                */
+    int32_t n_seg;          /* W                                                                  */
+    int32_t mask_kind;      /* SCB_MASK_*                                                         */
+    int32_t mode;           /* SCB_MODE_*                                                         */
+    int32_t engine;         /* SCB_ENGINE_*                                                       */
+    float inv_temperature;  /* 1/T                  losses.py:64-66                               */
+    float loss_scale;       /* T / base_temperature losses.py:90                                  */
+} scb_supcon_problem;
+
+/* Replaces main_supcon.py:283 (`F.normalize`, optional) + losses.py:52-53 (view-major stacking)
+ * + the dtype cast: features [n_samples, n_views, dim] (element strides given) -> rows
+ * [v*n_samples + b] of out_k (row stride ldk, columns dim..ldk-1 zero filled).
+ * out_k_lo (BF16X3) receives bf16(x - bf16(x)); out_inv_norm [n_views*n_samples] receives
+ * 1/max(||z||, eps) (1.0 when normalize == 0); both may be NULL. */
+int scb_supcon_prep(const void* features, int feat_dtype, int n_samples, int n_views, int dim,
+                    int64_t stride_sample, int64_t stride_view,
+                    int normalize, float eps,
+                    void* out_k, void* out_k_lo, int k_dtype, int ldk,
+                    float* out_inv_norm, void* stream);
+
+/* bytes of zero-initialised scratch the forward / backward of `p` need for `n_rows` local rows */
+int64_t scb_supcon_workspace_bytes(const scb_supcon_problem* p, int n_rows);
+
+/* Replaces losses.py:64-87 for the anchors among local rows [row_begin, row_begin+n_rows)
+ * (a whole number of segments' worth of rows of ONE segment on a multi-rank run, everything on
+ * one GPU).  Never materialises the [A, n_k] matrix.  Outputs, indexed by (row - row_begin):
+ *   out_lse    log sum_{j != i} exp(s_ij)            (natural log, s = k_i . k_j / T)
+ *   out_possum sum_j M_ij s_ij        out_npos  sum_j M_ij
+ *   out_loss[0] = (1/n_anchor_total) * sum over the LOCAL anchors of -(T/Tb)(possum/npos - lse)
+ *                 (losses.py:87-91; on one GPU this is the loss, across ranks the sum of the
+ *                 ranks' values is)
+ * Non-anchor local rows (mode `one`, v > 0) get lse = 0, npos = 1, possum = 0. */
+int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, int n_rows, int n_anchor_total,
+                       float* out_lse, float* out_possum, float* out_npos, float* out_loss,
+                       void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Replaces the autograd backward of losses.py:52-91 for the local rows: with
+ *   G_ij = coef * (exp(s_ij - lse_i) [i != j] - M_ij / npos_i),  coef = *grad_out * (T/Tb) / n_anchor_total
+ *   out_dk[row - row_begin, :] = (1/T) * sum_j ( [i anchor] G_ij + [j anchor] G_ji ) k_j
+ * lse_all / npos_all are indexed by GLOBAL row (length n_k; gathered across ranks by the caller).
+ * grad_out is a device scalar (the upstream gradient of the loss), so no host sync is needed.
+ * out_dk is float32 [n_rows, ld_dk]. */
+int scb_supcon_backward(const scb_supcon_problem* p, int row_begin, int n_rows,
+                        const float* lse_all, const float* npos_all, const float* grad_out,
+                        int n_anchor_total, float* out_dk, int ld_dk,
+                        void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Replaces the backward of main_supcon.py:283 (optional) and of losses.py:52-53: turns
+ * dK rows [v*n_samples + b] into d features [n_samples, n_views, dim] of dtype feat_dtype:
+ *   g = dk_row;  if normalize: g = (g - zh (zh . g)) * inv_norm,  zh = z * inv_norm. */
+int scb_supcon_finish(const float* dk, int ld_dk, const void* features, int feat_dtype,
+                      int n_samples, int n_views, int dim,
+                      int64_t stride_sample, int64_t stride_view,
+                      int normalize, const float* inv_norm,
+                      void* out_dfeatures, int64_t out_stride_sample, int64_t out_stride_view,
+                      void* stream);
+
+/* ================================================================== path 2: SyncBatchNorm
+ *
+ * Layout: x is [outer, C, inner] with element strides (stride_outer, 1*inner... ) described by
+ * `channels_last`: 1 -> memory is [M, C] with C contiguous (NHWC; M = N*H*W),
+ *                  0 -> memory is [N, C, HW] contiguous (NCHW; inner = HW).
+ */
+
+/* bytes of zero-initialised scratch for the two reduction kernels below */
+int64_t scb_bn_workspace_bytes(int channels);
+
+/* Replaces torch.batch_norm_stats (_functions.py:39): per-channel statistics of this rank's
+ * slice.  out_stats is the (2C+1)-float message the ranks exchange (_functions.py:41-79):
+ *   out_stats[0:C] = mean, out_stats[C:2C] = M2 = sum (x-mean)^2, out_stats[2C] = count. */
+int scb_bn_stats(const void* x, int dtype, int channels_last, int64_t outer, int channels,
+                 int64_t inner, float* out_stats, void* workspace, int64_t workspace_bytes,
+                 void* stream);
+
+/* Replaces torch.batch_norm_gather_stats_with_counts + torch.batch_norm_elemt
+ * (_functions.py:106-122; Normalization.cuh:458-502): merges `n_ranks` gathered messages
+ * stats_all [n_ranks, 2C+1] (Chan, rank order, empty ranks skipped), updates running_mean /
+ * running_var (momentum; unbiased global variance) when non-NULL, writes save_mean/save_invstd
+ * [C], save_count[0] = global element count per channel (kept on the device so the backward
+ * needs no host sync, cf. the count tensor of _functions.py:117) and y = (x - mean) * invstd * weight + bias (+ReLU with SCB_BN_RELU).
+ * With stats_all == NULL (eval mode, batchnorm.py:791-828) running_mean / running_var are used
+ * as the statistics and are not modified.  weight/bias may be NULL (affine=False). */
+int scb_bn_apply(const void* x, void* y, int dtype, int channels_last, int64_t outer, int channels,
+                 int64_t inner, const float* stats_all, int n_ranks,
+                 const float* weight, const float* bias,
+                 float* running_mean, float* running_var, float momentum, float eps,
+                 float* save_mean, float* save_invstd, float* save_count, int flags, void* stream);
+
+/* Replaces torch.batch_norm_backward_reduce (_functions.py:139-153):
+ *   out_sums[0:C] = sum dy, out_sums[C:2C] = sum dy (x - mean)   (the 2C floats all-reduced),
+ *   grad_weight = out_sums[C:2C] * invstd, grad_bias = out_sums[0:C]  (either may be NULL).
+ * With SCB_BN_RELU, dy is first gated by (y > 0), y recomputed from x (weight/bias needed). */
+int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, int channels_last,
+                           int64_t outer, int channels, int64_t inner,
+                           const float* mean, const float* invstd,
+                           const float* weight, const float* bias,
+                           float* out_sums, float* grad_weight, float* grad_bias, int flags,
+                           void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Replaces torch.batch_norm_backward_elemt (_functions.py:170-179):
+ *   dx = (dy - sum_dy/n - (x - mean) invstd^2 sum_dy_xmu/n) * weight * invstd,
+ * sums = the all-reduced [2C] vector, n_total[0] = global element count per channel (device). */
+int scb_bn_backward_apply(const void* dy, const void* x, void* dx, int dtype, int channels_last,
+                          int64_t outer, int channels, int64_t inner,
+                          const float* mean, const float* invstd,
+                          const float* weight, const float* bias,
+                          const float* sums, const float* n_total, int flags, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SIMCLR_B200_H_ */

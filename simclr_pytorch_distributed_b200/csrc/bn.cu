@@ -1,0 +1,734 @@
+// SyncBatchNorm hot path for sm_100a: HBM-bound streaming kernels.
+//
+// Replaces the five ATen ops nn.SyncBatchNorm runs per layer (torch/nn/modules/_functions.py:39,
+// 106,122,144,170; kernels in ATen/native/cuda/Normalization.cuh:970-1433) with four launches:
+//   bn_stats          x -> (mean, M2, count)                      1 read of x
+//   bn_apply          merge ranks' stats + running stats + y      1 read of x, 1 write of y
+//   bn_backward_reduce  dy, x -> (sum dy, sum dy*(x-mean)), dgamma, dbeta   2 reads
+//   bn_backward_apply   dy, x -> dx                                2 reads, 1 write
+// = 8 tensor passes per forward+backward, the algorithmic figure of SURVEY.md section 8(d).
+//
+// Layout in HBM: channels-last activations are a row-major [M, C] matrix (M = N*H*W).  A thread
+// owns VEC = 16/sizeof(T) consecutive channels and walks down the rows, so every global access is
+// a 16-byte vector and a warp touches 512 contiguous bytes (C >= 256) or several whole rows
+// (C < 256).  Partial sums go warp -> shared memory -> one float atomic per channel per CTA into
+// a zeroed accumulator; the last CTA to finish (ticket counter) turns the accumulators into the
+// result and zeroes them again, so the scratch is reusable without a memset.
+#include "common.cuh"
+
+namespace scb {
+
+constexpr int kBnThreads = 256;
+constexpr int kUnroll = 4;
+
+// ------------------------------------------------------------------ NHWC launch geometry
+struct NhwcGeom {
+    int vec, tx, ty, grid_x;
+    int64_t rows_per_cta, grid_y;
+};
+
+static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+static NhwcGeom nhwc_geom(int64_t M, int C, int elem_size, bool aligned16, int target_ctas) {
+    NhwcGeom g;
+    int vmax = 16 / elem_size;
+    g.vec = (aligned16 && C % vmax == 0) ? vmax : 1;
+    int cv = C / g.vec;
+    g.tx = next_pow2(cv) < 32 ? next_pow2(cv) : 32;
+    g.ty = kBnThreads / g.tx;
+    g.grid_x = (int)ceil_div(cv, g.tx);
+    int64_t want_y = target_ctas / g.grid_x; if (want_y < 1) want_y = 1;
+    int64_t chunk = (int64_t)g.ty * kUnroll;
+    int64_t rpc = ceil_div(ceil_div(M, want_y), chunk) * chunk;
+    if (rpc < chunk) rpc = chunk;
+    g.rows_per_cta = rpc;
+    g.grid_y = ceil_div(M, rpc); if (g.grid_y < 1) g.grid_y = 1;
+    return g;
+}
+
+// scratch layout: [0, 2C) float accumulators, then one unsigned ticket counter (at a 16-byte
+// aligned offset).  Zero on entry, zero again on exit.
+__host__ __device__ inline int64_t bn_ws_counter_offset(int C) { return ((int64_t)2 * C * 4 + 15) / 16 * 16; }
+
+// Block-level: sum `v[VEC]` over the ty rows of the CTA and atomically add into acc[c].
+template <int VEC>
+__device__ __forceinline__ void cta_reduce_to_global(float (&a)[VEC], float (&b)[VEC], float* sm,
+                                                     int tx, int ty, int TX, int TY, int c0, int C,
+                                                     float* acc_a, float* acc_b) {
+    // sm: [2][TY][TX*VEC]
+    const int W = TX * VEC;
+    float* sa = sm;
+    float* sb = sm + TY * W;
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        sa[ty * W + tx * VEC + i] = a[i];
+        sb[ty * W + tx * VEC + i] = b[i];
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < 2 * W; t += kBnThreads) {
+        const int which = t / W, col = t - which * W;
+        const float* s = which ? sb : sa;
+        float tot = 0.f;
+        for (int r = 0; r < TY; ++r) tot += s[r * W + col];
+        const int c = c0 - tx * VEC + col;    // c0 - tx*VEC = first channel of this CTA's tile
+        if (c < C) atomicAdd((which ? acc_b : acc_a) + c, tot);
+    }
+}
+
+// returns true in every thread of the last CTA of the grid to get here
+__device__ __forceinline__ bool last_cta_done(unsigned* counter, unsigned total) {
+    __shared__ unsigned s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = atomicAdd(counter, 1u);
+        s_last = (t == total - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_last) __threadfence();
+    return s_last != 0u;
+}
+
+// ------------------------------------------------------------------ B1: statistics (NHWC)
+// Shifted sums: every CTA uses the same per-channel shift K_c = x[0, c], accumulates
+// S1 = sum (x - K), S2 = sum (x - K)^2, which add across CTAs; mean = K + S1/n,
+// M2 = S2 - S1^2/n.  The shift removes the E[x^2]-E[x]^2 cancellation.
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads)
+bn_stats_nhwc_kernel(const T* __restrict__ x, int64_t M, int C, int TX, int64_t rows_per_cta,
+                     float* __restrict__ acc, unsigned* counter, float* __restrict__ out_stats) {
+    extern __shared__ float sm[];
+    const int TY = kBnThreads / TX;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = (blockIdx.x * TX + tx) * VEC;
+    const bool active = c0 < C;
+    float s1[VEC], s2[VEC], shift[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; shift[i] = 0.f; }
+    if (active) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) shift[i] = to_f32(x[c0 + i]);
+        const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
+        int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
+        const T* p = x + r * C + c0;
+        const int64_t step = (int64_t)TY * C;
+        for (; r + (kUnroll - 1) * TY < r_end; r += kUnroll * TY, p += kUnroll * step) {
+            float v[kUnroll][VEC];
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) load_row_vec<T, VEC>(p + u * step, v[u]);
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float d = v[u][i] - shift[i];
+                    s1[i] += d;
+                    s2[i] = fmaf(d, d, s2[i]);
+                }
+        }
+        for (; r < r_end; r += TY, p += step) {
+            float v[VEC];
+            load_row_vec<T, VEC>(p, v);
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                const float d = v[i] - shift[i];
+                s1[i] += d;
+                s2[i] = fmaf(d, d, s2[i]);
+            }
+        }
+    }
+    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
+    if (last_cta_done(counter, gridDim.x * gridDim.y)) {
+        const float n = (float)M;
+        for (int c = threadIdx.x; c < C; c += kBnThreads) {
+            const float a = __ldcg(acc + c), b = __ldcg(acc + C + c);
+            const float k = to_f32(x[c]);
+            out_stats[c] = k + a / n;
+            out_stats[C + c] = fmaxf(b - a * a / n, 0.f);
+            acc[c] = 0.f;
+            acc[C + c] = 0.f;
+        }
+        if (threadIdx.x == 0) { out_stats[2 * C] = n; *counter = 0u; }
+    }
+}
+
+// ------------------------------------------------------------------ per-channel coefficients
+// Merge the ranks' (mean, M2, n) messages for channel c (Normalization.cuh:458-502 restated
+// on M2 instead of 1/invstd^2 - eps), or take the running statistics in eval mode.
+__device__ __forceinline__ void merged_stats(const float* __restrict__ stats_all, int n_ranks, int C,
+                                             int c, const float* running_mean,
+                                             const float* running_var, float eps,
+                                             float& mean, float& invstd, float& m2, float& n) {
+    if (stats_all == nullptr) {
+        mean = running_mean[c];
+        invstd = rsqrtf(running_var[c] + eps);
+        m2 = 0.f; n = 1.f;      // eval: statistics are constants, the backward's 1/n terms vanish
+        return;
+    }
+    const int stride = 2 * C + 1;
+    n = 0.f; mean = 0.f; m2 = 0.f;
+    for (int r = 0; r < n_ranks; ++r) {
+        const float* s = stats_all + (int64_t)r * stride;
+        chan_merge(n, mean, m2, s[2 * C], s[c], s[C + c]);
+    }
+    invstd = rsqrtf(m2 / n + eps);
+}
+
+// ------------------------------------------------------------------ B2+B3: apply (NHWC)
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads)
+bn_apply_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, int TX,
+                     int64_t rows_per_cta, const float* __restrict__ stats_all, int n_ranks,
+                     const float* __restrict__ weight, const float* __restrict__ bias,
+                     float* running_mean, float* running_var, float momentum, float eps,
+                     float* save_mean, float* save_invstd, float* save_count, int flags) {
+    extern __shared__ float sm[];           // [2][TX*VEC]: scale a, offset b
+    const int TY = kBnThreads / TX;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int W = TX * VEC;
+    const int tile_c0 = blockIdx.x * W;
+    for (int t = threadIdx.x; t < W; t += kBnThreads) {
+        const int c = tile_c0 + t;
+        float a = 0.f, b = 0.f;
+        if (c < C) {
+            float mean, invstd, m2, n;
+            merged_stats(stats_all, n_ranks, C, c, running_mean, running_var, eps, mean, invstd, m2, n);
+            const float g = weight ? weight[c] : 1.f;
+            a = g * invstd;
+            b = (bias ? bias[c] : 0.f) - mean * a;
+            if (blockIdx.y == 0) {
+                if (save_mean) save_mean[c] = mean;
+                if (save_invstd) save_invstd[c] = invstd;
+                if (stats_all != nullptr) {
+                    if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                    if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+                }
+                if (c == 0 && save_count) save_count[0] = n;
+            }
+        }
+        sm[t] = a;
+        sm[W + t] = b;
+    }
+    __syncthreads();
+    const int c0 = tile_c0 + tx * VEC;
+    if (c0 >= C) return;
+    float a[VEC], b[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { a[i] = sm[tx * VEC + i]; b[i] = sm[W + tx * VEC + i]; }
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
+    int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
+    const int64_t step = (int64_t)TY * C;
+    const T* p = x + r * C + c0;
+    T* q = y + r * C + c0;
+    for (; r + (kUnroll - 1) * TY < r_end; r += kUnroll * TY, p += kUnroll * step, q += kUnroll * step) {
+        float v[kUnroll][VEC];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) load_row_vec<T, VEC>(p + u * step, v[u]);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                float o = fmaf(v[u][i], a[i], b[i]);
+                v[u][i] = relu ? fmaxf(o, 0.f) : o;
+            }
+            store_row_vec<T, VEC>(q + u * step, v[u]);
+        }
+    }
+    for (; r < r_end; r += TY, p += step, q += step) {
+        float v[VEC];
+        load_row_vec<T, VEC>(p, v);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            float o = fmaf(v[i], a[i], b[i]);
+            v[i] = relu ? fmaxf(o, 0.f) : o;
+        }
+        store_row_vec<T, VEC>(q, v);
+    }
+}
+
+// ------------------------------------------------------------------ B4: backward reduce (NHWC)
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t M, int C, int TX,
+                          int64_t rows_per_cta, const float* __restrict__ mean,
+                          const float* __restrict__ invstd, const float* __restrict__ weight,
+                          const float* __restrict__ bias, float* __restrict__ acc, unsigned* counter,
+                          float* __restrict__ out_sums, float* grad_weight, float* grad_bias, int flags) {
+    extern __shared__ float sm[];
+    const int TY = kBnThreads / TX;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = (blockIdx.x * TX + tx) * VEC;
+    const bool active = c0 < C;
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    float s1[VEC], s2[VEC], mu[VEC], a[VEC], b[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; mu[i] = 0.f; a[i] = 0.f; b[i] = 0.f; }
+    if (active) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            mu[i] = mean[c0 + i];
+            if (relu) {   // y = (x - mu) * a + b, gate dy by y > 0
+                a[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
+                b[i] = bias ? bias[c0 + i] : 0.f;
+            }
+        }
+        const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
+        int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
+        const int64_t step = (int64_t)TY * C;
+        const T* px = x + r * C + c0;
+        const T* pd = dy + r * C + c0;
+        constexpr int U = 2;   // 2 rows x 2 tensors = 4 vector loads in flight
+        for (; r + (U - 1) * TY < r_end; r += U * TY, px += U * step, pd += U * step) {
+            float vx[U][VEC], vd[U][VEC];
+#pragma unroll
+            for (int u = 0; u < U; ++u) { load_row_vec<T, VEC>(px + u * step, vx[u]); load_row_vec<T, VEC>(pd + u * step, vd[u]); }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float xm = vx[u][i] - mu[i];
+                    float g = vd[u][i];
+                    if (relu) g = (fmaf(xm, a[i], b[i]) > 0.f) ? g : 0.f;
+                    s1[i] += g;
+                    s2[i] = fmaf(g, xm, s2[i]);
+                }
+        }
+        for (; r < r_end; r += TY, px += step, pd += step) {
+            float vx[VEC], vd[VEC];
+            load_row_vec<T, VEC>(px, vx);
+            load_row_vec<T, VEC>(pd, vd);
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                const float xm = vx[i] - mu[i];
+                float g = vd[i];
+                if (relu) g = (fmaf(xm, a[i], b[i]) > 0.f) ? g : 0.f;
+                s1[i] += g;
+                s2[i] = fmaf(g, xm, s2[i]);
+            }
+        }
+    }
+    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
+    if (last_cta_done(counter, gridDim.x * gridDim.y)) {
+        for (int c = threadIdx.x; c < C; c += kBnThreads) {
+            const float sd = __ldcg(acc + c), sx = __ldcg(acc + C + c);
+            out_sums[c] = sd;
+            out_sums[C + c] = sx;
+            if (grad_weight) grad_weight[c] = sx * invstd[c];
+            if (grad_bias) grad_bias[c] = sd;
+            acc[c] = 0.f;
+            acc[C + c] = 0.f;
+        }
+        if (threadIdx.x == 0) *counter = 0u;
+    }
+}
+
+// ------------------------------------------------------------------ B5: backward apply (NHWC)
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_apply_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx,
+                         int64_t M, int C, int TX, int64_t rows_per_cta,
+                         const float* __restrict__ mean, const float* __restrict__ invstd,
+                         const float* __restrict__ weight, const float* __restrict__ bias,
+                         const float* __restrict__ sums, const float* __restrict__ n_total, int flags) {
+    const int TY = kBnThreads / TX;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = (blockIdx.x * TX + tx) * VEC;
+    if (c0 >= C) return;
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    const float inv_n = 1.f / n_total[0];
+    // dx = (dy - k2 - (x - mu) * k3) * k1
+    float mu[VEC], k1[VEC], k2[VEC], k3[VEC], bb[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        const int c = c0 + i;
+        const float is = invstd[c];
+        mu[i] = mean[c];
+        k1[i] = (weight ? weight[c] : 1.f) * is;
+        k2[i] = sums[c] * inv_n;
+        k3[i] = is * is * sums[C + c] * inv_n;
+        bb[i] = bias ? bias[c] : 0.f;
+    }
+    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
+    int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
+    const int64_t step = (int64_t)TY * C;
+    const T* px = x + r * C + c0;
+    const T* pd = dy + r * C + c0;
+    T* po = dx + r * C + c0;
+    constexpr int U = 2;
+    for (; r + (U - 1) * TY < r_end; r += U * TY, px += U * step, pd += U * step, po += U * step) {
+        float vx[U][VEC], vd[U][VEC];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { load_row_vec<T, VEC>(px + u * step, vx[u]); load_row_vec<T, VEC>(pd + u * step, vd[u]); }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                const float xm = vx[u][i] - mu[i];
+                float g = vd[u][i];
+                if (relu) g = (fmaf(xm, k1[i], bb[i]) > 0.f) ? g : 0.f;
+                vd[u][i] = (g - k2[i] - xm * k3[i]) * k1[i];
+            }
+            store_row_vec<T, VEC>(po + u * step, vd[u]);
+        }
+    }
+    for (; r < r_end; r += TY, px += step, pd += step, po += step) {
+        float vx[VEC], vd[VEC];
+        load_row_vec<T, VEC>(px, vx);
+        load_row_vec<T, VEC>(pd, vd);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            const float xm = vx[i] - mu[i];
+            float g = vd[i];
+            if (relu) g = (fmaf(xm, k1[i], bb[i]) > 0.f) ? g : 0.f;
+            vd[i] = (g - k2[i] - xm * k3[i]) * k1[i];
+        }
+        store_row_vec<T, VEC>(po, vd);
+    }
+}
+
+// ================================================================== NCHW ([N, C, inner]) family
+// One CTA per (channel, slice of N); threads walk the contiguous `inner` run of each sample.
+// This is the layout the reference model actually runs (no channels_last anywhere in
+// main_supcon.py), kept correct and vectorised but not the tuned path (BASELINE cfg 2 is NHWC).
+template <typename T, int VEC, typename F>
+__device__ __forceinline__ void nchw_foreach(int64_t n_begin, int64_t n_end, int C, int64_t inner,
+                                             int c, F&& f) {
+    // element index space of this CTA: (n, i) with i a multiple of VEC
+    const int64_t per_n = inner / VEC;
+    const int64_t total = (n_end - n_begin) * per_n;
+    for (int64_t e = threadIdx.x; e < total; e += kBnThreads) {
+        const int64_t n = n_begin + e / per_n;
+        const int64_t i = (e % per_n) * VEC;
+        f((n * C + c) * inner + i);
+    }
+}
+
+__device__ __forceinline__ float block_sum(float v, float* sm) {
+    v = warp_sum(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) sm[w] = v;
+    __syncthreads();
+    float t = (threadIdx.x < kBnThreads / 32) ? sm[threadIdx.x] : 0.f;
+    if (w == 0) t = warp_sum(t);
+    return t;   // valid in warp 0
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads)
+bn_stats_nchw_kernel(const T* __restrict__ x, int64_t N, int C, int64_t inner, int64_t n_per_cta,
+                     float* __restrict__ acc, unsigned* counter, float* __restrict__ out_stats) {
+    __shared__ float sm[32];
+    const int c = blockIdx.x;
+    const float shift = to_f32(x[(int64_t)c * inner]);
+    const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
+    float s1 = 0.f, s2 = 0.f;
+    nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
+        float v[VEC];
+        load_row_vec<T, VEC>(x + off, v);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) { const float d = v[i] - shift; s1 += d; s2 = fmaf(d, d, s2); }
+    });
+    s1 = block_sum(s1, sm);
+    s2 = block_sum(s2, sm);
+    if (threadIdx.x == 0) { atomicAdd(acc + c, s1); atomicAdd(acc + C + c, s2); }
+    if (last_cta_done(counter, gridDim.x * gridDim.y)) {
+        const float n = (float)(N * inner);
+        for (int cc = threadIdx.x; cc < C; cc += kBnThreads) {
+            const float a = __ldcg(acc + cc), b = __ldcg(acc + C + cc);
+            const float k = to_f32(x[(int64_t)cc * inner]);
+            out_stats[cc] = k + a / n;
+            out_stats[C + cc] = fmaxf(b - a * a / n, 0.f);
+            acc[cc] = 0.f; acc[C + cc] = 0.f;
+        }
+        if (threadIdx.x == 0) { out_stats[2 * C] = n; *counter = 0u; }
+    }
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads)
+bn_apply_nchw_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t N, int C, int64_t inner,
+                     int64_t n_per_cta, const float* __restrict__ stats_all, int n_ranks,
+                     const float* __restrict__ weight, const float* __restrict__ bias,
+                     float* running_mean, float* running_var, float momentum, float eps,
+                     float* save_mean, float* save_invstd, float* save_count, int flags) {
+    const int c = blockIdx.x;
+    float mean, invstd, m2, n;
+    merged_stats(stats_all, n_ranks, C, c, running_mean, running_var, eps, mean, invstd, m2, n);
+    const float a = (weight ? weight[c] : 1.f) * invstd;
+    const float b = (bias ? bias[c] : 0.f) - mean * a;
+    __syncthreads();   // every thread has read the running stats before thread 0 rewrites them
+    if (blockIdx.y == 0 && threadIdx.x == 0) {
+        if (save_mean) save_mean[c] = mean;
+        if (save_invstd) save_invstd[c] = invstd;
+        if (stats_all != nullptr) {
+            if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+            if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+        }
+        if (c == 0 && save_count) save_count[0] = n;
+    }
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
+    nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
+        float v[VEC];
+        load_row_vec<T, VEC>(x + off, v);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) { float o = fmaf(v[i], a, b); v[i] = relu ? fmaxf(o, 0.f) : o; }
+        store_row_vec<T, VEC>(y + off, v);
+    });
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t N, int C,
+                          int64_t inner, int64_t n_per_cta, const float* __restrict__ mean,
+                          const float* __restrict__ invstd, const float* __restrict__ weight,
+                          const float* __restrict__ bias, float* __restrict__ acc, unsigned* counter,
+                          float* __restrict__ out_sums, float* grad_weight, float* grad_bias, int flags) {
+    __shared__ float sm[32];
+    const int c = blockIdx.x;
+    const float mu = mean[c];
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    const float a = relu ? (weight ? weight[c] : 1.f) * invstd[c] : 0.f;
+    const float b = (relu && bias) ? bias[c] : 0.f;
+    const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
+    float s1 = 0.f, s2 = 0.f;
+    nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
+        float vx[VEC], vd[VEC];
+        load_row_vec<T, VEC>(x + off, vx);
+        load_row_vec<T, VEC>(dy + off, vd);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            const float xm = vx[i] - mu;
+            float g = vd[i];
+            if (relu) g = (fmaf(xm, a, b) > 0.f) ? g : 0.f;
+            s1 += g; s2 = fmaf(g, xm, s2);
+        }
+    });
+    s1 = block_sum(s1, sm);
+    s2 = block_sum(s2, sm);
+    if (threadIdx.x == 0) { atomicAdd(acc + c, s1); atomicAdd(acc + C + c, s2); }
+    if (last_cta_done(counter, gridDim.x * gridDim.y)) {
+        for (int cc = threadIdx.x; cc < C; cc += kBnThreads) {
+            const float sd = __ldcg(acc + cc), sx = __ldcg(acc + C + cc);
+            out_sums[cc] = sd; out_sums[C + cc] = sx;
+            if (grad_weight) grad_weight[cc] = sx * invstd[cc];
+            if (grad_bias) grad_bias[cc] = sd;
+            acc[cc] = 0.f; acc[C + cc] = 0.f;
+        }
+        if (threadIdx.x == 0) *counter = 0u;
+    }
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_apply_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx,
+                         int64_t N, int C, int64_t inner, int64_t n_per_cta,
+                         const float* __restrict__ mean, const float* __restrict__ invstd,
+                         const float* __restrict__ weight, const float* __restrict__ bias,
+                         const float* __restrict__ sums, const float* __restrict__ n_total, int flags) {
+    const int c = blockIdx.x;
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    const float inv_n = 1.f / n_total[0];
+    const float is = invstd[c], mu = mean[c];
+    const float k1 = (weight ? weight[c] : 1.f) * is;
+    const float k2 = sums[c] * inv_n;
+    const float k3 = is * is * sums[C + c] * inv_n;
+    const float bb = bias ? bias[c] : 0.f;
+    const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
+    nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
+        float vx[VEC], vd[VEC];
+        load_row_vec<T, VEC>(x + off, vx);
+        load_row_vec<T, VEC>(dy + off, vd);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            const float xm = vx[i] - mu;
+            float g = vd[i];
+            if (relu) g = (fmaf(xm, k1, bb) > 0.f) ? g : 0.f;
+            vd[i] = (g - k2 - xm * k3) * k1;
+        }
+        store_row_vec<T, VEC>(dx + off, vd);
+    });
+}
+
+// ------------------------------------------------------------------ host-side dispatch
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+struct NchwGeom { int vec; int64_t n_per_cta, grid_y; };
+static NchwGeom nchw_geom(int64_t N, int C, int64_t inner, int elem_size, bool al16, int target_ctas) {
+    NchwGeom g;
+    int vmax = 16 / elem_size;
+    g.vec = (al16 && inner % vmax == 0) ? vmax : 1;
+    int64_t want_y = target_ctas / C; if (want_y < 1) want_y = 1;
+    if (want_y > N) want_y = N;
+    g.n_per_cta = ceil_div(N, want_y);
+    g.grid_y = ceil_div(N, g.n_per_cta);
+    return g;
+}
+
+static int check_bn_common(const void* x, int dtype, int64_t outer, int channels, int64_t inner) {
+    SCB_REQUIRE(x != nullptr, "bn: null tensor pointer");
+    SCB_REQUIRE(dtype == SCB_F32 || dtype == SCB_BF16 || dtype == SCB_F16, "bn: unsupported dtype %d", dtype);
+    SCB_REQUIRE(channels > 0, "SyncBatchNorm number of input channels should be non-zero");
+    SCB_REQUIRE(outer >= 0 && inner >= 1, "bn: bad shape outer=%lld inner=%lld", (long long)outer, (long long)inner);
+    SCB_REQUIRE(outer * inner < (int64_t)1 << 40, "bn: tensor too large");
+    return SCB_OK;
+}
+
+}  // namespace scb
+
+using namespace scb;
+
+extern "C" int64_t scb_bn_workspace_bytes(int channels) {
+    if (channels <= 0) return 0;
+    return bn_ws_counter_offset(channels) + 16;
+}
+
+#define SCB_VEC_SWITCH(vecv, VEC_, ...)                                   \
+    if ((vecv) == 1) { constexpr int VEC_ = 1; __VA_ARGS__; }            \
+    else { constexpr int VEC_ = Vec16<T>::N; __VA_ARGS__; }
+
+extern "C" int scb_bn_stats(const void* x, int dtype, int channels_last, int64_t outer, int channels,
+                            int64_t inner, float* out_stats, void* workspace, int64_t workspace_bytes,
+                            void* stream_) {
+    if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
+    SCB_REQUIRE(out_stats && workspace, "bn_stats: null output/workspace");
+    SCB_REQUIRE(workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_stats: workspace too small");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int C = channels;
+    if (outer * inner == 0) {   // empty slice still sends a zero message (_functions.py:50-57)
+        SCB_CUDA_OK(cudaMemsetAsync(out_stats, 0, (2 * C + 1) * sizeof(float), stream));
+        return SCB_OK;
+    }
+    float* acc = (float*)workspace;
+    unsigned* counter = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
+    const int target = 2 * sm_count();
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        if (channels_last) {
+            const int64_t M = outer * inner;
+            NhwcGeom g = nhwc_geom(M, C, sizeof(T), aligned16(x), target);
+            dim3 grid(g.grid_x, (unsigned)g.grid_y);
+            size_t smem = 2 * kBnThreads * g.vec * sizeof(float);
+            SCB_VEC_SWITCH(g.vec, VEC, (bn_stats_nhwc_kernel<T, VEC><<<grid, kBnThreads, smem, stream>>>(
+                (const T*)x, M, C, g.tx, g.rows_per_cta, acc, counter, out_stats)));
+        } else {
+            NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), aligned16(x), target);
+            dim3 grid(C, (unsigned)g.grid_y);
+            SCB_VEC_SWITCH(g.vec, VEC, (bn_stats_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
+                (const T*)x, outer, C, inner, g.n_per_cta, acc, counter, out_stats)));
+        }
+    });
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_bn_apply(const void* x, void* y, int dtype, int channels_last, int64_t outer,
+                            int channels, int64_t inner, const float* stats_all, int n_ranks,
+                            const float* weight, const float* bias, float* running_mean,
+                            float* running_var, float momentum, float eps, float* save_mean,
+                            float* save_invstd, float* save_count, int flags, void* stream_) {
+    if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
+    SCB_REQUIRE(y != nullptr, "bn_apply: null output");
+    SCB_REQUIRE(stats_all != nullptr || (running_mean && running_var),
+                "bn_apply: eval mode needs running_mean and running_var");
+    SCB_REQUIRE(stats_all == nullptr || n_ranks >= 1, "bn_apply: n_ranks must be >= 1");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int C = channels;
+    if (outer * inner == 0) return SCB_OK;
+    const int target = 4 * sm_count();
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        if (channels_last) {
+            const int64_t M = outer * inner;
+            NhwcGeom g = nhwc_geom(M, C, sizeof(T), aligned16(x) && aligned16(y), target);
+            dim3 grid(g.grid_x, (unsigned)g.grid_y);
+            size_t smem = 2 * g.tx * g.vec * sizeof(float);
+            SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nhwc_kernel<T, VEC><<<grid, kBnThreads, smem, stream>>>(
+                (const T*)x, (T*)y, M, C, g.tx, g.rows_per_cta, stats_all, n_ranks, weight, bias,
+                running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
+        } else {
+            NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), aligned16(x) && aligned16(y), target);
+            dim3 grid(C, (unsigned)g.grid_y);
+            SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
+                (const T*)x, (T*)y, outer, C, inner, g.n_per_cta, stats_all, n_ranks, weight, bias,
+                running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
+        }
+    });
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, int channels_last,
+                                      int64_t outer, int channels, int64_t inner, const float* mean,
+                                      const float* invstd, const float* weight, const float* bias,
+                                      float* out_sums, float* grad_weight, float* grad_bias, int flags,
+                                      void* workspace, int64_t workspace_bytes, void* stream_) {
+    if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
+    SCB_REQUIRE(dy && mean && invstd && out_sums && workspace, "bn_backward_reduce: null pointer");
+    SCB_REQUIRE(workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_backward_reduce: workspace too small");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int C = channels;
+    if (outer * inner == 0) {
+        SCB_CUDA_OK(cudaMemsetAsync(out_sums, 0, 2 * C * sizeof(float), stream));
+        if (grad_weight) SCB_CUDA_OK(cudaMemsetAsync(grad_weight, 0, C * sizeof(float), stream));
+        if (grad_bias) SCB_CUDA_OK(cudaMemsetAsync(grad_bias, 0, C * sizeof(float), stream));
+        return SCB_OK;
+    }
+    float* acc = (float*)workspace;
+    unsigned* counter = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
+    const int target = 2 * sm_count();
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        if (channels_last) {
+            const int64_t M = outer * inner;
+            NhwcGeom g = nhwc_geom(M, C, sizeof(T), aligned16(x) && aligned16(dy), target);
+            dim3 grid(g.grid_x, (unsigned)g.grid_y);
+            size_t smem = 2 * kBnThreads * g.vec * sizeof(float);
+            SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_reduce_nhwc_kernel<T, VEC><<<grid, kBnThreads, smem, stream>>>(
+                (const T*)dy, (const T*)x, M, C, g.tx, g.rows_per_cta, mean, invstd, weight, bias, acc,
+                counter, out_sums, grad_weight, grad_bias, flags)));
+        } else {
+            NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), aligned16(x) && aligned16(dy), target);
+            dim3 grid(C, (unsigned)g.grid_y);
+            SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_reduce_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
+                (const T*)dy, (const T*)x, outer, C, inner, g.n_per_cta, mean, invstd, weight, bias, acc,
+                counter, out_sums, grad_weight, grad_bias, flags)));
+        }
+    });
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_bn_backward_apply(const void* dy, const void* x, void* dx, int dtype,
+                                     int channels_last, int64_t outer, int channels, int64_t inner,
+                                     const float* mean, const float* invstd, const float* weight,
+                                     const float* bias, const float* sums, const float* n_total,
+                                     int flags, void* stream_) {
+    if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
+    SCB_REQUIRE(dy && dx && mean && invstd && sums && n_total, "bn_backward_apply: null pointer");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int C = channels;
+    if (outer * inner == 0) return SCB_OK;
+    const int target = 4 * sm_count();
+    const bool al = aligned16(x) && aligned16(dy) && aligned16(dx);
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        if (channels_last) {
+            const int64_t M = outer * inner;
+            NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, target);
+            dim3 grid(g.grid_x, (unsigned)g.grid_y);
+            SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_apply_nhwc_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
+                (const T*)dy, (const T*)x, (T*)dx, M, C, g.tx, g.rows_per_cta, mean, invstd, weight, bias,
+                sums, n_total, flags)));
+        } else {
+            NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), al, target);
+            dim3 grid(C, (unsigned)g.grid_y);
+            SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_apply_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
+                (const T*)dy, (const T*)x, (T*)dx, outer, C, inner, g.n_per_cta, mean, invstd, weight,
+                bias, sums, n_total, flags)));
+        }
+    });
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}

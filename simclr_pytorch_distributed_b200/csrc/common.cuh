@@ -1,0 +1,122 @@
+// Shared helpers for the sm_100a kernels behind the C-ABI in include/simclr_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "../../include/simclr_b200.h"
+
+namespace scb {
+
+// ---------------------------------------------------------------- error reporting
+void set_error(const char* fmt, ...);
+
+#define SCB_CUDA_OK(expr)                                                              \
+    do {                                                                               \
+        cudaError_t _e = (expr);                                                       \
+        if (_e != cudaSuccess) {                                                       \
+            scb::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,               \
+                           cudaGetErrorString(_e));                                    \
+            return SCB_ERR_CUDA;                                                       \
+        }                                                                              \
+    } while (0)
+
+#define SCB_REQUIRE(cond, ...)                                                         \
+    do {                                                                               \
+        if (!(cond)) {                                                                 \
+            scb::set_error(__VA_ARGS__);                                               \
+            return SCB_ERR_ARG;                                                        \
+        }                                                                              \
+    } while (0)
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+int sm_count();   // SMs of the current device (cached per device)
+void count_launch(int n = 1);   // bookkeeping behind scb_launch_count()
+
+// ---------------------------------------------------------------- dtype plumbing
+template <typename T> struct Vec16 { static constexpr int N = 16 / sizeof(T); };
+
+__device__ __forceinline__ float to_f32(float v) { return v; }
+__device__ __forceinline__ float to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_f32(__half v) { return __half2float(v); }
+
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+
+// Streaming 16-byte global accesses: data is touched once per pass, keep it out of L1.
+__device__ __forceinline__ uint4 ldg_stream16(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg_stream16(void* p, const uint4& v) {
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// load VEC consecutive elements (VEC == 16/sizeof(T) -> one 16-byte access, VEC == 1 -> scalar)
+template <typename T, int VEC>
+__device__ __forceinline__ void load_row_vec(const T* p, float (&v)[VEC]) {
+    if constexpr (VEC == 1) {
+        v[0] = to_f32(*p);
+    } else {
+        static_assert(VEC * sizeof(T) == 16, "vector path is 16 bytes");
+        uint4 raw = ldg_stream16(p);
+        const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) v[i] = to_f32(e[i]);
+    }
+}
+template <typename T, int VEC>
+__device__ __forceinline__ void store_row_vec(T* p, const float (&v)[VEC]) {
+    if constexpr (VEC == 1) {
+        *p = from_f32<T>(v[0]);
+    } else {
+        uint4 raw;
+        T* e = reinterpret_cast<T*>(&raw);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) e[i] = from_f32<T>(v[i]);
+        stg_stream16(p, raw);
+    }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Chan's pairwise merge of two (count, mean, M2) summaries; (n == 0) entries are neutral.
+__device__ __forceinline__ void chan_merge(float& n, float& mean, float& m2,
+                                           float n2, float mean2, float m22) {
+    if (n2 <= 0.f) return;
+    const float tot = n + n2;
+    const float f = n2 / tot;
+    const float delta = mean2 - mean;
+    mean = fmaf(delta, f, mean);
+    m2 = m2 + m22 + delta * delta * n * f;
+    n = tot;
+}
+
+}  // namespace scb
+
+// dtype dispatch: binds `T` inside the lambda-like body
+#define SCB_DISPATCH_FLOAT(dtype, T, ...)                                              \
+    switch (dtype) {                                                                   \
+        case SCB_F32: { using T = float; __VA_ARGS__; break; }                         \
+        case SCB_BF16: { using T = __nv_bfloat16; __VA_ARGS__; break; }                \
+        case SCB_F16: { using T = __half; __VA_ARGS__; break; }                        \
+        default: scb::set_error("unsupported dtype code %d", (int)(dtype)); return SCB_ERR_ARG; \
+    }

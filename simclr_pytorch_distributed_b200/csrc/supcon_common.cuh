@@ -1,0 +1,51 @@
+// Row bookkeeping shared by the loss engines.
+#pragma once
+#include "common.cuh"
+
+namespace scb {
+
+// row = q*(V*seg) + v*seg + b ; sample id = q*seg + b   (include/simclr_b200.h, "Row order")
+struct RowMap {
+    int vseg;   // V * seg
+    int seg;
+    __host__ __device__ static RowMap of(const scb_supcon_problem* p) {
+        RowMap m; m.vseg = p->n_views * p->seg; m.seg = p->seg; return m;
+    }
+    __device__ __forceinline__ int sid(int row) const {
+        const int q = row / vseg, rem = row - q * vseg;
+        return q * seg + rem % seg;
+    }
+    // anchors: every row (`all`) or the view-0 rows (`one`)            losses.py:54-59
+    __device__ __forceinline__ bool is_anchor(int row, int mode) const {
+        return mode == SCB_MODE_ALL || (row % vseg) < seg;
+    }
+};
+
+// base mask m[sid_i, sid_j] before the self-contrast column is removed      losses.py:39-50
+struct MaskSpec {
+    const int64_t* labels;
+    const float* mask;
+    int kind;
+    int n_samples;   // n_seg * seg
+    __host__ __device__ static MaskSpec of(const scb_supcon_problem* p) {
+        MaskSpec m; m.labels = p->labels; m.mask = p->mask; m.kind = p->mask_kind;
+        m.n_samples = p->n_seg * p->seg; return m;
+    }
+    __device__ __forceinline__ float value(int sid_i, int sid_j) const {
+        if (kind == SCB_MASK_SIMCLR) return sid_i == sid_j ? 1.f : 0.f;
+        if (kind == SCB_MASK_LABELS) return labels[sid_i] == labels[sid_j] ? 1.f : 0.f;
+        return mask[(int64_t)sid_i * n_samples + sid_j];
+    }
+};
+
+// engines (supcon_generic.cu / supcon_tc.cu)
+int fp32_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* part, int n_split,
+                 cudaStream_t stream);
+int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
+                  const float* npos_all, const float* grad_out, int n_anchor_total, float* out_dk,
+                  int ld_dk, cudaStream_t stream);
+int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int row_begin,
+                    int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
+                    float* out_loss_sum, cudaStream_t stream);
+
+}  // namespace scb

@@ -1,0 +1,307 @@
+// SupCon / NT-Xent loss: layout kernels shared by every engine (prep, finalize, finish) and the
+// fp32 SIMT engine (SCB_ENGINE_FP32): the exact-arithmetic path that accepts any feature length
+// and any mask (user [B,B] float masks included).  The tensor-core engine lives in supcon_tc.cu.
+//
+// Reference being replaced: /root/reference/losses.py:52-91 and its autograd backward; closed
+// form in SURVEY.md Appendix A.  Nothing of size [A, n_k] is ever written to memory.
+#include "common.cuh"
+#include "supcon_common.cuh"
+
+namespace scb {
+
+// ------------------------------------------------------------------ prep (normalise + stack + cast)
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256)
+supcon_prep_kernel(const TI* __restrict__ feat, int n_samples, int n_views, int dim,
+                   int64_t stride_s, int64_t stride_v, int normalize, float eps,
+                   TO* __restrict__ out_k, __nv_bfloat16* __restrict__ out_lo, int ldk,
+                   float* __restrict__ out_inv_norm) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int n_rows = n_samples * n_views;
+    if (warp >= n_rows) return;
+    const int v = warp / n_samples, b = warp - v * n_samples;     // out row = v*n_samples + b
+    const TI* src = feat + (int64_t)b * stride_s + (int64_t)v * stride_v;
+    float inv = 1.f;
+    if (normalize) {
+        float ss = 0.f;
+        for (int d = lane; d < dim; d += 32) { const float x = to_f32(src[d]); ss = fmaf(x, x, ss); }
+        ss = warp_sum(ss);
+        inv = 1.f / fmaxf(sqrtf(ss), eps);                         // F.normalize: x / max(||x||, eps)
+    }
+    if (lane == 0 && out_inv_norm) out_inv_norm[warp] = inv;
+    TO* dst = out_k + (int64_t)warp * ldk;
+    for (int d = lane; d < ldk; d += 32) {
+        const float x = d < dim ? to_f32(src[d]) * inv : 0.f;
+        const TO hi = from_f32<TO>(x);
+        dst[d] = hi;
+        if (out_lo) out_lo[(int64_t)warp * ldk + d] = __float2bfloat16_rn(x - to_f32(hi));
+    }
+}
+
+// ------------------------------------------------------------------ finish (un-stack + normalise bwd)
+template <typename TF>
+__global__ void __launch_bounds__(256)
+supcon_finish_kernel(const float* __restrict__ dk, int ld_dk, const TF* __restrict__ feat,
+                     int n_samples, int n_views, int dim, int64_t stride_s, int64_t stride_v,
+                     int normalize, const float* __restrict__ inv_norm, TF* __restrict__ out,
+                     int64_t ostride_s, int64_t ostride_v) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int n_rows = n_samples * n_views;
+    if (warp >= n_rows) return;
+    const int v = warp / n_samples, b = warp - v * n_samples;
+    const float* g = dk + (int64_t)warp * ld_dk;
+    TF* dst = out + (int64_t)b * ostride_s + (int64_t)v * ostride_v;
+    if (!normalize) {
+        for (int d = lane; d < dim; d += 32) dst[d] = from_f32<TF>(g[d]);
+        return;
+    }
+    const TF* src = feat + (int64_t)b * stride_s + (int64_t)v * stride_v;
+    const float inv = inv_norm[warp];
+    float dot = 0.f;
+    for (int d = lane; d < dim; d += 32) dot = fmaf(g[d], to_f32(src[d]) * inv, dot);
+    dot = warp_sum(dot);
+    for (int d = lane; d < dim; d += 32) {
+        const float zh = to_f32(src[d]) * inv;
+        dst[d] = from_f32<TF>((g[d] - zh * dot) * inv);
+    }
+}
+
+// ------------------------------------------------------------------ finalize (merge column splits)
+// partials: [n_split][4][n_rows] = (running max m, sum exp(s - m), possum, npos) per local row.
+// One CTA, fixed summation order -> deterministic loss.
+__global__ void __launch_bounds__(1024)
+supcon_finalize_kernel(const float* __restrict__ part, int n_split, int n_rows, int row_begin,
+                       RowMap map, int mode, float loss_scale, double inv_anchors,
+                       float* __restrict__ out_lse,
+                       float* __restrict__ out_possum, float* __restrict__ out_npos,
+                       float* __restrict__ out_loss_sum) {
+    __shared__ double red[32];
+    double local = 0.0;
+    for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
+        float lse = 0.f, ps = 0.f, np = 1.f;
+        if (map.is_anchor(row_begin + r, mode)) {
+            float m = -INFINITY;
+            for (int s = 0; s < n_split; ++s) m = fmaxf(m, part[((int64_t)s * 4 + 0) * n_rows + r]);
+            float sum = 0.f; ps = 0.f; np = 0.f;
+            for (int s = 0; s < n_split; ++s) {
+                const float ms = part[((int64_t)s * 4 + 0) * n_rows + r];
+                if (ms > -INFINITY) sum += part[((int64_t)s * 4 + 1) * n_rows + r] * expf(ms - m);
+                ps += part[((int64_t)s * 4 + 2) * n_rows + r];
+                np += part[((int64_t)s * 4 + 3) * n_rows + r];
+            }
+            lse = m + logf(sum);
+            local += (double)(-loss_scale * (ps / np - lse));        // losses.py:87,90 (0/0 -> nan)
+        }
+        out_lse[r] = lse; out_possum[r] = ps; out_npos[r] = np;
+    }
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = local;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (threadIdx.x == 0) out_loss_sum[0] = (float)(t * inv_anchors);
+    }
+}
+
+// ------------------------------------------------------------------ fp32 engine: forward
+// CTA = 32 local rows x a strided set of 32-column tiles; warp ty owns row ty, lane tx a column.
+__global__ void __launch_bounds__(1024)
+supcon_fwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, RowMap map,
+                       MaskSpec msk, int mode, float inv_T, int row_begin, int n_rows,
+                       float* __restrict__ part) {
+    __shared__ float xs[32][33], ys[32][33];
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int i = row_begin + blockIdx.x * 32 + ty;
+    const bool row_ok = (blockIdx.x * 32 + ty) < n_rows && map.is_anchor(i, mode);
+    const int sid_i = map.sid(i < n_k ? i : 0);
+    float m = -INFINITY, sum = 0.f, possum = 0.f, npos = 0.f;
+    const int n_tiles = (n_k + 31) / 32;
+    for (int ct = blockIdx.y; ct < n_tiles; ct += gridDim.y) {
+        const int j0 = ct * 32;
+        float acc = 0.f;
+        for (int d0 = 0; d0 < dim; d0 += 32) {
+            const int d = d0 + tx;
+            const int ri = row_begin + blockIdx.x * 32 + ty, rj = j0 + ty;
+            xs[ty][tx] = (ri < n_k && d < dim) ? K[(int64_t)ri * ldk + d] : 0.f;
+            ys[ty][tx] = (rj < n_k && d < dim) ? K[(int64_t)rj * ldk + d] : 0.f;
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 32; ++k) acc = fmaf(xs[ty][k], ys[tx][k], acc);
+            __syncthreads();
+        }
+        const int j = j0 + tx;
+        const bool ok = row_ok && j < n_k && j != i;
+        const float s = acc * inv_T;
+        const float mv = ok ? msk.value(sid_i, map.sid(j < n_k ? j : 0)) : 0.f;
+        const float tm = warp_max(ok ? s : -INFINITY);
+        if (tm > -INFINITY) {
+            const float nm = fmaxf(m, tm);
+            const float e = ok ? expf(s - nm) : 0.f;
+            sum = sum * (m > -INFINITY ? expf(m - nm) : 0.f) + warp_sum(e);
+            m = nm;
+        }
+        possum += warp_sum(mv * (ok ? s : 0.f));
+        npos += warp_sum(mv);
+    }
+    const int r = blockIdx.x * 32 + ty;
+    if (tx == 0 && r < n_rows) {
+        const int64_t base = (int64_t)blockIdx.y * 4 * n_rows + r;
+        part[base] = m;
+        part[base + n_rows] = sum;
+        part[base + 2 * (int64_t)n_rows] = possum;
+        part[base + 3 * (int64_t)n_rows] = npos;
+    }
+}
+
+// ------------------------------------------------------------------ fp32 engine: backward
+// H_ij = [i anchor] G_ij + [j anchor] G_ji, dK_i = (1/T) sum_j H_ij k_j; each CTA owns 32 local
+// rows and a 128-wide slice of the feature axis (blockIdx.z), so there are no atomics.
+__global__ void __launch_bounds__(1024)
+supcon_bwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, RowMap map,
+                       MaskSpec msk, int mode, float inv_T, float coef_scale,
+                       const float* __restrict__ grad_out, int row_begin, int n_rows,
+                       const float* __restrict__ lse_all, const float* __restrict__ npos_all,
+                       float* __restrict__ out_dk, int ld_dk) {
+    __shared__ float xs[32][33], ys[32][33], hs[32][33];
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int r = blockIdx.x * 32 + ty;
+    const int i = row_begin + r;
+    const bool row_ok = r < n_rows;
+    const bool anchor_i = row_ok && map.is_anchor(i, mode);
+    const int sid_i = map.sid(i < n_k ? i : 0);
+    const float lse_i = anchor_i ? lse_all[i] : 0.f;
+    const float inv_np_i = anchor_i ? 1.f / npos_all[i] : 0.f;
+    const float coef = grad_out[0] * coef_scale;
+    const int dbeg = blockIdx.z * 128;
+    float accd[4] = {0.f, 0.f, 0.f, 0.f};
+    const int n_tiles = (n_k + 31) / 32;
+    for (int ct = 0; ct < n_tiles; ++ct) {
+        const int j0 = ct * 32;
+        float acc = 0.f;
+        for (int d0 = 0; d0 < dim; d0 += 32) {
+            const int d = d0 + tx;
+            const int rj = j0 + ty;
+            xs[ty][tx] = (i < n_k && row_ok && d < dim) ? K[(int64_t)i * ldk + d] : 0.f;
+            ys[ty][tx] = (rj < n_k && d < dim) ? K[(int64_t)rj * ldk + d] : 0.f;
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 32; ++k) acc = fmaf(xs[ty][k], ys[tx][k], acc);
+            __syncthreads();
+        }
+        const int j = j0 + tx;
+        float h = 0.f;
+        if (row_ok && j < n_k && j != i) {
+            const float s = acc * inv_T;
+            const int sid_j = map.sid(j);
+            if (anchor_i) h += expf(s - lse_i) - msk.value(sid_i, sid_j) * inv_np_i;
+            if (map.is_anchor(j, mode)) h += expf(s - lse_all[j]) - msk.value(sid_j, sid_i) / npos_all[j];
+            h *= coef * inv_T;
+        }
+        hs[ty][tx] = h;
+        __syncthreads();
+        const int jn = min(32, n_k - j0);
+        for (int c = 0; c < jn; ++c) {
+            const float hv = hs[ty][c];
+            const float* kj = K + (int64_t)(j0 + c) * ldk + dbeg + tx;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (dbeg + tx + 32 * k < dim) accd[k] = fmaf(hv, kj[32 * k], accd[k]);
+        }
+        __syncthreads();
+    }
+    if (row_ok) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int d = dbeg + tx + 32 * k;
+            if (d < dim) out_dk[(int64_t)r * ld_dk + d] = accd[k];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ host side
+int fp32_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* part, int n_split,
+                 cudaStream_t stream) {
+    dim3 grid((unsigned)ceil_div(n_rows, 32), (unsigned)n_split), block(32, 32);
+    supcon_fwd_fp32_kernel<<<grid, block, 0, stream>>>(
+        (const float*)p->k, p->ldk, p->dim, p->n_k, RowMap::of(p), MaskSpec::of(p), p->mode,
+        p->inv_temperature, row_begin, n_rows, part);
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
+                  const float* npos_all, const float* grad_out, int n_anchor_total, float* out_dk,
+                  int ld_dk, cudaStream_t stream) {
+    dim3 grid((unsigned)ceil_div(n_rows, 32), 1, (unsigned)ceil_div(p->dim, 128)), block(32, 32);
+    supcon_bwd_fp32_kernel<<<grid, block, 0, stream>>>(
+        (const float*)p->k, p->ldk, p->dim, p->n_k, RowMap::of(p), MaskSpec::of(p), p->mode,
+        p->inv_temperature, p->loss_scale / (float)n_anchor_total, grad_out, row_begin, n_rows,
+        lse_all, npos_all, out_dk, ld_dk);
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int row_begin,
+                    int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
+                    float* out_loss_sum, cudaStream_t stream) {
+    supcon_finalize_kernel<<<1, 1024, 0, stream>>>(part, n_split, n_rows, row_begin, RowMap::of(p),
+                                                   p->mode, p->loss_scale, inv_anchors, out_lse, out_possum,
+                                                   out_npos, out_loss_sum);
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+}  // namespace scb
+
+using namespace scb;
+
+extern "C" int scb_supcon_prep(const void* features, int feat_dtype, int n_samples, int n_views,
+                               int dim, int64_t stride_sample, int64_t stride_view, int normalize,
+                               float eps, void* out_k, void* out_k_lo, int k_dtype, int ldk,
+                               float* out_inv_norm, void* stream_) {
+    SCB_REQUIRE(features && out_k, "supcon_prep: null pointer");
+    SCB_REQUIRE(n_samples > 0 && n_views > 0 && dim > 0 && ldk >= dim, "supcon_prep: bad shape");
+    SCB_REQUIRE(k_dtype == SCB_F32 || k_dtype == SCB_BF16, "supcon_prep: k_dtype must be F32 or BF16");
+    SCB_REQUIRE(out_k_lo == nullptr || k_dtype == SCB_BF16, "supcon_prep: k_lo needs a BF16 k");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int64_t rows = (int64_t)n_samples * n_views;
+    const unsigned blocks = (unsigned)ceil_div(rows * 32, 256);
+    SCB_DISPATCH_FLOAT(feat_dtype, TI, {
+        if (k_dtype == SCB_F32)
+            supcon_prep_kernel<TI, float><<<blocks, 256, 0, stream>>>(
+                (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize, eps,
+                (float*)out_k, nullptr, ldk, out_inv_norm);
+        else
+            supcon_prep_kernel<TI, __nv_bfloat16><<<blocks, 256, 0, stream>>>(
+                (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize, eps,
+                (__nv_bfloat16*)out_k, (__nv_bfloat16*)out_k_lo, ldk, out_inv_norm);
+    });
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_supcon_finish(const float* dk, int ld_dk, const void* features, int feat_dtype,
+                                 int n_samples, int n_views, int dim, int64_t stride_sample,
+                                 int64_t stride_view, int normalize, const float* inv_norm,
+                                 void* out_dfeatures, int64_t out_stride_sample,
+                                 int64_t out_stride_view, void* stream_) {
+    SCB_REQUIRE(dk && out_dfeatures, "supcon_finish: null pointer");
+    SCB_REQUIRE(!normalize || (features && inv_norm), "supcon_finish: normalize needs features and inv_norm");
+    SCB_REQUIRE(n_samples > 0 && n_views > 0 && dim > 0 && ld_dk >= dim, "supcon_finish: bad shape");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int64_t rows = (int64_t)n_samples * n_views;
+    const unsigned blocks = (unsigned)ceil_div(rows * 32, 256);
+    SCB_DISPATCH_FLOAT(feat_dtype, TF, {
+        supcon_finish_kernel<TF><<<blocks, 256, 0, stream>>>(
+            dk, ld_dk, (const TF*)features, n_samples, n_views, dim, stride_sample, stride_view,
+            normalize, inv_norm, (TF*)out_dfeatures, out_stride_sample, out_stride_view);
+    });
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}

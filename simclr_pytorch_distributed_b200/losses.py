@@ -1,0 +1,237 @@
+"""`SupConLoss` -- drop-in for /root/reference/losses.py:7-93 on a B200.
+
+Same constructor, same `forward(features, labels=None, mask=None)`, same `ValueError`s, same
+value and gradient; the arithmetic runs in hand-written sm_100a kernels behind the C ABI of
+include/simclr_b200.h and never materialises the [A, V*B] similarity matrix.  CUDA tensors
+only: there is no CPU path (the reference's own code is the CPU path).
+
+Extras (all default to the reference's behaviour):
+  engine     'auto' | 'fp32' | 'bf16' | 'bf16x3'   arithmetic of the similarity tiles
+  normalize  fuse `F.normalize(features, dim=-1)` (main_supcon.py:283) into the kernels
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+_ENGINES = {'fp32': _lib.ENGINE_FP32, 'bf16': _lib.ENGINE_BF16, 'bf16x3': _lib.ENGINE_BF16X3}
+
+
+def _round_up(x, m):
+    return (x + m - 1) // m * m
+
+
+class _Workspace:
+    """Zero-initialised scratch per (device, stream); kernels leave it zeroed (include/simclr_b200.h)."""
+    _cache = {}
+
+    @classmethod
+    def get(cls, device, nbytes):
+        key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+        buf = cls._cache.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.zeros(_round_up(max(nbytes, 1 << 16), 256), dtype=torch.uint8, device=device)
+            cls._cache[key] = buf
+        return buf
+
+
+def tc_engine_supported(dim, mask_kind, n_k):
+    """Shapes the tcgen05 engine takes; everything else runs on the fp32 engine."""
+    return mask_kind != _lib.MASK_EXPLICIT and dim <= 256 and n_k >= 1
+
+
+def select_engine(requested, feat_dtype, dim, mask_kind, n_k):
+    req = os.environ.get('SIMCLR_B200_LOSS_ENGINE', requested)
+    if req == 'auto':
+        if not tc_engine_supported(dim, mask_kind, n_k):
+            return _lib.ENGINE_FP32
+        return _lib.ENGINE_BF16 if feat_dtype in (torch.bfloat16, torch.float16) else _lib.ENGINE_BF16X3
+    if req not in _ENGINES:
+        raise ValueError('Unknown engine: {}'.format(req))
+    eng = _ENGINES[req]
+    if eng != _lib.ENGINE_FP32 and not tc_engine_supported(dim, mask_kind, n_k):
+        raise ValueError('engine {!r} does not take this problem (dim={}, explicit mask={}); '
+                         'use engine="fp32" or "auto"'.format(req, dim, mask_kind == _lib.MASK_EXPLICIT))
+    return eng
+
+
+class LossPlan:
+    """Shape bookkeeping for one call: where the local rows sit in the (possibly gathered)
+    contrast matrix.  Row order is documented in include/simclr_b200.h."""
+
+    def __init__(self, n_local, n_views, dim, n_seg=1, seg_index=0, mode=_lib.MODE_ALL,
+                 mask_kind=_lib.MASK_SIMCLR, engine=_lib.ENGINE_FP32):
+        self.n_local, self.n_views, self.dim = n_local, n_views, dim
+        self.n_seg, self.seg_index = n_seg, seg_index
+        self.mode, self.mask_kind, self.engine = mode, mask_kind, engine
+        self.rows_local = n_views * n_local
+        self.n_k = n_seg * self.rows_local
+        self.row_begin = seg_index * self.rows_local
+        self.n_anchor_total = self.n_k if mode == _lib.MODE_ALL else n_seg * n_local
+        if engine == _lib.ENGINE_FP32:
+            self.k_dtype, self.k_torch, self.ldk = _lib.F32, torch.float32, _round_up(dim, 4)
+        else:
+            self.k_dtype, self.k_torch, self.ldk = _lib.BF16, torch.bfloat16, _round_up(dim, 64)
+
+
+def _problem(plan, k, k_lo, labels, mask, temperature, base_temperature):
+    p = _lib.SupconProblem()
+    p.k = k.data_ptr()
+    p.k_lo = k_lo.data_ptr() if k_lo is not None else None
+    p.labels = labels.data_ptr() if labels is not None else None
+    p.mask = mask.data_ptr() if mask is not None else None
+    p.k_dtype, p.n_k, p.dim, p.ldk = plan.k_dtype, plan.n_k, plan.dim, plan.ldk
+    p.n_views, p.seg, p.n_seg = plan.n_views, plan.n_local, plan.n_seg
+    p.mask_kind, p.mode, p.engine = plan.mask_kind, plan.mode, plan.engine
+    p.inv_temperature = 1.0 / temperature
+    p.loss_scale = temperature / base_temperature
+    return p
+
+
+def _stream(device):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def launch_prep(lib, feats, plan, normalize, k_rows, k_lo_rows, inv_norm):
+    """feats [n_local, V, D] (last dim contiguous) -> rows of the contrast matrix (scb_supcon_prep)."""
+    _lib.check(lib.scb_supcon_prep(
+        feats.data_ptr(), _lib.dtype_code(feats.dtype), plan.n_local, plan.n_views, plan.dim,
+        feats.stride(0), feats.stride(1), int(normalize), 1e-12,
+        k_rows.data_ptr(), k_lo_rows.data_ptr() if k_lo_rows is not None else None,
+        plan.k_dtype, plan.ldk, inv_norm.data_ptr() if inv_norm is not None else None,
+        _stream(feats.device)), 'scb_supcon_prep')
+
+
+def launch_forward(lib, prob, plan, lse, possum, npos, loss, device):
+    need = lib.scb_supcon_workspace_bytes(ctypes.byref(prob), plan.rows_local)
+    ws = _Workspace.get(device, need)
+    _lib.check(lib.scb_supcon_forward(
+        ctypes.byref(prob), plan.row_begin, plan.rows_local, plan.n_anchor_total,
+        lse.data_ptr(), possum.data_ptr(), npos.data_ptr(), loss.data_ptr(),
+        ws.data_ptr(), ws.numel(), _stream(device)), 'scb_supcon_forward')
+
+
+def launch_backward(lib, prob, plan, lse_all, npos_all, grad_out, dk, device):
+    need = lib.scb_supcon_workspace_bytes(ctypes.byref(prob), plan.rows_local)
+    ws = _Workspace.get(device, need)
+    _lib.check(lib.scb_supcon_backward(
+        ctypes.byref(prob), plan.row_begin, plan.rows_local, lse_all.data_ptr(), npos_all.data_ptr(),
+        grad_out.data_ptr(), plan.n_anchor_total, dk.data_ptr(), dk.stride(0),
+        ws.data_ptr(), ws.numel(), _stream(device)), 'scb_supcon_backward')
+
+
+def launch_finish(lib, dk, feats, plan, normalize, inv_norm, dfeats):
+    _lib.check(lib.scb_supcon_finish(
+        dk.data_ptr(), dk.stride(0), feats.data_ptr(), _lib.dtype_code(feats.dtype),
+        plan.n_local, plan.n_views, plan.dim, feats.stride(0), feats.stride(1), int(normalize),
+        inv_norm.data_ptr() if inv_norm is not None else None,
+        dfeats.data_ptr(), dfeats.stride(0), dfeats.stride(1), _stream(feats.device)),
+        'scb_supcon_finish')
+
+
+class _SupConFunction(torch.autograd.Function):
+    """Single-GPU loss: prep -> forward -> (backward -> finish).  losses.py:52-91 + autograd."""
+
+    @staticmethod
+    def forward(ctx, feats, labels, mask, plan, temperature, base_temperature, normalize):
+        lib = _lib.load()
+        dev = feats.device
+        with torch.cuda.device(dev):
+            n_k, ldk = plan.n_k, plan.ldk
+            k = torch.empty((n_k, ldk), dtype=plan.k_torch, device=dev)
+            k_lo = torch.empty_like(k) if plan.engine == _lib.ENGINE_BF16X3 else None
+            stats = torch.empty((4, n_k), dtype=torch.float32, device=dev)   # lse, possum, npos, inv_norm
+            loss = torch.empty((), dtype=torch.float32, device=dev)
+            inv_norm = stats[3] if normalize else None
+            launch_prep(lib, feats, plan, normalize, k, k_lo, inv_norm)
+            prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
+            launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
+        ctx.plan, ctx.prob_args = plan, (temperature, base_temperature, normalize)
+        ctx.save_for_backward(feats, labels, mask, k, k_lo, stats)
+        return loss.to(feats.dtype) if feats.dtype != torch.float32 else loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        feats, labels, mask, k, k_lo, stats = ctx.saved_tensors
+        plan = ctx.plan
+        temperature, base_temperature, normalize = ctx.prob_args
+        lib = _lib.load()
+        dev = feats.device
+        with torch.cuda.device(dev):
+            g = grad_out.detach().to(torch.float32).contiguous()
+            dk = torch.empty((plan.rows_local, plan.dim), dtype=torch.float32, device=dev)
+            prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
+            launch_backward(lib, prob, plan, stats[0], stats[2], g, dk, dev)
+            dfeats = torch.empty(feats.shape, dtype=feats.dtype, device=dev)
+            launch_finish(lib, dk, feats, plan, normalize, stats[3] if normalize else None, dfeats)
+        return dfeats, None, None, None, None, None, None
+
+
+def validate_inputs(features, labels, mask, contrast_mode):
+    """The reference's argument checks, in its order, with its messages (losses.py:33-61)."""
+    if len(features.shape) < 3:
+        raise ValueError('`features` needs to be [bsz, n_views, ...],'
+                         'at least 3 dimensions are required')
+    batch_size = features.shape[0]
+    if labels is not None and mask is not None:
+        raise ValueError('Cannot define both `labels` and `mask`')
+    if labels is not None:
+        labels = labels.contiguous().view(-1)
+        if labels.shape[0] != batch_size:
+            raise ValueError('Num of labels does not match num of features')
+    if contrast_mode == 'one':
+        mode = _lib.MODE_ONE
+    elif contrast_mode == 'all':
+        mode = _lib.MODE_ALL
+    else:
+        raise ValueError('Unknown mode: {}'.format(contrast_mode))
+    return labels, mode
+
+
+class SupConLoss(nn.Module):
+    """Supervised contrastive loss; SimCLR's NT-Xent when `labels` and `mask` are both None.
+
+    Mirrors /root/reference/losses.py:7-93 (constructor :10-15, forward :17-93).
+    """
+
+    def __init__(self, temperature=0.07, contrast_mode='all', base_temperature=0.07,
+                 engine='auto', normalize=False):
+        super(SupConLoss, self).__init__()
+        self.temperature = temperature
+        self.contrast_mode = contrast_mode
+        self.base_temperature = base_temperature
+        self.engine = engine
+        self.normalize = normalize
+
+    def forward(self, features, labels=None, mask=None):
+        """features [bsz, n_views, ...]; labels [bsz]; mask [bsz, bsz] (float, may be asymmetric).
+        Returns the 0-dim loss, differentiable with respect to `features`."""
+        labels, mode = validate_inputs(features, labels, mask, self.contrast_mode)
+        if not features.is_cuda:
+            raise RuntimeError('simclr_pytorch_distributed_b200.SupConLoss runs on CUDA tensors only '
+                               '(there is no CPU fallback); got a %s tensor' % features.device.type)
+        if len(features.shape) > 3:
+            features = features.view(features.shape[0], features.shape[1], -1)     # losses.py:36-37
+        if features.stride(2) != 1 and features.shape[2] > 1:
+            features = features.contiguous()
+        B, V, D = features.shape
+        dev = features.device
+        if labels is not None:
+            mask_kind = _lib.MASK_LABELS
+            labels = labels.to(device=dev, dtype=torch.int64)
+        elif mask is not None:
+            mask_kind = _lib.MASK_EXPLICIT
+            mask = mask.to(device=dev, dtype=torch.float32).contiguous()            # losses.py:50
+            if mask.shape != (B, B):
+                raise ValueError('`mask` must be [bsz, bsz]')
+        else:
+            mask_kind = _lib.MASK_SIMCLR
+        engine = select_engine(self.engine, features.dtype, D, mask_kind, V * B)
+        plan = LossPlan(B, V, D, mode=mode, mask_kind=mask_kind, engine=engine)
+        return _SupConFunction.apply(features, labels, mask, plan, float(self.temperature),
+                                     float(self.base_temperature), bool(self.normalize))

@@ -1,0 +1,279 @@
+"""`SyncBatchNorm` -- drop-in for the `torch.nn.SyncBatchNorm` layers that the reference's
+`--syncBN` flag swaps into the network (/root/reference/main_supcon.py:69-70,222-224; BN sites
+/root/reference/networks/resnet_big.py:14,16,22,44,46,48,54,77).
+
+Same constructor, parameters, buffers and state-dict keys as `torch.nn.SyncBatchNorm`
+(torch/nn/modules/batchnorm.py:718-733) and the same `convert_sync_batchnorm` classmethod
+(:844-905); the arithmetic (torch/nn/modules/_functions.py:10-209) runs in the sm_100a kernels of
+csrc/bn.cu through the C ABI.  Per layer and pass: one streaming reduction, one tiny NCCL
+exchange (only when world_size > 1) and one fused apply -- and no host synchronisation (stock
+SyncBatchNorm forces one per layer, _functions.py:88-100).
+
+CUDA tensors only; there is no CPU path.  `fuse_relu=True` additionally applies ReLU inside the
+apply kernels (the `relu(bn(x))` sites of resnet_big.py:26,58,59,111).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+from torch.nn.modules.batchnorm import _BatchNorm
+
+from . import _lib
+
+
+class _Kernels:
+    """Thin typed wrappers over the C ABI (one per entry point of include/simclr_b200.h)."""
+
+    _ws = {}
+
+    @classmethod
+    def workspace(cls, lib, device, channels):
+        key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+        need = lib.scb_bn_workspace_bytes(channels)
+        buf = cls._ws.get(key)
+        if buf is None or buf.numel() < need:
+            buf = torch.zeros(max(need, 1 << 16), dtype=torch.uint8, device=device)
+            cls._ws[key] = buf
+        return buf
+
+    @staticmethod
+    def stream(device):
+        return torch.cuda.current_stream(device).cuda_stream
+
+    @classmethod
+    def stats(cls, x, geom, out_stats):
+        lib = _lib.load()
+        cl, outer, C, inner = geom
+        ws = cls.workspace(lib, x.device, C)
+        _lib.check(lib.scb_bn_stats(x.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C, inner,
+                                    out_stats.data_ptr(), ws.data_ptr(), ws.numel(),
+                                    cls.stream(x.device)), 'scb_bn_stats')
+
+    @classmethod
+    def apply(cls, x, y, geom, stats_all, n_ranks, weight, bias, running_mean, running_var,
+              momentum, eps, saved, flags):
+        lib = _lib.load()
+        cl, outer, C, inner = geom
+        p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        sm = saved[0:C] if saved is not None else None
+        si = saved[C:2 * C] if saved is not None else None
+        sc = saved[2 * C:] if saved is not None else None
+        _lib.check(lib.scb_bn_apply(x.data_ptr(), y.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C,
+                                    inner, p(stats_all), n_ranks, p(weight), p(bias), p(running_mean),
+                                    p(running_var), momentum, eps, p(sm), p(si), p(sc), flags,
+                                    cls.stream(x.device)), 'scb_bn_apply')
+
+    @classmethod
+    def backward_reduce(cls, dy, x, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags):
+        lib = _lib.load()
+        cl, outer, C, inner = geom
+        p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        ws = cls.workspace(lib, x.device, C)
+        _lib.check(lib.scb_bn_backward_reduce(
+            dy.data_ptr(), x.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C, inner,
+            saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), sums.data_ptr(),
+            p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(), cls.stream(x.device)),
+            'scb_bn_backward_reduce')
+
+    @classmethod
+    def backward_apply(cls, dy, x, dx, geom, saved, weight, bias, sums, flags):
+        lib = _lib.load()
+        cl, outer, C, inner = geom
+        p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        _lib.check(lib.scb_bn_backward_apply(
+            dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C, inner,
+            saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), sums.data_ptr(),
+            saved[2 * C:].data_ptr(), flags, cls.stream(x.device)), 'scb_bn_backward_apply')
+
+
+def _is_channels_last(x):
+    return ((x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last)) or
+            (x.dim() == 5 and x.is_contiguous(memory_format=torch.channels_last_3d)))
+
+
+def _layout(x):
+    """Return (tensor in a supported layout, (channels_last, outer, C, inner)) -- the same
+    "keep channels_last, else make contiguous" rule as _functions.py:22-26."""
+    C = x.size(1)
+    if x.dim() == 2:
+        x = x.contiguous()
+        return x, (1, x.size(0), C, 1)                 # [N, C] is already "rows x channels"
+    if _is_channels_last(x):
+        return x, (1, x.numel() // C if C else 0, C, 1)
+    x = x.contiguous()
+    inner = x.numel() // (x.size(0) * C) if x.size(0) * C else 1
+    return x, (0, x.size(0), C, max(inner, 1))
+
+
+def _match_layout(t, like, geom):
+    """grad_output in the same memory layout as the saved input (_functions.py:129-133)."""
+    if geom[0] == 1 and like.dim() == 4:
+        return t.contiguous(memory_format=torch.channels_last)
+    if geom[0] == 1 and like.dim() == 5:
+        return t.contiguous(memory_format=torch.channels_last_3d)
+    return t.contiguous()
+
+
+def _f32(t):
+    return t if t is None or t.dtype == torch.float32 else t.float()
+
+
+class _SyncBNFunction(torch.autograd.Function):
+    """Training-mode forward/backward: _functions.py:10-209 on the sm_100a kernels."""
+
+    kernels = _Kernels      # tests swap this for an oracle-backed stand-in to check the host logic
+
+    @staticmethod
+    def forward(ctx, input, weight, bias, running_mean, running_var, eps, momentum, process_group,
+                world_size, fuse_relu, use_batch_stats):
+        kern = _SyncBNFunction.kernels
+        x, geom = _layout(input)
+        C = geom[2]
+        size = int(x.numel() // C)
+        if use_batch_stats and size == 1 and world_size < 2:
+            raise ValueError(f"Expected more than 1 value per channel when training, got input size {size}")
+        w32, b32 = _f32(weight), _f32(bias)
+        rm, rv = _f32(running_mean), _f32(running_var)
+        dev = x.device
+        if not use_batch_stats:
+            stats_all = None            # eval: the running statistics are the statistics
+        else:
+            # message of this rank: [mean(C), M2(C), count]  (_functions.py:41-49 sends mean, invstd, count)
+            stats = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
+            kern.stats(x, geom, stats)
+        if not use_batch_stats:
+            pass
+        elif world_size > 1:
+            stats_all = torch.empty(world_size * (2 * C + 1), dtype=torch.float32, device=dev)
+            if process_group._get_backend_name() != 'gloo':
+                dist.all_gather_into_tensor(stats_all, stats, process_group, async_op=False)
+            else:                                            # gloo has no all_gather_into_tensor
+                parts = [torch.empty_like(stats) for _ in range(world_size)]
+                dist.all_gather(parts, stats, process_group, async_op=False)
+                stats_all = torch.cat(parts)
+        else:
+            stats_all = stats
+        y = torch.empty_like(x)
+        saved = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)     # mean, invstd, n_total
+        flags = _lib.BN_RELU if fuse_relu else 0
+        kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags)
+        if rm is not running_mean and running_mean is not None:
+            running_mean.copy_(rm)
+        if rv is not running_var and running_var is not None:
+            running_var.copy_(rv)
+        ctx.save_for_backward(x, w32, b32, saved)
+        ctx.geom, ctx.flags, ctx.use_batch_stats = geom, flags, use_batch_stats
+        ctx.process_group, ctx.world_size = process_group, world_size
+        ctx.param_dtypes = (None if weight is None else weight.dtype, None if bias is None else bias.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        kern = _SyncBNFunction.kernels
+        x, w32, b32, saved = ctx.saved_tensors
+        geom, flags = ctx.geom, ctx.flags
+        C = geom[2]
+        dy = _match_layout(grad_output, x, geom)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dev = x.device
+        out = torch.empty(4 * C, dtype=torch.float32, device=dev)           # sums(2C), dgamma, dbeta
+        sums, gw, gb = out[0:2 * C], out[2 * C:3 * C], out[3 * C:]
+        kern.backward_reduce(dy, x, geom, saved, w32, b32, sums, gw, gb, flags)
+        grad_input = None
+        if ctx.needs_input_grad[0]:
+            if not ctx.use_batch_stats:
+                sums = torch.zeros_like(sums)               # eval: statistics do not depend on x
+            elif ctx.world_size > 1:                        # _functions.py:155-165
+                dist.all_reduce(sums, dist.ReduceOp.SUM, ctx.process_group, async_op=False)
+            grad_input = torch.empty_like(x)
+            kern.backward_apply(dy, x, grad_input, geom, saved, w32, b32, sums, flags)
+        wd, bd = ctx.param_dtypes
+        # dgamma / dbeta stay un-synced: DDP averages them (_functions.py:180-181)
+        grad_weight = gw.to(wd) if (w32 is not None and ctx.needs_input_grad[1]) else None
+        grad_bias = gb.to(bd) if (b32 is not None and ctx.needs_input_grad[2]) else None
+        return grad_input, grad_weight, grad_bias, None, None, None, None, None, None, None, None
+
+
+class SyncBatchNorm(_BatchNorm):
+    """Batch normalisation with statistics over the whole (cross-rank) mini-batch.
+
+    Argument meaning, buffers and error behaviour follow `torch.nn.SyncBatchNorm`
+    (torch/nn/modules/batchnorm.py:615-905).  Unlike the stock module it runs the same kernels at
+    world size 1 instead of falling back to cuDNN (:818-828), so one code path serves 1..8 GPUs.
+    """
+
+    def __init__(self, num_features, eps=1e-5, momentum=0.1, affine=True, track_running_stats=True,
+                 process_group=None, device=None, dtype=None, fuse_relu=False):
+        factory_kwargs = {'device': device, 'dtype': dtype}
+        super().__init__(num_features, eps, momentum, affine, track_running_stats, **factory_kwargs)
+        self.process_group = process_group
+        self.fuse_relu = fuse_relu
+
+    def _check_input_dim(self, input):
+        if input.dim() < 2:
+            raise ValueError(f"expected at least 2D input (got {input.dim()}D input)")
+
+    def _check_non_zero_input_channels(self, input):
+        if input.size(1) == 0:
+            raise ValueError("SyncBatchNorm number of input channels should be non-zero")
+
+    def forward(self, input):
+        self._check_input_dim(input)
+        self._check_non_zero_input_channels(input)
+        if input.size(1) != self.num_features:
+            raise ValueError(f"expected {self.num_features} channels, got {input.size(1)}")
+        if not input.is_cuda:
+            raise ValueError("SyncBatchNorm expected input tensor to be on GPU "
+                             "(simclr_pytorch_distributed_b200 has no CPU path)")
+
+        if self.momentum is None:
+            exponential_average_factor = 0.0
+        else:
+            exponential_average_factor = self.momentum
+        if self.training and self.track_running_stats:
+            self.num_batches_tracked.add_(1)
+            if self.momentum is None:                     # cumulative moving average
+                exponential_average_factor = 1.0 / self.num_batches_tracked.item()
+            else:
+                exponential_average_factor = self.momentum
+
+        if self.training:
+            bn_training = True
+        else:
+            bn_training = (self.running_mean is None) and (self.running_var is None)
+        running_mean = self.running_mean if not self.training or self.track_running_stats else None
+        running_var = self.running_var if not self.training or self.track_running_stats else None
+
+        world_size, process_group = 1, None
+        # statistics are exchanged only in training mode (batchnorm.py:791-815)
+        if bn_training and self.training and dist.is_available() and dist.is_initialized():
+            process_group = self.process_group if self.process_group else dist.group.WORLD
+            world_size = dist.get_world_size(process_group)
+        return _SyncBNFunction.apply(input, self.weight, self.bias, running_mean, running_var, self.eps,
+                                     float(exponential_average_factor), process_group, world_size,
+                                     self.fuse_relu, bn_training)
+
+    @classmethod
+    def convert_sync_batchnorm(cls, module, process_group=None):
+        """Replace every `BatchNorm*D` (and stock `torch.nn.SyncBatchNorm`) in `module` by this
+        class, sharing parameters and buffers, so state dicts stay interchangeable
+        (torch/nn/modules/batchnorm.py:844-905; swap site main_supcon.py:224)."""
+        module_output = module
+        if isinstance(module, _BatchNorm) and not isinstance(module, cls):
+            module_output = cls(module.num_features, module.eps, module.momentum, module.affine,
+                                module.track_running_stats, process_group)
+            if module.affine:
+                with torch.no_grad():
+                    module_output.weight = module.weight
+                    module_output.bias = module.bias
+            module_output.running_mean = module.running_mean
+            module_output.running_var = module.running_var
+            module_output.num_batches_tracked = module.num_batches_tracked
+            module_output.training = module.training
+            if hasattr(module, 'qconfig'):
+                module_output.qconfig = module.qconfig
+        for name, child in module.named_children():
+            module_output.add_module(name, cls.convert_sync_batchnorm(child, process_group))
+        del module
+        return module_output

@@ -1,0 +1,310 @@
+"""Parity of the CUDA SyncBatchNorm kernels (through the module and through the raw C ABI) with the
+oracle, the golden vectors, and torch's own batch-norm on the same GPU.  north_star tolerance:
+outputs and gradients within 1e-5 (fp32 quantities); bf16 tensors are compared after the same
+rounding, i.e. to within one bf16 ulp."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import golden
+from oracle import syncbn_forward, syncbn_backward
+from simclr_pytorch_distributed_b200 import SyncBatchNorm, _lib
+from simclr_pytorch_distributed_b200.sync_batchnorm import _Kernels, _layout
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda'
+
+
+def ours_fwd_bwd(x, dy, bn):
+    xd = x.clone().requires_grad_(True)
+    y = bn(xd)
+    y.backward(dy)
+    torch.cuda.synchronize()
+    return y.detach(), xd.grad, bn.weight.grad.clone() if bn.weight is not None else None, \
+        bn.bias.grad.clone() if bn.bias is not None else None
+
+
+def oracle_fwd_bwd(x, dy, bn_state, eps=1e-5, momentum=0.1):
+    w, b, rm, rv = bn_state
+    xs = [x.detach().double().cpu().numpy()]
+    ys, mean, invstd, n, rm1, rv1 = syncbn_forward(xs, w, b, eps, rm, rv, momentum)
+    dxs, gws, gbs, _, _ = syncbn_backward(xs, [dy.double().cpu().numpy()], mean, invstd, w)
+    return ys[0], dxs[0], gws[0], gbs[0], rm1, rv1, mean, invstd
+
+
+def make_bn(C, **kw):
+    bn = SyncBatchNorm(C, **kw).to(DEV)
+    with torch.no_grad():
+        if bn.weight is not None:
+            bn.weight.uniform_(0.5, 1.5)
+            bn.bias.normal_(0, 0.1)
+        if bn.running_mean is not None:
+            bn.running_mean.normal_(0, 0.3)
+            bn.running_var.uniform_(0.5, 2.0)
+    return bn
+
+
+def state(bn):
+    f = lambda t: None if t is None else t.detach().double().cpu().numpy().copy()   # noqa: E731
+    return f(bn.weight), f(bn.bias), f(bn.running_mean), f(bn.running_var)
+
+
+SHAPES = [((256, 256, 8, 8), True), ((32, 64, 32, 32), True), ((16, 2048, 4, 4), True),
+          ((8, 24, 5, 7), True), ((7, 13, 3, 3), True), ((64, 128), False), ((4, 6, 3, 3), False),
+          ((16, 64, 16, 16), False), ((5, 10, 7, 9), False), ((3, 4, 2, 3, 5), False)]
+
+
+@pytest.mark.parametrize('shape,cl', SHAPES)
+def test_fp32_matches_oracle_1e5(shape, cl):
+    torch.manual_seed(sum(shape))
+    C = shape[1]
+    mu = (torch.rand(C) * 4 - 2).view(1, C, *([1] * (len(shape) - 2)))
+    sg = (torch.rand(C) * 1.5 + 0.5).view(1, C, *([1] * (len(shape) - 2)))
+    x = (torch.randn(shape) * sg + mu).to(DEV)
+    dy = torch.randn(shape).to(DEV)
+    if cl:
+        x = x.contiguous(memory_format=torch.channels_last)
+        dy = dy.contiguous(memory_format=torch.channels_last)
+    bn = make_bn(C)
+    st = state(bn)
+    y, dx, gw, gb = ours_fwd_bwd(x, dy, bn)
+    ry, rdx, rgw, rgb, rm1, rv1, _, _ = oracle_fwd_bwd(x, dy, st)
+    assert y.shape == x.shape and y.stride() == x.stride()
+    assert np.abs(y.cpu().numpy() - ry).max() <= 1e-5 * max(1.0, np.abs(ry).max())
+    assert np.abs(dx.cpu().numpy() - rdx).max() <= 1e-5 * max(1.0, np.abs(rdx).max())
+    n = x.numel() // C
+    assert np.abs(gw.cpu().numpy() - rgw).max() <= 1e-5 * max(1.0, np.abs(rgw).max()) * max(1, n ** 0.5 / 8)
+    assert np.abs(gb.cpu().numpy() - rgb).max() <= 1e-5 * max(1.0, np.abs(rgb).max()) * max(1, n ** 0.5 / 8)
+    assert np.abs(bn.running_mean.cpu().numpy() - rm1).max() <= 1e-5
+    assert np.abs(bn.running_var.cpu().numpy() - rv1).max() <= 1e-5 * max(1.0, np.abs(rv1).max())
+    assert int(bn.num_batches_tracked) == 1
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize('shape,cl', SHAPES[:5] + SHAPES[6:8])
+def test_half_precision_io_within_one_ulp(shape, cl, dtype):
+    torch.manual_seed(sum(shape) + 1)
+    C = shape[1]
+    x = (torch.randn(shape) * 1.3 + 0.4).to(DEV, dtype)
+    dy = torch.randn(shape).to(DEV, dtype)
+    if cl:
+        x = x.contiguous(memory_format=torch.channels_last)
+        dy = dy.contiguous(memory_format=torch.channels_last)
+    bn = make_bn(C)
+    st = state(bn)
+    y, dx, gw, gb = ours_fwd_bwd(x, dy, bn)
+    assert y.dtype == dtype and dx.dtype == dtype and gw.dtype == torch.float32
+    ry, rdx, rgw, rgb, rm1, rv1, mean, invstd = oracle_fwd_bwd(x, dy, st)
+    ulp = 2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11
+    assert np.all(np.abs(y.float().cpu().numpy() - ry) <= ulp * np.abs(ry) + 1e-5)
+    assert np.all(np.abs(dx.float().cpu().numpy() - rdx) <= ulp * np.abs(rdx) + 1e-5)
+    # fp32 per-channel quantities keep the 1e-5 bar
+    assert np.abs(bn.running_mean.cpu().numpy() - rm1).max() <= 1e-5
+    assert np.abs(bn.running_var.cpu().numpy() - rv1).max() <= 1e-5 * max(1.0, np.abs(rv1).max())
+    n = x.numel() // C
+    assert np.abs(gb.cpu().numpy() - rgb).max() <= 1e-5 * max(1.0, np.abs(rgb).max()) * max(1, n ** 0.5 / 8)
+
+
+def test_matches_torch_batch_norm_on_gpu():
+    """torch's own kernels on the same device (F.batch_norm == nn.SyncBatchNorm at world size 1,
+    torch/nn/modules/batchnorm.py:818-828)."""
+    torch.manual_seed(11)
+    for shape, cl in SHAPES[:4] + SHAPES[5:8]:
+        C = shape[1]
+        x = (torch.randn(shape, device=DEV) * 2 + 1)
+        dy = torch.randn(shape, device=DEV)
+        if cl:
+            x = x.contiguous(memory_format=torch.channels_last)
+        bn = make_bn(C)
+        ref = torch.nn.BatchNorm2d(C).to(DEV) if len(shape) == 4 else torch.nn.BatchNorm1d(C).to(DEV)
+        ref.load_state_dict(bn.state_dict())
+        y, dx, gw, gb = ours_fwd_bwd(x, dy, bn)
+        xr = x.clone().requires_grad_(True)
+        yr = ref(xr)
+        yr.backward(dy)
+        assert torch.allclose(y, yr, atol=2e-5, rtol=1e-5)
+        assert torch.allclose(dx, xr.grad, atol=2e-5, rtol=1e-5)
+        assert torch.allclose(gw, ref.weight.grad, atol=1e-3, rtol=1e-4)
+        assert torch.allclose(bn.running_var, ref.running_var, atol=1e-5, rtol=1e-5)
+
+
+def test_matches_aten_sync_ops_on_gpu():
+    """The very ops stock SyncBatchNorm calls (_functions.py:39,122,144,170), NHWC bf16 cfg 2."""
+    torch.manual_seed(12)
+    x = (torch.randn(256, 256, 8, 8, device=DEV) * 1.5 + 0.5).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(256, 256, 8, 8, device=DEV).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    bn = make_bn(256)
+    w, b = bn.weight.detach(), bn.bias.detach()
+    mean, invstd = torch.batch_norm_stats(x, 1e-5)
+    y_ref = torch.batch_norm_elemt(x, w, b, mean, invstd, 1e-5)
+    sum_dy, sum_dy_xmu, gw_ref, gb_ref = torch.batch_norm_backward_reduce(dy, x, mean, invstd, w, True, True, True)
+    count = torch.full((1,), x.numel() // 256, dtype=torch.int32, device=DEV)
+    dx_ref = torch.batch_norm_backward_elemt(dy, x, mean, invstd, w, sum_dy, sum_dy_xmu, count)
+    y, dx, gw, gb = ours_fwd_bwd(x, dy, bn)
+    ulp = 2.0 ** -8
+    assert torch.all((y.float() - y_ref.float()).abs() <= ulp * y_ref.float().abs() + 1e-5)
+    assert torch.all((dx.float() - dx_ref.float()).abs() <= ulp * dx_ref.float().abs() + 1e-5)
+    assert torch.allclose(gw, gw_ref, rtol=1e-4, atol=1e-3)
+    assert torch.allclose(gb, gb_ref, rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.parametrize('name', ['bn_w1', 'bn_w2', 'bn_w3_ragged', 'bn_w2_f32'])
+@pytest.mark.parametrize('cl', [False, True])
+def test_golden_multi_rank_arithmetic_through_c_abi(name, cl):
+    """The W-rank exchange emulated on one GPU: each rank's kernels run one after the other, the
+    messages are concatenated as the all-gather would (stats_all [W, 2C+1]) and the 2C sums added
+    as the all-reduce would.  Ragged per-rank counts included (Chan merge with counts)."""
+    g = golden(name)
+    W = len(g['counts'])
+    K = _Kernels
+    f32 = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(DEV, torch.float32)   # noqa: E731
+    xs = [f32(g[f'x{r}']) for r in range(W)]
+    dys = [f32(g[f'dy{r}']) for r in range(W)]
+    if cl:
+        xs = [t.contiguous(memory_format=torch.channels_last) for t in xs]
+        dys = [t.contiguous(memory_format=torch.channels_last) for t in dys]
+    C = xs[0].shape[1]
+    w, b = f32(g['weight']), f32(g['bias'])
+    msgs = []
+    for x in xs:
+        x_, geom = _layout(x)
+        st = torch.empty(2 * C + 1, device=DEV)
+        K.stats(x_, geom, st)
+        msgs.append(st)
+    stats_all = torch.cat(msgs)
+    tol = 2e-5
+    saved_all, sums_tot = [], torch.zeros(2 * C, device=DEV)
+    gws, gbs = [], []
+    for r, x in enumerate(xs):
+        x_, geom = _layout(x)
+        rm, rv = f32(g['running_mean0']), f32(g['running_var0'])
+        y = torch.empty_like(x_)
+        saved = torch.empty(2 * C + 1, device=DEV)
+        K.apply(x_, y, geom, stats_all, W, w, b, rm, rv, float(g['momentum']), float(g['eps']), saved, 0)
+        assert np.abs(y.cpu().numpy() - g[f'y{r}']).max() <= tol * max(1, np.abs(g[f'y{r}']).max())
+        assert np.abs(rm.cpu().numpy() - g['running_mean1']).max() <= tol
+        assert np.abs(rv.cpu().numpy() - g['running_var1']).max() <= tol
+        saved_all.append(saved)
+        out = torch.empty(4 * C, device=DEV)
+        K.backward_reduce(dys[r], x_, geom, saved, w, b, out[:2 * C], out[2 * C:3 * C], out[3 * C:], 0)
+        sums_tot += out[:2 * C]
+        gws.append(out[2 * C:3 * C].clone())
+        gbs.append(out[3 * C:].clone())
+    for r, x in enumerate(xs):
+        x_, geom = _layout(x)
+        dx = torch.empty_like(x_)
+        K.backward_apply(dys[r], x_, dx, geom, saved_all[r], w, b, sums_tot, 0)
+        assert np.abs(dx.cpu().numpy() - g[f'dx{r}']).max() <= tol * max(1, np.abs(g[f'dx{r}']).max())
+    assert np.abs(sum(gws).cpu().numpy() - g['grad_weight']).max() <= 1e-4 * max(1, np.abs(g['grad_weight']).max())
+    assert np.abs(sum(gbs).cpu().numpy() - g['grad_bias']).max() <= 1e-4 * max(1, np.abs(g['grad_bias']).max())
+
+
+def test_module_variants():
+    torch.manual_seed(13)
+    x = torch.randn(16, 32, 6, 6, device=DEV) * 2 + 1
+    dy = torch.randn_like(x)
+    # affine=False
+    bn = make_bn(32, affine=False)
+    xd = x.clone().requires_grad_(True)
+    y = bn(xd)
+    y.backward(dy)
+    yr = F.batch_norm(x, None, None, None, None, True, 0.1, 1e-5)
+    assert torch.allclose(y, yr, atol=2e-5)
+    # momentum=None: cumulative moving average (batchnorm.py:760-767)
+    bn = make_bn(32, momentum=None)
+    ref = torch.nn.BatchNorm2d(32, momentum=None).to(DEV)
+    ref.load_state_dict(bn.state_dict())
+    for _ in range(3):
+        bn(x)
+        ref(x)
+    assert torch.allclose(bn.running_mean, ref.running_mean, atol=1e-5)
+    assert torch.allclose(bn.running_var, ref.running_var, atol=1e-5)
+    assert int(bn.num_batches_tracked) == 3
+    # track_running_stats=False: batch stats in eval too
+    bn = make_bn(32, track_running_stats=False).eval()
+    assert torch.allclose(bn(x), F.batch_norm(x, None, None, bn.weight, bn.bias, True, 0.0, 1e-5), atol=2e-5)
+    # eval mode uses running stats and leaves them alone; gradients still flow
+    bn = make_bn(32).eval()
+    rm0 = bn.running_mean.clone()
+    xd = x.clone().requires_grad_(True)
+    y = bn(xd)
+    y.backward(dy)
+    xr = x.clone().requires_grad_(True)
+    yr = F.batch_norm(xr, bn.running_mean, bn.running_var, bn.weight, bn.bias, False, 0.0, 1e-5)
+    yr.backward(dy)
+    assert torch.allclose(y, yr, atol=2e-5) and torch.equal(bn.running_mean, rm0)
+    assert torch.allclose(xd.grad, xr.grad, atol=2e-5)
+    # one value per channel in training mode
+    with pytest.raises(ValueError, match='Expected more than 1 value per channel'):
+        make_bn(4)(torch.randn(1, 4, device=DEV))
+    # repeated calls reuse the self-cleaning scratch
+    bn = make_bn(32)
+    a = bn(x)
+    bn2 = make_bn(32)
+    bn2.load_state_dict({k: v for k, v in bn.state_dict().items()})
+    c = bn(x)
+    assert torch.equal(a, c)
+
+
+def test_fused_relu():
+    torch.manual_seed(14)
+    for cl in (True, False):
+        x = torch.randn(8, 64, 10, 10, device=DEV)
+        dy = torch.randn_like(x)
+        if cl:
+            x = x.contiguous(memory_format=torch.channels_last)
+        bn = make_bn(64, fuse_relu=True)
+        ref = torch.nn.BatchNorm2d(64).to(DEV)
+        ref.load_state_dict(bn.state_dict())
+        y, dx, gw, gb = ours_fwd_bwd(x, dy, bn)
+        xr = x.clone().requires_grad_(True)
+        yr = torch.relu(ref(xr))
+        yr.backward(dy)
+        assert torch.allclose(y, yr, atol=2e-5)
+        assert torch.allclose(dx, xr.grad, atol=5e-5)
+        assert torch.allclose(gw, ref.weight.grad, atol=1e-3, rtol=1e-4)
+        assert torch.allclose(gb, ref.bias.grad, atol=1e-3, rtol=1e-4)
+
+
+def test_convert_and_train_small_cnn_like_reference_swap():
+    """main_supcon.py:222-224: convert_sync_batchnorm(model) then train."""
+    torch.manual_seed(15)
+    def net():
+        return torch.nn.Sequential(torch.nn.Conv2d(3, 16, 3, padding=1, bias=False), torch.nn.BatchNorm2d(16),
+                                   torch.nn.ReLU(), torch.nn.Conv2d(16, 32, 3, padding=1, bias=False),
+                                   torch.nn.BatchNorm2d(32), torch.nn.ReLU(), torch.nn.AdaptiveAvgPool2d(1),
+                                   torch.nn.Flatten(), torch.nn.Linear(32, 8))
+    a = net().to(DEV)
+    b = net().to(DEV)
+    b.load_state_dict(a.state_dict())
+    b = SyncBatchNorm.convert_sync_batchnorm(b)
+    x = torch.randn(32, 3, 16, 16, device=DEV)
+    la = a(x).square().mean()
+    lb = b(x).square().mean()
+    la.backward()
+    lb.backward()
+    assert torch.allclose(la, lb, rtol=1e-5)
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(pa.grad, pb.grad, atol=1e-5, rtol=1e-4)
+    assert list(a.state_dict().keys()) == list(b.state_dict().keys())
+
+
+def test_large_layer_shapes_property():
+    """ResNet-50 layer shapes at N=512 are too big for a CPU oracle in a unit
+    test: check size-independent properties instead -- per-channel mean 0 / variance 1 of the
+    output, sum of dx per channel = 0 and sum of dx*xhat = 0 (the BN backward projections)."""
+    torch.manual_seed(16)
+    for shape in [(512, 64, 32, 32), (512, 1024, 8, 8)]:
+        C = shape[1]
+        x = (torch.randn(shape, device=DEV, dtype=torch.float32) * 1.7 + 0.3).contiguous(memory_format=torch.channels_last)
+        dy = torch.randn(shape, device=DEV).contiguous(memory_format=torch.channels_last)
+        bn = SyncBatchNorm(C, affine=False).to(DEV)
+        xd = x.clone().requires_grad_(True)
+        y = bn(xd)
+        y.backward(dy)
+        m = y.double().mean(dim=(0, 2, 3))
+        v = y.double().var(dim=(0, 2, 3), unbiased=False)
+        assert m.abs().max() < 1e-5 and (v - 1).abs().max() < 1e-4
+        assert xd.grad.double().mean(dim=(0, 2, 3)).abs().max() < 1e-6
+        assert (xd.grad.double() * y.double()).mean(dim=(0, 2, 3)).abs().max() < 1e-5
