@@ -116,19 +116,44 @@ def barrier(world):
     torch.cuda.synchronize()
 
 
-def time_steps(step_fn, steps, warmup, world):
-    """W untimed steps, then exactly K steps between barrier+synchronize, CUDA events, max over ranks."""
+def time_steps(step_fn, steps, warmup, world, graph_pool=0):
+    """W untimed steps, then exactly K steps between barrier+synchronize, CUDA events, max over ranks.
+
+    graph_pool > 0: the K steps are replays of a CUDA graph that holds g consecutive steps (g = the
+    largest divisor of K not above graph_pool, each step on its own buffer set), so the launch-bound
+    host side of the eager module API does not starve the GPU.  Returns (ms, how)."""
     import torch
     for i in range(warmup):
         step_fn(i)
     barrier(world)
+    how, graph, reps = 'eager launches', None, 0
+    if graph_pool > 0 and world == 1 and os.environ.get('SIMCLR_B200_BENCH_NO_GRAPH') != '1':
+        g = max(d for d in range(1, min(graph_pool, steps) + 1) if steps % d == 0)
+        try:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                for i in range(g):
+                    step_fn(i)
+            graph.replay()
+            torch.cuda.synchronize()
+            reps = steps // g
+            how = 'CUDA graph of %d consecutive steps replayed %d times' % (g, reps)
+        except Exception as e:      # say so instead of hiding it
+            graph = None
+            how = 'eager launches (graph capture failed: %s)' % type(e).__name__
+            torch.cuda.synchronize()
+    barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(steps):
-        step_fn(warmup + i)
+    if graph is not None:
+        for _ in range(reps):
+            graph.replay()
+    else:
+        for i in range(steps):
+            step_fn(warmup + i)
     e1.record()
     barrier(world)
-    return max_over_ranks(e0.elapsed_time(e1), world)
+    return max_over_ranks(e0.elapsed_time(e1), world), how
 
 
 # ----------------------------------------------------------------------------- NT-Xent (ours)
@@ -193,6 +218,7 @@ def loss_kernel_breakdown(engine, steps):
     tot = [0.0] * 4
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
     for it in range(steps + 3):
+        torch.cuda._sleep(400000)      # let the host run ahead so the events see back-to-back kernels
         ev[0].record()
         L.launch_prep(lib, z, plan, False, k, k_lo, None)
         ev[1].record()
@@ -273,6 +299,7 @@ def bn_kernel_breakdown(steps, pool=8):
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
     for it in range(steps + 3):
         x, dy, y, dx = xs[it % pool], dys[it % pool], ys[it % pool], dxs[it % pool]
+        torch.cuda._sleep(400000)      # let the host run ahead so the events see back-to-back kernels
         ev[0].record()
         K.stats(x, geom, st)
         ev[1].record()
@@ -418,9 +445,12 @@ def main():
         pool = 64                                    # 64 x 2 MiB (bf16) of embeddings + grads > L2
         step_res, step_e2e, h2d, d2h, b_local = make_loss_runner(world, rank, engine, pool)
         c0 = lib.scb_launch_count()
-        ms = time_steps(step_res, args.steps, args.warmup, world)
-        launches = (lib.scb_launch_count() - c0) // (args.steps + args.warmup)
-        ms_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
+        step_res(0)
+        c0 = lib.scb_launch_count()
+        step_res(1)
+        launches = lib.scb_launch_count() - c0
+        ms, how = time_steps(step_res, args.steps, args.warmup, world, graph_pool=pool)
+        ms_e2e, _ = time_steps(step_e2e, args.steps, args.warmup, world)
         per = ms / args.steps
         A = C = N_VIEWS * B_GLOBAL
         flops_step = 6.0 * A * C * DIM
@@ -435,7 +465,7 @@ def main():
                        'engine': engine, 'l2': 'inputs rotate through a pool of %d embedding/gradient sets '
                                                '(> L2 in total); the 2 MiB working set of one step is L2-resident '
                                                'by construction' % pool,
-                       'launch': 'eager, public module API (SupConLoss.forward + autograd backward)'},
+                       'launch': 'public module API (SupConLoss.forward + autograd backward); ' + how},
             'e2e': {'value': B_GLOBAL / (ms_e2e / args.steps * 1e-3), 'unit': 'pairs/s',
                     'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
             'gpu_launches': int(launches),
@@ -455,16 +485,19 @@ def main():
         pool = 12                                    # 12 x (x, dy, y, dx) of 8 MiB each = 400 MB > L2
         step_res, step_e2e, S, bn = make_bn_runner(world, rank, pool)
         c0 = lib.scb_launch_count()
-        ms = time_steps(step_res, args.steps, args.warmup, world)
-        launches = (lib.scb_launch_count() - c0) // (args.steps + args.warmup)
-        ms_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
+        step_res(0)
+        c0 = lib.scb_launch_count()
+        step_res(1)
+        launches = lib.scb_launch_count() - c0
+        ms, how = time_steps(step_res, args.steps, args.warmup, world, graph_pool=pool)
+        ms_e2e, _ = time_steps(step_e2e, args.steps, args.warmup, world)
         per = ms / args.steps
         gbs = 8.0 * S / (per * 1e-3) / 1e9           # per GPU; algorithmic bytes of SURVEY 8(d)
         sb = {'metric': 'SyncBN fwd+bwd HBM GB/s', 'value': gbs * world, 'per_gpu': gbs, 'unit': 'GB/s',
               'ms_per_step': per, 'scaling': 'weak', 'dtype': 'bf16 I/O, f32 statistics',
               'config': {'workload': 'SyncBatchNorm fwd+bwd on [256,256,8,8] NHWC bf16 per GPU, %d GPU(s)' % world,
                          'l2': 'x/dy/y/dx rotate through %d buffer sets (> L2)' % pool,
-                         'launch': 'eager, public module API'},
+                         'launch': 'public module API (SyncBatchNorm.forward + autograd backward); ' + how},
               'e2e': {'value': 8.0 * S * world / (ms_e2e / args.steps * 1e-3) / 1e9, 'unit': 'GB/s',
                       'h2d_bytes_per_step': 2 * S, 'd2h_bytes_per_step': 2 * S},
               'gpu_launches': int(launches)}

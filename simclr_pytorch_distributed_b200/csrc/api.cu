@@ -97,14 +97,14 @@ extern "C" int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, in
     SCB_REQUIRE(workspace_bytes >= scb_supcon_workspace_bytes(p, n_rows), "supcon_forward: workspace too small");
     cudaStream_t stream = (cudaStream_t)stream_;
     float* part = (float*)workspace;
-    int n_split = 1;
+    int n_split = 1, flat_q = 0, flat_ct = 0;
     if (p->engine == SCB_ENGINE_FP32) {
         n_split = fp32_splits(n_rows, p->n_k);
         if (int e = fp32_forward(p, row_begin, n_rows, part, n_split, stream)) return e;
     } else {
-        if (int e = tc_forward(p, row_begin, n_rows, part, &n_split, stream)) return e;
+        if (int e = tc_forward(p, row_begin, n_rows, part, &n_split, &flat_q, &flat_ct, stream)) return e;
     }
-    return launch_finalize(p, part, n_split, row_begin, n_rows, 1.0 / (double)n_anchor_total, out_lse,
+    return launch_finalize(p, part, n_split, flat_q, flat_ct, row_begin, n_rows, 1.0 / (double)n_anchor_total, out_lse,
                            out_possum, out_npos, out_loss_sum, stream);
 }
 

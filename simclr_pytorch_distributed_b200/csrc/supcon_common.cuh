@@ -44,8 +44,9 @@ int fp32_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* 
 int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
                   const float* npos_all, const float* grad_out, int n_anchor_total, float* out_dk,
                   int ld_dk, cudaStream_t stream);
-int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int row_begin,
-                    int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
+// flat_q > 0: tensor-core engine, row block rb (256 rows) owns slots of the CTAs overlapping its tiles
+int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int flat_q, int flat_ct,
+                    int row_begin, int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
                     float* out_loss_sum, cudaStream_t stream);
 
 }  // namespace scb

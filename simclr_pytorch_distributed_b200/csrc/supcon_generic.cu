@@ -70,7 +70,8 @@ supcon_finish_kernel(const float* __restrict__ dk, int ld_dk, const TF* __restri
 // partials: [n_split][4][n_rows] = (running max m, sum exp(s - m), possum, npos) per local row.
 // One CTA, fixed summation order -> deterministic loss.
 __global__ void __launch_bounds__(1024)
-supcon_finalize_kernel(const float* __restrict__ part, int n_split, int n_rows, int row_begin,
+supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_q, int flat_ct, int n_rows,
+                       int row_begin,
                        RowMap map, int mode, float loss_scale, double inv_anchors,
                        float* __restrict__ out_lse,
                        float* __restrict__ out_possum, float* __restrict__ out_npos,
@@ -80,6 +81,11 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split, int n_rows, 
     for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
         float lse = 0.f, ps = 0.f, np = 1.f;
         if (map.is_anchor(row_begin + r, mode)) {
+            int n_split = n_split_in;
+            if (flat_q > 0) {      // slots = CTAs whose span [c*q, (c+1)*q) meets this row block's tiles
+                const int rb = r >> 8;
+                n_split = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
+            }
             float m = -INFINITY;
             for (int s = 0; s < n_split; ++s) m = fmaxf(m, part[((int64_t)s * 4 + 0) * n_rows + r]);
             float sum = 0.f; ps = 0.f; np = 0.f;
@@ -244,10 +250,10 @@ int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const 
     return SCB_OK;
 }
 
-int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int row_begin,
-                    int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
+int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int flat_q, int flat_ct,
+                    int row_begin, int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
                     float* out_loss_sum, cudaStream_t stream) {
-    supcon_finalize_kernel<<<1, 1024, 0, stream>>>(part, n_split, n_rows, row_begin, RowMap::of(p),
+    supcon_finalize_kernel<<<1, 1024, 0, stream>>>(part, n_split, flat_q, flat_ct, n_rows, row_begin, RowMap::of(p),
                                                    p->mode, p->loss_scale, inv_anchors, out_lse, out_possum,
                                                    out_npos, out_loss_sum);
     SCB_CUDA_OK(cudaGetLastError());

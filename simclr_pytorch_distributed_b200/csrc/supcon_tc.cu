@@ -1,19 +1,851 @@
-// Tensor-core engine of the loss (placeholder until the tcgen05 kernels land).
+// Tensor-core engine of the SupCon / NT-Xent loss for sm_100a: flash-style forward and
+// recompute backward that never write a similarity tile to memory.
+//
+//   * K (the [n_k, ldk] bf16 contrast matrix) is staged by TMA (cp.async.bulk.tensor, 128-byte
+//     swizzle) in [128 rows x 64 col] sub-tiles; a CTA owns a 256-row block (two 128-row halves)
+//     and walks a contiguous span of 128-column tiles, so every B tile feeds two MMAs.
+//   * S = K_i K_j^T runs on tcgen05.mma (kind::f16, M=128, N=128, K=16) with fp32 accumulators in
+//     TMEM; one elected thread issues, completion is tracked with tcgen05.commit -> mbarrier.
+//   * two epilogue warpgroups (one per half) pull S out of TMEM with tcgen05.ld and keep the
+//     online (max, sum exp, positive sum) row state in registers              -> forward
+//     or turn S into P = dL/dS (bf16, written to shared memory in the UMMA K-major layout) which
+//     a second tcgen05.mma multiplies with the very same K_j tile read MN-major, accumulating
+//     dK_i in TMEM                                                            -> backward
+//
+// Reference being replaced: /root/reference/losses.py:64-91 and its autograd backward.
+// Work split: the RB x CT tile grid is flattened row-block-major and cut into equal spans, one
+// per CTA (persistent, one CTA per SM); partial row results of CTAs that share a row block are
+// merged by the finalize kernel (forward) or by vector float reductions into dK (backward).
 #include "supcon_tc.cuh"
+#include "supcon_common.cuh"
+#include "tc_ptx.cuh"
 
 namespace scb {
+using namespace ptx;
 
-int64_t tc_workspace_bytes(const scb_supcon_problem*, int) { return 0; }
+constexpr int kBMH = 128;       // rows per half = one UMMA M
+constexpr int kBM = 256;        // rows per CTA tile
+constexpr int kBN = 128;        // columns per tile
+constexpr int kSub = 16384;     // bytes of one [128 x 64] bf16 swizzled sub-tile
+constexpr int kThreads = 320;   // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..9 epilogue (2 warpgroups)
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr float kSafeSpread = 60.f;
 
-int tc_forward(const scb_supcon_problem*, int, int, float*, int*, cudaStream_t) {
-    set_error("tensor-core engine not built yet");
-    return SCB_ERR_UNSUPPORTED;
+struct TcParams {
+    const __nv_bfloat16* k;
+    int ldk, n_k, dim;
+    int row_begin, n_rows, a_count;     // local rows; rows the forward treats as anchors
+    int CT, RB, T, q;                   // column tiles, row blocks, tiles, tiles per CTA
+    RowMap map;
+    int n_views, mode, mask_kind;
+    float c2, inv_T;                    // log2(e)/T, 1/T
+    float* part;                        // forward partials [slot][4][n_rows]
+    const int* rep_row;                 // labels: class representative per global row
+    const float* npos_row;              // labels: number of positives per global row
+    const float* nia_row;               // labels: [anchor]/npos per global row
+    const float* lse_all;
+    const float* grad_out;
+    float coef_scale;                   // (T/Tb) / n_anchor_total
+    float* out_dk;
+    int ld_dk;
+};
+
+__device__ __forceinline__ float bf16_dot_rows(const __nv_bfloat16* a, const __nv_bfloat16* b, int n) {
+    float acc = 0.f;
+    for (int d = 0; d < n; d += 8) {
+        const uint4 ua = *reinterpret_cast<const uint4*>(a + d);
+        const uint4 ub = *reinterpret_cast<const uint4*>(b + d);
+        const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&ua);
+        const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&ub);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float2 fa = __bfloat1622float2(pa[i]), fb = __bfloat1622float2(pb[i]);
+            acc = fmaf(fa.x, fb.x, acc);
+            acc = fmaf(fa.y, fb.y, acc);
+        }
+    }
+    return acc;
 }
 
-int tc_backward(const scb_supcon_problem*, int, int, const float*, const float*, const float*, int,
-                float*, int, void*, cudaStream_t) {
-    set_error("tensor-core engine not built yet");
-    return SCB_ERR_UNSUPPORTED;
+// =================================================================================== forward
+// smem: A[2][2*KCH*kSub] | B[2][KCH*kSub] | barriers | tmem slot
+template <int KCH, bool kLabels>
+__global__ void __launch_bounds__(kThreads, 1)
+supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    constexpr int A_BYTES = 2 * KCH * kSub;
+    constexpr int B_BYTES = KCH * kSub;
+    constexpr int NSB = 2;
+    uint8_t* a_smem = smem;
+    uint8_t* b_smem = smem + 2 * A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(b_smem + NSB * B_BYTES);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    const uint32_t bar0 = smem_u32(bars);
+    auto a_full = [&](int b) { return bar0 + 8u * (0 + b); };
+    auto a_empty = [&](int b) { return bar0 + 8u * (2 + b); };
+    auto b_full = [&](int s) { return bar0 + 8u * (4 + s); };
+    auto b_empty = [&](int s) { return bar0 + 8u * (6 + s); };
+    auto s_full = [&](int h, int b) { return bar0 + 8u * (8 + h * 2 + b); };
+    auto s_empty = [&](int h, int b) { return bar0 + 8u * (12 + h * 2 + b); };
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if ((smem_u32(smem) & 1023u) != 0u) __trap();
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);
+        for (int i = 12; i < 16; ++i) mbar_init(bar0 + 8u * i, kBMH);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
+    if (warp == 0 && lane == 0) prefetch_tensormap(&tmap);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int t0 = blockIdx.x * p.q;
+    const int t1 = min(p.T, t0 + p.q);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ------------------------------------------------ TMA producer
+            int n_a = 0, n_b = 0, cur_rb = -1;
+            for (int tau = t0; tau < t1; ++tau) {
+                const int rb = tau / p.CT, ct = tau - rb * p.CT;
+                if (rb != cur_rb) {
+                    cur_rb = rb;
+                    const int buf = n_a & 1;
+                    mbar_wait(a_empty(buf), ((n_a >> 1) & 1) ^ 1);
+                    mbar_arrive_expect_tx(a_full(buf), A_BYTES);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int kc = 0; kc < KCH; ++kc)
+                            tma_load_2d(smem_u32(a_smem + buf * A_BYTES + (h * KCH + kc) * kSub), &tmap, kc * 64,
+                                        p.row_begin + rb * kBM + h * kBMH, a_full(buf));
+                    ++n_a;
+                }
+                const int st = n_b % NSB;
+                mbar_wait(b_empty(st), ((n_b / NSB) & 1) ^ 1);
+                mbar_arrive_expect_tx(b_full(st), B_BYTES);
+#pragma unroll
+                for (int kc = 0; kc < KCH; ++kc)
+                    tma_load_2d(smem_u32(b_smem + st * B_BYTES + kc * kSub), &tmap, kc * 64, ct * kBN, b_full(st));
+                ++n_b;
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ------------------------------------------------ MMA issuer
+            constexpr uint32_t idesc = idesc_bf16(128, 128, 0);
+            int n_a = 0, n_b = 0, idx = 0, cur_rb = -1, abuf = 0;
+            for (int tau = t0; tau < t1; ++tau) {
+                const int rb = tau / p.CT;
+                if (rb != cur_rb) {
+                    if (cur_rb >= 0) umma_commit(a_empty(abuf));
+                    cur_rb = rb;
+                    abuf = n_a & 1;
+                    mbar_wait(a_full(abuf), (n_a >> 1) & 1);
+                    ++n_a;
+                }
+                const int st = n_b % NSB;
+                mbar_wait(b_full(st), (n_b / NSB) & 1);
+                ++n_b;
+                const int sbuf = idx & 1;
+                const uint32_t sphase = (idx >> 1) & 1;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    mbar_wait(s_empty(h, sbuf), sphase ^ 1);
+                    tc_fence_after();
+                    const uint32_t d = tmem_base + sbuf * 256 + h * 128;
+                    const uint32_t a0 = smem_u32(a_smem + abuf * A_BYTES + h * KCH * kSub);
+                    const uint32_t b0 = smem_u32(b_smem + st * B_BYTES);
+#pragma unroll
+                    for (int k16 = 0; k16 < KCH * 4; ++k16) {
+                        const uint32_t off = (k16 >> 2) * kSub + (k16 & 3) * 32;
+                        umma_bf16(d, smem_desc_sw128(a0 + off, 16, 1024), smem_desc_sw128(b0 + off, 16, 1024),
+                                  idesc, k16 > 0 ? 1u : 0u);
+                    }
+                    umma_commit(s_full(h, sbuf));
+                }
+                umma_commit(b_empty(st));
+                ++idx;
+            }
+        }
+    } else {
+        // ---------------------------------------------------- epilogue warpgroups
+        const int wg = (warp - 2) >> 2;                 // half of the row block
+        const int q4 = warp & 3;                        // TMEM lane quarter this warp may touch
+        const int r = q4 * 32 + lane;                   // row within the half
+        const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
+        float m = -INFINITY, sum = 0.f, possum = 0.f;
+        int cur_rb = -1, idx = 0, li = 0, gi = 0, rep_i = 0;
+
+        auto flush = [&](int rb) {
+            if (li >= p.a_count) return;
+            const int slot = blockIdx.x - (rb * p.CT) / p.q;
+            float ps = 0.f, np = 0.f;
+            if (kLabels) {
+                ps = possum * p.inv_T;
+                if (slot == 0) np = p.npos_row[gi];
+            } else if (slot == 0) {
+                // SimCLR positives: the other views of the same sample (closed form, losses.py:42-43)
+                const int base = (gi / p.map.vseg) * p.map.vseg, rem = gi - base;
+                const int v = rem / p.map.seg, b = rem - v * p.map.seg;
+                for (int vv = 0; vv < p.n_views; ++vv)
+                    if (vv != v)
+                        ps += bf16_dot_rows(p.k + (int64_t)gi * p.ldk,
+                                            p.k + (int64_t)(base + vv * p.map.seg + b) * p.ldk, p.ldk);
+                ps *= p.inv_T;
+                np = (float)(p.n_views - 1);
+            }
+            float* dst = p.part + (int64_t)slot * 4 * p.n_rows + li;
+            dst[0] = m * kLn2;
+            dst[p.n_rows] = sum;
+            dst[2 * (int64_t)p.n_rows] = ps;
+            dst[3 * (int64_t)p.n_rows] = np;
+        };
+
+        for (int tau = t0; tau < t1; ++tau) {
+            const int rb = tau / p.CT, ct = tau - rb * p.CT;
+            if (rb != cur_rb) {
+                if (cur_rb >= 0) flush(cur_rb);
+                cur_rb = rb;
+                m = -INFINITY; sum = 0.f; possum = 0.f;
+                li = rb * kBM + wg * kBMH + r;
+                gi = p.row_begin + li;
+                if (kLabels) rep_i = (gi < p.n_k) ? p.rep_row[gi] : -1;
+            }
+            const int sbuf = idx & 1;
+            mbar_wait(s_full(wg, sbuf), (idx >> 1) & 1);
+            tc_fence_after();
+            const int j0 = ct * kBN;
+            const int g_lo = p.row_begin + rb * kBM + wg * kBMH;
+            const bool pred = (j0 + kBN > p.n_k) || (g_lo < j0 + kBN && j0 < g_lo + kBMH);
+#pragma unroll 1
+            for (int cc = 0; cc < 4; ++cc) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + lane_addr + sbuf * 256 + wg * 128 + cc * 32, v);
+                tmem_ld_wait();
+                if (cc == 3) {
+                    tc_fence_before();
+                    mbar_arrive(s_empty(wg, sbuf));
+                }
+                const int jc = j0 + cc * 32;
+                if (!pred) {
+                    float cmax = __uint_as_float(v[0]);
+#pragma unroll
+                    for (int c = 1; c < 32; ++c) cmax = fmaxf(cmax, __uint_as_float(v[c]));
+                    const float nm = fmaxf(m, cmax * p.c2);
+                    sum *= ex2(m - nm);
+                    m = nm;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) sum += ex2(fmaf(__uint_as_float(v[c]), p.c2, -m));
+                    if (kLabels) {
+#pragma unroll
+                        for (int c4 = 0; c4 < 8; ++c4) {
+                            const int4 rj = __ldg(reinterpret_cast<const int4*>(p.rep_row + jc) + c4);
+                            possum += (rj.x == rep_i) ? __uint_as_float(v[c4 * 4 + 0]) : 0.f;
+                            possum += (rj.y == rep_i) ? __uint_as_float(v[c4 * 4 + 1]) : 0.f;
+                            possum += (rj.z == rep_i) ? __uint_as_float(v[c4 * 4 + 2]) : 0.f;
+                            possum += (rj.w == rep_i) ? __uint_as_float(v[c4 * 4 + 3]) : 0.f;
+                        }
+                    }
+                } else {
+                    // tiles that contain the self column (losses.py:74-79) or run past n_k
+                    float cmax = -INFINITY;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const int j = jc + c;
+                        const bool ok = (j < p.n_k) && (j != gi);
+                        const float x = ok ? __uint_as_float(v[c]) : -INFINITY;
+                        v[c] = __float_as_uint(x);
+                        cmax = fmaxf(cmax, x);
+                    }
+                    const float nm = fmaxf(m, cmax * p.c2);
+                    if (nm > -INFINITY) {
+                        sum *= ex2(m - nm);
+                        m = nm;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) sum += ex2(fmaf(__uint_as_float(v[c]), p.c2, -m));
+                    }
+                    if (kLabels) {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) {
+                            const int j = jc + c;
+                            const float x = __uint_as_float(v[c]);
+                            if (x > -INFINITY && p.rep_row[j] == rep_i) possum += x;
+                        }
+                    }
+                }
+            }
+            ++idx;
+        }
+        if (cur_rb >= 0) flush(cur_rb);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// =================================================================================== backward
+// smem: A[2*KCH*kSub] | B[3][KCH*kSub] | P[2][2*kSub] | cols[2 wg][2 buf][128] f32 | flags | barriers | tmem slot
+// TMEM: S[h] at columns h*128, dK[h] at columns 256 + h*128.
+template <int KCH, bool kLabels>
+__global__ void __launch_bounds__(kThreads, 1)
+supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    constexpr int A_BYTES = 2 * KCH * kSub;
+    constexpr int B_BYTES = KCH * kSub;
+    constexpr int P_BYTES = 2 * kSub;                  // one half: [128 rows x 128 cols] bf16
+    constexpr int NSB = 3;
+    uint8_t* a_smem = smem;
+    uint8_t* b_smem = a_smem + A_BYTES;
+    uint8_t* p_smem = b_smem + NSB * B_BYTES;
+    float* cols = reinterpret_cast<float*>(p_smem + 2 * P_BYTES);       // [2][2][128]
+    uint32_t* flags = reinterpret_cast<uint32_t*>(cols + 2 * 2 * 128);  // [2 wg][2 buf][4 warps]
+    float* rowred = reinterpret_cast<float*>(flags + 16);               // [2 wg][4 warps][2]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(rowred + 16);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    const uint32_t bar0 = smem_u32(bars);
+    // barrier map: 0 a_full, 1 a_empty, 2-4 b_full, 5-7 b_empty, 8-9 s_full, 10-11 s_empty,
+    //              12-13 p_full, 14-15 p_empty ... dz_full / dz_empty live in two extra slots
+    auto a_full = [&]() { return bar0 + 8u * 0; };
+    auto a_empty = [&]() { return bar0 + 8u * 1; };
+    auto b_full = [&](int s) { return bar0 + 8u * (2 + s); };
+    auto b_empty = [&](int s) { return bar0 + 8u * (5 + s); };
+    auto s_full = [&](int h) { return bar0 + 8u * (8 + h); };
+    auto s_empty = [&](int h) { return bar0 + 8u * (10 + h); };
+    auto p_full = [&](int h) { return bar0 + 8u * (12 + h); };
+    auto p_empty = [&](int h) { return bar0 + 8u * (14 + h); };
+    uint64_t* bars2 = reinterpret_cast<uint64_t*>(tmem_slot + 2);
+    const uint32_t dz_full = smem_u32(bars2), dz_empty = smem_u32(bars2 + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if ((smem_u32(smem) & 1023u) != 0u) __trap();
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 10; ++i) mbar_init(bar0 + 8u * i, 1);     // a, b, s_full
+        mbar_init(s_empty(0), kBMH); mbar_init(s_empty(1), kBMH);
+        mbar_init(p_full(0), kBMH); mbar_init(p_full(1), kBMH);
+        mbar_init(p_empty(0), 1); mbar_init(p_empty(1), 1);
+        mbar_init(dz_full, 1);
+        mbar_init(dz_empty, 2 * kBMH);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
+    if (warp == 0 && lane == 0) prefetch_tensormap(&tmap);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int t0 = blockIdx.x * p.q;
+    const int t1 = min(p.T, t0 + p.q);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ------------------------------------------------ TMA producer
+            int n_a = 0, n_b = 0, cur_rb = -1;
+            for (int tau = t0; tau < t1; ++tau) {
+                const int rb = tau / p.CT, ct = tau - rb * p.CT;
+                if (rb != cur_rb) {
+                    cur_rb = rb;
+                    mbar_wait(a_empty(), (n_a & 1) ^ 1);
+                    mbar_arrive_expect_tx(a_full(), A_BYTES);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int kc = 0; kc < KCH; ++kc)
+                            tma_load_2d(smem_u32(a_smem + (h * KCH + kc) * kSub), &tmap, kc * 64,
+                                        p.row_begin + rb * kBM + h * kBMH, a_full());
+                    ++n_a;
+                }
+                const int st = n_b % NSB;
+                mbar_wait(b_empty(st), ((n_b / NSB) & 1) ^ 1);
+                mbar_arrive_expect_tx(b_full(st), B_BYTES);
+#pragma unroll
+                for (int kc = 0; kc < KCH; ++kc)
+                    tma_load_2d(smem_u32(b_smem + st * B_BYTES + kc * kSub), &tmap, kc * 64, ct * kBN, b_full(st));
+                ++n_b;
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && t0 < t1) {
+            // ------------------------------------------------ MMA issuer
+            constexpr uint32_t idesc1 = idesc_bf16(128, 128, 0);
+            constexpr uint32_t idesc2 = idesc_bf16(128, KCH * 64, 1);
+            int n_a = 0, n_dz = 0;
+            int n_s[2] = {0, 0};
+            const int n_tiles = t1 - t0;
+
+            // S[h] = A_h * B^T for tile number `i` of the span (half h)
+            auto mma1 = [&](int i, int h) {
+                const int tau = t0 + i;
+                const int rb = tau / p.CT;
+                const bool first_of_rb = (i == 0) || ((tau - 1) / p.CT != rb);
+                const bool last_of_rb = (i == n_tiles - 1) || ((tau + 1) / p.CT != rb);
+                const int st = i % NSB;
+                if (h == 0) {
+                    if (first_of_rb) { mbar_wait(a_full(), n_a & 1); ++n_a; }
+                    mbar_wait(b_full(st), (i / NSB) & 1);
+                }
+                mbar_wait(s_empty(h), (n_s[h] & 1) ^ 1);
+                ++n_s[h];
+                tc_fence_after();
+                const uint32_t d = tmem_base + h * 128;
+                const uint32_t a0 = smem_u32(a_smem + h * KCH * kSub);
+                const uint32_t b0 = smem_u32(b_smem + st * B_BYTES);
+#pragma unroll
+                for (int k16 = 0; k16 < KCH * 4; ++k16) {
+                    const uint32_t off = (k16 >> 2) * kSub + (k16 & 3) * 32;
+                    umma_bf16(d, smem_desc_sw128(a0 + off, 16, 1024), smem_desc_sw128(b0 + off, 16, 1024), idesc1,
+                              k16 > 0 ? 1u : 0u);
+                }
+                umma_commit(s_full(h));
+                if (h == 1 && last_of_rb) umma_commit(a_empty());
+            };
+            // dK[h] += P_h * K_j  (K_j read MN-major from the same stage)
+            auto mma2 = [&](int i, int h) {
+                const int tau = t0 + i;
+                const int rb = tau / p.CT;
+                const bool first_of_rb = (i == 0) || ((tau - 1) / p.CT != rb);
+                const bool last_of_rb = (i == n_tiles - 1) || ((tau + 1) / p.CT != rb);
+                const int st = i % NSB;
+                mbar_wait(p_full(h), i & 1);
+                if (h == 0 && first_of_rb) { mbar_wait(dz_empty, (n_dz & 1) ^ 1); }
+                tc_fence_after();
+                const uint32_t d = tmem_base + 256 + h * 128;
+                const uint32_t a0 = smem_u32(p_smem + h * P_BYTES);
+                const uint32_t b0 = smem_u32(b_smem + st * B_BYTES);
+#pragma unroll
+                for (int j16 = 0; j16 < 8; ++j16) {
+                    const uint32_t aoff = (j16 >> 2) * kSub + (j16 & 3) * 32;
+                    umma_bf16(d, smem_desc_sw128(a0 + aoff, 16, 1024),
+                              smem_desc_sw128(b0 + j16 * 2048, kSub, 1024), idesc2,
+                              (first_of_rb && j16 == 0) ? 0u : 1u);
+                }
+                umma_commit(p_empty(h));
+                if (h == 1) {
+                    umma_commit(b_empty(st));
+                    if (last_of_rb) { umma_commit(dz_full); ++n_dz; }
+                }
+            };
+
+            mma1(0, 0);
+            mma1(0, 1);
+            for (int i = 0; i < n_tiles; ++i) {
+                mma2(i, 0);
+                if (i + 1 < n_tiles) mma1(i + 1, 0);
+                mma2(i, 1);
+                if (i + 1 < n_tiles) mma1(i + 1, 1);
+            }
+        }
+    } else {
+        // ---------------------------------------------------- epilogue warpgroups
+        const int wg = (warp - 2) >> 2;
+        const int q4 = warp & 3;
+        const int r = q4 * 32 + lane;
+        const int wtid = (warp - 2 - wg * 4) * 32 + lane;       // 0..127 inside the warpgroup
+        const int wwarp = wtid >> 5;
+        const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
+        const float coef = p.grad_out[0] * p.coef_scale * p.inv_T;
+        float* mycols = cols + wg * 256;
+        uint32_t* myflags = flags + wg * 8;
+        float* myrow = rowred + wg * 8;
+        uint8_t* myp = p_smem + wg * P_BYTES;
+        const bool mode_all = (p.mode == SCB_MODE_ALL);
+
+        int cur_rb = -1, idx = 0, li = 0, gi = 0, rep_i = 0, n_dz = 0;
+        bool row_ok = false, rb_fast = false;
+        float lse2_i = INFINITY, m0 = 0.f, R_i = 0.f, nia_i = 0.f;
+
+        auto drain = [&](int rb) {
+            mbar_wait(dz_full, n_dz & 1);
+            ++n_dz;
+            tc_fence_after();
+            const int lrow = rb * kBM + wg * kBMH + r;
+#pragma unroll 1
+            for (int cc = 0; cc < KCH * 2; ++cc) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + lane_addr + 256 + wg * 128 + cc * 32, v);
+                tmem_ld_wait();
+                if (lrow < p.n_rows) {
+                    float* dst = p.out_dk + (int64_t)lrow * p.ld_dk + cc * 32;
+#pragma unroll
+                    for (int c = 0; c < 32; c += 4)
+                        red_add_v4(dst + c, __uint_as_float(v[c]) * coef, __uint_as_float(v[c + 1]) * coef,
+                                   __uint_as_float(v[c + 2]) * coef, __uint_as_float(v[c + 3]) * coef);
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(dz_empty);
+        };
+
+        for (int tau = t0; tau < t1; ++tau) {
+            const int rb = tau / p.CT, ct = tau - rb * p.CT;
+            if (rb != cur_rb) {
+                if (cur_rb >= 0) drain(cur_rb);
+                cur_rb = rb;
+                li = rb * kBM + wg * kBMH + r;
+                gi = p.row_begin + li;
+                row_ok = (li < p.n_rows);
+                const bool anchor_i = row_ok && p.map.is_anchor(gi, p.mode);
+                lse2_i = anchor_i ? p.lse_all[gi] * kLog2e : INFINITY;
+                if (kLabels) {
+                    rep_i = row_ok ? p.rep_row[gi] : -1;
+                    nia_i = row_ok ? p.nia_row[gi] : 0.f;
+                }
+                // warpgroup-wide range of the rows' log-sum-exps (reference point of the 1-exp path)
+                float mx = anchor_i ? lse2_i : -INFINITY, mn = anchor_i ? lse2_i : INFINITY;
+                mx = warp_max(mx);
+                mn = -warp_max(-mn);
+                named_bar_sync(1 + wg, kBMH);      // previous users of myrow are done
+                if (lane == 0) { myrow[wwarp * 2] = mx; myrow[wwarp * 2 + 1] = mn; }
+                named_bar_sync(1 + wg, kBMH);
+                mx = fmaxf(fmaxf(myrow[0], myrow[2]), fmaxf(myrow[4], myrow[6]));
+                mn = fminf(fminf(myrow[1], myrow[3]), fminf(myrow[5], myrow[7]));
+                m0 = mx;
+                rb_fast = mode_all && (mx - mn <= kSafeSpread) && (mx > -INFINITY);
+                R_i = (anchor_i && rb_fast) ? ex2(lse2_i - m0) : 0.f;
+            }
+            const int j0 = ct * kBN;
+            const int cbuf = idx & 1;
+            // ---- per-column factors of this tile: C_j = [anchor_j] 2^(m0 - lse2_j)
+            {
+                const int j = j0 + wtid;
+                const bool okj = (j < p.n_k) && p.map.is_anchor(j, p.mode);
+                const float Lj = okj ? p.lse_all[j] * kLog2e : 0.f;
+                const float d = m0 - Lj;
+                const bool unsafe = okj && !(fabsf(d) <= kSafeSpread);
+                mycols[cbuf * 128 + wtid] = (okj && !unsafe) ? ex2(d) : 0.f;
+                const unsigned any = __any_sync(0xffffffffu, unsafe);
+                if (lane == 0) myflags[cbuf * 4 + wwarp] = any;
+            }
+            named_bar_sync(1 + wg, kBMH);
+            const bool fast = rb_fast &&
+                              ((myflags[cbuf * 4] | myflags[cbuf * 4 + 1] | myflags[cbuf * 4 + 2] | myflags[cbuf * 4 + 3]) == 0u);
+            const float* cj = mycols + cbuf * 128;
+
+            mbar_wait(s_full(wg), idx & 1);
+            tc_fence_after();
+            const int g_lo = p.row_begin + rb * kBM + wg * kBMH;
+            const bool pred = (j0 + kBN > p.n_k) || (g_lo < j0 + kBN && j0 < g_lo + kBMH);
+            mbar_wait(p_empty(wg), (idx & 1) ^ 1);     // MMA2 of the previous tile has consumed P
+#pragma unroll 1
+            for (int cc = 0; cc < 4; ++cc) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + lane_addr + wg * 128 + cc * 32, v);
+                tmem_ld_wait();
+                if (cc == 3) {
+                    tc_fence_before();
+                    mbar_arrive(s_empty(wg));
+                }
+                const int jc = j0 + cc * 32;
+                float pv[32];
+                if (fast) {
+#pragma unroll
+                    for (int c4 = 0; c4 < 8; ++c4) {
+                        const float4 cv = *reinterpret_cast<const float4*>(cj + cc * 32 + c4 * 4);
+                        const float cvv[4] = {cv.x, cv.y, cv.z, cv.w};
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float e = ex2(fmaf(__uint_as_float(v[c4 * 4 + u]), p.c2, -lse2_i));
+                            pv[c4 * 4 + u] = e * fmaf(R_i, cvv[u], 1.f);
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const int j = jc + c;
+                        const float x = __uint_as_float(v[c]);
+                        float e = ex2(fmaf(x, p.c2, -lse2_i));                 // lse2_i = +inf -> 0
+                        if (j < p.n_k && p.map.is_anchor(j, p.mode)) e += ex2(fmaf(x, p.c2, -p.lse_all[j] * kLog2e));
+                        pv[c] = e;
+                    }
+                }
+                if (kLabels) {
+#pragma unroll
+                    for (int c4 = 0; c4 < 8; ++c4) {
+                        const int jj = jc + c4 * 4;
+                        if (jj + 3 < p.n_k) {
+                            const int4 rj = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj));
+                            const float4 nj = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj));
+                            if (rj.x == rep_i) pv[c4 * 4 + 0] -= nia_i + nj.x;
+                            if (rj.y == rep_i) pv[c4 * 4 + 1] -= nia_i + nj.y;
+                            if (rj.z == rep_i) pv[c4 * 4 + 2] -= nia_i + nj.z;
+                            if (rj.w == rep_i) pv[c4 * 4 + 3] -= nia_i + nj.w;
+                        } else {
+                            for (int u = 0; u < 4; ++u)
+                                if (jj + u < p.n_k && p.rep_row[jj + u] == rep_i) pv[c4 * 4 + u] -= nia_i + p.nia_row[jj + u];
+                        }
+                    }
+                }
+                if (pred) {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const int j = jc + c;
+                        if (j >= p.n_k || j == gi) pv[c] = 0.f;
+                    }
+                }
+                if (!row_ok) {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) pv[c] = 0.f;
+                }
+                // bf16 pack + store in the UMMA K-major / 128B-swizzle layout
+                uint8_t* prow = myp + (cc >> 1) * kSub + r * 128;
+#pragma unroll
+                for (int qq = 0; qq < 4; ++qq) {
+                    uint4 pk;
+                    __nv_bfloat162 h0 = __floats2bfloat162_rn(pv[qq * 8 + 0], pv[qq * 8 + 1]);
+                    __nv_bfloat162 h1 = __floats2bfloat162_rn(pv[qq * 8 + 2], pv[qq * 8 + 3]);
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[qq * 8 + 4], pv[qq * 8 + 5]);
+                    __nv_bfloat162 h3 = __floats2bfloat162_rn(pv[qq * 8 + 6], pv[qq * 8 + 7]);
+                    pk.x = *reinterpret_cast<uint32_t*>(&h0);
+                    pk.y = *reinterpret_cast<uint32_t*>(&h1);
+                    pk.z = *reinterpret_cast<uint32_t*>(&h2);
+                    pk.w = *reinterpret_cast<uint32_t*>(&h3);
+                    const int chunk16 = ((cc & 1) << 2) + qq;
+                    *reinterpret_cast<uint4*>(prow + ((chunk16 ^ (r & 7)) << 4)) = pk;
+                }
+            }
+            fence_proxy_async_smem();
+            mbar_arrive(p_full(wg));
+            ++idx;
+        }
+        if (cur_rb >= 0) drain(cur_rb);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ------------------------------------------------------------------ label bookkeeping
+// rep_row[j]: smallest sample id with the same label as row j's sample (exact equality classes
+// for arbitrary int64 labels); npos_row[j] = V*count - 1; nia_row[j] = [anchor_j] / npos_row[j].
+__global__ void __launch_bounds__(256)
+label_rows_kernel(const int64_t* __restrict__ labels, int n_samples, RowMap map, int n_k, int n_views, int mode,
+                  int* __restrict__ rep_row, float* __restrict__ npos_row, float* __restrict__ nia_row) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_k) return;
+    const int64_t mine = labels[map.sid(j)];
+    int rep = -1, cnt = 0;
+    for (int s = 0; s < n_samples; ++s) {
+        const bool eq = labels[s] == mine;
+        cnt += eq ? 1 : 0;
+        if (eq && rep < 0) rep = s;
+    }
+    const float np = (float)(n_views * cnt - 1);
+    rep_row[j] = rep;
+    npos_row[j] = np;
+    nia_row[j] = map.is_anchor(j, mode) ? 1.f / np : 0.f;
+}
+
+// ------------------------------------------------------------------ dK initialisation
+// out_dk starts as the linear positive-pair term of SimCLR
+//   -(coef/T) * sum_{j: same sample, j != i} ([anchor_i] + [anchor_j]) / (V-1) * k_j
+// (zero for label masks, whose positive term is applied inside the tiles); the tile kernel then
+// accumulates the softmax part with float reductions.
+__global__ void __launch_bounds__(256)
+supcon_tc_init_dk_kernel(const __nv_bfloat16* __restrict__ k, int ldk, RowMap map, int n_views, int mode,
+                         int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
+                         float coef_scale_invT, float* __restrict__ out_dk, int ld_dk) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n_rows) return;
+    float* dst = out_dk + (int64_t)warp * ld_dk;
+    if (mask_kind != SCB_MASK_SIMCLR || n_views < 2) {
+        for (int d = lane; d < ldk; d += 32) dst[d] = 0.f;
+        return;
+    }
+    const int gi = row_begin + warp;
+    const int base = (gi / map.vseg) * map.vseg, rem = gi - base;
+    const int v = rem / map.seg, b = rem - v * map.seg;
+    const float ai = map.is_anchor(gi, mode) ? 1.f : 0.f;
+    const float c = -grad_out[0] * coef_scale_invT / (float)(n_views - 1);
+    for (int d = lane; d < ldk; d += 32) {
+        float acc = 0.f;
+        for (int vv = 0; vv < n_views; ++vv) {
+            if (vv == v) continue;
+            const int j = base + vv * map.seg + b;
+            const float aj = map.is_anchor(j, mode) ? 1.f : 0.f;
+            acc = fmaf(ai + aj, __bfloat162float(k[(int64_t)j * ldk + d]), acc);
+        }
+        dst[d] = c * acc;
+    }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn) return fn;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess || ptr == nullptr)
+        return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    return fn;
+}
+
+static int make_tmap(const scb_supcon_problem* p, CUtensorMap* out) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return SCB_ERR_CUDA; }
+    SCB_REQUIRE((reinterpret_cast<uintptr_t>(p->k) & 15u) == 0, "supcon: k must be 16-byte aligned");
+    cuuint64_t gdim[2] = {(cuuint64_t)p->ldk, (cuuint64_t)p->n_k};
+    cuuint64_t gstride[1] = {(cuuint64_t)p->ldk * 2};
+    cuuint32_t box[2] = {64, 128};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p->k), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with code %d", (int)r); return SCB_ERR_CUDA; }
+    return SCB_OK;
+}
+
+static constexpr int kMaxSlots = 32;
+
+struct TcGeom { int CT, RB, T, q, grid, n_split; };
+
+static TcGeom tc_geom(int n_k, int rows) {
+    TcGeom g;
+    g.CT = (int)ceil_div(n_k, kBN);
+    g.RB = (int)ceil_div(rows, kBM);
+    g.T = g.CT * g.RB;
+    int q = (int)ceil_div(g.T, sm_count());
+    const int qmin = (int)ceil_div(g.CT, kMaxSlots - 1);
+    if (q < qmin) q = qmin;
+    g.q = q;
+    g.grid = (int)ceil_div(g.T, q);
+    g.n_split = (int)ceil_div(g.CT, q) + 1;
+    if (g.n_split > kMaxSlots) g.n_split = kMaxSlots;
+    return g;
+}
+
+static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+
+int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows) {
+    if (p->engine == SCB_ENGINE_FP32) return 0;
+    return (int64_t)(align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float)) + 3 * align256((size_t)p->n_k * 4));
+}
+
+static int tc_supported(const scb_supcon_problem* p) {
+    if (p->engine == SCB_ENGINE_BF16X3) { set_error("the bf16x3 engine is not built yet"); return SCB_ERR_UNSUPPORTED; }
+    if (p->mask_kind == SCB_MASK_EXPLICIT) { set_error("tensor-core engine: explicit masks run on ENGINE_FP32"); return SCB_ERR_UNSUPPORTED; }
+    if (p->ldk != 64 && p->ldk != 128) { set_error("tensor-core engine: ldk must be 64 or 128 (dim <= 128), got %d", p->ldk); return SCB_ERR_UNSUPPORTED; }
+    return SCB_OK;
+}
+
+static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, int a_count, const TcGeom& g,
+                        void* workspace, TcParams* t) {
+    t->k = (const __nv_bfloat16*)p->k;
+    t->ldk = p->ldk; t->n_k = p->n_k; t->dim = p->dim;
+    t->row_begin = row_begin; t->n_rows = n_rows; t->a_count = a_count;
+    t->CT = g.CT; t->RB = g.RB; t->T = g.T; t->q = g.q;
+    t->map = RowMap::of(p);
+    t->n_views = p->n_views; t->mode = p->mode; t->mask_kind = p->mask_kind;
+    t->c2 = p->inv_temperature * kLog2e;
+    t->inv_T = p->inv_temperature;
+    char* ws = (char*)workspace;
+    t->part = (float*)ws;
+    ws += align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float));
+    t->rep_row = (const int*)ws; ws += align256((size_t)p->n_k * 4);
+    t->npos_row = (const float*)ws; ws += align256((size_t)p->n_k * 4);
+    t->nia_row = (const float*)ws;
+    t->lse_all = nullptr; t->grad_out = nullptr; t->coef_scale = 0.f; t->out_dk = nullptr; t->ld_dk = 0;
+}
+
+static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, cudaStream_t stream) {
+    if (p->mask_kind != SCB_MASK_LABELS) return SCB_OK;
+    label_rows_kernel<<<(unsigned)ceil_div(p->n_k, 256), 256, 0, stream>>>(
+        p->labels, p->n_seg * p->seg, t.map, p->n_k, p->n_views, p->mode, (int*)t.rep_row, (float*)t.npos_row,
+        (float*)t.nia_row);
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+template <typename Kern>
+static int set_smem(Kern kern, size_t bytes) {
+    SCB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return SCB_OK;
+}
+
+int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* part, int* n_split, int* q_out,
+               int* ct_out, cudaStream_t stream) {
+    if (int e = tc_supported(p)) return e;
+    CUtensorMap tmap;
+    if (int e = make_tmap(p, &tmap)) return e;
+    const int a_count = (p->mode == SCB_MODE_ALL) ? n_rows : (n_rows < p->seg ? n_rows : p->seg);
+    const TcGeom g = tc_geom(p->n_k, a_count);
+    TcParams t;
+    fill_params(p, row_begin, n_rows, a_count, g, part, &t);
+    if (int e = launch_label_rows(p, t, stream)) return e;
+    const int kch = p->ldk / 64;
+    const size_t smem = (size_t)2 * (2 * kch * kSub) + 2 * (kch * kSub) + 16 * 8 + 16;
+    const bool lab = p->mask_kind == SCB_MASK_LABELS;
+#define SCB_LAUNCH_FWD(KCH_, LAB_)                                                                      \
+    do {                                                                                                \
+        if (int e = set_smem(supcon_tc_fwd_kernel<KCH_, LAB_>, smem)) return e;                         \
+        supcon_tc_fwd_kernel<KCH_, LAB_><<<g.grid, kThreads, smem, stream>>>(tmap, t);                  \
+    } while (0)
+    if (kch == 2) { if (lab) SCB_LAUNCH_FWD(2, true); else SCB_LAUNCH_FWD(2, false); }
+    else { if (lab) SCB_LAUNCH_FWD(1, true); else SCB_LAUNCH_FWD(1, false); }
+#undef SCB_LAUNCH_FWD
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    *n_split = g.n_split;
+    *q_out = g.q;
+    *ct_out = g.CT;
+    return SCB_OK;
+}
+
+int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all, const float* npos_all,
+                const float* grad_out, int n_anchor_total, float* out_dk, int ld_dk, void* workspace,
+                cudaStream_t stream) {
+    (void)npos_all;
+    if (int e = tc_supported(p)) return e;
+    SCB_REQUIRE(ld_dk >= p->ldk && ld_dk % 4 == 0 && (reinterpret_cast<uintptr_t>(out_dk) & 15u) == 0,
+                "supcon_backward (tensor-core engine): out_dk must be 16-byte aligned with ld_dk >= ldk (%d)", p->ldk);
+    CUtensorMap tmap;
+    if (int e = make_tmap(p, &tmap)) return e;
+    const TcGeom g = tc_geom(p->n_k, n_rows);
+    TcParams t;
+    fill_params(p, row_begin, n_rows, n_rows, g, workspace, &t);
+    t.lse_all = lse_all; t.grad_out = grad_out;
+    t.coef_scale = p->loss_scale / (float)n_anchor_total;
+    t.out_dk = out_dk; t.ld_dk = ld_dk;
+    if (int e = launch_label_rows(p, t, stream)) return e;
+    supcon_tc_init_dk_kernel<<<(unsigned)ceil_div((int64_t)n_rows * 32, 256), 256, 0, stream>>>(
+        t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows, grad_out,
+        t.coef_scale * p->inv_temperature, out_dk, ld_dk);
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    const int kch = p->ldk / 64;
+    const size_t smem = (size_t)(2 * kch * kSub) + 3 * (kch * kSub) + 2 * (2 * kSub) + 2 * 2 * 128 * 4 + 64 + 64 +
+                        16 * 8 + 8 + 16;
+    const bool lab = p->mask_kind == SCB_MASK_LABELS;
+#define SCB_LAUNCH_BWD(KCH_, LAB_)                                                                      \
+    do {                                                                                                \
+        if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, LAB_>, smem)) return e;                         \
+        supcon_tc_bwd_kernel<KCH_, LAB_><<<g.grid, kThreads, smem, stream>>>(tmap, t);                  \
+    } while (0)
+    if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
+    else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
+#undef SCB_LAUNCH_BWD
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
 }
 
 }  // namespace scb

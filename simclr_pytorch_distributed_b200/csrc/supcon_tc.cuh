@@ -7,8 +7,9 @@ namespace scb {
 int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows);
 
 // writes per-row partials [n_split][4][n_rows] = (max, sum exp, possum, npos) like the fp32 engine
-int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* part, int* n_split,
-               cudaStream_t stream);
+// (slots of a row block = the CTAs whose tile span overlaps it: q tiles per CTA, ct column tiles)
+int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* part, int* n_split, int* q,
+               int* ct, cudaStream_t stream);
 
 int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
                 const float* npos_all, const float* grad_out, int n_anchor_total, float* out_dk,

@@ -42,7 +42,7 @@ class _Workspace:
 
 def tc_engine_supported(dim, mask_kind, n_k):
     """Shapes the tcgen05 engine takes; everything else runs on the fp32 engine."""
-    return mask_kind != _lib.MASK_EXPLICIT and dim <= 256 and n_k >= 1
+    return mask_kind != _lib.MASK_EXPLICIT and dim <= 128 and n_k >= 1
 
 
 def select_engine(requested, feat_dtype, dim, mask_kind, n_k):
@@ -50,7 +50,8 @@ def select_engine(requested, feat_dtype, dim, mask_kind, n_k):
     if req == 'auto':
         if not tc_engine_supported(dim, mask_kind, n_k):
             return _lib.ENGINE_FP32
-        return _lib.ENGINE_BF16 if feat_dtype in (torch.bfloat16, torch.float16) else _lib.ENGINE_BF16X3
+        # fp32 features keep fp32 arithmetic (the reference's); 16-bit features take the tensor cores
+        return _lib.ENGINE_BF16 if feat_dtype in (torch.bfloat16, torch.float16) else _lib.ENGINE_FP32
     if req not in _ENGINES:
         raise ValueError('Unknown engine: {}'.format(req))
     eng = _ENGINES[req]
@@ -164,7 +165,7 @@ class _SupConFunction(torch.autograd.Function):
         dev = feats.device
         with torch.cuda.device(dev):
             g = grad_out.detach().to(torch.float32).contiguous()
-            dk = torch.empty((plan.rows_local, plan.dim), dtype=torch.float32, device=dev)
+            dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
             prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
             launch_backward(lib, prob, plan, stats[0], stats[2], g, dk, dev)
             dfeats = torch.empty(feats.shape, dtype=feats.dtype, device=dev)

@@ -142,7 +142,7 @@ def test_matches_aten_sync_ops_on_gpu():
     count = torch.full((1,), x.numel() // 256, dtype=torch.int32, device=DEV)
     dx_ref = torch.batch_norm_backward_elemt(dy, x, mean, invstd, w, sum_dy, sum_dy_xmu, count)
     y, dx, gw, gb = ours_fwd_bwd(x, dy, bn)
-    ulp = 2.0 ** -8
+    ulp = 2.0 ** -7      # both sides are rounded to bf16 independently: they may land one ulp apart
     assert torch.all((y.float() - y_ref.float()).abs() <= ulp * y_ref.float().abs() + 1e-5)
     assert torch.all((dx.float() - dx_ref.float()).abs() <= ulp * dx_ref.float().abs() + 1e-5)
     assert torch.allclose(gw, gw_ref, rtol=1e-4, atol=1e-3)
