@@ -84,7 +84,7 @@ extern "C" int64_t scb_supcon_workspace_bytes(const scb_supcon_problem* p, int n
     if (!p || n_rows < 1) return 0;
     int64_t fp32 = (int64_t)64 * 4 * n_rows * sizeof(float);
     int64_t tc = tc_workspace_bytes(p, n_rows);
-    return (fp32 > tc ? fp32 : tc) + 256;
+    return (fp32 > tc ? fp32 : tc) + kFinScratchBytes + 256;
 }
 
 extern "C" int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, int n_rows,
@@ -96,7 +96,8 @@ extern "C" int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, in
     SCB_REQUIRE(n_anchor_total >= 1, "supcon_forward: n_anchor_total must be >= 1");
     SCB_REQUIRE(workspace_bytes >= scb_supcon_workspace_bytes(p, n_rows), "supcon_forward: workspace too small");
     cudaStream_t stream = (cudaStream_t)stream_;
-    float* part = (float*)workspace;
+    // workspace = [finalize scratch (zeroed, self-cleaning) | engine scratch]
+    float* part = (float*)((char*)workspace + kFinScratchBytes);
     int n_split = 1, flat_q = 0, flat_ct = 0;
     if (p->engine == SCB_ENGINE_FP32) {
         n_split = fp32_splits(n_rows, p->n_k);
@@ -105,7 +106,7 @@ extern "C" int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, in
         if (int e = tc_forward(p, row_begin, n_rows, part, &n_split, &flat_q, &flat_ct, stream)) return e;
     }
     return launch_finalize(p, part, n_split, flat_q, flat_ct, row_begin, n_rows, 1.0 / (double)n_anchor_total, out_lse,
-                           out_possum, out_npos, out_loss_sum, stream);
+                           out_possum, out_npos, out_loss_sum, workspace, stream);
 }
 
 extern "C" int scb_supcon_backward(const scb_supcon_problem* p, int row_begin, int n_rows,
@@ -122,5 +123,5 @@ extern "C" int scb_supcon_backward(const scb_supcon_problem* p, int row_begin, i
     SCB_REQUIRE(workspace && workspace_bytes >= scb_supcon_workspace_bytes(p, n_rows),
                 "supcon_backward: workspace too small");
     return tc_backward(p, row_begin, n_rows, lse_all, npos_all, grad_out, n_anchor_total, out_dk, ld_dk,
-                       workspace, stream);
+                       (char*)workspace + kFinScratchBytes, stream);
 }

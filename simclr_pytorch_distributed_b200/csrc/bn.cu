@@ -106,12 +106,17 @@ bn_stats_nhwc_kernel(const T* __restrict__ x, int64_t M, int C, int TX, int64_t 
 #pragma unroll
     for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; shift[i] = 0.f; }
     if (active) {
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) shift[i] = to_f32(x[c0 + i]);
+        // The thread accumulates around its own first row (no dependent load in front of the
+        // stream); the common reference K_c = x[0, c] is fetched alongside and only used at the
+        // end to re-centre the two sums so that they add across threads and CTAs.
+        float k0[VEC];
+        load_row_vec<T, VEC>(x + c0, k0);
         const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
         int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
+        const int64_t r_first = r;
         const T* p = x + r * C + c0;
         const int64_t step = (int64_t)TY * C;
+        if (r < r_end) load_row_vec<T, VEC>(p, shift);
         for (; r + (kUnroll - 1) * TY < r_end; r += kUnroll * TY, p += kUnroll * step) {
             float v[kUnroll][VEC];
 #pragma unroll
@@ -134,6 +139,14 @@ bn_stats_nhwc_kernel(const T* __restrict__ x, int64_t M, int C, int TX, int64_t 
                 s1[i] += d;
                 s2[i] = fmaf(d, d, s2[i]);
             }
+        }
+        // re-centre on K_c:  sum (x-K) = s1 + n d,  sum (x-K)^2 = s2 + 2 d s1 + n d^2,  d = shift - K
+        const float nt = r_first < r_end ? (float)((r_end - r_first + TY - 1) / TY) : 0.f;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            const float d = shift[i] - k0[i];
+            s2[i] = s2[i] + d * (2.f * s1[i] + nt * d);
+            s1[i] = fmaf(nt, d, s1[i]);
         }
     }
     cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
@@ -186,6 +199,19 @@ bn_apply_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int 
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int W = TX * VEC;
     const int tile_c0 = blockIdx.x * W;
+    // Put the first batch of row loads in flight before the (dependent) coefficient prologue.
+    const int c0 = tile_c0 + tx * VEC;
+    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
+    int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
+    const int64_t step = (int64_t)TY * C;
+    const T* p = x + r * C + c0;
+    T* q = y + r * C + c0;
+    float v0[kUnroll][VEC];
+    if (c0 < C) {
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (r + (int64_t)u * TY < r_end) load_row_vec<T, VEC>(p + u * step, v0[u]);
+    }
     for (int t = threadIdx.x; t < W; t += kBnThreads) {
         const int c = tile_c0 + t;
         float a = 0.f, b = 0.f;
@@ -209,17 +235,23 @@ bn_apply_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int 
         sm[W + t] = b;
     }
     __syncthreads();
-    const int c0 = tile_c0 + tx * VEC;
     if (c0 >= C) return;
     float a[VEC], b[VEC];
 #pragma unroll
     for (int i = 0; i < VEC; ++i) { a[i] = sm[tx * VEC + i]; b[i] = sm[W + tx * VEC + i]; }
     const bool relu = (flags & SCB_BN_RELU) != 0;
-    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
-    int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
-    const int64_t step = (int64_t)TY * C;
-    const T* p = x + r * C + c0;
-    T* q = y + r * C + c0;
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+        if (r + (int64_t)u * TY < r_end) {
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                float o = fmaf(v0[u][i], a[i], b[i]);
+                v0[u][i] = relu ? fmaxf(o, 0.f) : o;
+            }
+            store_row_vec<T, VEC>(q + u * step, v0[u]);
+        }
+    }
+    r += kUnroll * TY; p += kUnroll * step; q += kUnroll * step;
     for (; r + (kUnroll - 1) * TY < r_end; r += kUnroll * TY, p += kUnroll * step, q += kUnroll * step) {
         float v[kUnroll][VEC];
 #pragma unroll
@@ -277,7 +309,7 @@ bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, int
         const int64_t step = (int64_t)TY * C;
         const T* px = x + r * C + c0;
         const T* pd = dy + r * C + c0;
-        constexpr int U = 2;   // 2 rows x 2 tensors = 4 vector loads in flight
+        constexpr int U = 4;   // 4 rows x 2 tensors = 8 vector loads in flight
         for (; r + (U - 1) * TY < r_end; r += U * TY, px += U * step, pd += U * step) {
             float vx[U][VEC], vd[U][VEC];
 #pragma unroll
@@ -354,7 +386,7 @@ bn_bwd_apply_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
     const T* px = x + r * C + c0;
     const T* pd = dy + r * C + c0;
     T* po = dx + r * C + c0;
-    constexpr int U = 2;
+    constexpr int U = 4;
     for (; r + (U - 1) * TY < r_end; r += U * TY, px += U * step, pd += U * step, po += U * step) {
         float vx[U][VEC], vd[U][VEC];
 #pragma unroll
@@ -602,7 +634,7 @@ extern "C" int scb_bn_stats(const void* x, int dtype, int channels_last, int64_t
     }
     float* acc = (float*)workspace;
     unsigned* counter = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
-    const int target = 2 * sm_count();
+    const int target = 4 * sm_count();   // one resident wave: every load of the pass is in flight at once
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;
@@ -677,7 +709,7 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, 
     }
     float* acc = (float*)workspace;
     unsigned* counter = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
-    const int target = 2 * sm_count();
+    const int target = 4 * sm_count();   // one resident wave: every load of the pass is in flight at once
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;

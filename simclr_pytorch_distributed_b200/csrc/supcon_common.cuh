@@ -47,6 +47,7 @@ int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const 
 // flat_q > 0: tensor-core engine, row block rb (256 rows) owns slots of the CTAs overlapping its tiles
 int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int flat_q, int flat_ct,
                     int row_begin, int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
-                    float* out_loss_sum, cudaStream_t stream);
+                    float* out_loss_sum, void* scratch, cudaStream_t stream);
+constexpr int kFinScratchBytes = 4096;   // ticket + per-CTA partial sums of the finalize kernel
 
 }  // namespace scb

@@ -21,6 +21,39 @@ supcon_prep_kernel(const TI* __restrict__ feat, int n_samples, int n_views, int 
     if (warp >= n_rows) return;
     const int v = warp / n_samples, b = warp - v * n_samples;     // out row = v*n_samples + b
     const TI* src = feat + (int64_t)b * stride_s + (int64_t)v * stride_v;
+    TO* dst = out_k + (int64_t)warp * ldk;
+    // fast path (the common D = 128): a lane owns 4 consecutive elements, one vector access each way
+    const bool vec4 = (ldk == 128) && (dim == 128) && !out_lo &&
+                      ((reinterpret_cast<uintptr_t>(src) & (4 * sizeof(TI) - 1)) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(dst) & (4 * sizeof(TO) - 1)) == 0);
+    if (vec4) {
+        float x[4];
+        if constexpr (sizeof(TI) == 4) {
+            const float4 t = *reinterpret_cast<const float4*>(src + lane * 4);
+            x[0] = t.x; x[1] = t.y; x[2] = t.z; x[3] = t.w;
+        } else {
+            const uint2 t = *reinterpret_cast<const uint2*>(src + lane * 4);
+            const TI* e = reinterpret_cast<const TI*>(&t);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x[i] = to_f32(e[i]);
+        }
+        float inv = 1.f;
+        if (normalize) {
+            const float ss = warp_sum(x[0] * x[0] + x[1] * x[1] + x[2] * x[2] + x[3] * x[3]);
+            inv = 1.f / fmaxf(sqrtf(ss), eps);
+        }
+        if (lane == 0 && out_inv_norm) out_inv_norm[warp] = inv;
+        if constexpr (sizeof(TO) == 4) {
+            *reinterpret_cast<float4*>(dst + lane * 4) = make_float4(x[0] * inv, x[1] * inv, x[2] * inv, x[3] * inv);
+        } else {
+            uint2 o;
+            TO* e = reinterpret_cast<TO*>(&o);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) e[i] = from_f32<TO>(x[i] * inv);
+            *reinterpret_cast<uint2*>(dst + lane * 4) = o;
+        }
+        return;
+    }
     float inv = 1.f;
     if (normalize) {
         float ss = 0.f;
@@ -29,7 +62,6 @@ supcon_prep_kernel(const TI* __restrict__ feat, int n_samples, int n_views, int 
         inv = 1.f / fmaxf(sqrtf(ss), eps);                         // F.normalize: x / max(||x||, eps)
     }
     if (lane == 0 && out_inv_norm) out_inv_norm[warp] = inv;
-    TO* dst = out_k + (int64_t)warp * ldk;
     for (int d = lane; d < ldk; d += 32) {
         const float x = d < dim ? to_f32(src[d]) * inv : 0.f;
         const TO hi = from_f32<TO>(x);
@@ -51,6 +83,44 @@ supcon_finish_kernel(const float* __restrict__ dk, int ld_dk, const TF* __restri
     const int v = warp / n_samples, b = warp - v * n_samples;
     const float* g = dk + (int64_t)warp * ld_dk;
     TF* dst = out + (int64_t)b * ostride_s + (int64_t)v * ostride_v;
+    // fast path (D = 128): 4 consecutive elements per lane, vector loads/stores
+    if (dim == 128 && (ld_dk & 3) == 0 && (reinterpret_cast<uintptr_t>(dk) & 15) == 0 &&
+        (reinterpret_cast<uintptr_t>(dst) & (4 * sizeof(TF) - 1)) == 0 &&
+        (!normalize || (reinterpret_cast<uintptr_t>(feat + (int64_t)b * stride_s + (int64_t)v * stride_v) &
+                        (4 * sizeof(TF) - 1)) == 0)) {
+        const float4 gv = *reinterpret_cast<const float4*>(g + lane * 4);
+        float o[4] = {gv.x, gv.y, gv.z, gv.w};
+        if (normalize) {
+            const TF* src = feat + (int64_t)b * stride_s + (int64_t)v * stride_v;
+            const float inv = inv_norm[warp];
+            float z[4];
+            if constexpr (sizeof(TF) == 4) {
+                const float4 t = *reinterpret_cast<const float4*>(src + lane * 4);
+                z[0] = t.x; z[1] = t.y; z[2] = t.z; z[3] = t.w;
+            } else {
+                const uint2 t = *reinterpret_cast<const uint2*>(src + lane * 4);
+                const TF* e = reinterpret_cast<const TF*>(&t);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) z[i] = to_f32(e[i]);
+            }
+            float dot = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { z[i] *= inv; dot = fmaf(o[i], z[i], dot); }
+            dot = warp_sum(dot);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[i] = (o[i] - z[i] * dot) * inv;
+        }
+        if constexpr (sizeof(TF) == 4) {
+            *reinterpret_cast<float4*>(dst + lane * 4) = make_float4(o[0], o[1], o[2], o[3]);
+        } else {
+            uint2 pk;
+            TF* e = reinterpret_cast<TF*>(&pk);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) e[i] = from_f32<TF>(o[i]);
+            *reinterpret_cast<uint2*>(dst + lane * 4) = pk;
+        }
+        return;
+    }
     if (!normalize) {
         for (int d = lane; d < dim; d += 32) dst[d] = from_f32<TF>(g[d]);
         return;
@@ -68,17 +138,25 @@ supcon_finish_kernel(const float* __restrict__ dk, int ld_dk, const TF* __restri
 
 // ------------------------------------------------------------------ finalize (merge column splits)
 // partials: [n_split][4][n_rows] = (running max m, sum exp(s - m), possum, npos) per local row.
-// One CTA, fixed summation order -> deterministic loss.
-__global__ void __launch_bounds__(1024)
+// One row per thread; every CTA leaves its partial loss in `scratch`, the last CTA to finish
+// (ticket counter, self-resetting) adds them in CTA order -> deterministic loss, no atomics on
+// floating-point data.  scratch: [0] ticket counter, doubles from byte 16 on (zero on entry).
+constexpr int kFinThreads = 256;
+constexpr int kFinMaxCtas = 480;
+
+__global__ void __launch_bounds__(kFinThreads)
 supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_q, int flat_ct, int n_rows,
                        int row_begin,
                        RowMap map, int mode, float loss_scale, double inv_anchors,
                        float* __restrict__ out_lse,
                        float* __restrict__ out_possum, float* __restrict__ out_npos,
-                       float* __restrict__ out_loss_sum) {
+                       float* __restrict__ out_loss_sum, void* scratch) {
     __shared__ double red[32];
+    __shared__ unsigned s_last;
+    unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+    double* cta_sum = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + 16);
     double local = 0.0;
-    for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
         float lse = 0.f, ps = 0.f, np = 1.f;
         if (map.is_anchor(row_begin + r, mode)) {
             int n_split = n_split_in;
@@ -106,7 +184,22 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
     if (threadIdx.x < 32) {
         double t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-        if (threadIdx.x == 0) out_loss_sum[0] = (float)(t * inv_anchors);
+        if (threadIdx.x == 0) {
+            cta_sum[blockIdx.x] = t;
+            __threadfence();
+            s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+        }
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        __threadfence();
+        double t = 0.0;
+        for (unsigned b = 0; b < gridDim.x; ++b) {
+            t += __ldcg(cta_sum + b);
+            cta_sum[b] = 0.0;
+        }
+        out_loss_sum[0] = (float)(t * inv_anchors);
+        *ticket = 0u;
     }
 }
 
@@ -252,10 +345,12 @@ int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const 
 
 int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int flat_q, int flat_ct,
                     int row_begin, int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
-                    float* out_loss_sum, cudaStream_t stream) {
-    supcon_finalize_kernel<<<1, 1024, 0, stream>>>(part, n_split, flat_q, flat_ct, n_rows, row_begin, RowMap::of(p),
-                                                   p->mode, p->loss_scale, inv_anchors, out_lse, out_possum,
-                                                   out_npos, out_loss_sum);
+                    float* out_loss_sum, void* scratch, cudaStream_t stream) {
+    int ctas = (int)ceil_div(n_rows, kFinThreads);
+    if (ctas > kFinMaxCtas) ctas = kFinMaxCtas;
+    supcon_finalize_kernel<<<ctas, kFinThreads, 0, stream>>>(part, n_split, flat_q, flat_ct, n_rows, row_begin,
+                                                             RowMap::of(p), p->mode, p->loss_scale, inv_anchors,
+                                                             out_lse, out_possum, out_npos, out_loss_sum, scratch);
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     return SCB_OK;

@@ -222,34 +222,36 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             const int j0 = ct * kBN;
             const int g_lo = p.row_begin + rb * kBM + wg * kBMH;
             const bool pred = (j0 + kBN > p.n_k) || (g_lo < j0 + kBN && j0 < g_lo + kBMH);
-#pragma unroll 1
-            for (int cc = 0; cc < 4; ++cc) {
-                uint32_t v[32];
-                tmem_ld32(tmem_base + lane_addr + sbuf * 256 + wg * 128 + cc * 32, v);
-                tmem_ld_wait();
-                if (cc == 3) {
-                    tc_fence_before();
-                    mbar_arrive(s_empty(wg, sbuf));
-                }
+            const uint32_t taddr = tmem_base + lane_addr + sbuf * 256 + wg * 128;
+            // one 32-column chunk of this thread's row: online (max, sum) update + positive sum
+            auto process = [&](uint32_t (&v)[32], int cc) {
                 const int jc = j0 + cc * 32;
                 if (!pred) {
-                    float cmax = __uint_as_float(v[0]);
+                    float m8[8];
 #pragma unroll
-                    for (int c = 1; c < 32; ++c) cmax = fmaxf(cmax, __uint_as_float(v[c]));
+                    for (int i = 0; i < 8; ++i)
+                        m8[i] = fmaxf(fmaxf(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1])),
+                                      fmaxf(__uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3])));
+                    const float cmax = fmaxf(fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3])),
+                                             fmaxf(fmaxf(m8[4], m8[5]), fmaxf(m8[6], m8[7])));
                     const float nm = fmaxf(m, cmax * p.c2);
                     sum *= ex2(m - nm);
                     m = nm;
+                    float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) sum += ex2(fmaf(__uint_as_float(v[c]), p.c2, -m));
+                    for (int c = 0; c < 32; ++c) acc[c & 3] += ex2(fmaf(__uint_as_float(v[c]), p.c2, -m));
+                    sum += (acc[0] + acc[1]) + (acc[2] + acc[3]);
                     if (kLabels) {
+                        float pacc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                         for (int c4 = 0; c4 < 8; ++c4) {
                             const int4 rj = __ldg(reinterpret_cast<const int4*>(p.rep_row + jc) + c4);
-                            possum += (rj.x == rep_i) ? __uint_as_float(v[c4 * 4 + 0]) : 0.f;
-                            possum += (rj.y == rep_i) ? __uint_as_float(v[c4 * 4 + 1]) : 0.f;
-                            possum += (rj.z == rep_i) ? __uint_as_float(v[c4 * 4 + 2]) : 0.f;
-                            possum += (rj.w == rep_i) ? __uint_as_float(v[c4 * 4 + 3]) : 0.f;
+                            pacc[0] += (rj.x == rep_i) ? __uint_as_float(v[c4 * 4 + 0]) : 0.f;
+                            pacc[1] += (rj.y == rep_i) ? __uint_as_float(v[c4 * 4 + 1]) : 0.f;
+                            pacc[2] += (rj.z == rep_i) ? __uint_as_float(v[c4 * 4 + 2]) : 0.f;
+                            pacc[3] += (rj.w == rep_i) ? __uint_as_float(v[c4 * 4 + 3]) : 0.f;
                         }
+                        possum += (pacc[0] + pacc[1]) + (pacc[2] + pacc[3]);
                     }
                 } else {
                     // tiles that contain the self column (losses.py:74-79) or run past n_k
@@ -278,7 +280,23 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                         }
                     }
                 }
-            }
+            };
+            // software pipeline over the 4 chunks: the TMEM load of chunk c+1 flies while chunk c is processed
+            uint32_t va[32], vb[32];
+            tmem_ld32(taddr, va);
+            tmem_ld_wait_dep(va);
+            tmem_ld32(taddr + 32, vb);
+            process(va, 0);
+            tmem_ld_wait_dep(vb);
+            tmem_ld32(taddr + 64, va);
+            process(vb, 1);
+            tmem_ld_wait_dep(va);
+            tmem_ld32(taddr + 96, vb);
+            process(va, 2);
+            tmem_ld_wait_dep(vb);
+            tc_fence_before();
+            mbar_arrive(s_empty(wg, sbuf));      // S buffer is free for the next MMA
+            process(vb, 3);
             ++idx;
         }
         if (cur_rb >= 0) flush(cur_rb);
@@ -293,47 +311,52 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
 }
 
 // =================================================================================== backward
-// smem: A[2*KCH*kSub] | B[3][KCH*kSub] | P[2][2*kSub] | cols[2 wg][2 buf][128] f32 | flags | barriers | tmem slot
-// TMEM: S[h] at columns h*128, dK[h] at columns 256 + h*128.
+// 18 warps: warp 0 TMA, warp 1 MMA issue + TMEM, warps 2..17 = four epilogue warpgroups.
+// Warpgroup w = (h, a) owns row half h and column half a of every tile, so the unit of the
+// MMA <-> epilogue hand-over is a [128 x 64] sub-tile: S[w] (64 TMEM columns) and P[w] (one
+// 16 KB swizzled sub-tile in shared memory).  While one warpgroup waits for its MMA2 + next MMA1
+// the other three keep the MUFU pipe busy.
+// smem: A[2*KCH*kSub] | B[3][KCH*kSub] | P[4][kSub] | cols[4][2][64] f32 | flags | rowred | barriers | tmem slot
+// TMEM: S[w] at columns w*64, dK[h] at columns 256 + h*128.
+constexpr int kBwdThreads = 64 + 512;
+
 template <int KCH, bool kLabels>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kBwdThreads, 1)
 supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int A_BYTES = 2 * KCH * kSub;
     constexpr int B_BYTES = KCH * kSub;
-    constexpr int P_BYTES = 2 * kSub;                  // one half: [128 rows x 128 cols] bf16
     constexpr int NSB = 3;
     uint8_t* a_smem = smem;
     uint8_t* b_smem = a_smem + A_BYTES;
-    uint8_t* p_smem = b_smem + NSB * B_BYTES;
-    float* cols = reinterpret_cast<float*>(p_smem + 2 * P_BYTES);       // [2][2][128]
-    uint32_t* flags = reinterpret_cast<uint32_t*>(cols + 2 * 2 * 128);  // [2 wg][2 buf][4 warps]
-    float* rowred = reinterpret_cast<float*>(flags + 16);               // [2 wg][4 warps][2]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(rowred + 16);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    uint8_t* p_smem = b_smem + NSB * B_BYTES;                            // [4][kSub]
+    float* cols = reinterpret_cast<float*>(p_smem + 4 * kSub);            // [4 wg][2 buf][64]
+    uint32_t* flags = reinterpret_cast<uint32_t*>(cols + 4 * 2 * 64);     // [4 wg][2 buf][2 warps]
+    float* rowred = reinterpret_cast<float*>(flags + 16);                 // [4 wg][4 warps][2]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(rowred + 32);            // 26 used
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 28);
     const uint32_t bar0 = smem_u32(bars);
-    // barrier map: 0 a_full, 1 a_empty, 2-4 b_full, 5-7 b_empty, 8-9 s_full, 10-11 s_empty,
-    //              12-13 p_full, 14-15 p_empty ... dz_full / dz_empty live in two extra slots
     auto a_full = [&]() { return bar0 + 8u * 0; };
     auto a_empty = [&]() { return bar0 + 8u * 1; };
     auto b_full = [&](int s) { return bar0 + 8u * (2 + s); };
     auto b_empty = [&](int s) { return bar0 + 8u * (5 + s); };
-    auto s_full = [&](int h) { return bar0 + 8u * (8 + h); };
-    auto s_empty = [&](int h) { return bar0 + 8u * (10 + h); };
-    auto p_full = [&](int h) { return bar0 + 8u * (12 + h); };
-    auto p_empty = [&](int h) { return bar0 + 8u * (14 + h); };
-    uint64_t* bars2 = reinterpret_cast<uint64_t*>(tmem_slot + 2);
-    const uint32_t dz_full = smem_u32(bars2), dz_empty = smem_u32(bars2 + 1);
+    auto s_full = [&](int w) { return bar0 + 8u * (8 + w); };
+    auto s_empty = [&](int w) { return bar0 + 8u * (12 + w); };
+    auto p_full = [&](int w) { return bar0 + 8u * (16 + w); };
+    auto p_empty = [&](int w) { return bar0 + 8u * (20 + w); };
+    const uint32_t dz_full = bar0 + 8u * 24, dz_empty = bar0 + 8u * 25;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 10; ++i) mbar_init(bar0 + 8u * i, 1);     // a, b, s_full
-        mbar_init(s_empty(0), kBMH); mbar_init(s_empty(1), kBMH);
-        mbar_init(p_full(0), kBMH); mbar_init(p_full(1), kBMH);
-        mbar_init(p_empty(0), 1); mbar_init(p_empty(1), 1);
+        for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);          // a, b, s_full
+        for (int w = 0; w < 4; ++w) {
+            mbar_init(s_empty(w), kBMH);
+            mbar_init(p_full(w), kBMH);
+            mbar_init(p_empty(w), 1);
+        }
         mbar_init(dz_full, 1);
-        mbar_init(dz_empty, 2 * kBMH);
+        mbar_init(dz_empty, 4 * kBMH);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -376,105 +399,114 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     } else if (warp == 1) {
         if (lane == 0 && t0 < t1) {
             // ------------------------------------------------ MMA issuer
-            constexpr uint32_t idesc1 = idesc_bf16(128, 128, 0);
+            constexpr uint32_t idesc1 = idesc_bf16(128, 64, 0);
             constexpr uint32_t idesc2 = idesc_bf16(128, KCH * 64, 1);
             int n_a = 0, n_dz = 0;
-            int n_s[2] = {0, 0};
             const int n_tiles = t1 - t0;
 
-            // S[h] = A_h * B^T for tile number `i` of the span (half h)
-            auto mma1 = [&](int i, int h) {
+            // S[w] = A_h (128 rows) x B rows [a*64, a*64+64)^T of tile i
+            auto mma1 = [&](int i, int w) {
+                const int h = w >> 1, a = w & 1;
                 const int tau = t0 + i;
                 const int rb = tau / p.CT;
                 const bool first_of_rb = (i == 0) || ((tau - 1) / p.CT != rb);
                 const bool last_of_rb = (i == n_tiles - 1) || ((tau + 1) / p.CT != rb);
                 const int st = i % NSB;
-                if (h == 0) {
+                if (w == 0) {
                     if (first_of_rb) { mbar_wait(a_full(), n_a & 1); ++n_a; }
                     mbar_wait(b_full(st), (i / NSB) & 1);
                 }
-                mbar_wait(s_empty(h), (n_s[h] & 1) ^ 1);
-                ++n_s[h];
+                mbar_wait(s_empty(w), (i & 1) ^ 1);
                 tc_fence_after();
-                const uint32_t d = tmem_base + h * 128;
+                const uint32_t d = tmem_base + w * 64;
                 const uint32_t a0 = smem_u32(a_smem + h * KCH * kSub);
-                const uint32_t b0 = smem_u32(b_smem + st * B_BYTES);
+                const uint32_t b0 = smem_u32(b_smem + st * B_BYTES) + a * 8192;
 #pragma unroll
                 for (int k16 = 0; k16 < KCH * 4; ++k16) {
                     const uint32_t off = (k16 >> 2) * kSub + (k16 & 3) * 32;
                     umma_bf16(d, smem_desc_sw128(a0 + off, 16, 1024), smem_desc_sw128(b0 + off, 16, 1024), idesc1,
                               k16 > 0 ? 1u : 0u);
                 }
-                umma_commit(s_full(h));
-                if (h == 1 && last_of_rb) umma_commit(a_empty());
+                umma_commit(s_full(w));
+                if (w == 3 && last_of_rb) umma_commit(a_empty());
             };
-            // dK[h] += P_h * K_j  (K_j read MN-major from the same stage)
-            auto mma2 = [&](int i, int h) {
+            // dK[h] += P[w] (128 x 64, K-major) x K_j rows [a*64, a*64+64) read MN-major
+            auto mma2 = [&](int i, int w) {
+                const int h = w >> 1, a = w & 1;
                 const int tau = t0 + i;
                 const int rb = tau / p.CT;
                 const bool first_of_rb = (i == 0) || ((tau - 1) / p.CT != rb);
                 const bool last_of_rb = (i == n_tiles - 1) || ((tau + 1) / p.CT != rb);
                 const int st = i % NSB;
-                mbar_wait(p_full(h), i & 1);
-                if (h == 0 && first_of_rb) { mbar_wait(dz_empty, (n_dz & 1) ^ 1); }
+                mbar_wait(p_full(w), i & 1);
+                if (w == 0 && first_of_rb) mbar_wait(dz_empty, (n_dz & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t d = tmem_base + 256 + h * 128;
-                const uint32_t a0 = smem_u32(p_smem + h * P_BYTES);
-                const uint32_t b0 = smem_u32(b_smem + st * B_BYTES);
+                const uint32_t a0 = smem_u32(p_smem + w * kSub);
+                const uint32_t b0 = smem_u32(b_smem + st * B_BYTES) + a * 8192;
 #pragma unroll
-                for (int j16 = 0; j16 < 8; ++j16) {
-                    const uint32_t aoff = (j16 >> 2) * kSub + (j16 & 3) * 32;
-                    umma_bf16(d, smem_desc_sw128(a0 + aoff, 16, 1024),
+                for (int j16 = 0; j16 < 4; ++j16)
+                    umma_bf16(d, smem_desc_sw128(a0 + j16 * 32, 16, 1024),
                               smem_desc_sw128(b0 + j16 * 2048, kSub, 1024), idesc2,
-                              (first_of_rb && j16 == 0) ? 0u : 1u);
-                }
-                umma_commit(p_empty(h));
-                if (h == 1) {
+                              (first_of_rb && a == 0 && j16 == 0) ? 0u : 1u);
+                umma_commit(p_empty(w));
+                if (w == 3) {
                     umma_commit(b_empty(st));
                     if (last_of_rb) { umma_commit(dz_full); ++n_dz; }
                 }
             };
 
-            mma1(0, 0);
-            mma1(0, 1);
+            for (int w = 0; w < 4; ++w) mma1(0, w);
             for (int i = 0; i < n_tiles; ++i) {
-                mma2(i, 0);
-                if (i + 1 < n_tiles) mma1(i + 1, 0);
-                mma2(i, 1);
-                if (i + 1 < n_tiles) mma1(i + 1, 1);
+                for (int w = 0; w < 4; ++w) {
+                    mma2(i, w);
+                    if (i + 1 < n_tiles) mma1(i + 1, w);
+                }
             }
         }
     } else {
         // ---------------------------------------------------- epilogue warpgroups
-        const int wg = (warp - 2) >> 2;
-        const int q4 = warp & 3;
-        const int r = q4 * 32 + lane;
-        const int wtid = (warp - 2 - wg * 4) * 32 + lane;       // 0..127 inside the warpgroup
+        const int w = (warp - 2) >> 2;                  // warpgroup = (row half, column half)
+        const int h = w >> 1, a = w & 1;
+        const int q4 = warp & 3;                        // TMEM lane quarter this warp may touch
+        const int r = q4 * 32 + lane;                   // row within the half
+        const int wtid = (warp - 2 - w * 4) * 32 + lane;
         const int wwarp = wtid >> 5;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
         const float coef = p.grad_out[0] * p.coef_scale * p.inv_T;
-        float* mycols = cols + wg * 256;
-        uint32_t* myflags = flags + wg * 8;
-        float* myrow = rowred + wg * 8;
-        uint8_t* myp = p_smem + wg * P_BYTES;
+        float* mycols = cols + w * 128;
+        uint32_t* myflags = flags + w * 4;
+        float* myrow = rowred + w * 8;
+        uint8_t* myp = p_smem + w * kSub + r * 128;
         const bool mode_all = (p.mode == SCB_MODE_ALL);
+        const int bar_id = 1 + w;
 
         int cur_rb = -1, idx = 0, li = 0, gi = 0, rep_i = 0, n_dz = 0;
         bool row_ok = false, rb_fast = false;
         float lse2_i = INFINITY, m0 = 0.f, R_i = 0.f, nia_i = 0.f;
 
+        // raw log-sum-exp of the column this thread stages for a tile (threads 0..63 of the warpgroup)
+        auto load_col = [&](int tau) -> float {
+            if (wtid >= 64 || tau >= t1) return 0.f;
+            const int rbn = tau / p.CT;
+            const int j = (tau - rbn * p.CT) * kBN + a * 64 + wtid;
+            return (j < p.n_k) ? __ldg(p.lse_all + j) : 0.f;
+        };
+        float l_next = load_col(t0);
+
         auto drain = [&](int rb) {
             mbar_wait(dz_full, n_dz & 1);
             ++n_dz;
             tc_fence_after();
-            const int lrow = rb * kBM + wg * kBMH + r;
+            const int lrow = rb * kBM + h * kBMH + r;
 #pragma unroll 1
-            for (int cc = 0; cc < KCH * 2; ++cc) {
+            for (int cc = 0; cc < KCH; ++cc) {              // this warpgroup's half of the dK columns
+                const int c0 = a * (KCH * 32) + cc * 32;
                 uint32_t v[32];
-                tmem_ld32(tmem_base + lane_addr + 256 + wg * 128 + cc * 32, v);
-                tmem_ld_wait();
+                tmem_ld32(tmem_base + lane_addr + 256 + h * 128 + c0, v);
+                tmem_ld_wait_dep(v);
                 if (lrow < p.n_rows) {
-                    float* dst = p.out_dk + (int64_t)lrow * p.ld_dk + cc * 32;
+                    float* dst = p.out_dk + (int64_t)lrow * p.ld_dk + c0;
 #pragma unroll
                     for (int c = 0; c < 32; c += 4)
                         red_add_v4(dst + c, __uint_as_float(v[c]) * coef, __uint_as_float(v[c + 1]) * coef,
@@ -490,7 +522,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             if (rb != cur_rb) {
                 if (cur_rb >= 0) drain(cur_rb);
                 cur_rb = rb;
-                li = rb * kBM + wg * kBMH + r;
+                li = rb * kBM + h * kBMH + r;
                 gi = p.row_begin + li;
                 row_ok = (li < p.n_rows);
                 const bool anchor_i = row_ok && p.map.is_anchor(gi, p.mode);
@@ -503,117 +535,120 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 float mx = anchor_i ? lse2_i : -INFINITY, mn = anchor_i ? lse2_i : INFINITY;
                 mx = warp_max(mx);
                 mn = -warp_max(-mn);
-                named_bar_sync(1 + wg, kBMH);      // previous users of myrow are done
+                named_bar_sync(bar_id, kBMH);      // previous readers of myrow are done
                 if (lane == 0) { myrow[wwarp * 2] = mx; myrow[wwarp * 2 + 1] = mn; }
-                named_bar_sync(1 + wg, kBMH);
+                named_bar_sync(bar_id, kBMH);
                 mx = fmaxf(fmaxf(myrow[0], myrow[2]), fmaxf(myrow[4], myrow[6]));
                 mn = fminf(fminf(myrow[1], myrow[3]), fminf(myrow[5], myrow[7]));
                 m0 = mx;
                 rb_fast = mode_all && (mx - mn <= kSafeSpread) && (mx > -INFINITY);
                 R_i = (anchor_i && rb_fast) ? ex2(lse2_i - m0) : 0.f;
             }
-            const int j0 = ct * kBN;
+            const int j0 = ct * kBN + a * 64;             // first column of this warpgroup's sub-tile
             const int cbuf = idx & 1;
-            // ---- per-column factors of this tile: C_j = [anchor_j] 2^(m0 - lse2_j)
-            {
+            // ---- per-column factors of this sub-tile: C_j = [anchor_j] 2^(m0 - lse2_j)
+            if (wtid < 64) {
                 const int j = j0 + wtid;
                 const bool okj = (j < p.n_k) && p.map.is_anchor(j, p.mode);
-                const float Lj = okj ? p.lse_all[j] * kLog2e : 0.f;
-                const float d = m0 - Lj;
+                const float d = m0 - l_next * kLog2e;
                 const bool unsafe = okj && !(fabsf(d) <= kSafeSpread);
-                mycols[cbuf * 128 + wtid] = (okj && !unsafe) ? ex2(d) : 0.f;
+                mycols[cbuf * 64 + wtid] = (okj && !unsafe) ? ex2(d) : 0.f;
                 const unsigned any = __any_sync(0xffffffffu, unsafe);
-                if (lane == 0) myflags[cbuf * 4 + wwarp] = any;
+                if (lane == 0) myflags[cbuf * 2 + wwarp] = any;
             }
-            named_bar_sync(1 + wg, kBMH);
-            const bool fast = rb_fast &&
-                              ((myflags[cbuf * 4] | myflags[cbuf * 4 + 1] | myflags[cbuf * 4 + 2] | myflags[cbuf * 4 + 3]) == 0u);
-            const float* cj = mycols + cbuf * 128;
+            named_bar_sync(bar_id, kBMH);
+            const bool fast = rb_fast && ((myflags[cbuf * 2] | myflags[cbuf * 2 + 1]) == 0u);
+            const float* cj = mycols + cbuf * 64;
 
-            mbar_wait(s_full(wg), idx & 1);
+            mbar_wait(s_full(w), idx & 1);
             tc_fence_after();
-            const int g_lo = p.row_begin + rb * kBM + wg * kBMH;
-            const bool pred = (j0 + kBN > p.n_k) || (g_lo < j0 + kBN && j0 < g_lo + kBMH);
-            mbar_wait(p_empty(wg), (idx & 1) ^ 1);     // MMA2 of the previous tile has consumed P
-#pragma unroll 1
-            for (int cc = 0; cc < 4; ++cc) {
-                uint32_t v[32];
-                tmem_ld32(tmem_base + lane_addr + wg * 128 + cc * 32, v);
-                tmem_ld_wait();
-                if (cc == 3) {
-                    tc_fence_before();
-                    mbar_arrive(s_empty(wg));
-                }
+            uint32_t va[32], vb[32];
+            tmem_ld32(tmem_base + lane_addr + w * 64, va);
+            tmem_ld32(tmem_base + lane_addr + w * 64 + 32, vb);
+            l_next = load_col(tau + 1);                 // global load flies during this sub-tile
+            tmem_ld_wait_dep(va);
+            tmem_ld_wait_dep(vb);
+            tc_fence_before();
+            mbar_arrive(s_empty(w));                    // S[w] is in registers: next MMA1 may start
+
+            const int g_lo = p.row_begin + rb * kBM + h * kBMH;
+            const bool pred = (j0 + 64 > p.n_k) || (g_lo < j0 + 64 && j0 < g_lo + kBMH);
+            mbar_wait(p_empty(w), (idx & 1) ^ 1);       // MMA2 of the previous tile has consumed P[w]
+
+            auto process = [&](uint32_t (&v)[32], int cc) {
                 const int jc = j0 + cc * 32;
-                float pv[32];
-                if (fast) {
-#pragma unroll
-                    for (int c4 = 0; c4 < 8; ++c4) {
-                        const float4 cv = *reinterpret_cast<const float4*>(cj + cc * 32 + c4 * 4);
-                        const float cvv[4] = {cv.x, cv.y, cv.z, cv.w};
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const float e = ex2(fmaf(__uint_as_float(v[c4 * 4 + u]), p.c2, -lse2_i));
-                            pv[c4 * 4 + u] = e * fmaf(R_i, cvv[u], 1.f);
-                        }
-                    }
-                } else {
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const int j = jc + c;
-                        const float x = __uint_as_float(v[c]);
-                        float e = ex2(fmaf(x, p.c2, -lse2_i));                 // lse2_i = +inf -> 0
-                        if (j < p.n_k && p.map.is_anchor(j, p.mode)) e += ex2(fmaf(x, p.c2, -p.lse_all[j] * kLog2e));
-                        pv[c] = e;
-                    }
-                }
-                if (kLabels) {
-#pragma unroll
-                    for (int c4 = 0; c4 < 8; ++c4) {
-                        const int jj = jc + c4 * 4;
-                        if (jj + 3 < p.n_k) {
-                            const int4 rj = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj));
-                            const float4 nj = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj));
-                            if (rj.x == rep_i) pv[c4 * 4 + 0] -= nia_i + nj.x;
-                            if (rj.y == rep_i) pv[c4 * 4 + 1] -= nia_i + nj.y;
-                            if (rj.z == rep_i) pv[c4 * 4 + 2] -= nia_i + nj.z;
-                            if (rj.w == rep_i) pv[c4 * 4 + 3] -= nia_i + nj.w;
-                        } else {
-                            for (int u = 0; u < 4; ++u)
-                                if (jj + u < p.n_k && p.rep_row[jj + u] == rep_i) pv[c4 * 4 + u] -= nia_i + p.nia_row[jj + u];
-                        }
-                    }
-                }
-                if (pred) {
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const int j = jc + c;
-                        if (j >= p.n_k || j == gi) pv[c] = 0.f;
-                    }
-                }
-                if (!row_ok) {
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) pv[c] = 0.f;
-                }
-                // bf16 pack + store in the UMMA K-major / 128B-swizzle layout
-                uint8_t* prow = myp + (cc >> 1) * kSub + r * 128;
 #pragma unroll
                 for (int qq = 0; qq < 4; ++qq) {
+                    float pv[8];
+                    if (fast) {
+                        const float4 c0 = *reinterpret_cast<const float4*>(cj + cc * 32 + qq * 8);
+                        const float4 c1 = *reinterpret_cast<const float4*>(cj + cc * 32 + qq * 8 + 4);
+                        const float cvv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const float e = ex2(fmaf(__uint_as_float(v[qq * 8 + u]), p.c2, -lse2_i));
+                            pv[u] = e * fmaf(R_i, cvv[u], 1.f);
+                        }
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const int j = jc + qq * 8 + u;
+                            const float x = __uint_as_float(v[qq * 8 + u]);
+                            float e = ex2(fmaf(x, p.c2, -lse2_i));                 // lse2_i = +inf -> 0
+                            if (j < p.n_k && p.map.is_anchor(j, p.mode))
+                                e += ex2(fmaf(x, p.c2, -p.lse_all[j] * kLog2e));
+                            pv[u] = e;
+                        }
+                    }
+                    if (kLabels) {
+                        const int jj = jc + qq * 8;
+                        if (jj + 7 < p.n_k) {
+                            const int4 ra = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj));
+                            const int4 rb4 = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj + 4));
+                            const float4 na = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj));
+                            const float4 nb = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj + 4));
+                            if (ra.x == rep_i) pv[0] -= nia_i + na.x;
+                            if (ra.y == rep_i) pv[1] -= nia_i + na.y;
+                            if (ra.z == rep_i) pv[2] -= nia_i + na.z;
+                            if (ra.w == rep_i) pv[3] -= nia_i + na.w;
+                            if (rb4.x == rep_i) pv[4] -= nia_i + nb.x;
+                            if (rb4.y == rep_i) pv[5] -= nia_i + nb.y;
+                            if (rb4.z == rep_i) pv[6] -= nia_i + nb.z;
+                            if (rb4.w == rep_i) pv[7] -= nia_i + nb.w;
+                        } else {
+                            for (int u = 0; u < 8; ++u)
+                                if (jj + u < p.n_k && p.rep_row[jj + u] == rep_i) pv[u] -= nia_i + p.nia_row[jj + u];
+                        }
+                    }
+                    if (pred) {
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const int j = jc + qq * 8 + u;
+                            if (j >= p.n_k || j == gi) pv[u] = 0.f;
+                        }
+                    }
+                    if (!row_ok) {
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) pv[u] = 0.f;
+                    }
+                    // bf16 pack + store in the UMMA K-major / 128B-swizzle layout
                     uint4 pk;
-                    __nv_bfloat162 h0 = __floats2bfloat162_rn(pv[qq * 8 + 0], pv[qq * 8 + 1]);
-                    __nv_bfloat162 h1 = __floats2bfloat162_rn(pv[qq * 8 + 2], pv[qq * 8 + 3]);
-                    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[qq * 8 + 4], pv[qq * 8 + 5]);
-                    __nv_bfloat162 h3 = __floats2bfloat162_rn(pv[qq * 8 + 6], pv[qq * 8 + 7]);
+                    __nv_bfloat162 h0 = __floats2bfloat162_rn(pv[0], pv[1]);
+                    __nv_bfloat162 h1 = __floats2bfloat162_rn(pv[2], pv[3]);
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[4], pv[5]);
+                    __nv_bfloat162 h3 = __floats2bfloat162_rn(pv[6], pv[7]);
                     pk.x = *reinterpret_cast<uint32_t*>(&h0);
                     pk.y = *reinterpret_cast<uint32_t*>(&h1);
                     pk.z = *reinterpret_cast<uint32_t*>(&h2);
                     pk.w = *reinterpret_cast<uint32_t*>(&h3);
-                    const int chunk16 = ((cc & 1) << 2) + qq;
-                    *reinterpret_cast<uint4*>(prow + ((chunk16 ^ (r & 7)) << 4)) = pk;
+                    const int chunk16 = cc * 4 + qq;
+                    *reinterpret_cast<uint4*>(myp + ((chunk16 ^ (r & 7)) << 4)) = pk;
                 }
-            }
+            };
+            process(va, 0);
+            process(vb, 1);
             fence_proxy_async_smem();
-            mbar_arrive(p_full(wg));
+            mbar_arrive(p_full(w));
             ++idx;
         }
         if (cur_rb >= 0) drain(cur_rb);
@@ -832,13 +867,13 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     const int kch = p->ldk / 64;
-    const size_t smem = (size_t)(2 * kch * kSub) + 3 * (kch * kSub) + 2 * (2 * kSub) + 2 * 2 * 128 * 4 + 64 + 64 +
-                        16 * 8 + 8 + 16;
+    const size_t smem = (size_t)(2 * kch * kSub) + 3 * (kch * kSub) + 4 * kSub + 4 * 2 * 64 * 4 + 64 + 128 +
+                        28 * 8 + 16;
     const bool lab = p->mask_kind == SCB_MASK_LABELS;
 #define SCB_LAUNCH_BWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
         if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        supcon_tc_bwd_kernel<KCH_, LAB_><<<g.grid, kThreads, smem, stream>>>(tmap, t);                  \
+        supcon_tc_bwd_kernel<KCH_, LAB_><<<g.grid, kBwdThreads, smem, stream>>>(tmap, t);                  \
     } while (0)
     if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
     else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }

@@ -93,6 +93,11 @@ def test_ragged_shapes_simclr_and_labels(shape, mode, engine):
     if not _available(engine):
         pytest.skip('engine not built')
     B, V, D = shape
+    if engine != 'fp32' and not L.tc_engine_supported(D, _lib.MASK_SIMCLR, B * V):
+        # shapes outside the tensor-core engine are refused loudly, never re-routed silently
+        with pytest.raises(ValueError, match='does not take this problem'):
+            run_ours(np.zeros(shape, np.float32), None, None, engine)
+        return
     rng = np.random.default_rng(B * 1000 + V * 10 + D)
     z = rng.standard_normal((B, V, D)) + 0.5 * rng.standard_normal((1, 1, D))
     z = (z / np.linalg.norm(z, axis=-1, keepdims=True)).astype(np.float32)
