@@ -191,15 +191,19 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
         }
     }
     __syncthreads();
-    if (s_last && threadIdx.x == 0) {
+    if (s_last && threadIdx.x < 32) {
+        // last CTA: lanes fetch the partials in parallel, fixed-shape shuffle tree -> deterministic
         __threadfence();
         double t = 0.0;
-        for (unsigned b = 0; b < gridDim.x; ++b) {
+        for (unsigned b = threadIdx.x; b < gridDim.x; b += 32) {
             t += __ldcg(cta_sum + b);
             cta_sum[b] = 0.0;
         }
-        out_loss_sum[0] = (float)(t * inv_anchors);
-        *ticket = 0u;
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (threadIdx.x == 0) {
+            out_loss_sum[0] = (float)(t * inv_anchors);
+            *ticket = 0u;
+        }
     }
 }
 

@@ -310,6 +310,21 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     }
 }
 
+// pack 8 fp32 -> bf16 and store them as 16-byte chunk `chunk16` of row r of a [128 x 64] K-major,
+// 128B-swizzled UMMA operand tile (prow = tile base + r*128)
+__device__ __forceinline__ void store_p8(uint8_t* prow, int chunk16, int r, const float (&pv)[8]) {
+    uint4 pk;
+    __nv_bfloat162 h0 = __floats2bfloat162_rn(pv[0], pv[1]);
+    __nv_bfloat162 h1 = __floats2bfloat162_rn(pv[2], pv[3]);
+    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[4], pv[5]);
+    __nv_bfloat162 h3 = __floats2bfloat162_rn(pv[6], pv[7]);
+    pk.x = *reinterpret_cast<uint32_t*>(&h0);
+    pk.y = *reinterpret_cast<uint32_t*>(&h1);
+    pk.z = *reinterpret_cast<uint32_t*>(&h2);
+    pk.w = *reinterpret_cast<uint32_t*>(&h3);
+    *reinterpret_cast<uint4*>(prow + ((chunk16 ^ (r & 7)) << 4)) = pk;
+}
+
 // =================================================================================== backward
 // 18 warps: warp 0 TMA, warp 1 MMA issue + TMEM, warps 2..17 = four epilogue warpgroups.
 // Warpgroup w = (h, a) owns row half h and column half a of every tile, so the unit of the
@@ -474,7 +489,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         const int wwarp = wtid >> 5;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
         const float coef = p.grad_out[0] * p.coef_scale * p.inv_T;
-        float* mycols = cols + w * 128;
+        float* cj = cols + w * 128;                       // [64] 1-exp column factors
+        float* lj = cj + 64;                              // [64] column log-sum-exps (log2 domain)
         uint32_t* myflags = flags + w * 4;
         float* myrow = rowred + w * 8;
         uint8_t* myp = p_smem + w * kSub + r * 128;
@@ -545,42 +561,42 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 R_i = (anchor_i && rb_fast) ? ex2(lse2_i - m0) : 0.f;
             }
             const int j0 = ct * kBN + a * 64;             // first column of this warpgroup's sub-tile
-            const int cbuf = idx & 1;
-            // ---- per-column factors of this sub-tile: C_j = [anchor_j] 2^(m0 - lse2_j)
+            // ---- per-column data of this sub-tile (threads 0..63 stage one column each):
+            //      cj[c] = [anchor_j] 2^(m0 - lse2_j)   (1-exp path),  lj[c] = lse2_j or +inf   (2-exp path)
+            named_bar_sync(bar_id, kBMH);                 // everybody is done with the previous tile's columns
             if (wtid < 64) {
                 const int j = j0 + wtid;
                 const bool okj = (j < p.n_k) && p.map.is_anchor(j, p.mode);
-                const float d = m0 - l_next * kLog2e;
+                const float l2 = l_next * kLog2e;
+                const float d = m0 - l2;
                 const bool unsafe = okj && !(fabsf(d) <= kSafeSpread);
-                mycols[cbuf * 64 + wtid] = (okj && !unsafe) ? ex2(d) : 0.f;
+                cj[wtid] = (okj && !unsafe) ? ex2(d) : 0.f;
+                lj[wtid] = okj ? l2 : INFINITY;
                 const unsigned any = __any_sync(0xffffffffu, unsafe);
-                if (lane == 0) myflags[cbuf * 2 + wwarp] = any;
+                if (lane == 0) myflags[wwarp] = any;
             }
             named_bar_sync(bar_id, kBMH);
-            const bool fast = rb_fast && ((myflags[cbuf * 2] | myflags[cbuf * 2 + 1]) == 0u);
-            const float* cj = mycols + cbuf * 64;
+            const int g_lo = p.row_begin + rb * kBM + h * kBMH;
+            const bool pred = (j0 + 64 > p.n_k) || (g_lo < j0 + 64 && j0 < g_lo + kBMH);
+            const bool fast = rb_fast && !pred && ((myflags[0] | myflags[1]) == 0u);
 
             mbar_wait(s_full(w), idx & 1);
             tc_fence_after();
-            uint32_t va[32], vb[32];
-            tmem_ld32(tmem_base + lane_addr + w * 64, va);
-            tmem_ld32(tmem_base + lane_addr + w * 64 + 32, vb);
-            l_next = load_col(tau + 1);                 // global load flies during this sub-tile
-            tmem_ld_wait_dep(va);
-            tmem_ld_wait_dep(vb);
-            tc_fence_before();
-            mbar_arrive(s_empty(w));                    // S[w] is in registers: next MMA1 may start
-
-            const int g_lo = p.row_begin + rb * kBM + h * kBMH;
-            const bool pred = (j0 + 64 > p.n_k) || (g_lo < j0 + 64 && j0 < g_lo + kBMH);
-            mbar_wait(p_empty(w), (idx & 1) ^ 1);       // MMA2 of the previous tile has consumed P[w]
-
-            auto process = [&](uint32_t (&v)[32], int cc) {
-                const int jc = j0 + cc * 32;
+            if (fast) {
+                // ---------------- common case: one exp per element, fully unrolled, S released early
+                uint32_t va[32], vb[32];
+                tmem_ld32(tmem_base + lane_addr + w * 64, va);
+                tmem_ld32(tmem_base + lane_addr + w * 64 + 32, vb);
+                l_next = load_col(tau + 1);                 // global load flies during this sub-tile
+                tmem_ld_wait_dep(va);
+                tmem_ld_wait_dep(vb);
+                tc_fence_before();
+                mbar_arrive(s_empty(w));                    // S[w] is in registers: next MMA1 may start
+                mbar_wait(p_empty(w), (idx & 1) ^ 1);       // MMA2 of the previous tile has consumed P[w]
+                auto process = [&](uint32_t (&v)[32], int cc) {
 #pragma unroll
-                for (int qq = 0; qq < 4; ++qq) {
-                    float pv[8];
-                    if (fast) {
+                    for (int qq = 0; qq < 4; ++qq) {
+                        float pv[8];
                         const float4 c0 = *reinterpret_cast<const float4*>(cj + cc * 32 + qq * 8);
                         const float4 c1 = *reinterpret_cast<const float4*>(cj + cc * 32 + qq * 8 + 4);
                         const float cvv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
@@ -589,20 +605,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                             const float e = ex2(fmaf(__uint_as_float(v[qq * 8 + u]), p.c2, -lse2_i));
                             pv[u] = e * fmaf(R_i, cvv[u], 1.f);
                         }
-                    } else {
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) {
-                            const int j = jc + qq * 8 + u;
-                            const float x = __uint_as_float(v[qq * 8 + u]);
-                            float e = ex2(fmaf(x, p.c2, -lse2_i));                 // lse2_i = +inf -> 0
-                            if (j < p.n_k && p.map.is_anchor(j, p.mode))
-                                e += ex2(fmaf(x, p.c2, -p.lse_all[j] * kLog2e));
-                            pv[u] = e;
-                        }
-                    }
-                    if (kLabels) {
-                        const int jj = jc + qq * 8;
-                        if (jj + 7 < p.n_k) {
+                        if (kLabels) {
+                            const int jj = j0 + cc * 32 + qq * 8;      // fast => whole sub-tile in range
                             const int4 ra = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj));
                             const int4 rb4 = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj + 4));
                             const float4 na = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj));
@@ -615,38 +619,39 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                             if (rb4.y == rep_i) pv[5] -= nia_i + nb.y;
                             if (rb4.z == rep_i) pv[6] -= nia_i + nb.z;
                             if (rb4.w == rep_i) pv[7] -= nia_i + nb.w;
-                        } else {
-                            for (int u = 0; u < 8; ++u)
-                                if (jj + u < p.n_k && p.rep_row[jj + u] == rep_i) pv[u] -= nia_i + p.nia_row[jj + u];
                         }
+                        store_p8(myp, cc * 4 + qq, r, pv);
                     }
-                    if (pred) {
+                };
+                process(va, 0);
+                process(vb, 1);
+            } else {
+                // ---------------- rare case (self / ragged tiles, mode `one`, wild LSE ranges): two exps,
+                // eight columns at a time straight from TMEM, compact code
+                mbar_wait(p_empty(w), (idx & 1) ^ 1);
+#pragma unroll 1
+                for (int g8 = 0; g8 < 8; ++g8) {
+                    uint32_t v8[8];
+                    tmem_ld8(tmem_base + lane_addr + w * 64 + g8 * 8, v8);
+                    tmem_ld_wait_dep8(v8);
+                    float pv[8];
 #pragma unroll
-                        for (int u = 0; u < 8; ++u) {
-                            const int j = jc + qq * 8 + u;
-                            if (j >= p.n_k || j == gi) pv[u] = 0.f;
+                    for (int u = 0; u < 8; ++u) {
+                        const int c = g8 * 8 + u;
+                        const int j = j0 + c;
+                        const float x = __uint_as_float(v8[u]);
+                        float e = ex2(fmaf(x, p.c2, -lse2_i)) + ex2(fmaf(x, p.c2, -lj[c]));   // +inf -> 0
+                        if (kLabels) {
+                            if (j < p.n_k && p.rep_row[j] == rep_i) e -= nia_i + p.nia_row[j];
                         }
+                        pv[u] = (j >= p.n_k || j == gi) ? 0.f : e;
                     }
-                    if (!row_ok) {
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) pv[u] = 0.f;
-                    }
-                    // bf16 pack + store in the UMMA K-major / 128B-swizzle layout
-                    uint4 pk;
-                    __nv_bfloat162 h0 = __floats2bfloat162_rn(pv[0], pv[1]);
-                    __nv_bfloat162 h1 = __floats2bfloat162_rn(pv[2], pv[3]);
-                    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[4], pv[5]);
-                    __nv_bfloat162 h3 = __floats2bfloat162_rn(pv[6], pv[7]);
-                    pk.x = *reinterpret_cast<uint32_t*>(&h0);
-                    pk.y = *reinterpret_cast<uint32_t*>(&h1);
-                    pk.z = *reinterpret_cast<uint32_t*>(&h2);
-                    pk.w = *reinterpret_cast<uint32_t*>(&h3);
-                    const int chunk16 = cc * 4 + qq;
-                    *reinterpret_cast<uint4*>(myp + ((chunk16 ^ (r & 7)) << 4)) = pk;
+                    store_p8(myp, g8, r, pv);
                 }
-            };
-            process(va, 0);
-            process(vb, 1);
+                tc_fence_before();
+                mbar_arrive(s_empty(w));
+                l_next = load_col(tau + 1);
+            }
             fence_proxy_async_smem();
             mbar_arrive(p_full(w));
             ++idx;
@@ -696,7 +701,7 @@ supcon_tc_init_dk_kernel(const __nv_bfloat16* __restrict__ k, int ldk, RowMap ma
     if (warp >= n_rows) return;
     float* dst = out_dk + (int64_t)warp * ld_dk;
     if (mask_kind != SCB_MASK_SIMCLR || n_views < 2) {
-        for (int d = lane; d < ldk; d += 32) dst[d] = 0.f;
+        for (int d = lane * 4; d < ldk; d += 128) *reinterpret_cast<float4*>(dst + d) = make_float4(0.f, 0.f, 0.f, 0.f);
         return;
     }
     const int gi = row_begin + warp;
@@ -704,15 +709,20 @@ supcon_tc_init_dk_kernel(const __nv_bfloat16* __restrict__ k, int ldk, RowMap ma
     const int v = rem / map.seg, b = rem - v * map.seg;
     const float ai = map.is_anchor(gi, mode) ? 1.f : 0.f;
     const float c = -grad_out[0] * coef_scale_invT / (float)(n_views - 1);
-    for (int d = lane; d < ldk; d += 32) {
-        float acc = 0.f;
+    // a lane owns 4 consecutive features (8-byte bf16 loads, 16-byte fp32 stores); ldk % 64 == 0
+    for (int d = lane * 4; d < ldk; d += 128) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
         for (int vv = 0; vv < n_views; ++vv) {
             if (vv == v) continue;
             const int j = base + vv * map.seg + b;
-            const float aj = map.is_anchor(j, mode) ? 1.f : 0.f;
-            acc = fmaf(ai + aj, __bfloat162float(k[(int64_t)j * ldk + d]), acc);
+            const float wgt = ai + (map.is_anchor(j, mode) ? 1.f : 0.f);
+            const uint2 raw = *reinterpret_cast<const uint2*>(k + (int64_t)j * ldk + d);
+            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
+            const float2 f0 = __bfloat1622float2(h2[0]), f1 = __bfloat1622float2(h2[1]);
+            acc[0] = fmaf(wgt, f0.x, acc[0]); acc[1] = fmaf(wgt, f0.y, acc[1]);
+            acc[2] = fmaf(wgt, f1.x, acc[2]); acc[3] = fmaf(wgt, f1.y, acc[3]);
         }
-        dst[d] = c * acc;
+        *reinterpret_cast<float4*>(dst + d) = make_float4(c * acc[0], c * acc[1], c * acc[2], c * acc[3]);
     }
 }
 
