@@ -61,6 +61,9 @@ int scb_version(void);
 int scb_device_cc(void);
 /* number of kernels this library has launched in this process so far (bench bookkeeping) */
 int64_t scb_launch_count(void);
+/* diagnostics only: a device buffer of 3*1024 int64 that CTA 0 of the tensor-core backward fills
+ * with (event id, SM clock) pairs per role (0 MMA issuer, 1/2 epilogue warpgroups); NULL = off */
+int scb_debug_set_trace(void* device_buffer);
 
 /* ======================================================================== path 1: the loss
  *

@@ -72,6 +72,11 @@ extern "C" const char* scb_last_error(void) { return g_err; }
 extern "C" int scb_version(void) { return 100; }
 extern "C" int64_t scb_launch_count(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
 
+extern "C" int scb_debug_set_trace(void* device_buffer) {
+    tc_set_trace((long long*)device_buffer);
+    return SCB_OK;
+}
+
 extern "C" int scb_device_cc(void) {
     int dev = 0, major = 0, minor = 0;
     SCB_CUDA_OK(cudaGetDevice(&dev));

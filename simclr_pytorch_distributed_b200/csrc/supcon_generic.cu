@@ -162,7 +162,7 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
             int n_split = n_split_in;
             if (flat_q > 0) {      // slots = CTAs whose span [c*q, (c+1)*q) meets this row block's tiles
                 const int rb = r >> 8;
-                n_split = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
+                n_split = 2 * (((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1);
             }
             float m = -INFINITY;
             for (int s = 0; s < n_split; ++s) m = fmaxf(m, part[((int64_t)s * 4 + 0) * n_rows + r]);

@@ -27,7 +27,7 @@ constexpr int kBMH = 128;       // rows per half = one UMMA M
 constexpr int kBM = 256;        // rows per CTA tile
 constexpr int kBN = 128;        // columns per tile
 constexpr int kSub = 16384;     // bytes of one [128 x 64] bf16 swizzled sub-tile
-constexpr int kThreads = 320;   // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..9 epilogue (2 warpgroups)
+constexpr int kTcThreads = 576; // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..17 = four epilogue warpgroups
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kSafeSpread = 60.f;
@@ -49,6 +49,18 @@ struct TcParams {
     float coef_scale;                   // (T/Tb) / n_anchor_total
     float* out_dk;
     int ld_dk;
+    long long* trace;                   // optional (debug): per-role timestamps of CTA 0
+};
+
+// debug tracing: CTA 0, lane 0 of a warp appends (id, clock) pairs to its own 512-slot lane of the buffer
+struct Tracer {
+    long long* buf; int n;
+    __device__ Tracer(long long* base, int role) : buf(nullptr), n(0) {
+        if (base != nullptr && blockIdx.x == 0 && (threadIdx.x & 31) == 0 && role >= 0) buf = base + role * 1024;
+    }
+    __device__ __forceinline__ void operator()(int id) {
+        if (buf != nullptr && n < 510) { buf[2 * n] = id; buf[2 * n + 1] = clock64(); ++n; buf[1022] = n; }
+    }
 };
 
 __device__ __forceinline__ float bf16_dot_rows(const __nv_bfloat16* a, const __nv_bfloat16* b, int n) {
@@ -71,7 +83,7 @@ __device__ __forceinline__ float bf16_dot_rows(const __nv_bfloat16* a, const __n
 // =================================================================================== forward
 // smem: A[2][2*KCH*kSub] | B[2][KCH*kSub] | barriers | tmem slot
 template <int KCH, bool kLabels>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kTcThreads, 1)
 supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int A_BYTES = 2 * KCH * kSub;
@@ -93,7 +105,7 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
     if (threadIdx.x == 0) {
         for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);
-        for (int i = 12; i < 16; ++i) mbar_init(bar0 + 8u * i, kBMH);
+        for (int i = 12; i < 16; ++i) mbar_init(bar0 + 8u * i, 2 * kBMH);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -107,15 +119,15 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     const int t1 = min(p.T, t0 + p.q);
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------------------------ TMA producer
-            int n_a = 0, n_b = 0, cur_rb = -1;
-            for (int tau = t0; tau < t1; ++tau) {
-                const int rb = tau / p.CT, ct = tau - rb * p.CT;
-                if (rb != cur_rb) {
-                    cur_rb = rb;
-                    const int buf = n_a & 1;
-                    mbar_wait(a_empty(buf), ((n_a >> 1) & 1) ^ 1);
+        // ---------------------------------------------------- TMA producer (warp-uniform, one lane issues)
+        int n_a = 0, n_b = 0, cur_rb = -1;
+        for (int tau = t0; tau < t1; ++tau) {
+            const int rb = tau / p.CT, ct = tau - rb * p.CT;
+            if (rb != cur_rb) {
+                cur_rb = rb;
+                const int buf = n_a & 1;
+                mbar_wait(a_empty(buf), ((n_a >> 1) & 1) ^ 1);
+                if (elect_one()) {
                     mbar_arrive_expect_tx(a_full(buf), A_BYTES);
 #pragma unroll
                     for (int h = 0; h < 2; ++h)
@@ -123,58 +135,67 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                         for (int kc = 0; kc < KCH; ++kc)
                             tma_load_2d(smem_u32(a_smem + buf * A_BYTES + (h * KCH + kc) * kSub), &tmap, kc * 64,
                                         p.row_begin + rb * kBM + h * kBMH, a_full(buf));
-                    ++n_a;
                 }
-                const int st = n_b % NSB;
-                mbar_wait(b_empty(st), ((n_b / NSB) & 1) ^ 1);
+                __syncwarp();
+                ++n_a;
+            }
+            const int st = n_b % NSB;
+            mbar_wait(b_empty(st), ((n_b / NSB) & 1) ^ 1);
+            if (elect_one()) {
                 mbar_arrive_expect_tx(b_full(st), B_BYTES);
 #pragma unroll
                 for (int kc = 0; kc < KCH; ++kc)
                     tma_load_2d(smem_u32(b_smem + st * B_BYTES + kc * kSub), &tmap, kc * 64, ct * kBN, b_full(st));
-                ++n_b;
             }
+            __syncwarp();
+            ++n_b;
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ------------------------------------------------ MMA issuer
-            constexpr uint32_t idesc = idesc_bf16(128, 128, 0);
-            int n_a = 0, n_b = 0, idx = 0, cur_rb = -1, abuf = 0;
-            for (int tau = t0; tau < t1; ++tau) {
-                const int rb = tau / p.CT;
-                if (rb != cur_rb) {
-                    if (cur_rb >= 0) umma_commit(a_empty(abuf));
-                    cur_rb = rb;
-                    abuf = n_a & 1;
-                    mbar_wait(a_full(abuf), (n_a >> 1) & 1);
-                    ++n_a;
+        // ---------------------------------------------------- MMA issuer (warp-uniform, one lane issues)
+        constexpr uint32_t idesc = idesc_bf16(128, 128, 0);
+        int n_a = 0, n_b = 0, idx = 0, cur_rb = -1, abuf = 0;
+        for (int tau = t0; tau < t1; ++tau) {
+            const int rb = tau / p.CT;
+            if (rb != cur_rb) {
+                if (cur_rb >= 0) {
+                    if (elect_one()) umma_commit(a_empty(abuf));
+                    __syncwarp();
                 }
-                const int st = n_b % NSB;
-                mbar_wait(b_full(st), (n_b / NSB) & 1);
-                ++n_b;
-                const int sbuf = idx & 1;
-                const uint32_t sphase = (idx >> 1) & 1;
+                cur_rb = rb;
+                abuf = n_a & 1;
+                mbar_wait(a_full(abuf), (n_a >> 1) & 1);
+                ++n_a;
+            }
+            const int st = n_b % NSB;
+            mbar_wait(b_full(st), (n_b / NSB) & 1);
+            ++n_b;
+            const int sbuf = idx & 1;
+            const uint32_t sphase = (idx >> 1) & 1;
+            const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), 16);
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    mbar_wait(s_empty(h, sbuf), sphase ^ 1);
-                    tc_fence_after();
-                    const uint32_t d = tmem_base + sbuf * 256 + h * 128;
-                    const uint32_t a0 = smem_u32(a_smem + abuf * A_BYTES + h * KCH * kSub);
-                    const uint32_t b0 = smem_u32(b_smem + st * B_BYTES);
+            for (int h = 0; h < 2; ++h) {
+                mbar_wait(s_empty(h, sbuf), sphase ^ 1);
+                tc_fence_after();
+                const uint32_t d = tmem_base + sbuf * 256 + h * 128;
+                const uint32_t a_lo = desc_lo(smem_u32(a_smem + abuf * A_BYTES + h * KCH * kSub), 16);
+                if (elect_one()) {
 #pragma unroll
                     for (int k16 = 0; k16 < KCH * 4; ++k16) {
-                        const uint32_t off = (k16 >> 2) * kSub + (k16 & 3) * 32;
-                        umma_bf16(d, smem_desc_sw128(a0 + off, 16, 1024), smem_desc_sw128(b0 + off, 16, 1024),
-                                  idesc, k16 > 0 ? 1u : 0u);
+                        const uint32_t off = ((k16 >> 2) * kSub + (k16 & 3) * 32) >> 4;
+                        if (k16 == 0) umma_bf16_lo<false>(d, a_lo + off, b_lo + off, idesc);
+                        else umma_bf16_lo<true>(d, a_lo + off, b_lo + off, idesc);
                     }
                     umma_commit(s_full(h, sbuf));
+                    if (h == 1) umma_commit(b_empty(st));
                 }
-                umma_commit(b_empty(st));
-                ++idx;
+                __syncwarp();
             }
+            ++idx;
         }
     } else {
         // ---------------------------------------------------- epilogue warpgroups
-        const int wg = (warp - 2) >> 2;                 // half of the row block
+        const int w4 = (warp - 2) >> 2;                 // warpgroup = (row half wg, column half ca)
+        const int wg = w4 >> 1, ca = w4 & 1;
         const int q4 = warp & 3;                        // TMEM lane quarter this warp may touch
         const int r = q4 * 32 + lane;                   // row within the half
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
@@ -183,7 +204,8 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
 
         auto flush = [&](int rb) {
             if (li >= p.a_count) return;
-            const int slot = blockIdx.x - (rb * p.CT) / p.q;
+            // one slot per (CTA overlapping the row block, column half)
+            const int slot = 2 * (blockIdx.x - (rb * p.CT) / p.q) + ca;
             float ps = 0.f, np = 0.f;
             if (kLabels) {
                 ps = possum * p.inv_T;
@@ -219,10 +241,10 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             const int sbuf = idx & 1;
             mbar_wait(s_full(wg, sbuf), (idx >> 1) & 1);
             tc_fence_after();
-            const int j0 = ct * kBN;
+            const int j0 = ct * kBN + ca * 64;            // this warpgroup's 64 columns of the tile
             const int g_lo = p.row_begin + rb * kBM + wg * kBMH;
-            const bool pred = (j0 + kBN > p.n_k) || (g_lo < j0 + kBN && j0 < g_lo + kBMH);
-            const uint32_t taddr = tmem_base + lane_addr + sbuf * 256 + wg * 128;
+            const bool pred = (j0 + 64 > p.n_k) || (g_lo < j0 + 64 && j0 < g_lo + kBMH);
+            const uint32_t taddr = tmem_base + lane_addr + sbuf * 256 + wg * 128 + ca * 64;
             // one 32-column chunk of this thread's row: online (max, sum) update + positive sum
             auto process = [&](uint32_t (&v)[32], int cc) {
                 const int jc = j0 + cc * 32;
@@ -281,22 +303,16 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                     }
                 }
             };
-            // software pipeline over the 4 chunks: the TMEM load of chunk c+1 flies while chunk c is processed
+            // both 32-column chunks are pulled out of TMEM at once, then S[wg][sbuf] is handed back
             uint32_t va[32], vb[32];
             tmem_ld32(taddr, va);
-            tmem_ld_wait_dep(va);
             tmem_ld32(taddr + 32, vb);
-            process(va, 0);
-            tmem_ld_wait_dep(vb);
-            tmem_ld32(taddr + 64, va);
-            process(vb, 1);
             tmem_ld_wait_dep(va);
-            tmem_ld32(taddr + 96, vb);
-            process(va, 2);
             tmem_ld_wait_dep(vb);
             tc_fence_before();
             mbar_arrive(s_empty(wg, sbuf));      // S buffer is free for the next MMA
-            process(vb, 3);
+            process(va, 0);
+            process(vb, 1);
             ++idx;
         }
         if (cur_rb >= 0) flush(cur_rb);
@@ -332,11 +348,10 @@ __device__ __forceinline__ void store_p8(uint8_t* prow, int chunk16, int r, cons
 // 16 KB swizzled sub-tile in shared memory).  While one warpgroup waits for its MMA2 + next MMA1
 // the other three keep the MUFU pipe busy.
 // smem: A[2*KCH*kSub] | B[3][KCH*kSub] | P[4][kSub] | cols[4][2][64] f32 | flags | rowred | barriers | tmem slot
-// TMEM: S[w] at columns w*64, dK[h] at columns 256 + h*128.
-constexpr int kBwdThreads = 64 + 512;
+// TMEM: S[h] at columns h*128 (warpgroup (h, a) reads columns h*128 + a*64 ..), dK[h] at 256 + h*128.
 
 template <int KCH, bool kLabels>
-__global__ void __launch_bounds__(kBwdThreads, 1)
+__global__ void __launch_bounds__(kTcThreads, 1)
 supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int A_BYTES = 2 * KCH * kSub;
@@ -355,20 +370,19 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     auto a_empty = [&]() { return bar0 + 8u * 1; };
     auto b_full = [&](int s) { return bar0 + 8u * (2 + s); };
     auto b_empty = [&](int s) { return bar0 + 8u * (5 + s); };
-    auto s_full = [&](int w) { return bar0 + 8u * (8 + w); };
-    auto s_empty = [&](int w) { return bar0 + 8u * (12 + w); };
-    auto p_full = [&](int w) { return bar0 + 8u * (16 + w); };
-    auto p_empty = [&](int w) { return bar0 + 8u * (20 + w); };
+    // per row half h: S[h] ready / P[h] published by its two warpgroups / P[h] consumed
+    auto s_full = [&](int h) { return bar0 + 8u * (8 + h); };
+    auto p_full = [&](int h) { return bar0 + 8u * (16 + h); };
+    auto p_empty = [&](int h) { return bar0 + 8u * (20 + h); };
     const uint32_t dz_full = bar0 + 8u * 24, dz_empty = bar0 + 8u * 25;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
     if (threadIdx.x == 0) {
         for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);          // a, b, s_full
-        for (int w = 0; w < 4; ++w) {
-            mbar_init(s_empty(w), kBMH);
-            mbar_init(p_full(w), kBMH);
-            mbar_init(p_empty(w), 1);
+        for (int h = 0; h < 2; ++h) {
+            mbar_init(p_full(h), 2 * kBMH);
+            mbar_init(p_empty(h), 1);
         }
         mbar_init(dz_full, 1);
         mbar_init(dz_empty, 4 * kBMH);
@@ -385,14 +399,14 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     const int t1 = min(p.T, t0 + p.q);
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------------------------ TMA producer
-            int n_a = 0, n_b = 0, cur_rb = -1;
-            for (int tau = t0; tau < t1; ++tau) {
-                const int rb = tau / p.CT, ct = tau - rb * p.CT;
-                if (rb != cur_rb) {
-                    cur_rb = rb;
-                    mbar_wait(a_empty(), (n_a & 1) ^ 1);
+        // ---------------------------------------------------- TMA producer (warp-uniform, one lane issues)
+        int n_a = 0, n_b = 0, cur_rb = -1;
+        for (int tau = t0; tau < t1; ++tau) {
+            const int rb = tau / p.CT, ct = tau - rb * p.CT;
+            if (rb != cur_rb) {
+                cur_rb = rb;
+                mbar_wait(a_empty(), (n_a & 1) ^ 1);
+                if (elect_one()) {
                     mbar_arrive_expect_tx(a_full(), A_BYTES);
 #pragma unroll
                     for (int h = 0; h < 2; ++h)
@@ -400,83 +414,105 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                         for (int kc = 0; kc < KCH; ++kc)
                             tma_load_2d(smem_u32(a_smem + (h * KCH + kc) * kSub), &tmap, kc * 64,
                                         p.row_begin + rb * kBM + h * kBMH, a_full());
-                    ++n_a;
                 }
-                const int st = n_b % NSB;
-                mbar_wait(b_empty(st), ((n_b / NSB) & 1) ^ 1);
+                __syncwarp();
+                ++n_a;
+            }
+            const int st = n_b % NSB;
+            mbar_wait(b_empty(st), ((n_b / NSB) & 1) ^ 1);
+            if (elect_one()) {
                 mbar_arrive_expect_tx(b_full(st), B_BYTES);
 #pragma unroll
                 for (int kc = 0; kc < KCH; ++kc)
                     tma_load_2d(smem_u32(b_smem + st * B_BYTES + kc * kSub), &tmap, kc * 64, ct * kBN, b_full(st));
-                ++n_b;
             }
+            __syncwarp();
+            ++n_b;
         }
     } else if (warp == 1) {
-        if (lane == 0 && t0 < t1) {
-            // ------------------------------------------------ MMA issuer
-            constexpr uint32_t idesc1 = idesc_bf16(128, 64, 0);
+        if (t0 < t1) {
+            // ------------------------------------------------ MMA issuer (warp-uniform, one lane issues)
+            constexpr uint32_t idesc1 = idesc_bf16(128, 128, 0);
             constexpr uint32_t idesc2 = idesc_bf16(128, KCH * 64, 1);
+            Tracer tr(p.trace, 0);
             int n_a = 0, n_dz = 0;
             const int n_tiles = t1 - t0;
+            const uint32_t a_lo0 = desc_lo(smem_u32(a_smem), 16);
+            const uint32_t p_lo0 = desc_lo(smem_u32(p_smem), 16);
 
-            // S[w] = A_h (128 rows) x B rows [a*64, a*64+64)^T of tile i
-            auto mma1 = [&](int i, int w) {
-                const int h = w >> 1, a = w & 1;
-                const int tau = t0 + i;
-                const int rb = tau / p.CT;
-                const bool first_of_rb = (i == 0) || ((tau - 1) / p.CT != rb);
-                const bool last_of_rb = (i == n_tiles - 1) || ((tau + 1) / p.CT != rb);
+            // S[h] = A_h (128 rows) x B^T (128 columns) of tile i.  S[h] is known to be free: both of
+            // its warpgroups pulled it into registers before they published P[h], which the MMA2 of the
+            // previous tile waited for.
+            auto mma1 = [&](int i, int h, bool first_of_rb, bool last_of_rb) {
                 const int st = i % NSB;
-                if (w == 0) {
+                if (h == 0) {
                     if (first_of_rb) { mbar_wait(a_full(), n_a & 1); ++n_a; }
                     mbar_wait(b_full(st), (i / NSB) & 1);
+                    tc_fence_after();
                 }
-                mbar_wait(s_empty(w), (i & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t d = tmem_base + w * 64;
-                const uint32_t a0 = smem_u32(a_smem + h * KCH * kSub);
-                const uint32_t b0 = smem_u32(b_smem + st * B_BYTES) + a * 8192;
+                const uint32_t d = tmem_base + h * 128;
+                const uint32_t a_lo = a_lo0 + ((h * KCH * kSub) >> 4);
+                const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), 16);
+                if (elect_one()) {
 #pragma unroll
-                for (int k16 = 0; k16 < KCH * 4; ++k16) {
-                    const uint32_t off = (k16 >> 2) * kSub + (k16 & 3) * 32;
-                    umma_bf16(d, smem_desc_sw128(a0 + off, 16, 1024), smem_desc_sw128(b0 + off, 16, 1024), idesc1,
-                              k16 > 0 ? 1u : 0u);
+                    for (int k16 = 0; k16 < KCH * 4; ++k16) {
+                        const uint32_t off = ((k16 >> 2) * kSub + (k16 & 3) * 32) >> 4;
+                        if (k16 == 0) umma_bf16_lo<false>(d, a_lo + off, b_lo + off, idesc1);
+                        else umma_bf16_lo<true>(d, a_lo + off, b_lo + off, idesc1);
+                    }
+                    umma_commit(s_full(h));
+                    if (h == 1 && last_of_rb) umma_commit(a_empty());
                 }
-                umma_commit(s_full(w));
-                if (w == 3 && last_of_rb) umma_commit(a_empty());
+                __syncwarp();
             };
-            // dK[h] += P[w] (128 x 64, K-major) x K_j rows [a*64, a*64+64) read MN-major
-            auto mma2 = [&](int i, int w) {
-                const int h = w >> 1, a = w & 1;
-                const int tau = t0 + i;
-                const int rb = tau / p.CT;
-                const bool first_of_rb = (i == 0) || ((tau - 1) / p.CT != rb);
-                const bool last_of_rb = (i == n_tiles - 1) || ((tau + 1) / p.CT != rb);
+            // dK[h] += P[h] (128 x 128, K-major, two swizzled sub-tiles) x K_j (128 rows read MN-major)
+            auto mma2 = [&](int i, int h, bool first_of_rb, bool last_of_rb) {
                 const int st = i % NSB;
-                mbar_wait(p_full(w), i & 1);
-                if (w == 0 && first_of_rb) mbar_wait(dz_empty, (n_dz & 1) ^ 1);
+                tr(200 + h);
+                mbar_wait(p_full(h), i & 1);
+                if (h == 0 && first_of_rb) mbar_wait(dz_empty, (n_dz & 1) ^ 1);
                 tc_fence_after();
+                tr(210 + h);
                 const uint32_t d = tmem_base + 256 + h * 128;
-                const uint32_t a0 = smem_u32(p_smem + w * kSub);
-                const uint32_t b0 = smem_u32(b_smem + st * B_BYTES) + a * 8192;
+                const uint32_t a_lo = p_lo0 + ((h * 2 * kSub) >> 4);
+                const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), kSub);
+                if (elect_one()) {
+                    umma_bf16_lo_dyn(d, a_lo, b_lo, idesc2, first_of_rb ? 0u : 1u);
 #pragma unroll
-                for (int j16 = 0; j16 < 4; ++j16)
-                    umma_bf16(d, smem_desc_sw128(a0 + j16 * 32, 16, 1024),
-                              smem_desc_sw128(b0 + j16 * 2048, kSub, 1024), idesc2,
-                              (first_of_rb && a == 0 && j16 == 0) ? 0u : 1u);
-                umma_commit(p_empty(w));
-                if (w == 3) {
-                    umma_commit(b_empty(st));
-                    if (last_of_rb) { umma_commit(dz_full); ++n_dz; }
+                    for (int j16 = 1; j16 < 8; ++j16)
+                        umma_bf16_lo<true>(d, a_lo + (((j16 >> 2) * kSub + (j16 & 3) * 32) >> 4),
+                                           b_lo + ((j16 * 2048) >> 4), idesc2);
+                    umma_commit(p_empty(h));
+                    if (h == 1) {
+                        umma_commit(b_empty(st));
+                        if (last_of_rb) umma_commit(dz_full);
+                    }
                 }
+                __syncwarp();
+                if (h == 1 && last_of_rb) ++n_dz;
+                tr(220 + h);
             };
 
-            for (int w = 0; w < 4; ++w) mma1(0, w);
+            // tile bookkeeping without divisions: position of the current tile inside its row block
+            int ct_cur = t0 % p.CT;
+            bool first_cur = true;
+            bool last_cur = (n_tiles == 1) || (ct_cur == p.CT - 1);
+            mma1(0, 0, first_cur, last_cur);
+            mma1(0, 1, first_cur, last_cur);
             for (int i = 0; i < n_tiles; ++i) {
-                for (int w = 0; w < 4; ++w) {
-                    mma2(i, w);
-                    if (i + 1 < n_tiles) mma1(i + 1, w);
+                int ct_next = ct_cur + 1;
+                if (ct_next == p.CT) ct_next = 0;
+                const bool has_next = (i + 1 < n_tiles);
+                const bool first_next = (ct_next == 0);
+                const bool last_next = (i + 2 >= n_tiles) || (ct_next == p.CT - 1);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    mma2(i, h, first_cur, last_cur);
+                    if (has_next) mma1(i + 1, h, first_next, last_next);
                 }
+                ct_cur = ct_next;
+                first_cur = first_next;
+                last_cur = last_next;
             }
         }
     } else {
@@ -500,6 +536,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         int cur_rb = -1, idx = 0, li = 0, gi = 0, rep_i = 0, n_dz = 0;
         bool row_ok = false, rb_fast = false;
         float lse2_i = INFINITY, m0 = 0.f, R_i = 0.f, nia_i = 0.f;
+        Tracer tr(p.trace, (warp == 2) ? 1 : (warp == 6 ? 2 : -1));
 
         // raw log-sum-exp of the column this thread stages for a tile (threads 0..63 of the warpgroup)
         auto load_col = [&](int tau) -> float {
@@ -563,6 +600,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             const int j0 = ct * kBN + a * 64;             // first column of this warpgroup's sub-tile
             // ---- per-column data of this sub-tile (threads 0..63 stage one column each):
             //      cj[c] = [anchor_j] 2^(m0 - lse2_j)   (1-exp path),  lj[c] = lse2_j or +inf   (2-exp path)
+            tr(1);
             named_bar_sync(bar_id, kBMH);                 // everybody is done with the previous tile's columns
             if (wtid < 64) {
                 const int j = j0 + wtid;
@@ -580,7 +618,9 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             const bool pred = (j0 + 64 > p.n_k) || (g_lo < j0 + 64 && j0 < g_lo + kBMH);
             const bool fast = rb_fast && !pred && ((myflags[0] | myflags[1]) == 0u);
 
-            mbar_wait(s_full(w), idx & 1);
+            tr(2);
+            mbar_wait(s_full(h), idx & 1);
+            tr(3);
             tc_fence_after();
             if (fast) {
                 // ---------------- common case: one exp per element, fully unrolled, S released early
@@ -590,9 +630,9 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 l_next = load_col(tau + 1);                 // global load flies during this sub-tile
                 tmem_ld_wait_dep(va);
                 tmem_ld_wait_dep(vb);
-                tc_fence_before();
-                mbar_arrive(s_empty(w));                    // S[w] is in registers: next MMA1 may start
-                mbar_wait(p_empty(w), (idx & 1) ^ 1);       // MMA2 of the previous tile has consumed P[w]
+                tr(4);
+                mbar_wait(p_empty(h), (idx & 1) ^ 1);       // MMA2 of the previous tile has consumed P[h]
+                tr(5);
                 auto process = [&](uint32_t (&v)[32], int cc) {
 #pragma unroll
                     for (int qq = 0; qq < 4; ++qq) {
@@ -628,7 +668,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             } else {
                 // ---------------- rare case (self / ragged tiles, mode `one`, wild LSE ranges): two exps,
                 // eight columns at a time straight from TMEM, compact code
-                mbar_wait(p_empty(w), (idx & 1) ^ 1);
+                mbar_wait(p_empty(h), (idx & 1) ^ 1);
 #pragma unroll 1
                 for (int g8 = 0; g8 < 8; ++g8) {
                     uint32_t v8[8];
@@ -648,12 +688,14 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                     }
                     store_p8(myp, g8, r, pv);
                 }
-                tc_fence_before();
-                mbar_arrive(s_empty(w));
                 l_next = load_col(tau + 1);
             }
+            tr(6);
+            // publishing P[h] also hands S[h] back: every TMEM read of this thread is complete
+            tc_fence_before();
             fence_proxy_async_smem();
-            mbar_arrive(p_full(w));
+            mbar_arrive(p_full(h));
+            tr(7);
             ++idx;
         }
         if (cur_rb >= 0) drain(cur_rb);
@@ -759,6 +801,8 @@ static int make_tmap(const scb_supcon_problem* p, CUtensorMap* out) {
 }
 
 static constexpr int kMaxSlots = 32;
+static long long* g_trace = nullptr;   // set through scb_debug_set_trace (diagnostics only)
+void tc_set_trace(long long* p) { g_trace = p; }
 
 struct TcGeom { int CT, RB, T, q, grid, n_split; };
 
@@ -768,11 +812,11 @@ static TcGeom tc_geom(int n_k, int rows) {
     g.RB = (int)ceil_div(rows, kBM);
     g.T = g.CT * g.RB;
     int q = (int)ceil_div(g.T, sm_count());
-    const int qmin = (int)ceil_div(g.CT, kMaxSlots - 1);
+    const int qmin = (int)ceil_div(g.CT, kMaxSlots / 2 - 1);
     if (q < qmin) q = qmin;
     g.q = q;
     g.grid = (int)ceil_div(g.T, q);
-    g.n_split = (int)ceil_div(g.CT, q) + 1;
+    g.n_split = 2 * ((int)ceil_div(g.CT, q) + 1);      // (CTA overlapping the row block) x (column half)
     if (g.n_split > kMaxSlots) g.n_split = kMaxSlots;
     return g;
 }
@@ -808,6 +852,7 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
     t->npos_row = (const float*)ws; ws += align256((size_t)p->n_k * 4);
     t->nia_row = (const float*)ws;
     t->lse_all = nullptr; t->grad_out = nullptr; t->coef_scale = 0.f; t->out_dk = nullptr; t->ld_dk = 0;
+    t->trace = g_trace;
 }
 
 static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, cudaStream_t stream) {
@@ -842,7 +887,7 @@ int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* pa
 #define SCB_LAUNCH_FWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
         if (int e = set_smem(supcon_tc_fwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        supcon_tc_fwd_kernel<KCH_, LAB_><<<g.grid, kThreads, smem, stream>>>(tmap, t);                  \
+        supcon_tc_fwd_kernel<KCH_, LAB_><<<g.grid, kTcThreads, smem, stream>>>(tmap, t);                  \
     } while (0)
     if (kch == 2) { if (lab) SCB_LAUNCH_FWD(2, true); else SCB_LAUNCH_FWD(2, false); }
     else { if (lab) SCB_LAUNCH_FWD(1, true); else SCB_LAUNCH_FWD(1, false); }
@@ -883,7 +928,7 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
 #define SCB_LAUNCH_BWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
         if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        supcon_tc_bwd_kernel<KCH_, LAB_><<<g.grid, kBwdThreads, smem, stream>>>(tmap, t);                  \
+        supcon_tc_bwd_kernel<KCH_, LAB_><<<g.grid, kTcThreads, smem, stream>>>(tmap, t);                  \
     } while (0)
     if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
     else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }

@@ -15,4 +15,8 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
                 const float* npos_all, const float* grad_out, int n_anchor_total, float* out_dk,
                 int ld_dk, void* workspace, cudaStream_t stream);
 
+// diagnostics: device buffer of 3 x 1024 int64 that CTA 0 of the backward kernel fills with
+// (event id, clock64) pairs; nullptr switches tracing off
+void tc_set_trace(long long* p);
+
 }  // namespace scb

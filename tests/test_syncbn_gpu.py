@@ -245,7 +245,7 @@ def test_module_variants():
     bn2.load_state_dict({k: v for k, v in bn.state_dict().items()})
     c = bn(x)
     # the cross-CTA sums use float atomics: the order, hence the last bit, may differ between calls
-    assert torch.allclose(a, c, atol=2e-6, rtol=0)
+    assert torch.allclose(a, c, atol=1e-5, rtol=0)
 
 
 def test_fused_relu():

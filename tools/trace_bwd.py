@@ -1,0 +1,43 @@
+"""Timeline of CTA 0 of the tensor-core backward kernel (diagnostics): python tools/trace_bwd.py"""
+import os
+import sys
+
+import torch
+import torch.nn.functional as F
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from simclr_pytorch_distributed_b200 import _lib, losses as L   # noqa: E402
+
+lib = _lib.load()
+dev = torch.device('cuda')
+B, V, D = 4096, 2, 128
+z = F.normalize(torch.randn(B, V, D, device=dev), dim=-1).to(torch.bfloat16)
+plan = L.LossPlan(B, V, D, engine=_lib.ENGINE_BF16)
+k = torch.empty((plan.n_k, plan.ldk), dtype=plan.k_torch, device=dev)
+stats = torch.empty((4, plan.n_k), dtype=torch.float32, device=dev)
+loss = torch.empty((), dtype=torch.float32, device=dev)
+g = torch.ones((), dtype=torch.float32, device=dev)
+dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
+prob = L._problem(plan, k, None, None, None, 0.5, 0.07)
+L.launch_prep(lib, z, plan, False, k, None, None)
+L.launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
+for it in range(3):
+    L.launch_backward(lib, prob, plan, stats[0], stats[2], g, dk, dev)
+torch.cuda.synchronize()
+trace = torch.zeros(3 * 1024, dtype=torch.int64, device=dev)
+lib.scb_debug_set_trace(trace.data_ptr())
+L.launch_backward(lib, prob, plan, stats[0], stats[2], g, dk, dev)
+torch.cuda.synchronize()
+lib.scb_debug_set_trace(None)
+t = trace.cpu().view(3, 512, 2)
+t0 = min(int(t[r, 0, 1]) for r in range(3) if int(t[r, 511, 0]) > 0)
+names = {1: 'tile start', 2: 'cols staged', 3: 'S ready', 4: 'S in regs', 5: 'P free', 6: 'P written', 7: 'P published'}
+for role, label in ((0, 'MMA issuer'), (1, 'epilogue WG0'), (2, 'epilogue WG1')):
+    n = int(t[role, 511, 0])
+    print('==', label, n, 'events')
+    prev = None
+    for i in range(min(n, 90)):
+        eid, clk = int(t[role, i, 0]), int(t[role, i, 1]) - t0
+        d = '' if prev is None else '+%d' % (clk - prev)
+        prev = clk
+        print('  %6d %-6s %s %s' % (clk, d, eid, names.get(eid, '') if role else ''))
