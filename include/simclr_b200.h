@@ -157,6 +157,21 @@ int scb_bn_stats(const void* x, int dtype, int channels_last, int64_t outer, int
                  int64_t inner, float* out_stats, void* workspace, int64_t workspace_bytes,
                  void* stream);
 
+/* No counterpart in the reference.  Same result as scb_bn_stats, for callers that cannot allocate
+ * device memory where they need the statistics -- e.g. a host framework whose memory pool already
+ * owns the whole GPU, so that a cudaMalloc for scratch would fail or compete with it.  The scratch
+ * is a fixed array built into the library (about 33 KiB of device memory on every GPU that loads
+ * the library, kept until the process exits), so the entry point calls no cudaMalloc / cudaFree /
+ * allocating routine; the caller still passes x and out_stats.
+ *   - at most SCB_BN_NOALLOC_MAX_CHANNELS channels; more is rejected with SCB_ERR_ARG;
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress with
+ *     that device current); make that first call before any stream capture;
+ *   - every call uses the same array (the part it needs is cleared first, on `stream`): calls that
+ *     overlap on the GPU -- different streams, or two host threads -- race with each other. */
+#define SCB_BN_NOALLOC_MAX_CHANNELS 4096
+int scb_bn_stats_noalloc(const void* x, int dtype, int channels_last, int64_t outer, int channels,
+                         int64_t inner, float* out_stats, void* stream);
+
 /* Replaces torch.batch_norm_gather_stats_with_counts + torch.batch_norm_elemt
  * (_functions.py:106-122; Normalization.cuh:458-502): merges `n_ranks` gathered messages
  * stats_all [n_ranks, 2C+1] (Chan, rank order, empty ranks skipped), updates running_mean /

@@ -27,6 +27,7 @@ MASK_SIMCLR, MASK_LABELS, MASK_EXPLICIT = 0, 1, 2
 MODE_ALL, MODE_ONE = 0, 1
 ENGINE_FP32, ENGINE_BF16, ENGINE_BF16X3 = 0, 1, 2
 BN_RELU = 1
+BN_NOALLOC_MAX_CHANNELS = 4096      # SCB_BN_NOALLOC_MAX_CHANNELS
 
 _lock = threading.Lock()
 _lib = None
@@ -109,6 +110,7 @@ PROTOTYPES = {
     'scb_supcon_finish': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _i64, _i64, _vp]),
     'scb_bn_workspace_bytes': (_i64, [_i]),
     'scb_bn_stats': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i64, _vp]),
+    'scb_bn_stats_noalloc': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp]),
     'scb_bn_apply': (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _i, _vp, _vp, _vp, _vp, _f, _f,
                           _vp, _vp, _vp, _i, _vp]),
     'scb_bn_backward_reduce': (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp,

@@ -764,3 +764,52 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, void* dx, in
     count_launch();
     return SCB_OK;
 }
+
+// ================================================================== allocation-free statistics
+// Some hosts of this library are not allowed to ask CUDA for memory at the point where they call
+// batch-norm statistics: an embedding framework whose own pool has already claimed the whole
+// device (a cudaMalloc for our scratch would fail or fight that pool), or a call site where
+// allocating is simply against the rules of the surrounding system.  For them the scratch of the
+// statistics kernel lives inside the library image: a fixed array in device memory that every GPU
+// loading the library carries until the process exits.  Nothing here calls cudaMalloc, cudaFree or
+// any routine that allocates.
+//
+// kNoAllocMaxChannels bounds the array (2 floats per channel plus the ticket word).  Its name is a
+// host-side stand-in only: the device address is looked up once per device with
+// cudaGetSymbolAddress while that device is current, and that address is what the kernel receives.
+constexpr int kNoAllocMaxChannels = SCB_BN_NOALLOC_MAX_CHANNELS;
+constexpr size_t kNoAllocScratchBytes = (size_t)2 * kNoAllocMaxChannels * sizeof(float) + 256;
+static __device__ __align__(256) unsigned char g_bn_noalloc_scratch[kNoAllocScratchBytes];
+
+#include <mutex>
+namespace {
+std::mutex g_noalloc_mutex;
+void* g_noalloc_ptr[64] = {nullptr};   // device address of the array, per device ordinal
+}  // namespace
+
+extern "C" int scb_bn_stats_noalloc(const void* x, int dtype, int channels_last, int64_t outer, int channels,
+                                    int64_t inner, float* out_stats, void* stream_) {
+    SCB_REQUIRE(channels >= 1 && channels <= kNoAllocMaxChannels,
+                "bn_stats_noalloc: %d channels exceed the built-in scratch (at most %d); use scb_bn_stats with "
+                "caller-provided scratch instead", channels, kNoAllocMaxChannels);
+    int dev = 0;
+    SCB_CUDA_OK(cudaGetDevice(&dev));
+    SCB_REQUIRE(dev >= 0 && dev < 64, "bn_stats_noalloc: device ordinal %d out of range", dev);
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (g_noalloc_ptr[dev] == nullptr) {
+            // first call on this device: resolve the symbol to this device's copy of the array
+            void* ptr = nullptr;
+            SCB_CUDA_OK(cudaGetSymbolAddress((void**)&ptr, g_bn_noalloc_scratch));
+            g_noalloc_ptr[dev] = ptr;
+        }
+        scratch = g_noalloc_ptr[dev];
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    // The array is shared by every call and keeps whatever the last one left behind; the kernel needs
+    // its accumulators and ticket to start at zero, so clear the part this call uses.
+    const int64_t need = scb_bn_workspace_bytes(channels);
+    SCB_CUDA_OK(cudaMemsetAsync(scratch, 0, (size_t)need, stream));
+    return scb_bn_stats(x, dtype, channels_last, outer, channels, inner, out_stats, scratch, need, stream_);
+}
