@@ -1,0 +1,117 @@
+"""Multi-GPU parity on one box (NCCL, one process per GPU); skipped when fewer than 2 GPUs are visible.
+
+  * SyncBatchNorm (ours) vs stock torch.nn.SyncBatchNorm on the same per-rank inputs;
+  * DistributedSupConLoss vs the oracle evaluated on the concatenated global batch
+    (the W-rank restatement of /root/reference/main_supcon.py:266-290)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def _n_gpus():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+def _worker(rank, world, port, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
+    ok, notes = True, []
+    try:
+        from simclr_pytorch_distributed_b200 import SyncBatchNorm
+        from simclr_pytorch_distributed_b200.gather import DistributedSupConLoss
+        from oracle import supcon_forward_backward, normalize_rows, normalize_rows_backward
+        dev = torch.device('cuda', rank)
+        # ---------------- SyncBN vs stock SyncBatchNorm (NHWC bf16 and NCHW fp32)
+        for dtype, cl in ((torch.bfloat16, True), (torch.float32, False)):
+            g = torch.Generator().manual_seed(4321 + rank)
+            x = (torch.randn(32, 64, 8, 8, generator=g) * 1.5 + 0.5 + rank).to(dev, dtype)
+            dy = torch.randn(32, 64, 8, 8, generator=g).to(dev, dtype)
+            if cl:
+                x = x.contiguous(memory_format=torch.channels_last)
+                dy = dy.contiguous(memory_format=torch.channels_last)
+            ours = SyncBatchNorm(64).to(dev)
+            ref = torch.nn.SyncBatchNorm(64).to(dev)
+            with torch.no_grad():
+                ours.weight.uniform_(0.5, 1.5)
+                ours.bias.normal_(0, 0.1)
+            dist.broadcast(ours.weight.data, 0)
+            dist.broadcast(ours.bias.data, 0)
+            ref.load_state_dict(ours.state_dict())
+            xa = x.clone().requires_grad_(True)
+            xb = x.clone().requires_grad_(True)
+            ya = ours(xa)
+            ya.backward(dy)
+            yb = ref(xb)
+            yb.backward(dy)
+            tol = 2.0 ** -7 if dtype == torch.bfloat16 else 1e-5
+            e_y = ((ya.float() - yb.float()).abs() / (yb.float().abs() + 1)).max().item()
+            e_x = ((xa.grad.float() - xb.grad.float()).abs() / (xb.grad.float().abs() + 1)).max().item()
+            e_rv = (ours.running_var - ref.running_var).abs().max().item()
+            e_rm = (ours.running_mean - ref.running_mean).abs().max().item()
+            e_gw = ((ours.weight.grad - ref.weight.grad).abs() / (ref.weight.grad.abs() + 1)).max().item()
+            notes.append('bn %s: y %.2e dx %.2e rm %.2e rv %.2e dgamma %.2e' % (dtype, e_y, e_x, e_rm, e_rv, e_gw))
+            ok = ok and e_y <= tol and e_x <= tol and e_rv <= 1e-5 and e_rm <= 1e-5 and e_gw <= 1e-3
+        # ---------------- row-sharded loss vs oracle on the concatenated batch
+        bsz, V, D = 96, 2, 128
+        for engine, dtype, tol in (('fp32', torch.float32, 1e-4), ('bf16', torch.bfloat16, 2e-3 + 2 ** -8)):
+            rng = np.random.default_rng(99)
+            z_all = rng.standard_normal((world * bsz, V, D)) * 2.0 + 0.3          # raw (un-normalised) outputs
+            z_all = torch.from_numpy(z_all).to(dtype)
+            sl = slice(rank * bsz, (rank + 1) * bsz)
+            f = z_all[sl].to(dev).requires_grad_(True)
+            crit = DistributedSupConLoss(temperature=0.5, engine=engine, normalize=True)
+            loss = crit(f)
+            loss.backward()
+            raw = z_all.double().numpy()
+            zh = normalize_rows(raw)
+            if engine == 'bf16':       # operands are the bf16-rounded normalised rows
+                zh_used = torch.from_numpy(zh).to(torch.bfloat16).double().numpy()
+            else:
+                zh_used = zh
+            ref_loss, g_hat, _ = supcon_forward_backward(zh_used, temperature=0.5)
+            ref_grad = normalize_rows_backward(raw, g_hat)[sl]
+            e_l = abs(float(loss) - ref_loss) / abs(ref_loss)
+            got = f.grad.double().cpu().numpy()
+            e_g = np.linalg.norm((got - ref_grad).ravel()) / np.linalg.norm(ref_grad.ravel())
+            notes.append('loss %s: rel loss %.2e rel grad %.2e' % (engine, e_l, e_g))
+            ok = ok and e_l <= tol and e_g <= 2 * tol
+    except Exception as e:     # report instead of hanging the other ranks
+        ok = False
+        notes.append('EXC %r' % (e,))
+    finally:
+        q.put((rank, ok, notes))
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world', [2, 4, 8])
+def test_multi_gpu_parity(world):
+    if _n_gpus() < world:
+        pytest.skip('needs %d GPUs' % world)
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+    results = sorted(q.get(timeout=10) for _ in range(world))
+    for r in results:
+        print(r)
+    assert all(p.exitcode == 0 for p in procs)
+    assert all(r[1] for r in results), results
