@@ -520,19 +520,18 @@ def main():
             out.update({'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'higher_is_better': True,
                         'vs_baseline': None, 'data': 'synthetic'})
 
-    # keep the GPU under the same load until the clock sampler has a few readings
+    # keep the GPU under the same load until the clock sampler has a few readings.  Every rank runs
+    # the SAME number of extra steps (they contain collectives when N > 1): derived from the
+    # max-over-ranks step time, which all ranks hold.
+    n_extra = max(20, min(20000, int(1200.0 / max(ms / args.steps, 1e-3))))
+    for i in range(n_extra):
+        step_res(i)
+        if i % 50 == 49:
+            torch.cuda.synchronize()
+    torch.cuda.synchronize()
     if rank == 0:
-        t_end = time.time()
-        extra_t0 = time.time()
-        i = 0
-        while time.time() - extra_t0 < 1.2:
-            step_res(i)
-            i += 1
-            if i % 50 == 0:
-                torch.cuda.synchronize()
-        torch.cuda.synchronize()
         out['clocks'] = sampler.stop(t_load0, time.time())
-        out['clocks']['note'] = ('sampled every 100 ms from the first warm-up step to 1.2 s of the same steps '
+        out['clocks']['note'] = ('sampled every 100 ms from the first warm-up step to ~1.2 s of the same steps '
                                  'run right after the timed regions (the timed regions alone are shorter than '
                                  'one sampling period)')
     barrier(world)
