@@ -37,6 +37,14 @@ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 int sm_count();   // SMs of the current device (cached per device)
 void count_launch(int n = 1);   // bookkeeping behind scb_launch_count()
 
+// The loss pipeline alternates tiny helper kernels with the persistent tensor-core kernels, which need
+// the maximum shared-memory carve-out; asking for the same carve-out everywhere avoids an L1/shared
+// re-partition of every SM between consecutive launches.
+template <typename Kern>
+inline void prefer_max_smem_carveout(Kern kern) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+}
+
 // ---------------------------------------------------------------- dtype plumbing
 template <typename T> struct Vec16 { static constexpr int N = 16 / sizeof(T); };
 

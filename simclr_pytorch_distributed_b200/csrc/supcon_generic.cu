@@ -164,14 +164,34 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
                 const int rb = r >> 8;
                 n_split = 2 * (((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1);
             }
-            float m = -INFINITY;
-            for (int s = 0; s < n_split; ++s) m = fmaxf(m, part[((int64_t)s * 4 + 0) * n_rows + r]);
-            float sum = 0.f; ps = 0.f; np = 0.f;
-            for (int s = 0; s < n_split; ++s) {
-                const float ms = part[((int64_t)s * 4 + 0) * n_rows + r];
-                if (ms > -INFINITY) sum += part[((int64_t)s * 4 + 1) * n_rows + r] * expf(ms - m);
-                ps += part[((int64_t)s * 4 + 2) * n_rows + r];
-                np += part[((int64_t)s * 4 + 3) * n_rows + r];
+            // slots are merged eight at a time so that all their loads are in flight together
+            float m = -INFINITY, sum = 0.f;
+            ps = 0.f; np = 0.f;
+            for (int s0 = 0; s0 < n_split; s0 += 8) {
+                float vm[8], vs[8], vp[8], vn[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const bool ok = s0 + u < n_split;
+                    const float* q = part + ((int64_t)(s0 + u) * 4) * n_rows + r;
+                    vm[u] = ok ? q[0] : -INFINITY;
+                    vs[u] = ok ? q[n_rows] : 0.f;
+                    vp[u] = ok ? q[2 * (int64_t)n_rows] : 0.f;
+                    vn[u] = ok ? q[3 * (int64_t)n_rows] : 0.f;
+                }
+                float cm = vm[0];
+#pragma unroll
+                for (int u = 1; u < 8; ++u) cm = fmaxf(cm, vm[u]);
+                const float nm = fmaxf(m, cm);
+                if (nm > -INFINITY) {
+                    float acc = (m > -INFINITY) ? sum * expf(m - nm) : 0.f;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (vm[u] > -INFINITY) acc += vs[u] * expf(vm[u] - nm);
+                    sum = acc;
+                    m = nm;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) { ps += vp[u]; np += vn[u]; }
             }
             lse = m + logf(sum);
             local += (double)(-loss_scale * (ps / np - lse));        // losses.py:87,90 (0/0 -> nan)
@@ -352,6 +372,7 @@ int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split,
                     float* out_loss_sum, void* scratch, cudaStream_t stream) {
     int ctas = (int)ceil_div(n_rows, kFinThreads);
     if (ctas > kFinMaxCtas) ctas = kFinMaxCtas;
+    prefer_max_smem_carveout(supcon_finalize_kernel);
     supcon_finalize_kernel<<<ctas, kFinThreads, 0, stream>>>(part, n_split, flat_q, flat_ct, n_rows, row_begin,
                                                              RowMap::of(p), p->mode, p->loss_scale, inv_anchors,
                                                              out_lse, out_possum, out_npos, out_loss_sum, scratch);
@@ -376,6 +397,8 @@ extern "C" int scb_supcon_prep(const void* features, int feat_dtype, int n_sampl
     const int64_t rows = (int64_t)n_samples * n_views;
     const unsigned blocks = (unsigned)ceil_div(rows * 32, 256);
     SCB_DISPATCH_FLOAT(feat_dtype, TI, {
+        prefer_max_smem_carveout(supcon_prep_kernel<TI, float>);
+        prefer_max_smem_carveout(supcon_prep_kernel<TI, __nv_bfloat16>);
         if (k_dtype == SCB_F32)
             supcon_prep_kernel<TI, float><<<blocks, 256, 0, stream>>>(
                 (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize, eps,
@@ -402,6 +425,7 @@ extern "C" int scb_supcon_finish(const float* dk, int ld_dk, const void* feature
     const int64_t rows = (int64_t)n_samples * n_views;
     const unsigned blocks = (unsigned)ceil_div(rows * 32, 256);
     SCB_DISPATCH_FLOAT(feat_dtype, TF, {
+        prefer_max_smem_carveout(supcon_finish_kernel<TF>);
         supcon_finish_kernel<TF><<<blocks, 256, 0, stream>>>(
             dk, ld_dk, (const TF*)features, n_samples, n_views, dim, stride_sample, stride_view,
             normalize, inv_norm, (TF*)out_dfeatures, out_stride_sample, out_stride_view);

@@ -49,6 +49,7 @@ struct TcParams {
     float coef_scale;                   // (T/Tb) / n_anchor_total
     float* out_dk;
     int ld_dk;
+    float* dk_part;                     // backward partials [slot][RB*256][ldk] (one slot per CTA sharing a row block)
     long long* trace;                   // optional (debug): per-role timestamps of CTA 0
 };
 
@@ -326,19 +327,33 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     }
 }
 
-// pack 8 fp32 -> bf16 and store them as 16-byte chunk `chunk16` of row r of a [128 x 64] K-major,
-// 128B-swizzled UMMA operand tile (prow = tile base + r*128)
-__device__ __forceinline__ void store_p8(uint8_t* prow, int chunk16, int r, const float (&pv)[8]) {
-    uint4 pk;
-    __nv_bfloat162 h0 = __floats2bfloat162_rn(pv[0], pv[1]);
-    __nv_bfloat162 h1 = __floats2bfloat162_rn(pv[2], pv[3]);
-    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[4], pv[5]);
-    __nv_bfloat162 h3 = __floats2bfloat162_rn(pv[6], pv[7]);
-    pk.x = *reinterpret_cast<uint32_t*>(&h0);
-    pk.y = *reinterpret_cast<uint32_t*>(&h1);
-    pk.z = *reinterpret_cast<uint32_t*>(&h2);
-    pk.w = *reinterpret_cast<uint32_t*>(&h3);
-    *reinterpret_cast<uint4*>(prow + ((chunk16 ^ (r & 7)) << 4)) = pk;
+// In-register transpose of the 32 x 32 block a warp holds (v[i] of lane l = element (l, i)):
+// afterwards v[i] of lane l = element (i, l), so a store of v[i] writes 32 consecutive columns of row i.
+__device__ __forceinline__ void warp_transpose32(uint32_t (&v)[32], int lane) {
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+        const bool hi = (lane & s) != 0;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            if ((i & s) == 0) {
+                const uint32_t send = hi ? v[i] : v[i + s];
+                const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, s);
+                if (hi) v[i] = recv; else v[i + s] = recv;
+            }
+        }
+    }
+}
+
+// pack 16 fp32 -> bf16 and write them as 8 consecutive 32-bit TMEM columns of this thread's lane
+// (UMMA A operand in TMEM: two K-consecutive bf16 per column, even index in the low half)
+__device__ __forceinline__ void store_p16(uint32_t taddr, const float (&pv)[16]) {
+    uint32_t wds[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[2 * i], pv[2 * i + 1]);
+        wds[i] = *reinterpret_cast<uint32_t*>(&h2);
+    }
+    tmem_st8(taddr, wds);
 }
 
 // =================================================================================== backward
@@ -347,8 +362,12 @@ __device__ __forceinline__ void store_p8(uint8_t* prow, int chunk16, int r, cons
 // MMA <-> epilogue hand-over is a [128 x 64] sub-tile: S[w] (64 TMEM columns) and P[w] (one
 // 16 KB swizzled sub-tile in shared memory).  While one warpgroup waits for its MMA2 + next MMA1
 // the other three keep the MUFU pipe busy.
-// smem: A[2*KCH*kSub] | B[3][KCH*kSub] | P[4][kSub] | cols[4][2][64] f32 | flags | rowred | barriers | tmem slot
-// TMEM: S[h] at columns h*128 (warpgroup (h, a) reads columns h*128 + a*64 ..), dK[h] at 256 + h*128.
+// P never touches shared memory: each thread packs its 64 values to bf16 and writes them with tcgen05.st
+// over the first half of the S columns it has just read; the second MMA takes its A operand from TMEM.
+// (With P in shared memory the two MMAs plus the P stores need ~160 B/clk of shared-memory bandwidth.)
+// smem: A[2*KCH*kSub] | B[4][KCH*kSub] | cols[4][2][64] f32 | flags | rowred | barriers | tmem slot
+// TMEM: S[h] at columns h*128 (warpgroup (h, a) owns columns h*128 + a*64 .. +64 and stores its P words in
+//       the first 32 of them), dK[h] at 256 + h*128.
 
 template <int KCH, bool kLabels>
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -356,11 +375,10 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int A_BYTES = 2 * KCH * kSub;
     constexpr int B_BYTES = KCH * kSub;
-    constexpr int NSB = 3;
+    constexpr int NSB = 4;
     uint8_t* a_smem = smem;
     uint8_t* b_smem = a_smem + A_BYTES;
-    uint8_t* p_smem = b_smem + NSB * B_BYTES;                            // [4][kSub]
-    float* cols = reinterpret_cast<float*>(p_smem + 4 * kSub);            // [4 wg][2 buf][64]
+    float* cols = reinterpret_cast<float*>(b_smem + NSB * B_BYTES);       // [4 wg][2 arrays][64]
     uint32_t* flags = reinterpret_cast<uint32_t*>(cols + 4 * 2 * 64);     // [4 wg][2 buf][2 warps]
     float* rowred = reinterpret_cast<float*>(flags + 16);                 // [4 wg][4 warps][2]
     uint64_t* bars = reinterpret_cast<uint64_t*>(rowred + 32);            // 26 used
@@ -369,21 +387,18 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     auto a_full = [&]() { return bar0 + 8u * 0; };
     auto a_empty = [&]() { return bar0 + 8u * 1; };
     auto b_full = [&](int s) { return bar0 + 8u * (2 + s); };
-    auto b_empty = [&](int s) { return bar0 + 8u * (5 + s); };
-    // per row half h: S[h] ready / P[h] published by its two warpgroups / P[h] consumed
-    auto s_full = [&](int h) { return bar0 + 8u * (8 + h); };
+    auto b_empty = [&](int s) { return bar0 + 8u * (6 + s); };
+    // per row half h: S[h] ready / P[h] published (in TMEM) by its two warpgroups
+    auto s_full = [&](int h) { return bar0 + 8u * (10 + h); };
     auto p_full = [&](int h) { return bar0 + 8u * (16 + h); };
-    auto p_empty = [&](int h) { return bar0 + 8u * (20 + h); };
     const uint32_t dz_full = bar0 + 8u * 24, dz_empty = bar0 + 8u * 25;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[1023] = clock64();
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
     if (threadIdx.x == 0) {
         for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);          // a, b, s_full
-        for (int h = 0; h < 2; ++h) {
-            mbar_init(p_full(h), 2 * kBMH);
-            mbar_init(p_empty(h), 1);
-        }
+        for (int h = 0; h < 2; ++h) mbar_init(p_full(h), 2 * kBMH);
         mbar_init(dz_full, 1);
         mbar_init(dz_empty, 4 * kBMH);
         fence_barrier_init();
@@ -394,6 +409,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[2047] = clock64();
 
     const int t0 = blockIdx.x * p.q;
     const int t1 = min(p.T, t0 + p.q);
@@ -438,7 +454,6 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             int n_a = 0, n_dz = 0;
             const int n_tiles = t1 - t0;
             const uint32_t a_lo0 = desc_lo(smem_u32(a_smem), 16);
-            const uint32_t p_lo0 = desc_lo(smem_u32(p_smem), 16);
 
             // S[h] = A_h (128 rows) x B^T (128 columns) of tile i.  S[h] is known to be free: both of
             // its warpgroups pulled it into registers before they published P[h], which the MMA2 of the
@@ -465,7 +480,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 }
                 __syncwarp();
             };
-            // dK[h] += P[h] (128 x 128, K-major, two swizzled sub-tiles) x K_j (128 rows read MN-major)
+            // dK[h] += P[h] (128 x 128 bf16 held in TMEM over S[h]) x K_j (128 rows read MN-major)
             auto mma2 = [&](int i, int h, bool first_of_rb, bool last_of_rb) {
                 const int st = i % NSB;
                 tr(200 + h);
@@ -474,15 +489,13 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 tc_fence_after();
                 tr(210 + h);
                 const uint32_t d = tmem_base + 256 + h * 128;
-                const uint32_t a_lo = p_lo0 + ((h * 2 * kSub) >> 4);
+                const uint32_t pa = tmem_base + h * 128;
                 const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), kSub);
                 if (elect_one()) {
-                    umma_bf16_lo_dyn(d, a_lo, b_lo, idesc2, first_of_rb ? 0u : 1u);
+                    umma_bf16_ts_dyn(d, pa, b_lo, idesc2, first_of_rb ? 0u : 1u);
 #pragma unroll
-                    for (int j16 = 1; j16 < 8; ++j16)
-                        umma_bf16_lo<true>(d, a_lo + (((j16 >> 2) * kSub + (j16 & 3) * 32) >> 4),
-                                           b_lo + ((j16 * 2048) >> 4), idesc2);
-                    umma_commit(p_empty(h));
+                    for (int j16 = 1; j16 < 8; ++j16)      // 16 columns of P = 8 TMEM columns; column half a at +64
+                        umma_bf16_ts<true>(d, pa + (j16 >> 2) * 64 + (j16 & 3) * 8, b_lo + ((j16 * 2048) >> 4), idesc2);
                     if (h == 1) {
                         umma_commit(b_empty(st));
                         if (last_of_rb) umma_commit(dz_full);
@@ -524,12 +537,11 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         const int wtid = (warp - 2 - w * 4) * 32 + lane;
         const int wwarp = wtid >> 5;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
-        const float coef = p.grad_out[0] * p.coef_scale * p.inv_T;
         float* cj = cols + w * 128;                       // [64] 1-exp column factors
         float* lj = cj + 64;                              // [64] column log-sum-exps (log2 domain)
         uint32_t* myflags = flags + w * 4;
         float* myrow = rowred + w * 8;
-        uint8_t* myp = p_smem + w * kSub + r * 128;
+        const uint32_t p_taddr = tmem_base + lane_addr + w * 64;      // P words go over this thread's S columns
         const bool mode_all = (p.mode == SCB_MODE_ALL);
         const int bar_id = 1 + w;
 
@@ -539,39 +551,43 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         Tracer tr(p.trace, (warp == 2) ? 1 : (warp == 6 ? 2 : -1));
 
         // raw log-sum-exp of the column this thread stages for a tile (threads 0..63 of the warpgroup)
-        auto load_col = [&](int tau) -> float {
-            if (wtid >= 64 || tau >= t1) return 0.f;
-            const int rbn = tau / p.CT;
-            const int j = (tau - rbn * p.CT) * kBN + a * 64 + wtid;
+        auto load_col = [&](int ct_of_tile, bool tile_exists) -> float {
+            if (wtid >= 64 || !tile_exists) return 0.f;
+            const int j = ct_of_tile * kBN + a * 64 + wtid;
             return (j < p.n_k) ? __ldg(p.lse_all + j) : 0.f;
         };
-        float l_next = load_col(t0);
+        int rb = t0 / p.CT, ct = t0 - rb * p.CT;         // advanced incrementally: no division per tile
+        float l_next = load_col(ct, t0 < t1);
 
+        // dK of a finished row block leaves TMEM as plain vector stores into this CTA's slot of the
+        // partial buffer (the reduce kernel adds the slots); no float atomics on the hot path.
         auto drain = [&](int rb) {
+            tr(8);
             mbar_wait(dz_full, n_dz & 1);
+            tr(9);
             ++n_dz;
             tc_fence_after();
-            const int lrow = rb * kBM + h * kBMH + r;
+            const int slot = blockIdx.x - (rb * p.CT) / p.q;
+            // rows of this warp: q4*32 .. +32 of half h; after the transpose a store covers 128 contiguous bytes
+            float* dst_warp = p.dk_part + ((int64_t)slot * p.RB * kBM + (int64_t)rb * kBM + h * kBMH + q4 * 32) * p.ldk;
 #pragma unroll 1
             for (int cc = 0; cc < KCH; ++cc) {              // this warpgroup's half of the dK columns
                 const int c0 = a * (KCH * 32) + cc * 32;
                 uint32_t v[32];
                 tmem_ld32(tmem_base + lane_addr + 256 + h * 128 + c0, v);
                 tmem_ld_wait_dep(v);
-                if (lrow < p.n_rows) {
-                    float* dst = p.out_dk + (int64_t)lrow * p.ld_dk + c0;
+                warp_transpose32(v, lane);
+                float* dst = dst_warp + c0 + lane;
 #pragma unroll
-                    for (int c = 0; c < 32; c += 4)
-                        red_add_v4(dst + c, __uint_as_float(v[c]) * coef, __uint_as_float(v[c + 1]) * coef,
-                                   __uint_as_float(v[c + 2]) * coef, __uint_as_float(v[c + 3]) * coef);
-                }
+                for (int rr = 0; rr < 32; ++rr) dst[(int64_t)rr * p.ldk] = __uint_as_float(v[rr]);
             }
             tc_fence_before();
             mbar_arrive(dz_empty);
+            tr(10);
         };
 
         for (int tau = t0; tau < t1; ++tau) {
-            const int rb = tau / p.CT, ct = tau - rb * p.CT;
+            const int ct_next = (ct + 1 == p.CT) ? 0 : ct + 1;
             if (rb != cur_rb) {
                 if (cur_rb >= 0) drain(cur_rb);
                 cur_rb = rb;
@@ -627,82 +643,84 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 uint32_t va[32], vb[32];
                 tmem_ld32(tmem_base + lane_addr + w * 64, va);
                 tmem_ld32(tmem_base + lane_addr + w * 64 + 32, vb);
-                l_next = load_col(tau + 1);                 // global load flies during this sub-tile
+                l_next = load_col(ct_next, tau + 1 < t1);   // global load flies during this sub-tile
                 tmem_ld_wait_dep(va);
                 tmem_ld_wait_dep(vb);
                 tr(4);
-                mbar_wait(p_empty(h), (idx & 1) ^ 1);       // MMA2 of the previous tile has consumed P[h]
-                tr(5);
+                // 16 columns at a time: exp, weight, (label term), bf16 pack, 8 words back into TMEM
                 auto process = [&](uint32_t (&v)[32], int cc) {
 #pragma unroll
-                    for (int qq = 0; qq < 4; ++qq) {
-                        float pv[8];
-                        const float4 c0 = *reinterpret_cast<const float4*>(cj + cc * 32 + qq * 8);
-                        const float4 c1 = *reinterpret_cast<const float4*>(cj + cc * 32 + qq * 8 + 4);
-                        const float cvv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+                    for (int q2 = 0; q2 < 2; ++q2) {
+                        float pv[16];
 #pragma unroll
-                        for (int u = 0; u < 8; ++u) {
-                            const float e = ex2(fmaf(__uint_as_float(v[qq * 8 + u]), p.c2, -lse2_i));
-                            pv[u] = e * fmaf(R_i, cvv[u], 1.f);
+                        for (int q4c = 0; q4c < 4; ++q4c) {
+                            const float4 c4 = *reinterpret_cast<const float4*>(cj + cc * 32 + q2 * 16 + q4c * 4);
+                            const float cvv[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) {
+                                const float e = ex2(fmaf(__uint_as_float(v[q2 * 16 + q4c * 4 + u]), p.c2, -lse2_i));
+                                pv[q4c * 4 + u] = e * fmaf(R_i, cvv[u], 1.f);
+                            }
                         }
                         if (kLabels) {
-                            const int jj = j0 + cc * 32 + qq * 8;      // fast => whole sub-tile in range
-                            const int4 ra = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj));
-                            const int4 rb4 = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj + 4));
-                            const float4 na = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj));
-                            const float4 nb = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj + 4));
-                            if (ra.x == rep_i) pv[0] -= nia_i + na.x;
-                            if (ra.y == rep_i) pv[1] -= nia_i + na.y;
-                            if (ra.z == rep_i) pv[2] -= nia_i + na.z;
-                            if (ra.w == rep_i) pv[3] -= nia_i + na.w;
-                            if (rb4.x == rep_i) pv[4] -= nia_i + nb.x;
-                            if (rb4.y == rep_i) pv[5] -= nia_i + nb.y;
-                            if (rb4.z == rep_i) pv[6] -= nia_i + nb.z;
-                            if (rb4.w == rep_i) pv[7] -= nia_i + nb.w;
+                            const int jj = j0 + cc * 32 + q2 * 16;     // fast => whole sub-tile in range
+#pragma unroll
+                            for (int q4c = 0; q4c < 4; ++q4c) {
+                                const int4 ra = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj + q4c * 4));
+                                const float4 na = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj + q4c * 4));
+                                if (ra.x == rep_i) pv[q4c * 4 + 0] -= nia_i + na.x;
+                                if (ra.y == rep_i) pv[q4c * 4 + 1] -= nia_i + na.y;
+                                if (ra.z == rep_i) pv[q4c * 4 + 2] -= nia_i + na.z;
+                                if (ra.w == rep_i) pv[q4c * 4 + 3] -= nia_i + na.w;
+                            }
                         }
-                        store_p8(myp, cc * 4 + qq, r, pv);
+                        store_p16(p_taddr + cc * 16 + q2 * 8, pv);
                     }
                 };
                 process(va, 0);
                 process(vb, 1);
             } else {
                 // ---------------- rare case (self / ragged tiles, mode `one`, wild LSE ranges): two exps,
-                // eight columns at a time straight from TMEM, compact code
-                mbar_wait(p_empty(h), (idx & 1) ^ 1);
+                // sixteen columns at a time straight from TMEM, compact code
 #pragma unroll 1
-                for (int g8 = 0; g8 < 8; ++g8) {
-                    uint32_t v8[8];
-                    tmem_ld8(tmem_base + lane_addr + w * 64 + g8 * 8, v8);
-                    tmem_ld_wait_dep8(v8);
-                    float pv[8];
+                for (int g16 = 0; g16 < 4; ++g16) {
+                    uint32_t v8a[8], v8b[8];
+                    tmem_ld8(tmem_base + lane_addr + w * 64 + g16 * 16, v8a);
+                    tmem_ld8(tmem_base + lane_addr + w * 64 + g16 * 16 + 8, v8b);
+                    tmem_ld_wait_dep8(v8a);
+                    tmem_ld_wait_dep8(v8b);
+                    float pv[16];
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) {
-                        const int c = g8 * 8 + u;
+                    for (int u = 0; u < 16; ++u) {
+                        const int c = g16 * 16 + u;
                         const int j = j0 + c;
-                        const float x = __uint_as_float(v8[u]);
+                        const float x = __uint_as_float(u < 8 ? v8a[u & 7] : v8b[u & 7]);
                         float e = ex2(fmaf(x, p.c2, -lse2_i)) + ex2(fmaf(x, p.c2, -lj[c]));   // +inf -> 0
                         if (kLabels) {
                             if (j < p.n_k && p.rep_row[j] == rep_i) e -= nia_i + p.nia_row[j];
                         }
                         pv[u] = (j >= p.n_k || j == gi) ? 0.f : e;
                     }
-                    store_p8(myp, g8, r, pv);
+                    store_p16(p_taddr + g16 * 8, pv);      // words [8g, 8g+8) lie inside columns already read
                 }
-                l_next = load_col(tau + 1);
+                l_next = load_col(ct_next, tau + 1 < t1);
             }
             tr(6);
-            // publishing P[h] also hands S[h] back: every TMEM read of this thread is complete
+            // publishing P[h] also hands S[h] back: every TMEM access of this thread is complete
+            tmem_st_wait();
             tc_fence_before();
-            fence_proxy_async_smem();
             mbar_arrive(p_full(h));
             tr(7);
             ++idx;
+            if (ct_next == 0) ++rb;
+            ct = ct_next;
         }
         if (cur_rb >= 0) drain(cur_rb);
     }
 
     tc_fence_before();
     __syncthreads();
+    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[3071] = clock64();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
@@ -730,41 +748,47 @@ label_rows_kernel(const int64_t* __restrict__ labels, int n_samples, RowMap map,
     nia_row[j] = map.is_anchor(j, mode) ? 1.f / np : 0.f;
 }
 
-// ------------------------------------------------------------------ dK initialisation
-// out_dk starts as the linear positive-pair term of SimCLR
-//   -(coef/T) * sum_{j: same sample, j != i} ([anchor_i] + [anchor_j]) / (V-1) * k_j
-// (zero for label masks, whose positive term is applied inside the tiles); the tile kernel then
-// accumulates the softmax part with float reductions.
+// ------------------------------------------------------------------ dK reduction
+// out_dk[row] = (coef/T) * sum over the slots of the row block of the partial dK  (softmax part)
+//             - (coef/T) * sum_{j: same sample, j != i} ([anchor_i] + [anchor_j]) / (V-1) * k_j   (SimCLR positives,
+//               a closed form: the label masks apply their positive term inside the tiles instead)
+// One warp per row, a lane owns 4 consecutive features per 128-wide step.
 __global__ void __launch_bounds__(256)
-supcon_tc_init_dk_kernel(const __nv_bfloat16* __restrict__ k, int ldk, RowMap map, int n_views, int mode,
-                         int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
-                         float coef_scale_invT, float* __restrict__ out_dk, int ld_dk) {
+supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int flat_q, int flat_ct,
+                           const __nv_bfloat16* __restrict__ k, int ldk, RowMap map, int n_views, int mode,
+                           int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
+                           float coef_scale_invT, float* __restrict__ out_dk, int ld_dk) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= n_rows) return;
-    float* dst = out_dk + (int64_t)warp * ld_dk;
-    if (mask_kind != SCB_MASK_SIMCLR || n_views < 2) {
-        for (int d = lane * 4; d < ldk; d += 128) *reinterpret_cast<float4*>(dst + d) = make_float4(0.f, 0.f, 0.f, 0.f);
-        return;
-    }
+    const int rb = warp >> 8;
+    const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
+    const float coef = grad_out[0] * coef_scale_invT;
+    const bool simclr = (mask_kind == SCB_MASK_SIMCLR) && n_views >= 2;
     const int gi = row_begin + warp;
     const int base = (gi / map.vseg) * map.vseg, rem = gi - base;
     const int v = rem / map.seg, b = rem - v * map.seg;
     const float ai = map.is_anchor(gi, mode) ? 1.f : 0.f;
-    const float c = -grad_out[0] * coef_scale_invT / (float)(n_views - 1);
-    // a lane owns 4 consecutive features (8-byte bf16 loads, 16-byte fp32 stores); ldk % 64 == 0
+    const float cpos = -1.f / (float)(n_views > 1 ? n_views - 1 : 1);
+    float* dst = out_dk + (int64_t)warp * ld_dk;
     for (int d = lane * 4; d < ldk; d += 128) {
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int vv = 0; vv < n_views; ++vv) {
-            if (vv == v) continue;
-            const int j = base + vv * map.seg + b;
-            const float wgt = ai + (map.is_anchor(j, mode) ? 1.f : 0.f);
-            const uint2 raw = *reinterpret_cast<const uint2*>(k + (int64_t)j * ldk + d);
-            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
-            const float2 f0 = __bfloat1622float2(h2[0]), f1 = __bfloat1622float2(h2[1]);
-            acc[0] = fmaf(wgt, f0.x, acc[0]); acc[1] = fmaf(wgt, f0.y, acc[1]);
-            acc[2] = fmaf(wgt, f1.x, acc[2]); acc[3] = fmaf(wgt, f1.y, acc[3]);
+        for (int s = 0; s < n_slots; ++s) {
+            const float4 t = *reinterpret_cast<const float4*>(dk_part + ((int64_t)s * slot_rows + warp) * ldk + d);
+            acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
         }
-        *reinterpret_cast<float4*>(dst + d) = make_float4(c * acc[0], c * acc[1], c * acc[2], c * acc[3]);
+        if (simclr) {
+            for (int vv = 0; vv < n_views; ++vv) {
+                if (vv == v) continue;
+                const int j = base + vv * map.seg + b;
+                const float wgt = cpos * (ai + (map.is_anchor(j, mode) ? 1.f : 0.f));
+                const uint2 raw = *reinterpret_cast<const uint2*>(k + (int64_t)j * ldk + d);
+                const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
+                const float2 f0 = __bfloat1622float2(h2[0]), f1 = __bfloat1622float2(h2[1]);
+                acc[0] = fmaf(wgt, f0.x, acc[0]); acc[1] = fmaf(wgt, f0.y, acc[1]);
+                acc[2] = fmaf(wgt, f1.x, acc[2]); acc[3] = fmaf(wgt, f1.y, acc[3]);
+            }
+        }
+        *reinterpret_cast<float4*>(dst + d) = make_float4(coef * acc[0], coef * acc[1], coef * acc[2], coef * acc[3]);
     }
 }
 
@@ -823,9 +847,15 @@ static TcGeom tc_geom(int n_k, int rows) {
 
 static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
+static size_t dk_part_bytes(const scb_supcon_problem* p, int n_rows) {
+    const TcGeom g = tc_geom(p->n_k, n_rows);
+    return align256((size_t)(g.n_split / 2) * g.RB * kBM * p->ldk * sizeof(float));
+}
+
 int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows) {
     if (p->engine == SCB_ENGINE_FP32) return 0;
-    return (int64_t)(align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float)) + 3 * align256((size_t)p->n_k * 4));
+    return (int64_t)(align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float)) + 3 * align256((size_t)p->n_k * 4) +
+                     dk_part_bytes(p, n_rows));
 }
 
 static int tc_supported(const scb_supcon_problem* p) {
@@ -850,13 +880,15 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
     ws += align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float));
     t->rep_row = (const int*)ws; ws += align256((size_t)p->n_k * 4);
     t->npos_row = (const float*)ws; ws += align256((size_t)p->n_k * 4);
-    t->nia_row = (const float*)ws;
+    t->nia_row = (const float*)ws; ws += align256((size_t)p->n_k * 4);
+    t->dk_part = (float*)ws;
     t->lse_all = nullptr; t->grad_out = nullptr; t->coef_scale = 0.f; t->out_dk = nullptr; t->ld_dk = 0;
     t->trace = g_trace;
 }
 
 static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, cudaStream_t stream) {
     if (p->mask_kind != SCB_MASK_LABELS) return SCB_OK;
+    prefer_max_smem_carveout(label_rows_kernel);
     label_rows_kernel<<<(unsigned)ceil_div(p->n_k, 256), 256, 0, stream>>>(
         p->labels, p->n_seg * p->seg, t.map, p->n_k, p->n_views, p->mode, (int*)t.rep_row, (float*)t.npos_row,
         (float*)t.nia_row);
@@ -916,14 +948,8 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
     t.coef_scale = p->loss_scale / (float)n_anchor_total;
     t.out_dk = out_dk; t.ld_dk = ld_dk;
     if (int e = launch_label_rows(p, t, stream)) return e;
-    supcon_tc_init_dk_kernel<<<(unsigned)ceil_div((int64_t)n_rows * 32, 256), 256, 0, stream>>>(
-        t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows, grad_out,
-        t.coef_scale * p->inv_temperature, out_dk, ld_dk);
-    SCB_CUDA_OK(cudaGetLastError());
-    count_launch();
     const int kch = p->ldk / 64;
-    const size_t smem = (size_t)(2 * kch * kSub) + 3 * (kch * kSub) + 4 * kSub + 4 * 2 * 64 * 4 + 64 + 128 +
-                        28 * 8 + 16;
+    const size_t smem = (size_t)(2 * kch * kSub) + 4 * (kch * kSub) + 4 * 2 * 64 * 4 + 64 + 128 + 28 * 8 + 16;
     const bool lab = p->mask_kind == SCB_MASK_LABELS;
 #define SCB_LAUNCH_BWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
@@ -933,6 +959,12 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
     if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
     else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
 #undef SCB_LAUNCH_BWD
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    prefer_max_smem_carveout(supcon_tc_reduce_dk_kernel);
+    supcon_tc_reduce_dk_kernel<<<(unsigned)ceil_div((int64_t)n_rows * 32, 256), 256, 0, stream>>>(
+        t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows,
+        grad_out, t.coef_scale * p->inv_temperature, out_dk, ld_dk);
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     return SCB_OK;

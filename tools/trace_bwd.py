@@ -31,7 +31,10 @@ torch.cuda.synchronize()
 lib.scb_debug_set_trace(None)
 t = trace.cpu().view(3, 512, 2)
 t0 = min(int(t[r, 0, 1]) for r in range(3) if int(t[r, 511, 0]) > 0)
-names = {1: 'tile start', 2: 'cols staged', 3: 'S ready', 4: 'S in regs', 5: 'P free', 6: 'P written', 7: 'P published'}
+tc = trace.cpu()
+ends = [tc[1023], tc[2047], tc[3071]]
+print('kernel entry %d, setup done %d, exit %d (relative to first event)' % tuple(int(e) - t0 for e in ends))
+names = {8: 'drain wait', 9: 'dK complete', 10: 'dK stored', 1: 'tile start', 2: 'cols staged', 3: 'S ready', 4: 'S in regs', 5: 'P free', 6: 'P written', 7: 'P published'}
 for role, label in ((0, 'MMA issuer'), (1, 'epilogue WG0'), (2, 'epilogue WG1')):
     n = int(t[role, 511, 0])
     print('==', label, n, 'events')
