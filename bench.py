@@ -294,24 +294,31 @@ def bn_kernel_breakdown(steps, pool=8):
     saved = torch.empty(2 * C + 1, device=dev)
     out = torch.empty(4 * C, device=dev)
     _, geom = _layout(xs[0])
-    names = ['stats', 'apply', 'backward_reduce', 'backward_apply']
-    tot = [0.0] * 4
+    fused = K.fused_supported(xs[0], geom)
+    names = ['forward_fused', 'backward_fused'] if fused else ['stats', 'apply', 'backward_reduce', 'backward_apply']
+    tot = [0.0] * len(names)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
     for it in range(steps + 3):
         x, dy, y, dx = xs[it % pool], dys[it % pool], ys[it % pool], dxs[it % pool]
         torch.cuda._sleep(400000)      # let the host run ahead so the events see back-to-back kernels
         ev[0].record()
-        K.stats(x, geom, st)
-        ev[1].record()
-        K.apply(x, y, geom, st, 1, w, b, rm, rv, 0.1, 1e-5, saved, 0)
-        ev[2].record()
-        K.backward_reduce(dy, x, geom, saved, w, b, out[:2 * C], out[2 * C:3 * C], out[3 * C:], 0)
-        ev[3].record()
-        K.backward_apply(dy, x, dx, geom, saved, w, b, out[:2 * C], 0)
-        ev[4].record()
+        if fused:
+            K.forward_fused(x, y, geom, w, b, rm, rv, 0.1, 1e-5, saved, 0)
+            ev[1].record()
+            K.backward_fused(dy, x, dx, geom, saved, w, b, out[:2 * C], out[2 * C:3 * C], out[3 * C:], 0)
+            ev[2].record()
+        else:
+            K.stats(x, geom, st)
+            ev[1].record()
+            K.apply(x, y, geom, st, 1, w, b, rm, rv, 0.1, 1e-5, saved, 0)
+            ev[2].record()
+            K.backward_reduce(dy, x, geom, saved, w, b, out[:2 * C], out[2 * C:3 * C], out[3 * C:], 0)
+            ev[3].record()
+            K.backward_apply(dy, x, dx, geom, saved, w, b, out[:2 * C], 0)
+            ev[4].record()
         torch.cuda.synchronize()
         if it >= 3:
-            for j in range(4):
+            for j in range(len(names)):
                 tot[j] += ev[j].elapsed_time(ev[j + 1])
     return {n: t / steps * 1e3 for n, t in zip(names, tot)}
 
@@ -506,12 +513,14 @@ def main():
             tot_us = sum(kb.values())
             ach = 8.0 * S / (tot_us * 1e-6) / 1e9
             dom = max(kb, key=kb.get)
-            passes = {'stats': 1, 'apply': 2, 'backward_reduce': 2, 'backward_apply': 3}
+            # algorithmic passes over the tensor each launch stands for (fwd 3S, bwd 5S)
+            passes = {'stats': 1, 'apply': 2, 'backward_reduce': 2, 'backward_apply': 3,
+                      'forward_fused': 3, 'backward_fused': 5}
             ach_dom = passes[dom] * S / (kb[dom] * 1e-6) / 1e9
             sb['roofline'] = {'bound': 'hbm', 'achieved': ach_dom, 'peak': pk['hbm'], 'unit': 'GB/s',
                               'frac': ach_dom / pk['hbm'], 'traffic': None, 'kernel': 'bn_' + dom,
                               'peak_source': pk['src'], 'algorithmic_bytes_per_launch': passes[dom] * S,
-                              'four_kernels_sum': {'achieved': ach, 'frac': ach / pk['hbm'], 'us': tot_us},
+                              'all_kernels_sum': {'achieved': ach, 'frac': ach / pk['hbm'], 'us': tot_us},
                               'kernel_us': kb}
         if 'metric' in out:
             out['syncbn'] = sb

@@ -206,6 +206,23 @@ int scb_bn_backward_apply(const void* dy, const void* x, void* dx, int dtype, in
                           const float* weight, const float* bias,
                           const float* sums, const float* n_total, int flags, void* stream);
 
+/* Single-launch variants for ONE rank (no exchange between statistics and normalisation): the same
+ * arithmetic as scb_bn_stats + scb_bn_apply, resp. scb_bn_backward_reduce + scb_bn_backward_apply
+ * (torch/nn/modules/_functions.py:39-122 and :139-179 at world size 1, i.e. the F.batch_norm fallback of
+ * torch/nn/modules/batchnorm.py:818-828), with x (and dy) kept in registers across a grid-wide barrier
+ * of a cooperative launch.  Channels-last [rows, channels] only, and only when the tensor fits one
+ * resident wave: scb_bn_fused_supported() says so beforehand, otherwise they return SCB_ERR_UNSUPPORTED
+ * and the caller runs the two-kernel path. */
+int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner);
+int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t rows, int channels,
+                         const float* weight, const float* bias, float* running_mean, float* running_var,
+                         float momentum, float eps, float* save_mean, float* save_invstd, float* save_count,
+                         int flags, void* workspace, int64_t workspace_bytes, void* stream);
+int scb_bn_backward_fused(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
+                          const float* mean, const float* invstd, const float* weight, const float* bias,
+                          const float* n_total, float* out_sums, float* grad_weight, float* grad_bias, int flags,
+                          void* workspace, int64_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

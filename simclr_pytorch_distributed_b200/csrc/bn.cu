@@ -813,3 +813,325 @@ extern "C" int scb_bn_stats_noalloc(const void* x, int dtype, int channels_last,
     SCB_CUDA_OK(cudaMemsetAsync(scratch, 0, (size_t)need, stream));
     return scb_bn_stats(x, dtype, channels_last, outer, channels, inner, out_stats, scratch, need, stream_);
 }
+
+// ================================================================== single-launch passes (one rank)
+// When the whole activation fits in the registers of one resident wave (BASELINE cfg 2: 8 MiB over
+// 148 SMs), statistics and normalisation run in ONE cooperative launch: every thread keeps its rows
+// (raw 16-byte vectors) in registers across a grid-wide barrier, so x is read once and the second
+// kernel launch disappears (forward 3S -> 2S of traffic, backward 5S -> 3S).  Only used at world
+// size 1 -- with more ranks the statistics have to cross the NCCL exchange between the two halves --
+// and only for channels-last tensors with a vectorisable channel count; otherwise the two-kernel
+// path above runs.
+namespace scb {
+
+constexpr int kFusedRows = 4;      // rows a thread keeps in registers
+
+// grid-wide barrier for a cooperative launch (all CTAs are co-resident): arrive, then spin
+__device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned total) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        while (*reinterpret_cast<volatile unsigned*>(counter) < total) { }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads, 4)
+bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, int TX, int64_t rows_per_cta,
+                         float* __restrict__ acc, unsigned* counters,
+                         const float* __restrict__ weight, const float* __restrict__ bias,
+                         float* running_mean, float* running_var, float momentum, float eps,
+                         float* save_mean, float* save_invstd, float* save_count, int flags) {
+    extern __shared__ float sm[];
+    const int TY = kBnThreads / TX;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = (blockIdx.x * TX + tx) * VEC;
+    const bool active = c0 < C;
+    const unsigned total = gridDim.x * gridDim.y;
+    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta + ty;
+    const int64_t step = (int64_t)TY * C;
+    uint4 raw[kFusedRows];
+    float s1[VEC], s2[VEC], k0[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; k0[i] = 0.f; }
+    int nrow = 0;
+    if (active) {
+        load_row_vec<T, VEC>(x + c0, k0);
+        const T* p = x + r0 * C + c0;
+#pragma unroll
+        for (int u = 0; u < kFusedRows; ++u)
+            if (r0 + (int64_t)u * TY < r_end) { raw[u] = ldg_stream16(p + u * step); nrow = u + 1; }
+#pragma unroll
+        for (int u = 0; u < kFusedRows; ++u) {
+            if (u < nrow) {
+                const T* e = reinterpret_cast<const T*>(&raw[u]);
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float d = to_f32(e[i]) - k0[i];
+                    s1[i] += d;
+                    s2[i] = fmaf(d, d, s2[i]);
+                }
+            }
+        }
+    }
+    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
+    grid_barrier(counters, total);
+    // every CTA derives the coefficients of its channels from the completed sums
+    const float n = (float)M;
+    float a[VEC], b[VEC];
+    if (active) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            const int c = c0 + i;
+            const float sa = __ldcg(acc + c), sb = __ldcg(acc + C + c);
+            const float mean = k0[i] + sa / n;
+            const float m2 = fmaxf(sb - sa * sa / n, 0.f);
+            const float invstd = rsqrtf(m2 / n + eps);
+            a[i] = (weight ? weight[c] : 1.f) * invstd;
+            b[i] = (bias ? bias[c] : 0.f) - mean * a[i];
+            if (blockIdx.y == 0 && ty == 0) {
+                if (save_mean) save_mean[c] = mean;
+                if (save_invstd) save_invstd[c] = invstd;
+                if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+                if (c == 0 && save_count) save_count[0] = n;
+            }
+        }
+    }
+    // second ticket: once every CTA has read the sums, the last one re-arms the scratch
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(counters + 1, 1u) == total - 1) {
+            for (int c = 0; c < 2 * C; ++c) acc[c] = 0.f;
+            counters[0] = 0u;
+            counters[1] = 0u;
+        }
+    }
+    if (!active) return;
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    T* q = y + r0 * C + c0;
+#pragma unroll
+    for (int u = 0; u < kFusedRows; ++u) {
+        if (u < nrow) {
+            const T* e = reinterpret_cast<const T*>(&raw[u]);
+            uint4 o;
+            T* oe = reinterpret_cast<T*>(&o);
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                float v = fmaf(to_f32(e[i]), a[i], b[i]);
+                oe[i] = from_f32<T>(relu ? fmaxf(v, 0.f) : v);
+            }
+            stg_stream16(q + u * step, o);
+        }
+    }
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kBnThreads, 4)
+bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t M, int C, int TX,
+                         int64_t rows_per_cta, float* __restrict__ acc, unsigned* counters,
+                         const float* __restrict__ mean, const float* __restrict__ invstd,
+                         const float* __restrict__ weight, const float* __restrict__ bias,
+                         const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias,
+                         int flags) {
+    extern __shared__ float sm[];
+    const int TY = kBnThreads / TX;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = (blockIdx.x * TX + tx) * VEC;
+    const bool active = c0 < C;
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    const unsigned total = gridDim.x * gridDim.y;
+    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta + ty;
+    const int64_t step = (int64_t)TY * C;
+    uint4 rx[kFusedRows], rd[kFusedRows];
+    unsigned gated[kFusedRows];            // ReLU: bit i set = element i of the row had y <= 0 (dy is dropped)
+    float s1[VEC], s2[VEC], mu[VEC], k1[VEC], bb[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; mu[i] = 0.f; k1[i] = 0.f; bb[i] = 0.f; }
+    int nrow = 0;
+    if (active) {
+        const T* px = x + r0 * C + c0;
+        const T* pd = dy + r0 * C + c0;
+#pragma unroll
+        for (int u = 0; u < kFusedRows; ++u)
+            if (r0 + (int64_t)u * TY < r_end) {
+                rx[u] = ldg_stream16(px + u * step);
+                rd[u] = ldg_stream16(pd + u * step);
+                nrow = u + 1;
+            }
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            mu[i] = mean[c0 + i];
+            k1[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
+            bb[i] = bias ? bias[c0 + i] : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < kFusedRows; ++u) {
+            gated[u] = 0u;
+            if (u < nrow) {
+                const T* ex = reinterpret_cast<const T*>(&rx[u]);
+                const T* ed = reinterpret_cast<const T*>(&rd[u]);
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float xm = to_f32(ex[i]) - mu[i];
+                    float g = to_f32(ed[i]);
+                    if (relu && !(fmaf(xm, k1[i], bb[i]) > 0.f)) { g = 0.f; gated[u] |= 1u << i; }
+                    s1[i] += g;
+                    s2[i] = fmaf(g, xm, s2[i]);
+                }
+            }
+        }
+    }
+    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
+    grid_barrier(counters, total);
+    const float inv_n = 1.f / n_total[0];
+    float k2[VEC], k3[VEC];
+    if (active) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            const int c = c0 + i;
+            const float sd = __ldcg(acc + c), sx = __ldcg(acc + C + c);
+            const float is = invstd[c];
+            k2[i] = sd * inv_n;
+            k3[i] = is * is * sx * inv_n;
+            if (blockIdx.y == 0 && ty == 0) {
+                if (out_sums) { out_sums[c] = sd; out_sums[C + c] = sx; }
+                if (grad_weight) grad_weight[c] = sx * is;
+                if (grad_bias) grad_bias[c] = sd;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(counters + 1, 1u) == total - 1) {
+            for (int c = 0; c < 2 * C; ++c) acc[c] = 0.f;
+            counters[0] = 0u;
+            counters[1] = 0u;
+        }
+    }
+    if (!active) return;
+    T* po = dx + r0 * C + c0;
+#pragma unroll
+    for (int u = 0; u < kFusedRows; ++u) {
+        if (u < nrow) {
+            const T* ex = reinterpret_cast<const T*>(&rx[u]);
+            const T* ed = reinterpret_cast<const T*>(&rd[u]);
+            uint4 o;
+            T* oe = reinterpret_cast<T*>(&o);
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                const float xm = to_f32(ex[i]) - mu[i];
+                const float g = ((gated[u] >> i) & 1u) ? 0.f : to_f32(ed[i]);
+                oe[i] = from_f32<T>((g - k2[i] - xm * k3[i]) * k1[i]);
+            }
+            stg_stream16(po + u * step, o);
+        }
+    }
+}
+
+// geometry of the fused pass: one resident wave, <= kFusedRows rows per thread; false if it does not fit
+static bool fused_geom(int64_t M, int C, int elem_size, bool al16, NhwcGeom* g, int ctas_per_sm) {
+    const int vmax = 16 / elem_size;
+    if (!al16 || C % vmax != 0 || M < 2) return false;
+    *g = nhwc_geom(M, C, elem_size, true, ctas_per_sm * sm_count());
+    if (g->rows_per_cta > (int64_t)g->ty * kFusedRows) return false;           // would need more registers
+    if ((int64_t)g->grid_x * g->grid_y > (int64_t)ctas_per_sm * sm_count()) return false;   // not one wave
+    return true;
+}
+
+template <typename Kern>
+static int fused_ctas_per_sm(Kern kern, size_t smem) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kBnThreads, smem) != cudaSuccess) return 0;
+    return n;
+}
+
+}  // namespace scb
+
+extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner) {
+    if (!channels_last || channels <= 0) return 0;
+    const int es = (dtype == SCB_F32) ? 4 : 2;
+    NhwcGeom g;
+    return fused_geom(outer * inner, channels, es, true, &g, 4) ? 1 : 0;
+}
+
+extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t rows, int channels,
+                                    const float* weight, const float* bias, float* running_mean,
+                                    float* running_var, float momentum, float eps, float* save_mean,
+                                    float* save_invstd, float* save_count, int flags, void* workspace,
+                                    int64_t workspace_bytes, void* stream_) {
+    if (int e = check_bn_common(x, dtype, rows, channels, 1)) return e;
+    SCB_REQUIRE(y && workspace && workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_forward_fused: bad buffers");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int64_t M = rows;
+    int C = channels;
+    float* acc = (float*)workspace;
+    unsigned* counters = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
+    int rc = SCB_ERR_UNSUPPORTED;
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        constexpr int VEC = Vec16<T>::N;
+        NhwcGeom g;
+        auto kern = bn_fwd_fused_nhwc_kernel<T, VEC>;
+        const size_t smem = 2 * kBnThreads * VEC * sizeof(float);
+        const int per_sm = fused_ctas_per_sm(kern, smem);
+        if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(y), &g, per_sm < 4 ? per_sm : 4)) {
+            dim3 grid(g.grid_x, (unsigned)g.grid_y);
+            int TX = g.tx;
+            int64_t rpc = g.rows_per_cta;
+            const T* xp = (const T*)x;
+            T* yp = (T*)y;
+            void* args[] = {&xp, &yp, &M, &C, &TX, &rpc, &acc, &counters, &weight, &bias, &running_mean, &running_var,
+                            &momentum, &eps, &save_mean, &save_invstd, &save_count, &flags};
+            SCB_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(kBnThreads), args, smem, stream));
+            rc = SCB_OK;
+        }
+    });
+    if (rc == SCB_ERR_UNSUPPORTED) { set_error("bn_forward_fused: tensor does not fit one resident wave"); return rc; }
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_bn_backward_fused(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
+                                     const float* mean, const float* invstd, const float* weight, const float* bias,
+                                     const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
+                                     int flags, void* workspace, int64_t workspace_bytes, void* stream_) {
+    if (int e = check_bn_common(x, dtype, rows, channels, 1)) return e;
+    SCB_REQUIRE(dy && dx && mean && invstd && n_total && workspace &&
+                workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_backward_fused: bad buffers");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int64_t M = rows;
+    int C = channels;
+    float* acc = (float*)workspace;
+    unsigned* counters = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
+    int rc = SCB_ERR_UNSUPPORTED;
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        constexpr int VEC = Vec16<T>::N;
+        NhwcGeom g;
+        auto kern = bn_bwd_fused_nhwc_kernel<T, VEC>;
+        const size_t smem = 2 * kBnThreads * VEC * sizeof(float);
+        const int per_sm = fused_ctas_per_sm(kern, smem);
+        if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(dy) && aligned16(dx), &g,
+                                      per_sm < 4 ? per_sm : 4)) {
+            dim3 grid(g.grid_x, (unsigned)g.grid_y);
+            int TX = g.tx;
+            int64_t rpc = g.rows_per_cta;
+            const T* dyp = (const T*)dy;
+            const T* xp = (const T*)x;
+            T* dxp = (T*)dx;
+            void* args[] = {&dyp, &xp, &dxp, &M, &C, &TX, &rpc, &acc, &counters, &mean, &invstd, &weight, &bias,
+                            &n_total, &out_sums, &grad_weight, &grad_bias, &flags};
+            SCB_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(kBnThreads), args, smem, stream));
+            rc = SCB_OK;
+        }
+    });
+    if (rc == SCB_ERR_UNSUPPORTED) { set_error("bn_backward_fused: tensor does not fit one resident wave"); return rc; }
+    count_launch();
+    return SCB_OK;
+}

@@ -76,6 +76,36 @@ class _Kernels:
             'scb_bn_backward_reduce')
 
     @classmethod
+    def fused_supported(cls, x, geom):
+        """True when statistics + normalisation of this tensor fit the single-launch kernels."""
+        lib = _lib.load()
+        cl, outer, C, inner = geom
+        return bool(lib.scb_bn_fused_supported(_lib.dtype_code(x.dtype), cl, outer, C, inner))
+
+    @classmethod
+    def forward_fused(cls, x, y, geom, weight, bias, running_mean, running_var, momentum, eps, saved, flags):
+        lib = _lib.load()
+        cl, outer, C, inner = geom
+        p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        ws = cls.workspace(lib, x.device, C)
+        return lib.scb_bn_forward_fused(x.data_ptr(), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
+                                        p(weight), p(bias), p(running_mean), p(running_var), momentum, eps,
+                                        saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), saved[2 * C:].data_ptr(),
+                                        flags, ws.data_ptr(), ws.numel(), cls.stream(x.device))
+
+    @classmethod
+    def backward_fused(cls, dy, x, dx, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags):
+        lib = _lib.load()
+        cl, outer, C, inner = geom
+        p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        ws = cls.workspace(lib, x.device, C)
+        return lib.scb_bn_backward_fused(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _lib.dtype_code(x.dtype),
+                                         outer * inner, C, saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(),
+                                         p(weight), p(bias), saved[2 * C:].data_ptr(), sums.data_ptr(),
+                                         p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(),
+                                         cls.stream(x.device))
+
+    @classmethod
     def backward_apply(cls, dy, x, dx, geom, saved, weight, bias, sums, flags):
         lib = _lib.load()
         cl, outer, C, inner = geom
@@ -135,6 +165,27 @@ class _SyncBNFunction(torch.autograd.Function):
         w32, b32 = _f32(weight), _f32(bias)
         rm, rv = _f32(running_mean), _f32(running_var)
         dev = x.device
+        flags = _lib.BN_RELU if fuse_relu else 0
+        fused = (use_batch_stats and world_size == 1 and hasattr(kern, 'fused_supported')
+                 and kern.fused_supported(x, geom))
+        ctx.fused = False
+        if fused:
+            # one rank, tensor fits one resident wave: statistics + normalisation in a single launch
+            y = torch.empty_like(x)
+            saved = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
+            rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags)
+            if rc == 0:
+                if rm is not running_mean and running_mean is not None:
+                    running_mean.copy_(rm)
+                if rv is not running_var and running_var is not None:
+                    running_var.copy_(rv)
+                ctx.save_for_backward(x, w32, b32, saved)
+                ctx.geom, ctx.flags, ctx.use_batch_stats, ctx.fused = geom, flags, use_batch_stats, True
+                ctx.process_group, ctx.world_size = process_group, world_size
+                ctx.param_dtypes = (None if weight is None else weight.dtype, None if bias is None else bias.dtype)
+                return y
+            if rc != -3:
+                _lib.check(rc, 'scb_bn_forward_fused')
         if not use_batch_stats:
             stats_all = None            # eval: the running statistics are the statistics
         else:
@@ -179,9 +230,18 @@ class _SyncBNFunction(torch.autograd.Function):
         dev = x.device
         out = torch.empty(4 * C, dtype=torch.float32, device=dev)           # sums(2C), dgamma, dbeta
         sums, gw, gb = out[0:2 * C], out[2 * C:3 * C], out[3 * C:]
-        kern.backward_reduce(dy, x, geom, saved, w32, b32, sums, gw, gb, flags)
         grad_input = None
-        if ctx.needs_input_grad[0]:
+        done = False
+        if ctx.fused and ctx.needs_input_grad[0]:
+            grad_input = torch.empty_like(x)
+            rc = kern.backward_fused(dy, x, grad_input, geom, saved, w32, b32, sums, gw, gb, flags)
+            if rc == 0:
+                done = True
+            elif rc != -3:
+                _lib.check(rc, 'scb_bn_backward_fused')
+        if not done:
+            kern.backward_reduce(dy, x, geom, saved, w32, b32, sums, gw, gb, flags)
+        if not done and ctx.needs_input_grad[0]:
             if not ctx.use_batch_stats:
                 sums = torch.zeros_like(sums)               # eval: statistics do not depend on x
             elif ctx.world_size > 1:                        # _functions.py:155-165
