@@ -29,13 +29,14 @@ struct NhwcGeom {
 
 static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
-static NhwcGeom nhwc_geom(int64_t M, int C, int elem_size, bool aligned16, int target_ctas) {
+static NhwcGeom nhwc_geom(int64_t M, int C, int elem_size, bool aligned16, int target_ctas,
+                          int threads = kBnThreads) {
     NhwcGeom g;
     int vmax = 16 / elem_size;
     g.vec = (aligned16 && C % vmax == 0) ? vmax : 1;
     int cv = C / g.vec;
     g.tx = next_pow2(cv) < 32 ? next_pow2(cv) : 32;
-    g.ty = kBnThreads / g.tx;
+    g.ty = threads / g.tx;
     g.grid_x = (int)ceil_div(cv, g.tx);
     int64_t want_y = target_ctas / g.grid_x; if (want_y < 1) want_y = 1;
     int64_t chunk = (int64_t)g.ty * kUnroll;
@@ -46,9 +47,18 @@ static NhwcGeom nhwc_geom(int64_t M, int C, int elem_size, bool aligned16, int t
     return g;
 }
 
-// scratch layout: [0, 2C) float accumulators, then one unsigned ticket counter (at a 16-byte
-// aligned offset).  Zero on entry, zero again on exit.
-__host__ __device__ inline int64_t bn_ws_counter_offset(int C) { return ((int64_t)2 * C * 4 + 15) / 16 * 16; }
+// Cross-CTA sums go through float atomics in L2, and hundreds of CTAs adding into the same few cache
+// lines serialise there (~27 cycles per 128-byte warp-op per line).  The accumulators are therefore
+// replicated R times (CTA y uses replica y % R) and the R copies are added by whoever finalises.
+__host__ __device__ inline int bn_replicas(int C) {
+    (void)C;
+    return 1;       // measured on B200: replication does not pay (the latency chain per CTA dominates)
+}
+// scratch layout: [R][2C] float accumulators, then two unsigned tickets (at a 16-byte aligned
+// offset).  Zero on entry, zero again on exit.
+__host__ __device__ inline int64_t bn_ws_counter_offset(int C) {
+    return ((int64_t)bn_replicas(C) * 2 * C * 4 + 15) / 16 * 16;
+}
 
 // Block-level: sum `v[VEC]` over the ty rows of the CTA and atomically add into acc[c].
 template <int VEC>
@@ -59,13 +69,21 @@ __device__ __forceinline__ void cta_reduce_to_global(float (&a)[VEC], float (&b)
     const int W = TX * VEC;
     float* sa = sm;
     float* sb = sm + TY * W;
+    if constexpr (VEC % 4 == 0) {      // 16-byte shared stores: scalar ones would be 8-way bank conflicted
 #pragma unroll
-    for (int i = 0; i < VEC; ++i) {
-        sa[ty * W + tx * VEC + i] = a[i];
-        sb[ty * W + tx * VEC + i] = b[i];
+        for (int i = 0; i < VEC; i += 4) {
+            *reinterpret_cast<float4*>(sa + ty * W + tx * VEC + i) = make_float4(a[i], a[i + 1], a[i + 2], a[i + 3]);
+            *reinterpret_cast<float4*>(sb + ty * W + tx * VEC + i) = make_float4(b[i], b[i + 1], b[i + 2], b[i + 3]);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            sa[ty * W + tx * VEC + i] = a[i];
+            sb[ty * W + tx * VEC + i] = b[i];
+        }
     }
     __syncthreads();
-    for (int t = threadIdx.x; t < 2 * W; t += kBnThreads) {
+    for (int t = threadIdx.x; t < 2 * W; t += blockDim.x) {
         const int which = t / W, col = t - which * W;
         const float* s = which ? sb : sa;
         float tot = 0.f;
@@ -110,7 +128,7 @@ bn_stats_nhwc_kernel(const T* __restrict__ x, int64_t M, int C, int TX, int64_t 
         // stream); the common reference K_c = x[0, c] is fetched alongside and only used at the
         // end to re-centre the two sums so that they add across threads and CTAs.
         float k0[VEC];
-        load_row_vec<T, VEC>(x + c0, k0);
+        load_row_vec_cached<T, VEC>(x + c0, k0);
         const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
         int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
         const int64_t r_first = r;
@@ -149,16 +167,22 @@ bn_stats_nhwc_kernel(const T* __restrict__ x, int64_t M, int C, int TX, int64_t 
             s1[i] = fmaf(nt, d, s1[i]);
         }
     }
-    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
+    const int R = bn_replicas(C);
+    float* my_acc = acc + (size_t)(blockIdx.y % R) * 2 * C;
+    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, my_acc, my_acc + C);
     if (last_cta_done(counter, gridDim.x * gridDim.y)) {
         const float n = (float)M;
         for (int c = threadIdx.x; c < C; c += kBnThreads) {
-            const float a = __ldcg(acc + c), b = __ldcg(acc + C + c);
+            float a = 0.f, b = 0.f;
+            for (int rr = 0; rr < R; ++rr) {
+                a += __ldcg(acc + (size_t)rr * 2 * C + c);
+                b += __ldcg(acc + (size_t)rr * 2 * C + C + c);
+                acc[(size_t)rr * 2 * C + c] = 0.f;
+                acc[(size_t)rr * 2 * C + C + c] = 0.f;
+            }
             const float k = to_f32(x[c]);
             out_stats[c] = k + a / n;
             out_stats[C + c] = fmaxf(b - a * a / n, 0.f);
-            acc[c] = 0.f;
-            acc[C + c] = 0.f;
         }
         if (threadIdx.x == 0) { out_stats[2 * C] = n; *counter = 0u; }
     }
@@ -339,16 +363,22 @@ bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, int
             }
         }
     }
-    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
+    const int R = bn_replicas(C);
+    float* my_acc = acc + (size_t)(blockIdx.y % R) * 2 * C;
+    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, my_acc, my_acc + C);
     if (last_cta_done(counter, gridDim.x * gridDim.y)) {
         for (int c = threadIdx.x; c < C; c += kBnThreads) {
-            const float sd = __ldcg(acc + c), sx = __ldcg(acc + C + c);
+            float sd = 0.f, sx = 0.f;
+            for (int rr = 0; rr < R; ++rr) {
+                sd += __ldcg(acc + (size_t)rr * 2 * C + c);
+                sx += __ldcg(acc + (size_t)rr * 2 * C + C + c);
+                acc[(size_t)rr * 2 * C + c] = 0.f;
+                acc[(size_t)rr * 2 * C + C + c] = 0.f;
+            }
             out_sums[c] = sd;
             out_sums[C + c] = sx;
             if (grad_weight) grad_weight[c] = sx * invstd[c];
             if (grad_bias) grad_bias[c] = sd;
-            acc[c] = 0.f;
-            acc[C + c] = 0.f;
         }
         if (threadIdx.x == 0) *counter = 0u;
     }
@@ -778,7 +808,7 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, void* dx, in
 // host-side stand-in only: the device address is looked up once per device with
 // cudaGetSymbolAddress while that device is current, and that address is what the kernel receives.
 constexpr int kNoAllocMaxChannels = SCB_BN_NOALLOC_MAX_CHANNELS;
-constexpr size_t kNoAllocScratchBytes = (size_t)2 * kNoAllocMaxChannels * sizeof(float) + 256;
+constexpr size_t kNoAllocScratchBytes = (size_t)2 * kNoAllocMaxChannels * sizeof(float) + 256;   // >= scb_bn_workspace_bytes(c) for c <= max
 static __device__ __align__(256) unsigned char g_bn_noalloc_scratch[kNoAllocScratchBytes];
 
 #include <mutex>
@@ -825,6 +855,7 @@ extern "C" int scb_bn_stats_noalloc(const void* x, int dtype, int channels_last,
 namespace scb {
 
 constexpr int kFusedRows = 4;      // rows a thread keeps in registers
+constexpr int kFusedThreads = 1024; // one fat CTA per SM: a single load/reduce/barrier latency chain per SM
 
 // grid-wide barrier for a cooperative launch (all CTAs are co-resident): arrive, then spin
 __device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned total) {
@@ -838,15 +869,31 @@ __device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned total) 
     __syncthreads();
 }
 
+// After the grid barrier every CTA reads the sums; the last one to have done so (second ticket) zeroes
+// the accumulators and both tickets so the scratch is ready for the next launch.
+__device__ __forceinline__ void rearm_scratch(float* acc, unsigned* counters, unsigned total, int n_acc) {
+    __shared__ unsigned s_last2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last2 = (atomicAdd(counters + 1, 1u) == total - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_last2) {
+        for (int c = threadIdx.x; c < n_acc; c += blockDim.x) acc[c] = 0.f;
+        if (threadIdx.x == 0) { counters[0] = 0u; counters[1] = 0u; }
+    }
+}
+
 template <typename T, int VEC>
-__global__ void __launch_bounds__(kBnThreads, 4)
+__global__ void __launch_bounds__(kFusedThreads, 1)
 bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, int TX, int64_t rows_per_cta,
                          float* __restrict__ acc, unsigned* counters,
                          const float* __restrict__ weight, const float* __restrict__ bias,
                          float* running_mean, float* running_var, float momentum, float eps,
                          float* save_mean, float* save_invstd, float* save_count, int flags) {
     extern __shared__ float sm[];
-    const int TY = kBnThreads / TX;
+    const int TY = kFusedThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = (blockIdx.x * TX + tx) * VEC;
     const bool active = c0 < C;
@@ -860,7 +907,7 @@ bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, 
     for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; k0[i] = 0.f; }
     int nrow = 0;
     if (active) {
-        load_row_vec<T, VEC>(x + c0, k0);
+        load_row_vec_cached<T, VEC>(x + c0, k0);
         const T* p = x + r0 * C + c0;
 #pragma unroll
         for (int u = 0; u < kFusedRows; ++u)
@@ -878,22 +925,34 @@ bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, 
             }
         }
     }
-    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
+    const int R = bn_replicas(C);
+    {
+        float* my_acc = acc + (size_t)(blockIdx.y % R) * 2 * C;
+        cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, my_acc, my_acc + C);
+    }
     grid_barrier(counters, total);
-    // every CTA derives the coefficients of its channels from the completed sums
+    // One thread per channel of the CTA's tile fetches the completed sums (a single pass over a few
+    // cache lines per CTA -- letting every thread read them turns those lines into an L2 hot spot)
+    // and leaves the per-channel scale / offset in shared memory.
     const float n = (float)M;
-    float a[VEC], b[VEC];
-    if (active) {
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) {
-            const int c = c0 + i;
-            const float sa = __ldcg(acc + c), sb = __ldcg(acc + C + c);
-            const float mean = k0[i] + sa / n;
+    const int W = TX * VEC;
+    const int tile_c0 = blockIdx.x * W;
+    __syncthreads();                       // the reduction is done with sm[]
+    for (int t = threadIdx.x; t < W; t += blockDim.x) {
+        const int c = tile_c0 + t;
+        float av = 0.f, bv = 0.f;
+        if (c < C) {
+            float sa = 0.f, sb = 0.f;
+            for (int rr = 0; rr < R; ++rr) {
+                sa += __ldcg(acc + (size_t)rr * 2 * C + c);
+                sb += __ldcg(acc + (size_t)rr * 2 * C + C + c);
+            }
+            const float mean = to_f32(x[c]) + sa / n;
             const float m2 = fmaxf(sb - sa * sa / n, 0.f);
             const float invstd = rsqrtf(m2 / n + eps);
-            a[i] = (weight ? weight[c] : 1.f) * invstd;
-            b[i] = (bias ? bias[c] : 0.f) - mean * a[i];
-            if (blockIdx.y == 0 && ty == 0) {
+            av = (weight ? weight[c] : 1.f) * invstd;
+            bv = (bias ? bias[c] : 0.f) - mean * av;
+            if (blockIdx.y == 0) {
                 if (save_mean) save_mean[c] = mean;
                 if (save_invstd) save_invstd[c] = invstd;
                 if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
@@ -901,17 +960,15 @@ bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, 
                 if (c == 0 && save_count) save_count[0] = n;
             }
         }
+        sm[t] = av;
+        sm[W + t] = bv;
     }
-    // second ticket: once every CTA has read the sums, the last one re-arms the scratch
     __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        if (atomicAdd(counters + 1, 1u) == total - 1) {
-            for (int c = 0; c < 2 * C; ++c) acc[c] = 0.f;
-            counters[0] = 0u;
-            counters[1] = 0u;
-        }
-    }
+    float a[VEC], b[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { a[i] = sm[tx * VEC + i]; b[i] = sm[W + tx * VEC + i]; }
+    // second ticket: once every CTA has read the sums, the last one re-arms the scratch
+    rearm_scratch(acc, counters, total, R * 2 * C);
     if (!active) return;
     const bool relu = (flags & SCB_BN_RELU) != 0;
     T* q = y + r0 * C + c0;
@@ -932,7 +989,7 @@ bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, 
 }
 
 template <typename T, int VEC>
-__global__ void __launch_bounds__(kBnThreads, 4)
+__global__ void __launch_bounds__(kFusedThreads, 1)
 bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t M, int C, int TX,
                          int64_t rows_per_cta, float* __restrict__ acc, unsigned* counters,
                          const float* __restrict__ mean, const float* __restrict__ invstd,
@@ -940,7 +997,7 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
                          const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias,
                          int flags) {
     extern __shared__ float sm[];
-    const int TY = kBnThreads / TX;
+    const int TY = kFusedThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = (blockIdx.x * TX + tx) * VEC;
     const bool active = c0 < C;
@@ -988,34 +1045,42 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
             }
         }
     }
-    cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, acc, acc + C);
+    const int R = bn_replicas(C);
+    {
+        float* my_acc = acc + (size_t)(blockIdx.y % R) * 2 * C;
+        cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, my_acc, my_acc + C);
+    }
     grid_barrier(counters, total);
     const float inv_n = 1.f / n_total[0];
-    float k2[VEC], k3[VEC];
-    if (active) {
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) {
-            const int c = c0 + i;
-            const float sd = __ldcg(acc + c), sx = __ldcg(acc + C + c);
+    const int W = TX * VEC;
+    const int tile_c0 = blockIdx.x * W;
+    __syncthreads();
+    for (int t = threadIdx.x; t < W; t += blockDim.x) {     // one reader per channel (see the forward kernel)
+        const int c = tile_c0 + t;
+        float v2 = 0.f, v3 = 0.f;
+        if (c < C) {
+            float sd = 0.f, sx = 0.f;
+            for (int rr = 0; rr < R; ++rr) {
+                sd += __ldcg(acc + (size_t)rr * 2 * C + c);
+                sx += __ldcg(acc + (size_t)rr * 2 * C + C + c);
+            }
             const float is = invstd[c];
-            k2[i] = sd * inv_n;
-            k3[i] = is * is * sx * inv_n;
-            if (blockIdx.y == 0 && ty == 0) {
+            v2 = sd * inv_n;
+            v3 = is * is * sx * inv_n;
+            if (blockIdx.y == 0) {
                 if (out_sums) { out_sums[c] = sd; out_sums[C + c] = sx; }
                 if (grad_weight) grad_weight[c] = sx * is;
                 if (grad_bias) grad_bias[c] = sd;
             }
         }
+        sm[t] = v2;
+        sm[W + t] = v3;
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        if (atomicAdd(counters + 1, 1u) == total - 1) {
-            for (int c = 0; c < 2 * C; ++c) acc[c] = 0.f;
-            counters[0] = 0u;
-            counters[1] = 0u;
-        }
-    }
+    float k2[VEC], k3[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { k2[i] = sm[tx * VEC + i]; k3[i] = sm[W + tx * VEC + i]; }
+    rearm_scratch(acc, counters, total, R * 2 * C);
     if (!active) return;
     T* po = dx + r0 * C + c0;
 #pragma unroll
@@ -1040,7 +1105,7 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
 static bool fused_geom(int64_t M, int C, int elem_size, bool al16, NhwcGeom* g, int ctas_per_sm) {
     const int vmax = 16 / elem_size;
     if (!al16 || C % vmax != 0 || M < 2) return false;
-    *g = nhwc_geom(M, C, elem_size, true, ctas_per_sm * sm_count());
+    *g = nhwc_geom(M, C, elem_size, true, ctas_per_sm * sm_count(), kFusedThreads);
     if (g->rows_per_cta > (int64_t)g->ty * kFusedRows) return false;           // would need more registers
     if ((int64_t)g->grid_x * g->grid_y > (int64_t)ctas_per_sm * sm_count()) return false;   // not one wave
     return true;
@@ -1049,7 +1114,7 @@ static bool fused_geom(int64_t M, int C, int elem_size, bool al16, NhwcGeom* g, 
 template <typename Kern>
 static int fused_ctas_per_sm(Kern kern, size_t smem) {
     int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kBnThreads, smem) != cudaSuccess) return 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kFusedThreads, smem) != cudaSuccess) return 0;
     return n;
 }
 
@@ -1059,7 +1124,7 @@ extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t oute
     if (!channels_last || channels <= 0) return 0;
     const int es = (dtype == SCB_F32) ? 4 : 2;
     NhwcGeom g;
-    return fused_geom(outer * inner, channels, es, true, &g, 4) ? 1 : 0;
+    return fused_geom(outer * inner, channels, es, true, &g, 1) ? 1 : 0;
 }
 
 extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t rows, int channels,
@@ -1079,17 +1144,22 @@ extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t r
         constexpr int VEC = Vec16<T>::N;
         NhwcGeom g;
         auto kern = bn_fwd_fused_nhwc_kernel<T, VEC>;
-        const size_t smem = 2 * kBnThreads * VEC * sizeof(float);
+        const size_t smem = 2 * kFusedThreads * VEC * sizeof(float);
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         const int per_sm = fused_ctas_per_sm(kern, smem);
-        if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(y), &g, per_sm < 4 ? per_sm : 4)) {
+        if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(y), &g, 1)) {
             dim3 grid(g.grid_x, (unsigned)g.grid_y);
             int TX = g.tx;
             int64_t rpc = g.rows_per_cta;
             const T* xp = (const T*)x;
             T* yp = (T*)y;
-            void* args[] = {&xp, &yp, &M, &C, &TX, &rpc, &acc, &counters, &weight, &bias, &running_mean, &running_var,
-                            &momentum, &eps, &save_mean, &save_invstd, &save_count, &flags};
-            SCB_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(kBnThreads), args, smem, stream));
+            // A plain launch: the grid has at most one CTA per SM and each CTA owns a full SM (1024 threads,
+            // 64 KiB of shared memory), so all of them become resident without needing anything from each
+            // other; cudaLaunchCooperativeKernel would add tens of microseconds of launch latency here.
+            kern<<<grid, kFusedThreads, smem, stream>>>(xp, yp, M, C, TX, rpc, acc, counters, weight, bias, running_mean,
+                                                        running_var, momentum, eps, save_mean, save_invstd, save_count,
+                                                        flags);
+            SCB_CUDA_OK(cudaGetLastError());
             rc = SCB_OK;
         }
     });
@@ -1115,19 +1185,20 @@ extern "C" int scb_bn_backward_fused(const void* dy, const void* x, void* dx, in
         constexpr int VEC = Vec16<T>::N;
         NhwcGeom g;
         auto kern = bn_bwd_fused_nhwc_kernel<T, VEC>;
-        const size_t smem = 2 * kBnThreads * VEC * sizeof(float);
+        const size_t smem = 2 * kFusedThreads * VEC * sizeof(float);
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         const int per_sm = fused_ctas_per_sm(kern, smem);
         if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(dy) && aligned16(dx), &g,
-                                      per_sm < 4 ? per_sm : 4)) {
+                                      1)) {
             dim3 grid(g.grid_x, (unsigned)g.grid_y);
             int TX = g.tx;
             int64_t rpc = g.rows_per_cta;
             const T* dyp = (const T*)dy;
             const T* xp = (const T*)x;
             T* dxp = (T*)dx;
-            void* args[] = {&dyp, &xp, &dxp, &M, &C, &TX, &rpc, &acc, &counters, &mean, &invstd, &weight, &bias,
-                            &n_total, &out_sums, &grad_weight, &grad_bias, &flags};
-            SCB_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(kBnThreads), args, smem, stream));
+            kern<<<grid, kFusedThreads, smem, stream>>>(dyp, xp, dxp, M, C, TX, rpc, acc, counters, mean, invstd, weight,
+                                                        bias, n_total, out_sums, grad_weight, grad_bias, flags);
+            SCB_CUDA_OK(cudaGetLastError());
             rc = SCB_OK;
         }
     });

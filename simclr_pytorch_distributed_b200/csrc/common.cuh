@@ -82,6 +82,19 @@ __device__ __forceinline__ void load_row_vec(const T* p, float (&v)[VEC]) {
         for (int i = 0; i < VEC; ++i) v[i] = to_f32(e[i]);
     }
 }
+// same, through L1: for the few lines that EVERY thread of the grid reads (a common reference row, per-channel
+// vectors) -- streamed with L1::no_allocate they would all queue up on the same L2 lines
+template <typename T, int VEC>
+__device__ __forceinline__ void load_row_vec_cached(const T* p, float (&v)[VEC]) {
+    if constexpr (VEC == 1) {
+        v[0] = to_f32(__ldg(p));
+    } else {
+        const uint4 raw = __ldg(reinterpret_cast<const uint4*>(p));
+        const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) v[i] = to_f32(e[i]);
+    }
+}
 template <typename T, int VEC>
 __device__ __forceinline__ void store_row_vec(T* p, const float (&v)[VEC]) {
     if constexpr (VEC == 1) {
