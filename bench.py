@@ -127,7 +127,7 @@ def time_steps(step_fn, steps, warmup, world, graph_pool=0):
         step_fn(i)
     barrier(world)
     how, graph, reps = 'eager launches', None, 0
-    if graph_pool > 0 and world == 1 and os.environ.get('SIMCLR_B200_BENCH_NO_GRAPH') != '1':
+    if graph_pool > 0 and os.environ.get('SIMCLR_B200_BENCH_NO_GRAPH') != '1':
         g = max(d for d in range(1, min(graph_pool, steps) + 1) if steps % d == 0)
         try:
             graph = torch.cuda.CUDAGraph()
@@ -142,6 +142,12 @@ def time_steps(step_fn, steps, warmup, world, graph_pool=0):
             graph = None
             how = 'eager launches (graph capture failed: %s)' % type(e).__name__
             torch.cuda.synchronize()
+        if world > 1:               # all ranks must take the same path (the steps contain collectives)
+            import torch.distributed as dist
+            flag = torch.tensor([1 if graph is not None else 0], device='cuda')
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 0 and graph is not None:
+                graph, how = None, 'eager launches (graph capture failed on another rank)'
     barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
