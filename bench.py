@@ -37,6 +37,20 @@ def peaks():
     return dict(hbm=6650.0, tf=1590.0, tf_sus=1400.0, src='fallback')
 
 
+def profiled_traffic(kernel_prefix):
+    """DRAM bytes per launch of a kernel from the committed `ncu --set full` summary (profiles/traffic.json,
+    written by tools/make_profile_summary.py); None when no capture of that kernel is committed."""
+    path = os.path.join(ROOT, 'profiles', 'traffic.json')
+    if not os.path.exists(path):
+        return None
+    with open(path) as f:
+        t = json.load(f)
+    for k, v in t.items():
+        if k.startswith(kernel_prefix):
+            return v['dram_bytes']
+    return None
+
+
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons while the GPU is under the bench's load."""
@@ -489,7 +503,8 @@ def main():
             t_bwd = kb['backward']
             achieved = 4.0 * A * C * DIM / (t_bwd * 1e-6) / 1e12
             out['roofline'] = {'bound': 'tensor', 'achieved': achieved, 'peak': pk['tf'], 'unit': 'TFLOP/s',
-                               'frac': achieved / pk['tf'], 'traffic': None,
+                               'frac': achieved / pk['tf'],
+                               'traffic': profiled_traffic('supcon_tc_bwd_kernel') if engine != 'fp32' else None,
                                'kernel': 'supcon backward (%s engine)' % engine, 'peak_source': pk['src'] + ' burst',
                                'algorithmic_flops_per_launch': 4.0 * A * C * DIM,
                                'kernel_us': kb}
@@ -524,7 +539,10 @@ def main():
                       'forward_fused': 3, 'backward_fused': 5}
             ach_dom = passes[dom] * S / (kb[dom] * 1e-6) / 1e9
             sb['roofline'] = {'bound': 'hbm', 'achieved': ach_dom, 'peak': pk['hbm'], 'unit': 'GB/s',
-                              'frac': ach_dom / pk['hbm'], 'traffic': None, 'kernel': 'bn_' + dom,
+                              'frac': ach_dom / pk['hbm'],
+                              'traffic': profiled_traffic('bn_bwd_fused' if dom == 'backward_fused' else
+                                                          'bn_fwd_fused' if dom == 'forward_fused' else 'bn_' + dom),
+                              'kernel': 'bn_' + dom,
                               'peak_source': pk['src'], 'algorithmic_bytes_per_launch': passes[dom] * S,
                               'all_kernels_sum': {'achieved': ach, 'frac': ach / pk['hbm'], 'us': tot_us},
                               'kernel_us': kb}
