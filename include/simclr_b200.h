@@ -140,6 +140,17 @@ int scb_supcon_finish(const float* dk, int ld_dk, const void* features, int feat
                       void* out_dfeatures, int64_t out_stride_sample, int64_t out_stride_view,
                       void* stream);
 
+/* scb_supcon_backward followed by scb_supcon_finish in one call for the tensor-core engines (two
+ * launches instead of three, no [n_rows, ldk] fp32 round trip): the autograd backward of
+ * losses.py:52-91 plus that of main_supcon.py:283, written straight into d features.
+ * The fp32 engine returns SCB_ERR_UNSUPPORTED: use the two separate calls there. */
+int scb_supcon_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
+                                 const float* lse_all, const float* npos_all, const float* grad_out,
+                                 int n_anchor_total, const void* features, int feat_dtype, int n_samples,
+                                 int64_t stride_sample, int64_t stride_view, int normalize,
+                                 const float* inv_norm, void* out_dfeatures, int64_t out_stride_sample,
+                                 int64_t out_stride_view, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* ================================================================== path 2: SyncBatchNorm
  *
  * Layout: x is [outer, C, inner] with element strides (stride_outer, 1*inner... ) described by

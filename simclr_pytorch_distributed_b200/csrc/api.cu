@@ -130,3 +130,27 @@ extern "C" int scb_supcon_backward(const scb_supcon_problem* p, int row_begin, i
     return tc_backward(p, row_begin, n_rows, lse_all, npos_all, grad_out, n_anchor_total, out_dk, ld_dk,
                        (char*)workspace + kFinScratchBytes, stream);
 }
+
+extern "C" int scb_supcon_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
+                                            const float* lse_all, const float* npos_all, const float* grad_out,
+                                            int n_anchor_total, const void* features, int feat_dtype, int n_samples,
+                                            int64_t stride_sample, int64_t stride_view, int normalize,
+                                            const float* inv_norm, void* out_dfeatures, int64_t out_stride_sample,
+                                            int64_t out_stride_view, void* workspace, int64_t workspace_bytes,
+                                            void* stream_) {
+    if (int e = check_problem(p, row_begin, n_rows)) return e;
+    (void)npos_all;
+    SCB_REQUIRE(lse_all && grad_out && features && out_dfeatures, "supcon_backward_features: null pointer");
+    SCB_REQUIRE(!normalize || inv_norm, "supcon_backward_features: normalize needs inv_norm");
+    SCB_REQUIRE(n_anchor_total >= 1, "supcon_backward_features: bad n_anchor_total");
+    if (p->engine == SCB_ENGINE_FP32) {
+        set_error("supcon_backward_features: the fp32 engine uses scb_supcon_backward + scb_supcon_finish");
+        return SCB_ERR_UNSUPPORTED;
+    }
+    SCB_REQUIRE(workspace && workspace_bytes >= scb_supcon_workspace_bytes(p, n_rows),
+                "supcon_backward_features: workspace too small");
+    return tc_backward_features(p, row_begin, n_rows, lse_all, grad_out, n_anchor_total, features, feat_dtype,
+                                n_samples, stride_sample, stride_view, normalize, inv_norm, out_dfeatures,
+                                out_stride_sample, out_stride_view, (char*)workspace + kFinScratchBytes,
+                                (cudaStream_t)stream_);
+}

@@ -792,6 +792,72 @@ supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int
     }
 }
 
+// Same reduction, fused with the layout kernel that follows it (scb_supcon_finish): un-stack the rows into
+// d features [n_samples, n_views, dim], apply the backward of the optional L2 normalisation and cast.
+// Requires ldk <= 128 (one 4-wide step per lane), which is what the tensor-core engine takes anyway.
+template <typename TF>
+__global__ void __launch_bounds__(256)
+supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows, int flat_q, int flat_ct,
+                               const __nv_bfloat16* __restrict__ k, int ldk, RowMap map, int n_views, int mode,
+                               int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
+                               float coef_scale_invT, const TF* __restrict__ feat, int n_samples, int dim,
+                               int64_t stride_s, int64_t stride_v, int normalize, const float* __restrict__ inv_norm,
+                               TF* __restrict__ out, int64_t ostride_s, int64_t ostride_v) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n_rows) return;
+    const int d = lane * 4;
+    const bool on = d < ldk;
+    const int rb = warp >> 8;
+    const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    if (on) {
+        for (int s = 0; s < n_slots; ++s) {
+            const float4 t = *reinterpret_cast<const float4*>(dk_part + ((int64_t)s * slot_rows + warp) * ldk + d);
+            acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
+        }
+        if (mask_kind == SCB_MASK_SIMCLR && n_views >= 2) {
+            const int gi = row_begin + warp;
+            const int base = (gi / map.vseg) * map.vseg, rem = gi - base;
+            const int v = rem / map.seg, b = rem - v * map.seg;
+            const float ai = map.is_anchor(gi, mode) ? 1.f : 0.f;
+            const float cpos = -1.f / (float)(n_views - 1);
+            for (int vv = 0; vv < n_views; ++vv) {
+                if (vv == v) continue;
+                const int j = base + vv * map.seg + b;
+                const float wgt = cpos * (ai + (map.is_anchor(j, mode) ? 1.f : 0.f));
+                const uint2 raw = *reinterpret_cast<const uint2*>(k + (int64_t)j * ldk + d);
+                const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
+                const float2 f0 = __bfloat1622float2(h2[0]), f1 = __bfloat1622float2(h2[1]);
+                acc[0] = fmaf(wgt, f0.x, acc[0]); acc[1] = fmaf(wgt, f0.y, acc[1]);
+                acc[2] = fmaf(wgt, f1.x, acc[2]); acc[3] = fmaf(wgt, f1.y, acc[3]);
+            }
+        }
+    }
+    const float coef = grad_out[0] * coef_scale_invT;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[i] *= coef;
+    // local row = v*n_samples + b  ->  features[b, v, :]
+    const int v_l = warp / n_samples, b_l = warp - v_l * n_samples;
+    const TF* src = feat + (int64_t)b_l * stride_s + (int64_t)v_l * stride_v;
+    TF* dst = out + (int64_t)b_l * ostride_s + (int64_t)v_l * ostride_v;
+    if (normalize) {
+        const float inv = inv_norm[warp];
+        float z[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (d + i < dim) z[i] = to_f32(src[d + i]) * inv;
+        float dot = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dot = fmaf(acc[i], z[i], dot);
+        dot = warp_sum(dot);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[i] = (acc[i] - z[i] * dot) * inv;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (d + i < dim) dst[d + i] = from_f32<TF>(acc[i]);
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -932,13 +998,11 @@ int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* pa
     return SCB_OK;
 }
 
-int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all, const float* npos_all,
-                const float* grad_out, int n_anchor_total, float* out_dk, int ld_dk, void* workspace,
-                cudaStream_t stream) {
-    (void)npos_all;
+// main kernel of the backward: fills the per-slot partial dK blocks in the workspace
+static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
+                            const float* grad_out, int n_anchor_total, void* workspace, TcGeom* g_out, TcParams* t_out,
+                            cudaStream_t stream) {
     if (int e = tc_supported(p)) return e;
-    SCB_REQUIRE(ld_dk >= p->ldk && ld_dk % 4 == 0 && (reinterpret_cast<uintptr_t>(out_dk) & 15u) == 0,
-                "supcon_backward (tensor-core engine): out_dk must be 16-byte aligned with ld_dk >= ldk (%d)", p->ldk);
     CUtensorMap tmap;
     if (int e = make_tmap(p, &tmap)) return e;
     const TcGeom g = tc_geom(p->n_k, n_rows);
@@ -946,7 +1010,6 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
     fill_params(p, row_begin, n_rows, n_rows, g, workspace, &t);
     t.lse_all = lse_all; t.grad_out = grad_out;
     t.coef_scale = p->loss_scale / (float)n_anchor_total;
-    t.out_dk = out_dk; t.ld_dk = ld_dk;
     if (int e = launch_label_rows(p, t, stream)) return e;
     const int kch = p->ldk / 64;
     const size_t smem = (size_t)(2 * kch * kSub) + 4 * (kch * kSub) + 4 * 2 * 64 * 4 + 64 + 128 + 28 * 8 + 16;
@@ -954,17 +1017,54 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
 #define SCB_LAUNCH_BWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
         if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        supcon_tc_bwd_kernel<KCH_, LAB_><<<g.grid, kTcThreads, smem, stream>>>(tmap, t);                  \
+        supcon_tc_bwd_kernel<KCH_, LAB_><<<g.grid, kTcThreads, smem, stream>>>(tmap, t);                \
     } while (0)
     if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
     else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
 #undef SCB_LAUNCH_BWD
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
+    *g_out = g;
+    *t_out = t;
+    return SCB_OK;
+}
+
+int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all, const float* npos_all,
+                const float* grad_out, int n_anchor_total, float* out_dk, int ld_dk, void* workspace,
+                cudaStream_t stream) {
+    (void)npos_all;
+    SCB_REQUIRE(ld_dk >= p->ldk && ld_dk % 4 == 0 && (reinterpret_cast<uintptr_t>(out_dk) & 15u) == 0,
+                "supcon_backward (tensor-core engine): out_dk must be 16-byte aligned with ld_dk >= ldk (%d)", p->ldk);
+    TcGeom g;
+    TcParams t;
+    if (int e = tc_backward_main(p, row_begin, n_rows, lse_all, grad_out, n_anchor_total, workspace, &g, &t, stream))
+        return e;
     prefer_max_smem_carveout(supcon_tc_reduce_dk_kernel);
     supcon_tc_reduce_dk_kernel<<<(unsigned)ceil_div((int64_t)n_rows * 32, 256), 256, 0, stream>>>(
         t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows,
         grad_out, t.coef_scale * p->inv_temperature, out_dk, ld_dk);
+    SCB_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return SCB_OK;
+}
+
+int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
+                         const float* grad_out, int n_anchor_total, const void* features, int feat_dtype,
+                         int n_samples, int64_t stride_s, int64_t stride_v, int normalize, const float* inv_norm,
+                         void* out, int64_t ostride_s, int64_t ostride_v, void* workspace, cudaStream_t stream) {
+    SCB_REQUIRE(n_rows == n_samples * p->n_views, "supcon_backward_features: n_rows must be n_samples * n_views");
+    TcGeom g;
+    TcParams t;
+    if (int e = tc_backward_main(p, row_begin, n_rows, lse_all, grad_out, n_anchor_total, workspace, &g, &t, stream))
+        return e;
+    const unsigned blocks = (unsigned)ceil_div((int64_t)n_rows * 32, 256);
+    SCB_DISPATCH_FLOAT(feat_dtype, TF, {
+        prefer_max_smem_carveout(supcon_tc_reduce_finish_kernel<TF>);
+        supcon_tc_reduce_finish_kernel<TF><<<blocks, 256, 0, stream>>>(
+            t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows,
+            grad_out, t.coef_scale * p->inv_temperature, (const TF*)features, n_samples, p->dim, stride_s, stride_v,
+            normalize, inv_norm, (TF*)out, ostride_s, ostride_v);
+    });
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     return SCB_OK;

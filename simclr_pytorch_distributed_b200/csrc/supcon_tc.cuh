@@ -15,6 +15,12 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
                 const float* npos_all, const float* grad_out, int n_anchor_total, float* out_dk,
                 int ld_dk, void* workspace, cudaStream_t stream);
 
+// backward + un-stack / normalise-backward / cast in two launches (main kernel + fused reduce-finish)
+int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
+                         const float* grad_out, int n_anchor_total, const void* features, int feat_dtype,
+                         int n_samples, int64_t stride_s, int64_t stride_v, int normalize, const float* inv_norm,
+                         void* out, int64_t ostride_s, int64_t ostride_v, void* workspace, cudaStream_t stream);
+
 // diagnostics: device buffer of 3 x 1024 int64 that CTA 0 of the backward kernel fills with
 // (event id, clock64) pairs; nullptr switches tracing off
 void tc_set_trace(long long* p);

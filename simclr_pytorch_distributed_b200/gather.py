@@ -34,6 +34,7 @@ class _CudaOps:
     forward = staticmethod(L.launch_forward)
     backward = staticmethod(L.launch_backward)
     finish = staticmethod(L.launch_finish)
+    backward_features = staticmethod(L.launch_backward_features)
 
     @staticmethod
     def lib():
@@ -90,11 +91,14 @@ class _DistSupConFunction(torch.autograd.Function):
         temperature, base_temperature, normalize = ctx.args
         dev = feats.device
         g = grad_out.detach().to(torch.float32).contiguous()
-        dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
         prob = L._problem(plan, k_all, None, labels_all, None, temperature, base_temperature)
-        ops.backward(lib, prob, plan, lse_all, npos_all, g, dk, dev)            # no collective needed
         dfeats = torch.empty(feats.shape, dtype=feats.dtype, device=dev)
-        ops.finish(lib, dk, feats, plan, normalize, inv_norm, dfeats)
+        if plan.engine != _lib.ENGINE_FP32 and hasattr(ops, 'backward_features'):
+            ops.backward_features(lib, prob, plan, lse_all, npos_all, g, feats, normalize, inv_norm, dfeats, dev)
+        else:                                                                    # no collective needed either way
+            dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
+            ops.backward(lib, prob, plan, lse_all, npos_all, g, dk, dev)
+            ops.finish(lib, dk, feats, plan, normalize, inv_norm, dfeats)
         return dfeats, None, None, None, None, None, None
 
 

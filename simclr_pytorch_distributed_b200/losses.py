@@ -126,6 +126,18 @@ def launch_backward(lib, prob, plan, lse_all, npos_all, grad_out, dk, device):
         ws.data_ptr(), ws.numel(), _stream(device)), 'scb_supcon_backward')
 
 
+def launch_backward_features(lib, prob, plan, lse_all, npos_all, grad_out, feats, normalize, inv_norm, dfeats, device):
+    """Backward + finish in one call (tensor-core engines): scb_supcon_backward_features."""
+    need = lib.scb_supcon_workspace_bytes(ctypes.byref(prob), plan.rows_local)
+    ws = _Workspace.get(device, need)
+    _lib.check(lib.scb_supcon_backward_features(
+        ctypes.byref(prob), plan.row_begin, plan.rows_local, lse_all.data_ptr(), npos_all.data_ptr(),
+        grad_out.data_ptr(), plan.n_anchor_total, feats.data_ptr(), _lib.dtype_code(feats.dtype), plan.n_local,
+        feats.stride(0), feats.stride(1), int(normalize), inv_norm.data_ptr() if inv_norm is not None else None,
+        dfeats.data_ptr(), dfeats.stride(0), dfeats.stride(1), ws.data_ptr(), ws.numel(), _stream(device)),
+        'scb_supcon_backward_features')
+
+
 def launch_finish(lib, dk, feats, plan, normalize, inv_norm, dfeats):
     _lib.check(lib.scb_supcon_finish(
         dk.data_ptr(), dk.stride(0), feats.data_ptr(), _lib.dtype_code(feats.dtype),
@@ -165,11 +177,15 @@ class _SupConFunction(torch.autograd.Function):
         dev = feats.device
         with torch.cuda.device(dev):
             g = grad_out.detach().to(torch.float32).contiguous()
-            dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
             prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
-            launch_backward(lib, prob, plan, stats[0], stats[2], g, dk, dev)
             dfeats = torch.empty(feats.shape, dtype=feats.dtype, device=dev)
-            launch_finish(lib, dk, feats, plan, normalize, stats[3] if normalize else None, dfeats)
+            inv_norm = stats[3] if normalize else None
+            if plan.engine != _lib.ENGINE_FP32:
+                launch_backward_features(lib, prob, plan, stats[0], stats[2], g, feats, normalize, inv_norm, dfeats, dev)
+            else:
+                dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
+                launch_backward(lib, prob, plan, stats[0], stats[2], g, dk, dev)
+                launch_finish(lib, dk, feats, plan, normalize, inv_norm, dfeats)
         return dfeats, None, None, None, None, None, None
 
 
