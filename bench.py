@@ -229,7 +229,7 @@ def loss_kernel_breakdown(engine, steps):
     k = torch.empty((plan.n_k, plan.ldk), dtype=plan.k_torch, device=dev)
     k_lo = torch.empty_like(k) if engine == 'bf16x3' else None
     stats = torch.empty((4, plan.n_k), dtype=torch.float32, device=dev)
-    loss = torch.empty((), dtype=torch.float32, device=dev)
+    loss = torch.empty(2, dtype=torch.float32, device=dev)
     gout = torch.ones((), dtype=torch.float32, device=dev)
     dk = torch.empty((plan.rows_local, DIM), dtype=torch.float32, device=dev)
     dz = torch.empty_like(z)

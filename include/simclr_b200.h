@@ -88,6 +88,8 @@ typedef struct scb_supcon_problem {
     int32_t mask_kind;      /* SCB_MASK_*                                                         */
     int32_t mode;           /* SCB_MODE_*                                                         */
     int32_t engine;         /* SCB_ENGINE_*                                                       */
+    int32_t scalar_dtype;   /* SCB_F32/BF16/F16: dtype of the loss scalar handed to autograd, i.e. of
+                               out_loss[1] (forward) and of *grad_out (backward)                   */
     float inv_temperature;  /* 1/T                  losses.py:64-66                               */
     float loss_scale;       /* T / base_temperature losses.py:90                                  */
 } scb_supcon_problem;
@@ -111,7 +113,8 @@ int64_t scb_supcon_workspace_bytes(const scb_supcon_problem* p, int n_rows);
  * one GPU).  Never materialises the [A, n_k] matrix.  Outputs, indexed by (row - row_begin):
  *   out_lse    log sum_{j != i} exp(s_ij)            (natural log, s = k_i . k_j / T)
  *   out_possum sum_j M_ij s_ij        out_npos  sum_j M_ij
- *   out_loss[0] = (1/n_anchor_total) * sum over the LOCAL anchors of -(T/Tb)(possum/npos - lse)
+ *   out_loss (TWO floats): [0] = (1/n_anchor_total) * sum over the LOCAL anchors of -(T/Tb)(possum/npos - lse)
+ *                 and [1] = the same value rounded to p->scalar_dtype, stored in the low-order bytes
  *                 (losses.py:87-91; on one GPU this is the loss, across ranks the sum of the
  *                 ranks' values is)
  * Non-anchor local rows (mode `one`, v > 0) get lse = 0, npos = 1, possum = 0. */
@@ -123,7 +126,8 @@ int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, int n_rows, i
  *   G_ij = coef * (exp(s_ij - lse_i) [i != j] - M_ij / npos_i),  coef = *grad_out * (T/Tb) / n_anchor_total
  *   out_dk[row - row_begin, :] = (1/T) * sum_j ( [i anchor] G_ij + [j anchor] G_ji ) k_j
  * lse_all / npos_all are indexed by GLOBAL row (length n_k; gathered across ranks by the caller).
- * grad_out is a device scalar (the upstream gradient of the loss), so no host sync is needed.
+ * grad_out is a device scalar of dtype p->scalar_dtype (the upstream gradient of the loss; declared
+ * float* for the common case), so no host sync and no conversion kernel is needed.
  * out_dk is float32 [n_rows, ld_dk]. */
 int scb_supcon_backward(const scb_supcon_problem* p, int row_begin, int n_rows,
                         const float* lse_all, const float* npos_all, const float* grad_out,

@@ -88,7 +88,7 @@ class SupconProblem(ctypes.Structure):
         ('k_dtype', ctypes.c_int32), ('n_k', ctypes.c_int32), ('dim', ctypes.c_int32),
         ('ldk', ctypes.c_int32), ('n_views', ctypes.c_int32), ('seg', ctypes.c_int32),
         ('n_seg', ctypes.c_int32), ('mask_kind', ctypes.c_int32), ('mode', ctypes.c_int32),
-        ('engine', ctypes.c_int32), ('inv_temperature', ctypes.c_float),
+        ('engine', ctypes.c_int32), ('scalar_dtype', ctypes.c_int32), ('inv_temperature', ctypes.c_float),
         ('loss_scale', ctypes.c_float),
     ]
 

@@ -51,6 +51,8 @@ static int check_problem(const scb_supcon_problem* p, int row_begin, int n_rows)
     SCB_REQUIRE(p->mask_kind != SCB_MASK_LABELS || p->labels, "supcon: labels missing");
     SCB_REQUIRE(p->mask_kind != SCB_MASK_EXPLICIT || p->mask, "supcon: mask missing");
     SCB_REQUIRE(p->mask_kind >= 0 && p->mask_kind <= 2, "supcon: bad mask_kind");
+    SCB_REQUIRE(p->scalar_dtype == SCB_F32 || p->scalar_dtype == SCB_BF16 || p->scalar_dtype == SCB_F16,
+                "supcon: bad scalar_dtype %d", p->scalar_dtype);
     SCB_REQUIRE(row_begin >= 0 && n_rows >= 1 && row_begin + n_rows <= p->n_k, "supcon: bad row range");
     if (p->engine == SCB_ENGINE_FP32) {
         SCB_REQUIRE(p->k_dtype == SCB_F32, "supcon: ENGINE_FP32 needs an F32 contrast matrix");

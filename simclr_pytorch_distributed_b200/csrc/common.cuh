@@ -108,6 +108,12 @@ __device__ __forceinline__ void store_row_vec(T* p, const float (&v)[VEC]) {
     }
 }
 
+// a device scalar whose element type is only known at run time (SCB_F32 / SCB_BF16 / SCB_F16)
+__device__ __forceinline__ float load_scalar(const void* p, int dtype) {
+    if (dtype == SCB_BF16) return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(p));
+    if (dtype == SCB_F16) return __half2float(*reinterpret_cast<const __half*>(p));
+    return *reinterpret_cast<const float*>(p);
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -150,7 +150,7 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
                        RowMap map, int mode, float loss_scale, double inv_anchors,
                        float* __restrict__ out_lse,
                        float* __restrict__ out_possum, float* __restrict__ out_npos,
-                       float* __restrict__ out_loss_sum, void* scratch) {
+                       float* __restrict__ out_loss_sum, void* scratch, int scalar_dtype) {
     __shared__ double red[32];
     __shared__ unsigned s_last;
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
@@ -221,7 +221,12 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
         }
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
         if (threadIdx.x == 0) {
-            out_loss_sum[0] = (float)(t * inv_anchors);
+            const float loss = (float)(t * inv_anchors);
+            out_loss_sum[0] = loss;
+            out_loss_sum[1] = 0.f;                 // [1]: the loss in the caller's scalar dtype (low-order bytes)
+            if (scalar_dtype == SCB_BF16) *reinterpret_cast<__nv_bfloat16*>(out_loss_sum + 1) = __float2bfloat16_rn(loss);
+            else if (scalar_dtype == SCB_F16) *reinterpret_cast<__half*>(out_loss_sum + 1) = __float2half_rn(loss);
+            else out_loss_sum[1] = loss;
             *ticket = 0u;
         }
     }
@@ -283,7 +288,7 @@ supcon_fwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, R
 __global__ void __launch_bounds__(1024)
 supcon_bwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, RowMap map,
                        MaskSpec msk, int mode, float inv_T, float coef_scale,
-                       const float* __restrict__ grad_out, int row_begin, int n_rows,
+                       const float* __restrict__ grad_out, int grad_dtype, int row_begin, int n_rows,
                        const float* __restrict__ lse_all, const float* __restrict__ npos_all,
                        float* __restrict__ out_dk, int ld_dk) {
     __shared__ float xs[32][33], ys[32][33], hs[32][33];
@@ -295,7 +300,7 @@ supcon_bwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, R
     const int sid_i = map.sid(i < n_k ? i : 0);
     const float lse_i = anchor_i ? lse_all[i] : 0.f;
     const float inv_np_i = anchor_i ? 1.f / npos_all[i] : 0.f;
-    const float coef = grad_out[0] * coef_scale;
+    const float coef = load_scalar(grad_out, grad_dtype) * coef_scale;
     const int dbeg = blockIdx.z * 128;
     float accd[4] = {0.f, 0.f, 0.f, 0.f};
     const int n_tiles = (n_k + 31) / 32;
@@ -360,7 +365,7 @@ int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const 
     dim3 grid((unsigned)ceil_div(n_rows, 32), 1, (unsigned)ceil_div(p->dim, 128)), block(32, 32);
     supcon_bwd_fp32_kernel<<<grid, block, 0, stream>>>(
         (const float*)p->k, p->ldk, p->dim, p->n_k, RowMap::of(p), MaskSpec::of(p), p->mode,
-        p->inv_temperature, p->loss_scale / (float)n_anchor_total, grad_out, row_begin, n_rows,
+        p->inv_temperature, p->loss_scale / (float)n_anchor_total, grad_out, p->scalar_dtype, row_begin, n_rows,
         lse_all, npos_all, out_dk, ld_dk);
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
@@ -375,7 +380,7 @@ int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split,
     prefer_max_smem_carveout(supcon_finalize_kernel);
     supcon_finalize_kernel<<<ctas, kFinThreads, 0, stream>>>(part, n_split, flat_q, flat_ct, n_rows, row_begin,
                                                              RowMap::of(p), p->mode, p->loss_scale, inv_anchors,
-                                                             out_lse, out_possum, out_npos, out_loss_sum, scratch);
+                                                             out_lse, out_possum, out_npos, out_loss_sum, scratch, p->scalar_dtype);
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     return SCB_OK;

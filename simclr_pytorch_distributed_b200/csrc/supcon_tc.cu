@@ -757,12 +757,12 @@ __global__ void __launch_bounds__(256)
 supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int flat_q, int flat_ct,
                            const __nv_bfloat16* __restrict__ k, int ldk, RowMap map, int n_views, int mode,
                            int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
-                           float coef_scale_invT, float* __restrict__ out_dk, int ld_dk) {
+                           int grad_dtype, float coef_scale_invT, float* __restrict__ out_dk, int ld_dk) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= n_rows) return;
     const int rb = warp >> 8;
     const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
-    const float coef = grad_out[0] * coef_scale_invT;
+    const float coef = load_scalar(grad_out, grad_dtype) * coef_scale_invT;
     const bool simclr = (mask_kind == SCB_MASK_SIMCLR) && n_views >= 2;
     const int gi = row_begin + warp;
     const int base = (gi / map.vseg) * map.vseg, rem = gi - base;
@@ -772,9 +772,15 @@ supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int
     float* dst = out_dk + (int64_t)warp * ld_dk;
     for (int d = lane * 4; d < ldk; d += 128) {
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int s = 0; s < n_slots; ++s) {
-            const float4 t = *reinterpret_cast<const float4*>(dk_part + ((int64_t)s * slot_rows + warp) * ldk + d);
-            acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
+        for (int s0 = 0; s0 < n_slots; s0 += 8) {          // eight slots at a time: all loads in flight together
+            float4 t[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                t[u] = (s0 + u < n_slots)
+                           ? __ldcs(reinterpret_cast<const float4*>(dk_part + ((int64_t)(s0 + u) * slot_rows + warp) * ldk + d))
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { acc[0] += t[u].x; acc[1] += t[u].y; acc[2] += t[u].z; acc[3] += t[u].w; }
         }
         if (simclr) {
             for (int vv = 0; vv < n_views; ++vv) {
@@ -800,7 +806,7 @@ __global__ void __launch_bounds__(256)
 supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows, int flat_q, int flat_ct,
                                const __nv_bfloat16* __restrict__ k, int ldk, RowMap map, int n_views, int mode,
                                int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
-                               float coef_scale_invT, const TF* __restrict__ feat, int n_samples, int dim,
+                               int grad_dtype, float coef_scale_invT, const TF* __restrict__ feat, int n_samples, int dim,
                                int64_t stride_s, int64_t stride_v, int normalize, const float* __restrict__ inv_norm,
                                TF* __restrict__ out, int64_t ostride_s, int64_t ostride_v) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -811,9 +817,15 @@ supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows,
     const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     if (on) {
-        for (int s = 0; s < n_slots; ++s) {
-            const float4 t = *reinterpret_cast<const float4*>(dk_part + ((int64_t)s * slot_rows + warp) * ldk + d);
-            acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
+        for (int s0 = 0; s0 < n_slots; s0 += 8) {          // eight slots at a time: all loads in flight together
+            float4 t[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                t[u] = (s0 + u < n_slots)
+                           ? __ldcs(reinterpret_cast<const float4*>(dk_part + ((int64_t)(s0 + u) * slot_rows + warp) * ldk + d))
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { acc[0] += t[u].x; acc[1] += t[u].y; acc[2] += t[u].z; acc[3] += t[u].w; }
         }
         if (mask_kind == SCB_MASK_SIMCLR && n_views >= 2) {
             const int gi = row_begin + warp;
@@ -833,7 +845,7 @@ supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows,
             }
         }
     }
-    const float coef = grad_out[0] * coef_scale_invT;
+    const float coef = load_scalar(grad_out, grad_dtype) * coef_scale_invT;
 #pragma unroll
     for (int i = 0; i < 4; ++i) acc[i] *= coef;
     // local row = v*n_samples + b  ->  features[b, v, :]
@@ -1042,7 +1054,7 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
     prefer_max_smem_carveout(supcon_tc_reduce_dk_kernel);
     supcon_tc_reduce_dk_kernel<<<(unsigned)ceil_div((int64_t)n_rows * 32, 256), 256, 0, stream>>>(
         t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows,
-        grad_out, t.coef_scale * p->inv_temperature, out_dk, ld_dk);
+        grad_out, p->scalar_dtype, t.coef_scale * p->inv_temperature, out_dk, ld_dk);
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     return SCB_OK;
@@ -1062,7 +1074,7 @@ int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
         prefer_max_smem_carveout(supcon_tc_reduce_finish_kernel<TF>);
         supcon_tc_reduce_finish_kernel<TF><<<blocks, 256, 0, stream>>>(
             t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows,
-            grad_out, t.coef_scale * p->inv_temperature, (const TF*)features, n_samples, p->dim, stride_s, stride_v,
+            grad_out, p->scalar_dtype, t.coef_scale * p->inv_temperature, (const TF*)features, n_samples, p->dim, stride_s, stride_v,
             normalize, inv_norm, (TF*)out, ostride_s, ostride_v);
     });
     SCB_CUDA_OK(cudaGetLastError());

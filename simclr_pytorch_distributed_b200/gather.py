@@ -90,7 +90,7 @@ class _DistSupConFunction(torch.autograd.Function):
         plan = ctx.plan
         temperature, base_temperature, normalize = ctx.args
         dev = feats.device
-        g = grad_out.detach().to(torch.float32).contiguous()
+        g = L.grad_scalar(grad_out, feats.dtype)
         prob = L._problem(plan, k_all, None, labels_all, None, temperature, base_temperature)
         dfeats = torch.empty(feats.shape, dtype=feats.dtype, device=dev)
         if plan.engine != _lib.ENGINE_FP32 and hasattr(ops, 'backward_features'):
@@ -149,5 +149,6 @@ class DistributedSupConLoss(nn.Module):
         engine = L.select_engine(self.engine, features.dtype, dim, mask_kind, world * n_views * bsz)
         plan = L.LossPlan(bsz, n_views, dim, n_seg=world, seg_index=rank, mode=mode, mask_kind=mask_kind,
                           engine=engine)
+        plan.scalar_dtype = _lib.dtype_code(features.dtype)
         return _DistSupConFunction.apply(features, labels_all, plan, float(self.temperature),
                                          float(self.base_temperature), bool(self.normalize), group)

@@ -74,6 +74,7 @@ class LossPlan:
         self.n_k = n_seg * self.rows_local
         self.row_begin = seg_index * self.rows_local
         self.n_anchor_total = self.n_k if mode == _lib.MODE_ALL else n_seg * n_local
+        self.scalar_dtype = _lib.F32          # dtype of the loss / upstream-gradient scalars (set by the caller)
         if engine == _lib.ENGINE_FP32:
             self.k_dtype, self.k_torch, self.ldk = _lib.F32, torch.float32, _round_up(dim, 4)
         else:
@@ -89,6 +90,7 @@ def _problem(plan, k, k_lo, labels, mask, temperature, base_temperature):
     p.k_dtype, p.n_k, p.dim, p.ldk = plan.k_dtype, plan.n_k, plan.dim, plan.ldk
     p.n_views, p.seg, p.n_seg = plan.n_views, plan.n_local, plan.n_seg
     p.mask_kind, p.mode, p.engine = plan.mask_kind, plan.mode, plan.engine
+    p.scalar_dtype = plan.scalar_dtype
     p.inv_temperature = 1.0 / temperature
     p.loss_scale = temperature / base_temperature
     return p
@@ -147,6 +149,22 @@ def launch_finish(lib, dk, feats, plan, normalize, inv_norm, dfeats):
         'scb_supcon_finish')
 
 
+def typed_loss(loss2, dtype):
+    """The 0-dim loss in the features' dtype without a conversion kernel: the forward leaves the value
+    rounded to `scalar_dtype` in the low-order bytes of loss2[1] (include/simclr_b200.h)."""
+    if dtype == torch.float32:
+        return loss2[0]
+    return loss2[1:2].view(dtype)[0]
+
+
+def grad_scalar(grad_out, dtype):
+    """Upstream gradient as a device scalar of the dtype the kernels were told to expect."""
+    g = grad_out.detach()
+    if g.dtype != dtype:
+        g = g.to(dtype)
+    return g.contiguous()
+
+
 class _SupConFunction(torch.autograd.Function):
     """Single-GPU loss: prep -> forward -> (backward -> finish).  losses.py:52-91 + autograd."""
 
@@ -159,14 +177,14 @@ class _SupConFunction(torch.autograd.Function):
             k = torch.empty((n_k, ldk), dtype=plan.k_torch, device=dev)
             k_lo = torch.empty_like(k) if plan.engine == _lib.ENGINE_BF16X3 else None
             stats = torch.empty((4, n_k), dtype=torch.float32, device=dev)   # lse, possum, npos, inv_norm
-            loss = torch.empty((), dtype=torch.float32, device=dev)
+            loss = torch.empty(2, dtype=torch.float32, device=dev)     # [fp32 value, value in feats.dtype]
             inv_norm = stats[3] if normalize else None
             launch_prep(lib, feats, plan, normalize, k, k_lo, inv_norm)
             prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
             launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
         ctx.plan, ctx.prob_args = plan, (temperature, base_temperature, normalize)
         ctx.save_for_backward(feats, labels, mask, k, k_lo, stats)
-        return loss.to(feats.dtype) if feats.dtype != torch.float32 else loss
+        return typed_loss(loss, feats.dtype)
 
     @staticmethod
     def backward(ctx, grad_out):
@@ -176,7 +194,7 @@ class _SupConFunction(torch.autograd.Function):
         lib = _lib.load()
         dev = feats.device
         with torch.cuda.device(dev):
-            g = grad_out.detach().to(torch.float32).contiguous()
+            g = grad_scalar(grad_out, feats.dtype)
             prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
             dfeats = torch.empty(feats.shape, dtype=feats.dtype, device=dev)
             inv_norm = stats[3] if normalize else None
@@ -250,5 +268,6 @@ class SupConLoss(nn.Module):
             mask_kind = _lib.MASK_SIMCLR
         engine = select_engine(self.engine, features.dtype, D, mask_kind, V * B)
         plan = LossPlan(B, V, D, mode=mode, mask_kind=mask_kind, engine=engine)
+        plan.scalar_dtype = _lib.dtype_code(features.dtype)
         return _SupConFunction.apply(features, labels, mask, plan, float(self.temperature),
                                      float(self.base_temperature), bool(self.normalize))

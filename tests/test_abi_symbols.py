@@ -47,10 +47,11 @@ def test_header_argument_counts_match_prototypes():
 
 
 def test_problem_struct_layout_matches_header():
-    # 4 pointers, 10 int32, 2 float -> 32 + 40 + 8 = 80 bytes, no padding surprises
-    assert ctypes.sizeof(_lib.SupconProblem) == 80
+    # 4 pointers, 11 int32, 2 float -> 32 + 44 + 8 = 84, padded to the pointer alignment: 88 bytes
+    assert ctypes.sizeof(_lib.SupconProblem) == 88
     assert _lib.SupconProblem.k_dtype.offset == 32
-    assert _lib.SupconProblem.inv_temperature.offset == 72
+    assert _lib.SupconProblem.scalar_dtype.offset == 72
+    assert _lib.SupconProblem.inv_temperature.offset == 76
 
 
 def test_no_gpu_calls_fail_loudly_not_silently(lib):

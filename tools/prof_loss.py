@@ -22,7 +22,7 @@ def main():
     plan = L.LossPlan(B, V, D, engine=L._ENGINES[engine])
     k = torch.empty((plan.n_k, plan.ldk), dtype=plan.k_torch, device=dev)
     stats = torch.empty((4, plan.n_k), dtype=torch.float32, device=dev)
-    loss = torch.empty((), dtype=torch.float32, device=dev)
+    loss = torch.empty(2, dtype=torch.float32, device=dev)
     g = torch.ones((), dtype=torch.float32, device=dev)
     dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
     dz = torch.empty_like(z)
@@ -38,7 +38,7 @@ def main():
         L.launch_finish(lib, dk, z, plan, False, None, dz)
         torch.cuda.synchronize()
     print('loss %.6f  fwd(+finalize) %.1f us  bwd(+init) %.1f us' % (
-        loss.item(), ev[0].elapsed_time(ev[1]) * 1e3, ev[1].elapsed_time(ev[2]) * 1e3))
+        loss[0].item(), ev[0].elapsed_time(ev[1]) * 1e3, ev[1].elapsed_time(ev[2]) * 1e3))
 
 
 if __name__ == '__main__':

@@ -20,7 +20,7 @@ def run(engine, z, labels, mode, T=0.5, Tb=0.07, only_fwd=False):
     plan = L.LossPlan(B, V, D, mode=mode, mask_kind=mk, engine=L._ENGINES[engine])
     k = torch.zeros((plan.n_k, plan.ldk), dtype=plan.k_torch, device=dev)
     stats = torch.zeros((4, plan.n_k), dtype=torch.float32, device=dev)
-    loss = torch.zeros((), dtype=torch.float32, device=dev)
+    loss = torch.zeros(2, dtype=torch.float32, device=dev)
     L.launch_prep(lib, z, plan, False, k, None, None)
     prob = L._problem(plan, k, None, labels, None, T, Tb)
     L.launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
@@ -53,7 +53,7 @@ def main():
         e_ps = (s0[1, :n_a] - s1[1, :n_a]).abs().max().item()
         e_np = (s0[2, :n_a] - s1[2, :n_a]).abs().max().item()
         msg = 'B=%d V=%d D=%d lab=%s mode=%d: loss %.6f vs %.6f | max|dlse| %.2e |dpossum| %.2e |dnpos| %.2e' % (
-            B, V, D, bool(lab), mode, l0.item(), l1.item(), e_lse, e_ps, e_np)
+            B, V, D, bool(lab), mode, l0[0].item(), l1[0].item(), e_lse, e_ps, e_np)
         if d0 is not None:
             rel = ((d0 - d1).norm() / d0.norm()).item()
             msg += ' | dK rel-F %.2e max %.2e (ref max %.2e)' % (rel, (d0 - d1).abs().max().item(), d0.abs().max().item())

@@ -15,7 +15,7 @@ z = F.normalize(torch.randn(B, V, D, device=dev), dim=-1).to(torch.bfloat16)
 plan = L.LossPlan(B, V, D, engine=_lib.ENGINE_BF16)
 k = torch.empty((plan.n_k, plan.ldk), dtype=plan.k_torch, device=dev)
 stats = torch.empty((4, plan.n_k), dtype=torch.float32, device=dev)
-loss = torch.empty((), dtype=torch.float32, device=dev)
+loss = torch.empty(2, dtype=torch.float32, device=dev)
 g = torch.ones((), dtype=torch.float32, device=dev)
 dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
 prob = L._problem(plan, k, None, None, None, 0.5, 0.07)
