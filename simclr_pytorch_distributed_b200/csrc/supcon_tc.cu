@@ -887,7 +887,24 @@ static EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
+static bool thread_has_context() {
+    typedef CUresult (*GetCurrentFn)(CUcontext*);
+    static GetCurrentFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuCtxGetCurrent", &ptr, cudaEnableDefault, &qres) != cudaSuccess || !ptr) return false;
+        fn = reinterpret_cast<GetCurrentFn>(ptr);
+    }
+    CUcontext ctx = nullptr;
+    return fn(&ctx) == CUDA_SUCCESS && ctx != nullptr;
+}
+
 static int make_tmap(const scb_supcon_problem* p, CUtensorMap* out) {
+    // The encoder is a driver-API entry point and needs a context current on THIS thread; autograd calls
+    // the backward from its own thread, where nothing may have touched the runtime yet.
+    if (!thread_has_context()) SCB_CUDA_OK(cudaFree(nullptr));     // binds the primary context (never during capture:
+                                                                    // a thread that captures has used the runtime before)
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return SCB_ERR_CUDA; }
     SCB_REQUIRE((reinterpret_cast<uintptr_t>(p->k) & 15u) == 0, "supcon: k must be 16-byte aligned");
