@@ -3,6 +3,7 @@
 #include "supcon_common.cuh"
 #include "supcon_tc.cuh"
 
+#include <stdlib.h>
 #include <string.h>
 #include <atomic>
 
@@ -12,6 +13,14 @@ static thread_local char g_err[512] = "";
 static std::atomic<long long> g_launches{0};
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("SCB_PDL");
+        return !(e != nullptr && e[0] == '0');
+    }();
+    return on;
+}
 
 void set_error(const char* fmt, ...) {
     va_list ap;

@@ -45,6 +45,34 @@ inline void prefer_max_smem_carveout(Kern kern) {
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Kernels of one call chain (prep -> forward -> finalize -> backward -> reduce) are launched with
+// programmatic stream serialisation: the next grid is scheduled while the previous one still runs, does
+// its prologue (barrier init, TMEM allocation, descriptor prefetch) and then blocks in pdl_wait() until the
+// previous grid has completed and its memory is visible.  RULE: a kernel launched through launch_pdl()
+// calls pdl_wait() in every thread before its first global-memory access.  Without the launch
+// attribute both instructions are no-ops.  SCB_PDL=0 in the environment turns the attribute off.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();   // api.cu
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---------------------------------------------------------------- dtype plumbing
 template <typename T> struct Vec16 { static constexpr int N = 16 / sizeof(T); };
 

@@ -18,6 +18,8 @@ supcon_prep_kernel(const TI* __restrict__ feat, int n_samples, int n_views, int 
                    float* __restrict__ out_inv_norm) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const int n_rows = n_samples * n_views;
+    pdl_launch_dependents();
+    pdl_wait();
     if (warp >= n_rows) return;
     const int v = warp / n_samples, b = warp - v * n_samples;     // out row = v*n_samples + b
     const TI* src = feat + (int64_t)b * stride_s + (int64_t)v * stride_v;
@@ -79,6 +81,8 @@ supcon_finish_kernel(const float* __restrict__ dk, int ld_dk, const TF* __restri
                      int64_t ostride_s, int64_t ostride_v) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const int n_rows = n_samples * n_views;
+    pdl_launch_dependents();
+    pdl_wait();
     if (warp >= n_rows) return;
     const int v = warp / n_samples, b = warp - v * n_samples;
     const float* g = dk + (int64_t)warp * ld_dk;
@@ -156,6 +160,8 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
     double* cta_sum = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + 16);
     double local = 0.0;
+    pdl_launch_dependents();
+    pdl_wait();
     for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
         float lse = 0.f, ps = 0.f, np = 1.f;
         if (map.is_anchor(row_begin + r, mode)) {
@@ -378,10 +384,9 @@ int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split,
     int ctas = (int)ceil_div(n_rows, kFinThreads);
     if (ctas > kFinMaxCtas) ctas = kFinMaxCtas;
     prefer_max_smem_carveout(supcon_finalize_kernel);
-    supcon_finalize_kernel<<<ctas, kFinThreads, 0, stream>>>(part, n_split, flat_q, flat_ct, n_rows, row_begin,
-                                                             RowMap::of(p), p->mode, p->loss_scale, inv_anchors,
-                                                             out_lse, out_possum, out_npos, out_loss_sum, scratch, p->scalar_dtype);
-    SCB_CUDA_OK(cudaGetLastError());
+    SCB_CUDA_OK(launch_pdl(supcon_finalize_kernel, dim3(ctas), dim3(kFinThreads), 0, stream, part, n_split, flat_q,
+                           flat_ct, n_rows, row_begin, RowMap::of(p), p->mode, p->loss_scale, inv_anchors, out_lse,
+                           out_possum, out_npos, out_loss_sum, scratch, p->scalar_dtype));
     count_launch();
     return SCB_OK;
 }
@@ -405,15 +410,14 @@ extern "C" int scb_supcon_prep(const void* features, int feat_dtype, int n_sampl
         prefer_max_smem_carveout(supcon_prep_kernel<TI, float>);
         prefer_max_smem_carveout(supcon_prep_kernel<TI, __nv_bfloat16>);
         if (k_dtype == SCB_F32)
-            supcon_prep_kernel<TI, float><<<blocks, 256, 0, stream>>>(
-                (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize, eps,
-                (float*)out_k, nullptr, ldk, out_inv_norm);
+            SCB_CUDA_OK(launch_pdl(supcon_prep_kernel<TI, float>, dim3(blocks), dim3(256), 0, stream,
+                                   (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize,
+                                   eps, (float*)out_k, (__nv_bfloat16*)nullptr, ldk, out_inv_norm));
         else
-            supcon_prep_kernel<TI, __nv_bfloat16><<<blocks, 256, 0, stream>>>(
-                (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize, eps,
-                (__nv_bfloat16*)out_k, (__nv_bfloat16*)out_k_lo, ldk, out_inv_norm);
+            SCB_CUDA_OK(launch_pdl(supcon_prep_kernel<TI, __nv_bfloat16>, dim3(blocks), dim3(256), 0, stream,
+                                   (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize,
+                                   eps, (__nv_bfloat16*)out_k, (__nv_bfloat16*)out_k_lo, ldk, out_inv_norm));
     });
-    SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     return SCB_OK;
 }
@@ -431,11 +435,10 @@ extern "C" int scb_supcon_finish(const float* dk, int ld_dk, const void* feature
     const unsigned blocks = (unsigned)ceil_div(rows * 32, 256);
     SCB_DISPATCH_FLOAT(feat_dtype, TF, {
         prefer_max_smem_carveout(supcon_finish_kernel<TF>);
-        supcon_finish_kernel<TF><<<blocks, 256, 0, stream>>>(
-            dk, ld_dk, (const TF*)features, n_samples, n_views, dim, stride_sample, stride_view,
-            normalize, inv_norm, (TF*)out_dfeatures, out_stride_sample, out_stride_view);
+        SCB_CUDA_OK(launch_pdl(supcon_finish_kernel<TF>, dim3(blocks), dim3(256), 0, stream, dk, ld_dk,
+                               (const TF*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize,
+                               inv_norm, (TF*)out_dfeatures, out_stride_sample, out_stride_view));
     });
-    SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     return SCB_OK;
 }

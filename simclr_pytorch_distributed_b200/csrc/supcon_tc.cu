@@ -53,6 +53,13 @@ struct TcParams {
     long long* trace;                   // optional (debug): per-role timestamps of CTA 0
 };
 
+// wall clock in ns.  clock64() is NOT usable for these timelines: the per-sub-partition counters
+// fall behind while all of a sub-partition's warps are parked on a barrier.
+__device__ __forceinline__ long long global_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
 // debug tracing: CTA 0, lane 0 of a warp appends (id, clock) pairs to its own 512-slot lane of the buffer
 struct Tracer {
     long long* buf; int n;
@@ -60,9 +67,14 @@ struct Tracer {
         if (base != nullptr && blockIdx.x == 0 && (threadIdx.x & 31) == 0 && role >= 0) buf = base + role * 1024;
     }
     __device__ __forceinline__ void operator()(int id) {
-        if (buf != nullptr && n < 510) { buf[2 * n] = id; buf[2 * n + 1] = clock64(); ++n; buf[1022] = n; }
+        if (buf != nullptr && n < 510) { buf[2 * n] = id; buf[2 * n + 1] = global_ns(); ++n; buf[1022] = n; }
     }
 };
+
+// diagnostics: wall-clock (ns) entry / exit of every CTA at trace[3072 + 2*cta (+1)]
+__device__ __forceinline__ void stamp_cta(long long* trace, int which) {
+    if (trace != nullptr && threadIdx.x == 0 && blockIdx.x < 512) trace[3072 + 2 * blockIdx.x + which] = global_ns();
+}
 
 __device__ __forceinline__ float bf16_dot_rows(const __nv_bfloat16* a, const __nv_bfloat16* b, int n) {
     float acc = 0.f;
@@ -103,6 +115,9 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     auto s_empty = [&](int h, int b) { return bar0 + 8u * (12 + h * 2 + b); };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    auto stamp = [&](int slot) { if (p.trace != nullptr && blockIdx.x == 0) { p.trace[slot] = clock64(); p.trace[slot + 16] = global_ns(); } };
+    if (threadIdx.x == 0) stamp(0);
+    stamp_cta(p.trace, 0);
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
     if (threadIdx.x == 0) {
         for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);
@@ -115,6 +130,9 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) stamp(1);
+    pdl_launch_dependents();
+    pdl_wait();                                  // everything above touched no global memory
 
     const int t0 = blockIdx.x * p.q;
     const int t1 = min(p.T, t0 + p.q);
@@ -165,10 +183,12 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 cur_rb = rb;
                 abuf = n_a & 1;
                 mbar_wait(a_full(abuf), (n_a >> 1) & 1);
+                if (n_a == 0 && lane == 0) stamp(2);
                 ++n_a;
             }
             const int st = n_b % NSB;
             mbar_wait(b_full(st), (n_b / NSB) & 1);
+            if (n_b == 0 && lane == 0) stamp(3);
             ++n_b;
             const int sbuf = idx & 1;
             const uint32_t sphase = (idx >> 1) & 1;
@@ -203,6 +223,12 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         float m = -INFINITY, sum = 0.f, possum = 0.f;
         int cur_rb = -1, idx = 0, li = 0, gi = 0, rep_i = 0;
 
+        // SimCLR positives with two views are read out of S itself: row i's single positive is the
+        // column of its other view (losses.py:42-43).  pj = that column; [pj_lo, pj_hi] = the range the
+        // warp's 32 rows cover, so the test per 32-column chunk is warp-uniform.
+        const bool capture = !kLabels && p.n_views == 2;
+        int pj = -1, pj_lo = 0, pj_hi = -1;
+
         auto flush = [&](int rb) {
             if (li >= p.a_count) return;
             // one slot per (CTA overlapping the row block, column half)
@@ -211,8 +237,11 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             if (kLabels) {
                 ps = possum * p.inv_T;
                 if (slot == 0) np = p.npos_row[gi];
+            } else if (capture) {
+                ps = possum * p.inv_T;
+                if (slot == 0) np = 1.f;
             } else if (slot == 0) {
-                // SimCLR positives: the other views of the same sample (closed form, losses.py:42-43)
+                // more than two views: the other views of the same sample, as dot products
                 const int base = (gi / p.map.vseg) * p.map.vseg, rem = gi - base;
                 const int v = rem / p.map.seg, b = rem - v * p.map.seg;
                 for (int vv = 0; vv < p.n_views; ++vv)
@@ -238,9 +267,24 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 li = rb * kBM + wg * kBMH + r;
                 gi = p.row_begin + li;
                 if (kLabels) rep_i = (gi < p.n_k) ? p.rep_row[gi] : -1;
+                if (capture) {
+                    pj = -1;
+                    if (gi < p.n_k) {
+                        const int rem = gi % p.map.vseg;
+                        pj = rem < p.map.seg ? gi + p.map.seg : gi - p.map.seg;
+                    }
+                    int lo = pj < 0 ? 0x7fffffff : pj, hi = pj;
+#pragma unroll
+                    for (int o = 16; o >= 1; o >>= 1) {
+                        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+                        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+                    }
+                    pj_lo = lo; pj_hi = hi;
+                }
             }
             const int sbuf = idx & 1;
             mbar_wait(s_full(wg, sbuf), (idx >> 1) & 1);
+            if (idx == 0 && threadIdx.x == 64) stamp(4);
             tc_fence_after();
             const int j0 = ct * kBN + ca * 64;            // this warpgroup's 64 columns of the tile
             const int g_lo = p.row_begin + rb * kBM + wg * kBMH;
@@ -249,6 +293,11 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             // one 32-column chunk of this thread's row: online (max, sum) update + positive sum
             auto process = [&](uint32_t (&v)[32], int cc) {
                 const int jc = j0 + cc * 32;
+                if (capture && jc <= pj_hi && jc + 32 > pj_lo) {
+                    const int c_hit = pj - jc;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) possum += (c == c_hit) ? __uint_as_float(v[c]) : 0.f;
+                }
                 if (!pred) {
                     float m8[8];
 #pragma unroll
@@ -316,11 +365,15 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             process(vb, 1);
             ++idx;
         }
+        if (threadIdx.x == 64) stamp(5);
         if (cur_rb >= 0) flush(cur_rb);
+        if (threadIdx.x == 64) stamp(6);
     }
 
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) stamp(7);
+    stamp_cta(p.trace, 1);
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
@@ -394,7 +447,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     const uint32_t dz_full = bar0 + 8u * 24, dz_empty = bar0 + 8u * 25;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[1023] = clock64();
+    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[1023] = global_ns();
+    stamp_cta(p.trace, 0);
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
     if (threadIdx.x == 0) {
         for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);          // a, b, s_full
@@ -409,7 +463,9 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[2047] = clock64();
+    pdl_launch_dependents();
+    pdl_wait();                                  // everything above touched no global memory
+    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[2047] = global_ns();
 
     const int t0 = blockIdx.x * p.q;
     const int t1 = min(p.T, t0 + p.q);
@@ -548,7 +604,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         int cur_rb = -1, idx = 0, li = 0, gi = 0, rep_i = 0, n_dz = 0;
         bool row_ok = false, rb_fast = false;
         float lse2_i = INFINITY, m0 = 0.f, R_i = 0.f, nia_i = 0.f;
-        Tracer tr(p.trace, (warp == 2) ? 1 : (warp == 6 ? 2 : -1));
+        Tracer tr(p.trace, (warp == 2) ? 1 : (warp == 10 ? 2 : -1));   // (h=0, a=0) and (h=1, a=0)
 
         // raw log-sum-exp of the column this thread stages for a tile (threads 0..63 of the warpgroup)
         auto load_col = [&](int ct_of_tile, bool tile_exists) -> float {
@@ -720,7 +776,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
 
     tc_fence_before();
     __syncthreads();
-    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[3071] = clock64();
+    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[3071] = global_ns();
+    stamp_cta(p.trace, 1);
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
@@ -734,6 +791,8 @@ __global__ void __launch_bounds__(256)
 label_rows_kernel(const int64_t* __restrict__ labels, int n_samples, RowMap map, int n_k, int n_views, int mode,
                   int* __restrict__ rep_row, float* __restrict__ npos_row, float* __restrict__ nia_row) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    pdl_launch_dependents();
+    pdl_wait();
     if (j >= n_k) return;
     const int64_t mine = labels[map.sid(j)];
     int rep = -1, cnt = 0;
@@ -759,6 +818,8 @@ supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int
                            int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
                            int grad_dtype, float coef_scale_invT, float* __restrict__ out_dk, int ld_dk) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    pdl_launch_dependents();
+    pdl_wait();
     if (warp >= n_rows) return;
     const int rb = warp >> 8;
     const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
@@ -810,6 +871,8 @@ supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows,
                                int64_t stride_s, int64_t stride_v, int normalize, const float* __restrict__ inv_norm,
                                TF* __restrict__ out, int64_t ostride_s, int64_t ostride_v) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    pdl_launch_dependents();
+    pdl_wait();
     if (warp >= n_rows) return;
     const int d = lane * 4;
     const bool on = d < ldk;
@@ -984,10 +1047,9 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
 static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, cudaStream_t stream) {
     if (p->mask_kind != SCB_MASK_LABELS) return SCB_OK;
     prefer_max_smem_carveout(label_rows_kernel);
-    label_rows_kernel<<<(unsigned)ceil_div(p->n_k, 256), 256, 0, stream>>>(
-        p->labels, p->n_seg * p->seg, t.map, p->n_k, p->n_views, p->mode, (int*)t.rep_row, (float*)t.npos_row,
-        (float*)t.nia_row);
-    SCB_CUDA_OK(cudaGetLastError());
+    SCB_CUDA_OK(launch_pdl(label_rows_kernel, dim3((unsigned)ceil_div(p->n_k, 256)), dim3(256), 0, stream, p->labels,
+                           p->n_seg * p->seg, t.map, p->n_k, p->n_views, p->mode, (int*)t.rep_row, (float*)t.npos_row,
+                           (float*)t.nia_row));
     count_launch();
     return SCB_OK;
 }
@@ -1014,7 +1076,7 @@ int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* pa
 #define SCB_LAUNCH_FWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
         if (int e = set_smem(supcon_tc_fwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        supcon_tc_fwd_kernel<KCH_, LAB_><<<g.grid, kTcThreads, smem, stream>>>(tmap, t);                  \
+        SCB_CUDA_OK(launch_pdl(supcon_tc_fwd_kernel<KCH_, LAB_>, dim3(g.grid), dim3(kTcThreads), smem, stream, tmap, t)); \
     } while (0)
     if (kch == 2) { if (lab) SCB_LAUNCH_FWD(2, true); else SCB_LAUNCH_FWD(2, false); }
     else { if (lab) SCB_LAUNCH_FWD(1, true); else SCB_LAUNCH_FWD(1, false); }
@@ -1046,7 +1108,7 @@ static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_ro
 #define SCB_LAUNCH_BWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
         if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        supcon_tc_bwd_kernel<KCH_, LAB_><<<g.grid, kTcThreads, smem, stream>>>(tmap, t);                \
+        SCB_CUDA_OK(launch_pdl(supcon_tc_bwd_kernel<KCH_, LAB_>, dim3(g.grid), dim3(kTcThreads), smem, stream, tmap, t)); \
     } while (0)
     if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
     else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
@@ -1069,10 +1131,10 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
     if (int e = tc_backward_main(p, row_begin, n_rows, lse_all, grad_out, n_anchor_total, workspace, &g, &t, stream))
         return e;
     prefer_max_smem_carveout(supcon_tc_reduce_dk_kernel);
-    supcon_tc_reduce_dk_kernel<<<(unsigned)ceil_div((int64_t)n_rows * 32, 256), 256, 0, stream>>>(
-        t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows,
-        grad_out, p->scalar_dtype, t.coef_scale * p->inv_temperature, out_dk, ld_dk);
-    SCB_CUDA_OK(cudaGetLastError());
+    SCB_CUDA_OK(launch_pdl(supcon_tc_reduce_dk_kernel, dim3((unsigned)ceil_div((int64_t)n_rows * 32, 256)), dim3(256), 0,
+                           stream, (const float*)t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode,
+                           p->mask_kind, row_begin, n_rows, grad_out, p->scalar_dtype,
+                           t.coef_scale * p->inv_temperature, out_dk, ld_dk));
     count_launch();
     return SCB_OK;
 }
@@ -1089,12 +1151,12 @@ int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
     const unsigned blocks = (unsigned)ceil_div((int64_t)n_rows * 32, 256);
     SCB_DISPATCH_FLOAT(feat_dtype, TF, {
         prefer_max_smem_carveout(supcon_tc_reduce_finish_kernel<TF>);
-        supcon_tc_reduce_finish_kernel<TF><<<blocks, 256, 0, stream>>>(
-            t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode, p->mask_kind, row_begin, n_rows,
-            grad_out, p->scalar_dtype, t.coef_scale * p->inv_temperature, (const TF*)features, n_samples, p->dim, stride_s, stride_v,
-            normalize, inv_norm, (TF*)out, ostride_s, ostride_v);
+        SCB_CUDA_OK(launch_pdl(supcon_tc_reduce_finish_kernel<TF>, dim3(blocks), dim3(256), 0, stream,
+                               (const float*)t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode,
+                               p->mask_kind, row_begin, n_rows, grad_out, p->scalar_dtype,
+                               t.coef_scale * p->inv_temperature, (const TF*)features, n_samples, p->dim, stride_s,
+                               stride_v, normalize, inv_norm, (TF*)out, ostride_s, ostride_v));
     });
-    SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     return SCB_OK;
 }

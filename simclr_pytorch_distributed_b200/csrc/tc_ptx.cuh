@@ -34,12 +34,36 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
         : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
-// Bounded wait: a protocol bug must surface as a launch failure, never as a hung GPU.
+// try_wait with a suspend-time hint: the warp may be parked by the hardware for up to `ns` nanoseconds
+// (it wakes when the phase completes), instead of coming back to the issue slots every few hundred cycles.
+__device__ __forceinline__ bool mbar_try_wait_park(uint32_t bar, uint32_t parity, uint32_t ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity), "r"(ns) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ unsigned long long wall_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// Bounded wait: a protocol bug must surface as a launch failure, never as a hung GPU.  Waiting warps share
+// their sub-partition's issue slots with the warps that do the work, so the loop is kept as quiet as possible:
+// parked try_wait, no clock reads except once every 256 wake-ups.  (clock64() is no use here anyway: the
+// sub-partition counters fall behind while its warps are parked.)
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
-    const long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > 4000000000ll) __trap();   // ~2 s
+    unsigned long long t0 = 0;
+    for (uint32_t spins = 1;; ++spins) {
+        if (mbar_try_wait_park(bar, parity, 100000u)) return;
+        if ((spins & 255u) == 0u) {
+            const unsigned long long now = wall_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 2000000000ull) __trap();   // 2 s
+        }
     }
 }
 
