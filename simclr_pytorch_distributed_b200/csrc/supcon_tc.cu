@@ -49,9 +49,16 @@ struct TcParams {
     float coef_scale;                   // (T/Tb) / n_anchor_total
     float* out_dk;
     int ld_dk;
-    float* dk_part;                     // backward partials [slot][RB*256][ldk] (one slot per CTA sharing a row block)
+    float* dk_part;                     // backward partials [slot][RB*128][ldk] (one slot per CTA sharing a row block)
     long long* trace;                   // optional (debug): per-role timestamps of CTA 0
 };
+
+// The timeline instrumentation below is compiled in only with -DSCB_TRACE=1 (tools/build_trace_lib.sh): even
+// untaken, its tests cost a few dozen instructions per tile on paths where every instruction is latency.
+#ifndef SCB_TRACE
+#define SCB_TRACE 0
+#endif
+constexpr bool kTrace = SCB_TRACE != 0;
 
 // wall clock in ns.  clock64() is NOT usable for these timelines: the per-sub-partition counters
 // fall behind while all of a sub-partition's warps are parked on a barrier.
@@ -60,20 +67,27 @@ __device__ __forceinline__ long long global_ns() {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
-// debug tracing: CTA 0, lane 0 of a warp appends (id, clock) pairs to its own 512-slot lane of the buffer
+// debug tracing: CTA 0, lane 0 of a warp appends (id, clock) pairs to its own 512-slot lane of the buffer.
+// trace[4095] != 0 switches these per-event stamps off (the stores perturb the pipeline) and keeps only the
+// per-CTA entry / exit stamps.
 struct Tracer {
-    long long* buf; int n;
-    __device__ Tracer(long long* base, int role) : buf(nullptr), n(0) {
-        if (base != nullptr && blockIdx.x == 0 && (threadIdx.x & 31) == 0 && role >= 0) buf = base + role * 1024;
+    long long* buf; int n; unsigned mask;
+    __device__ Tracer(long long* base, int role) : buf(nullptr), n(0), mask(0xffffffffu) {
+        if (kTrace && base != nullptr && blockIdx.x == 0 && (threadIdx.x & 31) == 0 && role >= 0 && base[4095] == 0) {
+            buf = base + role * 1024;
+            if (base[4094] != 0) mask = (unsigned)base[4094];    // only events with bit (id & 31) set (a stamp costs ~150 ns)
+        }
     }
     __device__ __forceinline__ void operator()(int id) {
-        if (buf != nullptr && n < 510) { buf[2 * n] = id; buf[2 * n + 1] = global_ns(); ++n; buf[1022] = n; }
+        if (kTrace && buf != nullptr && n < 510 && ((mask >> (id & 31)) & 1u)) {
+            buf[2 * n] = id; buf[2 * n + 1] = global_ns(); ++n; buf[1022] = n;
+        }
     }
 };
 
 // diagnostics: wall-clock (ns) entry / exit of every CTA at trace[3072 + 2*cta (+1)]
 __device__ __forceinline__ void stamp_cta(long long* trace, int which) {
-    if (trace != nullptr && threadIdx.x == 0 && blockIdx.x < 512) trace[3072 + 2 * blockIdx.x + which] = global_ns();
+    if (kTrace && trace != nullptr && threadIdx.x == 0 && blockIdx.x < 512) trace[3072 + 2 * blockIdx.x + which] = global_ns();
 }
 
 __device__ __forceinline__ float bf16_dot_rows(const __nv_bfloat16* a, const __nv_bfloat16* b, int n) {
@@ -115,13 +129,13 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     auto s_empty = [&](int h, int b) { return bar0 + 8u * (12 + h * 2 + b); };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    auto stamp = [&](int slot) { if (p.trace != nullptr && blockIdx.x == 0) { p.trace[slot] = clock64(); p.trace[slot + 16] = global_ns(); } };
+    auto stamp = [&](int slot) { if (kTrace && p.trace != nullptr && blockIdx.x == 0) { p.trace[slot] = clock64(); p.trace[slot + 16] = global_ns(); } };
     if (threadIdx.x == 0) stamp(0);
     stamp_cta(p.trace, 0);
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
     if (threadIdx.x == 0) {
         for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);
-        for (int i = 12; i < 16; ++i) mbar_init(bar0 + 8u * i, 2 * kBMH);
+        for (int i = 12; i < 16; ++i) mbar_init(bar0 + 8u * i, 8);     // s_empty: one arrival per warp of the row half
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -360,7 +374,9 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             tmem_ld_wait_dep(va);
             tmem_ld_wait_dep(vb);
             tc_fence_before();
-            mbar_arrive(s_empty(wg, sbuf));      // S buffer is free for the next MMA
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_empty(wg, sbuf));      // S buffer is free for the next MMA (one arrival per warp:
+                                                                // 32 per-thread arrivals on one barrier word serialise)
             process(va, 0);
             process(vb, 1);
             ++idx;
@@ -397,64 +413,83 @@ __device__ __forceinline__ void warp_transpose32(uint32_t (&v)[32], int lane) {
     }
 }
 
-// pack 16 fp32 -> bf16 and write them as 8 consecutive 32-bit TMEM columns of this thread's lane
+// pack pv[off .. off+15] to bf16 and write them as 8 consecutive 32-bit TMEM columns of this thread's lane
 // (UMMA A operand in TMEM: two K-consecutive bf16 per column, even index in the low half)
-__device__ __forceinline__ void store_p16(uint32_t taddr, const float (&pv)[16]) {
+template <int N>
+__device__ __forceinline__ void store_p16(uint32_t taddr, const float (&pv)[N], int off) {
     uint32_t wds[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[2 * i], pv[2 * i + 1]);
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[off + 2 * i], pv[off + 2 * i + 1]);
         wds[i] = *reinterpret_cast<uint32_t*>(&h2);
     }
     tmem_st8(taddr, wds);
 }
 
 // =================================================================================== backward
-// 18 warps: warp 0 TMA, warp 1 MMA issue + TMEM, warps 2..17 = four epilogue warpgroups.
-// Warpgroup w = (h, a) owns row half h and column half a of every tile, so the unit of the
-// MMA <-> epilogue hand-over is a [128 x 64] sub-tile: S[w] (64 TMEM columns) and P[w] (one
-// 16 KB swizzled sub-tile in shared memory).  While one warpgroup waits for its MMA2 + next MMA1
-// the other three keep the MUFU pipe busy.
-// P never touches shared memory: each thread packs its 64 values to bf16 and writes them with tcgen05.st
-// over the first half of the S columns it has just read; the second MMA takes its A operand from TMEM.
-// (With P in shared memory the two MMAs plus the P stores need ~160 B/clk of shared-memory bandwidth.)
-// smem: A[2*KCH*kSub] | B[4][KCH*kSub] | cols[4][2][64] f32 | flags | rowred | barriers | tmem slot
-// TMEM: S[h] at columns h*128 (warpgroup (h, a) owns columns h*128 + a*64 .. +64 and stores its P words in
-//       the first 32 of them), dK[h] at 256 + h*128.
+// 18 warps: warp 0 = TMA producer + per-tile column factors, warp 1 = MMA issuer + TMEM owner,
+// warps 2..17 = four epilogue warpgroups.
+//
+// A CTA owns a 128-row block (one UMMA M) at a time and walks its span of 128-column tiles.  S is
+// TRIPLE-buffered in TMEM and all sixteen epilogue warps work on the same tile (warpgroup g takes columns
+// g*32 .. g*32+31 of every row), so
+//   * the MUFU pipe always has four warps per sub-partition to draw from (two were not enough to keep it
+//     busy: a warp's exps share six scoreboards), and
+//   * the tensor pipe runs two tiles ahead: while the warps turn S(t) into P(t), S(t+1) and S(t+2) are
+//     already waiting and dK += P(t-1) K_j(t-1) is in flight.  The chain MMA1 -> tcgen05.ld -> exp ->
+//     tcgen05.st -> MMA2 is as long as before, but three tiles are inside it instead of one per row half.
+// P never touches shared memory: each thread packs its 32 values to bf16 and writes the 16 words with
+// tcgen05.st over the first half of the S columns it has just read; the second MMA takes its A operand
+// from TMEM.  (With P in shared memory the two MMAs plus the P stores need ~160 B/clk of shared memory.)
+// No ordering barrier is needed between MMA2(t) (reads P in S buffer t%3) and MMA1(t+3) (overwrites it):
+// both are issued by the same thread and the tensor pipe executes in issue order.
+//
+// Column data of a tile (1-exp factors C_j, log-sum-exps, "unsafe" flag) is staged next to its B tile by
+// the otherwise idle producer warp, and becomes visible through the same b_full barrier.
+//
+// smem: A[KCH*kSub] | B[5][KCH*kSub] | cols[5][2][128] f32 | flags[5][4] u32 | barriers | tmem slot
+// TMEM: S[b] at columns b*128 (b = 0..2), dK at 384 .. 384 + 64*KCH.
+
+constexpr int kBMB = 128;       // rows per row block of the backward
+constexpr int kBwdThreads = 608;     // the forward's 18 warps + one more issuing warp
+constexpr int kBwdMma1Warp = 18;
 
 template <int KCH, bool kLabels>
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kBwdThreads, 1)
 supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    constexpr int A_BYTES = 2 * KCH * kSub;
+    constexpr int A_BYTES = KCH * kSub;
     constexpr int B_BYTES = KCH * kSub;
-    constexpr int NSB = 4;
+    constexpr int NSB = 5;
+    constexpr int NS = 3;                          // S buffers
+    constexpr int ND = KCH * 64;                   // dK columns
+    constexpr uint32_t kDkCol = 384;
     uint8_t* a_smem = smem;
     uint8_t* b_smem = a_smem + A_BYTES;
-    float* cols = reinterpret_cast<float*>(b_smem + NSB * B_BYTES);       // [4 wg][2 arrays][64]
-    uint32_t* flags = reinterpret_cast<uint32_t*>(cols + 4 * 2 * 64);     // [4 wg][2 buf][2 warps]
-    float* rowred = reinterpret_cast<float*>(flags + 16);                 // [4 wg][4 warps][2]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(rowred + 32);            // 26 used
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 28);
+    float* cols = reinterpret_cast<float*>(b_smem + NSB * B_BYTES);       // [NSB][2][128]
+    uint32_t* flags = reinterpret_cast<uint32_t*>(cols + NSB * 256);      // [NSB][4]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(flags + NSB * 4 + 4);    // 23 used
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
     const uint32_t bar0 = smem_u32(bars);
-    auto a_full = [&]() { return bar0 + 8u * 0; };
-    auto a_empty = [&]() { return bar0 + 8u * 1; };
+    const uint32_t a_full = bar0, a_empty = bar0 + 8u;
     auto b_full = [&](int s) { return bar0 + 8u * (2 + s); };
-    auto b_empty = [&](int s) { return bar0 + 8u * (6 + s); };
-    // per row half h: S[h] ready / P[h] published (in TMEM) by its two warpgroups
-    auto s_full = [&](int h) { return bar0 + 8u * (10 + h); };
-    auto p_full = [&](int h) { return bar0 + 8u * (16 + h); };
-    const uint32_t dz_full = bar0 + 8u * 24, dz_empty = bar0 + 8u * 25;
+    auto b_empty = [&](int s) { return bar0 + 8u * (7 + s); };
+    auto s_full = [&](int b) { return bar0 + 8u * (12 + b); };
+    auto p_full = [&](int b) { return bar0 + 8u * (15 + b); };
+    const uint32_t dz_full = bar0 + 8u * 18, dz_empty = bar0 + 8u * 19;
+    auto s_free = [&](int b) { return bar0 + 8u * (20 + b); };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[1023] = global_ns();
+    if (kTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[1023] = global_ns();
     stamp_cta(p.trace, 0);
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 12; ++i) mbar_init(bar0 + 8u * i, 1);          // a, b, s_full
-        for (int h = 0; h < 2; ++h) mbar_init(p_full(h), 2 * kBMH);
+        mbar_init(a_full, 1);
+        mbar_init(a_empty, 1);
+        for (int s = 0; s < NSB; ++s) { mbar_init(b_full(s), 2); mbar_init(b_empty(s), 1); }
+        for (int b = 0; b < NS; ++b) { mbar_init(s_full(b), 1); mbar_init(p_full(b), 8); mbar_init(s_free(b), 1); }    // p_full: one arrival per warp of a team
         mbar_init(dz_full, 1);
-        mbar_init(dz_empty, 4 * kBMH);
+        mbar_init(dz_empty, 16);                          // one arrival per epilogue warp
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -465,33 +500,50 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     const uint32_t tmem_base = *tmem_slot;
     pdl_launch_dependents();
     pdl_wait();                                  // everything above touched no global memory
-    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[2047] = global_ns();
+    if (kTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[2047] = global_ns();
 
     const int t0 = blockIdx.x * p.q;
-    const int t1 = min(p.T, t0 + p.q);
+    const int n_tiles = min(p.T, t0 + p.q) - t0;
+    const int rb0 = t0 / p.CT, ct0 = t0 - rb0 * p.CT;
+    // reference point of the 1-exp path: P_ij = 2^(s - l_i) (1 + R_i C_j), R_i = 2^(l_i - m0), C_j = 2^(m0 - l_j);
+    // any m0 works as long as every |l - m0| stays below kSafeSpread, so one global value does
+    const float m0 = __ldg(p.lse_all) * kLog2e;
 
     if (warp == 0) {
-        // ---------------------------------------------------- TMA producer (warp-uniform, one lane issues)
-        int n_a = 0, n_b = 0, cur_rb = -1;
-        for (int tau = t0; tau < t1; ++tau) {
-            const int rb = tau / p.CT, ct = tau - rb * p.CT;
-            if (rb != cur_rb) {
-                cur_rb = rb;
-                mbar_wait(a_empty(), (n_a & 1) ^ 1);
+        // ---------------------------------------------------- TMA producer + column factors
+        auto load_lse4 = [&](int ct_) {
+            const int j = ct_ * kBN + lane * 4;
+            float4 l;
+            l.x = (j + 0 < p.n_k) ? __ldg(p.lse_all + j + 0) : 0.f;
+            l.y = (j + 1 < p.n_k) ? __ldg(p.lse_all + j + 1) : 0.f;
+            l.z = (j + 2 < p.n_k) ? __ldg(p.lse_all + j + 2) : 0.f;
+            l.w = (j + 3 < p.n_k) ? __ldg(p.lse_all + j + 3) : 0.f;
+            return l;
+        };
+        // the log-sum-exps of a tile's columns are fetched three tiles ahead: a load issued and consumed in
+        // consecutive iterations would put one L2 round trip into every iteration of this loop
+        int rb = rb0, ct = ct0, n_a = 0, ct_pf = ct0;
+        auto next_pf = [&](int t_pf) {
+            float4 l = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (t_pf < n_tiles) l = load_lse4(ct_pf);
+            if (++ct_pf == p.CT) ct_pf = 0;
+            return l;
+        };
+        float4 l_cur = next_pf(0), l_n1 = next_pf(1), l_n2 = next_pf(2);
+        for (int t = 0; t < n_tiles; ++t) {
+            const int st = t % NSB;
+            if (t == 0 || ct == 0) {
+                mbar_wait(a_empty, (n_a & 1) ^ 1);
                 if (elect_one()) {
-                    mbar_arrive_expect_tx(a_full(), A_BYTES);
+                    mbar_arrive_expect_tx(a_full, A_BYTES);
 #pragma unroll
-                    for (int h = 0; h < 2; ++h)
-#pragma unroll
-                        for (int kc = 0; kc < KCH; ++kc)
-                            tma_load_2d(smem_u32(a_smem + (h * KCH + kc) * kSub), &tmap, kc * 64,
-                                        p.row_begin + rb * kBM + h * kBMH, a_full());
+                    for (int kc = 0; kc < KCH; ++kc)
+                        tma_load_2d(smem_u32(a_smem + kc * kSub), &tmap, kc * 64, p.row_begin + rb * kBMB, a_full);
                 }
                 __syncwarp();
                 ++n_a;
             }
-            const int st = n_b % NSB;
-            mbar_wait(b_empty(st), ((n_b / NSB) & 1) ^ 1);
+            mbar_wait(b_empty(st), ((t / NSB) & 1) ^ 1);
             if (elect_one()) {
                 mbar_arrive_expect_tx(b_full(st), B_BYTES);
 #pragma unroll
@@ -499,284 +551,260 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                     tma_load_2d(smem_u32(b_smem + st * B_BYTES + kc * kSub), &tmap, kc * 64, ct * kBN, b_full(st));
             }
             __syncwarp();
-            ++n_b;
+            // cj[c] = [anchor_j] 2^(m0 - l_j)  (1-exp path),  lj[c] = l_j or +inf  (2-exp path)
+            const float lv[4] = {l_cur.x, l_cur.y, l_cur.z, l_cur.w};
+            float cv[4], l2v[4];
+            bool unsafe = false;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = ct * kBN + lane * 4 + u;
+                const bool okj = (j < p.n_k) && p.map.is_anchor(j, p.mode);
+                const float l2 = lv[u] * kLog2e;
+                const float d = m0 - l2;
+                const bool bad = okj && !(fabsf(d) <= kSafeSpread);
+                unsafe = unsafe || bad;
+                cv[u] = (okj && !bad) ? ex2(d) : 0.f;
+                l2v[u] = okj ? l2 : INFINITY;
+            }
+            float* cst = cols + st * 256;
+            *reinterpret_cast<float4*>(cst + lane * 4) = make_float4(cv[0], cv[1], cv[2], cv[3]);
+            *reinterpret_cast<float4*>(cst + 128 + lane * 4) = make_float4(l2v[0], l2v[1], l2v[2], l2v[3]);
+            const unsigned any = __any_sync(0xffffffffu, unsafe) ? 1u : 0u;
+            if (lane == 0) flags[st * 4] = any;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(b_full(st));          // second arrival: the column data is in place
+            if (++ct == p.CT) { ct = 0; ++rb; }
+            l_cur = l_n1;
+            l_n1 = l_n2;
+            l_n2 = next_pf(t + 3);
+        }
+    } else if (warp == kBwdMma1Warp) {
+        // ---------------------------------------------------- MMA1 issuer: S[t%3] = A (128 rows) x B^T (128 columns)
+        // Two issuing warps, because one warp that alternates "wait for P(t), issue MMA2(t), issue MMA1(t+3)"
+        // puts two barrier wake-ups and two blocking issue bursts in series on every tile and leaves the tensor
+        // pipe idle in between.  tcgen05 ops of different threads are not ordered, so the reuse of an S buffer
+        // is handed over explicitly: s_free[b] completes when MMA2(t), which reads P out of it, has finished.
+        constexpr uint32_t idesc1 = idesc_bf16(128, 128, 0);
+        Tracer tr(p.trace, 0);
+        int n_a = 0, ct1 = ct0;
+        const uint32_t a_lo = desc_lo(smem_u32(a_smem), 16);
+        for (int t = 0; t < n_tiles; ++t) {
+            const bool first_of_rb = (t == 0) || (ct1 == 0);
+            const bool last_of_rb = (t == n_tiles - 1) || (ct1 == p.CT - 1);
+            const int st = t % NSB, buf = t % NS;
+            tr(100);
+            if (first_of_rb) { mbar_wait(a_full, n_a & 1); ++n_a; }
+            mbar_wait(b_full(st), (t / NSB) & 1);
+            mbar_wait(s_free(buf), ((t / NS) & 1) ^ 1);
+            tc_fence_after();
+            tr(101);
+            const uint32_t d = tmem_base + buf * 128;
+            const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), 16);
+            if (elect_one()) {
+#pragma unroll
+                for (int k16 = 0; k16 < KCH * 4; ++k16) {
+                    const uint32_t off = ((k16 >> 2) * kSub + (k16 & 3) * 32) >> 4;
+                    if (k16 == 0) umma_bf16_lo<false>(d, a_lo + off, b_lo + off, idesc1);
+                    else umma_bf16_lo<true>(d, a_lo + off, b_lo + off, idesc1);
+                }
+                umma_commit(s_full(buf));
+                if (last_of_rb) umma_commit(a_empty);
+            }
+            __syncwarp();
+            tr(102);
+            if (++ct1 == p.CT) ct1 = 0;
         }
     } else if (warp == 1) {
-        if (t0 < t1) {
-            // ------------------------------------------------ MMA issuer (warp-uniform, one lane issues)
-            constexpr uint32_t idesc1 = idesc_bf16(128, 128, 0);
-            constexpr uint32_t idesc2 = idesc_bf16(128, KCH * 64, 1);
-            Tracer tr(p.trace, 0);
-            int n_a = 0, n_dz = 0;
-            const int n_tiles = t1 - t0;
-            const uint32_t a_lo0 = desc_lo(smem_u32(a_smem), 16);
-
-            // S[h] = A_h (128 rows) x B^T (128 columns) of tile i.  S[h] is known to be free: both of
-            // its warpgroups pulled it into registers before they published P[h], which the MMA2 of the
-            // previous tile waited for.
-            auto mma1 = [&](int i, int h, bool first_of_rb, bool last_of_rb) {
-                const int st = i % NSB;
-                if (h == 0) {
-                    if (first_of_rb) { mbar_wait(a_full(), n_a & 1); ++n_a; }
-                    mbar_wait(b_full(st), (i / NSB) & 1);
-                    tc_fence_after();
-                }
-                const uint32_t d = tmem_base + h * 128;
-                const uint32_t a_lo = a_lo0 + ((h * KCH * kSub) >> 4);
-                const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), 16);
-                if (elect_one()) {
+        // ---------------------------------------------------- MMA2 issuer: dK += P(t) x K_j
+        // P(t): 128 x 128 bf16 held in TMEM over S[t%3]; K_j: the tile's 128 rows read MN-major
+        constexpr uint32_t idesc2 = idesc_bf16(128, ND, 1);
+        int n_dz = 0, ct2 = ct0;
+        for (int t = 0; t < n_tiles; ++t) {
+            const bool first_of_rb = (t == 0) || (ct2 == 0);
+            const bool last_of_rb = (t == n_tiles - 1) || (ct2 == p.CT - 1);
+            const int st = t % NSB, buf = t % NS;
+            mbar_wait(p_full(buf), (t / NS) & 1);
+            if (first_of_rb) mbar_wait(dz_empty, (n_dz & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t d = tmem_base + kDkCol;
+            const uint32_t pa = tmem_base + buf * 128;
+            const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), kSub);
+            if (elect_one()) {
+                // 16 columns of P = 8 TMEM words; the warpgroup of column half h keeps its 64 columns in words
+                // h*64 .. h*64+31
+                umma_bf16_ts_dyn(d, pa, b_lo, idesc2, first_of_rb ? 0u : 1u);
 #pragma unroll
-                    for (int k16 = 0; k16 < KCH * 4; ++k16) {
-                        const uint32_t off = ((k16 >> 2) * kSub + (k16 & 3) * 32) >> 4;
-                        if (k16 == 0) umma_bf16_lo<false>(d, a_lo + off, b_lo + off, idesc1);
-                        else umma_bf16_lo<true>(d, a_lo + off, b_lo + off, idesc1);
-                    }
-                    umma_commit(s_full(h));
-                    if (h == 1 && last_of_rb) umma_commit(a_empty());
-                }
-                __syncwarp();
-            };
-            // dK[h] += P[h] (128 x 128 bf16 held in TMEM over S[h]) x K_j (128 rows read MN-major)
-            auto mma2 = [&](int i, int h, bool first_of_rb, bool last_of_rb) {
-                const int st = i % NSB;
-                tr(200 + h);
-                mbar_wait(p_full(h), i & 1);
-                if (h == 0 && first_of_rb) mbar_wait(dz_empty, (n_dz & 1) ^ 1);
-                tc_fence_after();
-                tr(210 + h);
-                const uint32_t d = tmem_base + 256 + h * 128;
-                const uint32_t pa = tmem_base + h * 128;
-                const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), kSub);
-                if (elect_one()) {
-                    umma_bf16_ts_dyn(d, pa, b_lo, idesc2, first_of_rb ? 0u : 1u);
-#pragma unroll
-                    for (int j16 = 1; j16 < 8; ++j16)      // 16 columns of P = 8 TMEM columns; column half a at +64
-                        umma_bf16_ts<true>(d, pa + (j16 >> 2) * 64 + (j16 & 3) * 8, b_lo + ((j16 * 2048) >> 4), idesc2);
-                    if (h == 1) {
-                        umma_commit(b_empty(st));
-                        if (last_of_rb) umma_commit(dz_full);
-                    }
-                }
-                __syncwarp();
-                if (h == 1 && last_of_rb) ++n_dz;
-                tr(220 + h);
-            };
-
-            // tile bookkeeping without divisions: position of the current tile inside its row block
-            int ct_cur = t0 % p.CT;
-            bool first_cur = true;
-            bool last_cur = (n_tiles == 1) || (ct_cur == p.CT - 1);
-            mma1(0, 0, first_cur, last_cur);
-            mma1(0, 1, first_cur, last_cur);
-            for (int i = 0; i < n_tiles; ++i) {
-                int ct_next = ct_cur + 1;
-                if (ct_next == p.CT) ct_next = 0;
-                const bool has_next = (i + 1 < n_tiles);
-                const bool first_next = (ct_next == 0);
-                const bool last_next = (i + 2 >= n_tiles) || (ct_next == p.CT - 1);
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    mma2(i, h, first_cur, last_cur);
-                    if (has_next) mma1(i + 1, h, first_next, last_next);
-                }
-                ct_cur = ct_next;
-                first_cur = first_next;
-                last_cur = last_next;
+                for (int j16 = 1; j16 < 8; ++j16)
+                    umma_bf16_ts<true>(d, pa + (j16 >> 2) * 64 + (j16 & 3) * 8, b_lo + ((j16 * 2048) >> 4), idesc2);
+                umma_commit(s_free(buf));
+                umma_commit(b_empty(st));
+                if (last_of_rb) umma_commit(dz_full);
             }
+            __syncwarp();
+            if (last_of_rb) ++n_dz;
+            if (++ct2 == p.CT) ct2 = 0;
         }
     } else {
         // ---------------------------------------------------- epilogue warpgroups
-        const int w = (warp - 2) >> 2;                  // warpgroup = (row half, column half)
-        const int h = w >> 1, a = w & 1;
+        // Two teams of two warpgroups take alternate tiles (team = tile parity); inside a team warpgroup
+        // `half` owns columns half*64 .. half*64+63 of the tile.  Every hand-over in a tile's chain
+        // (barrier wake-up, tcgen05.ld, tcgen05.st + wait, barrier arrive) costs 50..150 ns; with one team
+        // they add up on every tile, with two the other team's exps fill the gaps.
+        const int g = (warp - 2) >> 2;                  // warpgroup
+        const int team = g >> 1, half = g & 1;
         const int q4 = warp & 3;                        // TMEM lane quarter this warp may touch
-        const int r = q4 * 32 + lane;                   // row within the half
-        const int wtid = (warp - 2 - w * 4) * 32 + lane;
-        const int wwarp = wtid >> 5;
+        const int r = q4 * 32 + lane;                   // row within the block
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
-        float* cj = cols + w * 128;                       // [64] 1-exp column factors
-        float* lj = cj + 64;                              // [64] column log-sum-exps (log2 domain)
-        uint32_t* myflags = flags + w * 4;
-        float* myrow = rowred + w * 8;
-        const uint32_t p_taddr = tmem_base + lane_addr + w * 64;      // P words go over this thread's S columns
-        const bool mode_all = (p.mode == SCB_MODE_ALL);
-        const int bar_id = 1 + w;
 
-        int cur_rb = -1, idx = 0, li = 0, gi = 0, rep_i = 0, n_dz = 0;
-        bool row_ok = false, rb_fast = false;
-        float lse2_i = INFINITY, m0 = 0.f, R_i = 0.f, nia_i = 0.f;
-        Tracer tr(p.trace, (warp == 2) ? 1 : (warp == 10 ? 2 : -1));   // (h=0, a=0) and (h=1, a=0)
-
-        // raw log-sum-exp of the column this thread stages for a tile (threads 0..63 of the warpgroup)
-        auto load_col = [&](int ct_of_tile, bool tile_exists) -> float {
-            if (wtid >= 64 || !tile_exists) return 0.f;
-            const int j = ct_of_tile * kBN + a * 64 + wtid;
-            return (j < p.n_k) ? __ldg(p.lse_all + j) : 0.f;
-        };
-        int rb = t0 / p.CT, ct = t0 - rb * p.CT;         // advanced incrementally: no division per tile
-        float l_next = load_col(ct, t0 < t1);
+        int rb = rb0, ct = ct0, cur_rb = -1, li = 0, gi = 0, rep_i = 0, n_dz = 0;
+        bool rows_fast = false;
+        float lse2_i = INFINITY, R_i = 0.f, nia_i = 0.f;
+        Tracer tr(p.trace, (warp == 2) ? 1 : (warp == 10 ? 2 : -1));   // lane quarter 2 of teams 0 and 1
 
         // dK of a finished row block leaves TMEM as plain vector stores into this CTA's slot of the
         // partial buffer (the reduce kernel adds the slots); no float atomics on the hot path.
-        auto drain = [&](int rb) {
+        // All four warpgroups take part (32 columns each), whichever team computed the block's last tile.
+        auto drain = [&](int rb_) {
             tr(8);
             mbar_wait(dz_full, n_dz & 1);
             tr(9);
             ++n_dz;
             tc_fence_after();
-            const int slot = blockIdx.x - (rb * p.CT) / p.q;
-            // rows of this warp: q4*32 .. +32 of half h; after the transpose a store covers 128 contiguous bytes
-            float* dst_warp = p.dk_part + ((int64_t)slot * p.RB * kBM + (int64_t)rb * kBM + h * kBMH + q4 * 32) * p.ldk;
-#pragma unroll 1
-            for (int cc = 0; cc < KCH; ++cc) {              // this warpgroup's half of the dK columns
-                const int c0 = a * (KCH * 32) + cc * 32;
+            if (g * 32 < ND) {
+                const int slot = blockIdx.x - (rb_ * p.CT) / p.q;
+                // rows of this warp: q4*32 .. +32; after the transpose a store covers 128 contiguous bytes
+                float* dst = p.dk_part + ((int64_t)slot * p.RB * kBMB + (int64_t)rb_ * kBMB + q4 * 32) * p.ldk +
+                             g * 32 + lane;
                 uint32_t v[32];
-                tmem_ld32(tmem_base + lane_addr + 256 + h * 128 + c0, v);
+                tmem_ld32(tmem_base + lane_addr + kDkCol + g * 32, v);
                 tmem_ld_wait_dep(v);
                 warp_transpose32(v, lane);
-                float* dst = dst_warp + c0 + lane;
 #pragma unroll
                 for (int rr = 0; rr < 32; ++rr) dst[(int64_t)rr * p.ldk] = __uint_as_float(v[rr]);
             }
             tc_fence_before();
-            mbar_arrive(dz_empty);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(dz_empty);
             tr(10);
         };
 
-        for (int tau = t0; tau < t1; ++tau) {
-            const int ct_next = (ct + 1 == p.CT) ? 0 : ct + 1;
-            if (rb != cur_rb) {
-                if (cur_rb >= 0) drain(cur_rb);
-                cur_rb = rb;
-                li = rb * kBM + h * kBMH + r;
-                gi = p.row_begin + li;
-                row_ok = (li < p.n_rows);
-                const bool anchor_i = row_ok && p.map.is_anchor(gi, p.mode);
-                lse2_i = anchor_i ? p.lse_all[gi] * kLog2e : INFINITY;
-                if (kLabels) {
-                    rep_i = row_ok ? p.rep_row[gi] : -1;
-                    nia_i = row_ok ? p.nia_row[gi] : 0.f;
+        if (kTrace && p.trace != nullptr && warp == 2 && lane == 0 && blockIdx.x < 256) p.trace[4096 + 2 * blockIdx.x] = global_ns();
+        for (int t = 0; t < n_tiles; ++t) {
+            const bool last_of_rb = (t == n_tiles - 1) || (ct == p.CT - 1);
+            if (kTrace && t == n_tiles - 1 && p.trace != nullptr && warp == 2 && lane == 0 && blockIdx.x < 256)
+                p.trace[4096 + 2 * blockIdx.x + 1] = global_ns();      // diagnostics: last tile reached
+            if ((t & 1) == team) {
+                if (rb != cur_rb) {
+                    cur_rb = rb;
+                    li = rb * kBMB + r;
+                    gi = p.row_begin + li;
+                    const bool row_ok = (li < p.n_rows);
+                    const bool anchor_i = row_ok && p.map.is_anchor(gi, p.mode);
+                    lse2_i = anchor_i ? p.lse_all[gi] * kLog2e : INFINITY;
+                    if (kLabels) {
+                        rep_i = row_ok ? p.rep_row[gi] : -1;
+                        nia_i = row_ok ? p.nia_row[gi] : 0.f;
+                    }
+                    const float d = lse2_i - m0;
+                    const bool row_safe = anchor_i && (fabsf(d) <= kSafeSpread);
+                    R_i = row_safe ? ex2(d) : 0.f;
+                    // the 1-exp path needs every row of the warp to be an anchor with a tame log-sum-exp
+                    rows_fast = __all_sync(0xffffffffu, row_safe);
                 }
-                // warpgroup-wide range of the rows' log-sum-exps (reference point of the 1-exp path)
-                float mx = anchor_i ? lse2_i : -INFINITY, mn = anchor_i ? lse2_i : INFINITY;
-                mx = warp_max(mx);
-                mn = -warp_max(-mn);
-                named_bar_sync(bar_id, kBMH);      // previous readers of myrow are done
-                if (lane == 0) { myrow[wwarp * 2] = mx; myrow[wwarp * 2 + 1] = mn; }
-                named_bar_sync(bar_id, kBMH);
-                mx = fmaxf(fmaxf(myrow[0], myrow[2]), fmaxf(myrow[4], myrow[6]));
-                mn = fminf(fminf(myrow[1], myrow[3]), fminf(myrow[5], myrow[7]));
-                m0 = mx;
-                rb_fast = mode_all && (mx - mn <= kSafeSpread) && (mx > -INFINITY);
-                R_i = (anchor_i && rb_fast) ? ex2(lse2_i - m0) : 0.f;
-            }
-            const int j0 = ct * kBN + a * 64;             // first column of this warpgroup's sub-tile
-            // ---- per-column data of this sub-tile (threads 0..63 stage one column each):
-            //      cj[c] = [anchor_j] 2^(m0 - lse2_j)   (1-exp path),  lj[c] = lse2_j or +inf   (2-exp path)
-            tr(1);
-            named_bar_sync(bar_id, kBMH);                 // everybody is done with the previous tile's columns
-            if (wtid < 64) {
-                const int j = j0 + wtid;
-                const bool okj = (j < p.n_k) && p.map.is_anchor(j, p.mode);
-                const float l2 = l_next * kLog2e;
-                const float d = m0 - l2;
-                const bool unsafe = okj && !(fabsf(d) <= kSafeSpread);
-                cj[wtid] = (okj && !unsafe) ? ex2(d) : 0.f;
-                lj[wtid] = okj ? l2 : INFINITY;
-                const unsigned any = __any_sync(0xffffffffu, unsafe);
-                if (lane == 0) myflags[wwarp] = any;
-            }
-            named_bar_sync(bar_id, kBMH);
-            const int g_lo = p.row_begin + rb * kBM + h * kBMH;
-            const bool pred = (j0 + 64 > p.n_k) || (g_lo < j0 + 64 && j0 < g_lo + kBMH);
-            const bool fast = rb_fast && !pred && ((myflags[0] | myflags[1]) == 0u);
-
-            tr(2);
-            mbar_wait(s_full(h), idx & 1);
-            tr(3);
-            tc_fence_after();
-            if (fast) {
-                // ---------------- common case: one exp per element, fully unrolled, S released early
-                uint32_t va[32], vb[32];
-                tmem_ld32(tmem_base + lane_addr + w * 64, va);
-                tmem_ld32(tmem_base + lane_addr + w * 64 + 32, vb);
-                l_next = load_col(ct_next, tau + 1 < t1);   // global load flies during this sub-tile
-                tmem_ld_wait_dep(va);
-                tmem_ld_wait_dep(vb);
-                tr(4);
-                // 16 columns at a time: exp, weight, (label term), bf16 pack, 8 words back into TMEM
-                auto process = [&](uint32_t (&v)[32], int cc) {
+                const int st = t % NSB, buf = t % NS;
+                const int j0 = ct * kBN + half * 64;          // first column of this warpgroup's slice
+                const float* cj = cols + st * 256 + half * 64;   // 1-exp column factors
+                const float* lj = cj + 128;                   // column log-sum-exps (log2 domain) or +inf
+                const uint32_t taddr = tmem_base + lane_addr + buf * 128 + half * 64;
+                tr(1);
+                mbar_wait(b_full(st), (t / NSB) & 1);         // column data staged (the B tile itself landed long ago)
+                const bool fast = rows_fast && (flags[st * 4] == 0u) && (j0 + 64 <= p.n_k);
+                mbar_wait(s_full(buf), (t / NS) & 1);
+                tr(3);
+                tc_fence_after();
+                if (fast) {
+                    // ---------------- common case: one exp per element; two 32-column chunks, one copy of the code
+                    const int g_lo = p.row_begin + rb * kBMB + q4 * 32;   // first row of this warp
+#pragma unroll 1
+                    for (int cc = 0; cc < 2; ++cc) {
+                        uint32_t v[32];
+                        tmem_ld32(taddr + cc * 32, v);
+                        tmem_ld_wait_dep(v);
+                        if (cc == 0) tr(4);
+                        // exp, weight, (label term), (self column), bf16 pack, 16 words back into TMEM
+                        float pv[32];
 #pragma unroll
-                    for (int q2 = 0; q2 < 2; ++q2) {
-                        float pv[16];
-#pragma unroll
-                        for (int q4c = 0; q4c < 4; ++q4c) {
-                            const float4 c4 = *reinterpret_cast<const float4*>(cj + cc * 32 + q2 * 16 + q4c * 4);
-                            const float cvv[4] = {c4.x, c4.y, c4.z, c4.w};
+                        for (int c4 = 0; c4 < 8; ++c4) {
+                            const float4 c4v = *reinterpret_cast<const float4*>(cj + cc * 32 + c4 * 4);
+                            const float cvv[4] = {c4v.x, c4v.y, c4v.z, c4v.w};
 #pragma unroll
                             for (int u = 0; u < 4; ++u) {
-                                const float e = ex2(fmaf(__uint_as_float(v[q2 * 16 + q4c * 4 + u]), p.c2, -lse2_i));
-                                pv[q4c * 4 + u] = e * fmaf(R_i, cvv[u], 1.f);
+                                const float e = ex2(fmaf(__uint_as_float(v[c4 * 4 + u]), p.c2, -lse2_i));
+                                pv[c4 * 4 + u] = e * fmaf(R_i, cvv[u], 1.f);
                             }
                         }
+                        const int jc = j0 + cc * 32;
                         if (kLabels) {
-                            const int jj = j0 + cc * 32 + q2 * 16;     // fast => whole sub-tile in range
 #pragma unroll
-                            for (int q4c = 0; q4c < 4; ++q4c) {
-                                const int4 ra = __ldg(reinterpret_cast<const int4*>(p.rep_row + jj + q4c * 4));
-                                const float4 na = __ldg(reinterpret_cast<const float4*>(p.nia_row + jj + q4c * 4));
-                                if (ra.x == rep_i) pv[q4c * 4 + 0] -= nia_i + na.x;
-                                if (ra.y == rep_i) pv[q4c * 4 + 1] -= nia_i + na.y;
-                                if (ra.z == rep_i) pv[q4c * 4 + 2] -= nia_i + na.z;
-                                if (ra.w == rep_i) pv[q4c * 4 + 3] -= nia_i + na.w;
+                            for (int c4 = 0; c4 < 8; ++c4) {
+                                const int4 ra = __ldg(reinterpret_cast<const int4*>(p.rep_row + jc + c4 * 4));
+                                const float4 na = __ldg(reinterpret_cast<const float4*>(p.nia_row + jc + c4 * 4));
+                                if (ra.x == rep_i) pv[c4 * 4 + 0] -= nia_i + na.x;
+                                if (ra.y == rep_i) pv[c4 * 4 + 1] -= nia_i + na.y;
+                                if (ra.z == rep_i) pv[c4 * 4 + 2] -= nia_i + na.z;
+                                if (ra.w == rep_i) pv[c4 * 4 + 3] -= nia_i + na.w;
                             }
                         }
-                        store_p16(p_taddr + cc * 16 + q2 * 8, pv);
+                        // the self column (losses.py:74-79) only exists in slices on the diagonal: warp-uniform test
+                        if (g_lo < jc + 32 && jc < g_lo + 32) {
+                            const int c_self = gi - jc;
+#pragma unroll
+                            for (int c = 0; c < 32; ++c) pv[c] = (c == c_self) ? 0.f : pv[c];
+                        }
+                        store_p16(taddr + cc * 16, pv, 0);
+                        store_p16(taddr + cc * 16 + 8, pv, 16);
                     }
-                };
-                process(va, 0);
-                process(vb, 1);
-            } else {
-                // ---------------- rare case (self / ragged tiles, mode `one`, wild LSE ranges): two exps,
-                // sixteen columns at a time straight from TMEM, compact code
+                } else {
+                    // ---------------- rare case (ragged tiles, non-anchor rows, wild LSE ranges): two exps,
+                    // sixteen columns at a time straight from TMEM, compact code
 #pragma unroll 1
-                for (int g16 = 0; g16 < 4; ++g16) {
-                    uint32_t v8a[8], v8b[8];
-                    tmem_ld8(tmem_base + lane_addr + w * 64 + g16 * 16, v8a);
-                    tmem_ld8(tmem_base + lane_addr + w * 64 + g16 * 16 + 8, v8b);
-                    tmem_ld_wait_dep8(v8a);
-                    tmem_ld_wait_dep8(v8b);
-                    float pv[16];
+                    for (int g16 = 0; g16 < 4; ++g16) {
+                        uint32_t v8a[8], v8b[8];
+                        tmem_ld8(taddr + g16 * 16, v8a);
+                        tmem_ld8(taddr + g16 * 16 + 8, v8b);
+                        tmem_ld_wait_dep8(v8a);
+                        tmem_ld_wait_dep8(v8b);
+                        float pv[16];
 #pragma unroll
-                    for (int u = 0; u < 16; ++u) {
-                        const int c = g16 * 16 + u;
-                        const int j = j0 + c;
-                        const float x = __uint_as_float(u < 8 ? v8a[u & 7] : v8b[u & 7]);
-                        float e = ex2(fmaf(x, p.c2, -lse2_i)) + ex2(fmaf(x, p.c2, -lj[c]));   // +inf -> 0
-                        if (kLabels) {
-                            if (j < p.n_k && p.rep_row[j] == rep_i) e -= nia_i + p.nia_row[j];
+                        for (int u = 0; u < 16; ++u) {
+                            const int c = g16 * 16 + u;
+                            const int j = j0 + c;
+                            const float x = __uint_as_float(u < 8 ? v8a[u & 7] : v8b[u & 7]);
+                            float e = ex2(fmaf(x, p.c2, -lse2_i)) + ex2(fmaf(x, p.c2, -lj[c]));   // +inf -> 0
+                            if (kLabels) {
+                                if (j < p.n_k && p.rep_row[j] == rep_i) e -= nia_i + p.nia_row[j];
+                            }
+                            pv[u] = (j >= p.n_k || j == gi) ? 0.f : e;
                         }
-                        pv[u] = (j >= p.n_k || j == gi) ? 0.f : e;
+                        store_p16(taddr + g16 * 8, pv, 0);     // words [8g, 8g+8) lie inside columns already read
                     }
-                    store_p16(p_taddr + g16 * 8, pv);      // words [8g, 8g+8) lie inside columns already read
                 }
-                l_next = load_col(ct_next, tau + 1 < t1);
+                tr(6);
+                // publishing P also hands the S buffer back: every TMEM access of this thread is complete
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(p_full(buf));    // one arrival per warp: per-thread arrivals on one word serialise
+                tr(7);
             }
-            tr(6);
-            // publishing P[h] also hands S[h] back: every TMEM access of this thread is complete
-            tmem_st_wait();
-            tc_fence_before();
-            mbar_arrive(p_full(h));
-            tr(7);
-            ++idx;
-            if (ct_next == 0) ++rb;
-            ct = ct_next;
+            if (last_of_rb) drain(rb);
+            if (++ct == p.CT) { ct = 0; ++rb; }
         }
-        if (cur_rb >= 0) drain(cur_rb);
     }
 
     tc_fence_before();
     __syncthreads();
-    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[3071] = global_ns();
+    if (kTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[3071] = global_ns();
     stamp_cta(p.trace, 1);
     if (warp == 1) {
         tc_fence_after();
@@ -821,7 +849,7 @@ supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int
     pdl_launch_dependents();
     pdl_wait();
     if (warp >= n_rows) return;
-    const int rb = warp >> 8;
+    const int rb = warp >> 7;                      // 128-row blocks of the backward
     const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
     const float coef = load_scalar(grad_out, grad_dtype) * coef_scale_invT;
     const bool simclr = (mask_kind == SCB_MASK_SIMCLR) && n_views >= 2;
@@ -876,7 +904,7 @@ supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows,
     if (warp >= n_rows) return;
     const int d = lane * 4;
     const bool on = d < ldk;
-    const int rb = warp >> 8;
+    const int rb = warp >> 7;                      // 128-row blocks of the backward
     const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     if (on) {
@@ -1005,9 +1033,26 @@ static TcGeom tc_geom(int n_k, int rows) {
 
 static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
+// backward: 128-row blocks; n_split = slots of a row block = CTAs whose tile span overlaps it
+static constexpr int kMaxDkSlots = 16;
+static TcGeom tc_geom_bwd(int n_k, int rows) {
+    TcGeom g;
+    g.CT = (int)ceil_div(n_k, kBN);
+    g.RB = (int)ceil_div(rows, kBMB);
+    g.T = g.CT * g.RB;
+    int q = (int)ceil_div(g.T, sm_count());
+    const int qmin = (int)ceil_div(g.CT, kMaxDkSlots - 1);
+    if (q < qmin) q = qmin;
+    g.q = q;
+    g.grid = (int)ceil_div(g.T, q);
+    g.n_split = (int)ceil_div(g.CT, q) + 1;
+    if (g.n_split > kMaxDkSlots) g.n_split = kMaxDkSlots;
+    return g;
+}
+
 static size_t dk_part_bytes(const scb_supcon_problem* p, int n_rows) {
-    const TcGeom g = tc_geom(p->n_k, n_rows);
-    return align256((size_t)(g.n_split / 2) * g.RB * kBM * p->ldk * sizeof(float));
+    const TcGeom g = tc_geom_bwd(p->n_k, n_rows);
+    return align256((size_t)g.n_split * g.RB * kBMB * p->ldk * sizeof(float));
 }
 
 int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows) {
@@ -1096,19 +1141,19 @@ static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_ro
     if (int e = tc_supported(p)) return e;
     CUtensorMap tmap;
     if (int e = make_tmap(p, &tmap)) return e;
-    const TcGeom g = tc_geom(p->n_k, n_rows);
+    const TcGeom g = tc_geom_bwd(p->n_k, n_rows);
     TcParams t;
     fill_params(p, row_begin, n_rows, n_rows, g, workspace, &t);
     t.lse_all = lse_all; t.grad_out = grad_out;
     t.coef_scale = p->loss_scale / (float)n_anchor_total;
     if (int e = launch_label_rows(p, t, stream)) return e;
     const int kch = p->ldk / 64;
-    const size_t smem = (size_t)(2 * kch * kSub) + 4 * (kch * kSub) + 4 * 2 * 64 * 4 + 64 + 128 + 28 * 8 + 16;
+    const size_t smem = (size_t)(kch * kSub) + 5 * (kch * kSub) + 5 * 256 * 4 + (5 * 4 + 4) * 4 + 24 * 8 + 16;
     const bool lab = p->mask_kind == SCB_MASK_LABELS;
 #define SCB_LAUNCH_BWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
         if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        SCB_CUDA_OK(launch_pdl(supcon_tc_bwd_kernel<KCH_, LAB_>, dim3(g.grid), dim3(kTcThreads), smem, stream, tmap, t)); \
+        SCB_CUDA_OK(launch_pdl(supcon_tc_bwd_kernel<KCH_, LAB_>, dim3(g.grid), dim3(kBwdThreads), smem, stream, tmap, t)); \
     } while (0)
     if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
     else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
@@ -1132,7 +1177,7 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
         return e;
     prefer_max_smem_carveout(supcon_tc_reduce_dk_kernel);
     SCB_CUDA_OK(launch_pdl(supcon_tc_reduce_dk_kernel, dim3((unsigned)ceil_div((int64_t)n_rows * 32, 256)), dim3(256), 0,
-                           stream, (const float*)t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode,
+                           stream, (const float*)t.dk_part, g.RB * kBMB, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode,
                            p->mask_kind, row_begin, n_rows, grad_out, p->scalar_dtype,
                            t.coef_scale * p->inv_temperature, out_dk, ld_dk));
     count_launch();
@@ -1152,7 +1197,7 @@ int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
     SCB_DISPATCH_FLOAT(feat_dtype, TF, {
         prefer_max_smem_carveout(supcon_tc_reduce_finish_kernel<TF>);
         SCB_CUDA_OK(launch_pdl(supcon_tc_reduce_finish_kernel<TF>, dim3(blocks), dim3(256), 0, stream,
-                               (const float*)t.dk_part, g.RB * kBM, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode,
+                               (const float*)t.dk_part, g.RB * kBMB, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode,
                                p->mask_kind, row_begin, n_rows, grad_out, p->scalar_dtype,
                                t.coef_scale * p->inv_temperature, (const TF*)features, n_samples, p->dim, stride_s,
                                stride_v, normalize, inv_norm, (TF*)out, ostride_s, ostride_v));

@@ -54,8 +54,9 @@ __device__ __forceinline__ unsigned long long wall_ns() {
 // their sub-partition's issue slots with the warps that do the work, so the loop is kept as quiet as possible:
 // parked try_wait, no clock reads except once every 256 wake-ups.  (clock64() is no use here anyway: the
 // sub-partition counters fall behind while its warps are parked.)
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    if (mbar_try_wait(bar, parity)) return;
+// The slow path is kept out of line: the kernels wait in dozens of places and their code must stay inside
+// the instruction cache (a taken branch into cold code costs an L2 round trip).
+__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
     unsigned long long t0 = 0;
     for (uint32_t spins = 1;; ++spins) {
         if (mbar_try_wait_park(bar, parity, 100000u)) return;
@@ -65,6 +66,10 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             else if (now - t0 > 2000000000ull) __trap();   // 2 s
         }
     }
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    mbar_wait_slow(bar, parity);
 }
 
 // ---------------------------------------------------------------- TMA

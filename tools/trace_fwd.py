@@ -9,6 +9,7 @@ import torch.nn.functional as F
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from simclr_pytorch_distributed_b200 import _lib, losses as L   # noqa: E402
 
+_lib.LIB_PATH = os.environ.get('SCB_LIB') or os.path.join(os.path.dirname(os.path.abspath(__file__)), 'bin', 'libtrace.so')   # tools/build_trace_lib.sh
 lib = _lib.load()
 dev = torch.device('cuda')
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
@@ -28,6 +29,8 @@ for _ in range(200):
     _a @ _a
 torch.cuda.synchronize()
 trace = torch.zeros(5 * 1024, dtype=torch.int64, device=dev)
+if os.environ.get('QUIET'):
+    trace[4095] = 1          # per-CTA entry / exit stamps only
 lib.scb_debug_set_trace(trace.data_ptr())
 L.launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
 torch.cuda.synchronize()
