@@ -272,10 +272,14 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             dst[3 * (int64_t)p.n_rows] = np;
         };
 
-        for (int tau = t0; tau < t1; ++tau) {
-            const int rb = tau / p.CT, ct = tau - rb * p.CT;
-            if (rb != cur_rb) {
+        // incremental tile bookkeeping (no division per tile); one copy of the flush and of the chunk code:
+        // the code between two tiles is latency-bound scalar work and has to stay short and cache-resident
+        int rb = t0 / p.CT, ct = t0 - rb * p.CT;
+        for (int tau = t0;; ++tau) {
+            const bool more = tau < t1;
+            if (!more || rb != cur_rb) {
                 if (cur_rb >= 0) flush(cur_rb);
+                if (!more) break;
                 cur_rb = rb;
                 m = -INFINITY; sum = 0.f; possum = 0.f;
                 li = rb * kBM + wg * kBMH + r;
@@ -367,23 +371,23 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                     }
                 }
             };
-            // both 32-column chunks are pulled out of TMEM at once, then S[wg][sbuf] is handed back
-            uint32_t va[32], vb[32];
-            tmem_ld32(taddr, va);
-            tmem_ld32(taddr + 32, vb);
-            tmem_ld_wait_dep(va);
-            tmem_ld_wait_dep(vb);
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(s_empty(wg, sbuf));      // S buffer is free for the next MMA (one arrival per warp:
-                                                                // 32 per-thread arrivals on one barrier word serialise)
-            process(va, 0);
-            process(vb, 1);
+#pragma unroll 1
+            for (int cc = 0; cc < 2; ++cc) {
+                uint32_t v[32];
+                tmem_ld32(taddr + cc * 32, v);
+                tmem_ld_wait_dep(v);
+                if (cc == 1) {
+                    // every column of S[wg][sbuf] this thread needs is in registers: hand the buffer back
+                    // (one arrival per warp: 32 per-thread arrivals on one barrier word serialise)
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(s_empty(wg, sbuf));
+                }
+                process(v, cc);
+            }
             ++idx;
+            if (++ct == p.CT) { ct = 0; ++rb; }
         }
-        if (threadIdx.x == 64) stamp(5);
-        if (cur_rb >= 0) flush(cur_rb);
-        if (threadIdx.x == 64) stamp(6);
     }
 
     tc_fence_before();
@@ -689,11 +693,21 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         };
 
         if (kTrace && p.trace != nullptr && warp == 2 && lane == 0 && blockIdx.x < 256) p.trace[4096 + 2 * blockIdx.x] = global_ns();
-        for (int t = 0; t < n_tiles; ++t) {
-            const bool last_of_rb = (t == n_tiles - 1) || (ct == p.CT - 1);
-            if (kTrace && t == n_tiles - 1 && p.trace != nullptr && warp == 2 && lane == 0 && blockIdx.x < 256)
+        // The team walks its own tiles (t = team, team + 2, ...).  All bookkeeping is incremental: the code
+        // between two tiles is a chain of dependent scalar instructions, and every one of them is latency.
+        int st = team, bpar = 0, buf = team, spar = 0;      // B stage / S buffer of tile t and their phase parities
+        ct = ct0 + team;
+        while (ct >= p.CT) { ct -= p.CT; ++rb; }
+        int next_drain = rb0;                               // row blocks are drained in order, by all sixteen warps
+        const int rb_end = (t0 + n_tiles - 1) / p.CT + 1;
+        for (int t = team;; t += 2) {
+            const bool more = t < n_tiles;
+            const int rb_target = more ? rb : rb_end;       // every block before this tile's (at the end: all of them)
+            while (next_drain < rb_target) drain(next_drain++);
+            if (!more) break;
+            if (kTrace && t >= n_tiles - 2 && p.trace != nullptr && warp == 2 && lane == 0 && blockIdx.x < 256)
                 p.trace[4096 + 2 * blockIdx.x + 1] = global_ns();      // diagnostics: last tile reached
-            if ((t & 1) == team) {
+            {
                 if (rb != cur_rb) {
                     cur_rb = rb;
                     li = rb * kBMB + r;
@@ -711,13 +725,16 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                     // the 1-exp path needs every row of the warp to be an anchor with a tame log-sum-exp
                     rows_fast = __all_sync(0xffffffffu, row_safe);
                 }
-                const int st = t % NSB, buf = t % NS;
                 const int j0 = ct * kBN + half * 64;          // first column of this warpgroup's slice
                 const float* cj = cols + st * 256 + half * 64;   // 1-exp column factors
                 const float* lj = cj + 128;                   // column log-sum-exps (log2 domain) or +inf
                 const uint32_t taddr = tmem_base + lane_addr + buf * 128 + half * 64;
                 tr(1);
-                mbar_wait(b_full(st), (t / NSB) & 1);         // column data staged (the B tile itself landed long ago)
+                // S(t) ready implies the tile's column data is in place: MMA1(t) was issued after its b_full
+                // completed (B tile + the producer warp's column stores), so no second wait here
+                mbar_wait(s_full(buf), spar);
+                tr(3);
+                tc_fence_after();
                 const bool fast = rows_fast && (flags[st * 4] == 0u) && (j0 + 64 <= p.n_k);
                 mbar_wait(s_full(buf), (t / NS) & 1);
                 tr(3);
@@ -797,9 +814,14 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 if (lane == 0) mbar_arrive(p_full(buf));    // one arrival per warp: per-thread arrivals on one word serialise
                 tr(7);
             }
-            if (last_of_rb) drain(rb);
-            if (++ct == p.CT) { ct = 0; ++rb; }
+            ct += 2;
+            while (ct >= p.CT) { ct -= p.CT; ++rb; }
+            st += 2;
+            if (st >= NSB) { st -= NSB; bpar ^= 1; }
+            buf += 2;
+            if (buf >= NS) { buf -= NS; spar ^= 1; }
         }
+        (void)bpar;
     }
 
     tc_fence_before();
