@@ -72,7 +72,16 @@ int scb_debug_set_trace(void* device_buffer);
  *      row = q*(n_views*seg) + v*seg + b        sample id = q*seg + b
  * With n_seg == 1 this is exactly the reference's `cat(unbind(features, 1))` (losses.py:53).
  * Anchors are all rows (`all`) or the v == 0 rows (`one`), losses.py:54-59.
+ *
+ * row_layout = SCB_ROWS_SAMPLE_MAJOR keeps the samples' own order inside a segment instead,
+ *      row = q*(n_views*seg) + b*n_views + v    sample id = q*seg + b
+ * which is the memory order of a contiguous `features[bsz, n_views, dim]`: a bf16 feature tensor can then
+ * be handed over as K without the stacking copy (the loss is a sum over anchors, so the order of the rows
+ * changes nothing but the order of floating-point additions).  `all` mode only.
  */
+#define SCB_ROWS_VIEW_MAJOR 0
+#define SCB_ROWS_SAMPLE_MAJOR 1
+
 typedef struct scb_supcon_problem {
     const void* k;          /* [n_k, ldk] contrast matrix, dtype k_dtype (F32 for ENGINE_FP32, BF16 else) */
     const void* k_lo;       /* ENGINE_BF16X3 only: low-order halves, same shape (k ~= k + k_lo)   */
@@ -92,6 +101,7 @@ typedef struct scb_supcon_problem {
                                out_loss[1] (forward) and of *grad_out (backward)                   */
     float inv_temperature;  /* 1/T                  losses.py:64-66                               */
     float loss_scale;       /* T / base_temperature losses.py:90                                  */
+    int32_t row_layout;     /* SCB_ROWS_*                                                         */
 } scb_supcon_problem;
 
 /* Replaces main_supcon.py:283 (`F.normalize`, optional) + losses.py:52-53 (view-major stacking)

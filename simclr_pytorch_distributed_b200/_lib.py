@@ -26,6 +26,7 @@ F32, BF16, F16 = 0, 1, 2
 MASK_SIMCLR, MASK_LABELS, MASK_EXPLICIT = 0, 1, 2
 MODE_ALL, MODE_ONE = 0, 1
 ENGINE_FP32, ENGINE_BF16, ENGINE_BF16X3 = 0, 1, 2
+ROWS_VIEW_MAJOR, ROWS_SAMPLE_MAJOR = 0, 1
 BN_RELU = 1
 BN_NOALLOC_MAX_CHANNELS = 4096      # SCB_BN_NOALLOC_MAX_CHANNELS
 
@@ -89,7 +90,7 @@ class SupconProblem(ctypes.Structure):
         ('ldk', ctypes.c_int32), ('n_views', ctypes.c_int32), ('seg', ctypes.c_int32),
         ('n_seg', ctypes.c_int32), ('mask_kind', ctypes.c_int32), ('mode', ctypes.c_int32),
         ('engine', ctypes.c_int32), ('scalar_dtype', ctypes.c_int32), ('inv_temperature', ctypes.c_float),
-        ('loss_scale', ctypes.c_float),
+        ('loss_scale', ctypes.c_float), ('row_layout', ctypes.c_int32),
     ]
 
 

@@ -53,6 +53,8 @@ static int fp32_splits(int n_rows, int n_k) {
 static int check_problem(const scb_supcon_problem* p, int row_begin, int n_rows) {
     SCB_REQUIRE(p != nullptr && p->k != nullptr, "supcon: null problem / k");
     SCB_REQUIRE(p->n_views >= 1 && p->seg >= 1 && p->n_seg >= 1, "supcon: bad V/seg/n_seg");
+    SCB_REQUIRE(p->row_layout == SCB_ROWS_VIEW_MAJOR || (p->row_layout == SCB_ROWS_SAMPLE_MAJOR && p->mode == SCB_MODE_ALL),
+                "supcon: row_layout must be SCB_ROWS_VIEW_MAJOR, or SCB_ROWS_SAMPLE_MAJOR with mode `all`");
     SCB_REQUIRE((int64_t)p->n_k == (int64_t)p->n_views * p->seg * p->n_seg,
                 "supcon: n_k (%d) != n_seg*n_views*seg", p->n_k);
     SCB_REQUIRE(p->dim >= 1 && p->ldk >= p->dim, "supcon: bad dim/ldk");

@@ -4,20 +4,33 @@
 
 namespace scb {
 
-// row = q*(V*seg) + v*seg + b ; sample id = q*seg + b   (include/simclr_b200.h, "Row order")
+// view-major:   row = q*(V*seg) + v*seg + b     sample-major: row = q*(V*seg) + b*V + v
+// sample id = q*seg + b in both                                  (include/simclr_b200.h, "Row order")
 struct RowMap {
     int vseg;   // V * seg
     int seg;
+    int nv;     // V
+    int il;     // 1 = sample-major (views of a sample interleaved)
     __host__ __device__ static RowMap of(const scb_supcon_problem* p) {
-        RowMap m; m.vseg = p->n_views * p->seg; m.seg = p->seg; return m;
+        RowMap m; m.vseg = p->n_views * p->seg; m.seg = p->seg; m.nv = p->n_views;
+        m.il = (p->row_layout == SCB_ROWS_SAMPLE_MAJOR) ? 1 : 0; return m;
     }
     __device__ __forceinline__ int sid(int row) const {
         const int q = row / vseg, rem = row - q * vseg;
-        return q * seg + rem % seg;
+        return q * seg + (il ? rem / nv : rem % seg);
+    }
+    __device__ __forceinline__ int view_of(int row) const {
+        const int rem = row % vseg;
+        return il ? rem % nv : rem / seg;
+    }
+    // the row that holds view vv of the same sample
+    __device__ __forceinline__ int sibling(int row, int vv) const {
+        const int v = view_of(row);
+        return il ? row + (vv - v) : row + (vv - v) * seg;
     }
     // anchors: every row (`all`) or the view-0 rows (`one`)            losses.py:54-59
     __device__ __forceinline__ bool is_anchor(int row, int mode) const {
-        return mode == SCB_MODE_ALL || (row % vseg) < seg;
+        return mode == SCB_MODE_ALL || view_of(row) == 0;
     }
 };
 

@@ -256,12 +256,11 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 if (slot == 0) np = 1.f;
             } else if (slot == 0) {
                 // more than two views: the other views of the same sample, as dot products
-                const int base = (gi / p.map.vseg) * p.map.vseg, rem = gi - base;
-                const int v = rem / p.map.seg, b = rem - v * p.map.seg;
+                const int v = p.map.view_of(gi);
                 for (int vv = 0; vv < p.n_views; ++vv)
                     if (vv != v)
                         ps += bf16_dot_rows(p.k + (int64_t)gi * p.ldk,
-                                            p.k + (int64_t)(base + vv * p.map.seg + b) * p.ldk, p.ldk);
+                                            p.k + (int64_t)p.map.sibling(gi, vv) * p.ldk, p.ldk);
                 ps *= p.inv_T;
                 np = (float)(p.n_views - 1);
             }
@@ -287,10 +286,7 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 if (kLabels) rep_i = (gi < p.n_k) ? p.rep_row[gi] : -1;
                 if (capture) {
                     pj = -1;
-                    if (gi < p.n_k) {
-                        const int rem = gi % p.map.vseg;
-                        pj = rem < p.map.seg ? gi + p.map.seg : gi - p.map.seg;
-                    }
+                    if (gi < p.n_k) pj = p.map.sibling(gi, 1 - p.map.view_of(gi));
                     int lo = pj < 0 ? 0x7fffffff : pj, hi = pj;
 #pragma unroll
                     for (int o = 16; o >= 1; o >>= 1) {
@@ -876,8 +872,7 @@ supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int
     const float coef = load_scalar(grad_out, grad_dtype) * coef_scale_invT;
     const bool simclr = (mask_kind == SCB_MASK_SIMCLR) && n_views >= 2;
     const int gi = row_begin + warp;
-    const int base = (gi / map.vseg) * map.vseg, rem = gi - base;
-    const int v = rem / map.seg, b = rem - v * map.seg;
+    const int v = map.view_of(gi);
     const float ai = map.is_anchor(gi, mode) ? 1.f : 0.f;
     const float cpos = -1.f / (float)(n_views > 1 ? n_views - 1 : 1);
     float* dst = out_dk + (int64_t)warp * ld_dk;
@@ -896,7 +891,7 @@ supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int
         if (simclr) {
             for (int vv = 0; vv < n_views; ++vv) {
                 if (vv == v) continue;
-                const int j = base + vv * map.seg + b;
+                const int j = map.sibling(gi, vv);
                 const float wgt = cpos * (ai + (map.is_anchor(j, mode) ? 1.f : 0.f));
                 const uint2 raw = *reinterpret_cast<const uint2*>(k + (int64_t)j * ldk + d);
                 const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
@@ -942,13 +937,12 @@ supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows,
         }
         if (mask_kind == SCB_MASK_SIMCLR && n_views >= 2) {
             const int gi = row_begin + warp;
-            const int base = (gi / map.vseg) * map.vseg, rem = gi - base;
-            const int v = rem / map.seg, b = rem - v * map.seg;
+            const int v = map.view_of(gi);
             const float ai = map.is_anchor(gi, mode) ? 1.f : 0.f;
             const float cpos = -1.f / (float)(n_views - 1);
             for (int vv = 0; vv < n_views; ++vv) {
                 if (vv == v) continue;
-                const int j = base + vv * map.seg + b;
+                const int j = map.sibling(gi, vv);
                 const float wgt = cpos * (ai + (map.is_anchor(j, mode) ? 1.f : 0.f));
                 const uint2 raw = *reinterpret_cast<const uint2*>(k + (int64_t)j * ldk + d);
                 const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
@@ -961,8 +955,9 @@ supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows,
     const float coef = load_scalar(grad_out, grad_dtype) * coef_scale_invT;
 #pragma unroll
     for (int i = 0; i < 4; ++i) acc[i] *= coef;
-    // local row = v*n_samples + b  ->  features[b, v, :]
-    const int v_l = warp / n_samples, b_l = warp - v_l * n_samples;
+    // local row = v*n_samples + b (view-major) or b*n_views + v (sample-major)  ->  features[b, v, :]
+    const int v_l = map.il ? warp % n_views : warp / n_samples;
+    const int b_l = map.il ? warp / n_views : warp - v_l * n_samples;
     const TF* src = feat + (int64_t)b_l * stride_s + (int64_t)v_l * stride_v;
     TF* dst = out + (int64_t)b_l * ostride_s + (int64_t)v_l * ostride_v;
     if (normalize) {

@@ -75,6 +75,7 @@ class LossPlan:
         self.row_begin = seg_index * self.rows_local
         self.n_anchor_total = self.n_k if mode == _lib.MODE_ALL else n_seg * n_local
         self.scalar_dtype = _lib.F32          # dtype of the loss / upstream-gradient scalars (set by the caller)
+        self.row_layout = _lib.ROWS_VIEW_MAJOR
         if engine == _lib.ENGINE_FP32:
             self.k_dtype, self.k_torch, self.ldk = _lib.F32, torch.float32, _round_up(dim, 4)
         else:
@@ -91,6 +92,7 @@ def _problem(plan, k, k_lo, labels, mask, temperature, base_temperature):
     p.n_views, p.seg, p.n_seg = plan.n_views, plan.n_local, plan.n_seg
     p.mask_kind, p.mode, p.engine = plan.mask_kind, plan.mode, plan.engine
     p.scalar_dtype = plan.scalar_dtype
+    p.row_layout = plan.row_layout
     p.inv_temperature = 1.0 / temperature
     p.loss_scale = temperature / base_temperature
     return p
@@ -174,12 +176,21 @@ class _SupConFunction(torch.autograd.Function):
         dev = feats.device
         with torch.cuda.device(dev):
             n_k, ldk = plan.n_k, plan.ldk
-            k = torch.empty((n_k, ldk), dtype=plan.k_torch, device=dev)
+            # bf16 features that are already laid out as [bsz * n_views, ldk] need neither the stacking copy
+            # (losses.py:53) nor a cast: the kernels take the rows in the samples' own order
+            zero_copy = (plan.engine == _lib.ENGINE_BF16 and feats.dtype == torch.bfloat16 and not normalize and
+                         plan.mode == _lib.MODE_ALL and plan.n_seg == 1 and feats.is_contiguous() and
+                         plan.dim == ldk and feats.data_ptr() % 16 == 0)
+            plan.row_layout = _lib.ROWS_SAMPLE_MAJOR if zero_copy else _lib.ROWS_VIEW_MAJOR
+            k = None if zero_copy else torch.empty((n_k, ldk), dtype=plan.k_torch, device=dev)
             k_lo = torch.empty_like(k) if plan.engine == _lib.ENGINE_BF16X3 else None
             stats = torch.empty((4, n_k), dtype=torch.float32, device=dev)   # lse, possum, npos, inv_norm
             loss = torch.empty(2, dtype=torch.float32, device=dev)     # [fp32 value, value in feats.dtype]
             inv_norm = stats[3] if normalize else None
-            launch_prep(lib, feats, plan, normalize, k, k_lo, inv_norm)
+            if zero_copy:
+                k = feats.view(n_k, ldk)            # the feature tensor IS the contrast matrix (sample-major rows)
+            else:
+                launch_prep(lib, feats, plan, normalize, k, k_lo, inv_norm)
             prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
             launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
         ctx.plan, ctx.prob_args = plan, (temperature, base_temperature, normalize)

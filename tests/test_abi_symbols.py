@@ -52,6 +52,7 @@ def test_problem_struct_layout_matches_header():
     assert _lib.SupconProblem.k_dtype.offset == 32
     assert _lib.SupconProblem.scalar_dtype.offset == 72
     assert _lib.SupconProblem.inv_temperature.offset == 76
+    assert _lib.SupconProblem.row_layout.offset == 84
 
 
 def test_no_gpu_calls_fail_loudly_not_silently(lib):
