@@ -111,6 +111,7 @@ PROTOTYPES = {
     'scb_supcon_backward_features': (_i, [_pp, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i64, _i64, _i, _vp, _vp, _i64,
                                           _i64, _vp, _i64, _vp]),
     'scb_supcon_finish': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _i64, _i64, _vp]),
+    'scb_peer_bcast': (_i, [_vp, _vp, _i, _vp, _i, _vp]),
     'scb_bn_workspace_bytes': (_i64, [_i]),
     'scb_bn_stats': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i64, _vp]),
     'scb_bn_stats_noalloc': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp]),

@@ -353,6 +353,29 @@ supcon_bwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, R
     }
 }
 
+// ------------------------------------------------------------------ peer-memory broadcast
+struct PeerBcastArgs {
+    char* dst[16];
+    long long src_off[4], dst_off[4], bytes[4];
+    int n_dst, n_seg;
+};
+
+__global__ void __launch_bounds__(256)
+peer_bcast_kernel(const char* __restrict__ src, const PeerBcastArgs a) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (int s = 0; s < a.n_seg; ++s) {
+        const char* from = src + a.src_off[s];
+        for (long long i = tid * 16; i < a.bytes[s]; i += stride * 16) {
+            const uint4 v = *reinterpret_cast<const uint4*>(from + i);
+            for (int w = 0; w < a.n_dst; ++w) *reinterpret_cast<uint4*>(a.dst[w] + a.dst_off[s] + i) = v;
+        }
+    }
+    __threadfence_system();      // the writes are on their way to the peers before the grid retires
+}
+
 // ------------------------------------------------------------------ host side
 int fp32_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* part, int n_split,
                  cudaStream_t stream) {
@@ -439,6 +462,37 @@ extern "C" int scb_supcon_finish(const float* dk, int ld_dk, const void* feature
                                (const TF*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize,
                                inv_norm, (TF*)out_dfeatures, out_stride_sample, out_stride_view));
     });
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_peer_bcast(const void* src, const int64_t* seg, int n_seg, const void* const* dst_ptrs, int n_dst,
+                              void* stream_) {
+    SCB_REQUIRE(src && seg && dst_ptrs, "peer_bcast: null pointer");
+    SCB_REQUIRE(n_seg >= 1 && n_seg <= 4 && n_dst >= 1 && n_dst <= 16, "peer_bcast: 1..4 segments, 1..16 destinations");
+    PeerBcastArgs a;
+    a.n_dst = n_dst;
+    a.n_seg = n_seg;
+    long long total = 0;
+    for (int s = 0; s < n_seg; ++s) {
+        a.src_off[s] = seg[3 * s]; a.dst_off[s] = seg[3 * s + 1]; a.bytes[s] = seg[3 * s + 2];
+        SCB_REQUIRE(a.src_off[s] >= 0 && a.dst_off[s] >= 0 && a.bytes[s] >= 0 &&
+                    ((a.src_off[s] | a.dst_off[s] | a.bytes[s]) & 15) == 0,
+                    "peer_bcast: offsets and sizes must be non-negative multiples of 16");
+        total += a.bytes[s];
+    }
+    SCB_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15u) == 0, "peer_bcast: src must be 16-byte aligned");
+    for (int w = 0; w < n_dst; ++w) {
+        SCB_REQUIRE(dst_ptrs[w] && (reinterpret_cast<uintptr_t>(dst_ptrs[w]) & 15u) == 0,
+                    "peer_bcast: destinations must be non-null and 16-byte aligned");
+        a.dst[w] = (char*)const_cast<void*>(dst_ptrs[w]);
+    }
+    if (total == 0) return SCB_OK;
+    long long blocks = ceil_div(total / 16, 256);
+    if (blocks > 4 * sm_count()) blocks = 4 * sm_count();
+    if (blocks < 1) blocks = 1;
+    SCB_CUDA_OK(launch_pdl(peer_bcast_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream_,
+                           (const char*)src, a));
     count_launch();
     return SCB_OK;
 }

@@ -19,6 +19,10 @@ The loss is invariant under a consistent re-ordering of the samples, so this mat
 """
 from __future__ import annotations
 
+import ctypes
+import os
+import warnings
+
 import torch
 import torch.distributed as dist
 import torch.nn as nn
@@ -54,6 +58,84 @@ def _all_gather_flat(out, inp, group):
         dist.all_gather(parts, inp.reshape(-1), group=group)
 
 
+class _PeerExchange:
+    """The two exchanges of the sharded loss over peer memory instead of NCCL.
+
+    Every rank owns symmetric-memory buffers (torch.distributed._symmetric_memory: plumbing only) that its
+    peers map over NVLink.  An exchange is ONE kernel of this library (`scb_peer_bcast`) that stores the
+    rank's slice straight into every peer's buffer, followed by the handle's cross-rank stream barrier;
+    an NCCL all-gather of these few hundred kilobytes costs several times the transfer in latency.
+
+    Buffers rotate through GENERATIONS copies: a rank may only overwrite its peers' copy g once they are
+    done reading it, and the barrier of the generations in between guarantees that (each forward is
+    followed in stream order by its backward).  A backward that finds its generation re-used raises.
+    """
+    GENERATIONS = 4
+    _cache = {}
+    _failed = False
+
+    def __init__(self, group, dev, n_k, ldk, k_dtype, rows, world, rank):
+        import torch.distributed._symmetric_memory as symm
+        self.world, self.rank, self.rows, self.n_k, self.ldk = world, rank, rows, n_k, ldk
+        self.k_bufs, self.st_bufs, self.k_ptrs, self.st_ptrs, self.handles = [], [], [], [], []
+        self.st_len = 2 * n_k + 4 * world                      # [lse(n_k) | npos(n_k) | loss share per rank, padded to 4]
+        for _ in range(self.GENERATIONS):
+            kb = symm.empty((n_k, ldk), dtype=k_dtype, device=dev)
+            kh = symm.rendezvous(kb, group)
+            sb = symm.empty((self.st_len,), dtype=torch.float32, device=dev)
+            sh = symm.rendezvous(sb, group)
+            self.k_bufs.append(kb)
+            self.st_bufs.append(sb)
+            self.k_ptrs.append((ctypes.c_void_p * world)(*[int(p) for p in kh.buffer_ptrs]))
+            self.st_ptrs.append((ctypes.c_void_p * world)(*[int(p) for p in sh.buffer_ptrs]))
+            self.handles.append((kh, sh))
+        self.calls = 0
+        esz = kb.element_size()
+        self.k_seg = (ctypes.c_int64 * 3)(0, rank * rows * ldk * esz, rows * ldk * esz)
+        self.st_seg = (ctypes.c_int64 * 9)(0, rank * rows * 4, rows * 4,
+                                           rows * 4, (n_k + rank * rows) * 4, rows * 4,
+                                           2 * rows * 4, (2 * n_k + 4 * rank) * 4, 16)
+
+    @classmethod
+    def get(cls, group, dev, n_k, ldk, k_dtype, rows, world, rank):
+        """The exchange for this problem shape, or None when peer memory is not to be used."""
+        if cls._failed or os.environ.get('SCB_P2P', '1') == '0' or dist.get_backend(group) != 'nccl' or world > 16:
+            return None
+        if (rows * ldk * torch.empty((), dtype=k_dtype).element_size()) % 16 or (rows * 4) % 16:
+            return None
+        key = (id(group), dev.index, n_k, ldk, k_dtype, rows, world)
+        if key not in cls._cache:
+            try:
+                cls._cache[key] = cls(group, dev, n_k, ldk, k_dtype, rows, world, rank)
+            except Exception as e:       # no symmetric memory on this system: every rank fails alike -> NCCL
+                cls._failed = True
+                warnings.warn('peer-memory exchange unavailable (%s); using NCCL all-gather' % (e,))
+                return None
+        return cls._cache[key]
+
+    def next_generation(self):
+        g = self.calls % self.GENERATIONS
+        self.calls += 1
+        return g, self.calls
+
+    def check_alive(self, call_index):
+        if self.calls - call_index >= self.GENERATIONS:
+            raise RuntimeError('DistributedSupConLoss: backward of a forward that is more than %d calls old '
+                               '(its gathered embeddings were recycled)' % (self.GENERATIONS - 1))
+
+    def _bcast(self, lib, src, seg, n_seg, ptrs, handle, dev):
+        _lib.check(lib.scb_peer_bcast(src.data_ptr(), seg, n_seg, ptrs, self.world, L._stream(dev)), 'scb_peer_bcast')
+        handle.barrier(channel=0)
+
+    def share_rows(self, lib, g, k_local, dev):
+        self._bcast(lib, k_local, self.k_seg, 1, self.k_ptrs[g], self.handles[g][0], dev)
+        return self.k_bufs[g]
+
+    def share_stats(self, lib, g, packed, dev):
+        self._bcast(lib, packed, self.st_seg, 3, self.st_ptrs[g], self.handles[g][1], dev)
+        return self.st_bufs[g]
+
+
 class _DistSupConFunction(torch.autograd.Function):
 
     @staticmethod
@@ -66,18 +148,30 @@ class _DistSupConFunction(torch.autograd.Function):
         k_local = torch.empty((rows, ldk), dtype=plan.k_torch, device=dev)
         inv_norm = torch.empty(rows, dtype=torch.float32, device=dev) if normalize else None
         ops.prep(lib, feats, plan, normalize, k_local, None, inv_norm)
-        k_all = torch.empty((n_k, ldk), dtype=plan.k_torch, device=dev)
-        _all_gather_flat(k_all, k_local, group)                                  # exchange 1: embeddings
+        px = (_PeerExchange.get(group, dev, n_k, ldk, plan.k_torch, rows, world, plan.seg_index)
+              if ops.requires_cuda else None)
+        gen, call_index = px.next_generation() if px is not None else (0, 0)
+        if px is not None:
+            k_all = px.share_rows(lib, gen, k_local, dev)                        # exchange 1 over peer memory
+        else:
+            k_all = torch.empty((n_k, ldk), dtype=plan.k_torch, device=dev)
+            _all_gather_flat(k_all, k_local, group)                              # exchange 1: embeddings
         # local row statistics: [lse(rows) | npos(rows) | loss share, 3 pad]
         packed = torch.empty(2 * rows + 4, dtype=torch.float32, device=dev)
         possum = torch.empty(rows, dtype=torch.float32, device=dev)
         prob = L._problem(plan, k_all, None, labels_all, None, temperature, base_temperature)
         ops.forward(lib, prob, plan, packed[0:rows], possum, packed[rows:2 * rows], packed[2 * rows:2 * rows + 1], dev)
-        gathered = torch.empty((world, 2 * rows + 4), dtype=torch.float32, device=dev)
-        _all_gather_flat(gathered, packed, group)                               # exchange 2: row statistics
-        lse_all = gathered[:, 0:rows].contiguous().view(-1)
-        npos_all = gathered[:, rows:2 * rows].contiguous().view(-1)
-        loss = gathered[:, 2 * rows].sum()           # every rank's share of mean_i loss_i (losses.py:91)
+        if px is not None:
+            st = px.share_stats(lib, gen, packed, dev)                           # exchange 2 over peer memory
+            lse_all, npos_all = st[0:n_k], st[n_k:2 * n_k]
+            loss = st[2 * n_k:2 * n_k + 4 * world:4].sum()
+        else:
+            gathered = torch.empty((world, 2 * rows + 4), dtype=torch.float32, device=dev)
+            _all_gather_flat(gathered, packed, group)                           # exchange 2: row statistics
+            lse_all = gathered[:, 0:rows].contiguous().view(-1)
+            npos_all = gathered[:, rows:2 * rows].contiguous().view(-1)
+            loss = gathered[:, 2 * rows].sum()       # every rank's share of mean_i loss_i (losses.py:91)
+        ctx.px, ctx.call_index = px, call_index
         ctx.plan, ctx.args = plan, (temperature, base_temperature, normalize)
         ctx.save_for_backward(feats, labels_all, k_all, lse_all, npos_all, inv_norm)
         return loss.to(feats.dtype) if feats.dtype != torch.float32 else loss
@@ -87,6 +181,8 @@ class _DistSupConFunction(torch.autograd.Function):
         ops = OPS
         lib = ops.lib()
         feats, labels_all, k_all, lse_all, npos_all, inv_norm = ctx.saved_tensors
+        if ctx.px is not None:
+            ctx.px.check_alive(ctx.call_index)
         plan = ctx.plan
         temperature, base_temperature, normalize = ctx.args
         dev = feats.device

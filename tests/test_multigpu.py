@@ -68,28 +68,36 @@ def _worker(rank, world, port, q):
             ok = ok and e_y <= tol and e_x <= tol and e_rv <= 1e-5 and e_rm <= 1e-5 and e_gw <= 1e-3
         # ---------------- row-sharded loss vs oracle on the concatenated batch
         bsz, V, D = 96, 2, 128
-        for engine, dtype, tol in (('fp32', torch.float32, 1e-4), ('bf16', torch.bfloat16, 2e-3 + 2 ** -8)):
-            rng = np.random.default_rng(99)
-            z_all = rng.standard_normal((world * bsz, V, D)) * 2.0 + 0.3          # raw (un-normalised) outputs
-            z_all = torch.from_numpy(z_all).to(dtype)
-            sl = slice(rank * bsz, (rank + 1) * bsz)
-            f = z_all[sl].to(dev).requires_grad_(True)
-            crit = DistributedSupConLoss(temperature=0.5, engine=engine, normalize=True)
-            loss = crit(f)
-            loss.backward()
-            raw = z_all.double().numpy()
-            zh = normalize_rows(raw)
-            if engine == 'bf16':       # operands are the bf16-rounded normalised rows
-                zh_used = torch.from_numpy(zh).to(torch.bfloat16).double().numpy()
-            else:
-                zh_used = zh
-            ref_loss, g_hat, _ = supcon_forward_backward(zh_used, temperature=0.5)
-            ref_grad = normalize_rows_backward(raw, g_hat)[sl]
-            e_l = abs(float(loss) - ref_loss) / abs(ref_loss)
-            got = f.grad.double().cpu().numpy()
-            e_g = np.linalg.norm((got - ref_grad).ravel()) / np.linalg.norm(ref_grad.ravel())
-            notes.append('loss %s: rel loss %.2e rel grad %.2e' % (engine, e_l, e_g))
-            ok = ok and e_l <= tol and e_g <= 2 * tol
+        from simclr_pytorch_distributed_b200 import gather as G
+        # both exchange paths: peer memory (default) and NCCL all-gather (SCB_P2P=0), several steps each so
+        # that the rotating peer buffers are re-used
+        for engine, dtype, tol, p2p in (('fp32', torch.float32, 1e-4, '1'), ('bf16', torch.bfloat16, 2e-3 + 2 ** -8, '1'),
+                                        ('bf16', torch.bfloat16, 2e-3 + 2 ** -8, '0')):
+            os.environ['SCB_P2P'] = p2p
+            for step in range(6 if p2p == '1' else 1):
+                rng = np.random.default_rng(99 + step)
+                z_all = rng.standard_normal((world * bsz, V, D)) * 2.0 + 0.3          # raw (un-normalised) outputs
+                z_all = torch.from_numpy(z_all).to(dtype)
+                sl = slice(rank * bsz, (rank + 1) * bsz)
+                f = z_all[sl].to(dev).requires_grad_(True)
+                crit = DistributedSupConLoss(temperature=0.5, engine=engine, normalize=True)
+                loss = crit(f)
+                loss.backward()
+                raw = z_all.double().numpy()
+                zh = normalize_rows(raw)
+                if engine == 'bf16':       # operands are the bf16-rounded normalised rows
+                    zh_used = torch.from_numpy(zh).to(torch.bfloat16).double().numpy()
+                else:
+                    zh_used = zh
+                ref_loss, g_hat, _ = supcon_forward_backward(zh_used, temperature=0.5)
+                ref_grad = normalize_rows_backward(raw, g_hat)[sl]
+                e_l = abs(float(loss) - ref_loss) / abs(ref_loss)
+                got = f.grad.double().cpu().numpy()
+                e_g = np.linalg.norm((got - ref_grad).ravel()) / np.linalg.norm(ref_grad.ravel())
+                used = 'peer memory' if (p2p == '1' and not G._PeerExchange._failed) else 'nccl'
+                if step == 0:
+                    notes.append('loss %s via %s: rel loss %.2e rel grad %.2e' % (engine, used, e_l, e_g))
+                ok = ok and e_l <= tol and e_g <= 2 * tol
     except Exception as e:     # report instead of hanging the other ranks
         ok = False
         notes.append('EXC %r' % (e,))
