@@ -65,17 +65,6 @@ int64_t scb_launch_count(void);
  * with (event id, SM clock) pairs per role (0 MMA issuer, 1/2 epilogue warpgroups); NULL = off */
 int scb_debug_set_trace(void* device_buffer);
 
-/* Peer-memory exchange of the row-sharded loss (replaces the `gather_from_all` / all_gather calls of
- * main_supcon.py:268-279 on one NVLink/NVSwitch box).  Copies up to 4 byte ranges of `src` into EVERY
- * destination buffer (the caller's own and its peers', mapped into this process with symmetric / IPC
- * memory): segment s copies seg[3s+2] bytes from src + seg[3s] to dst_ptrs[w] + seg[3s+1] for all w.
- * Offsets and sizes are multiples of 16 bytes.  `seg` and `dst_ptrs` are HOST arrays read during the
- * call.  The stores travel over NVLink as plain 16-byte writes; the caller orders them against the peers'
- * reads with a cross-rank stream barrier after this kernel (gather.py uses the symmetric-memory
- * handle's barrier).  n_dst <= 16. */
-int scb_peer_bcast(const void* src, const int64_t* seg, int n_seg, const void* const* dst_ptrs, int n_dst,
-                   void* stream);
-
 /* ======================================================================== path 1: the loss
  *
  * Row order.  The contrast matrix K holds one embedding per row.  Rows are grouped in
@@ -176,6 +165,57 @@ int scb_supcon_backward_features(const scb_supcon_problem* p, int row_begin, int
                                  const float* inv_norm, void* out_dfeatures, int64_t out_stride_sample,
                                  int64_t out_stride_view, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ---- fused exchanges of the row-sharded loss over peer memory (NVLink / NVSwitch) ------------------
+ * Replace the two all-gathers around the loss (`gather_from_all`, main_supcon.py:268-279, and the
+ * exchange of the per-row statistics the sharded backward needs) by stores issued from the PRODUCING
+ * kernels themselves: the kernel that computes a rank's slice writes it into every rank's copy of the
+ * gathered buffer (its own and its peers', mapped with symmetric / IPC memory), and its last CTA then
+ * raises a flag in every rank's flag array.  The consumer side is scb_peer_wait, a one-warp kernel that
+ * blocks the stream until the flags of all ranks show the current exchange.
+ *
+ * Flags hold exchange counters: `state` (local, 2 words, zeroed once) carries this rank's CTA ticket
+ * and counter; every rank must issue the same sequence of exchanges on a channel.  Nothing here is
+ * baked into launch parameters, so the calls can be captured in CUDA graphs.  The caller rotates >= 2
+ * generations of destination buffers (a rank can run at most one exchange ahead of its slowest peer). */
+typedef struct scb_peer_channel {
+    void* dst[16];        /* destination buffers, index = rank (dst[my_rank] is the local copy)          */
+    uint32_t* flag[16];   /* flag[w] = address, in rank w's flag array, of the word that belongs to THIS
+                             rank (rank w's scb_peer_wait reads its own array)                          */
+    uint32_t* state;      /* local scratch: [0] CTA ticket (self re-arming), [1] exchange counter        */
+    int32_t n_dst;        /* world size W <= 16                                                          */
+} scb_peer_channel;
+
+/* scb_supcon_prep whose output rows [v*n_samples + b] go to row (row_offset + that) of EVERY
+ * ch->dst[w] ([n_k, ldk] matrices of dtype k_dtype), followed by the flag signal. */
+int scb_supcon_prep_peers(const void* features, int feat_dtype, int n_samples, int n_views, int dim,
+                          int64_t stride_sample, int64_t stride_view, int normalize, float eps,
+                          const scb_peer_channel* ch, int64_t row_offset, int k_dtype, int ldk,
+                          float* out_inv_norm, void* stream);
+
+/* scb_supcon_forward whose per-row results go to every rank: ch->dst[w] is a float array
+ * [lse (n_k) | npos (n_k) | loss share of rank r at 2*n_k + 4*r], filled at this rank's rows / slot.
+ * out_possum stays local. */
+int scb_supcon_forward_peers(const scb_supcon_problem* p, int row_begin, int n_rows, int n_anchor_total,
+                             float* out_possum, const scb_peer_channel* ch, void* workspace,
+                             int64_t workspace_bytes, void* stream);
+
+/* Blocks the stream until flags_local[w] >= state[1] for w < n (all ranks have delivered the current
+ * exchange of this channel).  If loss_shares != NULL it then adds the n values loss_shares[4*w] into
+ * out_loss[0] (float) and out_loss[1] (same value in scalar_dtype, low-order bytes). */
+int scb_peer_wait(const uint32_t* flags_local, const uint32_t* state, int n, const float* loss_shares,
+                  float* out_loss, int scalar_dtype, void* stream);
+
+/* Peer-memory exchange of the row-sharded loss (replaces the `gather_from_all` / all_gather calls of
+ * main_supcon.py:268-279 on one NVLink/NVSwitch box).  Copies up to 4 byte ranges of `src` into EVERY
+ * destination buffer (the caller's own and its peers', mapped into this process with symmetric / IPC
+ * memory): segment s copies seg[3s+2] bytes from src + seg[3s] to dst_ptrs[w] + seg[3s+1] for all w.
+ * Offsets and sizes are multiples of 16 bytes.  `seg` and `dst_ptrs` are HOST arrays read during the
+ * call.  The stores travel over NVLink as plain 16-byte writes; the caller orders them against the peers'
+ * reads with a cross-rank stream barrier after this kernel (gather.py uses the symmetric-memory
+ * handle's barrier).  n_dst <= 16. */
+int scb_peer_bcast(const void* src, const int64_t* seg, int n_seg, const void* const* dst_ptrs, int n_dst,
+                   void* stream);
+
 /* ================================================================== path 2: SyncBatchNorm
  *
  * Layout: x is [outer, C, inner] with element strides (stride_outer, 1*inner... ) described by
@@ -263,3 +303,5 @@ int scb_bn_backward_fused(const void* dy, const void* x, void* dx, int dtype, in
 }
 #endif
 #endif /* SIMCLR_B200_H_ */
+
+

@@ -81,6 +81,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB_PATH
 
 
+class PeerChannel(ctypes.Structure):
+    """`scb_peer_channel` of include/simclr_b200.h."""
+    _fields_ = [('dst', ctypes.c_void_p * 16), ('flag', ctypes.c_void_p * 16), ('state', ctypes.c_void_p),
+                ('n_dst', ctypes.c_int32)]
+
+
 class SupconProblem(ctypes.Structure):
     """`scb_supcon_problem` of include/simclr_b200.h."""
     _fields_ = [
@@ -112,6 +118,9 @@ PROTOTYPES = {
                                           _i64, _vp, _i64, _vp]),
     'scb_supcon_finish': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _i64, _i64, _vp]),
     'scb_peer_bcast': (_i, [_vp, _vp, _i, _vp, _i, _vp]),
+    'scb_supcon_prep_peers': (_i, [_vp, _i, _i, _i, _i, _i64, _i64, _i, _f, _vp, _i64, _i, _i, _vp, _vp]),
+    'scb_supcon_forward_peers': (_i, [_pp, _i, _i, _i, _vp, _vp, _vp, _i64, _vp]),
+    'scb_peer_wait': (_i, [_vp, _vp, _i, _vp, _vp, _i, _vp]),
     'scb_bn_workspace_bytes': (_i64, [_i]),
     'scb_bn_stats': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i64, _vp]),
     'scb_bn_stats_noalloc': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp]),

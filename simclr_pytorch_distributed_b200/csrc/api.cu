@@ -127,6 +127,30 @@ extern "C" int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, in
                            out_possum, out_npos, out_loss_sum, workspace, stream);
 }
 
+extern "C" int scb_supcon_forward_peers(const scb_supcon_problem* p, int row_begin, int n_rows, int n_anchor_total,
+                                        float* out_possum, const scb_peer_channel* ch, void* workspace,
+                                        int64_t workspace_bytes, void* stream_) {
+    if (int e = check_problem(p, row_begin, n_rows)) return e;
+    SCB_REQUIRE(out_possum && workspace && ch && ch->state, "supcon_forward_peers: null pointer");
+    SCB_REQUIRE(ch->n_dst == p->n_seg && row_begin % n_rows == 0 && (int64_t)n_rows * p->n_seg == p->n_k,
+                "supcon_forward_peers: one destination per segment, every rank holding n_k / n_seg rows");
+    for (int w = 0; w < ch->n_dst; ++w)
+        SCB_REQUIRE(ch->dst[w] && ch->flag[w], "supcon_forward_peers: destination %d is null", w);
+    SCB_REQUIRE(n_anchor_total >= 1, "supcon_forward_peers: n_anchor_total must be >= 1");
+    SCB_REQUIRE(workspace_bytes >= scb_supcon_workspace_bytes(p, n_rows), "supcon_forward_peers: workspace too small");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    float* part = (float*)((char*)workspace + kFinScratchBytes);
+    int n_split = 1, flat_q = 0, flat_ct = 0;
+    if (p->engine == SCB_ENGINE_FP32) {
+        n_split = fp32_splits(n_rows, p->n_k);
+        if (int e = fp32_forward(p, row_begin, n_rows, part, n_split, stream)) return e;
+    } else {
+        if (int e = tc_forward(p, row_begin, n_rows, part, &n_split, &flat_q, &flat_ct, stream)) return e;
+    }
+    return launch_finalize(p, part, n_split, flat_q, flat_ct, row_begin, n_rows, 1.0 / (double)n_anchor_total, nullptr,
+                           out_possum, nullptr, nullptr, workspace, stream, ch);
+}
+
 extern "C" int scb_supcon_backward(const scb_supcon_problem* p, int row_begin, int n_rows,
                                    const float* lse_all, const float* npos_all, const float* grad_out,
                                    int n_anchor_total, float* out_dk, int ld_dk, void* workspace,

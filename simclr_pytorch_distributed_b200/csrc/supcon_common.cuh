@@ -34,6 +34,44 @@ struct RowMap {
     }
 };
 
+// ---- peer-memory exchange (include/simclr_b200.h, scb_peer_channel)
+struct PeerOut {
+    char* dst[16];
+    unsigned* flag[16];
+    unsigned* state;     // [0] ticket, [1] exchange counter
+    int n_dst;           // 0: no peers, plain local output
+    __host__ static PeerOut none() { PeerOut o; o.n_dst = 0; o.state = nullptr; return o; }
+    __host__ static PeerOut of(const scb_peer_channel* ch) {
+        PeerOut o;
+        o.n_dst = ch->n_dst;
+        o.state = ch->state;
+        for (int w = 0; w < 16; ++w) {
+            o.dst[w] = w < ch->n_dst ? (char*)ch->dst[w] : nullptr;
+            o.flag[w] = w < ch->n_dst ? ch->flag[w] : nullptr;
+        }
+        return o;
+    }
+};
+
+// Called by every thread at the end of a producing kernel (after its last store to the peers).  The last
+// CTA to arrive bumps the exchange counter and raises this rank's flag on every rank.  Ordering: each
+// CTA fences its remote stores at system scope before taking the ticket; the flag stores are releases.
+__device__ __forceinline__ void peer_signal(const PeerOut& po) {
+    __syncthreads();                 // the CTA's stores happen-before thread 0's fence (fences are cumulative):
+    if (threadIdx.x == 0) {          // one system-scope fence per CTA instead of one per thread
+        __threadfence_system();
+        const unsigned total = gridDim.x * gridDim.y * gridDim.z;
+        if (atomicAdd(po.state, 1u) == total - 1) {
+            po.state[0] = 0u;
+            const unsigned e = po.state[1] + 1u;
+            po.state[1] = e;
+            __threadfence_system();
+            for (int w = 0; w < po.n_dst; ++w)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(po.flag[w]), "r"(e) : "memory");
+        }
+    }
+}
+
 // base mask m[sid_i, sid_j] before the self-contrast column is removed      losses.py:39-50
 struct MaskSpec {
     const int64_t* labels;
@@ -60,7 +98,7 @@ int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const 
 // flat_q > 0: tensor-core engine, row block rb (256 rows) owns slots of the CTAs overlapping its tiles
 int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int flat_q, int flat_ct,
                     int row_begin, int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
-                    float* out_loss_sum, void* scratch, cudaStream_t stream);
+                    float* out_loss_sum, void* scratch, cudaStream_t stream, const scb_peer_channel* ch = nullptr);
 constexpr int kFinScratchBytes = 4096;   // ticket + per-CTA partial sums of the finalize kernel
 
 }  // namespace scb

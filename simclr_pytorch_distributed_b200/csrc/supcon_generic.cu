@@ -11,16 +11,50 @@ namespace scb {
 
 // ------------------------------------------------------------------ prep (normalise + stack + cast)
 template <typename TI, typename TO>
+__device__ __forceinline__ void prep_row_impl(const TI* __restrict__ feat, int n_samples, int dim, int64_t stride_s,
+                                              int64_t stride_v, int normalize, float eps, TO* __restrict__ out_k,
+                                              __nv_bfloat16* __restrict__ out_lo, int ldk,
+                                              float* __restrict__ out_inv_norm, int warp, int lane);
+template <typename TI, typename TO>
+__device__ __forceinline__ void prep_row(const TI* __restrict__ feat, int n_samples, int dim, int64_t stride_s,
+                                         int64_t stride_v, int normalize, float eps, TO* __restrict__ out_k,
+                                         __nv_bfloat16* __restrict__ out_lo, int ldk, float* __restrict__ out_inv_norm,
+                                         int warp, int lane) {
+    prep_row_impl<TI, TO>(feat, n_samples, dim, stride_s, stride_v, normalize, eps, out_k, out_lo, ldk, out_inv_norm,
+                          warp, lane);
+}
+
+template <typename TI, typename TO>
 __global__ void __launch_bounds__(256)
 supcon_prep_kernel(const TI* __restrict__ feat, int n_samples, int n_views, int dim,
                    int64_t stride_s, int64_t stride_v, int normalize, float eps,
                    TO* __restrict__ out_k, __nv_bfloat16* __restrict__ out_lo, int ldk,
-                   float* __restrict__ out_inv_norm) {
+                   float* __restrict__ out_inv_norm, const PeerOut po, int64_t row_offset) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const int n_rows = n_samples * n_views;
     pdl_launch_dependents();
     pdl_wait();
+    if (po.n_dst > 0) {
+        // peer variant: the row goes to every rank's copy of the gathered matrix, then the flags are raised
+        // (grid-stride over the rows: the CTA ticket of peer_signal must stay a few hundred atomics)
+        const int n_warps = (gridDim.x * blockDim.x) >> 5;
+        for (int row = warp; row < n_rows; row += n_warps)
+            for (int w = 0; w < po.n_dst; ++w)
+                prep_row<TI, TO>(feat, n_samples, dim, stride_s, stride_v, normalize, eps,
+                                 reinterpret_cast<TO*>(po.dst[w]) + row_offset * ldk, nullptr, ldk,
+                                 w == 0 ? out_inv_norm : nullptr, row, lane);
+        peer_signal(po);
+        return;
+    }
     if (warp >= n_rows) return;
+    prep_row<TI, TO>(feat, n_samples, dim, stride_s, stride_v, normalize, eps, out_k, out_lo, ldk, out_inv_norm, warp, lane);
+}
+
+template <typename TI, typename TO>
+__device__ __forceinline__ void prep_row_impl(const TI* __restrict__ feat, int n_samples, int dim, int64_t stride_s,
+                                              int64_t stride_v, int normalize, float eps, TO* __restrict__ out_k,
+                                              __nv_bfloat16* __restrict__ out_lo, int ldk,
+                                              float* __restrict__ out_inv_norm, int warp, int lane) {
     const int v = warp / n_samples, b = warp - v * n_samples;     // out row = v*n_samples + b
     const TI* src = feat + (int64_t)b * stride_s + (int64_t)v * stride_v;
     TO* dst = out_k + (int64_t)warp * ldk;
@@ -154,7 +188,8 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
                        RowMap map, int mode, float loss_scale, double inv_anchors,
                        float* __restrict__ out_lse,
                        float* __restrict__ out_possum, float* __restrict__ out_npos,
-                       float* __restrict__ out_loss_sum, void* scratch, int scalar_dtype) {
+                       float* __restrict__ out_loss_sum, void* scratch, int scalar_dtype, const PeerOut po,
+                       int n_k, int my_slot) {
     __shared__ double red[32];
     __shared__ unsigned s_last;
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
@@ -202,7 +237,17 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
             lse = m + logf(sum);
             local += (double)(-loss_scale * (ps / np - lse));        // losses.py:87,90 (0/0 -> nan)
         }
-        out_lse[r] = lse; out_possum[r] = ps; out_npos[r] = np;
+        out_possum[r] = ps;
+        if (po.n_dst > 0) {
+            // every rank's [lse (n_k) | npos (n_k) | loss shares] array gets this rank's rows
+            for (int w = 0; w < po.n_dst; ++w) {
+                float* d = reinterpret_cast<float*>(po.dst[w]);
+                d[row_begin + r] = lse;
+                d[n_k + row_begin + r] = np;
+            }
+        } else {
+            out_lse[r] = lse; out_npos[r] = np;
+        }
     }
     for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = local;
@@ -228,13 +273,24 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
         if (threadIdx.x == 0) {
             const float loss = (float)(t * inv_anchors);
-            out_loss_sum[0] = loss;
-            out_loss_sum[1] = 0.f;                 // [1]: the loss in the caller's scalar dtype (low-order bytes)
-            if (scalar_dtype == SCB_BF16) *reinterpret_cast<__nv_bfloat16*>(out_loss_sum + 1) = __float2bfloat16_rn(loss);
-            else if (scalar_dtype == SCB_F16) *reinterpret_cast<__half*>(out_loss_sum + 1) = __float2half_rn(loss);
-            else out_loss_sum[1] = loss;
+            if (po.n_dst > 0) {
+                // this rank's share of the global mean goes to every rank; scb_peer_wait adds them up
+                for (int w = 0; w < po.n_dst; ++w) reinterpret_cast<float*>(po.dst[w])[2 * n_k + 4 * my_slot] = loss;
+            } else {
+                out_loss_sum[0] = loss;
+                out_loss_sum[1] = 0.f;             // [1]: the loss in the caller's scalar dtype (low-order bytes)
+                if (scalar_dtype == SCB_BF16) *reinterpret_cast<__nv_bfloat16*>(out_loss_sum + 1) = __float2bfloat16_rn(loss);
+                else if (scalar_dtype == SCB_F16) *reinterpret_cast<__half*>(out_loss_sum + 1) = __float2half_rn(loss);
+                else out_loss_sum[1] = loss;
+            }
             *ticket = 0u;
         }
+    }
+    if (po.n_dst > 0) {
+        // The loss share is written by the last CTA of the ticket above, which is not necessarily the last
+        // CTA to reach peer_signal: order it with the same fence + ticket pattern (peer_signal fences every
+        // CTA's stores, and the signalling CTA is the last to take ITS ticket).
+        peer_signal(po);
     }
 }
 
@@ -353,6 +409,39 @@ supcon_bwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, R
     }
 }
 
+// ------------------------------------------------------------------ consumer side of a peer exchange
+__global__ void __launch_bounds__(32)
+peer_wait_kernel(const unsigned* __restrict__ flags, const unsigned* __restrict__ state, int n,
+                 const float* __restrict__ loss_shares, float* __restrict__ out_loss, int scalar_dtype) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const unsigned want = state[1];               // bumped by this rank's own producer, earlier in the stream
+    if ((int)threadIdx.x < n) {
+        unsigned long long t0 = 0;
+        for (unsigned spins = 1;; ++spins) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+            if ((int)(v - want) >= 0) break;
+            if ((spins & 1023u) == 0u) {              // a peer that died must not hang this GPU for ever
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 30000000000ull) __trap();   // 30 s
+            }
+        }
+    }
+    __syncwarp();
+    if (loss_shares != nullptr && threadIdx.x == 0) {
+        float loss = 0.f;
+        for (int w = 0; w < n; ++w) loss += __ldcg(loss_shares + 4 * w);      // fixed order: identical on all ranks
+        out_loss[0] = loss;
+        out_loss[1] = 0.f;
+        if (scalar_dtype == SCB_BF16) *reinterpret_cast<__nv_bfloat16*>(out_loss + 1) = __float2bfloat16_rn(loss);
+        else if (scalar_dtype == SCB_F16) *reinterpret_cast<__half*>(out_loss + 1) = __float2half_rn(loss);
+        else out_loss[1] = loss;
+    }
+}
+
 // ------------------------------------------------------------------ peer-memory broadcast
 struct PeerBcastArgs {
     char* dst[16];
@@ -373,7 +462,6 @@ peer_bcast_kernel(const char* __restrict__ src, const PeerBcastArgs a) {
             for (int w = 0; w < a.n_dst; ++w) *reinterpret_cast<uint4*>(a.dst[w] + a.dst_off[s] + i) = v;
         }
     }
-    __threadfence_system();      // the writes are on their way to the peers before the grid retires
 }
 
 // ------------------------------------------------------------------ host side
@@ -403,13 +491,15 @@ int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const 
 
 int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int flat_q, int flat_ct,
                     int row_begin, int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
-                    float* out_loss_sum, void* scratch, cudaStream_t stream) {
+                    float* out_loss_sum, void* scratch, cudaStream_t stream, const scb_peer_channel* ch) {
     int ctas = (int)ceil_div(n_rows, kFinThreads);
     if (ctas > kFinMaxCtas) ctas = kFinMaxCtas;
     prefer_max_smem_carveout(supcon_finalize_kernel);
+    const PeerOut po = ch ? PeerOut::of(ch) : PeerOut::none();
+    const int my_slot = row_begin / n_rows;          // rank: every rank holds n_rows consecutive rows
     SCB_CUDA_OK(launch_pdl(supcon_finalize_kernel, dim3(ctas), dim3(kFinThreads), 0, stream, part, n_split, flat_q,
                            flat_ct, n_rows, row_begin, RowMap::of(p), p->mode, p->loss_scale, inv_anchors, out_lse,
-                           out_possum, out_npos, out_loss_sum, scratch, p->scalar_dtype));
+                           out_possum, out_npos, out_loss_sum, scratch, p->scalar_dtype, po, p->n_k, my_slot));
     count_launch();
     return SCB_OK;
 }
@@ -435,11 +525,13 @@ extern "C" int scb_supcon_prep(const void* features, int feat_dtype, int n_sampl
         if (k_dtype == SCB_F32)
             SCB_CUDA_OK(launch_pdl(supcon_prep_kernel<TI, float>, dim3(blocks), dim3(256), 0, stream,
                                    (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize,
-                                   eps, (float*)out_k, (__nv_bfloat16*)nullptr, ldk, out_inv_norm));
+                                   eps, (float*)out_k, (__nv_bfloat16*)nullptr, ldk, out_inv_norm, PeerOut::none(),
+                                   (int64_t)0));
         else
             SCB_CUDA_OK(launch_pdl(supcon_prep_kernel<TI, __nv_bfloat16>, dim3(blocks), dim3(256), 0, stream,
                                    (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize,
-                                   eps, (__nv_bfloat16*)out_k, (__nv_bfloat16*)out_k_lo, ldk, out_inv_norm));
+                                   eps, (__nv_bfloat16*)out_k, (__nv_bfloat16*)out_k_lo, ldk, out_inv_norm,
+                                   PeerOut::none(), (int64_t)0));
     });
     count_launch();
     return SCB_OK;
@@ -493,6 +585,52 @@ extern "C" int scb_peer_bcast(const void* src, const int64_t* seg, int n_seg, co
     if (blocks < 1) blocks = 1;
     SCB_CUDA_OK(launch_pdl(peer_bcast_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream_,
                            (const char*)src, a));
+    count_launch();
+    return SCB_OK;
+}
+
+static int check_channel(const scb_peer_channel* ch) {
+    SCB_REQUIRE(ch && ch->state && ch->n_dst >= 1 && ch->n_dst <= 16, "peer channel: needs state and 1..16 destinations");
+    for (int w = 0; w < ch->n_dst; ++w)
+        SCB_REQUIRE(ch->dst[w] && ch->flag[w] && (reinterpret_cast<uintptr_t>(ch->dst[w]) & 15u) == 0,
+                    "peer channel: destination %d is null or not 16-byte aligned", w);
+    return SCB_OK;
+}
+
+extern "C" int scb_supcon_prep_peers(const void* features, int feat_dtype, int n_samples, int n_views, int dim,
+                                     int64_t stride_sample, int64_t stride_view, int normalize, float eps,
+                                     const scb_peer_channel* ch, int64_t row_offset, int k_dtype, int ldk,
+                                     float* out_inv_norm, void* stream_) {
+    SCB_REQUIRE(features, "supcon_prep_peers: null pointer");
+    if (int e = check_channel(ch)) return e;
+    SCB_REQUIRE(n_samples > 0 && n_views > 0 && dim > 0 && ldk >= dim && row_offset >= 0, "supcon_prep_peers: bad shape");
+    SCB_REQUIRE(k_dtype == SCB_F32 || k_dtype == SCB_BF16, "supcon_prep_peers: k_dtype must be F32 or BF16");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int64_t rows = (int64_t)n_samples * n_views;
+    unsigned blocks = (unsigned)ceil_div(rows * 32, 256);
+    if (blocks > 4u * (unsigned)sm_count()) blocks = 4u * (unsigned)sm_count();
+    const PeerOut po = PeerOut::of(ch);
+    SCB_DISPATCH_FLOAT(feat_dtype, TI, {
+        if (k_dtype == SCB_F32)
+            SCB_CUDA_OK(launch_pdl(supcon_prep_kernel<TI, float>, dim3(blocks), dim3(256), 0, stream,
+                                   (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize,
+                                   eps, (float*)nullptr, (__nv_bfloat16*)nullptr, ldk, out_inv_norm, po, row_offset));
+        else
+            SCB_CUDA_OK(launch_pdl(supcon_prep_kernel<TI, __nv_bfloat16>, dim3(blocks), dim3(256), 0, stream,
+                                   (const TI*)features, n_samples, n_views, dim, stride_sample, stride_view, normalize,
+                                   eps, (__nv_bfloat16*)nullptr, (__nv_bfloat16*)nullptr, ldk, out_inv_norm, po,
+                                   row_offset));
+    });
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_peer_wait(const uint32_t* flags_local, const uint32_t* state, int n, const float* loss_shares,
+                             float* out_loss, int scalar_dtype, void* stream_) {
+    SCB_REQUIRE(flags_local && state && n >= 1 && n <= 16, "peer_wait: needs flags, state and 1..16 ranks");
+    SCB_REQUIRE(loss_shares == nullptr || out_loss != nullptr, "peer_wait: loss_shares needs out_loss");
+    SCB_CUDA_OK(launch_pdl(peer_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream_, (const unsigned*)flags_local,
+                           (const unsigned*)state, n, loss_shares, out_loss, scalar_dtype));
     count_launch();
     return SCB_OK;
 }

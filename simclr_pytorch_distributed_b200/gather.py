@@ -62,9 +62,12 @@ class _PeerExchange:
     """The two exchanges of the sharded loss over peer memory instead of NCCL.
 
     Every rank owns symmetric-memory buffers (torch.distributed._symmetric_memory: plumbing only) that its
-    peers map over NVLink.  An exchange is ONE kernel of this library (`scb_peer_bcast`) that stores the
-    rank's slice straight into every peer's buffer, followed by the handle's cross-rank stream barrier;
-    an NCCL all-gather of these few hundred kilobytes costs several times the transfer in latency.
+    peers map over NVLink.  Default: one kernel of this library (`scb_peer_bcast`) stores the rank's slice
+    straight into every rank's buffer, followed by the handle's cross-rank stream barrier (8 us per exchange at
+    2 GPUs against 12-18 us for the NCCL all-gather of the same few hundred kilobytes).  SCB_P2P=fused moves
+    the stores into the PRODUCING kernels, which then raise per-rank flags (`scb_supcon_prep_peers`,
+    `scb_supcon_forward_peers`, consumer side `scb_peer_wait`); it is correct but measured slower so far
+    (15 us per exchange: flag latency at system scope), so it is not the default.  SCB_P2P=0: NCCL all-gathers.
 
     Buffers rotate through GENERATIONS copies: a rank may only overwrite its peers' copy g once they are
     done reading it, and the barrier of the generations in between guarantees that (each forward is
@@ -89,6 +92,27 @@ class _PeerExchange:
             self.k_ptrs.append((ctypes.c_void_p * world)(*[int(p) for p in kh.buffer_ptrs]))
             self.st_ptrs.append((ctypes.c_void_p * world)(*[int(p) for p in sh.buffer_ptrs]))
             self.handles.append((kh, sh))
+        # fused mode: flag words [2 channels][16 ranks] in symmetric memory, local ticket/counter per channel
+        fl = symm.empty((32,), dtype=torch.int32, device=dev)
+        fl.zero_()
+        fh = symm.rendezvous(fl, group)
+        torch.cuda.synchronize(dev)
+        fh.barrier(channel=0)                 # nobody raises a flag before everybody has cleared its own
+        torch.cuda.synchronize(dev)
+        self.flags, self.flags_handle = fl, fh
+        self.state = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.channels = []                    # [generation][channel] -> scb_peer_channel
+        for g in range(self.GENERATIONS):
+            pair = []
+            for c, ptrs in ((0, self.k_ptrs[g]), (1, self.st_ptrs[g])):
+                ch = _lib.PeerChannel()
+                for w in range(world):
+                    ch.dst[w] = ptrs[w]
+                    ch.flag[w] = int(fh.buffer_ptrs[w]) + (c * 16 + rank) * 4
+                ch.state = self.state.data_ptr() + c * 8
+                ch.n_dst = world
+                pair.append(ch)
+            self.channels.append(pair)
         self.calls = 0
         esz = kb.element_size()
         self.k_seg = (ctypes.c_int64 * 3)(0, rank * rows * ldk * esz, rows * ldk * esz)
@@ -127,6 +151,11 @@ class _PeerExchange:
         _lib.check(lib.scb_peer_bcast(src.data_ptr(), seg, n_seg, ptrs, self.world, L._stream(dev)), 'scb_peer_bcast')
         handle.barrier(channel=0)
 
+    def wait(self, lib, channel, dev, loss_shares=None, out_loss=None, scalar_dtype=0):
+        """Consumer side of a fused exchange: the stream blocks until every rank's flag shows it."""
+        _lib.check(lib.scb_peer_wait(self.flags.data_ptr() + channel * 64, self.state.data_ptr() + channel * 8,
+                                     self.world, loss_shares, out_loss, scalar_dtype, L._stream(dev)), 'scb_peer_wait')
+
     def share_rows(self, lib, g, k_local, dev):
         self._bcast(lib, k_local, self.k_seg, 1, self.k_ptrs[g], self.handles[g][0], dev)
         return self.k_bufs[g]
@@ -145,12 +174,38 @@ class _DistSupConFunction(torch.autograd.Function):
         dev = feats.device
         rows, n_k, ldk = plan.rows_local, plan.n_k, plan.ldk
         world = plan.n_seg
-        k_local = torch.empty((rows, ldk), dtype=plan.k_torch, device=dev)
         inv_norm = torch.empty(rows, dtype=torch.float32, device=dev) if normalize else None
-        ops.prep(lib, feats, plan, normalize, k_local, None, inv_norm)
         px = (_PeerExchange.get(group, dev, n_k, ldk, plan.k_torch, rows, world, plan.seg_index)
               if ops.requires_cuda else None)
         gen, call_index = px.next_generation() if px is not None else (0, 0)
+        fused = px is not None and os.environ.get('SCB_P2P', '1') == 'fused'
+        possum = torch.empty(rows, dtype=torch.float32, device=dev)
+        if fused:
+            # exchange 1: the prep kernel stores this rank's rows into every rank's gathered matrix
+            _lib.check(lib.scb_supcon_prep_peers(
+                feats.data_ptr(), _lib.dtype_code(feats.dtype), plan.n_local, plan.n_views, plan.dim,
+                feats.stride(0), feats.stride(1), int(normalize), 1e-12, ctypes.byref(px.channels[gen][0]),
+                plan.row_begin, plan.k_dtype, ldk, inv_norm.data_ptr() if inv_norm is not None else None,
+                L._stream(dev)), 'scb_supcon_prep_peers')
+            px.wait(lib, 0, dev)
+            k_all = px.k_bufs[gen]
+            prob = L._problem(plan, k_all, None, labels_all, None, temperature, base_temperature)
+            # exchange 2: the finalize kernel stores (lse, npos, loss share) into every rank's statistics array
+            need = lib.scb_supcon_workspace_bytes(ctypes.byref(prob), rows)
+            ws = L._Workspace.get(dev, need)
+            _lib.check(lib.scb_supcon_forward_peers(
+                ctypes.byref(prob), plan.row_begin, rows, plan.n_anchor_total, possum.data_ptr(),
+                ctypes.byref(px.channels[gen][1]), ws.data_ptr(), ws.numel(), L._stream(dev)), 'scb_supcon_forward_peers')
+            st = px.st_bufs[gen]
+            loss2 = torch.empty(2, dtype=torch.float32, device=dev)
+            px.wait(lib, 1, dev, st.data_ptr() + 2 * n_k * 4, loss2.data_ptr(), plan.scalar_dtype)
+            lse_all, npos_all = st[0:n_k], st[n_k:2 * n_k]
+            ctx.px, ctx.call_index = px, call_index
+            ctx.plan, ctx.args = plan, (temperature, base_temperature, normalize)
+            ctx.save_for_backward(feats, labels_all, k_all, lse_all, npos_all, inv_norm)
+            return L.typed_loss(loss2, feats.dtype)
+        k_local = torch.empty((rows, ldk), dtype=plan.k_torch, device=dev)
+        ops.prep(lib, feats, plan, normalize, k_local, None, inv_norm)
         if px is not None:
             k_all = px.share_rows(lib, gen, k_local, dev)                        # exchange 1 over peer memory
         else:
@@ -158,7 +213,6 @@ class _DistSupConFunction(torch.autograd.Function):
             _all_gather_flat(k_all, k_local, group)                              # exchange 1: embeddings
         # local row statistics: [lse(rows) | npos(rows) | loss share, 3 pad]
         packed = torch.empty(2 * rows + 4, dtype=torch.float32, device=dev)
-        possum = torch.empty(rows, dtype=torch.float32, device=dev)
         prob = L._problem(plan, k_all, None, labels_all, None, temperature, base_temperature)
         ops.forward(lib, prob, plan, packed[0:rows], possum, packed[rows:2 * rows], packed[2 * rows:2 * rows + 1], dev)
         if px is not None:

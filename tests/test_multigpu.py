@@ -69,12 +69,14 @@ def _worker(rank, world, port, q):
         # ---------------- row-sharded loss vs oracle on the concatenated batch
         bsz, V, D = 96, 2, 128
         from simclr_pytorch_distributed_b200 import gather as G
-        # both exchange paths: peer memory (default) and NCCL all-gather (SCB_P2P=0), several steps each so
-        # that the rotating peer buffers are re-used
+        # all exchange paths: peer memory with a copy kernel + stream barrier (default), peer memory fused into
+        # the producing kernels (SCB_P2P=fused), NCCL all-gather (SCB_P2P=0); several steps so that the rotating
+        # peer buffers are re-used
         for engine, dtype, tol, p2p in (('fp32', torch.float32, 1e-4, '1'), ('bf16', torch.bfloat16, 2e-3 + 2 ** -8, '1'),
+                                        ('bf16', torch.bfloat16, 2e-3 + 2 ** -8, 'fused'),
                                         ('bf16', torch.bfloat16, 2e-3 + 2 ** -8, '0')):
             os.environ['SCB_P2P'] = p2p
-            for step in range(6 if p2p == '1' else 1):
+            for step in range(6 if p2p != '0' else 1):
                 rng = np.random.default_rng(99 + step)
                 z_all = rng.standard_normal((world * bsz, V, D)) * 2.0 + 0.3          # raw (un-normalised) outputs
                 z_all = torch.from_numpy(z_all).to(dtype)
@@ -94,7 +96,7 @@ def _worker(rank, world, port, q):
                 e_l = abs(float(loss) - ref_loss) / abs(ref_loss)
                 got = f.grad.double().cpu().numpy()
                 e_g = np.linalg.norm((got - ref_grad).ravel()) / np.linalg.norm(ref_grad.ravel())
-                used = 'peer memory' if (p2p == '1' and not G._PeerExchange._failed) else 'nccl'
+                used = 'nccl' if (p2p == '0' or G._PeerExchange._failed) else ('peer memory, fused' if p2p == 'fused' else 'peer memory, copy kernel')
                 if step == 0:
                     notes.append('loss %s via %s: rel loss %.2e rel grad %.2e' % (engine, used, e_l, e_g))
                 ok = ok and e_l <= tol and e_g <= 2 * tol

@@ -111,3 +111,13 @@ if os.environ.get('EVENTS'):
                     dl.append(nb[0] - x)
             if dl:
                 print('%s: %d -> %d median %d ns' % (label, a, b, sorted(dl)[len(dl) // 2]))
+
+# do CTAs whose span crosses a row-block boundary (an extra mid-kernel drain) take longer?
+CT, q = (2 * B * 1 + 127) // 128, None
+T = ((V * B + 127) // 128) * CT
+import math
+q = max(math.ceil(T / 148), math.ceil(CT / 15))
+cross = torch.tensor([((c * q) // CT) != ((min(T, (c + 1) * q) - 1) // CT) for c in range(len(life))])
+if cross.any() and (~cross).any():
+    print('CTAs inside one row block: median %.2f us; crossing a boundary: median %.2f us (%d of %d)' % (
+        float(life[~cross].median()), float(life[cross].median()), int(cross.sum()), len(life)))
