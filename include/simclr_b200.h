@@ -209,8 +209,8 @@ int scb_peer_wait(const uint32_t* flags_local, const uint32_t* state, int n, con
  * main_supcon.py:268-279 on one NVLink/NVSwitch box).  Copies up to 4 byte ranges of `src` into EVERY
  * destination buffer (the caller's own and its peers', mapped into this process with symmetric / IPC
  * memory): segment s copies seg[3s+2] bytes from src + seg[3s] to dst_ptrs[w] + seg[3s+1] for all w.
- * Offsets and sizes are multiples of 16 bytes.  `seg` and `dst_ptrs` are HOST arrays read during the
- * call.  The stores travel over NVLink as plain 16-byte writes; the caller orders them against the peers'
+ * Pointers, offsets and sizes are multiples of 4 bytes (16-byte copies when all are multiples of 16).
+ * `seg` and `dst_ptrs` are HOST arrays read during the call.  The stores travel over NVLink as plain 16-byte writes; the caller orders them against the peers'
  * reads with a cross-rank stream barrier after this kernel (gather.py uses the symmetric-memory
  * handle's barrier).  n_dst <= 16. */
 int scb_peer_bcast(const void* src, const int64_t* seg, int n_seg, const void* const* dst_ptrs, int n_dst,

@@ -449,19 +449,22 @@ struct PeerBcastArgs {
     int n_dst, n_seg;
 };
 
+template <typename W>      // uint4 when every offset and size is a multiple of 16 bytes, else 32-bit words
 __global__ void __launch_bounds__(256)
 peer_bcast_kernel(const char* __restrict__ src, const PeerBcastArgs a) {
     pdl_launch_dependents();
     pdl_wait();
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long stride = (long long)gridDim.x * blockDim.x;
+    constexpr long long B = sizeof(W);
     for (int s = 0; s < a.n_seg; ++s) {
         const char* from = src + a.src_off[s];
-        for (long long i = tid * 16; i < a.bytes[s]; i += stride * 16) {
-            const uint4 v = *reinterpret_cast<const uint4*>(from + i);
-            for (int w = 0; w < a.n_dst; ++w) *reinterpret_cast<uint4*>(a.dst[w] + a.dst_off[s] + i) = v;
+        for (long long i = tid * B; i < a.bytes[s]; i += stride * B) {
+            const W v = *reinterpret_cast<const W*>(from + i);
+            for (int w = 0; w < a.n_dst; ++w) *reinterpret_cast<W*>(a.dst[w] + a.dst_off[s] + i) = v;
         }
     }
+    // no fence here: the kernel boundary completes the stores before the caller's cross-rank barrier starts
 }
 
 // ------------------------------------------------------------------ host side
@@ -565,26 +568,31 @@ extern "C" int scb_peer_bcast(const void* src, const int64_t* seg, int n_seg, co
     PeerBcastArgs a;
     a.n_dst = n_dst;
     a.n_seg = n_seg;
-    long long total = 0;
+    long long total = 0, bits = reinterpret_cast<uintptr_t>(src);
     for (int s = 0; s < n_seg; ++s) {
         a.src_off[s] = seg[3 * s]; a.dst_off[s] = seg[3 * s + 1]; a.bytes[s] = seg[3 * s + 2];
-        SCB_REQUIRE(a.src_off[s] >= 0 && a.dst_off[s] >= 0 && a.bytes[s] >= 0 &&
-                    ((a.src_off[s] | a.dst_off[s] | a.bytes[s]) & 15) == 0,
-                    "peer_bcast: offsets and sizes must be non-negative multiples of 16");
+        SCB_REQUIRE(a.src_off[s] >= 0 && a.dst_off[s] >= 0 && a.bytes[s] >= 0,
+                    "peer_bcast: offsets and sizes must be non-negative");
+        bits |= a.src_off[s] | a.dst_off[s] | a.bytes[s];
         total += a.bytes[s];
     }
-    SCB_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15u) == 0, "peer_bcast: src must be 16-byte aligned");
     for (int w = 0; w < n_dst; ++w) {
-        SCB_REQUIRE(dst_ptrs[w] && (reinterpret_cast<uintptr_t>(dst_ptrs[w]) & 15u) == 0,
-                    "peer_bcast: destinations must be non-null and 16-byte aligned");
+        SCB_REQUIRE(dst_ptrs[w] != nullptr, "peer_bcast: destination %d is null", w);
+        bits |= reinterpret_cast<uintptr_t>(dst_ptrs[w]);
         a.dst[w] = (char*)const_cast<void*>(dst_ptrs[w]);
     }
+    SCB_REQUIRE((bits & 3) == 0, "peer_bcast: pointers, offsets and sizes must be multiples of 4 bytes");
     if (total == 0) return SCB_OK;
-    long long blocks = ceil_div(total / 16, 256);
+    const bool wide = (bits & 15) == 0;
+    long long blocks = ceil_div(total / (wide ? 16 : 4), 256);
     if (blocks > 4 * sm_count()) blocks = 4 * sm_count();
     if (blocks < 1) blocks = 1;
-    SCB_CUDA_OK(launch_pdl(peer_bcast_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream_,
-                           (const char*)src, a));
+    if (wide)
+        SCB_CUDA_OK(launch_pdl(peer_bcast_kernel<uint4>, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream_,
+                               (const char*)src, a));
+    else
+        SCB_CUDA_OK(launch_pdl(peer_bcast_kernel<uint32_t>, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream_,
+                               (const char*)src, a));
     count_launch();
     return SCB_OK;
 }

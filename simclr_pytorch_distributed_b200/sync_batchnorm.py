@@ -148,6 +148,61 @@ def _f32(t):
     return t if t is None or t.dtype == torch.float32 else t.float()
 
 
+class _PeerStats:
+    """The per-channel exchanges (_functions.py:41-56 all_gather, :155-165 all_reduce) over peer memory.
+
+    A few kilobytes per layer: an NCCL collective is pure latency here.  Each rank owns symmetric-memory
+    buffers (torch.distributed._symmetric_memory, plumbing only); `scb_peer_bcast` stores the rank's message
+    into every rank's copy and the handle's stream barrier orders it against the readers.  Buffers are shared
+    by all layers with the same message length and rotate through GENERATIONS copies (a rank is never more
+    than one exchange ahead of its slowest peer).  SCB_P2P=0 or any set-up failure -> NCCL."""
+    GENERATIONS = 4
+    _cache = {}
+    _failed = False
+
+    def __init__(self, group, dev, n, world, rank):
+        import ctypes
+        import torch.distributed._symmetric_memory as symm
+        self.world, self.n = world, n
+        self.bufs, self.ptrs, self.handles = [], [], []
+        for _ in range(self.GENERATIONS):
+            b = symm.empty((world * n,), dtype=torch.float32, device=dev)
+            h = symm.rendezvous(b, group)
+            self.bufs.append(b)
+            self.handles.append(h)
+            self.ptrs.append((ctypes.c_void_p * world)(*[int(p) for p in h.buffer_ptrs]))
+        self.seg = (ctypes.c_int64 * 3)(0, rank * n * 4, n * 4)
+        self.calls = 0
+
+    @classmethod
+    def get(cls, group, dev, n, world, rank):
+        import os
+        if cls._failed or os.environ.get('SCB_P2P', '1') == '0' or world > 16 or dev.type != 'cuda':
+            return None
+        if group._get_backend_name() != 'nccl':
+            return None
+        key = (id(group), dev.index, n, world)
+        if key not in cls._cache:
+            try:
+                cls._cache[key] = cls(group, dev, n, world, rank)
+            except Exception as e:       # every rank fails alike -> NCCL everywhere
+                import warnings
+                cls._failed = True
+                warnings.warn('peer-memory exchange unavailable (%s); SyncBatchNorm uses NCCL' % (e,))
+                return None
+        return cls._cache[key]
+
+    def all_gather(self, src, dev):
+        """src: n floats of this rank -> [world * n] floats, rank-major (valid until GENERATIONS-1 further calls)."""
+        lib = _lib.load()
+        g = self.calls % self.GENERATIONS
+        self.calls += 1
+        _lib.check(lib.scb_peer_bcast(src.data_ptr(), self.seg, 1, self.ptrs[g], self.world,
+                                      _Kernels.stream(dev)), 'scb_peer_bcast')
+        self.handles[g].barrier(channel=0)
+        return self.bufs[g]
+
+
 class _SyncBNFunction(torch.autograd.Function):
     """Training-mode forward/backward: _functions.py:10-209 on the sm_100a kernels."""
 
@@ -194,6 +249,10 @@ class _SyncBNFunction(torch.autograd.Function):
             kern.stats(x, geom, stats)
         if not use_batch_stats:
             pass
+        elif world_size > 1 and kern is _Kernels and _PeerStats.get(process_group, dev, 2 * C + 1, world_size,
+                                                                    dist.get_rank(process_group)) is not None:
+            px = _PeerStats.get(process_group, dev, 2 * C + 1, world_size, dist.get_rank(process_group))
+            stats_all = px.all_gather(stats, dev)
         elif world_size > 1:
             stats_all = torch.empty(world_size * (2 * C + 1), dtype=torch.float32, device=dev)
             if process_group._get_backend_name() != 'gloo':
@@ -245,7 +304,12 @@ class _SyncBNFunction(torch.autograd.Function):
             if not ctx.use_batch_stats:
                 sums = torch.zeros_like(sums)               # eval: statistics do not depend on x
             elif ctx.world_size > 1:                        # _functions.py:155-165
-                dist.all_reduce(sums, dist.ReduceOp.SUM, ctx.process_group, async_op=False)
+                px = (_PeerStats.get(ctx.process_group, dev, 2 * C, ctx.world_size, dist.get_rank(ctx.process_group))
+                      if kern is _Kernels else None)
+                if px is not None:                          # all-reduce = peer all-gather + a local sum
+                    sums = px.all_gather(sums, dev).view(ctx.world_size, 2 * C).sum(0)
+                else:
+                    dist.all_reduce(sums, dist.ReduceOp.SUM, ctx.process_group, async_op=False)
             grad_input = torch.empty_like(x)
             kern.backward_apply(dy, x, grad_input, geom, saved, w32, b32, sums, flags)
         wd, bd = ctx.param_dtypes

@@ -36,36 +36,38 @@ def _worker(rank, world, port, q):
         from simclr_pytorch_distributed_b200.gather import DistributedSupConLoss
         from oracle import supcon_forward_backward, normalize_rows, normalize_rows_backward
         dev = torch.device('cuda', rank)
-        # ---------------- SyncBN vs stock SyncBatchNorm (NHWC bf16 and NCHW fp32)
-        for dtype, cl in ((torch.bfloat16, True), (torch.float32, False)):
-            g = torch.Generator().manual_seed(4321 + rank)
-            x = (torch.randn(32, 64, 8, 8, generator=g) * 1.5 + 0.5 + rank).to(dev, dtype)
-            dy = torch.randn(32, 64, 8, 8, generator=g).to(dev, dtype)
-            if cl:
-                x = x.contiguous(memory_format=torch.channels_last)
-                dy = dy.contiguous(memory_format=torch.channels_last)
-            ours = SyncBatchNorm(64).to(dev)
-            ref = torch.nn.SyncBatchNorm(64).to(dev)
-            with torch.no_grad():
-                ours.weight.uniform_(0.5, 1.5)
-                ours.bias.normal_(0, 0.1)
-            dist.broadcast(ours.weight.data, 0)
-            dist.broadcast(ours.bias.data, 0)
-            ref.load_state_dict(ours.state_dict())
-            xa = x.clone().requires_grad_(True)
-            xb = x.clone().requires_grad_(True)
-            ya = ours(xa)
-            ya.backward(dy)
-            yb = ref(xb)
-            yb.backward(dy)
-            tol = 2.0 ** -7 if dtype == torch.bfloat16 else 1e-5
-            e_y = ((ya.float() - yb.float()).abs() / (yb.float().abs() + 1)).max().item()
-            e_x = ((xa.grad.float() - xb.grad.float()).abs() / (xb.grad.float().abs() + 1)).max().item()
-            e_rv = (ours.running_var - ref.running_var).abs().max().item()
-            e_rm = (ours.running_mean - ref.running_mean).abs().max().item()
-            e_gw = ((ours.weight.grad - ref.weight.grad).abs() / (ref.weight.grad.abs() + 1)).max().item()
-            notes.append('bn %s: y %.2e dx %.2e rm %.2e rv %.2e dgamma %.2e' % (dtype, e_y, e_x, e_rm, e_rv, e_gw))
-            ok = ok and e_y <= tol and e_x <= tol and e_rv <= 1e-5 and e_rm <= 1e-5 and e_gw <= 1e-3
+        # ---------------- SyncBN vs stock SyncBatchNorm (NHWC bf16 and NCHW fp32), exchanges over peer memory and over NCCL
+        for bn_p2p in ('1', '0'):
+            os.environ['SCB_P2P'] = bn_p2p
+            for dtype, cl in ((torch.bfloat16, True), (torch.float32, False)):
+                g = torch.Generator().manual_seed(4321 + rank)
+                x = (torch.randn(32, 64, 8, 8, generator=g) * 1.5 + 0.5 + rank).to(dev, dtype)
+                dy = torch.randn(32, 64, 8, 8, generator=g).to(dev, dtype)
+                if cl:
+                    x = x.contiguous(memory_format=torch.channels_last)
+                    dy = dy.contiguous(memory_format=torch.channels_last)
+                ours = SyncBatchNorm(64).to(dev)
+                ref = torch.nn.SyncBatchNorm(64).to(dev)
+                with torch.no_grad():
+                    ours.weight.uniform_(0.5, 1.5)
+                    ours.bias.normal_(0, 0.1)
+                dist.broadcast(ours.weight.data, 0)
+                dist.broadcast(ours.bias.data, 0)
+                ref.load_state_dict(ours.state_dict())
+                xa = x.clone().requires_grad_(True)
+                xb = x.clone().requires_grad_(True)
+                ya = ours(xa)
+                ya.backward(dy)
+                yb = ref(xb)
+                yb.backward(dy)
+                tol = 2.0 ** -7 if dtype == torch.bfloat16 else 1e-5
+                e_y = ((ya.float() - yb.float()).abs() / (yb.float().abs() + 1)).max().item()
+                e_x = ((xa.grad.float() - xb.grad.float()).abs() / (xb.grad.float().abs() + 1)).max().item()
+                e_rv = (ours.running_var - ref.running_var).abs().max().item()
+                e_rm = (ours.running_mean - ref.running_mean).abs().max().item()
+                e_gw = ((ours.weight.grad - ref.weight.grad).abs() / (ref.weight.grad.abs() + 1)).max().item()
+                notes.append('bn %s p2p=%s: y %.2e dx %.2e rm %.2e rv %.2e dgamma %.2e' % (dtype, bn_p2p, e_y, e_x, e_rm, e_rv, e_gw))
+                ok = ok and e_y <= tol and e_x <= tol and e_rv <= 1e-5 and e_rm <= 1e-5 and e_gw <= 1e-3
         # ---------------- row-sharded loss vs oracle on the concatenated batch
         bsz, V, D = 96, 2, 128
         from simclr_pytorch_distributed_b200 import gather as G
