@@ -18,6 +18,18 @@ __device__ __forceinline__ float ex2poly(float x) {
     return __int_as_float(__float_as_int(p) + ((int)fl << 23));
 }
 
+// the same without any conversion instruction (F2I / FRND run on the XU pipe next to MUFU): round-to-nearest
+// through the 1.5*2^23 magic number, 2^f on [-0.5, 0.5] as a cubic, exponent added to the bits
+__device__ __forceinline__ float ex2magic(float x) {
+    x = fmaxf(x, -125.f);
+    const float t = x + 12582912.f;
+    const float f = x - (t - 12582912.f);                   // [-0.5, 0.5]
+    float p = fmaf(f, 0.05550411f, 0.24022651f);
+    p = fmaf(p, f, 0.69314718f);
+    p = fmaf(p, f, 1.0f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(256) k(float* out, int iters, float seed) {
     float acc[8];
@@ -38,6 +50,14 @@ __global__ void __launch_bounds__(256) k(float* out, int iters, float seed) {
                 acc[i] += (i & 3) == 3 ? ex2poly(x[i]) : ex2f(x[i]);
             } else if (MODE == 4) {         // mixed 1:1
                 acc[i] += (i & 1) ? ex2poly(x[i]) : ex2f(x[i]);
+            } else if (MODE == 5) {
+                acc[i] += ex2magic(x[i]);
+            } else if (MODE == 6) {         // 3 MUFU : 1 magic poly
+                acc[i] += (i & 3) == 3 ? ex2magic(x[i]) : ex2f(x[i]);
+            } else if (MODE == 7) {         // 7 MUFU : 1 magic poly
+                acc[i] += (i & 7) == 7 ? ex2magic(x[i]) : ex2f(x[i]);
+            } else if (MODE == 8) {         // 1 : 1
+                acc[i] += (i & 1) ? ex2magic(x[i]) : ex2f(x[i]);
             }
             x[i] -= 0.001f;
         }
@@ -71,5 +91,9 @@ int main() {
     run<2>("MUFU ex2.f16x2 (2/instr)", 2);
     run<3>("3 MUFU : 1 poly", 1);
     run<4>("1 MUFU : 1 poly", 1);
+    run<5>("magic-number poly3", 1);
+    run<6>("3 MUFU : 1 magic poly", 1);
+    run<7>("7 MUFU : 1 magic poly", 1);
+    run<8>("1 MUFU : 1 magic poly", 1);
     return 0;
 }
