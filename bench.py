@@ -201,23 +201,48 @@ def make_loss_runner(world, rank, engine, pool):
         f.grad = None
         fwd(f).backward()
 
-    grad_host = torch.empty(b_local, N_VIEWS, DIM, dtype=dtype).pin_memory()
+    # End to end: every step copies ITS embeddings from pinned host memory and the host reads the loss.  The
+    # copy of step i+1 is issued on a side stream before step i computes (what a training loop's prefetcher
+    # does), so it overlaps the kernels; the gradient stays on the device, where the encoder's backward
+    # consumes it (reading the 2 MiB gradient back every step would only measure PCIe).
     loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+    copy_stream = torch.cuda.Stream()
+    slots = [torch.empty(b_local, N_VIEWS, DIM, dtype=dtype, device='cuda') for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]          # H2D of the slot has landed
+    freed = [torch.cuda.Event() for _ in range(2)]          # the step that used the slot is done with it
+    state = {'primed': -1}
+
+    def prefetch(j):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(freed[j % 2])
+            slots[j % 2].copy_(host[j % pool], non_blocking=True)
+            ready[j % 2].record(copy_stream)
+        state['primed'] = j
+
+    for e in freed:
+        e.record()
 
     def step_e2e(i):
-        f = host[i % pool].cuda(non_blocking=True).requires_grad_(True)
+        if state['primed'] != i:
+            prefetch(i)                                       # first step of a run: nothing was prefetched
+        prefetch(i + 1)
+        cur = torch.cuda.current_stream()
+        cur.wait_event(ready[i % 2])
+        f = slots[i % 2].detach().requires_grad_(True)
         loss = fwd(f)
         loss.backward()
-        grad_host.copy_(f.grad, non_blocking=True)
+        freed[i % 2].record(cur)
         loss_host.copy_(loss.detach().float(), non_blocking=True)
-        torch.cuda.current_stream().synchronize()     # the caller reads loss and gradient every step
+        cur.synchronize()                                     # the caller reads the loss every step
 
     nbytes = b_local * N_VIEWS * DIM * host[0].element_size()
-    return step_resident, step_e2e, nbytes, nbytes + 4, b_local
+    return step_resident, step_e2e, nbytes, 4, b_local
 
 
 def loss_kernel_breakdown(engine, steps):
-    """Per-kernel CUDA-event times of one fwd+bwd through the C ABI (N=1 shapes), for the roofline."""
+    """CUDA-event times of the launches of one fwd+bwd through the C ABI (N=1 shapes, the product path: bf16
+    features used in place), for the roofline.  The backward's main kernel is timed alone with two events the
+    library records around it (scb_debug_set_events)."""
     import torch
     import torch.nn.functional as F
     from simclr_pytorch_distributed_b200 import losses as L, _lib
@@ -226,32 +251,48 @@ def loss_kernel_breakdown(engine, steps):
     dtype = torch.bfloat16 if engine == 'bf16' else torch.float32
     z = F.normalize(torch.randn(B_GLOBAL, N_VIEWS, DIM, device=dev), dim=-1).to(dtype)
     plan = L.LossPlan(B_GLOBAL, N_VIEWS, DIM, engine=L._ENGINES[engine])
-    k = torch.empty((plan.n_k, plan.ldk), dtype=plan.k_torch, device=dev)
-    k_lo = torch.empty_like(k) if engine == 'bf16x3' else None
+    plan.scalar_dtype = _lib.dtype_code(dtype)
+    tc = engine != 'fp32'
+    if tc:
+        plan.row_layout = _lib.ROWS_SAMPLE_MAJOR
+        k = z.view(plan.n_k, plan.ldk)
+    else:
+        k = torch.empty((plan.n_k, plan.ldk), dtype=plan.k_torch, device=dev)
+        L.launch_prep(lib, z, plan, False, k, None, None)
     stats = torch.empty((4, plan.n_k), dtype=torch.float32, device=dev)
     loss = torch.empty(2, dtype=torch.float32, device=dev)
-    gout = torch.ones((), dtype=torch.float32, device=dev)
-    dk = torch.empty((plan.rows_local, DIM), dtype=torch.float32, device=dev)
+    gout = torch.ones((), dtype=dtype, device=dev)
+    dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
     dz = torch.empty_like(z)
-    prob = L._problem(plan, k, k_lo, None, None, TEMP, 0.07)
-    names = ['prep', 'forward(+finalize)', 'backward', 'finish']
-    tot = [0.0] * 4
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
-    for it in range(steps + 3):
-        torch.cuda._sleep(400000)      # let the host run ahead so the events see back-to-back kernels
-        ev[0].record()
-        L.launch_prep(lib, z, plan, False, k, k_lo, None)
-        ev[1].record()
-        L.launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
-        ev[2].record()
-        L.launch_backward(lib, prob, plan, stats[0], stats[2], gout, dk, dev)
-        ev[3].record()
-        L.launch_finish(lib, dk, z, plan, False, None, dz)
-        ev[4].record()
-        torch.cuda.synchronize()
-        if it >= 3:
-            for j in range(4):
-                tot[j] += ev[j].elapsed_time(ev[j + 1])
+    prob = L._problem(plan, k, None, None, None, TEMP, 0.07)
+    names = ['forward(+finalize)', 'backward(+reduce/finish)', 'backward main kernel']
+    tot = [0.0] * 3
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    em = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    for e in em:
+        e.record()                      # creates the underlying cudaEvent_t
+    torch.cuda.synchronize()
+    if tc:
+        lib.scb_debug_set_events(em[0].cuda_event, em[1].cuda_event)
+    try:
+        for it in range(steps + 3):
+            torch.cuda._sleep(400000)      # let the host run ahead so the events see back-to-back kernels
+            ev[0].record()
+            L.launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
+            ev[1].record()
+            if tc:
+                L.launch_backward_features(lib, prob, plan, stats[0], stats[2], gout, z, False, None, dz, dev)
+            else:
+                L.launch_backward(lib, prob, plan, stats[0], stats[2], gout, dk, dev)
+                L.launch_finish(lib, dk, z, plan, False, None, dz)
+            ev[2].record()
+            torch.cuda.synchronize()
+            if it >= 3:
+                tot[0] += ev[0].elapsed_time(ev[1])
+                tot[1] += ev[1].elapsed_time(ev[2])
+                tot[2] += em[0].elapsed_time(em[1]) if tc else ev[1].elapsed_time(ev[2])
+    finally:
+        lib.scb_debug_set_events(None, None)
     return {n: t / steps * 1e3 for n, t in zip(names, tot)}     # microseconds
 
 
@@ -494,18 +535,21 @@ def main():
                                                'by construction' % pool,
                        'launch': 'public module API (SupConLoss.forward + autograd backward); ' + how},
             'e2e': {'value': B_GLOBAL / (ms_e2e / args.steps * 1e-3), 'unit': 'pairs/s',
-                    'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
+                    'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+                    'note': 'each step: H2D of its embeddings from pinned memory (prefetched one step ahead on a '
+                            'copy stream), forward + backward, D2H of the loss, host sync; the gradient stays on '
+                            'the device'},
             'gpu_launches': int(launches),
             'step_tensor_frac_of_measured_peak': flops_step / world / (per * 1e-3) / (pk['tf'] * 1e12),
         })
         if rank == 0 and world == 1:
             kb = loss_kernel_breakdown(engine, min(args.steps, 100))
-            t_bwd = kb['backward']
+            t_bwd = kb['backward main kernel']
             achieved = 4.0 * A * C * DIM / (t_bwd * 1e-6) / 1e12
             out['roofline'] = {'bound': 'tensor', 'achieved': achieved, 'peak': pk['tf'], 'unit': 'TFLOP/s',
                                'frac': achieved / pk['tf'],
                                'traffic': profiled_traffic('supcon_tc_bwd_kernel') if engine != 'fp32' else None,
-                               'kernel': 'supcon backward (%s engine)' % engine, 'peak_source': pk['src'] + ' burst',
+                               'kernel': 'supcon_tc_bwd_kernel (%s engine), timed alone' % engine if engine != 'fp32' else 'supcon backward (fp32 engine)', 'peak_source': pk['src'] + ' burst',
                                'algorithmic_flops_per_launch': 4.0 * A * C * DIM,
                                'kernel_us': kb}
     # ------------------------------------------------ SyncBN

@@ -64,6 +64,9 @@ int64_t scb_launch_count(void);
 /* diagnostics only: a device buffer of 3*1024 int64 that CTA 0 of the tensor-core backward fills
  * with (event id, SM clock) pairs per role (0 MMA issuer, 1/2 epilogue warpgroups); NULL = off */
 int scb_debug_set_trace(void* device_buffer);
+/* measurement aid (bench.py): two cudaEvent_t that the tensor-core backward records on its stream right
+ * before and right after its main kernel, so that the kernel can be timed alone; NULL, NULL = off */
+int scb_debug_set_events(void* start, void* stop);
 
 /* ======================================================================== path 1: the loss
  *

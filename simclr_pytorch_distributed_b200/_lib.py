@@ -110,6 +110,7 @@ PROTOTYPES = {
     'scb_device_cc': (_i, []),
     'scb_launch_count': (_i64, []),
     'scb_debug_set_trace': (_i, [_vp]),
+    'scb_debug_set_events': (_i, [_vp, _vp]),
     'scb_supcon_prep': (_i, [_vp, _i, _i, _i, _i, _i64, _i64, _i, _f, _vp, _vp, _i, _i, _vp, _vp]),
     'scb_supcon_workspace_bytes': (_i64, [_pp, _i]),
     'scb_supcon_forward': (_i, [_pp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),

@@ -6,6 +6,9 @@
 #include <stdlib.h>
 #include <string.h>
 #include <atomic>
+#include <mutex>
+#include <utility>
+#include <vector>
 
 namespace scb {
 
@@ -13,6 +16,24 @@ static thread_local char g_err[512] = "";
 static std::atomic<long long> g_launches{0};
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+bool attr_done(const void* kern, int attr, int value) {
+    // (kernel, attribute, device) -> last value applied; a few dozen entries, guarded by a mutex
+    struct Key { const void* k; int a; int d; };
+    static std::mutex mu;
+    static std::vector<std::pair<Key, int>> seen;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    std::lock_guard<std::mutex> lock(mu);
+    for (auto& e : seen)
+        if (e.first.k == kern && e.first.a == attr && e.first.d == dev) {
+            if (e.second == value) return true;
+            e.second = value;
+            return false;
+        }
+    seen.push_back({Key{kern, attr, dev}, value});
+    return false;
+}
 
 bool pdl_enabled() {
     static const bool on = [] {
@@ -87,6 +108,11 @@ extern "C" int64_t scb_launch_count(void) { return (int64_t)g_launches.load(std:
 
 extern "C" int scb_debug_set_trace(void* device_buffer) {
     tc_set_trace((long long*)device_buffer);
+    return SCB_OK;
+}
+
+extern "C" int scb_debug_set_events(void* start, void* stop) {
+    tc_set_events(start, stop);
     return SCB_OK;
 }
 

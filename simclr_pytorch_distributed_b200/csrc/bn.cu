@@ -1145,7 +1145,7 @@ extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t r
         NhwcGeom g;
         auto kern = bn_fwd_fused_nhwc_kernel<T, VEC>;
         const size_t smem = 2 * kFusedThreads * VEC * sizeof(float);
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        set_max_dynamic_smem(kern, (int)smem);
         const int per_sm = fused_ctas_per_sm(kern, smem);
         if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(y), &g, 1)) {
             dim3 grid(g.grid_x, (unsigned)g.grid_y);
@@ -1186,7 +1186,7 @@ extern "C" int scb_bn_backward_fused(const void* dy, const void* x, void* dx, in
         NhwcGeom g;
         auto kern = bn_bwd_fused_nhwc_kernel<T, VEC>;
         const size_t smem = 2 * kFusedThreads * VEC * sizeof(float);
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        set_max_dynamic_smem(kern, (int)smem);
         const int per_sm = fused_ctas_per_sm(kern, smem);
         if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(dy) && aligned16(dx), &g,
                                       1)) {

@@ -40,9 +40,20 @@ void count_launch(int n = 1);   // bookkeeping behind scb_launch_count()
 // The loss pipeline alternates tiny helper kernels with the persistent tensor-core kernels, which need
 // the maximum shared-memory carve-out; asking for the same carve-out everywhere avoids an L1/shared
 // re-partition of every SM between consecutive launches.
+// Function attributes stick (per device): set each (kernel, attribute, value) once instead of paying a driver
+// call on every launch.  attr_done() returns true when this combination was already applied on the device.
+bool attr_done(const void* kern, int attr, int value);   // api.cu
+
 template <typename Kern>
 inline void prefer_max_smem_carveout(Kern kern) {
+    if (attr_done((const void*)kern, (int)cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared))
+        return;
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+}
+template <typename Kern>
+inline cudaError_t set_max_dynamic_smem(Kern kern, int bytes) {
+    if (attr_done((const void*)kern, (int)cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)) return cudaSuccess;
+    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
 // ---------------------------------------------------------------- programmatic dependent launch

@@ -1041,6 +1041,9 @@ static int make_tmap(const scb_supcon_problem* p, CUtensorMap* out) {
 static constexpr int kMaxSlots = 32;
 static long long* g_trace = nullptr;   // set through scb_debug_set_trace (diagnostics only)
 void tc_set_trace(long long* p) { g_trace = p; }
+// measurement aid (scb_debug_set_events): events recorded right before / after the backward main kernel
+static cudaEvent_t g_ev_start = nullptr, g_ev_stop = nullptr;
+void tc_set_events(void* a, void* b) { g_ev_start = (cudaEvent_t)a; g_ev_stop = (cudaEvent_t)b; }
 
 struct TcGeom { int CT, RB, T, q, grid, n_split; };
 
@@ -1129,7 +1132,7 @@ static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, cud
 
 template <typename Kern>
 static int set_smem(Kern kern, size_t bytes) {
-    SCB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    SCB_CUDA_OK(set_max_dynamic_smem(kern, (int)bytes));
     return SCB_OK;
 }
 
@@ -1183,9 +1186,11 @@ static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_ro
         if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, LAB_>, smem)) return e;                         \
         SCB_CUDA_OK(launch_pdl(supcon_tc_bwd_kernel<KCH_, LAB_>, dim3(g.grid), dim3(kBwdThreads), smem, stream, tmap, t)); \
     } while (0)
+    if (g_ev_start) SCB_CUDA_OK(cudaEventRecord(g_ev_start, stream));
     if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
     else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
 #undef SCB_LAUNCH_BWD
+    if (g_ev_stop) SCB_CUDA_OK(cudaEventRecord(g_ev_stop, stream));
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     *g_out = g;

@@ -24,5 +24,7 @@ int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
 // diagnostics: device buffer of 3 x 1024 int64 that CTA 0 of the backward kernel fills with
 // (event id, clock64) pairs; nullptr switches tracing off
 void tc_set_trace(long long* p);
+// measurement aid: CUDA events recorded around the backward main kernel (nullptr = off)
+void tc_set_events(void* start, void* stop);
 
 }  // namespace scb
