@@ -302,6 +302,25 @@ int scb_bn_backward_fused(const void* dy, const void* x, void* dx, int dtype, in
                           const float* n_total, float* out_sums, float* grad_weight, float* grad_bias, int flags,
                           void* workspace, int64_t workspace_bytes, void* stream);
 
+
+/* The fused kernels with a cross-GPU phase (world size > 1 on one NVLink/NVSwitch box): after the local grid
+ * barrier one CTA stores this rank's per-channel message ([mean | M2 | count] forward, [sum dy | sum dy (x - mean)]
+ * backward) into every rank's gathered buffer ch->dst[w] at slot `rank`, raises this rank's flag on every rank,
+ * and all CTAs wait for the flags of all ranks before they read the gathered messages from `gathered_local`
+ * (this rank's copy, = ch->dst[rank]).  Replaces the all_gather / all_reduce of torch/nn/modules/_functions.py
+ * :41-56 and :155-165 without leaving the kernel.  `flags_local`: this rank's flag array (one word per rank);
+ * channel conventions as for scb_peer_channel above.  Every rank must take this path for the same layer call. */
+int scb_bn_forward_fused_peers(const void* x, void* y, int dtype, int64_t rows, int channels,
+                               const float* weight, const float* bias, float* running_mean, float* running_var,
+                               float momentum, float eps, float* save_mean, float* save_invstd, float* save_count,
+                               int flags, void* workspace, int64_t workspace_bytes, const scb_peer_channel* ch,
+                               const float* gathered_local, const uint32_t* flags_local, int rank, void* stream);
+int scb_bn_backward_fused_peers(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
+                                const float* mean, const float* invstd, const float* weight, const float* bias,
+                                const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
+                                int flags, void* workspace, int64_t workspace_bytes, const scb_peer_channel* ch,
+                                const float* gathered_local, const uint32_t* flags_local, int rank, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -133,6 +133,9 @@ PROTOTYPES = {
     'scb_bn_forward_fused': (_i, [_vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _i, _vp, _i64, _vp]),
     'scb_bn_backward_fused': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp,
                                    _i64, _vp]),
+    'scb_bn_forward_fused_peers': (_i, [_vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _i, _vp, _i64, _vp, _vp, _vp, _i, _vp]),
+    'scb_bn_backward_fused_peers': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp,
+                                   _i64, _vp, _vp, _vp, _i, _vp]),
     'scb_bn_backward_apply': (_i, [_vp, _vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _i, _vp]),
 }

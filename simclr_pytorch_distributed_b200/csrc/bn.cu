@@ -15,6 +15,7 @@
 // a zeroed accumulator; the last CTA to finish (ticket counter) turns the accumulators into the
 // result and zeroes them again, so the scratch is reusable without a memset.
 #include "common.cuh"
+#include "supcon_common.cuh"   // PeerOut (peer-memory destinations + flags)
 
 namespace scb {
 
@@ -869,6 +870,46 @@ __device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned total) 
     __syncthreads();
 }
 
+// ---- cross-GPU phase of the fused kernels (world size > 1) ------------------------------------------
+// After the local grid barrier CTA (0,0) stores this rank's per-channel message into every rank's gathered
+// buffer over NVLink and raises this rank's flag everywhere; every CTA then waits until the flags of all
+// ranks show the current exchange and reads the gathered messages from its OWN copy.  The exchange number
+// is state[1] + 1, read by every CTA before the grid barrier (CTA (0,0) only bumps it after the barrier).
+struct BnPeer {
+    PeerOut po;                 // n_dst = 0: single rank, no exchange
+    const float* gathered;      // this rank's copy: [n_dst][message length]
+    const unsigned* flags;      // this rank's flag array, one word per rank
+    int rank;
+};
+
+__device__ __forceinline__ void bn_peer_publish(const BnPeer& bp, unsigned want) {   // CTA (0,0), all threads
+    __syncthreads();                            // the CTA's remote stores happen-before thread 0's fence
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        bp.po.state[1] = want;
+        for (int w = 0; w < bp.po.n_dst; ++w)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(bp.po.flag[w]), "r"(want) : "memory");
+    }
+}
+
+__device__ __forceinline__ void bn_peer_wait(const BnPeer& bp, unsigned want) {      // every CTA, all threads
+    if ((int)threadIdx.x < bp.po.n_dst) {
+        unsigned long long t0 = 0;
+        for (unsigned spins = 1;; ++spins) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(bp.flags + threadIdx.x) : "memory");
+            if ((int)(v - want) >= 0) break;
+            if ((spins & 1023u) == 0u) {            // a peer that died must not hang this GPU for ever
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 30000000000ull) __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+
 // After the grid barrier every CTA reads the sums; the last one to have done so (second ticket) zeroes
 // the accumulators and both tickets so the scratch is ready for the next launch.
 __device__ __forceinline__ void rearm_scratch(float* acc, unsigned* counters, unsigned total, int n_acc) {
@@ -891,13 +932,14 @@ bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, 
                          float* __restrict__ acc, unsigned* counters,
                          const float* __restrict__ weight, const float* __restrict__ bias,
                          float* running_mean, float* running_var, float momentum, float eps,
-                         float* save_mean, float* save_invstd, float* save_count, int flags) {
+                         float* save_mean, float* save_invstd, float* save_count, int flags, const BnPeer bp) {
     extern __shared__ float sm[];
     const int TY = kFusedThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = (blockIdx.x * TX + tx) * VEC;
     const bool active = c0 < C;
     const unsigned total = gridDim.x * gridDim.y;
+    const unsigned want = (bp.po.n_dst > 0) ? __ldcg(bp.po.state + 1) + 1u : 0u;
     const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta + ty;
     const int64_t step = (int64_t)TY * C;
@@ -931,10 +973,35 @@ bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, 
         cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, my_acc, my_acc + C);
     }
     grid_barrier(counters, total);
+    const float n = (float)M;
+    if (bp.po.n_dst > 0) {
+        if (blockIdx.x == 0 && blockIdx.y == 0) {
+            // this rank's message [mean (C) | M2 (C) | count] goes to every rank (_functions.py:41-56)
+            const int stride = 2 * C + 1;
+            for (int c = threadIdx.x; c < C; c += blockDim.x) {
+                float sa = 0.f, sb = 0.f;
+                for (int rr = 0; rr < R; ++rr) {
+                    sa += __ldcg(acc + (size_t)rr * 2 * C + c);
+                    sb += __ldcg(acc + (size_t)rr * 2 * C + C + c);
+                }
+                const float mean_r = to_f32(x[c]) + sa / n;
+                const float m2_r = fmaxf(sb - sa * sa / n, 0.f);
+                for (int w = 0; w < bp.po.n_dst; ++w) {
+                    float* d = reinterpret_cast<float*>(bp.po.dst[w]) + (size_t)bp.rank * stride;
+                    d[c] = mean_r;
+                    d[C + c] = m2_r;
+                }
+            }
+            if (threadIdx.x == 0)
+                for (int w = 0; w < bp.po.n_dst; ++w)
+                    reinterpret_cast<float*>(bp.po.dst[w])[(size_t)bp.rank * stride + 2 * C] = n;
+            bn_peer_publish(bp, want);
+        }
+        bn_peer_wait(bp, want);
+    }
     // One thread per channel of the CTA's tile fetches the completed sums (a single pass over a few
     // cache lines per CTA -- letting every thread read them turns those lines into an L2 hot spot)
     // and leaves the per-channel scale / offset in shared memory.
-    const float n = (float)M;
     const int W = TX * VEC;
     const int tile_c0 = blockIdx.x * W;
     __syncthreads();                       // the reduction is done with sm[]
@@ -942,22 +1009,27 @@ bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, 
         const int c = tile_c0 + t;
         float av = 0.f, bv = 0.f;
         if (c < C) {
-            float sa = 0.f, sb = 0.f;
-            for (int rr = 0; rr < R; ++rr) {
-                sa += __ldcg(acc + (size_t)rr * 2 * C + c);
-                sb += __ldcg(acc + (size_t)rr * 2 * C + C + c);
+            float mean, m2, invstd, nn = n;
+            if (bp.po.n_dst > 0) {
+                merged_stats(bp.gathered, bp.po.n_dst, C, c, nullptr, nullptr, eps, mean, invstd, m2, nn);
+            } else {
+                float sa = 0.f, sb = 0.f;
+                for (int rr = 0; rr < R; ++rr) {
+                    sa += __ldcg(acc + (size_t)rr * 2 * C + c);
+                    sb += __ldcg(acc + (size_t)rr * 2 * C + C + c);
+                }
+                mean = to_f32(x[c]) + sa / n;
+                m2 = fmaxf(sb - sa * sa / n, 0.f);
+                invstd = rsqrtf(m2 / n + eps);
             }
-            const float mean = to_f32(x[c]) + sa / n;
-            const float m2 = fmaxf(sb - sa * sa / n, 0.f);
-            const float invstd = rsqrtf(m2 / n + eps);
             av = (weight ? weight[c] : 1.f) * invstd;
             bv = (bias ? bias[c] : 0.f) - mean * av;
             if (blockIdx.y == 0) {
                 if (save_mean) save_mean[c] = mean;
                 if (save_invstd) save_invstd[c] = invstd;
                 if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-                if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
-                if (c == 0 && save_count) save_count[0] = n;
+                if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (nn - 1.f));
+                if (c == 0 && save_count) save_count[0] = nn;
             }
         }
         sm[t] = av;
@@ -995,8 +1067,9 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
                          const float* __restrict__ mean, const float* __restrict__ invstd,
                          const float* __restrict__ weight, const float* __restrict__ bias,
                          const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias,
-                         int flags) {
+                         int flags, const BnPeer bp) {
     extern __shared__ float sm[];
+    const unsigned want = (bp.po.n_dst > 0) ? __ldcg(bp.po.state + 1) + 1u : 0u;
     const int TY = kFusedThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = (blockIdx.x * TX + tx) * VEC;
@@ -1051,6 +1124,20 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
         cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, my_acc, my_acc + C);
     }
     grid_barrier(counters, total);
+    if (bp.po.n_dst > 0) {
+        if (blockIdx.x == 0 && blockIdx.y == 0) {
+            // this rank's sums [sum dy (C) | sum dy (x - mean) (C)] go to every rank: the all-reduce of
+            // _functions.py:155-165 as an all-gather + a local sum in fixed rank order
+            for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+                float v = 0.f;
+                for (int rr = 0; rr < R; ++rr) v += __ldcg(acc + (size_t)rr * 2 * C + c);
+                for (int w = 0; w < bp.po.n_dst; ++w)
+                    reinterpret_cast<float*>(bp.po.dst[w])[(size_t)bp.rank * 2 * C + c] = v;
+            }
+            bn_peer_publish(bp, want);
+        }
+        bn_peer_wait(bp, want);
+    }
     const float inv_n = 1.f / n_total[0];
     const int W = TX * VEC;
     const int tile_c0 = blockIdx.x * W;
@@ -1065,8 +1152,16 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
                 sx += __ldcg(acc + (size_t)rr * 2 * C + C + c);
             }
             const float is = invstd[c];
-            v2 = sd * inv_n;
-            v3 = is * is * sx * inv_n;
+            float gd = sd, gx = sx;                 // global sums (dx); dgamma / dbeta below stay local
+            if (bp.po.n_dst > 0) {
+                gd = 0.f; gx = 0.f;
+                for (int w = 0; w < bp.po.n_dst; ++w) {
+                    gd += __ldcg(bp.gathered + (size_t)w * 2 * C + c);
+                    gx += __ldcg(bp.gathered + (size_t)w * 2 * C + C + c);
+                }
+            }
+            v2 = gd * inv_n;
+            v3 = is * is * gx * inv_n;
             if (blockIdx.y == 0) {
                 if (out_sums) { out_sums[c] = sd; out_sums[C + c] = sx; }
                 if (grad_weight) grad_weight[c] = sx * is;
@@ -1127,11 +1222,27 @@ extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t oute
     return fused_geom(outer * inner, channels, es, true, &g, 1) ? 1 : 0;
 }
 
-extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t rows, int channels,
-                                    const float* weight, const float* bias, float* running_mean,
-                                    float* running_var, float momentum, float eps, float* save_mean,
-                                    float* save_invstd, float* save_count, int flags, void* workspace,
-                                    int64_t workspace_bytes, void* stream_) {
+static int make_bn_peer(const scb_peer_channel* ch, const float* gathered_local, const uint32_t* flags_local, int rank,
+                        BnPeer* bp) {
+    bp->po = PeerOut::none();
+    bp->gathered = nullptr; bp->flags = nullptr; bp->rank = 0;
+    if (ch == nullptr) return SCB_OK;
+    SCB_REQUIRE(ch->state && ch->n_dst >= 1 && ch->n_dst <= 16 && gathered_local && flags_local && rank >= 0 &&
+                rank < ch->n_dst, "bn fused peers: bad channel, buffers or rank");
+    for (int w = 0; w < ch->n_dst; ++w)
+        SCB_REQUIRE(ch->dst[w] && ch->flag[w], "bn fused peers: destination %d is null", w);
+    bp->po = PeerOut::of(ch);
+    bp->gathered = gathered_local;
+    bp->flags = (const unsigned*)flags_local;
+    bp->rank = rank;
+    return SCB_OK;
+}
+
+static int bn_forward_fused_impl(const void* x, void* y, int dtype, int64_t rows, int channels,
+                                 const float* weight, const float* bias, float* running_mean,
+                                 float* running_var, float momentum, float eps, float* save_mean,
+                                 float* save_invstd, float* save_count, int flags, void* workspace,
+                                 int64_t workspace_bytes, void* stream_, const BnPeer& bp) {
     if (int e = check_bn_common(x, dtype, rows, channels, 1)) return e;
     SCB_REQUIRE(y && workspace && workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_forward_fused: bad buffers");
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -1158,7 +1269,7 @@ extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t r
             // other; cudaLaunchCooperativeKernel would add tens of microseconds of launch latency here.
             kern<<<grid, kFusedThreads, smem, stream>>>(xp, yp, M, C, TX, rpc, acc, counters, weight, bias, running_mean,
                                                         running_var, momentum, eps, save_mean, save_invstd, save_count,
-                                                        flags);
+                                                        flags, bp);
             SCB_CUDA_OK(cudaGetLastError());
             rc = SCB_OK;
         }
@@ -1168,10 +1279,10 @@ extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t r
     return SCB_OK;
 }
 
-extern "C" int scb_bn_backward_fused(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
-                                     const float* mean, const float* invstd, const float* weight, const float* bias,
-                                     const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
-                                     int flags, void* workspace, int64_t workspace_bytes, void* stream_) {
+static int bn_backward_fused_impl(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
+                                  const float* mean, const float* invstd, const float* weight, const float* bias,
+                                  const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
+                                  int flags, void* workspace, int64_t workspace_bytes, void* stream_, const BnPeer& bp) {
     if (int e = check_bn_common(x, dtype, rows, channels, 1)) return e;
     SCB_REQUIRE(dy && dx && mean && invstd && n_total && workspace &&
                 workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_backward_fused: bad buffers");
@@ -1197,7 +1308,7 @@ extern "C" int scb_bn_backward_fused(const void* dy, const void* x, void* dx, in
             const T* xp = (const T*)x;
             T* dxp = (T*)dx;
             kern<<<grid, kFusedThreads, smem, stream>>>(dyp, xp, dxp, M, C, TX, rpc, acc, counters, mean, invstd, weight,
-                                                        bias, n_total, out_sums, grad_weight, grad_bias, flags);
+                                                        bias, n_total, out_sums, grad_weight, grad_bias, flags, bp);
             SCB_CUDA_OK(cudaGetLastError());
             rc = SCB_OK;
         }
@@ -1205,4 +1316,53 @@ extern "C" int scb_bn_backward_fused(const void* dy, const void* x, void* dx, in
     if (rc == SCB_ERR_UNSUPPORTED) { set_error("bn_backward_fused: tensor does not fit one resident wave"); return rc; }
     count_launch();
     return SCB_OK;
+}
+
+extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t rows, int channels,
+                                    const float* weight, const float* bias, float* running_mean,
+                                    float* running_var, float momentum, float eps, float* save_mean,
+                                    float* save_invstd, float* save_count, int flags, void* workspace,
+                                    int64_t workspace_bytes, void* stream_) {
+    BnPeer bp;
+    make_bn_peer(nullptr, nullptr, nullptr, 0, &bp);
+    return bn_forward_fused_impl(x, y, dtype, rows, channels, weight, bias, running_mean, running_var, momentum, eps,
+                                 save_mean, save_invstd, save_count, flags, workspace, workspace_bytes, stream_, bp);
+}
+
+extern "C" int scb_bn_backward_fused(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
+                                     const float* mean, const float* invstd, const float* weight, const float* bias,
+                                     const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
+                                     int flags, void* workspace, int64_t workspace_bytes, void* stream_) {
+    BnPeer bp;
+    make_bn_peer(nullptr, nullptr, nullptr, 0, &bp);
+    return bn_backward_fused_impl(dy, x, dx, dtype, rows, channels, mean, invstd, weight, bias, n_total, out_sums,
+                                  grad_weight, grad_bias, flags, workspace, workspace_bytes, stream_, bp);
+}
+
+extern "C" int scb_bn_forward_fused_peers(const void* x, void* y, int dtype, int64_t rows, int channels,
+                                          const float* weight, const float* bias, float* running_mean,
+                                          float* running_var, float momentum, float eps, float* save_mean,
+                                          float* save_invstd, float* save_count, int flags, void* workspace,
+                                          int64_t workspace_bytes, const scb_peer_channel* ch,
+                                          const float* gathered_local, const uint32_t* flags_local, int rank,
+                                          void* stream_) {
+    SCB_REQUIRE(ch != nullptr, "bn_forward_fused_peers: null channel");
+    BnPeer bp;
+    if (int e = make_bn_peer(ch, gathered_local, flags_local, rank, &bp)) return e;
+    return bn_forward_fused_impl(x, y, dtype, rows, channels, weight, bias, running_mean, running_var, momentum, eps,
+                                 save_mean, save_invstd, save_count, flags, workspace, workspace_bytes, stream_, bp);
+}
+
+extern "C" int scb_bn_backward_fused_peers(const void* dy, const void* x, void* dx, int dtype, int64_t rows,
+                                           int channels, const float* mean, const float* invstd, const float* weight,
+                                           const float* bias, const float* n_total, float* out_sums,
+                                           float* grad_weight, float* grad_bias, int flags, void* workspace,
+                                           int64_t workspace_bytes, const scb_peer_channel* ch,
+                                           const float* gathered_local, const uint32_t* flags_local, int rank,
+                                           void* stream_) {
+    SCB_REQUIRE(ch != nullptr, "bn_backward_fused_peers: null channel");
+    BnPeer bp;
+    if (int e = make_bn_peer(ch, gathered_local, flags_local, rank, &bp)) return e;
+    return bn_backward_fused_impl(dy, x, dx, dtype, rows, channels, mean, invstd, weight, bias, n_total, out_sums,
+                                  grad_weight, grad_bias, flags, workspace, workspace_bytes, stream_, bp);
 }

@@ -83,22 +83,39 @@ class _Kernels:
         return bool(lib.scb_bn_fused_supported(_lib.dtype_code(x.dtype), cl, outer, C, inner))
 
     @classmethod
-    def forward_fused(cls, x, y, geom, weight, bias, running_mean, running_var, momentum, eps, saved, flags):
+    def forward_fused(cls, x, y, geom, weight, bias, running_mean, running_var, momentum, eps, saved, flags,
+                      peer=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
         ws = cls.workspace(lib, x.device, C)
+        if peer is not None:       # (channel struct, gathered_local ptr, flags_local ptr, rank)
+            import ctypes
+            return lib.scb_bn_forward_fused_peers(
+                x.data_ptr(), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
+                p(weight), p(bias), p(running_mean), p(running_var), momentum, eps,
+                saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), saved[2 * C:].data_ptr(),
+                flags, ws.data_ptr(), ws.numel(), ctypes.byref(peer[0]), peer[1], peer[2], peer[3],
+                cls.stream(x.device))
         return lib.scb_bn_forward_fused(x.data_ptr(), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
                                         p(weight), p(bias), p(running_mean), p(running_var), momentum, eps,
                                         saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), saved[2 * C:].data_ptr(),
                                         flags, ws.data_ptr(), ws.numel(), cls.stream(x.device))
 
     @classmethod
-    def backward_fused(cls, dy, x, dx, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags):
+    def backward_fused(cls, dy, x, dx, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags, peer=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
         ws = cls.workspace(lib, x.device, C)
+        if peer is not None:
+            import ctypes
+            return lib.scb_bn_backward_fused_peers(
+                dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _lib.dtype_code(x.dtype),
+                outer * inner, C, saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(),
+                p(weight), p(bias), saved[2 * C:].data_ptr(), sums.data_ptr(),
+                p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(),
+                ctypes.byref(peer[0]), peer[1], peer[2], peer[3], cls.stream(x.device))
         return lib.scb_bn_backward_fused(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _lib.dtype_code(x.dtype),
                                          outer * inner, C, saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(),
                                          p(weight), p(bias), saved[2 * C:].data_ptr(), sums.data_ptr(),
@@ -173,6 +190,25 @@ class _PeerStats:
             self.ptrs.append((ctypes.c_void_p * world)(*[int(p) for p in h.buffer_ptrs]))
         self.seg = (ctypes.c_int64 * 3)(0, rank * n * 4, n * 4)
         self.calls = 0
+        # in-kernel exchange of the fused kernels: flag words (one per rank) in symmetric memory, local counter
+        self.rank = rank
+        fl = symm.empty((16,), dtype=torch.int32, device=dev)
+        fl.zero_()
+        fh = symm.rendezvous(fl, group)
+        torch.cuda.synchronize(dev)
+        fh.barrier(channel=0)                 # nobody raises a flag before everybody has cleared its own
+        torch.cuda.synchronize(dev)
+        self.flags, self.flags_handle = fl, fh
+        self.state = torch.zeros(2, dtype=torch.int32, device=dev)
+        self.channels = []
+        for g in range(self.GENERATIONS):
+            ch = _lib.PeerChannel()
+            for w in range(world):
+                ch.dst[w] = int(self.handles[g].buffer_ptrs[w])
+                ch.flag[w] = int(fh.buffer_ptrs[w]) + rank * 4
+            ch.state = self.state.data_ptr()
+            ch.n_dst = world
+            self.channels.append(ch)
 
     @classmethod
     def get(cls, group, dev, n, world, rank):
@@ -191,6 +227,12 @@ class _PeerStats:
                 warnings.warn('peer-memory exchange unavailable (%s); SyncBatchNorm uses NCCL' % (e,))
                 return None
         return cls._cache[key]
+
+    def fused_peer(self):
+        """Arguments of the next in-kernel exchange: (channel, gathered_local ptr, flags_local ptr, rank)."""
+        g = self.calls % self.GENERATIONS
+        self.calls += 1
+        return (self.channels[g], self.bufs[g].data_ptr(), self.flags.data_ptr(), self.rank)
 
     def all_gather(self, src, dev):
         """src: n floats of this rank -> [world * n] floats, rank-major (valid until GENERATIONS-1 further calls)."""
@@ -221,14 +263,25 @@ class _SyncBNFunction(torch.autograd.Function):
         rm, rv = _f32(running_mean), _f32(running_var)
         dev = x.device
         flags = _lib.BN_RELU if fuse_relu else 0
-        fused = (use_batch_stats and world_size == 1 and hasattr(kern, 'fused_supported')
-                 and kern.fused_supported(x, geom))
+        fused = (use_batch_stats and hasattr(kern, 'fused_supported') and kern.fused_supported(x, geom))
+        px = None
+        if fused and world_size > 1:
+            # several ranks: the fused kernel exchanges the statistics itself over peer memory.  Needs every
+            # rank to take this path (same per-rank shape); SCB_BN_FUSED_PEERS=0 keeps the four-kernel path.
+            import os
+            px = (_PeerStats.get(process_group, dev, 2 * C + 1, world_size, dist.get_rank(process_group))
+                  if kern is _Kernels and os.environ.get('SCB_BN_FUSED_PEERS', '1') != '0' else None)
+            fused = px is not None
         ctx.fused = False
         if fused:
-            # one rank, tensor fits one resident wave: statistics + normalisation in a single launch
+            # tensor fits one resident wave: statistics (+ exchange) + normalisation in a single launch
             y = torch.empty_like(x)
             saved = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
-            rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags)
+            if px is not None:
+                rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags,
+                                        peer=px.fused_peer())
+            else:
+                rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags)
             if rc == 0:
                 if rm is not running_mean and running_mean is not None:
                     running_mean.copy_(rm)
@@ -291,9 +344,16 @@ class _SyncBNFunction(torch.autograd.Function):
         sums, gw, gb = out[0:2 * C], out[2 * C:3 * C], out[3 * C:]
         grad_input = None
         done = False
-        if ctx.fused and ctx.needs_input_grad[0]:
+        px = None
+        if ctx.fused and ctx.world_size > 1:
+            px = _PeerStats.get(ctx.process_group, dev, 2 * C, ctx.world_size, dist.get_rank(ctx.process_group))
+        if ctx.fused and ctx.needs_input_grad[0] and (ctx.world_size == 1 or px is not None):
             grad_input = torch.empty_like(x)
-            rc = kern.backward_fused(dy, x, grad_input, geom, saved, w32, b32, sums, gw, gb, flags)
+            if px is not None:
+                rc = kern.backward_fused(dy, x, grad_input, geom, saved, w32, b32, sums, gw, gb, flags,
+                                         peer=px.fused_peer())
+            else:
+                rc = kern.backward_fused(dy, x, grad_input, geom, saved, w32, b32, sums, gw, gb, flags)
             if rc == 0:
                 done = True
             elif rc != -3:
