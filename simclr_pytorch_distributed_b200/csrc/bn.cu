@@ -84,12 +84,13 @@ __device__ __forceinline__ void cta_reduce_to_global(float (&a)[VEC], float (&b)
         }
     }
     __syncthreads();
+    const int tile_c = c0 - tx * VEC;         // first channel of this CTA's tile
     for (int t = threadIdx.x; t < 2 * W; t += blockDim.x) {
         const int which = t / W, col = t - which * W;
         const float* s = which ? sb : sa;
         float tot = 0.f;
         for (int r = 0; r < TY; ++r) tot += s[r * W + col];
-        const int c = c0 - tx * VEC + col;    // c0 - tx*VEC = first channel of this CTA's tile
+        const int c = tile_c + col;
         if (c < C) atomicAdd((which ? acc_b : acc_a) + c, tot);
     }
 }
@@ -1060,7 +1061,9 @@ bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, 
     }
 }
 
-template <typename T, int VEC>
+// kRelu is a template parameter: without it the kernel keeps eight fewer per-channel values alive across the
+// barrier (gate scale / offset, gate bits) and fits its 64 registers without spilling.
+template <typename T, int VEC, bool kRelu>
 __global__ void __launch_bounds__(kFusedThreads, 1)
 bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t M, int C, int TX,
                          int64_t rows_per_cta, float* __restrict__ acc, unsigned* counters,
@@ -1074,7 +1077,7 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = (blockIdx.x * TX + tx) * VEC;
     const bool active = c0 < C;
-    const bool relu = (flags & SCB_BN_RELU) != 0;
+    (void)flags;
     const unsigned total = gridDim.x * gridDim.y;
     const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta + ty;
@@ -1098,8 +1101,10 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
 #pragma unroll
         for (int i = 0; i < VEC; ++i) {
             mu[i] = mean[c0 + i];
-            k1[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
-            bb[i] = bias ? bias[c0 + i] : 0.f;
+            if (kRelu) {
+                k1[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
+                bb[i] = bias ? bias[c0 + i] : 0.f;
+            }
         }
 #pragma unroll
         for (int u = 0; u < kFusedRows; ++u) {
@@ -1111,7 +1116,7 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
                 for (int i = 0; i < VEC; ++i) {
                     const float xm = to_f32(ex[i]) - mu[i];
                     float g = to_f32(ed[i]);
-                    if (relu && !(fmaf(xm, k1[i], bb[i]) > 0.f)) { g = 0.f; gated[u] |= 1u << i; }
+                    if (kRelu && !(fmaf(xm, k1[i], bb[i]) > 0.f)) { g = 0.f; gated[u] |= 1u << i; }
                     s1[i] += g;
                     s2[i] = fmaf(g, xm, s2[i]);
                 }
@@ -1175,6 +1180,10 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
     float k2[VEC], k3[VEC];
 #pragma unroll
     for (int i = 0; i < VEC; ++i) { k2[i] = sm[tx * VEC + i]; k3[i] = sm[W + tx * VEC + i]; }
+    if (!kRelu && active) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) k1[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
+    }
     rearm_scratch(acc, counters, total, R * 2 * C);
     if (!active) return;
     T* po = dx + r0 * C + c0;
@@ -1188,7 +1197,7 @@ bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
 #pragma unroll
             for (int i = 0; i < VEC; ++i) {
                 const float xm = to_f32(ex[i]) - mu[i];
-                const float g = ((gated[u] >> i) & 1u) ? 0.f : to_f32(ed[i]);
+                const float g = (kRelu && ((gated[u] >> i) & 1u)) ? 0.f : to_f32(ed[i]);
                 oe[i] = from_f32<T>((g - k2[i] - xm * k3[i]) * k1[i]);
             }
             stg_stream16(po + u * step, o);
@@ -1295,7 +1304,7 @@ static int bn_backward_fused_impl(const void* dy, const void* x, void* dx, int d
     SCB_DISPATCH_FLOAT(dtype, T, {
         constexpr int VEC = Vec16<T>::N;
         NhwcGeom g;
-        auto kern = bn_bwd_fused_nhwc_kernel<T, VEC>;
+        auto kern = (flags & SCB_BN_RELU) ? bn_bwd_fused_nhwc_kernel<T, VEC, true> : bn_bwd_fused_nhwc_kernel<T, VEC, false>;
         const size_t smem = 2 * kFusedThreads * VEC * sizeof(float);
         set_max_dynamic_smem(kern, (int)smem);
         const int per_sm = fused_ctas_per_sm(kern, smem);

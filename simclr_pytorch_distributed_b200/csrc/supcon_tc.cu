@@ -2,20 +2,22 @@
 // recompute backward that never write a similarity tile to memory.
 //
 //   * K (the [n_k, ldk] bf16 contrast matrix) is staged by TMA (cp.async.bulk.tensor, 128-byte
-//     swizzle) in [128 rows x 64 col] sub-tiles; a CTA owns a 256-row block (two 128-row halves)
-//     and walks a contiguous span of 128-column tiles, so every B tile feeds two MMAs.
+//     swizzle) in [128 rows x 64 col] sub-tiles.  The forward walks 256-row blocks (two UMMA M = 128
+//     halves, every B tile feeds two MMAs), the backward 128-row blocks; column tiles are 128 wide.
 //   * S = K_i K_j^T runs on tcgen05.mma (kind::f16, M=128, N=128, K=16) with fp32 accumulators in
 //     TMEM; one elected thread issues, completion is tracked with tcgen05.commit -> mbarrier.
-//   * two epilogue warpgroups (one per half) pull S out of TMEM with tcgen05.ld and keep the
-//     online (max, sum exp, positive sum) row state in registers              -> forward
-//     or turn S into P = dL/dS (bf16, written to shared memory in the UMMA K-major layout) which
-//     a second tcgen05.mma multiplies with the very same K_j tile read MN-major, accumulating
-//     dK_i in TMEM                                                            -> backward
+//   * forward: four epilogue warpgroups pull S out of TMEM with tcgen05.ld and keep the online
+//     (max, sum exp, positive sum) row state in registers.
+//   * backward: the epilogue turns S into P = dL/dS, packs it to bf16 and writes it back into TMEM over the
+//     S columns it came from; a second tcgen05.mma takes P as its A operand from TMEM and the very same K_j
+//     tile, read MN-major, as B: dK_i accumulates in TMEM.  (Structure and the measurements behind it:
+//     comment above supcon_tc_bwd_kernel and DESIGN.md section 3.2.)
 //
 // Reference being replaced: /root/reference/losses.py:64-91 and its autograd backward.
 // Work split: the RB x CT tile grid is flattened row-block-major and cut into equal spans, one
 // per CTA (persistent, one CTA per SM); partial row results of CTAs that share a row block are
-// merged by the finalize kernel (forward) or by vector float reductions into dK (backward).
+// merged by the finalize kernel (forward) or summed from per-CTA partial dK blocks by the reduce
+// kernels (backward): no float atomics anywhere.
 #include "supcon_tc.cuh"
 #include "supcon_common.cuh"
 #include "tc_ptx.cuh"
