@@ -1029,6 +1029,13 @@ static int make_tmap(const scb_supcon_problem* p, CUtensorMap* out) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return SCB_ERR_CUDA; }
     SCB_REQUIRE((reinterpret_cast<uintptr_t>(p->k) & 15u) == 0, "supcon: k must be 16-byte aligned");
+    // the descriptor depends on (address, rows, row stride) only: forward and backward of a step, and every
+    // step of a training loop that re-uses its buffers, hit this small per-thread cache instead of the driver
+    struct Entry { const void* k; int n_k, ldk; CUtensorMap map; };
+    static thread_local Entry cache[4] = {};
+    static thread_local int next = 0;
+    for (const Entry& e : cache)
+        if (e.k == p->k && e.n_k == p->n_k && e.ldk == p->ldk) { *out = e.map; return SCB_OK; }
     cuuint64_t gdim[2] = {(cuuint64_t)p->ldk, (cuuint64_t)p->n_k};
     cuuint64_t gstride[1] = {(cuuint64_t)p->ldk * 2};
     cuuint32_t box[2] = {64, 128};
@@ -1037,6 +1044,8 @@ static int make_tmap(const scb_supcon_problem* p, CUtensorMap* out) {
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with code %d", (int)r); return SCB_ERR_CUDA; }
+    cache[next] = Entry{p->k, p->n_k, p->ldk, *out};
+    next = (next + 1) & 3;
     return SCB_OK;
 }
 

@@ -31,8 +31,8 @@ class _Workspace:
     _cache = {}
 
     @classmethod
-    def get(cls, device, nbytes):
-        key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    def get(cls, device, nbytes, stream=None):
+        key = (device.index, stream if stream is not None else torch.cuda.current_stream(device).cuda_stream)
         buf = cls._cache.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = torch.zeros(_round_up(max(nbytes, 1 << 16), 256), dtype=torch.uint8, device=device)
@@ -102,6 +102,36 @@ def _stream(device):
     return torch.cuda.current_stream(device).cuda_stream
 
 
+class _on_device:
+    """`with torch.cuda.device(dev)` that costs nothing when `dev` is already current (the usual case:
+    one process per GPU); the eager module API is host-bound, every microsecond of Python counts."""
+    __slots__ = ('ctx',)
+
+    def __init__(self, dev):
+        self.ctx = None if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+        return False
+
+
+_WS_BYTES = {}
+
+
+def _workspace_need(lib, prob, plan):
+    """scb_supcon_workspace_bytes, remembered per problem shape."""
+    key = (plan.n_k, plan.rows_local, plan.ldk, plan.engine, plan.mask_kind)
+    need = _WS_BYTES.get(key)
+    if need is None:
+        need = _WS_BYTES[key] = lib.scb_supcon_workspace_bytes(ctypes.byref(prob), plan.rows_local)
+    return need
+
+
 def launch_prep(lib, feats, plan, normalize, k_rows, k_lo_rows, inv_norm):
     """feats [n_local, V, D] (last dim contiguous) -> rows of the contrast matrix (scb_supcon_prep)."""
     _lib.check(lib.scb_supcon_prep(
@@ -113,16 +143,17 @@ def launch_prep(lib, feats, plan, normalize, k_rows, k_lo_rows, inv_norm):
 
 
 def launch_forward(lib, prob, plan, lse, possum, npos, loss, device):
-    need = lib.scb_supcon_workspace_bytes(ctypes.byref(prob), plan.rows_local)
-    ws = _Workspace.get(device, need)
+    need = _workspace_need(lib, prob, plan)
+    st = _stream(device)
+    ws = _Workspace.get(device, need, st)
     _lib.check(lib.scb_supcon_forward(
         ctypes.byref(prob), plan.row_begin, plan.rows_local, plan.n_anchor_total,
         lse.data_ptr(), possum.data_ptr(), npos.data_ptr(), loss.data_ptr(),
-        ws.data_ptr(), ws.numel(), _stream(device)), 'scb_supcon_forward')
+        ws.data_ptr(), ws.numel(), st), 'scb_supcon_forward')
 
 
 def launch_backward(lib, prob, plan, lse_all, npos_all, grad_out, dk, device):
-    need = lib.scb_supcon_workspace_bytes(ctypes.byref(prob), plan.rows_local)
+    need = _workspace_need(lib, prob, plan)
     ws = _Workspace.get(device, need)
     _lib.check(lib.scb_supcon_backward(
         ctypes.byref(prob), plan.row_begin, plan.rows_local, lse_all.data_ptr(), npos_all.data_ptr(),
@@ -132,13 +163,14 @@ def launch_backward(lib, prob, plan, lse_all, npos_all, grad_out, dk, device):
 
 def launch_backward_features(lib, prob, plan, lse_all, npos_all, grad_out, feats, normalize, inv_norm, dfeats, device):
     """Backward + finish in one call (tensor-core engines): scb_supcon_backward_features."""
-    need = lib.scb_supcon_workspace_bytes(ctypes.byref(prob), plan.rows_local)
-    ws = _Workspace.get(device, need)
+    need = _workspace_need(lib, prob, plan)
+    st = _stream(device)
+    ws = _Workspace.get(device, need, st)
     _lib.check(lib.scb_supcon_backward_features(
         ctypes.byref(prob), plan.row_begin, plan.rows_local, lse_all.data_ptr(), npos_all.data_ptr(),
         grad_out.data_ptr(), plan.n_anchor_total, feats.data_ptr(), _lib.dtype_code(feats.dtype), plan.n_local,
         feats.stride(0), feats.stride(1), int(normalize), inv_norm.data_ptr() if inv_norm is not None else None,
-        dfeats.data_ptr(), dfeats.stride(0), dfeats.stride(1), ws.data_ptr(), ws.numel(), _stream(device)),
+        dfeats.data_ptr(), dfeats.stride(0), dfeats.stride(1), ws.data_ptr(), ws.numel(), st),
         'scb_supcon_backward_features')
 
 
@@ -174,7 +206,7 @@ class _SupConFunction(torch.autograd.Function):
     def forward(ctx, feats, labels, mask, plan, temperature, base_temperature, normalize):
         lib = _lib.load()
         dev = feats.device
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             n_k, ldk = plan.n_k, plan.ldk
             # bf16 features that are already laid out as [bsz * n_views, ldk] need neither the stacking copy
             # (losses.py:53) nor a cast: the kernels take the rows in the samples' own order
@@ -193,7 +225,7 @@ class _SupConFunction(torch.autograd.Function):
                 launch_prep(lib, feats, plan, normalize, k, k_lo, inv_norm)
             prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
             launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
-        ctx.plan, ctx.prob_args = plan, (temperature, base_temperature, normalize)
+        ctx.plan, ctx.prob_args, ctx.prob = plan, (temperature, base_temperature, normalize), prob
         ctx.save_for_backward(feats, labels, mask, k, k_lo, stats)
         return typed_loss(loss, feats.dtype)
 
@@ -204,9 +236,9 @@ class _SupConFunction(torch.autograd.Function):
         temperature, base_temperature, normalize = ctx.prob_args
         lib = _lib.load()
         dev = feats.device
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             g = grad_scalar(grad_out, feats.dtype)
-            prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
+            prob = ctx.prob          # the struct built by forward (its pointers are kept alive by the saved tensors)
             dfeats = torch.empty(feats.shape, dtype=feats.dtype, device=dev)
             inv_norm = stats[3] if normalize else None
             if plan.engine != _lib.ENGINE_FP32:
