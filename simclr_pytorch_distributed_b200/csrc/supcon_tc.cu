@@ -1085,9 +1085,16 @@ static TcGeom tc_geom_bwd(int n_k, int rows) {
     int q = (int)ceil_div(g.T, sm_count());
     const int qmin = (int)ceil_div(g.CT, kMaxDkSlots - 1);
     if (q < qmin) q = qmin;
+    // A span that stays inside one row block saves its CTA a mid-kernel drain (3.3 us) and the reduce kernel a
+    // slot: take the next q that divides CT (or is a multiple of it) when that costs at most 15 % more tiles
+    // per CTA.
+    bool aligned = false;
+    for (int qa = q; qa * 100 <= q * 115; ++qa)
+        if (g.CT % qa == 0 || qa % g.CT == 0) { q = qa; aligned = true; break; }
     g.q = q;
     g.grid = (int)ceil_div(g.T, q);
-    g.n_split = (int)ceil_div(g.CT, q) + 1;
+    g.n_split = aligned ? (int)ceil_div(g.CT, q) : (int)ceil_div(g.CT, q) + 1;
+    if (g.n_split < 1) g.n_split = 1;
     if (g.n_split > kMaxDkSlots) g.n_split = kMaxDkSlots;
     return g;
 }
