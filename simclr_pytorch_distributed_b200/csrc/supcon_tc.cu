@@ -425,6 +425,18 @@ __device__ __forceinline__ void warp_transpose32(uint32_t (&v)[32], int lane) {
     }
 }
 
+// One warp's [32 rows x 32 columns] block of dK: TMEM -> registers -> transposed, coalesced stores.  Out of line
+// (scalar arguments only): it runs once or twice per CTA and its ~600 instructions would otherwise sit in the
+// middle of the epilogue's loop code.
+__device__ __noinline__ void drain_block(uint32_t taddr, float* dst, int ldk, int lane) {
+    uint32_t v[32];
+    tmem_ld32(taddr, v);
+    tmem_ld_wait_dep(v);
+    warp_transpose32(v, lane);
+#pragma unroll
+    for (int rr = 0; rr < 32; ++rr) dst[(int64_t)rr * ldk] = __uint_as_float(v[rr]);
+}
+
 // pack pv[off .. off+15] to bf16 and write them as 8 consecutive 32-bit TMEM columns of this thread's lane
 // (UMMA A operand in TMEM: two K-consecutive bf16 per column, even index in the low half)
 template <int N>
@@ -687,12 +699,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 // rows of this warp: q4*32 .. +32; after the transpose a store covers 128 contiguous bytes
                 float* dst = p.dk_part + ((int64_t)slot * p.RB * kBMB + (int64_t)rb_ * kBMB + q4 * 32) * p.ldk +
                              g * 32 + lane;
-                uint32_t v[32];
-                tmem_ld32(tmem_base + lane_addr + kDkCol + g * 32, v);
-                tmem_ld_wait_dep(v);
-                warp_transpose32(v, lane);
-#pragma unroll
-                for (int rr = 0; rr < 32; ++rr) dst[(int64_t)rr * p.ldk] = __uint_as_float(v[rr]);
+                drain_block(tmem_base + lane_addr + kDkCol + g * 32, dst, p.ldk, lane);
             }
             tc_fence_before();
             __syncwarp();
