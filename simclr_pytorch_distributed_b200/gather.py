@@ -204,8 +204,17 @@ class _DistSupConFunction(torch.autograd.Function):
             ctx.plan, ctx.args = plan, (temperature, base_temperature, normalize)
             ctx.save_for_backward(feats, labels_all, k_all, lse_all, npos_all, inv_norm)
             return L.typed_loss(loss2, feats.dtype)
-        k_local = torch.empty((rows, ldk), dtype=plan.k_torch, device=dev)
-        ops.prep(lib, feats, plan, normalize, k_local, None, inv_norm)
+        # bf16 features that need no normalisation are this rank's rows already (sample-major order inside the
+        # segment, include/simclr_b200.h): no stacking copy, the exchange reads them where they are
+        zero_copy = (ops.requires_cuda and plan.engine == _lib.ENGINE_BF16 and feats.dtype == torch.bfloat16 and
+                     not normalize and plan.mode == _lib.MODE_ALL and feats.is_contiguous() and plan.dim == ldk and
+                     feats.data_ptr() % 16 == 0)
+        if zero_copy:
+            plan.row_layout = _lib.ROWS_SAMPLE_MAJOR
+            k_local = feats.detach().view(rows, ldk)
+        else:
+            k_local = torch.empty((rows, ldk), dtype=plan.k_torch, device=dev)
+            ops.prep(lib, feats, plan, normalize, k_local, None, inv_norm)
         if px is not None:
             k_all = px.share_rows(lib, gen, k_local, dev)                        # exchange 1 over peer memory
         else:

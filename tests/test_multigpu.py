@@ -102,6 +102,22 @@ def _worker(rank, world, port, q):
                 if step == 0:
                     notes.append('loss %s via %s: rel loss %.2e rel grad %.2e' % (engine, used, e_l, e_g))
                 ok = ok and e_l <= tol and e_g <= 2 * tol
+        # ---------------- pre-normalised bf16 embeddings, normalize=False: the rows are used in place
+        # (sample-major order, no stacking copy) on both exchange paths
+        for p2p in ('1', '0'):
+            os.environ['SCB_P2P'] = p2p
+            rng = np.random.default_rng(7)
+            zh = torch.from_numpy(normalize_rows(rng.standard_normal((world * bsz, V, D)))).to(torch.bfloat16)
+            sl = slice(rank * bsz, (rank + 1) * bsz)
+            f = zh[sl].to(dev).requires_grad_(True)
+            loss = DistributedSupConLoss(temperature=0.5, engine='bf16', normalize=False)(f)
+            loss.backward()
+            ref_loss, g_hat, _ = supcon_forward_backward(zh.double().numpy(), temperature=0.5)
+            e_l = abs(float(loss) - ref_loss) / abs(ref_loss)
+            e_g = (np.linalg.norm((f.grad.double().cpu().numpy() - g_hat[sl]).ravel()) /
+                   np.linalg.norm(g_hat[sl].ravel()))
+            notes.append('loss bf16 in place, p2p=%s: rel loss %.2e rel grad %.2e' % (p2p, e_l, e_g))
+            ok = ok and e_l <= 2e-3 and e_g <= 2 * (2e-3 + 2 ** -8)
     except Exception as e:     # report instead of hanging the other ranks
         ok = False
         notes.append('EXC %r' % (e,))
