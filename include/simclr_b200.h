@@ -61,8 +61,9 @@ int scb_version(void);
 int scb_device_cc(void);
 /* number of kernels this library has launched in this process so far (bench bookkeeping) */
 int64_t scb_launch_count(void);
-/* diagnostics only: a device buffer of 3*1024 int64 that CTA 0 of the tensor-core backward fills
- * with (event id, SM clock) pairs per role (0 MMA issuer, 1/2 epilogue warpgroups); NULL = off */
+/* diagnostics only, effective in builds with -DSCB_TRACE=1 (tools/build_trace_lib.sh): a device buffer of
+ * 6*1024 int64 that the tensor-core kernels fill with (event id, %globaltimer ns) pairs per role of CTA 0 and
+ * with the entry / exit times of every CTA (tools/trace_fwd.py, tools/trace_bwd.py read it); NULL = off */
 int scb_debug_set_trace(void* device_buffer);
 /* measurement aid (bench.py): two cudaEvent_t that the tensor-core backward records on its stream right
  * before and right after its main kernel, so that the kernel can be timed alone; NULL, NULL = off */

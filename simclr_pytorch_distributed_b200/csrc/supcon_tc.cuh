@@ -21,8 +21,8 @@ int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
                          int n_samples, int64_t stride_s, int64_t stride_v, int normalize, const float* inv_norm,
                          void* out, int64_t ostride_s, int64_t ostride_v, void* workspace, cudaStream_t stream);
 
-// diagnostics: device buffer of 3 x 1024 int64 that CTA 0 of the backward kernel fills with
-// (event id, clock64) pairs; nullptr switches tracing off
+// diagnostics (-DSCB_TRACE=1 builds): device buffer of 6 x 1024 int64 for (event id, %globaltimer) pairs of
+// CTA 0's roles and the entry / exit time of every CTA; nullptr switches tracing off
 void tc_set_trace(long long* p);
 // measurement aid: CUDA events recorded around the backward main kernel (nullptr = off)
 void tc_set_events(void* start, void* stop);
