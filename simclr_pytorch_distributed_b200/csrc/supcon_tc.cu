@@ -41,6 +41,38 @@ constexpr float kSafeSpread = 60.f;
 // epilogues are bound by per-tile latency, not by the MUFU pipe, so it stays off.
 constexpr int kPolyLane = SCB_POLY_LANE;
 
+// Merge of the forward's per-CTA row partials inside the forward kernel itself: the last CTA to deliver its
+// partials for a row block (ticket per row block) turns them into lse / possum / npos and the block's share of
+// the loss; the last row block to finish adds the shares in block order (deterministic) and writes the scalar.
+struct FwdOut {
+    unsigned* rb_count;     // [RB] tickets, zero on entry, zero again on exit
+    unsigned* done_count;   // row blocks merged so far (self re-arming)
+    double* rb_loss;        // [RB] per-row-block sums of -(T/Tb)(possum/npos - lse)
+    float* out_lse;
+    float* out_possum;
+    float* out_npos;
+    float* out_loss;        // [0] fp32 value, [1] value in scalar_dtype (low-order bytes)
+    float loss_scale;
+    double inv_anchors;
+    int scalar_dtype;
+    int n_k, my_slot;       // peers: layout of every rank's [lse (n_k) | npos (n_k) | loss shares] array
+    PeerOut po;             // n_dst > 0: lse / npos / loss share go to every rank, then the flags are raised
+};
+
+// Everything the last step of the backward needs to turn a summed dK row into d features: scale by the upstream
+// gradient, closed-form positive-pair term (fp32), un-stack, backward of the optional L2 normalisation, cast.
+struct FinishParams {
+    const void* feat;       // features [n_samples, n_views, dim] (only read when normalize != 0)
+    void* out;              // d features, same dtype
+    int feat_dtype, n_samples, normalize;
+    int64_t stride_s, stride_v, ostride_s, ostride_v;
+    const float* inv_norm;
+    int grad_dtype;
+    float coef_scale_invT;  // (T/Tb) / n_anchor_total / T
+    const float* cls_all;   // labels: [n_samples_total][ldk] sum of the rows of the class (slot = representative sample)
+    const float* cls_anc;   // labels: same over the anchor rows only (== cls_all in mode `all`)
+};
+
 struct TcParams {
     const __nv_bfloat16* k;
     int ldk, n_k, dim;
@@ -50,7 +82,7 @@ struct TcParams {
     int n_views, mode, mask_kind;
     float c2, inv_T;                    // log2(e)/T, 1/T
     float* part;                        // forward partials [slot][4][n_rows]
-    const int* rep_row;                 // labels: class representative per global row
+    const int* rep_row;                 // labels: class representative (a sample id) per global row
     const float* npos_row;              // labels: number of positives per global row
     const float* nia_row;               // labels: [anchor]/npos per global row
     const float* lse_all;
@@ -59,6 +91,9 @@ struct TcParams {
     float* out_dk;
     int ld_dk;
     float* dk_part;                     // backward partials [slot][RB*128][ldk] (one slot per CTA sharing a row block)
+    int pair;                           // backward, direct finish: CTAs per row block (1, or 2 = a cluster pair)
+    FwdOut fo;
+    FinishParams fin;
     long long* trace;                   // optional (debug): per-role timestamps of CTA 0
 };
 
@@ -116,11 +151,138 @@ __device__ __forceinline__ float bf16_dot_rows(const __nv_bfloat16* a, const __n
     return acc;
 }
 
+__device__ __forceinline__ double warp_sum_f64(double v) {      // fixed xor tree: deterministic
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ void store_loss_scalar(float* out, float loss, int scalar_dtype) {
+    out[0] = loss;
+    out[1] = 0.f;                         // [1]: the loss in the caller's scalar dtype (low-order bytes)
+    if (scalar_dtype == SCB_BF16) *reinterpret_cast<__nv_bfloat16*>(out + 1) = __float2bfloat16_rn(loss);
+    else if (scalar_dtype == SCB_F16) *reinterpret_cast<__half*>(out + 1) = __float2half_rn(loss);
+    else out[1] = loss;
+}
+
+// Called by the 512 epilogue threads of the CTA that delivered the LAST partials of row block `rb` (losses.py:83-91
+// for those 256 rows): merges the (max, sum, possum, npos) slots of every row, writes lse / possum / npos, and leaves
+// the block's share of the loss in rb_loss[rb]; whoever completes the last row block adds the shares in block order.
+// Out of line: it runs once or twice per CTA and must not sit in the middle of the tile loop's code.
+__device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta, double* s_red) {
+    const int e = (int)threadIdx.x - 64;          // 0..511
+    const FwdOut& o = p.fo;
+    __threadfence();                              // acquire side of the row-block ticket
+    double contrib = 0.0;
+    const int li = rb * kBM + e;
+    if (e < kBM && li < p.a_count) {
+        const int n_split = 2 * n_cta;
+        float m = -INFINITY, sum = 0.f, ps = 0.f, np = 0.f;
+        for (int s0 = 0; s0 < n_split; s0 += 8) {          // eight slots at a time: their loads are in flight together
+            float vm[8], vs[8], vp[8], vn[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const bool ok = s0 + u < n_split;
+                const float* q = p.part + ((int64_t)(s0 + u) * 4) * p.n_rows + li;
+                vm[u] = ok ? __ldcg(q) : -INFINITY;
+                vs[u] = ok ? __ldcg(q + p.n_rows) : 0.f;
+                vp[u] = ok ? __ldcg(q + 2 * (int64_t)p.n_rows) : 0.f;
+                vn[u] = ok ? __ldcg(q + 3 * (int64_t)p.n_rows) : 0.f;
+            }
+            float cm = vm[0];
+#pragma unroll
+            for (int u = 1; u < 8; ++u) cm = fmaxf(cm, vm[u]);
+            const float nm = fmaxf(m, cm);
+            if (nm > -INFINITY) {
+                float acc = (m > -INFINITY) ? sum * expf(m - nm) : 0.f;
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (vm[u] > -INFINITY) acc += vs[u] * expf(vm[u] - nm);
+                sum = acc;
+                m = nm;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { ps += vp[u]; np += vn[u]; }
+        }
+        const float lse = m + logf(sum);
+        contrib = (double)(-o.loss_scale * (ps / np - lse));          // losses.py:87,90 (0/0 -> nan)
+        o.out_possum[li] = ps;
+        if (o.po.n_dst > 0) {
+            for (int w = 0; w < o.po.n_dst; ++w) {
+                float* d = reinterpret_cast<float*>(o.po.dst[w]);
+                d[p.row_begin + li] = lse;
+                d[o.n_k + p.row_begin + li] = np;
+            }
+        } else {
+            o.out_lse[li] = lse;
+            o.out_npos[li] = np;
+        }
+    }
+    if (p.n_rows > p.a_count) {
+        // local rows that are not anchors (mode `one`, views > 0): lse = 0, possum = 0, npos = 1; every merging CTA
+        // fills its share of them
+        const int extra = p.n_rows - p.a_count, chunk = (extra + p.RB - 1) / p.RB;
+        const int x1 = min(extra, (rb + 1) * chunk);
+        for (int x = rb * chunk + e; x < x1; x += 512) {
+            const int r = p.a_count + x;
+            o.out_possum[r] = 0.f;
+            if (o.po.n_dst > 0) {
+                for (int w = 0; w < o.po.n_dst; ++w) {
+                    float* d = reinterpret_cast<float*>(o.po.dst[w]);
+                    d[p.row_begin + r] = 0.f;
+                    d[o.n_k + p.row_begin + r] = 1.f;
+                }
+            } else {
+                o.out_lse[r] = 0.f;
+                o.out_npos[r] = 1.f;
+            }
+        }
+    }
+    contrib = warp_sum_f64(contrib);
+    if ((e & 31) == 0) s_red[e >> 5] = contrib;
+    named_bar_sync(1, 512);                       // also orders every thread's stores before thread 0's fence below
+    if (e < 32) {
+        double t = (e < 16) ? s_red[e] : 0.0;
+        t = warp_sum_f64(t);
+        unsigned last = 0u;
+        if (e == 0) {
+            o.rb_loss[rb] = t;
+            o.rb_count[rb] = 0u;                  // re-arm the ticket for the next launch
+            if (o.po.n_dst > 0) __threadfence_system(); else __threadfence();
+            last = (atomicAdd(o.done_count, 1u) == (unsigned)p.RB - 1u) ? 1u : 0u;
+        }
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (last) {
+            __threadfence();
+            double tot = 0.0;
+            for (int b = e; b < p.RB; b += 32) tot += __ldcg(o.rb_loss + b);
+            tot = warp_sum_f64(tot);
+            if (e == 0) {
+                const float loss = (float)(tot * o.inv_anchors);
+                *o.done_count = 0u;
+                if (o.po.n_dst > 0) {
+                    // this rank's share of the global mean goes to every rank, then the rank's flag is raised there
+                    for (int w = 0; w < o.po.n_dst; ++w)
+                        reinterpret_cast<float*>(o.po.dst[w])[2 * o.n_k + 4 * o.my_slot] = loss;
+                    __threadfence_system();
+                    const unsigned ex = o.po.state[1] + 1u;
+                    o.po.state[1] = ex;
+                    for (int w = 0; w < o.po.n_dst; ++w)
+                        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(o.po.flag[w]), "r"(ex) : "memory");
+                } else {
+                    store_loss_scalar(o.out_loss, loss, o.scalar_dtype);
+                }
+            }
+        }
+    }
+    named_bar_sync(1, 512);                       // s_red may be reused by this CTA's next merge
+}
+
 // =================================================================================== forward
-// smem: A[2][2*KCH*kSub] | B[2][KCH*kSub] | barriers | tmem slot
+// smem: A[2][2*KCH*kSub] | B[2][KCH*kSub] | barriers | tmem slot | merge scratch
 template <int KCH, bool kLabels>
 __global__ void __launch_bounds__(kTcThreads, 1)
-supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
+supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int A_BYTES = 2 * KCH * kSub;
     constexpr int B_BYTES = KCH * kSub;
@@ -129,6 +291,8 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
     uint8_t* b_smem = smem + 2 * A_BYTES;
     uint64_t* bars = reinterpret_cast<uint64_t*>(b_smem + NSB * B_BYTES);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    double* s_red = reinterpret_cast<double*>(bars + 18);                  // [16] merge scratch
+    volatile uint32_t* s_ticket = reinterpret_cast<volatile uint32_t*>(bars + 34);
     const uint32_t bar0 = smem_u32(bars);
     auto a_full = [&](int b) { return bar0 + 8u * (0 + b); };
     auto a_empty = [&](int b) { return bar0 + 8u * (2 + b); };
@@ -253,31 +417,42 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         int pj = -1, pj_lo = 0, pj_hi = -1;
 
         auto flush = [&](int rb) {
-            if (li >= p.a_count) return;
-            // one slot per (CTA overlapping the row block, column half)
-            const int slot = 2 * (blockIdx.x - (rb * p.CT) / p.q) + ca;
-            float ps = 0.f, np = 0.f;
-            if (kLabels) {
-                ps = possum * p.inv_T;
-                if (slot == 0) np = p.npos_row[gi];
-            } else if (capture) {
-                ps = possum * p.inv_T;
-                if (slot == 0) np = 1.f;
-            } else if (slot == 0) {
-                // more than two views: the other views of the same sample, as dot products
-                const int v = p.map.view_of(gi);
-                for (int vv = 0; vv < p.n_views; ++vv)
-                    if (vv != v)
-                        ps += bf16_dot_rows(p.k + (int64_t)gi * p.ldk,
-                                            p.k + (int64_t)p.map.sibling(gi, vv) * p.ldk, p.ldk);
-                ps *= p.inv_T;
-                np = (float)(p.n_views - 1);
+            const int first_cta = (rb * p.CT) / p.q;      // CTAs [first_cta, last_cta] overlap this row block
+            if (li < p.a_count) {
+                // one slot per (CTA overlapping the row block, column half)
+                const int slot = 2 * (blockIdx.x - first_cta) + ca;
+                float ps = 0.f, np = 0.f;
+                if (kLabels) {
+                    ps = possum * p.inv_T;
+                    if (slot == 0) np = p.npos_row[gi];
+                } else if (capture) {
+                    ps = possum * p.inv_T;
+                    if (slot == 0) np = 1.f;
+                } else if (slot == 0) {
+                    // more than two views: the other views of the same sample, as dot products
+                    const int v = p.map.view_of(gi);
+                    for (int vv = 0; vv < p.n_views; ++vv)
+                        if (vv != v)
+                            ps += bf16_dot_rows(p.k + (int64_t)gi * p.ldk,
+                                                p.k + (int64_t)p.map.sibling(gi, vv) * p.ldk, p.ldk);
+                    ps *= p.inv_T;
+                    np = (float)(p.n_views - 1);
+                }
+                float* dst = p.part + (int64_t)slot * 4 * p.n_rows + li;
+                dst[0] = m * kLn2;
+                dst[p.n_rows] = sum;
+                dst[2 * (int64_t)p.n_rows] = ps;
+                dst[3 * (int64_t)p.n_rows] = np;
             }
-            float* dst = p.part + (int64_t)slot * 4 * p.n_rows + li;
-            dst[0] = m * kLn2;
-            dst[p.n_rows] = sum;
-            dst[2 * (int64_t)p.n_rows] = ps;
-            dst[3 * (int64_t)p.n_rows] = np;
+            // row-block ticket: the CTA that delivers the last partials of the block merges them (fwd_merge_rows)
+            const int n_cta = ((rb + 1) * p.CT - 1) / p.q - first_cta + 1;
+            named_bar_sync(1, 512);                       // all partial stores of this CTA are issued ...
+            if (threadIdx.x == 64) {
+                __threadfence();                          // ... and made visible before the ticket (cumulative)
+                *s_ticket = atomicAdd(p.fo.rb_count + rb, 1u);
+            }
+            named_bar_sync(1, 512);
+            if (*s_ticket == (unsigned)n_cta - 1u) fwd_merge_rows(p, rb, n_cta, s_red);
         };
 
         // incremental tile bookkeeping (no division per tile); one copy of the flush and of the chunk code:
