@@ -625,6 +625,179 @@ __device__ __forceinline__ void store_p16(uint32_t taddr, const float (&pv)[N], 
     tmem_st8(taddr, wds);
 }
 
+// ------------------------------------------------------------------ finishing a summed dK row
+// The tiles only carry the softmax part of the gradient, P_ij + P_ji (rounded to bf16 for the second MMA).  The
+// positive-pair part, -(1/T) sum_{j != i} (M_ij [i anchor]/npos_i + M_ji [j anchor]/npos_j) k_j, has a closed form
+// per row and is added here in fp32 (Appendix A of SURVEY.md):
+//   SimCLR: the other views of the same sample, weight ([anchor_i] + [anchor_j]) / (V - 1);
+//   labels: with S_all / S_anc the sums of the rows / anchor rows of the row's class and c = 1 / npos,
+//           nia_i (S_all - k_i) + c (S_anc - [anchor_i] k_i)            (label_rows_kernel builds the sums).
+__device__ __forceinline__ void load_k4(const __nv_bfloat16* row, int d, float (&o)[4]) {
+    const uint2 raw = *reinterpret_cast<const uint2*>(row + d);
+    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
+    const float2 f0 = __bfloat1622float2(h2[0]), f1 = __bfloat1622float2(h2[1]);
+    o[0] = f0.x; o[1] = f0.y; o[2] = f1.x; o[3] = f1.y;
+}
+
+// the positive-pair term of global row gi at features d .. d+3 (to be ADDED to the softmax part)
+__device__ __forceinline__ void positive_term(const TcParams& p, int gi, int d, float (&pos)[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) pos[i] = 0.f;
+    if (p.mask_kind == SCB_MASK_SIMCLR && p.n_views >= 2) {
+        const int v = p.map.view_of(gi);
+        const float ai = p.map.is_anchor(gi, p.mode) ? 1.f : 0.f;
+        const float cpos = -1.f / (float)(p.n_views - 1);
+        for (int vv = 0; vv < p.n_views; ++vv) {
+            if (vv == v) continue;
+            const int j = p.map.sibling(gi, vv);
+            const float wgt = cpos * (ai + (p.map.is_anchor(j, p.mode) ? 1.f : 0.f));
+            float kj[4];
+            load_k4(p.k + (int64_t)j * p.ldk, d, kj);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) pos[i] = fmaf(wgt, kj[i], pos[i]);
+        }
+    } else if (p.mask_kind == SCB_MASK_LABELS) {
+        const int rep = p.rep_row[gi];
+        const float nia_i = p.nia_row[gi];
+        const float c = 1.f / p.npos_row[gi];
+        const float ai = p.map.is_anchor(gi, p.mode) ? 1.f : 0.f;
+        const float4 sa = *reinterpret_cast<const float4*>(p.fin.cls_all + (int64_t)rep * p.ldk + d);
+        const float4 sn = *reinterpret_cast<const float4*>(p.fin.cls_anc + (int64_t)rep * p.ldk + d);
+        float ki[4];
+        load_k4(p.k + (int64_t)gi * p.ldk, d, ki);
+        pos[0] = -(nia_i * (sa.x - ki[0]) + c * (sn.x - ai * ki[0]));
+        pos[1] = -(nia_i * (sa.y - ki[1]) + c * (sn.y - ai * ki[1]));
+        pos[2] = -(nia_i * (sa.z - ki[2]) + c * (sn.z - ai * ki[2]));
+        pos[3] = -(nia_i * (sa.w - ki[3]) + c * (sn.w - ai * ki[3]));
+    }
+}
+
+__device__ __forceinline__ float load_elem(const void* base, int dtype, int64_t idx) {
+    if (dtype == SCB_BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[idx]);
+    if (dtype == SCB_F16) return __half2float(reinterpret_cast<const __half*>(base)[idx]);
+    return reinterpret_cast<const float*>(base)[idx];
+}
+__device__ __forceinline__ void store_elem(void* base, int dtype, int64_t idx, float v) {
+    if (dtype == SCB_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
+    else if (dtype == SCB_F16) reinterpret_cast<__half*>(base)[idx] = __float2half_rn(v);
+    else reinterpret_cast<float*>(base)[idx] = v;
+}
+
+// NB local rows per warp at a time (lane = features lane*4 .. +3): acc[b] holds the summed softmax part of row
+// lrow[b] (-1 = no row).  All global loads of the batch are issued before the first dependent use, so the batch
+// costs one memory round trip, not NB.  Writes d features[b, v, :] (losses.py:52-53 un-stacked,
+// main_supcon.py:283 backward).
+template <int NB>
+__device__ __forceinline__ void finish_rows(const TcParams& p, float (&acc)[NB][4], const int (&lrow)[NB], int lane,
+                                            float coef) {
+    const FinishParams& f = p.fin;
+    const int d = lane * 4;
+    const bool on = d < p.ldk;
+    float pos[NB][4], z[NB][4], inv[NB];
+    int64_t src_off[NB], dst_off[NB];
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+        const bool ok = lrow[b] >= 0;
+        const int lr = ok ? lrow[b] : 0;
+        // local row = v*n_samples + b (view-major) or b*n_views + v (sample-major)  ->  features[b, v, :]
+        const int v_l = p.map.il ? lr % p.n_views : lr / f.n_samples;
+        const int b_l = p.map.il ? lr / p.n_views : lr - v_l * f.n_samples;
+        src_off[b] = (int64_t)b_l * f.stride_s + (int64_t)v_l * f.stride_v;
+        dst_off[b] = (int64_t)b_l * f.ostride_s + (int64_t)v_l * f.ostride_v;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { pos[b][i] = 0.f; z[b][i] = 0.f; }
+        inv[b] = 1.f;
+        if (ok && on) positive_term(p, p.row_begin + lr, d, pos[b]);
+        if (ok && f.normalize) {
+            inv[b] = f.inv_norm[lr];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (d + i < p.dim) z[b][i] = load_elem(f.feat, f.feat_dtype, src_off[b] + d + i);
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+        if (lrow[b] < 0) continue;                 // warp-uniform
+        float a[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = on ? (acc[b][i] + pos[b][i]) * coef : 0.f;
+        if (f.normalize) {
+            float dot = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { z[b][i] *= inv[b]; dot = fmaf(a[i], z[b][i], dot); }
+            dot = warp_sum(dot);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = (a[i] - z[b][i] * dot) * inv[b];
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (d + i < p.dim) store_elem(f.out, f.feat_dtype, dst_off[b] + d + i, a[i]);
+    }
+}
+
+// Direct finish of the backward (one or two CTAs per row block): a warp's [32 rows x 32 columns] block of dK goes
+// from TMEM into a [rows][pitch] fp32 staging array in shared memory -- this CTA's, or the partner CTA's of the
+// cluster pair (shared::cluster address) for the rows the partner finishes.  Out of line, scalar arguments.
+__device__ __noinline__ void stage_block(uint32_t taddr, uint32_t dst, int remote) {
+    uint32_t v[32];
+    tmem_ld32(taddr, v);
+    tmem_ld_wait_dep(v);
+    if (remote) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + 16u * i), "r"(v[4 * i]),
+                         "r"(v[4 * i + 1]), "r"(v[4 * i + 2]), "r"(v[4 * i + 3]) : "memory");
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + 16u * i), "r"(v[4 * i]),
+                         "r"(v[4 * i + 1]), "r"(v[4 * i + 2]), "r"(v[4 * i + 3]) : "memory");
+    }
+}
+
+// The sixteen epilogue warps turn the staged rows into d features, four rows per warp at a time.
+// own / recv: [n_keep][pitch] fp32 (recv = the partner's contribution, or nullptr).
+__device__ __noinline__ void finish_staged(const TcParams& p, const float* own, const float* recv, int pitch,
+                                           int lrow0, int n_keep, int ew, int lane) {
+    const float coef = load_scalar(p.grad_out, p.fin.grad_dtype) * p.fin.coef_scale_invT;
+    const int d = lane * 4;
+    for (int r0 = ew * 4; r0 < n_keep; r0 += 64) {
+        float acc[4][4];
+        int lrow[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int rr = r0 + b;
+            lrow[b] = (rr < n_keep && lrow0 + rr < p.n_rows) ? lrow0 + rr : -1;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[b][i] = 0.f;
+            if (lrow[b] >= 0 && d < p.ldk) {
+                float4 a = *reinterpret_cast<const float4*>(own + rr * pitch + d);
+                if (recv != nullptr) {
+                    const float4 c = *reinterpret_cast<const float4*>(recv + rr * pitch + d);
+                    a.x += c.x; a.y += c.y; a.z += c.z; a.w += c.w;
+                }
+                acc[b][0] = a.x; acc[b][1] = a.y; acc[b][2] = a.z; acc[b][3] = a.w;
+            }
+        }
+        finish_rows<4>(p, acc, lrow, lane, coef);
+    }
+}
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {     // every thread of every CTA of the cluster
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // =================================================================================== backward
 // 18 warps: warp 0 = TMA producer + per-tile column factors, warp 1 = MMA issuer + TMEM owner,
 // warps 2..17 = four epilogue warpgroups.
@@ -855,9 +1028,9 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         const int r = q4 * 32 + lane;                   // row within the block
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
 
-        int rb = rb0, ct = ct0, cur_rb = -1, li = 0, gi = 0, rep_i = 0, n_dz = 0;
+        int rb = rb0, ct = ct0, cur_rb = -1, li = 0, gi = 0, n_dz = 0;
         bool rows_fast = false;
-        float lse2_i = INFINITY, R_i = 0.f, nia_i = 0.f;
+        float lse2_i = INFINITY, R_i = 0.f;
         Tracer tr(p.trace, (warp == 2) ? 1 : (warp == 10 ? 2 : -1));   // lane quarter 2 of teams 0 and 1
 
         // dK of a finished row block leaves TMEM as plain vector stores into this CTA's slot of the
@@ -905,10 +1078,6 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                     const bool row_ok = (li < p.n_rows);
                     const bool anchor_i = row_ok && p.map.is_anchor(gi, p.mode);
                     lse2_i = anchor_i ? p.lse_all[gi] * kLog2e : INFINITY;
-                    if (kLabels) {
-                        rep_i = row_ok ? p.rep_row[gi] : -1;
-                        nia_i = row_ok ? p.nia_row[gi] : 0.f;
-                    }
                     const float d = lse2_i - m0;
                     const bool row_safe = anchor_i && (fabsf(d) <= kSafeSpread);
                     R_i = row_safe ? ex2(d) : 0.f;
@@ -926,9 +1095,6 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                 tr(3);
                 tc_fence_after();
                 const bool fast = rows_fast && (flags[st * 4] == 0u) && (j0 + 64 <= p.n_k);
-                mbar_wait(s_full(buf), (t / NS) & 1);
-                tr(3);
-                tc_fence_after();
                 if (fast) {
                     // ---------------- common case: one exp per element; two 32-column chunks, one copy of the code
                     const int g_lo = p.row_begin + rb * kBMB + q4 * 32;   // first row of this warp
@@ -952,17 +1118,6 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                             }
                         }
                         const int jc = j0 + cc * 32;
-                        if (kLabels) {
-#pragma unroll
-                            for (int c4 = 0; c4 < 8; ++c4) {
-                                const int4 ra = __ldg(reinterpret_cast<const int4*>(p.rep_row + jc + c4 * 4));
-                                const float4 na = __ldg(reinterpret_cast<const float4*>(p.nia_row + jc + c4 * 4));
-                                if (ra.x == rep_i) pv[c4 * 4 + 0] -= nia_i + na.x;
-                                if (ra.y == rep_i) pv[c4 * 4 + 1] -= nia_i + na.y;
-                                if (ra.z == rep_i) pv[c4 * 4 + 2] -= nia_i + na.z;
-                                if (ra.w == rep_i) pv[c4 * 4 + 3] -= nia_i + na.w;
-                            }
-                        }
                         // the self column (losses.py:74-79) only exists in slices on the diagonal: warp-uniform test
                         if (g_lo < jc + 32 && jc < g_lo + 32) {
                             const int c_self = gi - jc;
@@ -988,10 +1143,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
                             const int c = g16 * 16 + u;
                             const int j = j0 + c;
                             const float x = __uint_as_float(u < 8 ? v8a[u & 7] : v8b[u & 7]);
-                            float e = ex2(fmaf(x, p.c2, -lse2_i)) + ex2(fmaf(x, p.c2, -lj[c]));   // +inf -> 0
-                            if (kLabels) {
-                                if (j < p.n_k && p.rep_row[j] == rep_i) e -= nia_i + p.nia_row[j];
-                            }
+                            const float e = ex2(fmaf(x, p.c2, -lse2_i)) + ex2(fmaf(x, p.c2, -lj[c]));   // +inf -> 0
                             pv[u] = (j >= p.n_k || j == gi) ? 0.f : e;
                         }
                         store_p16(taddr + g16 * 8, pv, 0);     // words [8g, 8g+8) lie inside columns already read
