@@ -23,6 +23,11 @@ struct RowMap {
         const int rem = row % vseg;
         return il ? rem % nv : rem / seg;
     }
+    // the row that holds view v of sample `sample_id`
+    __device__ __forceinline__ int row_of(int sample_id, int v) const {
+        const int q = sample_id / seg, b = sample_id - q * seg;
+        return q * vseg + (il ? b * nv + v : v * seg + b);
+    }
     // the row that holds view vv of the same sample
     __device__ __forceinline__ int sibling(int row, int vv) const {
         const int v = view_of(row);

@@ -826,9 +826,9 @@ constexpr int kBMB = 128;       // rows per row block of the backward
 constexpr int kBwdThreads = 608;     // the forward's 18 warps + one more issuing warp
 constexpr int kBwdMma1Warp = 18;
 
-template <int KCH, bool kLabels>
+template <int KCH, bool kDirect>
 __global__ void __launch_bounds__(kBwdThreads, 1)
-supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
+supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int A_BYTES = KCH * kSub;
     constexpr int B_BYTES = KCH * kSub;
@@ -1065,8 +1065,10 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
         const int rb_end = (t0 + n_tiles - 1) / p.CT + 1;
         for (int t = team;; t += 2) {
             const bool more = t < n_tiles;
-            const int rb_target = more ? rb : rb_end;       // every block before this tile's (at the end: all of them)
-            while (next_drain < rb_target) drain(next_drain++);
+            if (!kDirect) {
+                const int rb_target = more ? rb : rb_end;   // every block before this tile's (at the end: all of them)
+                while (next_drain < rb_target) drain(next_drain++);
+            }
             if (!more) break;
             if (kTrace && t >= n_tiles - 2 && p.trace != nullptr && warp == 2 && lane == 0 && blockIdx.x < 256)
                 p.trace[4096 + 2 * blockIdx.x + 1] = global_ns();      // diagnostics: last tile reached
@@ -1164,11 +1166,51 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
             buf += 2;
             if (buf >= NS) { buf -= NS; spar ^= 1; }
         }
-        (void)bpar;
+        (void)bpar; (void)next_drain; (void)rb_end;
+        if (kDirect) {
+            // the CTA's single row block is complete once the last MMA2 has landed in TMEM
+            mbar_wait(dz_full, 0);
+            tc_fence_after();
+        }
     }
 
     tc_fence_before();
     __syncthreads();
+    if (kDirect) {
+        // ---------------------------------------------------- direct finish (no partial buffer, no reduce kernel)
+        // The CTA walked (part of) ONE row block.  With two CTAs per block (a cluster pair, p.pair == 2) CTA c of
+        // the pair finishes rows c*64 .. c*64+63: each CTA stages its own contribution to the rows it keeps in
+        // `own` and ships the other 64 rows into the partner's `recv` over distributed shared memory.  The B
+        // stages are free by now (all MMAs have completed), the staging arrays live there.
+        const int pitch = p.ldk + 4;                       // floats; 16-byte rows, conflict-free float4 columns
+        float* own = reinterpret_cast<float*>(b_smem);
+        float* recv = own + 128 * pitch;
+        const int rb_d = rb0;
+        const uint32_t crank = (p.pair == 2) ? cluster_ctarank() : 0u;
+        if (p.pair == 2) cluster_sync_all();               // the partner, too, is done with its B stages
+        if (warp >= 2 && warp < 18) {
+            const int g = (warp - 2) >> 2, q4 = warp & 3;
+            tc_fence_after();
+            if (g * 32 < ND) {
+                const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + kDkCol + g * 32;
+                if (p.pair == 2) {
+                    const bool keep = (uint32_t)(q4 >> 1) == crank;
+                    const int rr = (q4 & 1) * 32 + lane;                     // row within the kept half
+                    const uint32_t local = smem_u32((keep ? own : recv) + rr * pitch + g * 32);
+                    stage_block(taddr, keep ? local : mapa_shared(local, crank ^ 1u), keep ? 0 : 1);
+                } else {
+                    stage_block(taddr, smem_u32(own + (q4 * 32 + lane) * pitch + g * 32), 0);
+                }
+            }
+        }
+        if (p.pair == 2) cluster_sync_all(); else __syncthreads();
+        if (warp >= 2 && warp < 18) {
+            if (p.pair == 2) finish_staged(p, own, recv, pitch, rb_d * kBMB + (int)crank * 64, 64, warp - 2, lane);
+            else finish_staged(p, own, nullptr, pitch, rb_d * kBMB, 128, warp - 2, lane);
+        }
+        tc_fence_before();
+        __syncthreads();
+    }
     if (kTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[3071] = global_ns();
     stamp_cta(p.trace, 1);
     if (warp == 1) {
@@ -1178,151 +1220,120 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p)
 }
 
 // ------------------------------------------------------------------ label bookkeeping
-// rep_row[j]: smallest sample id with the same label as row j's sample (exact equality classes
-// for arbitrary int64 labels); npos_row[j] = V*count - 1; nia_row[j] = [anchor_j] / npos_row[j].
+// One warp per sample s: scans the labels once (ballots), which gives the class representative rep = smallest
+// sample id with the same label (exact equality classes for arbitrary int64 labels) and the class size; fills
+//   rep_row[j] = rep, npos_row[j] = V*count - 1, nia_row[j] = [anchor_j] / npos_row[j]      for the V rows j of s.
+// With cls_all != nullptr the warp of a representative then adds up the rows of its class in a fixed order:
+//   cls_all[rep] = sum of all rows of the class, cls_anc[rep] = sum of its anchor rows (mode `one`: view 0)
+// -- the fp32 closed form of the positive-pair part of the gradient (positive_term above).
 __global__ void __launch_bounds__(256)
-label_rows_kernel(const int64_t* __restrict__ labels, int n_samples, RowMap map, int n_k, int n_views, int mode,
-                  int* __restrict__ rep_row, float* __restrict__ npos_row, float* __restrict__ nia_row) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+label_rows_kernel(const int64_t* __restrict__ labels, int n_samples, RowMap map, int n_views, int mode,
+                  const __nv_bfloat16* __restrict__ k, int ldk, int* __restrict__ rep_row,
+                  float* __restrict__ npos_row, float* __restrict__ nia_row, float* __restrict__ cls_all,
+                  float* __restrict__ cls_anc) {
+    const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     pdl_launch_dependents();
     pdl_wait();
-    if (j >= n_k) return;
-    const int64_t mine = labels[map.sid(j)];
-    int rep = -1, cnt = 0;
-    for (int s = 0; s < n_samples; ++s) {
-        const bool eq = labels[s] == mine;
-        cnt += eq ? 1 : 0;
-        if (eq && rep < 0) rep = s;
+    if (s >= n_samples) return;
+    const int64_t mine = labels[s];
+    int cnt = 0, rep = -1;
+    for (int t0 = 0; t0 < n_samples; t0 += 32) {
+        const int t = t0 + lane;
+        const bool eq = t < n_samples && labels[t] == mine;
+        const unsigned bits = __ballot_sync(0xffffffffu, eq);
+        cnt += __popc(bits);
+        if (bits != 0u && rep < 0) rep = t0 + __ffs(bits) - 1;
     }
     const float np = (float)(n_views * cnt - 1);
-    rep_row[j] = rep;
-    npos_row[j] = np;
-    nia_row[j] = map.is_anchor(j, mode) ? 1.f / np : 0.f;
-}
-
-// ------------------------------------------------------------------ dK reduction
-// out_dk[row] = (coef/T) * sum over the slots of the row block of the partial dK  (softmax part)
-//             - (coef/T) * sum_{j: same sample, j != i} ([anchor_i] + [anchor_j]) / (V-1) * k_j   (SimCLR positives,
-//               a closed form: the label masks apply their positive term inside the tiles instead)
-// One warp per row, a lane owns 4 consecutive features per 128-wide step.
-__global__ void __launch_bounds__(256)
-supcon_tc_reduce_dk_kernel(const float* __restrict__ dk_part, int slot_rows, int flat_q, int flat_ct,
-                           const __nv_bfloat16* __restrict__ k, int ldk, RowMap map, int n_views, int mode,
-                           int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
-                           int grad_dtype, float coef_scale_invT, float* __restrict__ out_dk, int ld_dk) {
-    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    pdl_launch_dependents();
-    pdl_wait();
-    if (warp >= n_rows) return;
-    const int rb = warp >> 7;                      // 128-row blocks of the backward
-    const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
-    const float coef = load_scalar(grad_out, grad_dtype) * coef_scale_invT;
-    const bool simclr = (mask_kind == SCB_MASK_SIMCLR) && n_views >= 2;
-    const int gi = row_begin + warp;
-    const int v = map.view_of(gi);
-    const float ai = map.is_anchor(gi, mode) ? 1.f : 0.f;
-    const float cpos = -1.f / (float)(n_views > 1 ? n_views - 1 : 1);
-    float* dst = out_dk + (int64_t)warp * ld_dk;
-    for (int d = lane * 4; d < ldk; d += 128) {
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int s0 = 0; s0 < n_slots; s0 += 8) {          // eight slots at a time: all loads in flight together
-            float4 t[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-                t[u] = (s0 + u < n_slots)
-                           ? __ldcs(reinterpret_cast<const float4*>(dk_part + ((int64_t)(s0 + u) * slot_rows + warp) * ldk + d))
-                           : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { acc[0] += t[u].x; acc[1] += t[u].y; acc[2] += t[u].z; acc[3] += t[u].w; }
-        }
-        if (simclr) {
-            for (int vv = 0; vv < n_views; ++vv) {
-                if (vv == v) continue;
-                const int j = map.sibling(gi, vv);
-                const float wgt = cpos * (ai + (map.is_anchor(j, mode) ? 1.f : 0.f));
-                const uint2 raw = *reinterpret_cast<const uint2*>(k + (int64_t)j * ldk + d);
-                const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
-                const float2 f0 = __bfloat1622float2(h2[0]), f1 = __bfloat1622float2(h2[1]);
-                acc[0] = fmaf(wgt, f0.x, acc[0]); acc[1] = fmaf(wgt, f0.y, acc[1]);
-                acc[2] = fmaf(wgt, f1.x, acc[2]); acc[3] = fmaf(wgt, f1.y, acc[3]);
-            }
-        }
-        *reinterpret_cast<float4*>(dst + d) = make_float4(coef * acc[0], coef * acc[1], coef * acc[2], coef * acc[3]);
+    for (int v = lane; v < n_views; v += 32) {
+        const int j = map.row_of(s, v);
+        rep_row[j] = rep;
+        npos_row[j] = np;
+        nia_row[j] = map.is_anchor(j, mode) ? 1.f / np : 0.f;
     }
-}
-
-// Same reduction, fused with the layout kernel that follows it (scb_supcon_finish): un-stack the rows into
-// d features [n_samples, n_views, dim], apply the backward of the optional L2 normalisation and cast.
-// Requires ldk <= 128 (one 4-wide step per lane), which is what the tensor-core engine takes anyway.
-template <typename TF>
-__global__ void __launch_bounds__(256)
-supcon_tc_reduce_finish_kernel(const float* __restrict__ dk_part, int slot_rows, int flat_q, int flat_ct,
-                               const __nv_bfloat16* __restrict__ k, int ldk, RowMap map, int n_views, int mode,
-                               int mask_kind, int row_begin, int n_rows, const float* __restrict__ grad_out,
-                               int grad_dtype, float coef_scale_invT, const TF* __restrict__ feat, int n_samples, int dim,
-                               int64_t stride_s, int64_t stride_v, int normalize, const float* __restrict__ inv_norm,
-                               TF* __restrict__ out, int64_t ostride_s, int64_t ostride_v) {
-    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    pdl_launch_dependents();
-    pdl_wait();
-    if (warp >= n_rows) return;
+    if (cls_all == nullptr || rep != s) return;
     const int d = lane * 4;
     const bool on = d < ldk;
-    const int rb = warp >> 7;                      // 128-row blocks of the backward
-    const int n_slots = ((rb + 1) * flat_ct - 1) / flat_q - (rb * flat_ct) / flat_q + 1;
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    if (on) {
-        for (int s0 = 0; s0 < n_slots; s0 += 8) {          // eight slots at a time: all loads in flight together
-            float4 t[8];
+    float sa[4] = {0.f, 0.f, 0.f, 0.f}, sn[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int t0 = 0; t0 < n_samples; t0 += 32) {
+        const int t = t0 + lane;
+        const bool eq = t < n_samples && labels[t] == mine;
+        unsigned bits = __ballot_sync(0xffffffffu, eq);
+        while (bits != 0u) {
+            const int tt = t0 + __ffs(bits) - 1;
+            bits &= bits - 1u;
+            for (int v = 0; v < n_views; ++v) {
+                const int j = map.row_of(tt, v);
+                if (on) {
+                    float kj[4];
+                    load_k4(k + (int64_t)j * ldk, d, kj);
+                    const bool anc = map.is_anchor(j, mode);
 #pragma unroll
-            for (int u = 0; u < 8; ++u)
-                t[u] = (s0 + u < n_slots)
-                           ? __ldcs(reinterpret_cast<const float4*>(dk_part + ((int64_t)(s0 + u) * slot_rows + warp) * ldk + d))
-                           : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { acc[0] += t[u].x; acc[1] += t[u].y; acc[2] += t[u].z; acc[3] += t[u].w; }
-        }
-        if (mask_kind == SCB_MASK_SIMCLR && n_views >= 2) {
-            const int gi = row_begin + warp;
-            const int v = map.view_of(gi);
-            const float ai = map.is_anchor(gi, mode) ? 1.f : 0.f;
-            const float cpos = -1.f / (float)(n_views - 1);
-            for (int vv = 0; vv < n_views; ++vv) {
-                if (vv == v) continue;
-                const int j = map.sibling(gi, vv);
-                const float wgt = cpos * (ai + (map.is_anchor(j, mode) ? 1.f : 0.f));
-                const uint2 raw = *reinterpret_cast<const uint2*>(k + (int64_t)j * ldk + d);
-                const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
-                const float2 f0 = __bfloat1622float2(h2[0]), f1 = __bfloat1622float2(h2[1]);
-                acc[0] = fmaf(wgt, f0.x, acc[0]); acc[1] = fmaf(wgt, f0.y, acc[1]);
-                acc[2] = fmaf(wgt, f1.x, acc[2]); acc[3] = fmaf(wgt, f1.y, acc[3]);
+                    for (int i = 0; i < 4; ++i) { sa[i] += kj[i]; sn[i] += anc ? kj[i] : 0.f; }
+                }
             }
         }
     }
-    const float coef = load_scalar(grad_out, grad_dtype) * coef_scale_invT;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) acc[i] *= coef;
-    // local row = v*n_samples + b (view-major) or b*n_views + v (sample-major)  ->  features[b, v, :]
-    const int v_l = map.il ? warp % n_views : warp / n_samples;
-    const int b_l = map.il ? warp / n_views : warp - v_l * n_samples;
-    const TF* src = feat + (int64_t)b_l * stride_s + (int64_t)v_l * stride_v;
-    TF* dst = out + (int64_t)b_l * ostride_s + (int64_t)v_l * ostride_v;
-    if (normalize) {
-        const float inv = inv_norm[warp];
-        float z[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-            if (d + i < dim) z[i] = to_f32(src[d + i]) * inv;
-        float dot = 0.f;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) dot = fmaf(acc[i], z[i], dot);
-        dot = warp_sum(dot);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) acc[i] = (acc[i] - z[i] * dot) * inv;
+    if (on) {
+        *reinterpret_cast<float4*>(cls_all + (int64_t)s * ldk + d) = make_float4(sa[0], sa[1], sa[2], sa[3]);
+        if (cls_anc != cls_all)
+            *reinterpret_cast<float4*>(cls_anc + (int64_t)s * ldk + d) = make_float4(sn[0], sn[1], sn[2], sn[3]);
     }
+}
+
+// ------------------------------------------------------------------ dK reduction (general geometry)
+// Used when a row block is shared by more than two CTAs or a CTA walks several row blocks (the backward main
+// kernel then leaves per-slot partial dK blocks in the workspace).  One warp per local row:
+//   sum over the slots of the row block + closed-form positive-pair term, times coef/T.
+__device__ __forceinline__ void sum_dk_slots(const TcParams& p, int lrow, int d, float (&acc)[4]) {
+    const int rb = lrow >> 7;                      // 128-row blocks of the backward
+    const int n_slots = ((rb + 1) * p.CT - 1) / p.q - (rb * p.CT) / p.q + 1;
+    const int slot_rows = p.RB * kBMB;
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-        if (d + i < dim) dst[d + i] = from_f32<TF>(acc[i]);
+    for (int i = 0; i < 4; ++i) acc[i] = 0.f;
+    for (int s0 = 0; s0 < n_slots; s0 += 8) {          // eight slots at a time: all loads in flight together
+        float4 t[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            t[u] = (s0 + u < n_slots)
+                       ? __ldcs(reinterpret_cast<const float4*>(p.dk_part + ((int64_t)(s0 + u) * slot_rows + lrow) * p.ldk + d))
+                       : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { acc[0] += t[u].x; acc[1] += t[u].y; acc[2] += t[u].z; acc[3] += t[u].w; }
+    }
+}
+
+// fp32 dK rows out (scb_supcon_backward)
+__global__ void __launch_bounds__(256)
+supcon_tc_reduce_dk_kernel(const __grid_constant__ TcParams p) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    pdl_launch_dependents();
+    pdl_wait();
+    if (warp >= p.n_rows) return;
+    const float coef = load_scalar(p.grad_out, p.fin.grad_dtype) * p.fin.coef_scale_invT;
+    float* dst = p.out_dk + (int64_t)warp * p.ld_dk;
+    const int d = lane * 4;
+    if (d >= p.ldk) return;
+    float acc[4], pos[4];
+    sum_dk_slots(p, warp, d, acc);
+    positive_term(p, p.row_begin + warp, d, pos);
+    *reinterpret_cast<float4*>(dst + d) = make_float4(coef * (acc[0] + pos[0]), coef * (acc[1] + pos[1]),
+                                                      coef * (acc[2] + pos[2]), coef * (acc[3] + pos[3]));
+}
+
+// d features out (scb_supcon_backward_features): same reduction + un-stack, normalise-backward, cast
+__global__ void __launch_bounds__(256)
+supcon_tc_reduce_finish_kernel(const __grid_constant__ TcParams p) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    pdl_launch_dependents();
+    pdl_wait();
+    if (warp >= p.n_rows) return;
+    const float coef = load_scalar(p.grad_out, p.fin.grad_dtype) * p.fin.coef_scale_invT;
+    float acc[1][4];
+    const int lrow[1] = {warp};
+    if (lane * 4 < p.ldk) sum_dk_slots(p, warp, lane * 4, acc[0]);
+    else { acc[0][0] = acc[0][1] = acc[0][2] = acc[0][3] = 0.f; }
+    finish_rows<1>(p, acc, lrow, lane, coef);
 }
 
 // ------------------------------------------------------------------ host side
