@@ -22,6 +22,9 @@
 #include "supcon_common.cuh"
 #include "tc_ptx.cuh"
 
+#include <stdlib.h>
+#include <string.h>
+
 namespace scb {
 using namespace ptx;
 
@@ -1401,7 +1404,7 @@ void tc_set_trace(long long* p) { g_trace = p; }
 static cudaEvent_t g_ev_start = nullptr, g_ev_stop = nullptr;
 void tc_set_events(void* a, void* b) { g_ev_start = (cudaEvent_t)a; g_ev_stop = (cudaEvent_t)b; }
 
-struct TcGeom { int CT, RB, T, q, grid, n_split; };
+struct TcGeom { int CT, RB, T, q, grid, n_split, direct; };
 
 static TcGeom tc_geom(int n_k, int rows) {
     TcGeom g;
@@ -1415,6 +1418,7 @@ static TcGeom tc_geom(int n_k, int rows) {
     g.grid = (int)ceil_div(g.T, q);
     g.n_split = 2 * ((int)ceil_div(g.CT, q) + 1);      // (CTA overlapping the row block) x (column half)
     if (g.n_split > kMaxSlots) g.n_split = kMaxSlots;
+    g.direct = 0;
     return g;
 }
 
@@ -1441,6 +1445,8 @@ static TcGeom tc_geom_bwd(int n_k, int rows) {
     g.n_split = aligned ? (int)ceil_div(g.CT, q) : (int)ceil_div(g.CT, q) + 1;
     if (g.n_split < 1) g.n_split = 1;
     if (g.n_split > kMaxDkSlots) g.n_split = kMaxDkSlots;
+    // one or two CTAs per row block, each inside it: the kernel finishes the rows itself (cluster pair, no partials)
+    g.direct = (aligned && q <= g.CT && g.CT % q == 0 && g.CT / q <= 2) ? g.CT / q : 0;
     return g;
 }
 
@@ -1449,10 +1455,30 @@ static size_t dk_part_bytes(const scb_supcon_problem* p, int n_rows) {
     return align256((size_t)g.n_split * g.RB * kBMB * p->ldk * sizeof(float));
 }
 
+// label block: rep_row | npos_row | nia_row [n_k] | cls_all | cls_anc [n_samples][ldk]
+static size_t label_block_bytes(const scb_supcon_problem* p) {
+    if (p->mask_kind != SCB_MASK_LABELS) return 0;
+    return 3 * align256((size_t)p->n_k * 4) + 2 * align256((size_t)p->n_seg * p->seg * p->ldk * sizeof(float));
+}
+int64_t tc_label_cache_bytes(const scb_supcon_problem* p) { return (int64_t)label_block_bytes(p); }
+
+struct TcWs { float* part; char* labels; unsigned* rb_count; double* rb_loss; float* dk_part; size_t total; };
+static TcWs tc_ws_carve(const scb_supcon_problem* p, int n_rows, void* base) {
+    TcWs w;
+    char* ws = (char*)base;
+    const int rbf = (int)ceil_div(n_rows, kBM);
+    w.part = (float*)ws; ws += align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float));
+    w.labels = ws; ws += label_block_bytes(p);
+    w.rb_count = (unsigned*)ws; ws += align256(((size_t)rbf + 4) * sizeof(unsigned));     // [rbf] tickets | done counter
+    w.rb_loss = (double*)ws; ws += align256((size_t)rbf * sizeof(double));
+    w.dk_part = (float*)ws; ws += dk_part_bytes(p, n_rows);
+    w.total = (size_t)(ws - (char*)base);
+    return w;
+}
+
 int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows) {
     if (p->engine == SCB_ENGINE_FP32) return 0;
-    return (int64_t)(align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float)) + 3 * align256((size_t)p->n_k * 4) +
-                     dk_part_bytes(p, n_rows));
+    return (int64_t)tc_ws_carve(p, n_rows, nullptr).total;
 }
 
 static int tc_supported(const scb_supcon_problem* p) {
@@ -1464,6 +1490,7 @@ static int tc_supported(const scb_supcon_problem* p) {
 
 static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, int a_count, const TcGeom& g,
                         void* workspace, TcParams* t) {
+    memset(t, 0, sizeof(*t));
     t->k = (const __nv_bfloat16*)p->k;
     t->ldk = p->ldk; t->n_k = p->n_k; t->dim = p->dim;
     t->row_begin = row_begin; t->n_rows = n_rows; t->a_count = a_count;
@@ -1472,23 +1499,33 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
     t->n_views = p->n_views; t->mode = p->mode; t->mask_kind = p->mask_kind;
     t->c2 = p->inv_temperature * kLog2e;
     t->inv_T = p->inv_temperature;
-    char* ws = (char*)workspace;
-    t->part = (float*)ws;
-    ws += align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float));
-    t->rep_row = (const int*)ws; ws += align256((size_t)p->n_k * 4);
-    t->npos_row = (const float*)ws; ws += align256((size_t)p->n_k * 4);
-    t->nia_row = (const float*)ws; ws += align256((size_t)p->n_k * 4);
-    t->dk_part = (float*)ws;
-    t->lse_all = nullptr; t->grad_out = nullptr; t->coef_scale = 0.f; t->out_dk = nullptr; t->ld_dk = 0;
+    const TcWs w = tc_ws_carve(p, n_rows, workspace);
+    t->part = w.part;
+    if (p->mask_kind == SCB_MASK_LABELS) {
+        char* lb = p->label_cache ? (char*)p->label_cache : w.labels;
+        t->rep_row = (const int*)lb; lb += align256((size_t)p->n_k * 4);
+        t->npos_row = (const float*)lb; lb += align256((size_t)p->n_k * 4);
+        t->nia_row = (const float*)lb; lb += align256((size_t)p->n_k * 4);
+        t->fin.cls_all = (const float*)lb; lb += align256((size_t)p->n_seg * p->seg * p->ldk * sizeof(float));
+        t->fin.cls_anc = (p->mode == SCB_MODE_ALL) ? t->fin.cls_all : (const float*)lb;
+    }
+    t->fo.rb_count = w.rb_count;
+    t->fo.done_count = w.rb_count + (int)ceil_div(n_rows, kBM);
+    t->fo.rb_loss = w.rb_loss;
+    t->fo.po = PeerOut::none();
+    t->dk_part = w.dk_part;
+    t->pair = 0;
     t->trace = g_trace;
 }
 
-static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, cudaStream_t stream) {
+static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, bool with_sums, cudaStream_t stream) {
     if (p->mask_kind != SCB_MASK_LABELS) return SCB_OK;
     prefer_max_smem_carveout(label_rows_kernel);
-    SCB_CUDA_OK(launch_pdl(label_rows_kernel, dim3((unsigned)ceil_div(p->n_k, 256)), dim3(256), 0, stream, p->labels,
-                           p->n_seg * p->seg, t.map, p->n_k, p->n_views, p->mode, (int*)t.rep_row, (float*)t.npos_row,
-                           (float*)t.nia_row));
+    const int n_samples = p->n_seg * p->seg;
+    SCB_CUDA_OK(launch_pdl(label_rows_kernel, dim3((unsigned)ceil_div((int64_t)n_samples * 32, 256)), dim3(256), 0, stream,
+                           p->labels, n_samples, t.map, p->n_views, p->mode, t.k, p->ldk, (int*)t.rep_row,
+                           (float*)t.npos_row, (float*)t.nia_row, with_sums ? (float*)t.fin.cls_all : (float*)nullptr,
+                           with_sums ? (float*)t.fin.cls_anc : (float*)nullptr));
     count_launch();
     return SCB_OK;
 }
@@ -1499,18 +1536,58 @@ static int set_smem(Kern kern, size_t bytes) {
     return SCB_OK;
 }
 
-int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* part, int* n_split, int* q_out,
-               int* ct_out, cudaStream_t stream) {
+// programmatic stream serialisation + (optionally) a thread-block cluster of `cluster_x` consecutive CTAs
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                      int cluster_x, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    int n = 0;
+    if (pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    if (cluster_x > 1) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = (unsigned)cluster_x;
+        attr[n].val.clusterDim.y = 1;
+        attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+// Forward for the anchors among the local rows: ONE launch (plus the label bookkeeping kernel for label masks);
+// the per-CTA partials are merged inside the kernel (fwd_merge_rows).  ch != nullptr: the per-row results and the
+// rank's loss share go to every rank's statistics array and the rank's flag is raised (scb_supcon_forward_peers).
+int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, int n_anchor_total, float* out_lse,
+               float* out_possum, float* out_npos, float* out_loss, void* workspace, const scb_peer_channel* ch,
+               cudaStream_t stream) {
     if (int e = tc_supported(p)) return e;
     CUtensorMap tmap;
     if (int e = make_tmap(p, &tmap)) return e;
     const int a_count = (p->mode == SCB_MODE_ALL) ? n_rows : (n_rows < p->seg ? n_rows : p->seg);
     const TcGeom g = tc_geom(p->n_k, a_count);
     TcParams t;
-    fill_params(p, row_begin, n_rows, a_count, g, part, &t);
-    if (int e = launch_label_rows(p, t, stream)) return e;
+    fill_params(p, row_begin, n_rows, a_count, g, workspace, &t);
+    t.fo.out_lse = out_lse; t.fo.out_possum = out_possum; t.fo.out_npos = out_npos; t.fo.out_loss = out_loss;
+    t.fo.loss_scale = p->loss_scale;
+    t.fo.inv_anchors = 1.0 / (double)n_anchor_total;
+    t.fo.scalar_dtype = p->scalar_dtype;
+    t.fo.n_k = p->n_k;
+    t.fo.my_slot = row_begin / n_rows;               // rank: every rank holds n_rows consecutive rows
+    if (ch) t.fo.po = PeerOut::of(ch);
+    // with a label cache the class sums of the backward are built here, once per step
+    if (int e = launch_label_rows(p, t, p->label_cache != nullptr, stream)) return e;
     const int kch = p->ldk / 64;
-    const size_t smem = (size_t)2 * (2 * kch * kSub) + 2 * (kch * kSub) + 16 * 8 + 16;
+    const size_t smem = (size_t)2 * (2 * kch * kSub) + 2 * (kch * kSub) + 16 * 8 + 16 + 16 * 8 + 16;
     const bool lab = p->mask_kind == SCB_MASK_LABELS;
 #define SCB_LAUNCH_FWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
@@ -1522,36 +1599,47 @@ int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* pa
 #undef SCB_LAUNCH_FWD
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
-    *n_split = g.n_split;
-    *q_out = g.q;
-    *ct_out = g.CT;
     return SCB_OK;
 }
 
-// main kernel of the backward: fills the per-slot partial dK blocks in the workspace
+// main kernel of the backward.  fin == nullptr: fills the per-slot partial dK blocks in the workspace (a reduce
+// kernel follows).  fin != nullptr and a geometry with one or two CTAs per row block: the kernel writes d features
+// itself (g_out->direct != 0) and nothing follows.
 static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
-                            const float* grad_out, int n_anchor_total, void* workspace, TcGeom* g_out, TcParams* t_out,
-                            cudaStream_t stream) {
+                            const float* grad_out, int n_anchor_total, void* workspace, const FinishParams* fin,
+                            TcGeom* g_out, TcParams* t_out, cudaStream_t stream) {
     if (int e = tc_supported(p)) return e;
     CUtensorMap tmap;
     if (int e = make_tmap(p, &tmap)) return e;
-    const TcGeom g = tc_geom_bwd(p->n_k, n_rows);
+    TcGeom g = tc_geom_bwd(p->n_k, n_rows);
+    static const bool no_direct = [] { const char* e = getenv("SCB_BWD_DIRECT"); return e != nullptr && e[0] == '0'; }();
+    if (fin == nullptr || no_direct) g.direct = 0;
     TcParams t;
     fill_params(p, row_begin, n_rows, n_rows, g, workspace, &t);
     t.lse_all = lse_all; t.grad_out = grad_out;
     t.coef_scale = p->loss_scale / (float)n_anchor_total;
-    if (int e = launch_label_rows(p, t, stream)) return e;
+    {
+        const float* ca = t.fin.cls_all; const float* cn = t.fin.cls_anc;
+        if (fin) t.fin = *fin;
+        t.fin.cls_all = ca; t.fin.cls_anc = cn;
+        t.fin.grad_dtype = p->scalar_dtype;
+        t.fin.coef_scale_invT = t.coef_scale * p->inv_temperature;
+    }
+    t.pair = g.direct;
+    // class sums of the positive-pair term: built by the forward when the caller passed a label cache
+    if (p->label_cache == nullptr)
+        if (int e = launch_label_rows(p, t, true, stream)) return e;
     const int kch = p->ldk / 64;
     const size_t smem = (size_t)(kch * kSub) + 5 * (kch * kSub) + 5 * 256 * 4 + (5 * 4 + 4) * 4 + 24 * 8 + 16;
-    const bool lab = p->mask_kind == SCB_MASK_LABELS;
-#define SCB_LAUNCH_BWD(KCH_, LAB_)                                                                      \
+#define SCB_LAUNCH_BWD(KCH_, DIR_)                                                                      \
     do {                                                                                                \
-        if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        SCB_CUDA_OK(launch_pdl(supcon_tc_bwd_kernel<KCH_, LAB_>, dim3(g.grid), dim3(kBwdThreads), smem, stream, tmap, t)); \
+        if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, DIR_>, smem)) return e;                         \
+        SCB_CUDA_OK(launch_pdl_cluster(supcon_tc_bwd_kernel<KCH_, DIR_>, dim3(g.grid), dim3(kBwdThreads), smem, stream, \
+                                       DIR_ ? g.direct : 1, tmap, t));                                  \
     } while (0)
     if (g_ev_start) SCB_CUDA_OK(cudaEventRecord(g_ev_start, stream));
-    if (kch == 2) { if (lab) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
-    else { if (lab) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
+    if (kch == 2) { if (g.direct) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
+    else { if (g.direct) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
 #undef SCB_LAUNCH_BWD
     if (g_ev_stop) SCB_CUDA_OK(cudaEventRecord(g_ev_stop, stream));
     SCB_CUDA_OK(cudaGetLastError());
@@ -1569,13 +1657,13 @@ int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const fl
                 "supcon_backward (tensor-core engine): out_dk must be 16-byte aligned with ld_dk >= ldk (%d)", p->ldk);
     TcGeom g;
     TcParams t;
-    if (int e = tc_backward_main(p, row_begin, n_rows, lse_all, grad_out, n_anchor_total, workspace, &g, &t, stream))
+    if (int e = tc_backward_main(p, row_begin, n_rows, lse_all, grad_out, n_anchor_total, workspace, nullptr, &g, &t,
+                                 stream))
         return e;
+    t.out_dk = out_dk; t.ld_dk = ld_dk;
     prefer_max_smem_carveout(supcon_tc_reduce_dk_kernel);
     SCB_CUDA_OK(launch_pdl(supcon_tc_reduce_dk_kernel, dim3((unsigned)ceil_div((int64_t)n_rows * 32, 256)), dim3(256), 0,
-                           stream, (const float*)t.dk_part, g.RB * kBMB, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode,
-                           p->mask_kind, row_begin, n_rows, grad_out, p->scalar_dtype,
-                           t.coef_scale * p->inv_temperature, out_dk, ld_dk));
+                           stream, t));
     count_launch();
     return SCB_OK;
 }
@@ -1585,19 +1673,21 @@ int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
                          int n_samples, int64_t stride_s, int64_t stride_v, int normalize, const float* inv_norm,
                          void* out, int64_t ostride_s, int64_t ostride_v, void* workspace, cudaStream_t stream) {
     SCB_REQUIRE(n_rows == n_samples * p->n_views, "supcon_backward_features: n_rows must be n_samples * n_views");
+    SCB_REQUIRE(feat_dtype == SCB_F32 || feat_dtype == SCB_BF16 || feat_dtype == SCB_F16,
+                "supcon_backward_features: unsupported feature dtype %d", feat_dtype);
+    FinishParams fin;
+    memset(&fin, 0, sizeof(fin));
+    fin.feat = features; fin.out = out; fin.feat_dtype = feat_dtype; fin.n_samples = n_samples;
+    fin.normalize = normalize; fin.stride_s = stride_s; fin.stride_v = stride_v;
+    fin.ostride_s = ostride_s; fin.ostride_v = ostride_v; fin.inv_norm = inv_norm;
     TcGeom g;
     TcParams t;
-    if (int e = tc_backward_main(p, row_begin, n_rows, lse_all, grad_out, n_anchor_total, workspace, &g, &t, stream))
+    if (int e = tc_backward_main(p, row_begin, n_rows, lse_all, grad_out, n_anchor_total, workspace, &fin, &g, &t, stream))
         return e;
+    if (g.direct) return SCB_OK;
     const unsigned blocks = (unsigned)ceil_div((int64_t)n_rows * 32, 256);
-    SCB_DISPATCH_FLOAT(feat_dtype, TF, {
-        prefer_max_smem_carveout(supcon_tc_reduce_finish_kernel<TF>);
-        SCB_CUDA_OK(launch_pdl(supcon_tc_reduce_finish_kernel<TF>, dim3(blocks), dim3(256), 0, stream,
-                               (const float*)t.dk_part, g.RB * kBMB, g.q, g.CT, t.k, p->ldk, t.map, p->n_views, p->mode,
-                               p->mask_kind, row_begin, n_rows, grad_out, p->scalar_dtype,
-                               t.coef_scale * p->inv_temperature, (const TF*)features, n_samples, p->dim, stride_s,
-                               stride_v, normalize, inv_norm, (TF*)out, ostride_s, ostride_v));
-    });
+    prefer_max_smem_carveout(supcon_tc_reduce_finish_kernel);
+    SCB_CUDA_OK(launch_pdl(supcon_tc_reduce_finish_kernel, dim3(blocks), dim3(256), 0, stream, t));
     count_launch();
     return SCB_OK;
 }
