@@ -106,6 +106,12 @@ typedef struct scb_supcon_problem {
     float inv_temperature;  /* 1/T                  losses.py:64-66                               */
     float loss_scale;       /* T / base_temperature losses.py:90                                  */
     int32_t row_layout;     /* SCB_ROWS_*                                                         */
+    void* label_cache;      /* optional, SCB_MASK_LABELS on the tensor-core engines: a device buffer of
+                               scb_supcon_label_cache_bytes(p) bytes that scb_supcon_forward fills with the
+                               label bookkeeping (class representative / positive count per row, per-class
+                               row sums) and that the backward of the SAME problem then re-uses, so that
+                               the labels are scanned once per step; NULL: each pass recomputes what it
+                               needs in the workspace                                                 */
 } scb_supcon_problem;
 
 /* Replaces main_supcon.py:283 (`F.normalize`, optional) + losses.py:52-53 (view-major stacking)
@@ -121,6 +127,9 @@ int scb_supcon_prep(const void* features, int feat_dtype, int n_samples, int n_v
 
 /* bytes of zero-initialised scratch the forward / backward of `p` need for `n_rows` local rows */
 int64_t scb_supcon_workspace_bytes(const scb_supcon_problem* p, int n_rows);
+/* size of p->label_cache (0 when the problem has no labels or runs on ENGINE_FP32); the label bookkeeping
+ * replaces the [B, B] mask of losses.py:44-48 and the `mask.repeat` / `mask * logits_mask` of :72-80 */
+int64_t scb_supcon_label_cache_bytes(const scb_supcon_problem* p);
 
 /* Replaces losses.py:64-87 for the anchors among local rows [row_begin, row_begin+n_rows)
  * (a whole number of segments' worth of rows of ONE segment on a multi-rank run, everything on

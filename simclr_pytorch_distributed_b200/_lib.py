@@ -96,7 +96,7 @@ class SupconProblem(ctypes.Structure):
         ('ldk', ctypes.c_int32), ('n_views', ctypes.c_int32), ('seg', ctypes.c_int32),
         ('n_seg', ctypes.c_int32), ('mask_kind', ctypes.c_int32), ('mode', ctypes.c_int32),
         ('engine', ctypes.c_int32), ('scalar_dtype', ctypes.c_int32), ('inv_temperature', ctypes.c_float),
-        ('loss_scale', ctypes.c_float), ('row_layout', ctypes.c_int32),
+        ('loss_scale', ctypes.c_float), ('row_layout', ctypes.c_int32), ('label_cache', ctypes.c_void_p),
     ]
 
 
@@ -113,6 +113,7 @@ PROTOTYPES = {
     'scb_debug_set_events': (_i, [_vp, _vp]),
     'scb_supcon_prep': (_i, [_vp, _i, _i, _i, _i, _i64, _i64, _i, _f, _vp, _vp, _i, _i, _vp, _vp]),
     'scb_supcon_workspace_bytes': (_i64, [_pp, _i]),
+    'scb_supcon_label_cache_bytes': (_i64, [_pp]),
     'scb_supcon_forward': (_i, [_pp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),
     'scb_supcon_backward': (_i, [_pp, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _i64, _vp]),
     'scb_supcon_backward_features': (_i, [_pp, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i64, _i64, _i, _vp, _vp, _i64,

@@ -131,6 +131,11 @@ extern "C" int64_t scb_supcon_workspace_bytes(const scb_supcon_problem* p, int n
     return (fp32 > tc ? fp32 : tc) + kFinScratchBytes + 256;
 }
 
+extern "C" int64_t scb_supcon_label_cache_bytes(const scb_supcon_problem* p) {
+    if (!p || p->engine == SCB_ENGINE_FP32) return 0;
+    return tc_label_cache_bytes(p);
+}
+
 extern "C" int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, int n_rows,
                                   int n_anchor_total, float* out_lse, float* out_possum,
                                   float* out_npos, float* out_loss_sum, void* workspace,
@@ -147,7 +152,8 @@ extern "C" int scb_supcon_forward(const scb_supcon_problem* p, int row_begin, in
         n_split = fp32_splits(n_rows, p->n_k);
         if (int e = fp32_forward(p, row_begin, n_rows, part, n_split, stream)) return e;
     } else {
-        if (int e = tc_forward(p, row_begin, n_rows, part, &n_split, &flat_q, &flat_ct, stream)) return e;
+        return tc_forward(p, row_begin, n_rows, n_anchor_total, out_lse, out_possum, out_npos, out_loss_sum, part, nullptr,
+                          stream);
     }
     return launch_finalize(p, part, n_split, flat_q, flat_ct, row_begin, n_rows, 1.0 / (double)n_anchor_total, out_lse,
                            out_possum, out_npos, out_loss_sum, workspace, stream);
@@ -171,7 +177,7 @@ extern "C" int scb_supcon_forward_peers(const scb_supcon_problem* p, int row_beg
         n_split = fp32_splits(n_rows, p->n_k);
         if (int e = fp32_forward(p, row_begin, n_rows, part, n_split, stream)) return e;
     } else {
-        if (int e = tc_forward(p, row_begin, n_rows, part, &n_split, &flat_q, &flat_ct, stream)) return e;
+        return tc_forward(p, row_begin, n_rows, n_anchor_total, nullptr, out_possum, nullptr, nullptr, part, ch, stream);
     }
     return launch_finalize(p, part, n_split, flat_q, flat_ct, row_begin, n_rows, 1.0 / (double)n_anchor_total, nullptr,
                            out_possum, nullptr, nullptr, workspace, stream, ch);

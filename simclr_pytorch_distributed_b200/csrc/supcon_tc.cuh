@@ -6,16 +6,21 @@ namespace scb {
 
 int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows);
 
-// writes per-row partials [n_split][4][n_rows] = (max, sum exp, possum, npos) like the fp32 engine
-// (slots of a row block = the CTAs whose tile span overlaps it: q tiles per CTA, ct column tiles)
-int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, float* part, int* n_split, int* q,
-               int* ct, cudaStream_t stream);
+int64_t tc_label_cache_bytes(const scb_supcon_problem* p);
+
+// forward for the anchors among the local rows in ONE launch: the per-CTA row partials are merged inside the kernel
+// (last CTA of a row block), which also writes the scalar loss; ch != nullptr sends the per-row results and the
+// loss share to every rank instead (scb_supcon_forward_peers)
+int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, int n_anchor_total, float* out_lse,
+               float* out_possum, float* out_npos, float* out_loss, void* workspace, const scb_peer_channel* ch,
+               cudaStream_t stream);
 
 int tc_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
                 const float* npos_all, const float* grad_out, int n_anchor_total, float* out_dk,
                 int ld_dk, void* workspace, cudaStream_t stream);
 
-// backward + un-stack / normalise-backward / cast in two launches (main kernel + fused reduce-finish)
+// backward + un-stack / normalise-backward / cast: one launch when a row block belongs to one or two CTAs (cluster
+// pair, rows finished inside the kernel), else main kernel + fused reduce-finish
 int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows, const float* lse_all,
                          const float* grad_out, int n_anchor_total, const void* features, int feat_dtype,
                          int n_samples, int64_t stride_s, int64_t stride_v, int normalize, const float* inv_norm,

@@ -302,7 +302,7 @@ class DistributedSupConLoss(nn.Module):
         mask_kind = _lib.MASK_SIMCLR
         if labels is not None:
             mask_kind = _lib.MASK_LABELS
-            labels = labels.to(device=dev, dtype=torch.int64).contiguous()
+            labels = L.label_ids(labels, dev)
             labels_all = torch.empty(world * bsz, dtype=torch.int64, device=dev)
             _all_gather_flat(labels_all, labels, group)       # sample id = rank*bsz + b
         engine = L.select_engine(self.engine, features.dtype, dim, mask_kind, world * n_views * bsz)

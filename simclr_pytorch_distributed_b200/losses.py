@@ -82,8 +82,29 @@ class LossPlan:
             self.k_dtype, self.k_torch, self.ldk = _lib.BF16, torch.bfloat16, _round_up(dim, 64)
 
 
+def label_ids(labels, device):
+    """Labels as int64 class ids whose equality is the reference's `torch.eq(labels, labels.T)` (losses.py:48):
+    integer and bool labels are widened, floating-point labels keep their exact value (bit pattern of the
+    float64, -0.0 folded onto +0.0) instead of being truncated."""
+    labels = labels.to(device=device)
+    if labels.is_floating_point():
+        return (labels.to(torch.float64) + 0.0).contiguous().view(torch.int64)
+    return labels.to(torch.int64).contiguous()
+
+
+def label_cache_for(lib, prob, device):
+    """Device buffer for the label bookkeeping of one forward/backward pair (include/simclr_b200.h), or None."""
+    need = lib.scb_supcon_label_cache_bytes(ctypes.byref(prob))
+    if need <= 0:
+        return None
+    cache = torch.empty(need, dtype=torch.uint8, device=device)
+    prob.label_cache = cache.data_ptr()
+    return cache
+
+
 def _problem(plan, k, k_lo, labels, mask, temperature, base_temperature):
     p = _lib.SupconProblem()
+    p.label_cache = None
     p.k = k.data_ptr()
     p.k_lo = k_lo.data_ptr() if k_lo is not None else None
     p.labels = labels.data_ptr() if labels is not None else None
@@ -224,14 +245,15 @@ class _SupConFunction(torch.autograd.Function):
             else:
                 launch_prep(lib, feats, plan, normalize, k, k_lo, inv_norm)
             prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
+            cache = label_cache_for(lib, prob, dev)      # labels are scanned once per step, by the forward
             launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
         ctx.plan, ctx.prob_args, ctx.prob = plan, (temperature, base_temperature, normalize), prob
-        ctx.save_for_backward(feats, labels, mask, k, k_lo, stats)
+        ctx.save_for_backward(feats, labels, mask, k, k_lo, stats, cache)
         return typed_loss(loss, feats.dtype)
 
     @staticmethod
     def backward(ctx, grad_out):
-        feats, labels, mask, k, k_lo, stats = ctx.saved_tensors
+        feats, labels, mask, k, k_lo, stats, _cache = ctx.saved_tensors
         plan = ctx.plan
         temperature, base_temperature, normalize = ctx.prob_args
         lib = _lib.load()
@@ -301,7 +323,7 @@ class SupConLoss(nn.Module):
         dev = features.device
         if labels is not None:
             mask_kind = _lib.MASK_LABELS
-            labels = labels.to(device=dev, dtype=torch.int64)
+            labels = label_ids(labels, dev)
         elif mask is not None:
             mask_kind = _lib.MASK_EXPLICIT
             mask = mask.to(device=dev, dtype=torch.float32).contiguous()            # losses.py:50

@@ -48,7 +48,8 @@ def test_header_argument_counts_match_prototypes():
 
 def test_problem_struct_layout_matches_header():
     # 4 pointers, 11 int32, 2 float -> 32 + 44 + 8 = 84, padded to the pointer alignment: 88 bytes
-    assert ctypes.sizeof(_lib.SupconProblem) == 88
+    assert ctypes.sizeof(_lib.SupconProblem) == 96
+    assert _lib.SupconProblem.label_cache.offset == 88
     assert _lib.SupconProblem.k_dtype.offset == 32
     assert _lib.SupconProblem.scalar_dtype.offset == 72
     assert _lib.SupconProblem.inv_temperature.offset == 76
