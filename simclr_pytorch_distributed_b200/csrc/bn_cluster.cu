@@ -1,0 +1,345 @@
+// SyncBatchNorm, single-launch passes for activations that fit the register file of one resident wave
+// (BASELINE cfg 2: [256,256,8,8] bf16 = 8 MiB): statistics and normalisation in ONE kernel, x (and dy) read once.
+//
+// Replaces torch.batch_norm_stats + batch_norm_gather_stats_with_counts + batch_norm_elemt, resp.
+// batch_norm_backward_reduce + batch_norm_backward_elemt (torch/nn/modules/_functions.py:39-122, :139-179).
+//
+// Structure: a thread-block CLUSTER owns a slab of channels end to end.
+//   * the [M, C] channels-last matrix is cut into C / CW channel slabs (CW channels = TX 16-byte vectors);
+//     the CS CTAs of a cluster split the M rows of their slab; a thread keeps <= 8 rows x 16 bytes of x
+//     (and of dy) in registers -- every load of the pass is in flight at once;
+//   * per-channel partial sums: registers -> warp shuffles -> shared memory -> each CTA stores its 2*CW
+//     partials into EVERY CTA of the cluster over distributed shared memory -> barrier.cluster -> every CTA
+//     adds the CS partials in rank order (deterministic, identical everywhere);
+//   * the rows still sitting in registers are normalised and stored.
+// No global atomics, no grid-wide barrier and no co-residency assumption between clusters: a cluster that
+// cannot be scheduled yet (MPS / MIG limits, a concurrent NCCL kernel holding SMs) simply runs later.
+#include "common.cuh"
+
+#include <stdlib.h>
+
+namespace scb {
+
+constexpr int kClThreads = 512;    // one CTA per SM; 128 registers per thread: up to 16 rows x 16 bytes stay in registers
+constexpr int kClRows = 8;         // rows a thread keeps in registers (per tensor); 16 in the large forward variant
+constexpr int kClMaxCS = 16;
+
+__device__ __forceinline__ uint32_t cl_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t cl_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cl_store_remote(uint32_t local_addr, uint32_t rank, float v) {
+    uint32_t ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_addr), "r"(rank));
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(v) : "memory");
+}
+__device__ __forceinline__ void cl_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// Makes a register quadruple opaque to the optimiser: conversions of the raw rows done before the reduction are
+// not kept alive across it (the converted copy would double the register footprint), they are redone afterwards.
+__device__ __forceinline__ void cl_opaque(uint4& v) {
+    asm volatile("" : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w));
+}
+
+struct ClGeom {
+    int TX;              // threads (16-byte vectors) across a slab row; power of two <= 32
+    int CS;              // CTAs per cluster (1 = no cluster)
+    int n_slabs;
+    int64_t rows_per_cta;
+};
+
+// CTA-level sum of a[VEC], b[VEC] over the threads with the same tx, then all-gather + sum over the cluster.
+// Returns, in threads j < 2*CW (CW = TX*VEC), the cluster total of element j (j < CW: a, else b); other threads 0.
+// sm: [warps][2*CW] floats, gath: [CS][2*CW] floats.
+template <int VEC>
+__device__ __forceinline__ float cluster_channel_sums(float (&a)[VEC], float (&b)[VEC], float* sm, float* gath,
+                                                      int TX, int CS, uint32_t rank) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int CW = TX * VEC;
+    // lanes with equal (lane % TX) hold the same channels
+    for (int o = 16; o >= TX; o >>= 1) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            a[i] += __shfl_xor_sync(0xffffffffu, a[i], o);
+            b[i] += __shfl_xor_sync(0xffffffffu, b[i], o);
+        }
+    }
+    if (lane < TX) {
+        float* dst = sm + warp * 2 * CW + lane * VEC;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) { dst[i] = a[i]; dst[CW + i] = b[i]; }
+    }
+    __syncthreads();
+    float tot = 0.f;
+    const int j = threadIdx.x;
+    if (j < 2 * CW) {
+#pragma unroll 8
+        for (int w = 0; w < kClThreads / 32; ++w) tot += sm[w * 2 * CW + j];
+        if (CS > 1) {
+            const uint32_t local = cl_smem_u32(gath + rank * 2 * CW + j);
+            for (int r = 0; r < CS; ++r) cl_store_remote(local, (uint32_t)r, tot);
+        }
+    }
+    if (CS > 1) {
+        cl_sync();
+        if (j < 2 * CW) {
+            tot = 0.f;
+            for (int r = 0; r < CS; ++r) tot += gath[r * 2 * CW + j];      // rank order: same bits in every CTA
+        }
+    }
+    return tot;
+}
+
+// ------------------------------------------------------------------ forward
+// kMode 0: statistics + apply (one rank);  kMode 1: statistics only -> out_stats message (several ranks)
+template <typename T, int kMode, bool kAdd, int ROWS>
+__global__ void __launch_bounds__(kClThreads, 1)
+bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __restrict__ y, int64_t M, int C,
+                      const ClGeom g, const float* __restrict__ weight, const float* __restrict__ bias,
+                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                      float* save_invstd, float* save_count, float* out_stats, int flags) {
+    constexpr int VEC = Vec16<T>::N;
+    extern __shared__ float smf[];
+    const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
+    float* sm = smf;                                   // [warps][2*CW]
+    float* gath = sm + (kClThreads / 32) * 2 * CW;     // [CS][2*CW]
+    float* ab = gath + kClMaxCS * 2 * CW;              // [2][CW]
+    const uint32_t rank = (CS > 1) ? cl_ctarank() : 0u;
+    const int slab = blockIdx.x / CS;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = slab * CW + tx * VEC;
+    const int64_t r_begin = (int64_t)rank * g.rows_per_cta;
+    const int64_t r_end = min(M, r_begin + g.rows_per_cta);
+    const int64_t r0 = r_begin + ty;
+    const int64_t step = (int64_t)TY * C;
+    uint4 raw[ROWS], rz[ROWS];
+    float s1[VEC], s2[VEC], k0[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
+    int nrow = 0;
+    {
+        const T* p = x + r0 * C + c0;
+#pragma unroll
+        for (int u = 0; u < ROWS; ++u)
+            if (r0 + (int64_t)u * TY < r_end) { raw[u] = ldg_stream16(p + u * step); nrow = u + 1; }
+        if (kAdd && kMode == 0) {
+            const T* pz = z + r0 * C + c0;
+#pragma unroll
+            for (int u = 0; u < ROWS; ++u)
+                if (u < nrow) rz[u] = ldg_stream16(pz + u * step);
+        }
+        load_row_vec_cached<T, VEC>(x + c0, k0);       // common shift K_c = x[0, c]: no E[x^2] - E[x]^2 cancellation
+#pragma unroll
+        for (int u = 0; u < ROWS; ++u) {
+            if (u < nrow) {
+                const T* e = reinterpret_cast<const T*>(&raw[u]);
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float d = to_f32(e[i]) - k0[i];
+                    s1[i] += d;
+                    s2[i] = fmaf(d, d, s2[i]);
+                }
+            }
+        }
+    }
+    const float tot = cluster_channel_sums<VEC>(s1, s2, sm, gath, TX, CS, rank);
+    // threads j < CW own channel slab*CW + j: tot = S1 there, S2 sits in thread j + CW -> through shared memory
+    if ((int)threadIdx.x < 2 * CW) ab[threadIdx.x] = tot;
+    __syncthreads();
+    const float n = (float)M;
+    float av = 0.f, bv = 0.f;
+    if ((int)threadIdx.x < CW) {
+        const int c = slab * CW + threadIdx.x;
+        const float S1 = ab[threadIdx.x], S2 = ab[CW + threadIdx.x];
+        const float mean = to_f32(x[c]) + S1 / n;
+        const float m2 = fmaxf(S2 - S1 * S1 / n, 0.f);
+        if (kMode == 1) {
+            if (rank == 0) {
+                out_stats[c] = mean;
+                out_stats[C + c] = m2;
+                if (c == 0) out_stats[2 * C] = n;
+            }
+        } else {
+            const float invstd = rsqrtf(m2 / n + eps);
+            av = (weight ? weight[c] : 1.f) * invstd;
+            bv = (bias ? bias[c] : 0.f) - mean * av;
+            if (rank == 0) {
+                if (save_mean) save_mean[c] = mean;
+                if (save_invstd) save_invstd[c] = invstd;
+                if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+                if (c == 0 && save_count) save_count[0] = n;
+            }
+        }
+    }
+    if (kMode == 1) return;
+    __syncthreads();                                   // everybody has read S1 / S2
+    if ((int)threadIdx.x < CW) { ab[threadIdx.x] = av; ab[CW + threadIdx.x] = bv; }
+    __syncthreads();
+    float a[VEC], b[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { a[i] = ab[tx * VEC + i]; b[i] = ab[CW + tx * VEC + i]; }
+#pragma unroll
+    for (int u = 0; u < ROWS; ++u) { cl_opaque(raw[u]); if (kAdd) cl_opaque(rz[u]); }
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    T* q = y + r0 * C + c0;
+#pragma unroll
+    for (int u = 0; u < ROWS; ++u) {
+        if (u < nrow) {
+            const T* e = reinterpret_cast<const T*>(&raw[u]);
+            const T* ez = reinterpret_cast<const T*>(&rz[u]);
+            uint4 o;
+            T* oe = reinterpret_cast<T*>(&o);
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                float v = fmaf(to_f32(e[i]), a[i], b[i]);
+                if (kAdd) v += to_f32(ez[i]);
+                oe[i] = from_f32<T>(relu ? fmaxf(v, 0.f) : v);
+            }
+            stg_stream16(q + u * step, o);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ backward
+// kGate 0: plain; 1: ReLU, gate recomputed from x (y = (x - mean) a + b > 0); 2: gate read from the saved output y
+// (y > 0: ReLU after a residual add), the gated dy is also written to dz (the gradient of the residual input).
+// kMode 0: reduce + apply (one rank); 1: reduce only -> out_sums, dgamma, dbeta (several ranks)
+template <typename T, int kMode, int kGate>
+__global__ void __launch_bounds__(kClThreads, 1)
+bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yout,
+                      T* __restrict__ dx, T* __restrict__ dz, int64_t M, int C, const ClGeom g,
+                      const float* __restrict__ mean, const float* __restrict__ invstd,
+                      const float* __restrict__ weight, const float* __restrict__ bias,
+                      const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias) {
+    constexpr int VEC = Vec16<T>::N;
+    extern __shared__ float smf[];
+    const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
+    float* sm = smf;
+    float* gath = sm + (kClThreads / 32) * 2 * CW;
+    float* ab = gath + kClMaxCS * 2 * CW;
+    const uint32_t rank = (CS > 1) ? cl_ctarank() : 0u;
+    const int slab = blockIdx.x / CS;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = slab * CW + tx * VEC;
+    const int64_t r_begin = (int64_t)rank * g.rows_per_cta;
+    const int64_t r_end = min(M, r_begin + g.rows_per_cta);
+    const int64_t r0 = r_begin + ty;
+    const int64_t step = (int64_t)TY * C;
+    uint4 rx[kClRows], rd[kClRows];
+    unsigned gated[kClRows];               // bit i set: element i of the row is gated off (dy dropped)
+    float s1[VEC], s2[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
+    int nrow = 0;
+    {
+        const T* px = x + r0 * C + c0;
+        const T* pd = dy + r0 * C + c0;
+#pragma unroll
+        for (int u = 0; u < kClRows; ++u)
+            if (r0 + (int64_t)u * TY < r_end) {
+                rx[u] = ldg_stream16(px + u * step);
+                rd[u] = ldg_stream16(pd + u * step);
+                nrow = u + 1;
+            }
+#pragma unroll
+        for (int u = 0; u < kClRows; ++u) gated[u] = 0u;
+        if (kGate == 2) {
+            const T* py = yout + r0 * C + c0;
+#pragma unroll
+            for (int u = 0; u < kClRows; ++u) {
+                if (u < nrow) {
+                    const uint4 ry = ldg_stream16(py + u * step);
+                    const T* ey = reinterpret_cast<const T*>(&ry);
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i)
+                        if (!(to_f32(ey[i]) > 0.f)) gated[u] |= 1u << i;
+                }
+            }
+        }
+        float mu[VEC], k1[VEC], bb[VEC];
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            mu[i] = mean[c0 + i];
+            // the scale is only needed before the reduction when the gate is recomputed from x
+            k1[i] = (kGate == 1) ? (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i] : 0.f;
+            bb[i] = (kGate == 1 && bias) ? bias[c0 + i] : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < kClRows; ++u) {
+            if (u < nrow) {
+                const T* ex = reinterpret_cast<const T*>(&rx[u]);
+                const T* ed = reinterpret_cast<const T*>(&rd[u]);
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float xm = to_f32(ex[i]) - mu[i];
+                    float gv = to_f32(ed[i]);
+                    if (kGate == 1 && !(fmaf(xm, k1[i], bb[i]) > 0.f)) gated[u] |= 1u << i;
+                    if (kGate != 0 && ((gated[u] >> i) & 1u)) gv = 0.f;
+                    s1[i] += gv;
+                    s2[i] = fmaf(gv, xm, s2[i]);
+                }
+            }
+        }
+    }
+    const float tot = cluster_channel_sums<VEC>(s1, s2, sm, gath, TX, CS, rank);
+    if ((int)threadIdx.x < 2 * CW) ab[threadIdx.x] = tot;
+    __syncthreads();
+    float v2 = 0.f, v3 = 0.f;
+    if ((int)threadIdx.x < CW) {
+        const int c = slab * CW + threadIdx.x;
+        const float sd = ab[threadIdx.x], sx = ab[CW + threadIdx.x];
+        const float is = invstd[c];
+        const float inv_n = 1.f / n_total[0];
+        v2 = sd * inv_n;
+        v3 = is * is * sx * inv_n;
+        if (rank == 0) {
+            if (out_sums) { out_sums[c] = sd; out_sums[C + c] = sx; }
+            if (grad_weight) grad_weight[c] = sx * is;
+            if (grad_bias) grad_bias[c] = sd;
+        }
+    }
+    if (kMode == 1) return;
+    __syncthreads();
+    if ((int)threadIdx.x < CW) { ab[threadIdx.x] = v2; ab[CW + threadIdx.x] = v3; }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < kClRows; ++u) { cl_opaque(rx[u]); cl_opaque(rd[u]); }
+    // dx = (g - k2 - (x - mu) k3) k1  =  g A + x B + D   with  A = k1, B = -k3 k1, D = (mu k3 - k2) k1:
+    // three coefficient vectors instead of four, and no subtraction of the mean per element
+    float cA[VEC], cB[VEC], cD[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        const float k2 = ab[tx * VEC + i], k3 = ab[CW + tx * VEC + i];
+        const float kk = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
+        cA[i] = kk;
+        cB[i] = -k3 * kk;
+        cD[i] = (mean[c0 + i] * k3 - k2) * kk;
+    }
+    T* po = dx + r0 * C + c0;
+    T* pz = (kGate == 2 && dz != nullptr) ? dz + r0 * C + c0 : nullptr;
+#pragma unroll
+    for (int u = 0; u < kClRows; ++u) {
+        if (u < nrow) {
+            const T* ex = reinterpret_cast<const T*>(&rx[u]);
+            const T* ed = reinterpret_cast<const T*>(&rd[u]);
+            uint4 o, oz;
+            T* oe = reinterpret_cast<T*>(&o);
+            T* oze = reinterpret_cast<T*>(&oz);
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                const bool off = (kGate != 0) && ((gated[u] >> i) & 1u);
+                const float gv = off ? 0.f : to_f32(ed[i]);
+                oe[i] = from_f32<T>(fmaf(to_f32(ex[i]), cB[i], fmaf(gv, cA[i], cD[i])));
+                if (kGate == 2) oze[i] = off ? from_f32<T>(0.f) : ed[i];
+            }
+            stg_stream16(po + u * step, o);
+            if (kGate == 2 && pz != nullptr) stg_stream16(pz + u * step, oz);
+        }
+    }
+}
+
