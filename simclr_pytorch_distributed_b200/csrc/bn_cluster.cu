@@ -343,3 +343,256 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
     }
 }
 
+// ------------------------------------------------------------------ host side: geometry
+static bool cl_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Largest cluster size the device accepts for kernels of this shape (16 needs the non-portable opt-in and a GPC
+// with 16 free SMs); probed once per device with the occupancy API on a representative kernel.
+template <typename Kern>
+static int cl_probe_max_cs(Kern kern, size_t smem) {
+    for (int cs = kClMaxCS; cs > 1; cs >>= 1) {
+        if (cs > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+            cudaGetLastError();
+            continue;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(cs);
+        cfg.blockDim = dim3(kClThreads);
+        cfg.dynamicSmemBytes = smem;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n >= 1) return cs;
+        cudaGetLastError();
+    }
+    return 1;
+}
+
+static size_t cl_smem_bytes(int TX, int vec) {
+    return (size_t)(kClThreads / 32 + kClMaxCS + 1) * 2 * TX * vec * sizeof(float);
+}
+
+static int cl_max_cs() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 1;
+    if (cached[dev] == 0) {
+        const char* e = getenv("SCB_BN_MAX_CLUSTER");
+        const int cap = e ? atoi(e) : kClMaxCS;
+        auto kern = bn_fwd_cluster_kernel<__nv_bfloat16, 0, false, 8>;
+        int m = cl_probe_max_cs(kern, cl_smem_bytes(4, 8));
+        if (cap >= 1 && m > cap) m = cap;
+        cached[dev] = m < 1 ? 1 : m;
+    }
+    return cached[dev];
+}
+
+// CTAs of one cluster size that can be resident at once on a B200 (148 SMs in 8 GPCs of 16..20): the grid should
+// not exceed it (a second wave doubles the time of a latency-bound pass)
+static int cl_wave_cap(int cs) {
+    const int sms = sm_count();
+    if (cs >= 8) return (sms * 128 / 148) / cs * cs;      // two clusters of 8 (one of 16) per GPC
+    if (cs == 4) return (sms * 132 / 148) / 4 * 4;
+    return sms / cs * cs;
+}
+
+// picks (TX, CS) so that the tensor fits the registers of ONE resident wave; false if it does not
+static bool cl_geom(int64_t M, int C, int es, int rows, ClGeom* out) {
+    const int vec = 16 / es;
+    if (C % vec != 0 || M < 2) return false;
+    const int cv = C / vec;
+    const int max_cs = cl_max_cs();
+    bool found = false;
+    int64_t best_cost = 0;
+    for (int cs = max_cs; cs >= 1; cs >>= 1) {
+        for (int tx = 32; tx >= 1; tx >>= 1) {
+            if (cv % tx != 0) continue;
+            const int ty = kClThreads / tx;
+            const int64_t rpc = ceil_div(M, cs);
+            if (rpc > (int64_t)rows * ty) continue;
+            const int64_t grid = (int64_t)(cv / tx) * cs;
+            if (grid > cl_wave_cap(cs)) continue;
+            if (cl_smem_bytes(tx, vec) > 200 * 1024) continue;
+            // cost ~ bytes per CTA; narrow pieces (< 64 bytes per row) waste DRAM sectors
+            const int64_t cost = rpc * tx * (tx * 16 >= 64 ? 4 : (tx * 16 >= 32 ? 5 : 8));
+            if (!found || cost < best_cost) {
+                found = true; best_cost = cost;
+                out->TX = tx; out->CS = cs; out->n_slabs = cv / tx; out->rows_per_cta = rpc;
+            }
+        }
+    }
+    return found;
+}
+
+template <typename... KArgs, typename... Args>
+static cudaError_t cl_launch(void (*kernel)(KArgs...), const ClGeom& g, size_t smem, cudaStream_t stream, Args&&... args) {
+    cudaError_t e = set_max_dynamic_smem(kernel, (int)smem);
+    if (e != cudaSuccess) return e;
+    if (g.CS > 8 && !attr_done((const void*)kernel, (int)cudaFuncAttributeNonPortableClusterSizeAllowed, 1)) {
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e != cudaSuccess) return e;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(g.n_slabs * g.CS));
+    cfg.blockDim = dim3(kClThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)g.CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g.CS > 1 ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+static int cl_check(const void* x, int dtype, int64_t rows, int channels) {
+    SCB_REQUIRE(x != nullptr, "bn fused: null tensor pointer");
+    SCB_REQUIRE(dtype == SCB_F32 || dtype == SCB_BF16 || dtype == SCB_F16, "bn fused: unsupported dtype %d", dtype);
+    SCB_REQUIRE(channels > 0, "SyncBatchNorm number of input channels should be non-zero");
+    SCB_REQUIRE(rows >= 0 && rows < (int64_t)1 << 40, "bn fused: bad row count");
+    return SCB_OK;
+}
+
+template <typename T, int kMode, int kGate>
+static cudaError_t cl_launch_bwd(const ClGeom& g, cudaStream_t stream, const void* dy, const void* x, const void* y,
+                                 void* dx, void* dz, int64_t M, int C, const float* mean, const float* invstd,
+                                 const float* weight, const float* bias, const float* n_total, float* out_sums,
+                                 float* grad_weight, float* grad_bias) {
+    return cl_launch(bn_bwd_cluster_kernel<T, kMode, kGate>, g, cl_smem_bytes(g.TX, Vec16<T>::N), stream, (const T*)dy,
+                     (const T*)x, (const T*)y, (T*)dx, (T*)dz, M, C, g, mean, invstd, weight, bias, n_total, out_sums,
+                     grad_weight, grad_bias);
+}
+
+}  // namespace scb
+
+using namespace scb;
+
+// which = 0: forward (with or without a residual operand, see `flags`), 1: backward
+extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner,
+                                      int which, int flags) {
+    if (!channels_last || channels <= 0) return 0;
+    if (dtype != SCB_F32 && dtype != SCB_BF16 && dtype != SCB_F16) return 0;
+    const int es = (dtype == SCB_F32) ? 4 : 2;
+    ClGeom g;
+    const int rows = (which == 0 && !(flags & SCB_BN_ADD)) ? 2 * kClRows : kClRows;
+    return cl_geom(outer * inner, channels, es, rows, &g) ? 1 : 0;
+}
+
+#define SCB_CL_UNSUPPORTED(what)                                                             \
+    do { set_error(what ": tensor does not fit the registers of one resident wave (or is not 16-byte aligned)"); \
+         return SCB_ERR_UNSUPPORTED; } while (0)
+
+extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int dtype, int64_t rows, int channels,
+                                    const float* weight, const float* bias, float* running_mean,
+                                    float* running_var, float momentum, float eps, float* save_mean,
+                                    float* save_invstd, float* save_count, int flags, void* stream_) {
+    if (int e = cl_check(x, dtype, rows, channels)) return e;
+    SCB_REQUIRE(y != nullptr, "bn_forward_fused: null output");
+    const bool add = (flags & SCB_BN_ADD) != 0;
+    SCB_REQUIRE(!add || z != nullptr, "bn_forward_fused: SCB_BN_ADD needs the residual operand z");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int64_t M = rows;
+    const int C = channels;
+    if (!cl_aligned16(x) || !cl_aligned16(y) || (add && !cl_aligned16(z))) SCB_CL_UNSUPPORTED("bn_forward_fused");
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        constexpr int VEC = Vec16<T>::N;
+        ClGeom g;
+        bool ok = cl_geom(M, C, sizeof(T), kClRows, &g);
+        int nrows = kClRows;
+        if (!ok && !add) { ok = cl_geom(M, C, sizeof(T), 2 * kClRows, &g); nrows = 2 * kClRows; }
+        if (!ok) SCB_CL_UNSUPPORTED("bn_forward_fused");
+        const size_t smem = cl_smem_bytes(g.TX, VEC);
+        const T* xp = (const T*)x; const T* zp = (const T*)z; T* yp = (T*)y;
+        float* none = nullptr;
+        if (add)
+            SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, true, kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, none, flags));
+        else if (nrows == kClRows)
+            SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, false, kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, none, flags));
+        else
+            SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, false, 2 * kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, none, flags));
+    });
+    count_launch();
+    return SCB_OK;
+}
+
+// statistics only, through the same cluster reduction: the (2C+1)-float message of scb_bn_stats without scratch
+extern "C" int scb_bn_stats_fused(const void* x, int dtype, int64_t rows, int channels, float* out_stats,
+                                  void* stream_) {
+    if (int e = cl_check(x, dtype, rows, channels)) return e;
+    SCB_REQUIRE(out_stats != nullptr, "bn_stats_fused: null output");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int64_t M = rows;
+    const int C = channels;
+    if (!cl_aligned16(x)) SCB_CL_UNSUPPORTED("bn_stats_fused");
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        constexpr int VEC = Vec16<T>::N;
+        ClGeom g;
+        if (!cl_geom(M, C, sizeof(T), 2 * kClRows, &g)) SCB_CL_UNSUPPORTED("bn_stats_fused");
+        const size_t smem = cl_smem_bytes(g.TX, VEC);
+        const T* xp = (const T*)x; const T* zp = nullptr; T* yp = nullptr;
+        float* none = nullptr; const float* cnone = nullptr;
+        SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 1, false, 2 * kClRows>, g, smem, stream, xp, zp, yp, M, C, g, cnone, cnone,
+                              none, none, 0.f, 0.f, none, none, none, out_stats, 0));
+    });
+    count_launch();
+    return SCB_OK;
+}
+
+static int bn_backward_cluster(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype,
+                               int64_t rows, int channels, const float* mean, const float* invstd,
+                               const float* weight, const float* bias, const float* n_total, float* out_sums,
+                               float* grad_weight, float* grad_bias, int flags, int reduce_only, void* stream_) {
+    if (int e = cl_check(x, dtype, rows, channels)) return e;
+    SCB_REQUIRE(dy && mean && invstd && n_total, "bn_backward_fused: null pointer");
+    SCB_REQUIRE(reduce_only || dx != nullptr, "bn_backward_fused: null dx");
+    const int gate = (flags & SCB_BN_RELU) ? ((flags & SCB_BN_ADD) ? 2 : 1) : 0;
+    SCB_REQUIRE(gate != 2 || y != nullptr, "bn_backward_fused: SCB_BN_RELU|SCB_BN_ADD needs the saved output y");
+    if (gate != 2) dz = nullptr;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int64_t M = rows;
+    const int C = channels;
+    if (!cl_aligned16(x) || !cl_aligned16(dy) || (dx && !cl_aligned16(dx)) || (gate == 2 && !cl_aligned16(y)) ||
+        (dz && !cl_aligned16(dz)))
+        SCB_CL_UNSUPPORTED("bn_backward_fused");
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        ClGeom g;
+        if (!cl_geom(M, C, sizeof(T), kClRows, &g)) SCB_CL_UNSUPPORTED("bn_backward_fused");
+        cudaError_t err;
+        if (reduce_only) {
+            if (gate == 2) err = cl_launch_bwd<T, 1, 2>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+            else if (gate == 1) err = cl_launch_bwd<T, 1, 1>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+            else err = cl_launch_bwd<T, 1, 0>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+        } else {
+            if (gate == 2) err = cl_launch_bwd<T, 0, 2>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+            else if (gate == 1) err = cl_launch_bwd<T, 0, 1>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+            else err = cl_launch_bwd<T, 0, 0>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+        }
+        SCB_CUDA_OK(err);
+    });
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_bn_backward_fused(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype,
+                                     int64_t rows, int channels, const float* mean, const float* invstd,
+                                     const float* weight, const float* bias, const float* n_total, float* out_sums,
+                                     float* grad_weight, float* grad_bias, int flags, void* stream_) {
+    return bn_backward_cluster(dy, x, y, dx, dz, dtype, rows, channels, mean, invstd, weight, bias, n_total, out_sums,
+                               grad_weight, grad_bias, flags, 0, stream_);
+}
+
+extern "C" int scb_bn_backward_reduce_fused(const void* dy, const void* x, const void* y, int dtype, int64_t rows,
+                                            int channels, const float* mean, const float* invstd,
+                                            const float* weight, const float* bias, const float* n_total,
+                                            float* out_sums, float* grad_weight, float* grad_bias, int flags,
+                                            void* stream_) {
+    SCB_REQUIRE(out_sums != nullptr, "bn_backward_reduce_fused: null out_sums");
+    return bn_backward_cluster(dy, x, y, nullptr, nullptr, dtype, rows, channels, mean, invstd, weight, bias, n_total,
+                               out_sums, grad_weight, grad_bias, flags, 1, stream_);
+}
