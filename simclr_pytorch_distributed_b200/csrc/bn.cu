@@ -15,7 +15,6 @@
 // a zeroed accumulator; the last CTA to finish (ticket counter) turns the accumulators into the
 // result and zeroes them again, so the scratch is reusable without a memset.
 #include "common.cuh"
-#include "supcon_common.cuh"   // PeerOut (peer-memory destinations + flags)
 
 namespace scb {
 
@@ -213,9 +212,11 @@ __device__ __forceinline__ void merged_stats(const float* __restrict__ stats_all
 }
 
 // ------------------------------------------------------------------ B2+B3: apply (NHWC)
-template <typename T, int VEC>
+// y = x * a_c + b_c (+ z) (ReLU).  The CTA walks its rows from the LAST chunk to the first: the statistics pass
+// before it read the same rows front to back, so the tail of every CTA's range is what the L2 still holds.
+template <typename T, int VEC, bool kAdd>
 __global__ void __launch_bounds__(kBnThreads)
-bn_apply_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, int TX,
+bn_apply_nhwc_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __restrict__ y, int64_t M, int C, int TX,
                      int64_t rows_per_cta, const float* __restrict__ stats_all, int n_ranks,
                      const float* __restrict__ weight, const float* __restrict__ bias,
                      float* running_mean, float* running_var, float momentum, float eps,
@@ -225,19 +226,7 @@ bn_apply_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int 
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int W = TX * VEC;
     const int tile_c0 = blockIdx.x * W;
-    // Put the first batch of row loads in flight before the (dependent) coefficient prologue.
     const int c0 = tile_c0 + tx * VEC;
-    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
-    int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
-    const int64_t step = (int64_t)TY * C;
-    const T* p = x + r * C + c0;
-    T* q = y + r * C + c0;
-    float v0[kUnroll][VEC];
-    if (c0 < C) {
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u)
-            if (r + (int64_t)u * TY < r_end) load_row_vec<T, VEC>(p + u * step, v0[u]);
-    }
     for (int t = threadIdx.x; t < W; t += kBnThreads) {
         const int c = tile_c0 + t;
         float a = 0.f, b = 0.f;
@@ -266,58 +255,59 @@ bn_apply_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int 
 #pragma unroll
     for (int i = 0; i < VEC; ++i) { a[i] = sm[tx * VEC + i]; b[i] = sm[W + tx * VEC + i]; }
     const bool relu = (flags & SCB_BN_RELU) != 0;
-#pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-        if (r + (int64_t)u * TY < r_end) {
-#pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                float o = fmaf(v0[u][i], a[i], b[i]);
-                v0[u][i] = relu ? fmaxf(o, 0.f) : o;
-            }
-            store_row_vec<T, VEC>(q + u * step, v0[u]);
-        }
-    }
-    r += kUnroll * TY; p += kUnroll * step; q += kUnroll * step;
-    for (; r + (kUnroll - 1) * TY < r_end; r += kUnroll * TY, p += kUnroll * step, q += kUnroll * step) {
-        float v[kUnroll][VEC];
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) load_row_vec<T, VEC>(p + u * step, v[u]);
+    const int64_t r_beg = (int64_t)blockIdx.y * rows_per_cta;
+    const int64_t r_end = min(M, r_beg + rows_per_cta);
+    const int64_t chunk = (int64_t)kUnroll * TY;
+    for (int64_t k = (r_end - r_beg + chunk - 1) / chunk - 1; k >= 0; --k) {
+        const int64_t rk = r_beg + k * chunk + ty;
+        float v[kUnroll][VEC], vz[kUnroll][VEC];
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-#pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                float o = fmaf(v[u][i], a[i], b[i]);
-                v[u][i] = relu ? fmaxf(o, 0.f) : o;
+            const int64_t r = rk + (int64_t)u * TY;
+            if (r < r_end) {
+                load_row_vec<T, VEC>(x + r * C + c0, v[u]);
+                if (kAdd) load_row_vec<T, VEC>(z + r * C + c0, vz[u]);
             }
-            store_row_vec<T, VEC>(q + u * step, v[u]);
         }
-    }
-    for (; r < r_end; r += TY, p += step, q += step) {
-        float v[VEC];
-        load_row_vec<T, VEC>(p, v);
 #pragma unroll
-        for (int i = 0; i < VEC; ++i) {
-            float o = fmaf(v[i], a[i], b[i]);
-            v[i] = relu ? fmaxf(o, 0.f) : o;
+        for (int u = 0; u < kUnroll; ++u) {
+            const int64_t r = rk + (int64_t)u * TY;
+            if (r < r_end) {
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    float o = fmaf(v[u][i], a[i], b[i]);
+                    if (kAdd) o += vz[u][i];
+                    v[u][i] = relu ? fmaxf(o, 0.f) : o;
+                }
+                store_row_vec<T, VEC>(y + r * C + c0, v[u]);
+            }
         }
-        store_row_vec<T, VEC>(q, v);
     }
 }
 
+// gate of the fused ReLU in the backward passes:
+//   kGate 0: none;  1: ReLU directly after the normalisation, y > 0 recomputed from x;
+//   2: ReLU after a residual add (SCB_BN_RELU | SCB_BN_ADD): y > 0 read from the saved output
+template <int kGate>
+__device__ __forceinline__ float gate_dy(float g, float xm, float a, float b, float yv) {
+    if (kGate == 1) return (fmaf(xm, a, b) > 0.f) ? g : 0.f;
+    if (kGate == 2) return (yv > 0.f) ? g : 0.f;
+    return g;
+}
+
 // ------------------------------------------------------------------ B4: backward reduce (NHWC)
-template <typename T, int VEC>
+template <typename T, int VEC, int kGate>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t M, int C, int TX,
-                          int64_t rows_per_cta, const float* __restrict__ mean,
+bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yout, int64_t M,
+                          int C, int TX, int64_t rows_per_cta, const float* __restrict__ mean,
                           const float* __restrict__ invstd, const float* __restrict__ weight,
                           const float* __restrict__ bias, float* __restrict__ acc, unsigned* counter,
-                          float* __restrict__ out_sums, float* grad_weight, float* grad_bias, int flags) {
+                          float* __restrict__ out_sums, float* grad_weight, float* grad_bias) {
     extern __shared__ float sm[];
     const int TY = kBnThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = (blockIdx.x * TX + tx) * VEC;
     const bool active = c0 < C;
-    const bool relu = (flags & SCB_BN_RELU) != 0;
     float s1[VEC], s2[VEC], mu[VEC], a[VEC], b[VEC];
 #pragma unroll
     for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; mu[i] = 0.f; a[i] = 0.f; b[i] = 0.f; }
@@ -325,43 +315,36 @@ bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, int
 #pragma unroll
         for (int i = 0; i < VEC; ++i) {
             mu[i] = mean[c0 + i];
-            if (relu) {   // y = (x - mu) * a + b, gate dy by y > 0
+            if (kGate == 1) {   // y = (x - mu) * a + b, gate dy by y > 0
                 a[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
                 b[i] = bias ? bias[c0 + i] : 0.f;
             }
         }
         const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
-        int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
-        const int64_t step = (int64_t)TY * C;
-        const T* px = x + r * C + c0;
-        const T* pd = dy + r * C + c0;
-        constexpr int U = 4;   // 4 rows x 2 tensors = 8 vector loads in flight
-        for (; r + (U - 1) * TY < r_end; r += U * TY, px += U * step, pd += U * step) {
-            float vx[U][VEC], vd[U][VEC];
+        constexpr int U = 4;   // 4 rows x 2 (3) tensors = 8 (12) vector loads in flight
+        for (int64_t rk = (int64_t)blockIdx.y * rows_per_cta + ty; rk < r_end; rk += (int64_t)U * TY) {
+            float vx[U][VEC], vd[U][VEC], vy[U][VEC];
 #pragma unroll
-            for (int u = 0; u < U; ++u) { load_row_vec<T, VEC>(px + u * step, vx[u]); load_row_vec<T, VEC>(pd + u * step, vd[u]); }
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-#pragma unroll
-                for (int i = 0; i < VEC; ++i) {
-                    const float xm = vx[u][i] - mu[i];
-                    float g = vd[u][i];
-                    if (relu) g = (fmaf(xm, a[i], b[i]) > 0.f) ? g : 0.f;
-                    s1[i] += g;
-                    s2[i] = fmaf(g, xm, s2[i]);
+            for (int u = 0; u < U; ++u) {
+                const int64_t r = rk + (int64_t)u * TY;
+                if (r < r_end) {
+                    load_row_vec<T, VEC>(x + r * C + c0, vx[u]);
+                    load_row_vec<T, VEC>(dy + r * C + c0, vd[u]);
+                    if (kGate == 2) load_row_vec<T, VEC>(yout + r * C + c0, vy[u]);
                 }
-        }
-        for (; r < r_end; r += TY, px += step, pd += step) {
-            float vx[VEC], vd[VEC];
-            load_row_vec<T, VEC>(px, vx);
-            load_row_vec<T, VEC>(pd, vd);
+            }
 #pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                const float xm = vx[i] - mu[i];
-                float g = vd[i];
-                if (relu) g = (fmaf(xm, a[i], b[i]) > 0.f) ? g : 0.f;
-                s1[i] += g;
-                s2[i] = fmaf(g, xm, s2[i]);
+            for (int u = 0; u < U; ++u) {
+                const int64_t r = rk + (int64_t)u * TY;
+                if (r < r_end) {
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) {
+                        const float xm = vx[u][i] - mu[i];
+                        const float g = gate_dy<kGate>(vd[u][i], xm, a[i], b[i], kGate == 2 ? vy[u][i] : 0.f);
+                        s1[i] += g;
+                        s2[i] = fmaf(g, xm, s2[i]);
+                    }
+                }
             }
         }
     }
@@ -387,18 +370,19 @@ bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, int
 }
 
 // ------------------------------------------------------------------ B5: backward apply (NHWC)
-template <typename T, int VEC>
+// rows walked back to front (see bn_apply_nhwc_kernel); kGate 2 also writes dz = gated dy, the gradient of the
+// residual operand
+template <typename T, int VEC, int kGate>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_apply_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx,
-                         int64_t M, int C, int TX, int64_t rows_per_cta,
+bn_bwd_apply_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yout,
+                         T* __restrict__ dx, T* __restrict__ dz, int64_t M, int C, int TX, int64_t rows_per_cta,
                          const float* __restrict__ mean, const float* __restrict__ invstd,
                          const float* __restrict__ weight, const float* __restrict__ bias,
-                         const float* __restrict__ sums, const float* __restrict__ n_total, int flags) {
+                         const float* __restrict__ sums, const float* __restrict__ n_total) {
     const int TY = kBnThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = (blockIdx.x * TX + tx) * VEC;
     if (c0 >= C) return;
-    const bool relu = (flags & SCB_BN_RELU) != 0;
     const float inv_n = 1.f / n_total[0];
     // dx = (dy - k2 - (x - mu) * k3) * k1
     float mu[VEC], k1[VEC], k2[VEC], k3[VEC], bb[VEC];
@@ -412,41 +396,37 @@ bn_bwd_apply_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
         k3[i] = is * is * sums[C + c] * inv_n;
         bb[i] = bias ? bias[c] : 0.f;
     }
-    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
-    int64_t r = (int64_t)blockIdx.y * rows_per_cta + ty;
-    const int64_t step = (int64_t)TY * C;
-    const T* px = x + r * C + c0;
-    const T* pd = dy + r * C + c0;
-    T* po = dx + r * C + c0;
+    const int64_t r_beg = (int64_t)blockIdx.y * rows_per_cta;
+    const int64_t r_end = min(M, r_beg + rows_per_cta);
     constexpr int U = 4;
-    for (; r + (U - 1) * TY < r_end; r += U * TY, px += U * step, pd += U * step, po += U * step) {
-        float vx[U][VEC], vd[U][VEC];
-#pragma unroll
-        for (int u = 0; u < U; ++u) { load_row_vec<T, VEC>(px + u * step, vx[u]); load_row_vec<T, VEC>(pd + u * step, vd[u]); }
+    const int64_t chunk = (int64_t)U * TY;
+    for (int64_t k = (r_end - r_beg + chunk - 1) / chunk - 1; k >= 0; --k) {
+        const int64_t rk = r_beg + k * chunk + ty;
+        float vx[U][VEC], vd[U][VEC], vy[U][VEC];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-#pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                const float xm = vx[u][i] - mu[i];
-                float g = vd[u][i];
-                if (relu) g = (fmaf(xm, k1[i], bb[i]) > 0.f) ? g : 0.f;
-                vd[u][i] = (g - k2[i] - xm * k3[i]) * k1[i];
+            const int64_t r = rk + (int64_t)u * TY;
+            if (r < r_end) {
+                load_row_vec<T, VEC>(x + r * C + c0, vx[u]);
+                load_row_vec<T, VEC>(dy + r * C + c0, vd[u]);
+                if (kGate == 2) load_row_vec<T, VEC>(yout + r * C + c0, vy[u]);
             }
-            store_row_vec<T, VEC>(po + u * step, vd[u]);
         }
-    }
-    for (; r < r_end; r += TY, px += step, pd += step, po += step) {
-        float vx[VEC], vd[VEC];
-        load_row_vec<T, VEC>(px, vx);
-        load_row_vec<T, VEC>(pd, vd);
 #pragma unroll
-        for (int i = 0; i < VEC; ++i) {
-            const float xm = vx[i] - mu[i];
-            float g = vd[i];
-            if (relu) g = (fmaf(xm, k1[i], bb[i]) > 0.f) ? g : 0.f;
-            vd[i] = (g - k2[i] - xm * k3[i]) * k1[i];
+        for (int u = 0; u < U; ++u) {
+            const int64_t r = rk + (int64_t)u * TY;
+            if (r < r_end) {
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float xm = vx[u][i] - mu[i];
+                    const float g = gate_dy<kGate>(vd[u][i], xm, k1[i], bb[i], kGate == 2 ? vy[u][i] : 0.f);
+                    vd[u][i] = g;
+                    vx[u][i] = (g - k2[i] - xm * k3[i]) * k1[i];
+                }
+                store_row_vec<T, VEC>(dx + r * C + c0, vx[u]);
+                if (kGate == 2 && dz != nullptr) store_row_vec<T, VEC>(dz + r * C + c0, vd[u]);
+            }
         }
-        store_row_vec<T, VEC>(po, vd);
     }
 }
 
@@ -846,532 +826,3 @@ extern "C" int scb_bn_stats_noalloc(const void* x, int dtype, int channels_last,
     return scb_bn_stats(x, dtype, channels_last, outer, channels, inner, out_stats, scratch, need, stream_);
 }
 
-// ================================================================== single-launch passes (one rank)
-// When the whole activation fits in the registers of one resident wave (BASELINE cfg 2: 8 MiB over
-// 148 SMs), statistics and normalisation run in ONE cooperative launch: every thread keeps its rows
-// (raw 16-byte vectors) in registers across a grid-wide barrier, so x is read once and the second
-// kernel launch disappears (forward 3S -> 2S of traffic, backward 5S -> 3S).  Only used at world
-// size 1 -- with more ranks the statistics have to cross the NCCL exchange between the two halves --
-// and only for channels-last tensors with a vectorisable channel count; otherwise the two-kernel
-// path above runs.
-namespace scb {
-
-constexpr int kFusedRows = 4;      // rows a thread keeps in registers
-constexpr int kFusedThreads = 1024; // one fat CTA per SM: a single load/reduce/barrier latency chain per SM
-
-// grid-wide barrier for a cooperative launch (all CTAs are co-resident): arrive, then spin
-__device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned total) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(counter, 1u);
-        while (*reinterpret_cast<volatile unsigned*>(counter) < total) { }
-        __threadfence();
-    }
-    __syncthreads();
-}
-
-// ---- cross-GPU phase of the fused kernels (world size > 1) ------------------------------------------
-// After the local grid barrier CTA (0,0) stores this rank's per-channel message into every rank's gathered
-// buffer over NVLink and raises this rank's flag everywhere; every CTA then waits until the flags of all
-// ranks show the current exchange and reads the gathered messages from its OWN copy.  The exchange number
-// is state[1] + 1, read by every CTA before the grid barrier (CTA (0,0) only bumps it after the barrier).
-struct BnPeer {
-    PeerOut po;                 // n_dst = 0: single rank, no exchange
-    const float* gathered;      // this rank's copy: [n_dst][message length]
-    const unsigned* flags;      // this rank's flag array, one word per rank
-    int rank;
-};
-
-__device__ __forceinline__ void bn_peer_publish(const BnPeer& bp, unsigned want) {   // CTA (0,0), all threads
-    __syncthreads();                            // the CTA's remote stores happen-before thread 0's fence
-    if (threadIdx.x == 0) {
-        __threadfence_system();
-        bp.po.state[1] = want;
-        for (int w = 0; w < bp.po.n_dst; ++w)
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(bp.po.flag[w]), "r"(want) : "memory");
-    }
-}
-
-__device__ __forceinline__ void bn_peer_wait(const BnPeer& bp, unsigned want) {      // every CTA, all threads
-    if ((int)threadIdx.x < bp.po.n_dst) {
-        unsigned long long t0 = 0;
-        for (unsigned spins = 1;; ++spins) {
-            unsigned v;
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(bp.flags + threadIdx.x) : "memory");
-            if ((int)(v - want) >= 0) break;
-            if ((spins & 1023u) == 0u) {            // a peer that died must not hang this GPU for ever
-                unsigned long long now;
-                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
-                if (t0 == 0) t0 = now;
-                else if (now - t0 > 30000000000ull) __trap();
-            }
-        }
-    }
-    __syncthreads();
-}
-
-// After the grid barrier every CTA reads the sums; the last one to have done so (second ticket) zeroes
-// the accumulators and both tickets so the scratch is ready for the next launch.
-__device__ __forceinline__ void rearm_scratch(float* acc, unsigned* counters, unsigned total, int n_acc) {
-    __shared__ unsigned s_last2;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        s_last2 = (atomicAdd(counters + 1, 1u) == total - 1) ? 1u : 0u;
-    }
-    __syncthreads();
-    if (s_last2) {
-        for (int c = threadIdx.x; c < n_acc; c += blockDim.x) acc[c] = 0.f;
-        if (threadIdx.x == 0) { counters[0] = 0u; counters[1] = 0u; }
-    }
-}
-
-template <typename T, int VEC>
-__global__ void __launch_bounds__(kFusedThreads, 1)
-bn_fwd_fused_nhwc_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, int TX, int64_t rows_per_cta,
-                         float* __restrict__ acc, unsigned* counters,
-                         const float* __restrict__ weight, const float* __restrict__ bias,
-                         float* running_mean, float* running_var, float momentum, float eps,
-                         float* save_mean, float* save_invstd, float* save_count, int flags, const BnPeer bp) {
-    extern __shared__ float sm[];
-    const int TY = kFusedThreads / TX;
-    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
-    const int c0 = (blockIdx.x * TX + tx) * VEC;
-    const bool active = c0 < C;
-    const unsigned total = gridDim.x * gridDim.y;
-    const unsigned want = (bp.po.n_dst > 0) ? __ldcg(bp.po.state + 1) + 1u : 0u;
-    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
-    const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta + ty;
-    const int64_t step = (int64_t)TY * C;
-    uint4 raw[kFusedRows];
-    float s1[VEC], s2[VEC], k0[VEC];
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; k0[i] = 0.f; }
-    int nrow = 0;
-    if (active) {
-        load_row_vec_cached<T, VEC>(x + c0, k0);
-        const T* p = x + r0 * C + c0;
-#pragma unroll
-        for (int u = 0; u < kFusedRows; ++u)
-            if (r0 + (int64_t)u * TY < r_end) { raw[u] = ldg_stream16(p + u * step); nrow = u + 1; }
-#pragma unroll
-        for (int u = 0; u < kFusedRows; ++u) {
-            if (u < nrow) {
-                const T* e = reinterpret_cast<const T*>(&raw[u]);
-#pragma unroll
-                for (int i = 0; i < VEC; ++i) {
-                    const float d = to_f32(e[i]) - k0[i];
-                    s1[i] += d;
-                    s2[i] = fmaf(d, d, s2[i]);
-                }
-            }
-        }
-    }
-    const int R = bn_replicas(C);
-    {
-        float* my_acc = acc + (size_t)(blockIdx.y % R) * 2 * C;
-        cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, my_acc, my_acc + C);
-    }
-    grid_barrier(counters, total);
-    const float n = (float)M;
-    if (bp.po.n_dst > 0) {
-        if (blockIdx.x == 0 && blockIdx.y == 0) {
-            // this rank's message [mean (C) | M2 (C) | count] goes to every rank (_functions.py:41-56)
-            const int stride = 2 * C + 1;
-            for (int c = threadIdx.x; c < C; c += blockDim.x) {
-                float sa = 0.f, sb = 0.f;
-                for (int rr = 0; rr < R; ++rr) {
-                    sa += __ldcg(acc + (size_t)rr * 2 * C + c);
-                    sb += __ldcg(acc + (size_t)rr * 2 * C + C + c);
-                }
-                const float mean_r = to_f32(x[c]) + sa / n;
-                const float m2_r = fmaxf(sb - sa * sa / n, 0.f);
-                for (int w = 0; w < bp.po.n_dst; ++w) {
-                    float* d = reinterpret_cast<float*>(bp.po.dst[w]) + (size_t)bp.rank * stride;
-                    d[c] = mean_r;
-                    d[C + c] = m2_r;
-                }
-            }
-            if (threadIdx.x == 0)
-                for (int w = 0; w < bp.po.n_dst; ++w)
-                    reinterpret_cast<float*>(bp.po.dst[w])[(size_t)bp.rank * stride + 2 * C] = n;
-            bn_peer_publish(bp, want);
-        }
-        bn_peer_wait(bp, want);
-    }
-    // One thread per channel of the CTA's tile fetches the completed sums (a single pass over a few
-    // cache lines per CTA -- letting every thread read them turns those lines into an L2 hot spot)
-    // and leaves the per-channel scale / offset in shared memory.
-    const int W = TX * VEC;
-    const int tile_c0 = blockIdx.x * W;
-    __syncthreads();                       // the reduction is done with sm[]
-    for (int t = threadIdx.x; t < W; t += blockDim.x) {
-        const int c = tile_c0 + t;
-        float av = 0.f, bv = 0.f;
-        if (c < C) {
-            float mean, m2, invstd, nn = n;
-            if (bp.po.n_dst > 0) {
-                merged_stats(bp.gathered, bp.po.n_dst, C, c, nullptr, nullptr, eps, mean, invstd, m2, nn);
-            } else {
-                float sa = 0.f, sb = 0.f;
-                for (int rr = 0; rr < R; ++rr) {
-                    sa += __ldcg(acc + (size_t)rr * 2 * C + c);
-                    sb += __ldcg(acc + (size_t)rr * 2 * C + C + c);
-                }
-                mean = to_f32(x[c]) + sa / n;
-                m2 = fmaxf(sb - sa * sa / n, 0.f);
-                invstd = rsqrtf(m2 / n + eps);
-            }
-            av = (weight ? weight[c] : 1.f) * invstd;
-            bv = (bias ? bias[c] : 0.f) - mean * av;
-            if (blockIdx.y == 0) {
-                if (save_mean) save_mean[c] = mean;
-                if (save_invstd) save_invstd[c] = invstd;
-                if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-                if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (nn - 1.f));
-                if (c == 0 && save_count) save_count[0] = nn;
-            }
-        }
-        sm[t] = av;
-        sm[W + t] = bv;
-    }
-    __syncthreads();
-    float a[VEC], b[VEC];
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) { a[i] = sm[tx * VEC + i]; b[i] = sm[W + tx * VEC + i]; }
-    // second ticket: once every CTA has read the sums, the last one re-arms the scratch
-    rearm_scratch(acc, counters, total, R * 2 * C);
-    if (!active) return;
-    const bool relu = (flags & SCB_BN_RELU) != 0;
-    T* q = y + r0 * C + c0;
-#pragma unroll
-    for (int u = 0; u < kFusedRows; ++u) {
-        if (u < nrow) {
-            const T* e = reinterpret_cast<const T*>(&raw[u]);
-            uint4 o;
-            T* oe = reinterpret_cast<T*>(&o);
-#pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                float v = fmaf(to_f32(e[i]), a[i], b[i]);
-                oe[i] = from_f32<T>(relu ? fmaxf(v, 0.f) : v);
-            }
-            stg_stream16(q + u * step, o);
-        }
-    }
-}
-
-// kRelu is a template parameter: without it the kernel keeps eight fewer per-channel values alive across the
-// barrier (gate scale / offset, gate bits) and fits its 64 registers without spilling.
-template <typename T, int VEC, bool kRelu>
-__global__ void __launch_bounds__(kFusedThreads, 1)
-bn_bwd_fused_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t M, int C, int TX,
-                         int64_t rows_per_cta, float* __restrict__ acc, unsigned* counters,
-                         const float* __restrict__ mean, const float* __restrict__ invstd,
-                         const float* __restrict__ weight, const float* __restrict__ bias,
-                         const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias,
-                         int flags, const BnPeer bp) {
-    extern __shared__ float sm[];
-    const unsigned want = (bp.po.n_dst > 0) ? __ldcg(bp.po.state + 1) + 1u : 0u;
-    const int TY = kFusedThreads / TX;
-    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
-    const int c0 = (blockIdx.x * TX + tx) * VEC;
-    const bool active = c0 < C;
-    (void)flags;
-    const unsigned total = gridDim.x * gridDim.y;
-    const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
-    const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta + ty;
-    const int64_t step = (int64_t)TY * C;
-    uint4 rx[kFusedRows], rd[kFusedRows];
-    unsigned gated[kFusedRows];            // ReLU: bit i set = element i of the row had y <= 0 (dy is dropped)
-    float s1[VEC], s2[VEC], mu[VEC], k1[VEC], bb[VEC];
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; mu[i] = 0.f; k1[i] = 0.f; bb[i] = 0.f; }
-    int nrow = 0;
-    if (active) {
-        const T* px = x + r0 * C + c0;
-        const T* pd = dy + r0 * C + c0;
-#pragma unroll
-        for (int u = 0; u < kFusedRows; ++u)
-            if (r0 + (int64_t)u * TY < r_end) {
-                rx[u] = ldg_stream16(px + u * step);
-                rd[u] = ldg_stream16(pd + u * step);
-                nrow = u + 1;
-            }
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) {
-            mu[i] = mean[c0 + i];
-            if (kRelu) {
-                k1[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
-                bb[i] = bias ? bias[c0 + i] : 0.f;
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < kFusedRows; ++u) {
-            gated[u] = 0u;
-            if (u < nrow) {
-                const T* ex = reinterpret_cast<const T*>(&rx[u]);
-                const T* ed = reinterpret_cast<const T*>(&rd[u]);
-#pragma unroll
-                for (int i = 0; i < VEC; ++i) {
-                    const float xm = to_f32(ex[i]) - mu[i];
-                    float g = to_f32(ed[i]);
-                    if (kRelu && !(fmaf(xm, k1[i], bb[i]) > 0.f)) { g = 0.f; gated[u] |= 1u << i; }
-                    s1[i] += g;
-                    s2[i] = fmaf(g, xm, s2[i]);
-                }
-            }
-        }
-    }
-    const int R = bn_replicas(C);
-    {
-        float* my_acc = acc + (size_t)(blockIdx.y % R) * 2 * C;
-        cta_reduce_to_global<VEC>(s1, s2, sm, tx, ty, TX, TY, c0, C, my_acc, my_acc + C);
-    }
-    grid_barrier(counters, total);
-    if (bp.po.n_dst > 0) {
-        if (blockIdx.x == 0 && blockIdx.y == 0) {
-            // this rank's sums [sum dy (C) | sum dy (x - mean) (C)] go to every rank: the all-reduce of
-            // _functions.py:155-165 as an all-gather + a local sum in fixed rank order
-            for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
-                float v = 0.f;
-                for (int rr = 0; rr < R; ++rr) v += __ldcg(acc + (size_t)rr * 2 * C + c);
-                for (int w = 0; w < bp.po.n_dst; ++w)
-                    reinterpret_cast<float*>(bp.po.dst[w])[(size_t)bp.rank * 2 * C + c] = v;
-            }
-            bn_peer_publish(bp, want);
-        }
-        bn_peer_wait(bp, want);
-    }
-    const float inv_n = 1.f / n_total[0];
-    const int W = TX * VEC;
-    const int tile_c0 = blockIdx.x * W;
-    __syncthreads();
-    for (int t = threadIdx.x; t < W; t += blockDim.x) {     // one reader per channel (see the forward kernel)
-        const int c = tile_c0 + t;
-        float v2 = 0.f, v3 = 0.f;
-        if (c < C) {
-            float sd = 0.f, sx = 0.f;
-            for (int rr = 0; rr < R; ++rr) {
-                sd += __ldcg(acc + (size_t)rr * 2 * C + c);
-                sx += __ldcg(acc + (size_t)rr * 2 * C + C + c);
-            }
-            const float is = invstd[c];
-            float gd = sd, gx = sx;                 // global sums (dx); dgamma / dbeta below stay local
-            if (bp.po.n_dst > 0) {
-                gd = 0.f; gx = 0.f;
-                for (int w = 0; w < bp.po.n_dst; ++w) {
-                    gd += __ldcg(bp.gathered + (size_t)w * 2 * C + c);
-                    gx += __ldcg(bp.gathered + (size_t)w * 2 * C + C + c);
-                }
-            }
-            v2 = gd * inv_n;
-            v3 = is * is * gx * inv_n;
-            if (blockIdx.y == 0) {
-                if (out_sums) { out_sums[c] = sd; out_sums[C + c] = sx; }
-                if (grad_weight) grad_weight[c] = sx * is;
-                if (grad_bias) grad_bias[c] = sd;
-            }
-        }
-        sm[t] = v2;
-        sm[W + t] = v3;
-    }
-    __syncthreads();
-    float k2[VEC], k3[VEC];
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) { k2[i] = sm[tx * VEC + i]; k3[i] = sm[W + tx * VEC + i]; }
-    if (!kRelu && active) {
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) k1[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
-    }
-    rearm_scratch(acc, counters, total, R * 2 * C);
-    if (!active) return;
-    T* po = dx + r0 * C + c0;
-#pragma unroll
-    for (int u = 0; u < kFusedRows; ++u) {
-        if (u < nrow) {
-            const T* ex = reinterpret_cast<const T*>(&rx[u]);
-            const T* ed = reinterpret_cast<const T*>(&rd[u]);
-            uint4 o;
-            T* oe = reinterpret_cast<T*>(&o);
-#pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                const float xm = to_f32(ex[i]) - mu[i];
-                const float g = (kRelu && ((gated[u] >> i) & 1u)) ? 0.f : to_f32(ed[i]);
-                oe[i] = from_f32<T>((g - k2[i] - xm * k3[i]) * k1[i]);
-            }
-            stg_stream16(po + u * step, o);
-        }
-    }
-}
-
-// geometry of the fused pass: one resident wave, <= kFusedRows rows per thread; false if it does not fit
-static bool fused_geom(int64_t M, int C, int elem_size, bool al16, NhwcGeom* g, int ctas_per_sm) {
-    const int vmax = 16 / elem_size;
-    if (!al16 || C % vmax != 0 || M < 2) return false;
-    *g = nhwc_geom(M, C, elem_size, true, ctas_per_sm * sm_count(), kFusedThreads);
-    if (g->rows_per_cta > (int64_t)g->ty * kFusedRows) return false;           // would need more registers
-    if ((int64_t)g->grid_x * g->grid_y > (int64_t)ctas_per_sm * sm_count()) return false;   // not one wave
-    return true;
-}
-
-template <typename Kern>
-static int fused_ctas_per_sm(Kern kern, size_t smem) {
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kFusedThreads, smem) != cudaSuccess) return 0;
-    return n;
-}
-
-}  // namespace scb
-
-extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner) {
-    if (!channels_last || channels <= 0) return 0;
-    const int es = (dtype == SCB_F32) ? 4 : 2;
-    NhwcGeom g;
-    return fused_geom(outer * inner, channels, es, true, &g, 1) ? 1 : 0;
-}
-
-static int make_bn_peer(const scb_peer_channel* ch, const float* gathered_local, const uint32_t* flags_local, int rank,
-                        BnPeer* bp) {
-    bp->po = PeerOut::none();
-    bp->gathered = nullptr; bp->flags = nullptr; bp->rank = 0;
-    if (ch == nullptr) return SCB_OK;
-    SCB_REQUIRE(ch->state && ch->n_dst >= 1 && ch->n_dst <= 16 && gathered_local && flags_local && rank >= 0 &&
-                rank < ch->n_dst, "bn fused peers: bad channel, buffers or rank");
-    for (int w = 0; w < ch->n_dst; ++w)
-        SCB_REQUIRE(ch->dst[w] && ch->flag[w], "bn fused peers: destination %d is null", w);
-    bp->po = PeerOut::of(ch);
-    bp->gathered = gathered_local;
-    bp->flags = (const unsigned*)flags_local;
-    bp->rank = rank;
-    return SCB_OK;
-}
-
-static int bn_forward_fused_impl(const void* x, void* y, int dtype, int64_t rows, int channels,
-                                 const float* weight, const float* bias, float* running_mean,
-                                 float* running_var, float momentum, float eps, float* save_mean,
-                                 float* save_invstd, float* save_count, int flags, void* workspace,
-                                 int64_t workspace_bytes, void* stream_, const BnPeer& bp) {
-    if (int e = check_bn_common(x, dtype, rows, channels, 1)) return e;
-    SCB_REQUIRE(y && workspace && workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_forward_fused: bad buffers");
-    cudaStream_t stream = (cudaStream_t)stream_;
-    int64_t M = rows;
-    int C = channels;
-    float* acc = (float*)workspace;
-    unsigned* counters = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
-    int rc = SCB_ERR_UNSUPPORTED;
-    SCB_DISPATCH_FLOAT(dtype, T, {
-        constexpr int VEC = Vec16<T>::N;
-        NhwcGeom g;
-        auto kern = bn_fwd_fused_nhwc_kernel<T, VEC>;
-        const size_t smem = 2 * kFusedThreads * VEC * sizeof(float);
-        set_max_dynamic_smem(kern, (int)smem);
-        const int per_sm = fused_ctas_per_sm(kern, smem);
-        if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(y), &g, 1)) {
-            dim3 grid(g.grid_x, (unsigned)g.grid_y);
-            int TX = g.tx;
-            int64_t rpc = g.rows_per_cta;
-            const T* xp = (const T*)x;
-            T* yp = (T*)y;
-            // A plain launch: the grid has at most one CTA per SM and each CTA owns a full SM (1024 threads,
-            // 64 KiB of shared memory), so all of them become resident without needing anything from each
-            // other; cudaLaunchCooperativeKernel would add tens of microseconds of launch latency here.
-            kern<<<grid, kFusedThreads, smem, stream>>>(xp, yp, M, C, TX, rpc, acc, counters, weight, bias, running_mean,
-                                                        running_var, momentum, eps, save_mean, save_invstd, save_count,
-                                                        flags, bp);
-            SCB_CUDA_OK(cudaGetLastError());
-            rc = SCB_OK;
-        }
-    });
-    if (rc == SCB_ERR_UNSUPPORTED) { set_error("bn_forward_fused: tensor does not fit one resident wave"); return rc; }
-    count_launch();
-    return SCB_OK;
-}
-
-static int bn_backward_fused_impl(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
-                                  const float* mean, const float* invstd, const float* weight, const float* bias,
-                                  const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
-                                  int flags, void* workspace, int64_t workspace_bytes, void* stream_, const BnPeer& bp) {
-    if (int e = check_bn_common(x, dtype, rows, channels, 1)) return e;
-    SCB_REQUIRE(dy && dx && mean && invstd && n_total && workspace &&
-                workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_backward_fused: bad buffers");
-    cudaStream_t stream = (cudaStream_t)stream_;
-    int64_t M = rows;
-    int C = channels;
-    float* acc = (float*)workspace;
-    unsigned* counters = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
-    int rc = SCB_ERR_UNSUPPORTED;
-    SCB_DISPATCH_FLOAT(dtype, T, {
-        constexpr int VEC = Vec16<T>::N;
-        NhwcGeom g;
-        auto kern = (flags & SCB_BN_RELU) ? bn_bwd_fused_nhwc_kernel<T, VEC, true> : bn_bwd_fused_nhwc_kernel<T, VEC, false>;
-        const size_t smem = 2 * kFusedThreads * VEC * sizeof(float);
-        set_max_dynamic_smem(kern, (int)smem);
-        const int per_sm = fused_ctas_per_sm(kern, smem);
-        if (per_sm >= 1 && fused_geom(M, C, sizeof(T), aligned16(x) && aligned16(dy) && aligned16(dx), &g,
-                                      1)) {
-            dim3 grid(g.grid_x, (unsigned)g.grid_y);
-            int TX = g.tx;
-            int64_t rpc = g.rows_per_cta;
-            const T* dyp = (const T*)dy;
-            const T* xp = (const T*)x;
-            T* dxp = (T*)dx;
-            kern<<<grid, kFusedThreads, smem, stream>>>(dyp, xp, dxp, M, C, TX, rpc, acc, counters, mean, invstd, weight,
-                                                        bias, n_total, out_sums, grad_weight, grad_bias, flags, bp);
-            SCB_CUDA_OK(cudaGetLastError());
-            rc = SCB_OK;
-        }
-    });
-    if (rc == SCB_ERR_UNSUPPORTED) { set_error("bn_backward_fused: tensor does not fit one resident wave"); return rc; }
-    count_launch();
-    return SCB_OK;
-}
-
-extern "C" int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t rows, int channels,
-                                    const float* weight, const float* bias, float* running_mean,
-                                    float* running_var, float momentum, float eps, float* save_mean,
-                                    float* save_invstd, float* save_count, int flags, void* workspace,
-                                    int64_t workspace_bytes, void* stream_) {
-    BnPeer bp;
-    make_bn_peer(nullptr, nullptr, nullptr, 0, &bp);
-    return bn_forward_fused_impl(x, y, dtype, rows, channels, weight, bias, running_mean, running_var, momentum, eps,
-                                 save_mean, save_invstd, save_count, flags, workspace, workspace_bytes, stream_, bp);
-}
-
-extern "C" int scb_bn_backward_fused(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
-                                     const float* mean, const float* invstd, const float* weight, const float* bias,
-                                     const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
-                                     int flags, void* workspace, int64_t workspace_bytes, void* stream_) {
-    BnPeer bp;
-    make_bn_peer(nullptr, nullptr, nullptr, 0, &bp);
-    return bn_backward_fused_impl(dy, x, dx, dtype, rows, channels, mean, invstd, weight, bias, n_total, out_sums,
-                                  grad_weight, grad_bias, flags, workspace, workspace_bytes, stream_, bp);
-}
-
-extern "C" int scb_bn_forward_fused_peers(const void* x, void* y, int dtype, int64_t rows, int channels,
-                                          const float* weight, const float* bias, float* running_mean,
-                                          float* running_var, float momentum, float eps, float* save_mean,
-                                          float* save_invstd, float* save_count, int flags, void* workspace,
-                                          int64_t workspace_bytes, const scb_peer_channel* ch,
-                                          const float* gathered_local, const uint32_t* flags_local, int rank,
-                                          void* stream_) {
-    SCB_REQUIRE(ch != nullptr, "bn_forward_fused_peers: null channel");
-    BnPeer bp;
-    if (int e = make_bn_peer(ch, gathered_local, flags_local, rank, &bp)) return e;
-    return bn_forward_fused_impl(x, y, dtype, rows, channels, weight, bias, running_mean, running_var, momentum, eps,
-                                 save_mean, save_invstd, save_count, flags, workspace, workspace_bytes, stream_, bp);
-}
-
-extern "C" int scb_bn_backward_fused_peers(const void* dy, const void* x, void* dx, int dtype, int64_t rows,
-                                           int channels, const float* mean, const float* invstd, const float* weight,
-                                           const float* bias, const float* n_total, float* out_sums,
-                                           float* grad_weight, float* grad_bias, int flags, void* workspace,
-                                           int64_t workspace_bytes, const scb_peer_channel* ch,
-                                           const float* gathered_local, const uint32_t* flags_local, int rank,
-                                           void* stream_) {
-    SCB_REQUIRE(ch != nullptr, "bn_backward_fused_peers: null channel");
-    BnPeer bp;
-    if (int e = make_bn_peer(ch, gathered_local, flags_local, rank, &bp)) return e;
-    return bn_backward_fused_impl(dy, x, dx, dtype, rows, channels, mean, invstd, weight, bias, n_total, out_sums,
-                                  grad_weight, grad_bias, flags, workspace, workspace_bytes, stream_, bp);
-}
