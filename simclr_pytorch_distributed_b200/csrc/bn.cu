@@ -491,7 +491,7 @@ bn_stats_nchw_kernel(const T* __restrict__ x, int64_t N, int C, int64_t inner, i
 
 template <typename T, int VEC>
 __global__ void __launch_bounds__(kBnThreads)
-bn_apply_nchw_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t N, int C, int64_t inner,
+bn_apply_nchw_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __restrict__ y, int64_t N, int C, int64_t inner,
                      int64_t n_per_cta, const float* __restrict__ stats_all, int n_ranks,
                      const float* __restrict__ weight, const float* __restrict__ bias,
                      float* running_mean, float* running_var, float momentum, float eps,
@@ -514,17 +514,22 @@ bn_apply_nchw_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t N, int 
     const bool relu = (flags & SCB_BN_RELU) != 0;
     const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
     nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
-        float v[VEC];
+        float v[VEC], vz[VEC];
         load_row_vec<T, VEC>(x + off, v);
+        if (z != nullptr) load_row_vec<T, VEC>(z + off, vz);
 #pragma unroll
-        for (int i = 0; i < VEC; ++i) { float o = fmaf(v[i], a, b); v[i] = relu ? fmaxf(o, 0.f) : o; }
+        for (int i = 0; i < VEC; ++i) {
+            float o = fmaf(v[i], a, b);
+            if (z != nullptr) o += vz[i];
+            v[i] = relu ? fmaxf(o, 0.f) : o;
+        }
         store_row_vec<T, VEC>(y + off, v);
     });
 }
 
 template <typename T, int VEC>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_reduce_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t N, int C,
+bn_bwd_reduce_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yout, int64_t N, int C,
                           int64_t inner, int64_t n_per_cta, const float* __restrict__ mean,
                           const float* __restrict__ invstd, const float* __restrict__ weight,
                           const float* __restrict__ bias, float* __restrict__ acc, unsigned* counter,
@@ -533,19 +538,22 @@ bn_bwd_reduce_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, int
     const int c = blockIdx.x;
     const float mu = mean[c];
     const bool relu = (flags & SCB_BN_RELU) != 0;
+    const bool by_y = relu && (flags & SCB_BN_ADD) != 0;          // gate read from the saved output
     const float a = relu ? (weight ? weight[c] : 1.f) * invstd[c] : 0.f;
     const float b = (relu && bias) ? bias[c] : 0.f;
     const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
     float s1 = 0.f, s2 = 0.f;
     nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
-        float vx[VEC], vd[VEC];
+        float vx[VEC], vd[VEC], vy[VEC];
         load_row_vec<T, VEC>(x + off, vx);
         load_row_vec<T, VEC>(dy + off, vd);
+        if (by_y) load_row_vec<T, VEC>(yout + off, vy);
 #pragma unroll
         for (int i = 0; i < VEC; ++i) {
             const float xm = vx[i] - mu;
             float g = vd[i];
-            if (relu) g = (fmaf(xm, a, b) > 0.f) ? g : 0.f;
+            if (by_y) g = (vy[i] > 0.f) ? g : 0.f;
+            else if (relu) g = (fmaf(xm, a, b) > 0.f) ? g : 0.f;
             s1 += g; s2 = fmaf(g, xm, s2);
         }
     });
@@ -566,8 +574,8 @@ bn_bwd_reduce_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, int
 
 template <typename T, int VEC>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_apply_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx,
-                         int64_t N, int C, int64_t inner, int64_t n_per_cta,
+bn_bwd_apply_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yout,
+                         T* __restrict__ dx, T* __restrict__ dz, int64_t N, int C, int64_t inner, int64_t n_per_cta,
                          const float* __restrict__ mean, const float* __restrict__ invstd,
                          const float* __restrict__ weight, const float* __restrict__ bias,
                          const float* __restrict__ sums, const float* __restrict__ n_total, int flags) {
@@ -580,18 +588,23 @@ bn_bwd_apply_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* _
     const float k3 = is * is * sums[C + c] * inv_n;
     const float bb = bias ? bias[c] : 0.f;
     const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
+    const bool by_y = relu && (flags & SCB_BN_ADD) != 0;
     nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
-        float vx[VEC], vd[VEC];
+        float vx[VEC], vd[VEC], vy[VEC];
         load_row_vec<T, VEC>(x + off, vx);
         load_row_vec<T, VEC>(dy + off, vd);
+        if (by_y) load_row_vec<T, VEC>(yout + off, vy);
 #pragma unroll
         for (int i = 0; i < VEC; ++i) {
             const float xm = vx[i] - mu;
             float g = vd[i];
-            if (relu) g = (fmaf(xm, k1, bb) > 0.f) ? g : 0.f;
-            vd[i] = (g - k2 - xm * k3) * k1;
+            if (by_y) g = (vy[i] > 0.f) ? g : 0.f;
+            else if (relu) g = (fmaf(xm, k1, bb) > 0.f) ? g : 0.f;
+            vd[i] = g;
+            vx[i] = (g - k2 - xm * k3) * k1;
         }
-        store_row_vec<T, VEC>(dx + off, vd);
+        store_row_vec<T, VEC>(dx + off, vx);
+        if (by_y && dz != nullptr) store_row_vec<T, VEC>(dz + off, vd);
     });
 }
 
