@@ -680,7 +680,7 @@ extern "C" int scb_bn_stats(const void* x, int dtype, int channels_last, int64_t
     return SCB_OK;
 }
 
-extern "C" int scb_bn_apply(const void* x, void* y, int dtype, int channels_last, int64_t outer,
+extern "C" int scb_bn_apply(const void* x, const void* z, void* y, int dtype, int channels_last, int64_t outer,
                             int channels, int64_t inner, const float* stats_all, int n_ranks,
                             const float* weight, const float* bias, float* running_mean,
                             float* running_var, float momentum, float eps, float* save_mean,
@@ -690,24 +690,34 @@ extern "C" int scb_bn_apply(const void* x, void* y, int dtype, int channels_last
     SCB_REQUIRE(stats_all != nullptr || (running_mean && running_var),
                 "bn_apply: eval mode needs running_mean and running_var");
     SCB_REQUIRE(stats_all == nullptr || n_ranks >= 1, "bn_apply: n_ranks must be >= 1");
+    const bool add = (flags & SCB_BN_ADD) != 0;
+    SCB_REQUIRE(!add || z != nullptr, "bn_apply: SCB_BN_ADD needs the residual operand z");
+    if (!add) z = nullptr;
     cudaStream_t stream = (cudaStream_t)stream_;
     const int C = channels;
     if (outer * inner == 0) return SCB_OK;
     const int target = 4 * sm_count();
+    const bool al = aligned16(x) && aligned16(y) && (!add || aligned16(z));
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;
-            NhwcGeom g = nhwc_geom(M, C, sizeof(T), aligned16(x) && aligned16(y), target);
+            NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, target);
             dim3 grid(g.grid_x, (unsigned)g.grid_y);
             size_t smem = 2 * g.tx * g.vec * sizeof(float);
-            SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nhwc_kernel<T, VEC><<<grid, kBnThreads, smem, stream>>>(
-                (const T*)x, (T*)y, M, C, g.tx, g.rows_per_cta, stats_all, n_ranks, weight, bias,
-                running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
+            if (add) {
+                SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nhwc_kernel<T, VEC, true><<<grid, kBnThreads, smem, stream>>>(
+                    (const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta, stats_all, n_ranks, weight, bias,
+                    running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
+            } else {
+                SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nhwc_kernel<T, VEC, false><<<grid, kBnThreads, smem, stream>>>(
+                    (const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta, stats_all, n_ranks, weight, bias,
+                    running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
+            }
         } else {
-            NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), aligned16(x) && aligned16(y), target);
+            NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), al, target);
             dim3 grid(C, (unsigned)g.grid_y);
             SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
-                (const T*)x, (T*)y, outer, C, inner, g.n_per_cta, stats_all, n_ranks, weight, bias,
+                (const T*)x, (const T*)z, (T*)y, outer, C, inner, g.n_per_cta, stats_all, n_ranks, weight, bias,
                 running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
         }
     });
@@ -716,7 +726,15 @@ extern "C" int scb_bn_apply(const void* x, void* y, int dtype, int channels_last
     return SCB_OK;
 }
 
-extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, int channels_last,
+// gate mode of the backward kernels from the flags of the forward
+static int gate_mode(int flags) { return (flags & SCB_BN_RELU) ? ((flags & SCB_BN_ADD) ? 2 : 1) : 0; }
+
+#define SCB_GATE_SWITCH(gatev, GATE_, ...)                                \
+    if ((gatev) == 2) { constexpr int GATE_ = 2; __VA_ARGS__; }          \
+    else if ((gatev) == 1) { constexpr int GATE_ = 1; __VA_ARGS__; }     \
+    else { constexpr int GATE_ = 0; __VA_ARGS__; }
+
+extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, const void* y, int dtype, int channels_last,
                                       int64_t outer, int channels, int64_t inner, const float* mean,
                                       const float* invstd, const float* weight, const float* bias,
                                       float* out_sums, float* grad_weight, float* grad_bias, int flags,
@@ -724,6 +742,8 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, 
     if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
     SCB_REQUIRE(dy && mean && invstd && out_sums && workspace, "bn_backward_reduce: null pointer");
     SCB_REQUIRE(workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_backward_reduce: workspace too small");
+    const int gate = gate_mode(flags);
+    SCB_REQUIRE(gate != 2 || y != nullptr, "bn_backward_reduce: SCB_BN_RELU|SCB_BN_ADD needs the saved output y");
     cudaStream_t stream = (cudaStream_t)stream_;
     const int C = channels;
     if (outer * inner == 0) {
@@ -735,20 +755,23 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, 
     float* acc = (float*)workspace;
     unsigned* counter = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
     const int target = 4 * sm_count();   // one resident wave: every load of the pass is in flight at once
+    const bool al = aligned16(x) && aligned16(dy) && (gate != 2 || aligned16(y));
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;
-            NhwcGeom g = nhwc_geom(M, C, sizeof(T), aligned16(x) && aligned16(dy), target);
+            NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, target);
             dim3 grid(g.grid_x, (unsigned)g.grid_y);
             size_t smem = 2 * kBnThreads * g.vec * sizeof(float);
-            SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_reduce_nhwc_kernel<T, VEC><<<grid, kBnThreads, smem, stream>>>(
-                (const T*)dy, (const T*)x, M, C, g.tx, g.rows_per_cta, mean, invstd, weight, bias, acc,
-                counter, out_sums, grad_weight, grad_bias, flags)));
+            SCB_GATE_SWITCH(gate, GATE, {
+                SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_reduce_nhwc_kernel<T, VEC, GATE><<<grid, kBnThreads, smem, stream>>>(
+                    (const T*)dy, (const T*)x, (const T*)y, M, C, g.tx, g.rows_per_cta, mean, invstd, weight, bias, acc,
+                    counter, out_sums, grad_weight, grad_bias)));
+            });
         } else {
-            NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), aligned16(x) && aligned16(dy), target);
+            NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), al, target);
             dim3 grid(C, (unsigned)g.grid_y);
             SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_reduce_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
-                (const T*)dy, (const T*)x, outer, C, inner, g.n_per_cta, mean, invstd, weight, bias, acc,
+                (const T*)dy, (const T*)x, (const T*)y, outer, C, inner, g.n_per_cta, mean, invstd, weight, bias, acc,
                 counter, out_sums, grad_weight, grad_bias, flags)));
         }
     });
@@ -757,31 +780,37 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, 
     return SCB_OK;
 }
 
-extern "C" int scb_bn_backward_apply(const void* dy, const void* x, void* dx, int dtype,
+extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype,
                                      int channels_last, int64_t outer, int channels, int64_t inner,
                                      const float* mean, const float* invstd, const float* weight,
                                      const float* bias, const float* sums, const float* n_total,
                                      int flags, void* stream_) {
     if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
     SCB_REQUIRE(dy && dx && mean && invstd && sums && n_total, "bn_backward_apply: null pointer");
+    const int gate = gate_mode(flags);
+    SCB_REQUIRE(gate != 2 || y != nullptr, "bn_backward_apply: SCB_BN_RELU|SCB_BN_ADD needs the saved output y");
+    if (gate != 2) dz = nullptr;
     cudaStream_t stream = (cudaStream_t)stream_;
     const int C = channels;
     if (outer * inner == 0) return SCB_OK;
     const int target = 4 * sm_count();
-    const bool al = aligned16(x) && aligned16(dy) && aligned16(dx);
+    const bool al = aligned16(x) && aligned16(dy) && aligned16(dx) && (gate != 2 || aligned16(y)) &&
+                    (dz == nullptr || aligned16(dz));
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;
             NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, target);
             dim3 grid(g.grid_x, (unsigned)g.grid_y);
-            SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_apply_nhwc_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
-                (const T*)dy, (const T*)x, (T*)dx, M, C, g.tx, g.rows_per_cta, mean, invstd, weight, bias,
-                sums, n_total, flags)));
+            SCB_GATE_SWITCH(gate, GATE, {
+                SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_apply_nhwc_kernel<T, VEC, GATE><<<grid, kBnThreads, 0, stream>>>(
+                    (const T*)dy, (const T*)x, (const T*)y, (T*)dx, (T*)dz, M, C, g.tx, g.rows_per_cta, mean, invstd,
+                    weight, bias, sums, n_total)));
+            });
         } else {
             NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), al, target);
             dim3 grid(C, (unsigned)g.grid_y);
             SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_apply_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
-                (const T*)dy, (const T*)x, (T*)dx, outer, C, inner, g.n_per_cta, mean, invstd, weight,
+                (const T*)dy, (const T*)x, (const T*)y, (T*)dx, (T*)dz, outer, C, inner, g.n_per_cta, mean, invstd, weight,
                 bias, sums, n_total, flags)));
         }
     });
