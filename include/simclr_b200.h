@@ -53,7 +53,10 @@ extern "C" {
 #define SCB_ENGINE_BF16X3 2 /* same kernels, operands split hi+lo (3 MMAs): ~fp32-accurate      */
 
 /* flags of the batch-norm apply kernels */
-#define SCB_BN_RELU 1       /* y = max(y, 0) fused into the apply      */
+#define SCB_BN_RELU 1       /* y = max(y, 0) fused into the apply (resnet_big.py:26,58,59,111)   */
+#define SCB_BN_ADD 2        /* y = bn(x) + z: the residual add of resnet_big.py:27-30,60-63;
+                               with SCB_BN_RELU the ReLU comes after the add and the backward
+                               gates dy by the SAVED output (y > 0) and also returns dz          */
 
 const char* scb_last_error(void);
 int scb_version(void);
@@ -266,10 +269,12 @@ int scb_bn_stats_noalloc(const void* x, int dtype, int channels_last, int64_t ou
  * stats_all [n_ranks, 2C+1] (Chan, rank order, empty ranks skipped), updates running_mean /
  * running_var (momentum; unbiased global variance) when non-NULL, writes save_mean/save_invstd
  * [C], save_count[0] = global element count per channel (kept on the device so the backward
- * needs no host sync, cf. the count tensor of _functions.py:117) and y = (x - mean) * invstd * weight + bias (+ReLU with SCB_BN_RELU).
+ * needs no host sync, cf. the count tensor of _functions.py:117) and
+ *   y = (x - mean) * invstd * weight + bias  (+ z with SCB_BN_ADD)  (then ReLU with SCB_BN_RELU).
+ * z is the residual operand of resnet_big.py:27-30,60-63 (same shape and layout as x; NULL without SCB_BN_ADD).
  * With stats_all == NULL (eval mode, batchnorm.py:791-828) running_mean / running_var are used
  * as the statistics and are not modified.  weight/bias may be NULL (affine=False). */
-int scb_bn_apply(const void* x, void* y, int dtype, int channels_last, int64_t outer, int channels,
+int scb_bn_apply(const void* x, const void* z, void* y, int dtype, int channels_last, int64_t outer, int channels,
                  int64_t inner, const float* stats_all, int n_ranks,
                  const float* weight, const float* bias,
                  float* running_mean, float* running_var, float momentum, float eps,
@@ -278,8 +283,9 @@ int scb_bn_apply(const void* x, void* y, int dtype, int channels_last, int64_t o
 /* Replaces torch.batch_norm_backward_reduce (_functions.py:139-153):
  *   out_sums[0:C] = sum dy, out_sums[C:2C] = sum dy (x - mean)   (the 2C floats all-reduced),
  *   grad_weight = out_sums[C:2C] * invstd, grad_bias = out_sums[0:C]  (either may be NULL).
- * With SCB_BN_RELU, dy is first gated by (y > 0), y recomputed from x (weight/bias needed). */
-int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, int channels_last,
+ * With SCB_BN_RELU, dy is first gated by (y > 0): y recomputed from x (weight/bias needed), or, with
+ * SCB_BN_ADD as well, read from the saved output `y` (NULL otherwise). */
+int scb_bn_backward_reduce(const void* dy, const void* x, const void* y, int dtype, int channels_last,
                            int64_t outer, int channels, int64_t inner,
                            const float* mean, const float* invstd,
                            const float* weight, const float* bias,
@@ -288,48 +294,42 @@ int scb_bn_backward_reduce(const void* dy, const void* x, int dtype, int channel
 
 /* Replaces torch.batch_norm_backward_elemt (_functions.py:170-179):
  *   dx = (dy - sum_dy/n - (x - mean) invstd^2 sum_dy_xmu/n) * weight * invstd,
- * sums = the all-reduced [2C] vector, n_total[0] = global element count per channel (device). */
-int scb_bn_backward_apply(const void* dy, const void* x, void* dx, int dtype, int channels_last,
-                          int64_t outer, int channels, int64_t inner,
+ * sums = the all-reduced [2C] vector, n_total[0] = global element count per channel (device).
+ * dy is gated as in scb_bn_backward_reduce; with SCB_BN_RELU|SCB_BN_ADD the gated dy is also written to dz
+ * (gradient of the residual operand; may be NULL). */
+int scb_bn_backward_apply(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype,
+                          int channels_last, int64_t outer, int channels, int64_t inner,
                           const float* mean, const float* invstd,
                           const float* weight, const float* bias,
                           const float* sums, const float* n_total, int flags, void* stream);
 
-/* Single-launch variants for ONE rank (no exchange between statistics and normalisation): the same
- * arithmetic as scb_bn_stats + scb_bn_apply, resp. scb_bn_backward_reduce + scb_bn_backward_apply
- * (torch/nn/modules/_functions.py:39-122 and :139-179 at world size 1, i.e. the F.batch_norm fallback of
- * torch/nn/modules/batchnorm.py:818-828), with x (and dy) kept in registers across a grid-wide barrier
- * of a cooperative launch.  Channels-last [rows, channels] only, and only when the tensor fits one
- * resident wave: scb_bn_fused_supported() says so beforehand, otherwise they return SCB_ERR_UNSUPPORTED
- * and the caller runs the two-kernel path. */
-int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner);
-int scb_bn_forward_fused(const void* x, void* y, int dtype, int64_t rows, int channels,
+/* Single-launch variants (csrc/bn_cluster.cu): the same arithmetic as scb_bn_stats + scb_bn_apply, resp.
+ * scb_bn_backward_reduce + scb_bn_backward_apply (torch/nn/modules/_functions.py:39-122 and :139-179 at world
+ * size 1, i.e. the F.batch_norm fallback of torch/nn/modules/batchnorm.py:818-828) with x (and dy) read ONCE and
+ * kept in registers.  A thread-block cluster owns a slab of channels: per-channel partial sums meet over
+ * distributed shared memory and a cluster barrier -- no scratch, no global atomics, no grid-wide barrier, no
+ * assumption that the whole grid is resident.  Channels-last [rows, channels] only, and only when the tensor
+ * fits the register file of one resident wave: scb_bn_fused_supported(which = 0 forward / 1 backward, flags)
+ * says so beforehand, otherwise they return SCB_ERR_UNSUPPORTED and the caller runs the two-kernel path. */
+int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner, int which,
+                           int flags);
+int scb_bn_forward_fused(const void* x, const void* z, void* y, int dtype, int64_t rows, int channels,
                          const float* weight, const float* bias, float* running_mean, float* running_var,
                          float momentum, float eps, float* save_mean, float* save_invstd, float* save_count,
-                         int flags, void* workspace, int64_t workspace_bytes, void* stream);
-int scb_bn_backward_fused(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
-                          const float* mean, const float* invstd, const float* weight, const float* bias,
-                          const float* n_total, float* out_sums, float* grad_weight, float* grad_bias, int flags,
-                          void* workspace, int64_t workspace_bytes, void* stream);
-
-
-/* The fused kernels with a cross-GPU phase (world size > 1 on one NVLink/NVSwitch box): after the local grid
- * barrier one CTA stores this rank's per-channel message ([mean | M2 | count] forward, [sum dy | sum dy (x - mean)]
- * backward) into every rank's gathered buffer ch->dst[w] at slot `rank`, raises this rank's flag on every rank,
- * and all CTAs wait for the flags of all ranks before they read the gathered messages from `gathered_local`
- * (this rank's copy, = ch->dst[rank]).  Replaces the all_gather / all_reduce of torch/nn/modules/_functions.py
- * :41-56 and :155-165 without leaving the kernel.  `flags_local`: this rank's flag array (one word per rank);
- * channel conventions as for scb_peer_channel above.  Every rank must take this path for the same layer call. */
-int scb_bn_forward_fused_peers(const void* x, void* y, int dtype, int64_t rows, int channels,
-                               const float* weight, const float* bias, float* running_mean, float* running_var,
-                               float momentum, float eps, float* save_mean, float* save_invstd, float* save_count,
-                               int flags, void* workspace, int64_t workspace_bytes, const scb_peer_channel* ch,
-                               const float* gathered_local, const uint32_t* flags_local, int rank, void* stream);
-int scb_bn_backward_fused_peers(const void* dy, const void* x, void* dx, int dtype, int64_t rows, int channels,
-                                const float* mean, const float* invstd, const float* weight, const float* bias,
-                                const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
-                                int flags, void* workspace, int64_t workspace_bytes, const scb_peer_channel* ch,
-                                const float* gathered_local, const uint32_t* flags_local, int rank, void* stream);
+                         int flags, void* stream);
+int scb_bn_backward_fused(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t rows,
+                          int channels, const float* mean, const float* invstd, const float* weight,
+                          const float* bias, const float* n_total, float* out_sums, float* grad_weight,
+                          float* grad_bias, int flags, void* stream);
+/* The reductions alone through the same cluster scheme, for several ranks (the exchange of
+ * _functions.py:41-79 / :155-165 sits between them and scb_bn_apply / scb_bn_backward_apply):
+ * scb_bn_stats_fused writes the (2C+1)-float message of scb_bn_stats, scb_bn_backward_reduce_fused the
+ * outputs of scb_bn_backward_reduce; neither needs scratch. */
+int scb_bn_stats_fused(const void* x, int dtype, int64_t rows, int channels, float* out_stats, void* stream);
+int scb_bn_backward_reduce_fused(const void* dy, const void* x, const void* y, int dtype, int64_t rows, int channels,
+                                 const float* mean, const float* invstd, const float* weight, const float* bias,
+                                 const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
+                                 int flags, void* stream);
 
 #ifdef __cplusplus
 }

@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, 'csrc')
 ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(CSRC, 'libsimclr_b200.so')
-SOURCES = ['api.cu', 'bn.cu', 'supcon_generic.cu', 'supcon_tc.cu']
+SOURCES = ['api.cu', 'bn.cu', 'bn_cluster.cu', 'supcon_generic.cu', 'supcon_tc.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
 
@@ -28,6 +28,7 @@ MODE_ALL, MODE_ONE = 0, 1
 ENGINE_FP32, ENGINE_BF16, ENGINE_BF16X3 = 0, 1, 2
 ROWS_VIEW_MAJOR, ROWS_SAMPLE_MAJOR = 0, 1
 BN_RELU = 1
+BN_ADD = 2
 BN_NOALLOC_MAX_CHANNELS = 4096      # SCB_BN_NOALLOC_MAX_CHANNELS
 
 _lock = threading.Lock()
@@ -126,19 +127,19 @@ PROTOTYPES = {
     'scb_bn_workspace_bytes': (_i64, [_i]),
     'scb_bn_stats': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i64, _vp]),
     'scb_bn_stats_noalloc': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp]),
-    'scb_bn_apply': (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _i, _vp, _vp, _vp, _vp, _f, _f,
+    'scb_bn_apply': (_i, [_vp, _vp, _vp, _i, _i, _i64, _i, _i64, _vp, _i, _vp, _vp, _vp, _vp, _f, _f,
                           _vp, _vp, _vp, _i, _vp]),
-    'scb_bn_backward_reduce': (_i, [_vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp,
+    'scb_bn_backward_reduce': (_i, [_vp, _vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp,
                                     _vp, _i, _vp, _i64, _vp]),
-    'scb_bn_fused_supported': (_i, [_i, _i, _i64, _i, _i64]),
-    'scb_bn_forward_fused': (_i, [_vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _i, _vp, _i64, _vp]),
-    'scb_bn_backward_fused': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp,
-                                   _i64, _vp]),
-    'scb_bn_forward_fused_peers': (_i, [_vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _i, _vp, _i64, _vp, _vp, _vp, _i, _vp]),
-    'scb_bn_backward_fused_peers': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp,
-                                   _i64, _vp, _vp, _vp, _i, _vp]),
-    'scb_bn_backward_apply': (_i, [_vp, _vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _vp, _vp, _vp,
+    'scb_bn_backward_apply': (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _i, _vp]),
+    'scb_bn_fused_supported': (_i, [_i, _i, _i64, _i, _i64, _i, _i]),
+    'scb_bn_forward_fused': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _i, _vp]),
+    'scb_bn_backward_fused': (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                   _i, _vp]),
+    'scb_bn_stats_fused': (_i, [_vp, _i, _i64, _i, _vp, _vp]),
+    'scb_bn_backward_reduce_fused': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i,
+                                          _vp]),
 }
 
 
