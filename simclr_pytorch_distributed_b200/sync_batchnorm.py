@@ -41,9 +41,23 @@ class _Kernels:
         return torch.cuda.current_stream(device).cuda_stream
 
     @classmethod
+    def fused_supported(cls, x, geom, which, flags=0):
+        """True when this tensor fits the single-launch cluster kernels (which: 0 forward, 1 backward)."""
+        import os
+        if os.environ.get('SCB_BN_FUSED', '1') == '0':          # tests / measurements: force the multi-kernel path
+            return False
+        lib = _lib.load()
+        cl, outer, C, inner = geom
+        return bool(lib.scb_bn_fused_supported(_lib.dtype_code(x.dtype), cl, outer, C, inner, which, flags))
+
+    @classmethod
     def stats(cls, x, geom, out_stats):
         lib = _lib.load()
         cl, outer, C, inner = geom
+        if cls.fused_supported(x, geom, 0) and x.data_ptr() % 16 == 0:      # cluster reduction, no scratch
+            _lib.check(lib.scb_bn_stats_fused(x.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
+                                              out_stats.data_ptr(), cls.stream(x.device)), 'scb_bn_stats_fused')
+            return
         ws = cls.workspace(lib, x.device, C)
         _lib.check(lib.scb_bn_stats(x.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C, inner,
                                     out_stats.data_ptr(), ws.data_ptr(), ws.numel(),
@@ -51,84 +65,66 @@ class _Kernels:
 
     @classmethod
     def apply(cls, x, y, geom, stats_all, n_ranks, weight, bias, running_mean, running_var,
-              momentum, eps, saved, flags):
+              momentum, eps, saved, flags, z=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
         sm = saved[0:C] if saved is not None else None
         si = saved[C:2 * C] if saved is not None else None
         sc = saved[2 * C:] if saved is not None else None
-        _lib.check(lib.scb_bn_apply(x.data_ptr(), y.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C,
+        _lib.check(lib.scb_bn_apply(x.data_ptr(), p(z), y.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C,
                                     inner, p(stats_all), n_ranks, p(weight), p(bias), p(running_mean),
                                     p(running_var), momentum, eps, p(sm), p(si), p(sc), flags,
                                     cls.stream(x.device)), 'scb_bn_apply')
 
     @classmethod
-    def backward_reduce(cls, dy, x, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags):
+    def backward_reduce(cls, dy, x, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags, yout=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        if (cls.fused_supported(x, geom, 1, flags) and x.data_ptr() % 16 == 0 and dy.data_ptr() % 16 == 0 and
+                (yout is None or yout.data_ptr() % 16 == 0)):
+            _lib.check(lib.scb_bn_backward_reduce_fused(
+                dy.data_ptr(), x.data_ptr(), p(yout), _lib.dtype_code(x.dtype), outer * inner, C,
+                saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), saved[2 * C:].data_ptr(),
+                sums.data_ptr(), p(grad_weight), p(grad_bias), flags, cls.stream(x.device)),
+                'scb_bn_backward_reduce_fused')
+            return
         ws = cls.workspace(lib, x.device, C)
         _lib.check(lib.scb_bn_backward_reduce(
-            dy.data_ptr(), x.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C, inner,
+            dy.data_ptr(), x.data_ptr(), p(yout), _lib.dtype_code(x.dtype), cl, outer, C, inner,
             saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), sums.data_ptr(),
             p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(), cls.stream(x.device)),
             'scb_bn_backward_reduce')
 
     @classmethod
-    def fused_supported(cls, x, geom):
-        """True when statistics + normalisation of this tensor fit the single-launch kernels."""
-        lib = _lib.load()
-        cl, outer, C, inner = geom
-        return bool(lib.scb_bn_fused_supported(_lib.dtype_code(x.dtype), cl, outer, C, inner))
-
-    @classmethod
-    def forward_fused(cls, x, y, geom, weight, bias, running_mean, running_var, momentum, eps, saved, flags,
-                      peer=None):
+    def forward_fused(cls, x, y, geom, weight, bias, running_mean, running_var, momentum, eps, saved, flags, z=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
-        ws = cls.workspace(lib, x.device, C)
-        if peer is not None:       # (channel struct, gathered_local ptr, flags_local ptr, rank)
-            import ctypes
-            return lib.scb_bn_forward_fused_peers(
-                x.data_ptr(), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
-                p(weight), p(bias), p(running_mean), p(running_var), momentum, eps,
-                saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), saved[2 * C:].data_ptr(),
-                flags, ws.data_ptr(), ws.numel(), ctypes.byref(peer[0]), peer[1], peer[2], peer[3],
-                cls.stream(x.device))
-        return lib.scb_bn_forward_fused(x.data_ptr(), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
+        return lib.scb_bn_forward_fused(x.data_ptr(), p(z), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
                                         p(weight), p(bias), p(running_mean), p(running_var), momentum, eps,
                                         saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), saved[2 * C:].data_ptr(),
-                                        flags, ws.data_ptr(), ws.numel(), cls.stream(x.device))
+                                        flags, cls.stream(x.device))
 
     @classmethod
-    def backward_fused(cls, dy, x, dx, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags, peer=None):
+    def backward_fused(cls, dy, x, dx, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags,
+                       yout=None, dz=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
-        ws = cls.workspace(lib, x.device, C)
-        if peer is not None:
-            import ctypes
-            return lib.scb_bn_backward_fused_peers(
-                dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _lib.dtype_code(x.dtype),
-                outer * inner, C, saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(),
-                p(weight), p(bias), saved[2 * C:].data_ptr(), sums.data_ptr(),
-                p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(),
-                ctypes.byref(peer[0]), peer[1], peer[2], peer[3], cls.stream(x.device))
-        return lib.scb_bn_backward_fused(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _lib.dtype_code(x.dtype),
-                                         outer * inner, C, saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(),
-                                         p(weight), p(bias), saved[2 * C:].data_ptr(), sums.data_ptr(),
-                                         p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(),
-                                         cls.stream(x.device))
+        return lib.scb_bn_backward_fused(dy.data_ptr(), x.data_ptr(), p(yout), dx.data_ptr(), p(dz),
+                                         _lib.dtype_code(x.dtype), outer * inner, C, saved[0:C].data_ptr(),
+                                         saved[C:2 * C].data_ptr(), p(weight), p(bias), saved[2 * C:].data_ptr(),
+                                         sums.data_ptr(), p(grad_weight), p(grad_bias), flags, cls.stream(x.device))
 
     @classmethod
-    def backward_apply(cls, dy, x, dx, geom, saved, weight, bias, sums, flags):
+    def backward_apply(cls, dy, x, dx, geom, saved, weight, bias, sums, flags, yout=None, dz=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
         _lib.check(lib.scb_bn_backward_apply(
-            dy.data_ptr(), x.data_ptr(), dx.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C, inner,
+            dy.data_ptr(), x.data_ptr(), p(yout), dx.data_ptr(), p(dz), _lib.dtype_code(x.dtype), cl, outer, C, inner,
             saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), sums.data_ptr(),
             saved[2 * C:].data_ptr(), flags, cls.stream(x.device)), 'scb_bn_backward_apply')
 
