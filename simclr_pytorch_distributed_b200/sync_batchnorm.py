@@ -5,12 +5,14 @@
 Same constructor, parameters, buffers and state-dict keys as `torch.nn.SyncBatchNorm`
 (torch/nn/modules/batchnorm.py:718-733) and the same `convert_sync_batchnorm` classmethod
 (:844-905); the arithmetic (torch/nn/modules/_functions.py:10-209) runs in the sm_100a kernels of
-csrc/bn.cu through the C ABI.  Per layer and pass: one streaming reduction, one tiny NCCL
+csrc/bn.cu and csrc/bn_cluster.cu through the C ABI.  Per layer and pass: one launch on one rank when the
+tensor fits the registers of a resident wave, else one streaming reduction, one tiny peer-memory
 exchange (only when world_size > 1) and one fused apply -- and no host synchronisation (stock
 SyncBatchNorm forces one per layer, _functions.py:88-100).
 
 CUDA tensors only; there is no CPU path.  `fuse_relu=True` additionally applies ReLU inside the
-apply kernels (the `relu(bn(x))` sites of resnet_big.py:26,58,59,111).
+apply kernels (the `relu(bn(x))` sites of resnet_big.py:26,58,59,111), and
+`forward(x, z)` adds the residual operand of resnet_big.py:27-30,60-63 before that ReLU.
 """
 from __future__ import annotations
 
@@ -168,7 +170,10 @@ class _PeerStats:
     buffers (torch.distributed._symmetric_memory, plumbing only); `scb_peer_bcast` stores the rank's message
     into every rank's copy and the handle's stream barrier orders it against the readers.  Buffers are shared
     by all layers with the same message length and rotate through GENERATIONS copies (a rank is never more
-    than one exchange ahead of its slowest peer).  SCB_P2P=0 or any set-up failure -> NCCL."""
+    than one exchange ahead of its slowest peer).  SCB_P2P=0 or any set-up failure -> NCCL.
+
+    The kernels of this library never wait on another GPU: the cross-rank wait is the stream barrier between two
+    launches, so a concurrent NCCL kernel (DDP's bucket all-reduce) can neither starve nor be starved by them."""
     GENERATIONS = 4
     _cache = {}
     _failed = False
@@ -186,25 +191,7 @@ class _PeerStats:
             self.ptrs.append((ctypes.c_void_p * world)(*[int(p) for p in h.buffer_ptrs]))
         self.seg = (ctypes.c_int64 * 3)(0, rank * n * 4, n * 4)
         self.calls = 0
-        # in-kernel exchange of the fused kernels: flag words (one per rank) in symmetric memory, local counter
         self.rank = rank
-        fl = symm.empty((16,), dtype=torch.int32, device=dev)
-        fl.zero_()
-        fh = symm.rendezvous(fl, group)
-        torch.cuda.synchronize(dev)
-        fh.barrier(channel=0)                 # nobody raises a flag before everybody has cleared its own
-        torch.cuda.synchronize(dev)
-        self.flags, self.flags_handle = fl, fh
-        self.state = torch.zeros(2, dtype=torch.int32, device=dev)
-        self.channels = []
-        for g in range(self.GENERATIONS):
-            ch = _lib.PeerChannel()
-            for w in range(world):
-                ch.dst[w] = int(self.handles[g].buffer_ptrs[w])
-                ch.flag[w] = int(fh.buffer_ptrs[w]) + rank * 4
-            ch.state = self.state.data_ptr()
-            ch.n_dst = world
-            self.channels.append(ch)
 
     @classmethod
     def get(cls, group, dev, n, world, rank):
@@ -224,12 +211,6 @@ class _PeerStats:
                 return None
         return cls._cache[key]
 
-    def fused_peer(self):
-        """Arguments of the next in-kernel exchange: (channel, gathered_local ptr, flags_local ptr, rank)."""
-        g = self.calls % self.GENERATIONS
-        self.calls += 1
-        return (self.channels[g], self.bufs[g].data_ptr(), self.flags.data_ptr(), self.rank)
-
     def all_gather(self, src, dev):
         """src: n floats of this rank -> [world * n] floats, rank-major (valid until GENERATIONS-1 further calls)."""
         lib = _lib.load()
@@ -241,13 +222,32 @@ class _PeerStats:
         return self.bufs[g]
 
 
+def _exchange(kern, vec, n, process_group, world_size, dev):
+    """All-gather of one per-rank message of n floats -> [world_size * n] floats, rank-major."""
+    px = (_PeerStats.get(process_group, dev, n, world_size, dist.get_rank(process_group))
+          if kern is _Kernels else None)
+    if px is not None:
+        return px.all_gather(vec, dev)
+    out = torch.empty(world_size * n, dtype=torch.float32, device=dev)
+    if process_group._get_backend_name() != 'gloo':
+        dist.all_gather_into_tensor(out, vec, process_group, async_op=False)
+    else:                                            # gloo has no all_gather_into_tensor
+        parts = [torch.empty_like(vec) for _ in range(world_size)]
+        dist.all_gather(parts, vec, process_group, async_op=False)
+        out = torch.cat(parts)
+    return out
+
+
 class _SyncBNFunction(torch.autograd.Function):
-    """Training-mode forward/backward: _functions.py:10-209 on the sm_100a kernels."""
+    """Training-mode forward/backward: _functions.py:10-209 on the sm_100a kernels.
+
+    `z` (optional) is a residual operand added after the normalisation and before the fused ReLU
+    (resnet_big.py:27-30,60-63): y = relu(bn(x) + z)."""
 
     kernels = _Kernels      # tests swap this for an oracle-backed stand-in to check the host logic
 
     @staticmethod
-    def forward(ctx, input, weight, bias, running_mean, running_var, eps, momentum, process_group,
+    def forward(ctx, input, z, weight, bias, running_mean, running_var, eps, momentum, process_group,
                 world_size, fuse_relu, use_batch_stats):
         kern = _SyncBNFunction.kernels
         x, geom = _layout(input)
@@ -258,75 +258,45 @@ class _SyncBNFunction(torch.autograd.Function):
         w32, b32 = _f32(weight), _f32(bias)
         rm, rv = _f32(running_mean), _f32(running_var)
         dev = x.device
-        flags = _lib.BN_RELU if fuse_relu else 0
-        fused = (use_batch_stats and hasattr(kern, 'fused_supported') and kern.fused_supported(x, geom))
-        px = None
-        if fused and world_size > 1:
-            # several ranks: the fused kernel exchanges the statistics itself over peer memory.  Needs every
-            # rank to take this path (same per-rank shape); SCB_BN_FUSED_PEERS=0 keeps the four-kernel path.
-            # Measured (fwd+bwd of cfg 2): 44.7 / 52.9 / 70.2 us at 2 / 4 / 8 GPUs against 56.9 / 57.9 / 63.7 us for
-            # the four-kernel path -- every CTA waits on every rank's flag, so the in-kernel exchange is the
-            # default up to 4 ranks only (SCB_BN_FUSED_PEERS=1 forces it, =0 disables it).
-            import os
-            want = os.environ.get('SCB_BN_FUSED_PEERS', 'auto')
-            use = want == '1' or (want != '0' and world_size <= 4)
-            px = (_PeerStats.get(process_group, dev, 2 * C + 1, world_size, dist.get_rank(process_group))
-                  if kern is _Kernels and use else None)
-            fused = px is not None
-        ctx.fused = False
-        if fused:
-            # tensor fits one resident wave: statistics (+ exchange) + normalisation in a single launch
-            y = torch.empty_like(x)
-            saved = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
-            if px is not None:
-                rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags,
-                                        peer=px.fused_peer())
-            else:
-                rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags)
-            if rc == 0:
-                if rm is not running_mean and running_mean is not None:
-                    running_mean.copy_(rm)
-                if rv is not running_var and running_var is not None:
-                    running_var.copy_(rv)
-                ctx.save_for_backward(x, w32, b32, saved)
-                ctx.geom, ctx.flags, ctx.use_batch_stats, ctx.fused = geom, flags, use_batch_stats, True
-                ctx.process_group, ctx.world_size = process_group, world_size
-                ctx.param_dtypes = (None if weight is None else weight.dtype, None if bias is None else bias.dtype)
-                return y
-            if rc != -3:
-                _lib.check(rc, 'scb_bn_forward_fused')
-        if not use_batch_stats:
-            stats_all = None            # eval: the running statistics are the statistics
-        else:
-            # message of this rank: [mean(C), M2(C), count]  (_functions.py:41-49 sends mean, invstd, count)
-            stats = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
-            kern.stats(x, geom, stats)
-        if not use_batch_stats:
-            pass
-        elif world_size > 1 and kern is _Kernels and _PeerStats.get(process_group, dev, 2 * C + 1, world_size,
-                                                                    dist.get_rank(process_group)) is not None:
-            px = _PeerStats.get(process_group, dev, 2 * C + 1, world_size, dist.get_rank(process_group))
-            stats_all = px.all_gather(stats, dev)
-        elif world_size > 1:
-            stats_all = torch.empty(world_size * (2 * C + 1), dtype=torch.float32, device=dev)
-            if process_group._get_backend_name() != 'gloo':
-                dist.all_gather_into_tensor(stats_all, stats, process_group, async_op=False)
-            else:                                            # gloo has no all_gather_into_tensor
-                parts = [torch.empty_like(stats) for _ in range(world_size)]
-                dist.all_gather(parts, stats, process_group, async_op=False)
-                stats_all = torch.cat(parts)
-        else:
-            stats_all = stats
+        flags = (_lib.BN_RELU if fuse_relu else 0) | (_lib.BN_ADD if z is not None else 0)
+        if z is not None:
+            if z.shape != input.shape:
+                raise ValueError('the residual operand must have the shape of the input')
+            z = _match_layout(z, x, geom)
+            if z.dtype != x.dtype:
+                z = z.to(x.dtype)
         y = torch.empty_like(x)
         saved = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)     # mean, invstd, n_total
-        flags = _lib.BN_RELU if fuse_relu else 0
-        kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags)
+        done = False
+        if (use_batch_stats and world_size == 1 and hasattr(kern, 'forward_fused') and
+                kern.fused_supported(x, geom, 0, flags)):
+            # one rank, tensor fits one resident wave: statistics + normalisation in a single launch
+            rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags, z=z)
+            if rc == 0:
+                done = True
+            elif rc != -3:
+                _lib.check(rc, 'scb_bn_forward_fused')
+        if not done:
+            if not use_batch_stats:
+                stats_all = None            # eval: the running statistics are the statistics
+            else:
+                # message of this rank: [mean(C), M2(C), count]  (_functions.py:41-49 sends mean, invstd, count)
+                stats_all = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
+                kern.stats(x, geom, stats_all)
+                if world_size > 1:
+                    stats_all = _exchange(kern, stats_all, 2 * C + 1, process_group, world_size, dev)
+            if z is not None:
+                kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags, z=z)
+            else:
+                kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags)
         if rm is not running_mean and running_mean is not None:
             running_mean.copy_(rm)
         if rv is not running_var and running_var is not None:
             running_var.copy_(rv)
-        ctx.save_for_backward(x, w32, b32, saved)
+        gate_by_y = fuse_relu and z is not None
+        ctx.save_for_backward(x, w32, b32, saved, y if gate_by_y else None)
         ctx.geom, ctx.flags, ctx.use_batch_stats = geom, flags, use_batch_stats
+        ctx.has_z = z is not None
         ctx.process_group, ctx.world_size = process_group, world_size
         ctx.param_dtypes = (None if weight is None else weight.dtype, None if bias is None else bias.dtype)
         return y
@@ -334,7 +304,7 @@ class _SyncBNFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_output):
         kern = _SyncBNFunction.kernels
-        x, w32, b32, saved = ctx.saved_tensors
+        x, w32, b32, saved, yout = ctx.saved_tensors
         geom, flags = ctx.geom, ctx.flags
         C = geom[2]
         dy = _match_layout(grad_output, x, geom)
@@ -343,41 +313,45 @@ class _SyncBNFunction(torch.autograd.Function):
         dev = x.device
         out = torch.empty(4 * C, dtype=torch.float32, device=dev)           # sums(2C), dgamma, dbeta
         sums, gw, gb = out[0:2 * C], out[2 * C:3 * C], out[3 * C:]
-        grad_input = None
+        need_dx = ctx.needs_input_grad[0]
+        need_dz = ctx.has_z and ctx.needs_input_grad[1]
+        gated = yout is not None                                             # ReLU after the residual add
+        grad_input = torch.empty_like(x) if need_dx else None
+        grad_z = torch.empty_like(x) if (need_dz and gated) else None
+        kw = {}
+        if gated:
+            kw['yout'] = yout
         done = False
-        px = None
-        if ctx.fused and ctx.world_size > 1:
-            px = _PeerStats.get(ctx.process_group, dev, 2 * C, ctx.world_size, dist.get_rank(ctx.process_group))
-        if ctx.fused and ctx.needs_input_grad[0] and (ctx.world_size == 1 or px is not None):
-            grad_input = torch.empty_like(x)
-            if px is not None:
-                rc = kern.backward_fused(dy, x, grad_input, geom, saved, w32, b32, sums, gw, gb, flags,
-                                         peer=px.fused_peer())
-            else:
-                rc = kern.backward_fused(dy, x, grad_input, geom, saved, w32, b32, sums, gw, gb, flags)
+        if (need_dx and ctx.use_batch_stats and ctx.world_size == 1 and hasattr(kern, 'backward_fused') and
+                kern.fused_supported(x, geom, 1, flags)):
+            rc = kern.backward_fused(dy, x, grad_input, geom, saved, w32, b32, sums, gw, gb, flags, yout=yout,
+                                     dz=grad_z)
             if rc == 0:
                 done = True
             elif rc != -3:
                 _lib.check(rc, 'scb_bn_backward_fused')
         if not done:
-            kern.backward_reduce(dy, x, geom, saved, w32, b32, sums, gw, gb, flags)
-        if not done and ctx.needs_input_grad[0]:
-            if not ctx.use_batch_stats:
-                sums = torch.zeros_like(sums)               # eval: statistics do not depend on x
-            elif ctx.world_size > 1:                        # _functions.py:155-165
-                px = (_PeerStats.get(ctx.process_group, dev, 2 * C, ctx.world_size, dist.get_rank(ctx.process_group))
-                      if kern is _Kernels else None)
-                if px is not None:                          # all-reduce = peer all-gather + a local sum
-                    sums = px.all_gather(sums, dev).view(ctx.world_size, 2 * C).sum(0)
-                else:
-                    dist.all_reduce(sums, dist.ReduceOp.SUM, ctx.process_group, async_op=False)
-            grad_input = torch.empty_like(x)
-            kern.backward_apply(dy, x, grad_input, geom, saved, w32, b32, sums, flags)
+            kern.backward_reduce(dy, x, geom, saved, w32, b32, sums, gw, gb, flags, **kw)
+            if need_dx or grad_z is not None:
+                if not ctx.use_batch_stats:
+                    sums = torch.zeros_like(sums)               # eval: statistics do not depend on x
+                elif ctx.world_size > 1:                        # _functions.py:155-165: all-reduce = all-gather + sum
+                    sums = _exchange(kern, sums, 2 * C, ctx.process_group, ctx.world_size, dev) \
+                        .view(ctx.world_size, 2 * C).sum(0)
+                if grad_input is None:
+                    grad_input = torch.empty_like(x)
+                if gated:
+                    kw['dz'] = grad_z
+                kern.backward_apply(dy, x, grad_input, geom, saved, w32, b32, sums, flags, **kw)
+        if need_dz and not gated:
+            grad_z = dy                                          # plain add: the gradient passes through
+        if not need_dx:
+            grad_input = None
         wd, bd = ctx.param_dtypes
         # dgamma / dbeta stay un-synced: DDP averages them (_functions.py:180-181)
-        grad_weight = gw.to(wd) if (w32 is not None and ctx.needs_input_grad[1]) else None
-        grad_bias = gb.to(bd) if (b32 is not None and ctx.needs_input_grad[2]) else None
-        return grad_input, grad_weight, grad_bias, None, None, None, None, None, None, None, None
+        grad_weight = gw.to(wd) if (w32 is not None and ctx.needs_input_grad[2]) else None
+        grad_bias = gb.to(bd) if (b32 is not None and ctx.needs_input_grad[3]) else None
+        return grad_input, grad_z, grad_weight, grad_bias, None, None, None, None, None, None, None, None
 
 
 class SyncBatchNorm(_BatchNorm):
@@ -403,7 +377,9 @@ class SyncBatchNorm(_BatchNorm):
         if input.size(1) == 0:
             raise ValueError("SyncBatchNorm number of input channels should be non-zero")
 
-    def forward(self, input):
+    def forward(self, input, z=None):
+        """`z`: optional residual operand, y = bn(input) + z (then ReLU with fuse_relu=True): the tail of a
+        residual block, resnet_big.py:27-30,60-63, in one pass."""
         self._check_input_dim(input)
         self._check_non_zero_input_channels(input)
         if input.size(1) != self.num_features:
@@ -435,7 +411,7 @@ class SyncBatchNorm(_BatchNorm):
         if bn_training and self.training and dist.is_available() and dist.is_initialized():
             process_group = self.process_group if self.process_group else dist.group.WORLD
             world_size = dist.get_world_size(process_group)
-        return _SyncBNFunction.apply(input, self.weight, self.bias, running_mean, running_var, self.eps,
+        return _SyncBNFunction.apply(input, z, self.weight, self.bias, running_mean, running_var, self.eps,
                                      float(exponential_average_factor), process_group, world_size,
                                      self.fuse_relu, bn_training)
 

@@ -264,7 +264,7 @@ def _bn_worker(rank, world, port, fixture, q):
         b = torch.from_numpy(g['bias']).float().requires_grad_(True)
         rm = torch.from_numpy(g['running_mean0']).float()
         rv = torch.from_numpy(g['running_var0']).float()
-        y = _SyncBNFunction.apply(x, w, b, rm, rv, float(g['eps']), float(g['momentum']), dist.group.WORLD,
+        y = _SyncBNFunction.apply(x, None, w, b, rm, rv, float(g['eps']), float(g['momentum']), dist.group.WORLD,
                                   world, False, True)
         y.backward(dy)
         tol = 2e-5

@@ -140,59 +140,3 @@ def test_both_row_layouts_give_the_reference_result(labels):
         assert abs(loss_v - ref_loss) <= 2e-3 * abs(ref_loss)
         assert np.linalg.norm((grad - ref_grad).ravel()) <= tol * np.linalg.norm(ref_grad.ravel())
     assert abs(results[0][0] - results[1][0]) <= 1e-5 * abs(ref_loss)
-
-
-def test_fused_batchnorm_with_in_kernel_exchange_and_a_local_peer():
-    """scb_bn_forward_fused_peers / scb_bn_backward_fused_peers with W = 1 (the rank is its own peer): same
-    results as the single-rank fused kernels, flags and counter advance by one per call."""
-    from simclr_pytorch_distributed_b200.sync_batchnorm import _Kernels, _layout
-    lib = _lib.load()
-    dev = torch.device('cuda')
-    torch.manual_seed(3)
-    C = 128
-    x = (torch.randn(64, C, 8, 8, device=dev) * 1.7 + 0.4).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-    dy = torch.randn(64, C, 8, 8, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-    xl, geom = _layout(x)
-    dyl, _ = _layout(dy)
-    assert _Kernels.fused_supported(xl, geom)
-    w = torch.rand(C, device=dev) + 0.5
-    b = torch.randn(C, device=dev) * 0.1
-
-    def run(peer_f, peer_b):
-        rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
-        y = torch.empty_like(xl)
-        saved = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
-        rc = _Kernels.forward_fused(xl, y, geom, w, b, rm, rv, 0.1, 1e-5, saved, 0, **({'peer': peer_f} if peer_f else {}))
-        assert rc == 0, lib.scb_last_error()
-        dx = torch.empty_like(xl)
-        out = torch.empty(4 * C, dtype=torch.float32, device=dev)
-        rc = _Kernels.backward_fused(dyl, xl, dx, geom, saved, w, b, out[0:2 * C], out[2 * C:3 * C], out[3 * C:], 0,
-                                     **({'peer': peer_b} if peer_b else {}))
-        assert rc == 0, lib.scb_last_error()
-        torch.cuda.synchronize()
-        return y, dx, saved, rm, rv, out
-
-    ref = run(None, None)
-    flags = torch.zeros(32, dtype=torch.int32, device=dev)
-    state = torch.zeros(4, dtype=torch.int32, device=dev)
-    gath_f = torch.zeros(2 * C + 1, dtype=torch.float32, device=dev)
-    gath_b = torch.zeros(2 * C, dtype=torch.float32, device=dev)
-    peers = []
-    for c, buf in ((0, gath_f), (1, gath_b)):
-        ch = _lib.PeerChannel()
-        ch.dst[0] = buf.data_ptr()
-        ch.flag[0] = flags.data_ptr() + c * 64
-        ch.state = state.data_ptr() + c * 8
-        ch.n_dst = 1
-        peers.append((ch, buf.data_ptr(), flags.data_ptr() + c * 64, 0))
-    for it in range(2):
-        got = run(peers[0], peers[1])
-        for a, r in zip(got, ref):
-            # the W-rank path merges (mean, M2, n) messages instead of using the shifted sums directly: fp32
-            # quantities agree to rounding, bf16 tensors to one bf16 ulp
-            # (sums are accumulated with float atomics: their order, hence the last bits, changes from run to run)
-            tol = 2.0 ** -7 if a.dtype == torch.bfloat16 else 1e-4
-            assert torch.allclose(a.float(), r.float(), rtol=tol, atol=tol)
-        assert state.tolist() == [0, it + 1, 0, it + 1] and int(flags[0]) == it + 1 and int(flags[16]) == it + 1
-    assert torch.allclose(gath_f[0:C], ref[2][0:C], rtol=1e-6, atol=1e-6)        # the message: this rank's mean
-    assert float(gath_f[2 * C]) == float(64 * 8 * 8)
