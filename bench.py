@@ -355,7 +355,7 @@ def bn_kernel_breakdown(steps, pool=8):
     saved = torch.empty(2 * C + 1, device=dev)
     out = torch.empty(4 * C, device=dev)
     _, geom = _layout(xs[0])
-    fused = K.fused_supported(xs[0], geom)
+    fused = K.fused_supported(xs[0], geom, 1)
     names = ['forward_fused', 'backward_fused'] if fused else ['stats', 'apply', 'backward_reduce', 'backward_apply']
     tot = [0.0] * len(names)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]

@@ -1,0 +1,119 @@
+"""Parity cases the north_star names explicitly: BASELINE configs[4] at full size (SupCon with labels, batch 1024,
+100 classes, T = 0.07, contrast_mode all vs one, /root/reference/losses.py:44-48,54-59,87) and the bf16 engine held
+to a FLAT 2e-3 with fp32 features in and out (no allowance for a bf16 output).  The oracle is fed the embeddings the
+engine actually multiplies (fp32 features rounded to bf16 once)."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import supcon_forward_backward, normalize_rows, normalize_rows_backward
+from simclr_pytorch_distributed_b200 import SupConLoss
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_f(a, b):
+    return np.linalg.norm((a - b).ravel()) / np.linalg.norm(b.ravel())
+
+
+def run(z, labels, engine, **kw):
+    f = torch.from_numpy(z).cuda().requires_grad_(True)
+    lab = None if labels is None else torch.from_numpy(labels).cuda()
+    loss = SupConLoss(engine=engine, **kw)(f, labels=lab)
+    loss.backward()
+    torch.cuda.synchronize()
+    return float(loss), f.grad.cpu().numpy().astype(np.float64)
+
+
+def unit_rows(rng, B, V, D, common=0.5):
+    z = rng.standard_normal((B, V, D)) + common * rng.standard_normal((1, 1, D))
+    return (z / np.linalg.norm(z, axis=-1, keepdims=True)).astype(np.float32)
+
+
+@pytest.mark.parametrize('engine', ['fp32', 'bf16'])
+@pytest.mark.parametrize('mode', ['all', 'one'])
+def test_cfg5_full_size_labels(mode, engine):
+    """B = 1024, V = 2, D = 128, 100 classes, T = base_T = 0.07."""
+    rng = np.random.default_rng(2024)
+    z = unit_rows(rng, 1024, 2, 128)
+    labels = rng.integers(0, 100, size=1024)
+    kw = dict(temperature=0.07, base_temperature=0.07, contrast_mode=mode)
+    loss, grad = run(z, labels, engine, **kw)
+    used = z if engine == 'fp32' else torch.from_numpy(z).to(torch.bfloat16).float().numpy()
+    ref_loss, ref_grad, _ = supcon_forward_backward(used.astype(np.float64), labels, None, **kw)
+    tol = 1e-4 if engine == 'fp32' else 2e-3
+    assert abs(loss - ref_loss) <= tol * abs(ref_loss), (loss, ref_loss)
+    assert rel_f(grad, ref_grad.reshape(grad.shape)) <= tol, rel_f(grad, ref_grad.reshape(grad.shape))
+
+
+CASES = [('simclr', 'all', 0.5), ('simclr', 'one', 0.5), ('labels', 'all', 0.1), ('labels', 'one', 0.1)]
+
+
+@pytest.mark.parametrize('kind,mode,T', CASES)
+@pytest.mark.parametrize('shape', [(512, 2, 128), (300, 2, 64), (130, 3, 128)])
+def test_bf16_engine_flat_2e3_with_fp32_io(shape, kind, mode, T):
+    B, V, D = shape
+    rng = np.random.default_rng(B + V + D)
+    z = unit_rows(rng, B, V, D)
+    labels = rng.integers(0, max(2, B // 8), size=B) if kind == 'labels' else None
+    kw = dict(temperature=T, contrast_mode=mode)
+    loss, grad = run(z, labels, 'bf16', **kw)
+    used = torch.from_numpy(z).to(torch.bfloat16).double().numpy()
+    ref_loss, ref_grad, _ = supcon_forward_backward(used, labels, None, **kw)
+    assert abs(loss - ref_loss) <= 2e-3 * abs(ref_loss), (loss, ref_loss)
+    r = rel_f(grad, ref_grad.reshape(grad.shape))
+    assert r <= 2e-3, r
+
+
+def test_bf16_engine_flat_2e3_fused_normalize():
+    rng = np.random.default_rng(77)
+    raw = (rng.standard_normal((512, 2, 128)) * 3.0).astype(np.float32)
+    f = torch.from_numpy(raw).cuda().requires_grad_(True)
+    loss = SupConLoss(temperature=0.5, engine='bf16', normalize=True)(f)
+    loss.backward()
+    # the engine multiplies the normalised rows rounded to bf16: the oracle gets exactly those, and the
+    # normalisation backward is taken around the un-rounded rows (what the kernel does)
+    zh = normalize_rows(raw)
+    used = torch.from_numpy(zh).to(torch.bfloat16).double().numpy()
+    ref_loss, g_hat, _ = supcon_forward_backward(used, temperature=0.5)
+    ref_grad = normalize_rows_backward(raw, g_hat)
+    assert abs(float(loss) - ref_loss) <= 2e-3 * abs(ref_loss)
+    r = rel_f(f.grad.cpu().numpy().astype(np.float64), ref_grad.reshape(raw.shape))
+    assert r <= 2e-3, r
+
+
+def test_float_labels_are_not_truncated():
+    """losses.py:48 compares the raw labels: 1.2 and 1.7 are different classes."""
+    rng = np.random.default_rng(5)
+    z = unit_rows(rng, 64, 2, 32)
+    lab_f = np.tile(np.array([1.2, 1.7, 2.0, -0.0]), 16)
+    lab_i = np.tile(np.array([0, 1, 2, 3]), 16)
+    f = torch.from_numpy(z).cuda()
+    a = SupConLoss(engine='fp32')(f, labels=torch.from_numpy(lab_f).cuda())
+    b = SupConLoss(engine='fp32')(f, labels=torch.from_numpy(lab_i).cuda())
+    assert float(a) == float(b)
+
+
+def test_backward_general_geometry_matches_direct(monkeypatch):
+    """The two backward paths (rows finished inside the kernel by a CTA pair / per-slot partials + reduce kernel)
+    are the same arithmetic up to the order of two additions."""
+    import os
+    import subprocess
+    import sys
+    code = ("import torch, numpy as np, torch.nn.functional as F\n"
+            "from simclr_pytorch_distributed_b200 import SupConLoss\n"
+            "g = torch.Generator().manual_seed(3)\n"
+            "z = F.normalize(torch.randn(4096, 2, 128, generator=g), dim=-1).to(torch.bfloat16).cuda().requires_grad_(True)\n"
+            "l = SupConLoss(temperature=0.5, engine='bf16')(z); l.backward(); torch.cuda.synchronize()\n"
+            "np.save(__import__('sys').argv[1], z.grad.float().cpu().numpy()); print(float(l))\n")
+    outs = []
+    for direct in ('1', '0'):
+        path = '/tmp/scb_bwd_%s.npy' % direct
+        env = dict(os.environ, SCB_BWD_DIRECT=direct)
+        r = subprocess.run([sys.executable, '-c', code, path], env=env, capture_output=True, text=True, timeout=300,
+                           cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append((float(r.stdout.strip().splitlines()[-1]), np.load(path)))
+    assert outs[0][0] == outs[1][0]
+    assert rel_f(outs[0][1].astype(np.float64), outs[1][1].astype(np.float64)) <= 2.0 ** -8

@@ -309,3 +309,77 @@ def test_large_layer_shapes_property():
         assert m.abs().max() < 1e-5 and (v - 1).abs().max() < 1e-4
         assert xd.grad.double().mean(dim=(0, 2, 3)).abs().max() < 1e-6
         assert (xd.grad.double() * y.double()).mean(dim=(0, 2, 3)).abs().max() < 1e-5
+
+
+# ----------------------------------------------------------------------------- residual add + ReLU (resnet_big.py:27-30,60-63)
+@pytest.mark.parametrize('shape,cl,dtype', [((32, 64, 16, 16), True, torch.float32), ((256, 256, 8, 8), True, torch.bfloat16),
+                                            ((512, 64, 32, 32), True, torch.bfloat16), ((16, 24, 5, 7), False, torch.float32),
+                                            ((64, 128), False, torch.float32)])
+@pytest.mark.parametrize('relu', [True, False])
+def test_residual_add_relu_matches_unfused_expression(shape, cl, dtype, relu):
+    """y = relu(bn(x) + z) in one pass vs torch autograd on the unfused expression (fp64 reference)."""
+    torch.manual_seed(sum(shape) + int(relu))
+    C = shape[1]
+    x = (torch.randn(shape, device=DEV) * 1.5 + 0.3).to(dtype)
+    z = torch.randn(shape, device=DEV).to(dtype)
+    dy = torch.randn(shape, device=DEV).to(dtype)
+    if cl:
+        x, z, dy = (t.contiguous(memory_format=torch.channels_last) for t in (x, z, dy))
+    bn = make_bn(C, fuse_relu=relu)
+    ref = (torch.nn.BatchNorm2d(C) if len(shape) == 4 else torch.nn.BatchNorm1d(C)).to(DEV).double()
+    ref.load_state_dict(bn.state_dict())
+    xd, zd = x.clone().requires_grad_(True), z.clone().requires_grad_(True)
+    y = bn(xd, zd)
+    y.backward(dy)
+    xr, zr = x.double().requires_grad_(True), z.double().requires_grad_(True)
+    yr = ref(xr) + zr
+    if relu:
+        yr = torch.relu(yr)
+    # gate by OUR output where the reference is within rounding of zero (a bf16 y may round onto the other side)
+    yr.backward(dy.double())
+    if dtype == torch.float32:
+        assert torch.allclose(y.double(), yr, atol=2e-5)
+        assert torch.allclose(xd.grad.double(), xr.grad, atol=5e-5)
+        assert torch.allclose(zd.grad.double(), zr.grad, atol=1e-6)
+    else:
+        ulp = 2.0 ** -7
+        assert torch.all((y.double() - yr).abs() <= ulp * yr.abs() + 2e-2)
+        near0 = yr.abs() < 2e-2
+        assert torch.all(((xd.grad.double() - xr.grad).abs() <= ulp * xr.grad.abs() + 2e-2) | near0)
+        assert torch.all((zd.grad.double() == zr.grad) | near0)
+    assert torch.allclose(bn.weight.grad.double(), ref.weight.grad, rtol=2e-3 if dtype != torch.float32 else 1e-4,
+                          atol=5e-2 if dtype != torch.float32 else 1e-3)
+
+
+@pytest.mark.parametrize('shape,dtype', [((256, 256, 8, 8), torch.bfloat16), ((64, 128, 8, 8), torch.float32),
+                                         ((512, 512, 4, 4), torch.bfloat16), ((128, 256, 16, 16), torch.bfloat16)])
+def test_cluster_kernels_match_multi_kernel_path(shape, dtype, monkeypatch):
+    """Single-launch cluster kernels vs stats -> apply / reduce -> apply on the same tensors."""
+    torch.manual_seed(5)
+    C = shape[1]
+    x = (torch.randn(shape, device=DEV) * 1.7 + 0.4).to(dtype).contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(shape, device=DEV).to(dtype).contiguous(memory_format=torch.channels_last)
+    outs = []
+    for fused in ('1', '0'):
+        monkeypatch.setenv('SCB_BN_FUSED', fused)
+        bn = make_bn(C, fuse_relu=True)
+        with torch.no_grad():
+            bn.running_mean.zero_(); bn.running_var.fill_(1.0)
+            bn.weight.fill_(1.25); bn.bias.fill_(0.1)
+        y, dx, gw, gb = ours_fwd_bwd(x, dy, bn)
+        outs.append((y.float(), dx.float(), gw, gb, bn.running_mean.clone(), bn.running_var.clone()))
+    tol = 2.0 ** -7 if dtype == torch.bfloat16 else 1e-5
+    # the ReLU gate may flip for outputs within rounding of zero: compare away from it
+    far = outs[1][0].abs() > 1e-2
+    assert torch.all(((outs[0][0] - outs[1][0]).abs() <= tol * outs[1][0].abs() + 1e-5) | ~far)
+    assert torch.all(((outs[0][1] - outs[1][1]).abs() <= tol * outs[1][1].abs() + 1e-4) | ~far)
+    for a, b in zip(outs[0][2:], outs[1][2:]):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-3 * max(1.0, float(b.abs().max())))
+
+
+def test_fused_supported_reports_capacity():
+    """[256,256,8,8] bf16 fits forward and backward; a 268 MB layer does not."""
+    x = torch.empty(256, 256, 8, 8, device=DEV, dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    x_, geom = _layout(x)
+    assert _Kernels.fused_supported(x_, geom, 0) and _Kernels.fused_supported(x_, geom, 1)
+    assert not _Kernels.fused_supported(x_, (1, 512 * 32 * 32, 256, 1), 1)
