@@ -104,6 +104,10 @@ int fp32_backward(const scb_supcon_problem* p, int row_begin, int n_rows, const 
 int launch_finalize(const scb_supcon_problem* p, const float* part, int n_split, int flat_q, int flat_ct,
                     int row_begin, int n_rows, double inv_anchors, float* out_lse, float* out_possum, float* out_npos,
                     float* out_loss_sum, void* scratch, cudaStream_t stream, const scb_peer_channel* ch = nullptr);
-constexpr int kFinScratchBytes = 4096;   // ticket + per-CTA partial sums of the finalize kernel
+// Start of every loss workspace: [4096 bytes: ticket + per-CTA partial sums of the finalize kernel (fp32 engine)]
+// [kTicketRegionBytes: row-block tickets of the tensor-core forward].  Both are zero on entry and re-arm themselves;
+// nothing else is ever written there, whatever engine or shape used the workspace last.
+constexpr int kTicketRegionBytes = 16384;
+constexpr int kFinScratchBytes = 4096 + kTicketRegionBytes;
 
 }  // namespace scb

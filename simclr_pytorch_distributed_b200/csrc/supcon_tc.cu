@@ -95,6 +95,7 @@ struct TcParams {
     int ld_dk;
     float* dk_part;                     // backward partials [slot][RB*128][ldk] (one slot per CTA sharing a row block)
     int pair;                           // backward, direct finish: CTAs per row block (1, or 2 = a cluster pair)
+    int dbg;                            // timing experiments only (SCB_DBG): skip parts of the tails, results are wrong
     FwdOut fo;
     FinishParams fin;
     long long* trace;                   // optional (debug): per-role timestamps of CTA 0
@@ -449,13 +450,14 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             }
             // row-block ticket: the CTA that delivers the last partials of the block merges them (fwd_merge_rows)
             const int n_cta = ((rb + 1) * p.CT - 1) / p.q - first_cta + 1;
+            if (p.dbg & 16) return;
             named_bar_sync(1, 512);                       // all partial stores of this CTA are issued ...
             if (threadIdx.x == 64) {
                 __threadfence();                          // ... and made visible before the ticket (cumulative)
                 *s_ticket = atomicAdd(p.fo.rb_count + rb, 1u);
             }
             named_bar_sync(1, 512);
-            if (*s_ticket == (unsigned)n_cta - 1u) fwd_merge_rows(p, rb, n_cta, s_red);
+            if (*s_ticket == (unsigned)n_cta - 1u && !(p.dbg & 8)) fwd_merge_rows(p, rb, n_cta, s_red);
         };
 
         // incremental tile bookkeeping (no division per tile); one copy of the flush and of the chunk code:
@@ -1190,8 +1192,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
         float* recv = own + 128 * pitch;
         const int rb_d = rb0;
         const uint32_t crank = (p.pair == 2) ? cluster_ctarank() : 0u;
-        if (p.pair == 2) cluster_sync_all();               // the partner, too, is done with its B stages
-        if (warp >= 2 && warp < 18) {
+        if (p.pair == 2 && !(p.dbg & 4)) cluster_sync_all();               // the partner, too, is done with its B stages
+        if (warp >= 2 && warp < 18 && !(p.dbg & 2)) {
             const int g = (warp - 2) >> 2, q4 = warp & 3;
             tc_fence_after();
             if (g * 32 < ND) {
@@ -1206,8 +1208,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                 }
             }
         }
-        if (p.pair == 2) cluster_sync_all(); else __syncthreads();
-        if (warp >= 2 && warp < 18) {
+        if (p.pair == 2 && !(p.dbg & 4)) cluster_sync_all(); else __syncthreads();
+        if (warp >= 2 && warp < 18 && !(p.dbg & 1)) {
             if (p.pair == 2) finish_staged(p, own, recv, pitch, rb_d * kBMB + (int)crank * 64, 64, warp - 2, lane);
             else finish_staged(p, own, nullptr, pitch, rb_d * kBMB, 128, warp - 2, lane);
         }
@@ -1462,14 +1464,18 @@ static size_t label_block_bytes(const scb_supcon_problem* p) {
 }
 int64_t tc_label_cache_bytes(const scb_supcon_problem* p) { return (int64_t)label_block_bytes(p); }
 
+static constexpr int kMaxFwdRowBlocks = 4092;                 // 256-row blocks of the forward: up to ~1M local rows
+static_assert((size_t)(kMaxFwdRowBlocks + 4) * sizeof(unsigned) <= (size_t)kTicketRegionBytes, "ticket region");
 struct TcWs { float* part; char* labels; unsigned* rb_count; double* rb_loss; float* dk_part; size_t total; };
 static TcWs tc_ws_carve(const scb_supcon_problem* p, int n_rows, void* base) {
     TcWs w;
     char* ws = (char*)base;
     const int rbf = (int)ceil_div(n_rows, kBM);
+    // The tickets must find zeros: they sit at a FIXED place in front of the engine scratch (supcon_common.cuh),
+    // where nothing else is ever written whatever the previous call on this workspace was, and re-arm themselves.
+    w.rb_count = base ? (unsigned*)(ws - kTicketRegionBytes) : nullptr;       // [kMaxFwdRowBlocks] tickets | done counter
     w.part = (float*)ws; ws += align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float));
     w.labels = ws; ws += label_block_bytes(p);
-    w.rb_count = (unsigned*)ws; ws += align256(((size_t)rbf + 4) * sizeof(unsigned));     // [rbf] tickets | done counter
     w.rb_loss = (double*)ws; ws += align256((size_t)rbf * sizeof(double));
     w.dk_part = (float*)ws; ws += dk_part_bytes(p, n_rows);
     w.total = (size_t)(ws - (char*)base);
@@ -1484,6 +1490,7 @@ int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows) {
 static int tc_supported(const scb_supcon_problem* p) {
     if (p->engine == SCB_ENGINE_BF16X3) { set_error("the bf16x3 engine is not built yet"); return SCB_ERR_UNSUPPORTED; }
     if (p->mask_kind == SCB_MASK_EXPLICIT) { set_error("tensor-core engine: explicit masks run on ENGINE_FP32"); return SCB_ERR_UNSUPPORTED; }
+    if ((int64_t)p->n_k > (int64_t)kMaxFwdRowBlocks * kBM) { set_error("tensor-core engine: more than %d rows", kMaxFwdRowBlocks * kBM); return SCB_ERR_UNSUPPORTED; }
     if (p->ldk != 64 && p->ldk != 128) { set_error("tensor-core engine: ldk must be 64 or 128 (dim <= 128), got %d", p->ldk); return SCB_ERR_UNSUPPORTED; }
     return SCB_OK;
 }
@@ -1510,11 +1517,12 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
         t->fin.cls_anc = (p->mode == SCB_MODE_ALL) ? t->fin.cls_all : (const float*)lb;
     }
     t->fo.rb_count = w.rb_count;
-    t->fo.done_count = w.rb_count + (int)ceil_div(n_rows, kBM);
+    t->fo.done_count = w.rb_count + kMaxFwdRowBlocks;
     t->fo.rb_loss = w.rb_loss;
     t->fo.po = PeerOut::none();
     t->dk_part = w.dk_part;
     t->pair = 0;
+    { const char* e = getenv("SCB_DBG"); t->dbg = e ? atoi(e) : 0; }
     t->trace = g_trace;
 }
 
