@@ -313,6 +313,8 @@ int scb_bn_backward_apply(const void* dy, const void* x, const void* y, void* dx
  * says so beforehand, otherwise they return SCB_ERR_UNSUPPORTED and the caller runs the two-kernel path. */
 int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner, int which,
                            int flags);
+/* diagnostics: how many clusters of `cluster_size` CTAs of these kernels the current device holds at once */
+int scb_bn_cluster_occupancy(int cluster_size);
 int scb_bn_forward_fused(const void* x, const void* z, void* y, int dtype, int64_t rows, int channels,
                          const float* weight, const float* bias, float* running_mean, float* running_var,
                          float momentum, float eps, float* save_mean, float* save_invstd, float* save_count,

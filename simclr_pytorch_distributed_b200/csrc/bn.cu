@@ -16,10 +16,15 @@
 // result and zeroes them again, so the scratch is reusable without a memset.
 #include "common.cuh"
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 namespace scb {
 
 constexpr int kBnThreads = 256;
 constexpr int kUnroll = 4;
+constexpr int kStatsUnroll = 8;     // rows in flight per thread in the read-only statistics pass
 
 // ------------------------------------------------------------------ NHWC launch geometry
 struct NhwcGeom {
@@ -28,6 +33,11 @@ struct NhwcGeom {
 };
 
 static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+static int nhwc_vec(int C, int elem_size, bool aligned16) {
+    const int vmax = 16 / elem_size;
+    return (aligned16 && C % vmax == 0) ? vmax : 1;
+}
 
 static NhwcGeom nhwc_geom(int64_t M, int C, int elem_size, bool aligned16, int target_ctas,
                           int threads = kBnThreads) {
@@ -136,12 +146,12 @@ bn_stats_nhwc_kernel(const T* __restrict__ x, int64_t M, int C, int TX, int64_t 
         const T* p = x + r * C + c0;
         const int64_t step = (int64_t)TY * C;
         if (r < r_end) load_row_vec<T, VEC>(p, shift);
-        for (; r + (kUnroll - 1) * TY < r_end; r += kUnroll * TY, p += kUnroll * step) {
-            float v[kUnroll][VEC];
+        for (; r + (kStatsUnroll - 1) * TY < r_end; r += kStatsUnroll * TY, p += kStatsUnroll * step) {
+            float v[kStatsUnroll][VEC];
 #pragma unroll
-            for (int u = 0; u < kUnroll; ++u) load_row_vec<T, VEC>(p + u * step, v[u]);
+            for (int u = 0; u < kStatsUnroll; ++u) load_row_vec<T, VEC>(p + u * step, v[u]);
 #pragma unroll
-            for (int u = 0; u < kUnroll; ++u)
+            for (int u = 0; u < kStatsUnroll; ++u)
 #pragma unroll
                 for (int i = 0; i < VEC; ++i) {
                     const float d = v[u][i] - shift[i];
@@ -611,6 +621,33 @@ bn_bwd_apply_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, cons
 // ------------------------------------------------------------------ host-side dispatch
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// CTAs of `kern` that are resident at once on the current device: the streaming kernels are launched as exactly one
+// resident wave (a grid sized for 4 CTAs per SM when only 3 fit runs a second, nearly empty wave and takes twice as
+// long).  Cached per (kernel, device).
+template <typename Kern>
+static int resident_ctas(Kern kern, size_t smem) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, int> cache;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const std::pair<const void*, int> key((const void*)kern, dev);
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = cache.find(key);
+        if (it != cache.end()) return it->second;
+    }
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kBnThreads, smem) != cudaSuccess || occ < 1) {
+        cudaGetLastError();
+        occ = 2;
+    }
+    if (occ > 4) occ = 4;
+    const int n = occ * sm_count();
+    std::lock_guard<std::mutex> lock(mu);
+    cache[key] = n;
+    return n;
+}
+
 struct NchwGeom { int vec; int64_t n_per_cta, grid_y; };
 static NchwGeom nchw_geom(int64_t N, int C, int64_t inner, int elem_size, bool al16, int target_ctas) {
     NchwGeom g;
@@ -663,11 +700,13 @@ extern "C" int scb_bn_stats(const void* x, int dtype, int channels_last, int64_t
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;
-            NhwcGeom g = nhwc_geom(M, C, sizeof(T), aligned16(x), target);
-            dim3 grid(g.grid_x, (unsigned)g.grid_y);
-            size_t smem = 2 * kBnThreads * g.vec * sizeof(float);
-            SCB_VEC_SWITCH(g.vec, VEC, (bn_stats_nhwc_kernel<T, VEC><<<grid, kBnThreads, smem, stream>>>(
-                (const T*)x, M, C, g.tx, g.rows_per_cta, acc, counter, out_stats)));
+            SCB_VEC_SWITCH(nhwc_vec(C, sizeof(T), aligned16(x)), VEC, {
+                auto kern = bn_stats_nhwc_kernel<T, VEC>;
+                const size_t smem = 2 * kBnThreads * VEC * sizeof(float);
+                NhwcGeom g = nhwc_geom(M, C, sizeof(T), aligned16(x), resident_ctas(kern, smem));
+                dim3 grid(g.grid_x, (unsigned)g.grid_y);
+                kern<<<grid, kBnThreads, smem, stream>>>((const T*)x, M, C, g.tx, g.rows_per_cta, acc, counter, out_stats);
+            });
         } else {
             NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), aligned16(x), target);
             dim3 grid(C, (unsigned)g.grid_y);
@@ -701,17 +740,26 @@ extern "C" int scb_bn_apply(const void* x, const void* z, void* y, int dtype, in
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;
-            NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, target);
-            dim3 grid(g.grid_x, (unsigned)g.grid_y);
-            size_t smem = 2 * g.tx * g.vec * sizeof(float);
-            if (add) {
-                SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nhwc_kernel<T, VEC, true><<<grid, kBnThreads, smem, stream>>>(
-                    (const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta, stats_all, n_ranks, weight, bias,
-                    running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
+if (add) {
+                SCB_VEC_SWITCH(nhwc_vec(C, sizeof(T), al), VEC, {
+                    auto kern = bn_apply_nhwc_kernel<T, VEC, true>;
+                    const size_t smem = 2 * 32 * VEC * sizeof(float);
+                    NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, resident_ctas(kern, smem));
+                    dim3 grid(g.grid_x, (unsigned)g.grid_y);
+                    kern<<<grid, kBnThreads, smem, stream>>>((const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta,
+                        stats_all, n_ranks, weight, bias, running_mean, running_var, momentum, eps, save_mean,
+                        save_invstd, save_count, flags);
+                });
             } else {
-                SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nhwc_kernel<T, VEC, false><<<grid, kBnThreads, smem, stream>>>(
-                    (const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta, stats_all, n_ranks, weight, bias,
-                    running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
+                SCB_VEC_SWITCH(nhwc_vec(C, sizeof(T), al), VEC, {
+                    auto kern = bn_apply_nhwc_kernel<T, VEC, false>;
+                    const size_t smem = 2 * 32 * VEC * sizeof(float);
+                    NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, resident_ctas(kern, smem));
+                    dim3 grid(g.grid_x, (unsigned)g.grid_y);
+                    kern<<<grid, kBnThreads, smem, stream>>>((const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta,
+                        stats_all, n_ranks, weight, bias, running_mean, running_var, momentum, eps, save_mean,
+                        save_invstd, save_count, flags);
+                });
             }
         } else {
             NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), al, target);
@@ -759,13 +807,15 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, const void*
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;
-            NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, target);
-            dim3 grid(g.grid_x, (unsigned)g.grid_y);
-            size_t smem = 2 * kBnThreads * g.vec * sizeof(float);
             SCB_GATE_SWITCH(gate, GATE, {
-                SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_reduce_nhwc_kernel<T, VEC, GATE><<<grid, kBnThreads, smem, stream>>>(
-                    (const T*)dy, (const T*)x, (const T*)y, M, C, g.tx, g.rows_per_cta, mean, invstd, weight, bias, acc,
-                    counter, out_sums, grad_weight, grad_bias)));
+                SCB_VEC_SWITCH(nhwc_vec(C, sizeof(T), al), VEC, {
+                    auto kern = bn_bwd_reduce_nhwc_kernel<T, VEC, GATE>;
+                    const size_t smem = 2 * kBnThreads * VEC * sizeof(float);
+                    NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, resident_ctas(kern, smem));
+                    dim3 grid(g.grid_x, (unsigned)g.grid_y);
+                    kern<<<grid, kBnThreads, smem, stream>>>((const T*)dy, (const T*)x, (const T*)y, M, C, g.tx,
+                        g.rows_per_cta, mean, invstd, weight, bias, acc, counter, out_sums, grad_weight, grad_bias);
+                });
             });
         } else {
             NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), al, target);
@@ -799,12 +849,14 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* 
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (channels_last) {
             const int64_t M = outer * inner;
-            NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, target);
-            dim3 grid(g.grid_x, (unsigned)g.grid_y);
             SCB_GATE_SWITCH(gate, GATE, {
-                SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_apply_nhwc_kernel<T, VEC, GATE><<<grid, kBnThreads, 0, stream>>>(
-                    (const T*)dy, (const T*)x, (const T*)y, (T*)dx, (T*)dz, M, C, g.tx, g.rows_per_cta, mean, invstd,
-                    weight, bias, sums, n_total)));
+                SCB_VEC_SWITCH(nhwc_vec(C, sizeof(T), al), VEC, {
+                    auto kern = bn_bwd_apply_nhwc_kernel<T, VEC, GATE>;
+                    NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, resident_ctas(kern, 0));
+                    dim3 grid(g.grid_x, (unsigned)g.grid_y);
+                    kern<<<grid, kBnThreads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)y, (T*)dx, (T*)dz, M, C,
+                        g.tx, g.rows_per_cta, mean, invstd, weight, bias, sums, n_total);
+                });
             });
         } else {
             NchwGeom g = nchw_geom(outer, C, inner, sizeof(T), al, target);

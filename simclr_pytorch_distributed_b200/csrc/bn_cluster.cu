@@ -390,14 +390,40 @@ static int cl_max_cs() {
     return cached[dev];
 }
 
-// CTAs of one cluster size that can be resident at once on a B200 (148 SMs in 8 GPCs of 16..20): the grid should
-// not exceed it (a second wave doubles the time of a latency-bound pass)
-static int cl_wave_cap(int cs) {
-    const int sms = sm_count();
-    if (cs >= 8) return (sms * 128 / 148) / cs * cs;      // two clusters of 8 (one of 16) per GPC
-    if (cs == 4) return (sms * 132 / 148) / 4 * 4;
-    return sms / cs * cs;
+// Clusters of `cs` CTAs of these kernels that the device can hold at once (occupancy API; cached per device).  On
+// a B200 not every GPC has 16 free SMs: measured 7 clusters of 16, i.e. an 8-cluster grid runs a second wave.
+static int cl_max_active(int cs) {
+    static int cached[64][kClMaxCS + 1] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || cs < 1 || cs > kClMaxCS) return 1;
+    if (cached[dev][cs] == 0) {
+        auto kern = bn_bwd_cluster_kernel<__nv_bfloat16, 0, 0>;
+        const size_t smem = cl_smem_bytes(4, 8);
+        int n = 0;
+        if (cs == 1) {
+            n = sm_count();
+        } else {
+            if (cs > 8) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(cs * 64);
+            cfg.blockDim = dim3(kClThreads);
+            cfg.dynamicSmemBytes = smem;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
+        }
+        cached[dev][cs] = n > 0 ? n : -1;
+    }
+    return cached[dev][cs] > 0 ? cached[dev][cs] : 0;
 }
+
+// CTAs of one cluster size that can be resident at once: the grid should not exceed it (a second wave doubles the
+// time of a latency-bound pass)
+static int cl_wave_cap(int cs) { return cl_max_active(cs) * cs; }
 
 // picks (TX, CS) so that the tensor fits the registers of ONE resident wave; false if it does not
 static bool cl_geom(int64_t M, int C, int es, int rows, ClGeom* out) {
@@ -469,6 +495,9 @@ static cudaError_t cl_launch_bwd(const ClGeom& g, cudaStream_t stream, const voi
 }  // namespace scb
 
 using namespace scb;
+
+// diagnostics: clusters of `cluster_size` CTAs of the fused kernels the current device can hold at once
+extern "C" int scb_bn_cluster_occupancy(int cluster_size) { return cl_max_active(cluster_size); }
 
 // which = 0: forward (with or without a residual operand, see `flags`), 1: backward
 extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner,

@@ -182,6 +182,8 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
     if (e < kBM && li < p.a_count) {
         const int n_split = 2 * n_cta;
         float m = -INFINITY, sum = 0.f, ps = 0.f, np = 0.f;
+        // partial maxima are in the log2 domain (as the tile loop keeps them); MUFU ex2 / lg2 keep this code short --
+        // it runs once per row block, cold, so its size is its cost
         for (int s0 = 0; s0 < n_split; s0 += 8) {          // eight slots at a time: their loads are in flight together
             float vm[8], vs[8], vp[8], vn[8];
 #pragma unroll
@@ -198,17 +200,16 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
             for (int u = 1; u < 8; ++u) cm = fmaxf(cm, vm[u]);
             const float nm = fmaxf(m, cm);
             if (nm > -INFINITY) {
-                float acc = (m > -INFINITY) ? sum * expf(m - nm) : 0.f;
+                float acc = sum * ex2(m - nm);                 // m = -inf: sum is 0 and ex2(-inf) = 0
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    if (vm[u] > -INFINITY) acc += vs[u] * expf(vm[u] - nm);
+                for (int u = 0; u < 8; ++u) acc = fmaf(vs[u], ex2(vm[u] - nm), acc);
                 sum = acc;
                 m = nm;
             }
 #pragma unroll
             for (int u = 0; u < 8; ++u) { ps += vp[u]; np += vn[u]; }
         }
-        const float lse = m + logf(sum);
+        const float lse = (m + __log2f(sum)) * kLn2;
         contrib = (double)(-o.loss_scale * (ps / np - lse));          // losses.py:87,90 (0/0 -> nan)
         o.out_possum[li] = ps;
         if (o.po.n_dst > 0) {
@@ -443,7 +444,7 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                     np = (float)(p.n_views - 1);
                 }
                 float* dst = p.part + (int64_t)slot * 4 * p.n_rows + li;
-                dst[0] = m * kLn2;
+                dst[0] = m;                               // log2 domain
                 dst[p.n_rows] = sum;
                 dst[2 * (int64_t)p.n_rows] = ps;
                 dst[3 * (int64_t)p.n_rows] = np;
@@ -760,31 +761,124 @@ __device__ __noinline__ void stage_block(uint32_t taddr, uint32_t dst, int remot
     }
 }
 
-// The sixteen epilogue warps turn the staged rows into d features, four rows per warp at a time.
-// own / recv: [n_keep][pitch] fp32 (recv = the partner's contribution, or nullptr).
+// ---- compact 8-wide row finish of the direct backward.  This code runs ONCE per CTA, cold: every kilobyte of it is
+// an instruction-cache miss at the tail of the kernel, so it is written for size -- one copy of everything, rolled
+// loops, 16-byte typed vector accesses (the host only takes this path for 16-byte aligned features with dim % 8 == 0).
+__device__ __forceinline__ void load_k8(const __nv_bfloat16* row, int d, float (&o)[8]) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(row + d);
+    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h2[i]); o[2 * i] = f.x; o[2 * i + 1] = f.y; }
+}
+__device__ __noinline__ void load8_typed(const void* base, int dtype, int64_t idx, float (&o)[8]) {
+    if (dtype == SCB_F32) {
+        const float4 a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(base) + idx);
+        const float4 b = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(base) + idx + 4);
+        o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+    } else if (dtype == SCB_BF16) {
+        load_k8(reinterpret_cast<const __nv_bfloat16*>(base) + idx, 0, o);
+    } else {
+        const uint4 raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const __half*>(base) + idx);
+        const __half2* h2 = reinterpret_cast<const __half2*>(&raw);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(h2[i]); o[2 * i] = f.x; o[2 * i + 1] = f.y; }
+    }
+}
+__device__ __noinline__ void store8_typed(void* base, int dtype, int64_t idx, const float (&v)[8]) {
+    if (dtype == SCB_F32) {
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(base) + idx) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(base) + idx + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    } else {
+        uint4 raw;
+        if (dtype == SCB_BF16) {
+            __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h2[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(base) + idx) = raw;
+        } else {
+            __half2* h2 = reinterpret_cast<__half2*>(&raw);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h2[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+            *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(base) + idx) = raw;
+        }
+    }
+}
+
+// The sixteen epilogue warps turn the staged rows into d features.  A row is spread over ldk / 8 lanes (8 features
+// each), so a warp finishes 2 (ldk = 128) or 4 (ldk = 64) rows per pass.  own / recv: [n_keep][pitch] fp32 (recv = the
+// partner CTA's contribution, or nullptr).
 __device__ __noinline__ void finish_staged(const TcParams& p, const float* own, const float* recv, int pitch,
                                            int lrow0, int n_keep, int ew, int lane) {
-    const float coef = load_scalar(p.grad_out, p.fin.grad_dtype) * p.fin.coef_scale_invT;
-    const int d = lane * 4;
-    for (int r0 = ew * 4; r0 < n_keep; r0 += 64) {
-        float acc[4][4];
-        int lrow[4];
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            const int rr = r0 + b;
-            lrow[b] = (rr < n_keep && lrow0 + rr < p.n_rows) ? lrow0 + rr : -1;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) acc[b][i] = 0.f;
-            if (lrow[b] >= 0 && d < p.ldk) {
-                float4 a = *reinterpret_cast<const float4*>(own + rr * pitch + d);
-                if (recv != nullptr) {
-                    const float4 c = *reinterpret_cast<const float4*>(recv + rr * pitch + d);
-                    a.x += c.x; a.y += c.y; a.z += c.z; a.w += c.w;
-                }
-                acc[b][0] = a.x; acc[b][1] = a.y; acc[b][2] = a.z; acc[b][3] = a.w;
+    const FinishParams& f = p.fin;
+    const float coef = load_scalar(p.grad_out, f.grad_dtype) * f.coef_scale_invT;
+    const int lpr = p.ldk >> 3, rpw = 32 / lpr;              // lanes per row, rows per warp pass
+    const int sub = lane / lpr, d = (lane - sub * lpr) * 8;
+#pragma unroll 1
+    for (int r0 = ew * rpw; r0 < n_keep; r0 += 16 * rpw) {
+        const int rr = r0 + sub;
+        const int lrow = lrow0 + rr;
+        const bool ok = rr < n_keep && lrow < p.n_rows;
+        const int lr = ok ? lrow : lrow0;
+        const int gi = p.row_begin + lr;
+        float a[8];
+        {
+            const float4 a0 = *reinterpret_cast<const float4*>(own + (ok ? rr : 0) * pitch + d);
+            const float4 a1 = *reinterpret_cast<const float4*>(own + (ok ? rr : 0) * pitch + d + 4);
+            a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+            if (recv != nullptr) {
+                const float4 c0 = *reinterpret_cast<const float4*>(recv + (ok ? rr : 0) * pitch + d);
+                const float4 c1 = *reinterpret_cast<const float4*>(recv + (ok ? rr : 0) * pitch + d + 4);
+                a[0] += c0.x; a[1] += c0.y; a[2] += c0.z; a[3] += c0.w; a[4] += c1.x; a[5] += c1.y; a[6] += c1.z; a[7] += c1.w;
             }
         }
-        finish_rows<4>(p, acc, lrow, lane, coef);
+        // positive-pair term (see positive_term): one weighted row per other view, or the class sums
+        if (p.mask_kind == SCB_MASK_SIMCLR && p.n_views >= 2) {
+            const int v = p.map.view_of(gi);
+            const float ai = p.map.is_anchor(gi, p.mode) ? 1.f : 0.f;
+            const float cpos = -1.f / (float)(p.n_views - 1);
+#pragma unroll 1
+            for (int vv = 0; vv < p.n_views; ++vv) {
+                if (vv == v) continue;
+                const int j = p.map.sibling(gi, vv);
+                const float wgt = cpos * (ai + (p.map.is_anchor(j, p.mode) ? 1.f : 0.f));
+                float kj[8];
+                load_k8(p.k + (int64_t)j * p.ldk, d, kj);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) a[i] = fmaf(wgt, kj[i], a[i]);
+            }
+        } else if (p.mask_kind == SCB_MASK_LABELS) {
+            const int rep = p.rep_row[gi];
+            const float nia_i = p.nia_row[gi];
+            const float c = 1.f / p.npos_row[gi];
+            const float ai = p.map.is_anchor(gi, p.mode) ? 1.f : 0.f;
+            float ki[8], sa[8], sn[8];
+            load_k8(p.k + (int64_t)gi * p.ldk, d, ki);
+            load8_typed(f.cls_all, SCB_F32, (int64_t)rep * p.ldk + d, sa);
+            load8_typed(f.cls_anc, SCB_F32, (int64_t)rep * p.ldk + d, sn);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] -= nia_i * (sa[i] - ki[i]) + c * (sn[i] - ai * ki[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] *= coef;
+        // local row = v*n_samples + b (view-major) or b*n_views + v (sample-major)  ->  features[b, v, :]
+        const int v_l = p.map.il ? lr % p.n_views : lr / f.n_samples;
+        const int b_l = p.map.il ? lr / p.n_views : lr - v_l * f.n_samples;
+        const bool in_dim = d < p.dim;
+        if (f.normalize) {                                   // backward of main_supcon.py:283
+            const float inv = f.inv_norm[lr];
+            float z[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) z[i] = 0.f;
+            if (in_dim) load8_typed(f.feat, f.feat_dtype, (int64_t)b_l * f.stride_s + (int64_t)v_l * f.stride_v + d, z);
+            float dot = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { z[i] *= inv; dot = fmaf(a[i], z[i], dot); }
+            for (int o = lpr >> 1; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = (a[i] - z[i] * dot) * inv;
+        }
+        if (ok && in_dim)
+            store8_typed(f.out, f.feat_dtype, (int64_t)b_l * f.ostride_s + (int64_t)v_l * f.ostride_v + d, a);
     }
 }
 
@@ -1622,6 +1716,16 @@ static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_ro
     TcGeom g = tc_geom_bwd(p->n_k, n_rows);
     static const bool no_direct = [] { const char* e = getenv("SCB_BWD_DIRECT"); return e != nullptr && e[0] == '0'; }();
     if (fin == nullptr || no_direct) g.direct = 0;
+    if (fin != nullptr && g.direct) {
+        // the in-kernel finish uses 16-byte vector accesses on 8 consecutive features
+        const int es = fin->feat_dtype == SCB_F32 ? 4 : 2;
+        const bool vec_ok = p->dim % 8 == 0 && (reinterpret_cast<uintptr_t>(fin->out) & 15u) == 0 &&
+                            fin->ostride_s % 8 == 0 && fin->ostride_v % 8 == 0 &&
+                            (!fin->normalize || ((reinterpret_cast<uintptr_t>(fin->feat) & 15u) == 0 &&
+                                                 fin->stride_s % 8 == 0 && fin->stride_v % 8 == 0));
+        (void)es;
+        if (!vec_ok) g.direct = 0;
+    }
     TcParams t;
     fill_params(p, row_begin, n_rows, n_rows, g, workspace, &t);
     t.lse_all = lse_all; t.grad_out = grad_out;
