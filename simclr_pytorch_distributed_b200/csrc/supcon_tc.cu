@@ -298,6 +298,12 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
     double* s_red = reinterpret_cast<double*>(bars + 18);                  // [16] merge scratch
     volatile uint32_t* s_ticket = reinterpret_cast<volatile uint32_t*>(bars + 34);
+    // shared-memory copy of the parameters for the out-of-line tail code: through a reference, kernel parameters
+    // are read with generic loads from the parameter window (an L2 round trip per dependent field; measured 7 us
+    // per tail), from shared memory they cost an LDS
+    TcParams* sp = reinterpret_cast<TcParams*>(bars + 40);
+    for (int i = threadIdx.x; i < (int)(sizeof(TcParams) / 4); i += kTcThreads)
+        reinterpret_cast<uint32_t*>(sp)[i] = reinterpret_cast<const uint32_t*>(&p)[i];
     const uint32_t bar0 = smem_u32(bars);
     auto a_full = [&](int b) { return bar0 + 8u * (0 + b); };
     auto a_empty = [&](int b) { return bar0 + 8u * (2 + b); };
@@ -458,7 +464,7 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                 *s_ticket = atomicAdd(p.fo.rb_count + rb, 1u);
             }
             named_bar_sync(1, 512);
-            if (*s_ticket == (unsigned)n_cta - 1u && !(p.dbg & 8)) fwd_merge_rows(p, rb, n_cta, s_red);
+            if (*s_ticket == (unsigned)n_cta - 1u && !(p.dbg & 8)) fwd_merge_rows(*sp, rb, n_cta, s_red);
         };
 
         // incremental tile bookkeeping (no division per tile); one copy of the flush and of the chunk code:
@@ -941,6 +947,10 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
     uint32_t* flags = reinterpret_cast<uint32_t*>(cols + NSB * 256);      // [NSB][4]
     uint64_t* bars = reinterpret_cast<uint64_t*>(flags + NSB * 4 + 4);    // 23 used
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+    TcParams* sp = reinterpret_cast<TcParams*>(bars + 28);          // see the forward kernel
+    if (kDirect)
+        for (int i = threadIdx.x; i < (int)(sizeof(TcParams) / 4); i += kBwdThreads)
+            reinterpret_cast<uint32_t*>(sp)[i] = reinterpret_cast<const uint32_t*>(&p)[i];
     const uint32_t bar0 = smem_u32(bars);
     const uint32_t a_full = bar0, a_empty = bar0 + 8u;
     auto b_full = [&](int s) { return bar0 + 8u * (2 + s); };
@@ -1304,8 +1314,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
         }
         if (p.pair == 2 && !(p.dbg & 4)) cluster_sync_all(); else __syncthreads();
         if (warp >= 2 && warp < 18 && !(p.dbg & 1)) {
-            if (p.pair == 2) finish_staged(p, own, recv, pitch, rb_d * kBMB + (int)crank * 64, 64, warp - 2, lane);
-            else finish_staged(p, own, nullptr, pitch, rb_d * kBMB, 128, warp - 2, lane);
+            if (p.pair == 2) finish_staged(*sp, own, recv, pitch, rb_d * kBMB + (int)crank * 64, 64, warp - 2, lane);
+            else finish_staged(*sp, own, nullptr, pitch, rb_d * kBMB, 128, warp - 2, lane);
         }
         tc_fence_before();
         __syncthreads();
@@ -1500,6 +1510,7 @@ void tc_set_trace(long long* p) { g_trace = p; }
 static cudaEvent_t g_ev_start = nullptr, g_ev_stop = nullptr;
 void tc_set_events(void* a, void* b) { g_ev_start = (cudaEvent_t)a; g_ev_stop = (cudaEvent_t)b; }
 
+static_assert(sizeof(TcParams) % 4 == 0 && sizeof(TcParams) <= 1024, "TcParams copy in shared memory");
 struct TcGeom { int CT, RB, T, q, grid, n_split, direct; };
 
 static TcGeom tc_geom(int n_k, int rows) {
@@ -1689,7 +1700,7 @@ int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, int n_anc
     // with a label cache the class sums of the backward are built here, once per step
     if (int e = launch_label_rows(p, t, p->label_cache != nullptr, stream)) return e;
     const int kch = p->ldk / 64;
-    const size_t smem = (size_t)2 * (2 * kch * kSub) + 2 * (kch * kSub) + 16 * 8 + 16 + 16 * 8 + 16;
+    const size_t smem = (size_t)2 * (2 * kch * kSub) + 2 * (kch * kSub) + 40 * 8 + 1024;
     const bool lab = p->mask_kind == SCB_MASK_LABELS;
 #define SCB_LAUNCH_FWD(KCH_, LAB_)                                                                      \
     do {                                                                                                \
@@ -1742,7 +1753,7 @@ static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_ro
     if (p->label_cache == nullptr)
         if (int e = launch_label_rows(p, t, true, stream)) return e;
     const int kch = p->ldk / 64;
-    const size_t smem = (size_t)(kch * kSub) + 5 * (kch * kSub) + 5 * 256 * 4 + (5 * 4 + 4) * 4 + 24 * 8 + 16;
+    const size_t smem = (size_t)(kch * kSub) + 5 * (kch * kSub) + 5 * 256 * 4 + (5 * 4 + 4) * 4 + 28 * 8 + 1024;
 #define SCB_LAUNCH_BWD(KCH_, DIR_)                                                                      \
     do {                                                                                                \
         if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, DIR_>, smem)) return e;                         \
