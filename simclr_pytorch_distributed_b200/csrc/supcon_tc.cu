@@ -49,8 +49,7 @@ constexpr int kPolyLane = SCB_POLY_LANE;
 // the loss; the last row block to finish adds the shares in block order (deterministic) and writes the scalar.
 struct FwdOut {
     unsigned* rb_count;     // [RB] tickets, zero on entry, zero again on exit
-    unsigned* done_count;   // row blocks merged so far (self re-arming)
-    double* rb_loss;        // [RB] per-row-block sums of -(T/Tb)(possum/npos - lse)
+    unsigned long long* acc;  // packed (fixed-point loss sum << 12 | row blocks merged), self re-arming
     float* out_lse;
     float* out_possum;
     float* out_npos;
@@ -171,7 +170,7 @@ __device__ __forceinline__ void store_loss_scalar(float* out, float loss, int sc
 
 // Called by the 512 epilogue threads of the CTA that delivered the LAST partials of row block `rb` (losses.py:83-91
 // for those 256 rows): merges the (max, sum, possum, npos) slots of every row, writes lse / possum / npos, and leaves
-// the block's share of the loss in rb_loss[rb]; whoever completes the last row block adds the shares in block order.
+// the block's share of the loss in a packed 64-bit accumulator; whoever completes the last row block holds the total.
 // Out of line: it runs once or twice per CTA and must not sit in the middle of the tile loop's code.
 __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta, double* s_red) {
     const int e = (int)threadIdx.x - 64;          // 0..511
@@ -184,10 +183,10 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
         float m = -INFINITY, sum = 0.f, ps = 0.f, np = 0.f;
         // partial maxima are in the log2 domain (as the tile loop keeps them); MUFU ex2 / lg2 keep this code short --
         // it runs once per row block, cold, so its size is its cost
-        for (int s0 = 0; s0 < n_split; s0 += 8) {          // eight slots at a time: their loads are in flight together
-            float vm[8], vs[8], vp[8], vn[8];
+        for (int s0 = 0; s0 < n_split; s0 += 12) {         // twelve slots at a time (a row block is shared by <= 6 CTAs): one round trip
+            float vm[12], vs[12], vp[12], vn[12];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
+            for (int u = 0; u < 12; ++u) {
                 const bool ok = s0 + u < n_split;
                 const float* q = p.part + ((int64_t)(s0 + u) * 4) * p.n_rows + li;
                 vm[u] = ok ? __ldcg(q) : -INFINITY;
@@ -197,17 +196,17 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
             }
             float cm = vm[0];
 #pragma unroll
-            for (int u = 1; u < 8; ++u) cm = fmaxf(cm, vm[u]);
+            for (int u = 1; u < 12; ++u) cm = fmaxf(cm, vm[u]);
             const float nm = fmaxf(m, cm);
             if (nm > -INFINITY) {
                 float acc = sum * ex2(m - nm);                 // m = -inf: sum is 0 and ex2(-inf) = 0
 #pragma unroll
-                for (int u = 0; u < 8; ++u) acc = fmaf(vs[u], ex2(vm[u] - nm), acc);
+                for (int u = 0; u < 12; ++u) acc = fmaf(vs[u], ex2(vm[u] - nm), acc);
                 sum = acc;
                 m = nm;
             }
 #pragma unroll
-            for (int u = 0; u < 8; ++u) { ps += vp[u]; np += vn[u]; }
+            for (int u = 0; u < 12; ++u) { ps += vp[u]; np += vn[u]; }
         }
         const float lse = (m + __log2f(sum)) * kLn2;
         contrib = (double)(-o.loss_scale * (ps / np - lse));          // losses.py:87,90 (0/0 -> nan)
@@ -245,28 +244,30 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
     }
     contrib = warp_sum_f64(contrib);
     if ((e & 31) == 0) s_red[e >> 5] = contrib;
-    named_bar_sync(1, 512);                       // also orders every thread's stores before thread 0's fence below
+    named_bar_sync(1, 512);                       // also orders every thread's stores before thread 0's atomic below
     if (e < 32) {
         double t = (e < 16) ? s_red[e] : 0.0;
         t = warp_sum_f64(t);
-        unsigned last = 0u;
         if (e == 0) {
-            o.rb_loss[rb] = t;
             o.rb_count[rb] = 0u;                  // re-arm the ticket for the next launch
+            // The block's share joins the others in ONE 64-bit atomic: bits 12.. carry the sum in fixed point
+            // (2^-20 units: integer addition is exact and order-independent, so the loss is deterministic), bits
+            // 0..11 count the row blocks.  Whoever brings the count to RB holds the exact total -- no second
+            // ticket, no re-read of the shares.  A non-finite share (an anchor without positives, losses.py:87)
+            // is sent as a huge value that the reader turns back into NaN.
+            const bool finite = fabs(t) < 1e12;
+            const long long fx = finite ? __double2ll_rn(t * 1048576.0) : (1ll << 50);
+            const unsigned long long add = ((unsigned long long)fx << 12) + 1ull;
             if (o.po.n_dst > 0) __threadfence_system(); else __threadfence();
-            last = (atomicAdd(o.done_count, 1u) == (unsigned)p.RB - 1u) ? 1u : 0u;
-        }
-        last = __shfl_sync(0xffffffffu, last, 0);
-        if (last) {
-            __threadfence();
-            double tot = 0.0;
-            for (int b = e; b < p.RB; b += 32) tot += __ldcg(o.rb_loss + b);
-            tot = warp_sum_f64(tot);
-            if (e == 0) {
-                const float loss = (float)(tot * o.inv_anchors);
-                *o.done_count = 0u;
+            const unsigned long long now = atomicAdd(o.acc, add) + add;
+            if ((int)(now & 4095ull) == p.RB) {
+                *o.acc = 0ull;
+                const long long tot_fx = (long long)now >> 12;
+                float loss = (float)((double)tot_fx * (1.0 / 1048576.0) * o.inv_anchors);
+                if (tot_fx >= (1ll << 49) || tot_fx <= -(1ll << 49)) loss = __int_as_float(0x7fc00000);
                 if (o.po.n_dst > 0) {
                     // this rank's share of the global mean goes to every rank, then the rank's flag is raised there
+                    __threadfence_system();
                     for (int w = 0; w < o.po.n_dst; ++w)
                         reinterpret_cast<float*>(o.po.dst[w])[2 * o.n_k + 4 * o.my_slot] = loss;
                     __threadfence_system();
@@ -816,7 +817,7 @@ __device__ __noinline__ void store8_typed(void* base, int dtype, int64_t idx, co
 __device__ __noinline__ void finish_staged(const TcParams& p, const float* own, const float* recv, int pitch,
                                            int lrow0, int n_keep, int ew, int lane) {
     const FinishParams& f = p.fin;
-    const float coef = load_scalar(p.grad_out, f.grad_dtype) * f.coef_scale_invT;
+    const float coef = f.coef_scale_invT;                    // already times the upstream gradient (kernel prologue)
     const int lpr = p.ldk >> 3, rpw = 32 / lpr;              // lanes per row, rows per warp pass
     const int sub = lane / lpr, d = (lane - sub * lpr) * 8;
 #pragma unroll 1
@@ -982,6 +983,10 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
     pdl_launch_dependents();
     pdl_wait();                                  // everything above touched no global memory
     if (kTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[2047] = global_ns();
+    // the tail's scale factor, upstream gradient included: fetched now, so that the finish does not start with a
+    // global-memory round trip
+    if (kDirect && threadIdx.x == 32)
+        sp->fin.coef_scale_invT = load_scalar(p.grad_out, p.fin.grad_dtype) * p.fin.coef_scale_invT;
 
     const int t0 = blockIdx.x * p.q;
     const int n_tiles = min(p.T, t0 + p.q) - t0;
@@ -1569,19 +1574,17 @@ static size_t label_block_bytes(const scb_supcon_problem* p) {
 }
 int64_t tc_label_cache_bytes(const scb_supcon_problem* p) { return (int64_t)label_block_bytes(p); }
 
-static constexpr int kMaxFwdRowBlocks = 4092;                 // 256-row blocks of the forward: up to ~1M local rows
+static constexpr int kMaxFwdRowBlocks = 4090;                 // 256-row blocks of the forward: up to ~1M local rows
 static_assert((size_t)(kMaxFwdRowBlocks + 4) * sizeof(unsigned) <= (size_t)kTicketRegionBytes, "ticket region");
-struct TcWs { float* part; char* labels; unsigned* rb_count; double* rb_loss; float* dk_part; size_t total; };
+struct TcWs { float* part; char* labels; unsigned* rb_count; float* dk_part; size_t total; };
 static TcWs tc_ws_carve(const scb_supcon_problem* p, int n_rows, void* base) {
     TcWs w;
     char* ws = (char*)base;
-    const int rbf = (int)ceil_div(n_rows, kBM);
     // The tickets must find zeros: they sit at a FIXED place in front of the engine scratch (supcon_common.cuh),
     // where nothing else is ever written whatever the previous call on this workspace was, and re-arm themselves.
     w.rb_count = base ? (unsigned*)(ws - kTicketRegionBytes) : nullptr;       // [kMaxFwdRowBlocks] tickets | done counter
     w.part = (float*)ws; ws += align256((size_t)kMaxSlots * 4 * n_rows * sizeof(float));
     w.labels = ws; ws += label_block_bytes(p);
-    w.rb_loss = (double*)ws; ws += align256((size_t)rbf * sizeof(double));
     w.dk_part = (float*)ws; ws += dk_part_bytes(p, n_rows);
     w.total = (size_t)(ws - (char*)base);
     return w;
@@ -1622,8 +1625,7 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
         t->fin.cls_anc = (p->mode == SCB_MODE_ALL) ? t->fin.cls_all : (const float*)lb;
     }
     t->fo.rb_count = w.rb_count;
-    t->fo.done_count = w.rb_count + kMaxFwdRowBlocks;
-    t->fo.rb_loss = w.rb_loss;
+    t->fo.acc = reinterpret_cast<unsigned long long*>(w.rb_count + kMaxFwdRowBlocks);
     t->fo.po = PeerOut::none();
     t->dk_part = w.dk_part;
     t->pair = 0;
