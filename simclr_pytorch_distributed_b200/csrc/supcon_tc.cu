@@ -32,7 +32,7 @@ constexpr int kBMH = 128;       // rows per half = one UMMA M
 constexpr int kBM = 256;        // rows per CTA tile
 constexpr int kBN = 128;        // columns per tile
 constexpr int kSub = 16384;     // bytes of one [128 x 64] bf16 swizzled sub-tile
-constexpr int kTcThreads = 608; // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..17 = four epilogue warpgroups, warp 18 = code prefetch
+constexpr int kTcThreads = 576; // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..17 = four epilogue warpgroups
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kSafeSpread = 60.f;
@@ -172,9 +172,8 @@ __device__ __forceinline__ void store_loss_scalar(float* out, float loss, int sc
 // for those 256 rows): merges the (max, sum, possum, npos) slots of every row, writes lse / possum / npos, and leaves
 // the block's share of the loss in a packed 64-bit accumulator; whoever completes the last row block holds the total.
 // Out of line: it runs once or twice per CTA and must not sit in the middle of the tile loop's code.
-// dry != 0: executed once at kernel start by the code-prefetch warp (e = its lane): same instructions, no stores, no
-// barriers, no atomics -- it only pulls this cold code into the SM's instruction cache before the tail needs it.
-__device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta, double* s_red, int e, int dry) {
+__device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta, double* s_red) {
+    const int e = (int)threadIdx.x - 64;          // 0..511
     const FwdOut& o = p.fo;
     __threadfence();                              // acquire side of the row-block ticket
     double contrib = 0.0;
@@ -211,21 +210,19 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
         }
         const float lse = (m + __log2f(sum)) * kLn2;
         contrib = (double)(-o.loss_scale * (ps / np - lse));          // losses.py:87,90 (0/0 -> nan)
-        if (dry) {
-        } else if (o.po.n_dst > 0) {
-            o.out_possum[li] = ps;
+        o.out_possum[li] = ps;
+        if (o.po.n_dst > 0) {
             for (int w = 0; w < o.po.n_dst; ++w) {
                 float* d = reinterpret_cast<float*>(o.po.dst[w]);
                 d[p.row_begin + li] = lse;
                 d[o.n_k + p.row_begin + li] = np;
             }
         } else {
-            o.out_possum[li] = ps;
             o.out_lse[li] = lse;
             o.out_npos[li] = np;
         }
     }
-    if (p.n_rows > p.a_count && !dry) {
+    if (p.n_rows > p.a_count) {
         // local rows that are not anchors (mode `one`, views > 0): lse = 0, possum = 0, npos = 1; every merging CTA
         // fills its share of them
         const int extra = p.n_rows - p.a_count, chunk = (extra + p.RB - 1) / p.RB;
@@ -246,14 +243,12 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
         }
     }
     contrib = warp_sum_f64(contrib);
-    if (!dry) {
-        if ((e & 31) == 0) s_red[e >> 5] = contrib;
-        named_bar_sync(1, 512);                   // also orders every thread's stores before thread 0's atomic below
-    }
+    if ((e & 31) == 0) s_red[e >> 5] = contrib;
+    named_bar_sync(1, 512);                       // also orders every thread's stores before thread 0's atomic below
     if (e < 32) {
         double t = (e < 16) ? s_red[e] : 0.0;
         t = warp_sum_f64(t);
-        if (e == 0 && !dry) {
+        if (e == 0) {
             o.rb_count[rb] = 0u;                  // re-arm the ticket for the next launch
             // The block's share joins the others in ONE 64-bit atomic: bits 12.. carry the sum in fixed point
             // (2^-20 units: integer addition is exact and order-independent, so the loss is deterministic), bits
@@ -286,7 +281,7 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
             }
         }
     }
-    if (!dry) named_bar_sync(1, 512);             // s_red may be reused by this CTA's next merge
+    named_bar_sync(1, 512);                       // s_red may be reused by this CTA's next merge
 }
 
 // =================================================================================== forward
@@ -417,10 +412,6 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             }
             ++idx;
         }
-    } else if (warp == 18) {
-        // ---------------------------------------------------- code prefetch: a dry run of the tail code (see
-        // fwd_merge_rows) while the pipeline fills; the tail is instruction-fetch bound when it runs cold
-        fwd_merge_rows(*sp, 0, 1, s_red, lane, 1);
     } else {
         // ---------------------------------------------------- epilogue warpgroups
         const int w4 = (warp - 2) >> 2;                 // warpgroup = (row half wg, column half ca)
@@ -474,7 +465,7 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                 *s_ticket = atomicAdd(p.fo.rb_count + rb, 1u);
             }
             named_bar_sync(1, 512);
-            if (*s_ticket == (unsigned)n_cta - 1u && !(p.dbg & 8)) fwd_merge_rows(*sp, rb, n_cta, s_red, (int)threadIdx.x - 64, 0);
+            if (*s_ticket == (unsigned)n_cta - 1u && !(p.dbg & 8)) fwd_merge_rows(*sp, rb, n_cta, s_red);
         };
 
         // incremental tile bookkeeping (no division per tile); one copy of the flush and of the chunk code:
@@ -823,9 +814,8 @@ __device__ __noinline__ void store8_typed(void* base, int dtype, int64_t idx, co
 // The sixteen epilogue warps turn the staged rows into d features.  A row is spread over ldk / 8 lanes (8 features
 // each), so a warp finishes 2 (ldk = 128) or 4 (ldk = 64) rows per pass.  own / recv: [n_keep][pitch] fp32 (recv = the
 // partner CTA's contribution, or nullptr).
-// dry != 0: the code-prefetch warp's run at kernel start -- same instructions, nothing stored.
 __device__ __noinline__ void finish_staged(const TcParams& p, const float* own, const float* recv, int pitch,
-                                           int lrow0, int n_keep, int ew, int lane, int dry) {
+                                           int lrow0, int n_keep, int ew, int lane) {
     const FinishParams& f = p.fin;
     const float coef = f.coef_scale_invT;                    // already times the upstream gradient (kernel prologue)
     const int lpr = p.ldk >> 3, rpw = 32 / lpr;              // lanes per row, rows per warp pass
@@ -894,7 +884,7 @@ __device__ __noinline__ void finish_staged(const TcParams& p, const float* own, 
 #pragma unroll
             for (int i = 0; i < 8; ++i) a[i] = (a[i] - z[i] * dot) * inv;
         }
-        if (ok && in_dim && !dry)
+        if (ok && in_dim)
             store8_typed(f.out, f.feat_dtype, (int64_t)b_l * f.ostride_s + (int64_t)v_l * f.ostride_v + d, a);
     }
 }
@@ -939,7 +929,7 @@ __device__ __forceinline__ void cluster_sync_all() {     // every thread of ever
 // TMEM: S[b] at columns b*128 (b = 0..2), dK at 384 .. 384 + 64*KCH.
 
 constexpr int kBMB = 128;       // rows per row block of the backward
-constexpr int kBwdThreads = 640;     // 18 warps as in the forward + one more issuing warp + the code-prefetch warp
+constexpr int kBwdThreads = 608;     // the forward's 18 warps + one more issuing warp
 constexpr int kBwdMma1Warp = 18;
 
 template <int KCH, bool kDirect>
@@ -1109,14 +1099,6 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             __syncwarp();
             tr(102);
             if (++ct1 == p.CT) ct1 = 0;
-        }
-    } else if (warp == 19) {
-        // ---------------------------------------------------- code prefetch: a dry run of the finish code while the
-        // pipeline fills (the tail is instruction-fetch bound when it runs cold); reads only, stores nothing
-        if (kDirect) {
-            const int pitch = p.ldk + 4;
-            const float* own = reinterpret_cast<const float*>(b_smem);
-            finish_staged(*sp, own, p.pair == 2 ? own + 128 * pitch : nullptr, pitch, 0, 32, 0, lane, 1);
         }
     } else if (warp == 1) {
         // ---------------------------------------------------- MMA2 issuer: dK += P(t) x K_j
@@ -1337,8 +1319,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
         }
         if (p.pair == 2 && !(p.dbg & 4)) cluster_sync_all(); else __syncthreads();
         if (warp >= 2 && warp < 18 && !(p.dbg & 1)) {
-            if (p.pair == 2) finish_staged(*sp, own, recv, pitch, rb_d * kBMB + (int)crank * 64, 64, warp - 2, lane, 0);
-            else finish_staged(*sp, own, nullptr, pitch, rb_d * kBMB, 128, warp - 2, lane, 0);
+            if (p.pair == 2) finish_staged(*sp, own, recv, pitch, rb_d * kBMB + (int)crank * 64, 64, warp - 2, lane);
+            else finish_staged(*sp, own, nullptr, pitch, rb_d * kBMB, 128, warp - 2, lane);
         }
         tc_fence_before();
         __syncthreads();
