@@ -812,80 +812,98 @@ __device__ __noinline__ void store8_typed(void* base, int dtype, int64_t idx, co
 }
 
 // The sixteen epilogue warps turn the staged rows into d features.  A row is spread over ldk / 8 lanes (8 features
-// each), so a warp finishes 2 (ldk = 128) or 4 (ldk = 64) rows per pass.  own / recv: [n_keep][pitch] fp32 (recv = the
-// partner CTA's contribution, or nullptr).
+// each) and a lane group works on kFinRows rows at once, so that their global loads share one round trip: with
+// ldk = 128 the 64 rows of a CTA pair's half are done in a single pass.  own / recv: [n_keep][pitch] fp32 (recv =
+// the partner CTA's contribution, or nullptr).
+constexpr int kFinRows = 1;       // 2 measured slower: the tail is bound by the amount of (cold) code, not by load latency
 __device__ __noinline__ void finish_staged(const TcParams& p, const float* own, const float* recv, int pitch,
                                            int lrow0, int n_keep, int ew, int lane) {
     const FinishParams& f = p.fin;
     const float coef = f.coef_scale_invT;                    // already times the upstream gradient (kernel prologue)
     const int lpr = p.ldk >> 3, rpw = 32 / lpr;              // lanes per row, rows per warp pass
     const int sub = lane / lpr, d = (lane - sub * lpr) * 8;
+    const bool in_dim = d < p.dim;
 #pragma unroll 1
-    for (int r0 = ew * rpw; r0 < n_keep; r0 += 16 * rpw) {
-        const int rr = r0 + sub;
-        const int lrow = lrow0 + rr;
-        const bool ok = rr < n_keep && lrow < p.n_rows;
-        const int lr = ok ? lrow : lrow0;
-        const int gi = p.row_begin + lr;
-        float a[8];
-        {
-            const float4 a0 = *reinterpret_cast<const float4*>(own + (ok ? rr : 0) * pitch + d);
-            const float4 a1 = *reinterpret_cast<const float4*>(own + (ok ? rr : 0) * pitch + d + 4);
-            a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+    for (int r0 = ew * rpw * kFinRows; r0 < n_keep; r0 += 16 * rpw * kFinRows) {
+        float a[kFinRows][8], z[kFinRows][8], inv[kFinRows];
+        int64_t src_off[kFinRows], dst_off[kFinRows];
+        bool ok[kFinRows];
+        // ---- phase 1: everything that comes from memory, for all rows of the group
+#pragma unroll
+        for (int q = 0; q < kFinRows; ++q) {
+            const int rr = r0 + q * rpw + sub;
+            ok[q] = rr < n_keep && lrow0 + rr < p.n_rows;
+            const int rs = ok[q] ? rr : 0;
+            const int lr = lrow0 + rs;
+            const int gi = p.row_begin + lr;
+            const float4 a0 = *reinterpret_cast<const float4*>(own + rs * pitch + d);
+            const float4 a1 = *reinterpret_cast<const float4*>(own + rs * pitch + d + 4);
+            a[q][0] = a0.x; a[q][1] = a0.y; a[q][2] = a0.z; a[q][3] = a0.w;
+            a[q][4] = a1.x; a[q][5] = a1.y; a[q][6] = a1.z; a[q][7] = a1.w;
             if (recv != nullptr) {
-                const float4 c0 = *reinterpret_cast<const float4*>(recv + (ok ? rr : 0) * pitch + d);
-                const float4 c1 = *reinterpret_cast<const float4*>(recv + (ok ? rr : 0) * pitch + d + 4);
-                a[0] += c0.x; a[1] += c0.y; a[2] += c0.z; a[3] += c0.w; a[4] += c1.x; a[5] += c1.y; a[6] += c1.z; a[7] += c1.w;
+                const float4 c0 = *reinterpret_cast<const float4*>(recv + rs * pitch + d);
+                const float4 c1 = *reinterpret_cast<const float4*>(recv + rs * pitch + d + 4);
+                a[q][0] += c0.x; a[q][1] += c0.y; a[q][2] += c0.z; a[q][3] += c0.w;
+                a[q][4] += c1.x; a[q][5] += c1.y; a[q][6] += c1.z; a[q][7] += c1.w;
             }
-        }
-        // positive-pair term (see positive_term): one weighted row per other view, or the class sums
-        if (p.mask_kind == SCB_MASK_SIMCLR && p.n_views >= 2) {
-            const int v = p.map.view_of(gi);
-            const float ai = p.map.is_anchor(gi, p.mode) ? 1.f : 0.f;
-            const float cpos = -1.f / (float)(p.n_views - 1);
+            // local row = v*n_samples + b (view-major) or b*n_views + v (sample-major)  ->  features[b, v, :]
+            // (ONE division; view, siblings and anchor flags follow from it: the local rows are one segment)
+            const int qd = (unsigned)lr / (unsigned)(p.map.il ? p.n_views : f.n_samples);
+            const int v_l = p.map.il ? lr - qd * p.n_views : qd;
+            const int b_l = p.map.il ? qd : lr - qd * f.n_samples;
+            src_off[q] = (int64_t)b_l * f.stride_s + (int64_t)v_l * f.stride_v + d;
+            dst_off[q] = (int64_t)b_l * f.ostride_s + (int64_t)v_l * f.ostride_v + d;
+            const bool all = p.mode == SCB_MODE_ALL;
+            // positive-pair term (see positive_term): one weighted row per other view, or the class sums
+            if (p.mask_kind == SCB_MASK_SIMCLR && p.n_views >= 2) {
+                const float ai = (all || v_l == 0) ? 1.f : 0.f;
+                const float cpos = -1.f / (float)(p.n_views - 1);
+                const int vstep = p.map.il ? 1 : p.map.seg;
 #pragma unroll 1
-            for (int vv = 0; vv < p.n_views; ++vv) {
-                if (vv == v) continue;
-                const int j = p.map.sibling(gi, vv);
-                const float wgt = cpos * (ai + (p.map.is_anchor(j, p.mode) ? 1.f : 0.f));
-                float kj[8];
-                load_k8(p.k + (int64_t)j * p.ldk, d, kj);
+                for (int vv = 0; vv < p.n_views; ++vv) {
+                    if (vv == v_l) continue;
+                    const int j = gi + (vv - v_l) * vstep;
+                    const float wgt = cpos * (ai + ((all || vv == 0) ? 1.f : 0.f));
+                    float kj[8];
+                    load_k8(p.k + (int64_t)j * p.ldk, d, kj);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) a[i] = fmaf(wgt, kj[i], a[i]);
+                    for (int i = 0; i < 8; ++i) a[q][i] = fmaf(wgt, kj[i], a[q][i]);
+                }
+            } else if (p.mask_kind == SCB_MASK_LABELS) {
+                const int rep = p.rep_row[gi];
+                const float nia_i = p.nia_row[gi];
+                const float c = 1.f / p.npos_row[gi];
+                const float ai = (all || v_l == 0) ? 1.f : 0.f;
+                float ki[8], sa[8], sn[8];
+                load_k8(p.k + (int64_t)gi * p.ldk, d, ki);
+                load8_typed(f.cls_all, SCB_F32, (int64_t)rep * p.ldk + d, sa);
+                load8_typed(f.cls_anc, SCB_F32, (int64_t)rep * p.ldk + d, sn);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) a[q][i] -= nia_i * (sa[i] - ki[i]) + c * (sn[i] - ai * ki[i]);
             }
-        } else if (p.mask_kind == SCB_MASK_LABELS) {
-            const int rep = p.rep_row[gi];
-            const float nia_i = p.nia_row[gi];
-            const float c = 1.f / p.npos_row[gi];
-            const float ai = p.map.is_anchor(gi, p.mode) ? 1.f : 0.f;
-            float ki[8], sa[8], sn[8];
-            load_k8(p.k + (int64_t)gi * p.ldk, d, ki);
-            load8_typed(f.cls_all, SCB_F32, (int64_t)rep * p.ldk + d, sa);
-            load8_typed(f.cls_anc, SCB_F32, (int64_t)rep * p.ldk + d, sn);
+            inv[q] = 1.f;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] -= nia_i * (sa[i] - ki[i]) + c * (sn[i] - ai * ki[i]);
+            for (int i = 0; i < 8; ++i) z[q][i] = 0.f;
+            if (f.normalize) {                               // backward of main_supcon.py:283
+                inv[q] = f.inv_norm[lr];
+                if (in_dim) load8_typed(f.feat, f.feat_dtype, src_off[q], z[q]);
+            }
         }
+        // ---- phase 2: arithmetic and the stores
 #pragma unroll
-        for (int i = 0; i < 8; ++i) a[i] *= coef;
-        // local row = v*n_samples + b (view-major) or b*n_views + v (sample-major)  ->  features[b, v, :]
-        const int v_l = p.map.il ? lr % p.n_views : lr / f.n_samples;
-        const int b_l = p.map.il ? lr / p.n_views : lr - v_l * f.n_samples;
-        const bool in_dim = d < p.dim;
-        if (f.normalize) {                                   // backward of main_supcon.py:283
-            const float inv = f.inv_norm[lr];
-            float z[8];
+        for (int q = 0; q < kFinRows; ++q) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) z[i] = 0.f;
-            if (in_dim) load8_typed(f.feat, f.feat_dtype, (int64_t)b_l * f.stride_s + (int64_t)v_l * f.stride_v + d, z);
-            float dot = 0.f;
+            for (int i = 0; i < 8; ++i) a[q][i] *= coef;
+            if (f.normalize) {
+                float dot = 0.f;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { z[i] *= inv; dot = fmaf(a[i], z[i], dot); }
-            for (int o = lpr >> 1; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+                for (int i = 0; i < 8; ++i) { z[q][i] *= inv[q]; dot = fmaf(a[q][i], z[q][i], dot); }
+                for (int o = lpr >> 1; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] = (a[i] - z[i] * dot) * inv;
+                for (int i = 0; i < 8; ++i) a[q][i] = (a[q][i] - z[q][i] * dot) * inv[q];
+            }
+            if (ok[q] && in_dim) store8_typed(f.out, f.feat_dtype, dst_off[q], a[q]);
         }
-        if (ok && in_dim)
-            store8_typed(f.out, f.feat_dtype, (int64_t)b_l * f.ostride_s + (int64_t)v_l * f.ostride_v + d, a);
     }
 }
 
