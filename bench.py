@@ -196,10 +196,12 @@ def make_loss_runner(world, rank, engine, pool):
         crit = DistributedSupConLoss(temperature=TEMP, engine=engine, normalize=False)
         fwd = lambda f: crit(f)                                                     # noqa: E731
 
+    ones = torch.ones((), dtype=dtype, device='cuda')       # upstream gradient of the scalar loss, allocated once
+
     def step_resident(i):
         f = dev[i % pool]
         f.grad = None
-        fwd(f).backward()
+        fwd(f).backward(ones)
 
     # End to end: every step copies ITS embeddings from pinned host memory and the host reads the loss.  The
     # copy of step i+1 is issued on a side stream before step i computes (what a training loop's prefetcher
@@ -382,6 +384,165 @@ def bn_kernel_breakdown(steps, pool=8):
             for j in range(len(names)):
                 tot[j] += ev[j].elapsed_time(ev[j + 1])
     return {n: t / steps * 1e3 for n, t in zip(names, tot)}
+
+
+# ----------------------------------------------------------------------------- parity of what is timed
+def all_gather_cat(t, world):
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return t
+    parts = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(parts, t.contiguous())
+    return torch.cat(parts, 0)
+
+
+def loss_parity(world, rank, engine):
+    """Loss and this rank's gradient on the bench's own inputs against the reference's dense algorithm
+    (oracle/dense_port.py: /root/reference/losses.py:52-91 restated, eager PyTorch, fp64, on the GPU) fed the
+    all-gathered embeddings.  Checker only: nothing of this is timed as ours."""
+    import torch
+    import torch.nn.functional as F
+    from oracle.dense_port import dense_supcon_loss
+    from simclr_pytorch_distributed_b200 import SupConLoss
+    b_local = B_GLOBAL // world
+    dtype = torch.bfloat16 if engine == 'bf16' else torch.float32
+    g = torch.Generator().manual_seed(99 + rank)
+    z = F.normalize(torch.randn(b_local, N_VIEWS, DIM, generator=g), dim=-1).to(dtype).cuda()
+    f = z.clone().requires_grad_(True)
+    if world == 1:
+        loss = SupConLoss(temperature=TEMP, engine=engine)(f)
+    else:
+        from simclr_pytorch_distributed_b200.gather import DistributedSupConLoss
+        loss = DistributedSupConLoss(temperature=TEMP, engine=engine, normalize=False)(f)
+    loss.backward()
+    z_all = all_gather_cat(z, world)
+    out = None
+    if rank == 0:
+        ref_in = z_all.double().requires_grad_(True)
+        ref = dense_supcon_loss(ref_in, temperature=TEMP)
+        ref.backward()
+        gref = ref_in.grad[:b_local]
+        out = {'loss_rel_err': abs(float(loss) - float(ref)) / abs(float(ref)),
+               'grad_rel_fro_err': float((f.grad.double() - gref).norm() / gref.norm()),
+               'tolerance': 2e-3 if engine == 'bf16' else 1e-4,
+               'against': 'dense fp64 algorithm of losses.py:52-91 (oracle/dense_port.py, eager torch on the GPU) on the '
+                          'all-gathered bf16 embeddings; gradient of rank 0 vs its slice'}
+        del ref_in, ref
+    torch.cuda.empty_cache()
+    return out
+
+
+def bn_parity(world, rank):
+    """SyncBatchNorm y / dx / running statistics on per-rank tensors against stock torch.nn.SyncBatchNorm (NCCL,
+    world > 1) or torch.nn.BatchNorm2d (world 1): bf16 NHWC cfg 2 (within one bf16 ulp) and fp32 (1e-5)."""
+    import torch
+    from simclr_pytorch_distributed_b200 import SyncBatchNorm
+    res = {}
+    for name, dtype, shape in (('bf16_cfg2', torch.bfloat16, BN_SHAPE), ('fp32', torch.float32, (64, 256, 8, 8))):
+        N, C, H, W_ = shape
+        g = torch.Generator().manual_seed(777 + rank)
+        x = (torch.randn(shape, generator=g) * 1.5 + 0.5).to(dtype).cuda().contiguous(memory_format=torch.channels_last)
+        dy = torch.randn(shape, generator=g).to(dtype).cuda().contiguous(memory_format=torch.channels_last)
+        ours = SyncBatchNorm(C).cuda()
+        ref = (torch.nn.SyncBatchNorm(C) if world > 1 else torch.nn.BatchNorm2d(C)).cuda()
+        with torch.no_grad():
+            ours.weight.uniform_(0.5, 1.5)
+            ours.bias.normal_(0, 0.1)
+        if world > 1:
+            import torch.distributed as dist
+            for t in (ours.weight, ours.bias):
+                dist.broadcast(t.data, 0)
+        ref.load_state_dict(ours.state_dict())
+        xo, xr = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+        yo = ours(xo)
+        yo.backward(dy)
+        yr = ref(xr)
+        yr.backward(dy)
+        ulp = 2.0 ** -8 if dtype == torch.bfloat16 else 0.0
+
+        def err(a, b):      # worst error beyond one output ulp, relative to the largest reference magnitude
+            a, b = a.double(), b.double()
+            return float(((a - b).abs() - ulp * b.abs()).clamp_min(0).max() / b.abs().max())
+        res[name] = {'y_err': err(yo, yr), 'dx_err': err(xo.grad, xr.grad),
+                     'running_mean_err': float((ours.running_mean - ref.running_mean).abs().max()),
+                     'running_var_rel_err': float(((ours.running_var - ref.running_var).abs() / ref.running_var).max()),
+                     'dgamma_rel_err': float((ours.weight.grad - ref.weight.grad).norm() / ref.weight.grad.norm())}
+    res['tolerance'] = 1e-5
+    res['against'] = ('torch.nn.SyncBatchNorm over NCCL' if world > 1 else 'torch.nn.BatchNorm2d') + \
+                     ' on the same per-rank tensors; *_err = error beyond one ulp of the output dtype / max |reference|'
+    return res
+
+
+# ----------------------------------------------------------------------------- on-box GPU bar (SURVEY F12)
+def gpu_loss_baseline(steps=10):
+    """The reference's dense algorithm in eager PyTorch on THIS GPU (fp32, as main_supcon.py runs it; and with TF32
+    matmuls allowed), full 2N = 8192 problem on one GPU -- what every rank of the reference computes."""
+    import torch
+    import torch.nn.functional as F
+    from oracle.dense_port import dense_supcon_fwd_bwd
+    z = F.normalize(torch.randn(B_GLOBAL, N_VIEWS, DIM, device='cuda'), dim=-1)
+    out = {}
+    for name, tf32 in (('fp32', False), ('tf32', True)):
+        old = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = tf32
+        try:
+            for _ in range(3):
+                dense_supcon_fwd_bwd(z, temperature=TEMP)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                dense_supcon_fwd_bwd(z, temperature=TEMP)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            out[name] = {'ms_per_step': ms, 'value': B_GLOBAL / (ms * 1e-3), 'unit': 'pairs/s'}
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = old
+    out['what'] = 'oracle/dense_port.py (losses.py:52-91 restated) in eager PyTorch on the B200, 2N=8192 on one GPU'
+    torch.cuda.empty_cache()
+    return out
+
+
+def gpu_bn_baseline(world, steps=20, pool=12):
+    """Stock torch.nn.SyncBatchNorm (NCCL, world > 1) or the four ATen ops it runs (world 1) on cfg 2."""
+    import torch
+    N, C, H, W_ = BN_SHAPE
+    xs = [(torch.randn(BN_SHAPE, device='cuda') * 1.5 + 0.5).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last).requires_grad_(True) for _ in range(pool)]
+    dys = [torch.randn(BN_SHAPE, device='cuda').to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+           for _ in range(pool)]
+    if world > 1:
+        bn = torch.nn.SyncBatchNorm(C).cuda()
+
+        def step(i):
+            xs[i % pool].grad = None
+            bn(xs[i % pool]).backward(dys[i % pool])
+        what = 'torch.nn.SyncBatchNorm fwd+bwd over NCCL, eager'
+    else:
+        w, b = torch.ones(C, device='cuda'), torch.zeros(C, device='cuda')
+        count = torch.full((1,), N * H * W_, dtype=torch.int32, device='cuda')
+
+        def step(i):
+            x, dy = xs[i % pool].detach(), dys[i % pool]
+            mean, invstd = torch.batch_norm_stats(x, 1e-5)
+            torch.batch_norm_elemt(x, w, b, mean, invstd, 1e-5)
+            sd, sx, _, _ = torch.batch_norm_backward_reduce(dy, x, mean, invstd, w, True, True, True)
+            torch.batch_norm_backward_elemt(dy, x, mean, invstd, w, sd, sx, count)
+        what = 'the four ATen ops of torch/nn/modules/_functions.py:39,122,144,170, eager'
+    for i in range(5):
+        step(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    S = N * C * H * W_ * 2
+    return {'ms_per_step': ms, 'value': 8.0 * S / (ms * 1e-3) / 1e9, 'unit': 'GB/s per GPU', 'what': what}
 
 
 # ----------------------------------------------------------------------------- CPU baselines

@@ -1,5 +1,6 @@
-"""torch-CPU port of the reference's *dense* algorithm, used only as the timed CPU baseline
-(`bench.py` cpu_baseline / `--impl reference`) and as a second checker in tests.
+"""torch port of the reference's *dense* algorithm, used only as the timed baseline (`bench.py` cpu_baseline /
+`--impl reference` on the host cores, `gpu_baseline` / `parity` in eager PyTorch on the GPU: the on-box bar of
+SURVEY.md F12) and as a second checker in tests.
 TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).
 
 Why a port: the reference is pure Python on PyTorch; /root/reference does not
@@ -26,7 +27,7 @@ def dense_supcon_loss(features, labels=None, mask=None, temperature=0.07,
     if labels is not None and mask is not None:                             # :40-41
         raise ValueError('Cannot define both `labels` and `mask`')
     if labels is None and mask is None:                                     # :42-43
-        base = torch.eye(n_samples, dtype=torch.float32)
+        base = torch.eye(n_samples, dtype=torch.float32, device=feats.device)
     elif labels is not None:                                                # :44-48
         col = labels.contiguous().view(-1, 1)
         if col.shape[0] != n_samples:
@@ -45,7 +46,7 @@ def dense_supcon_loss(features, labels=None, mask=None, temperature=0.07,
     sim = sim - sim.max(dim=1, keepdim=True).values.detach()                # :68-69
     tiled = base.repeat(n_anchor_views, n_views)                            # :72
     keep = torch.ones_like(tiled)                                           # :74-79
-    rows = torch.arange(n_samples * n_anchor_views)
+    rows = torch.arange(n_samples * n_anchor_views, device=feats.device)
     keep[rows, rows] = 0
     tiled = tiled * keep                                                    # :80
     expo = torch.exp(sim) * keep                                            # :83
