@@ -177,12 +177,13 @@ def time_steps(step_fn, steps, warmup, world, graph_pool=0):
 
 
 # ----------------------------------------------------------------------------- NT-Xent (ours)
-def make_loss_runner(world, rank, engine, pool):
-    """Returns step functions for the loss on this rank's shard of the 2N=8192 global batch."""
+def make_loss_runner(world, rank, engine, pool, b_local=None):
+    """Returns step functions for the loss on this rank's shard of the 2N=8192 global batch (b_local given: that
+    many pairs per rank instead -- the weak-scaling series, 2N = 2 * b_local * world)."""
     import torch
     import torch.nn.functional as F
     from simclr_pytorch_distributed_b200 import SupConLoss
-    b_local = B_GLOBAL // world
+    b_local = B_GLOBAL // world if b_local is None else b_local
     dtype = torch.bfloat16 if engine == 'bf16' else torch.float32
     g = torch.Generator().manual_seed(1234 + rank)
     host = [F.normalize(torch.randn(b_local, N_VIEWS, DIM, generator=g), dim=-1).to(dtype).pin_memory()
@@ -642,9 +643,10 @@ def main():
     ap.add_argument('--steps', type=int, default=200)
     ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--workload', default='both', choices=['both', 'ntxent', 'syncbn'])
+    ap.add_argument('--workload', default='both', choices=['both', 'ntxent', 'syncbn', 'syncbn-census'])
     ap.add_argument('--engine', default=os.environ.get('SIMCLR_B200_BENCH_ENGINE', 'bf16'))
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-gpu-baseline', action='store_true')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == 'reference':
@@ -668,6 +670,24 @@ def main():
     sampler = ClockSampler(local) if rank == 0 else None
     t_load0 = time.time()
     out = {}
+
+    # ------------------------------------------------ SyncBN over the layer shapes of the reference ResNet-50
+    if args.workload == 'syncbn-census':
+        import importlib.util
+        spec = importlib.util.spec_from_file_location('bn_census', os.path.join(ROOT, 'tools', 'bn_census.py'))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        rows = mod.census(iters=max(5, min(args.steps, 20)))
+        for r in rows:
+            r['frac_of_hbm_peak'] = r['ours_GBs'] / pk['hbm']
+            r['ours_over_aten'] = r['aten_us'] / (r['ours_graph_us'] or r['ours_us'])
+        if rank == 0:
+            print(json.dumps({'metric': 'SyncBN fwd+bwd HBM GB/s (8*S algorithmic bytes) per layer shape', 'unit': 'GB/s',
+                              'n_gpus': world, 'higher_is_better': True, 'data': 'synthetic', 'dtype': 'bf16 I/O, f32 statistics',
+                              'config': {'workload': 'SURVEY Appendix B shapes at N=512 per GPU, NHWC bf16, plus cfg 2; '
+                                                     'beside the four ATen ops of stock SyncBatchNorm on the same tensors'},
+                              'peak': pk['hbm'], 'peak_source': pk['src'], 'census': rows}), flush=True)
+        return
 
     # ------------------------------------------------ NT-Xent
     if args.workload in ('both', 'ntxent'):
@@ -701,18 +721,38 @@ def main():
                             'copy stream), forward + backward, D2H of the loss, host sync; the gradient stays on '
                             'the device'},
             'gpu_launches': int(launches),
-            'step_tensor_frac_of_measured_peak': flops_step / world / (per * 1e-3) / (pk['tf'] * 1e12),
         })
+        # roofline of the STEP (6*A*C*D algorithmic FLOPs of SURVEY 8(d) over the graph-replayed step time, per GPU);
+        # the isolated kernels are listed under kernel_us
+        ach_step = flops_step / world / (per * 1e-3) / 1e12
+        out['roofline'] = {'bound': 'tensor', 'achieved': ach_step, 'peak': pk['tf'], 'unit': 'TFLOP/s',
+                           'frac': ach_step / pk['tf'],
+                           'frac_of_sustained_peak': ach_step / pk['tf_sus'] if pk.get('tf_sus') else None,
+                           'traffic': profiled_traffic('supcon_tc_bwd_kernel') if engine != 'fp32' else None,
+                           'kernel': 'whole step = supcon_tc_fwd_kernel + supcon_tc_bwd_kernel (%d launches), '
+                                     'CUDA-graph replay' % launches,
+                           'peak_source': pk['src'] + ' burst',
+                           'algorithmic_flops_per_step_per_gpu': flops_step / world}
         if rank == 0 and world == 1:
             kb = loss_kernel_breakdown(engine, min(args.steps, 100))
             t_bwd = kb['backward main kernel']
-            achieved = 4.0 * A * C * DIM / (t_bwd * 1e-6) / 1e12
-            out['roofline'] = {'bound': 'tensor', 'achieved': achieved, 'peak': pk['tf'], 'unit': 'TFLOP/s',
-                               'frac': achieved / pk['tf'],
-                               'traffic': profiled_traffic('supcon_tc_bwd_kernel') if engine != 'fp32' else None,
-                               'kernel': 'supcon_tc_bwd_kernel (%s engine), timed alone' % engine if engine != 'fp32' else 'supcon backward (fp32 engine)', 'peak_source': pk['src'] + ' burst',
-                               'algorithmic_flops_per_launch': 4.0 * A * C * DIM,
-                               'kernel_us': kb}
+            out['roofline']['kernel_us'] = kb
+            out['roofline']['kernel_us_note'] = ('event-bracketed isolated launches (they include launch gaps and add '
+                                                 'up to more than the graph-replayed step)')
+            out['roofline']['backward_kernel_frac'] = 4.0 * A * C * DIM / (t_bwd * 1e-6) / 1e12 / pk['tf']
+        par = loss_parity(world, rank, engine)
+        if rank == 0:
+            out['parity'] = par
+        if rank == 0 and not args.no_gpu_baseline:
+            out['gpu_baseline'] = gpu_loss_baseline()
+            out['gpu_baseline']['ours_over_gpu_baseline_fp32'] = out['value'] / out['gpu_baseline']['fp32']['value']
+        barrier(world)
+        if world > 1:
+            # weak-scaling series of SURVEY 8(d): 512 pairs per GPU, 2N = 1024 * world
+            w_res, _, _, _, _ = make_loss_runner(world, rank, engine, 16, b_local=512)
+            ms_w, _ = time_steps(w_res, args.steps, args.warmup, world, graph_pool=16)
+            out['scaling_weak'] = {'pairs_per_gpu': 512, 'global_2N': 1024 * world, 'ms_per_step': ms_w / args.steps,
+                                   'value': 512 * world / (ms_w / args.steps * 1e-3), 'unit': 'pairs/s'}
     # ------------------------------------------------ SyncBN
     if args.workload in ('both', 'syncbn'):
         pool = 12                                    # 12 x (x, dy, y, dx) of 8 MiB each = 400 MB > L2
@@ -734,23 +774,24 @@ def main():
               'e2e': {'value': 8.0 * S * world / (ms_e2e / args.steps * 1e-3) / 1e9, 'unit': 'GB/s',
                       'h2d_bytes_per_step': 2 * S, 'd2h_bytes_per_step': 2 * S},
               'gpu_launches': int(launches)}
+        # roofline of the STEP: 8*S algorithmic bytes over the graph-replayed fwd+bwd, per GPU
+        sb['roofline'] = {'bound': 'hbm', 'achieved': gbs, 'peak': pk['hbm'], 'unit': 'GB/s', 'frac': gbs / pk['hbm'],
+                          'traffic': profiled_traffic('bn_bwd_cluster'), 'kernel': 'whole step (%d launches): '
+                          'bn_fwd_cluster_kernel + bn_bwd_cluster_kernel' % launches,
+                          'peak_source': pk['src'], 'algorithmic_bytes_per_step': 8 * S,
+                          'note': 'the single-launch passes move 5*S (x once forward; x, dy once backward; y, dx written)'}
         if rank == 0 and world == 1:
             kb = bn_kernel_breakdown(min(args.steps, 100))
-            tot_us = sum(kb.values())
-            ach = 8.0 * S / (tot_us * 1e-6) / 1e9
-            dom = max(kb, key=kb.get)
-            # algorithmic passes over the tensor each launch stands for (fwd 3S, bwd 5S)
-            passes = {'stats': 1, 'apply': 2, 'backward_reduce': 2, 'backward_apply': 3,
-                      'forward_fused': 3, 'backward_fused': 5}
-            ach_dom = passes[dom] * S / (kb[dom] * 1e-6) / 1e9
-            sb['roofline'] = {'bound': 'hbm', 'achieved': ach_dom, 'peak': pk['hbm'], 'unit': 'GB/s',
-                              'frac': ach_dom / pk['hbm'],
-                              'traffic': profiled_traffic('bn_bwd_fused' if dom == 'backward_fused' else
-                                                          'bn_fwd_fused' if dom == 'forward_fused' else 'bn_' + dom),
-                              'kernel': 'bn_' + dom,
-                              'peak_source': pk['src'], 'algorithmic_bytes_per_launch': passes[dom] * S,
-                              'all_kernels_sum': {'achieved': ach, 'frac': ach / pk['hbm'], 'us': tot_us},
-                              'kernel_us': kb}
+            sb['roofline']['kernel_us'] = kb
+            sb['roofline']['kernel_us_note'] = 'event-bracketed isolated launches (include launch gaps)'
+        parb = bn_parity(world, rank)
+        if rank == 0:
+            sb['parity'] = parb
+        if not args.no_gpu_baseline:
+            gb = gpu_bn_baseline(world)
+            if rank == 0:
+                sb['gpu_baseline'] = gb
+                sb['gpu_baseline']['ours_over_gpu_baseline'] = gbs / gb['value']
         if 'metric' in out:
             out['syncbn'] = sb
         else:

@@ -62,6 +62,10 @@ const char* scb_last_error(void);
 int scb_version(void);
 /* compute capability of the current device as major*10+minor (100 on B200), negative on error */
 int scb_device_cc(void);
+/* id of the CUDA-graph capture `stream` is part of (0: not capturing, negative: error).  The host side of the
+ * peer-memory exchanges uses it to restart its buffer rotation at every capture, so that a replayed graph never
+ * re-uses a buffer its peers may still be reading (gather.py, sync_batchnorm.py) */
+int64_t scb_stream_capture_id(void* stream);
 /* number of kernels this library has launched in this process so far (bench bookkeeping) */
 int64_t scb_launch_count(void);
 /* diagnostics only, effective in builds with -DSCB_TRACE=1 (tools/build_trace_lib.sh): a device buffer of

@@ -110,6 +110,7 @@ PROTOTYPES = {
     'scb_version': (_i, []),
     'scb_device_cc': (_i, []),
     'scb_launch_count': (_i64, []),
+    'scb_stream_capture_id': (_i64, [_vp]),
     'scb_debug_set_trace': (_i, [_vp]),
     'scb_debug_set_events': (_i, [_vp, _vp]),
     'scb_supcon_prep': (_i, [_vp, _i, _i, _i, _i, _i64, _i64, _i, _f, _vp, _vp, _i, _i, _vp, _vp]),

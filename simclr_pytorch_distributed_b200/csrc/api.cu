@@ -116,6 +116,13 @@ extern "C" int scb_debug_set_events(void* start, void* stop) {
     return SCB_OK;
 }
 
+extern "C" int64_t scb_stream_capture_id(void* stream_) {
+    cudaStreamCaptureStatus status = cudaStreamCaptureStatusNone;
+    unsigned long long id = 0;
+    if (cudaStreamGetCaptureInfo((cudaStream_t)stream_, &status, &id) != cudaSuccess) { cudaGetLastError(); return -1; }
+    return status == cudaStreamCaptureStatusActive ? (int64_t)id : 0;
+}
+
 extern "C" int scb_device_cc(void) {
     int dev = 0, major = 0, minor = 0;
     SCB_CUDA_OK(cudaGetDevice(&dev));

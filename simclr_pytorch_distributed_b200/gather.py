@@ -114,6 +114,7 @@ class _PeerExchange:
                 pair.append(ch)
             self.channels.append(pair)
         self.calls = 0
+        self.capture_id, self.capture_calls = 0, 0
         esz = kb.element_size()
         self.k_seg = (ctypes.c_int64 * 3)(0, rank * rows * ldk * esz, rows * ldk * esz)
         self.st_seg = (ctypes.c_int64 * 9)(0, rank * rows * 4, rows * 4,
@@ -137,10 +138,28 @@ class _PeerExchange:
                 return None
         return cls._cache[key]
 
-    def next_generation(self):
+    def next_generation(self, lib, dev):
+        """Buffer generation of the next forward, and whether the first exchange must be preceded by a barrier.
+
+        Eager calls rotate through the generations.  Inside a CUDA-graph capture the choice is baked into the graph
+        and replays repeat it, so the rotation restarts at every capture (all ranks capture alike) and the first
+        exchange of the graph waits for every rank to have finished whatever ran before: the seam between two
+        replays -- or between eager steps and a replay -- can then never hand a rank a buffer that a peer is
+        still reading, whatever the number of steps in the graph."""
+        cap = lib.scb_stream_capture_id(L._stream(dev)) if dev.type == 'cuda' else 0
+        pre_barrier = False
+        if cap > 0:
+            if cap != self.capture_id:
+                self.capture_id, self.capture_calls, pre_barrier = cap, 0, True
+            g = self.capture_calls % self.GENERATIONS
+            self.capture_calls += 1
+            self.calls += 1
+            return g, self.calls, pre_barrier
+        if self.capture_id != 0:           # first eager call after replays of a captured graph
+            self.capture_id, pre_barrier = 0, True
         g = self.calls % self.GENERATIONS
         self.calls += 1
-        return g, self.calls
+        return g, self.calls, pre_barrier
 
     def check_alive(self, call_index):
         if self.calls - call_index >= self.GENERATIONS:
@@ -177,7 +196,9 @@ class _DistSupConFunction(torch.autograd.Function):
         inv_norm = torch.empty(rows, dtype=torch.float32, device=dev) if normalize else None
         px = (_PeerExchange.get(group, dev, n_k, ldk, plan.k_torch, rows, world, plan.seg_index)
               if ops.requires_cuda else None)
-        gen, call_index = px.next_generation() if px is not None else (0, 0)
+        gen, call_index, pre_barrier = px.next_generation(lib, dev) if px is not None else (0, 0, False)
+        if pre_barrier:
+            px.handles[gen][0].barrier(channel=0)
         fused = px is not None and os.environ.get('SCB_P2P', '1') == 'fused'
         possum = torch.empty(rows, dtype=torch.float32, device=dev)
         if fused:
@@ -206,12 +227,16 @@ class _DistSupConFunction(torch.autograd.Function):
             return L.typed_loss(loss2, feats.dtype)
         # bf16 features that need no normalisation are this rank's rows already (sample-major order inside the
         # segment, include/simclr_b200.h): no stacking copy, the exchange reads them where they are
+        # The choice (and with it the row order of every segment of the gathered matrix) depends only on things that
+        # are the same on every rank; a rank whose tensor is strided or misaligned copies it, keeping the order.
         zero_copy = (ops.requires_cuda and plan.engine == _lib.ENGINE_BF16 and feats.dtype == torch.bfloat16 and
-                     not normalize and plan.mode == _lib.MODE_ALL and feats.is_contiguous() and plan.dim == ldk and
-                     feats.data_ptr() % 16 == 0)
+                     not normalize and plan.mode == _lib.MODE_ALL and plan.dim == ldk)
         if zero_copy:
             plan.row_layout = _lib.ROWS_SAMPLE_MAJOR
-            k_local = feats.detach().view(rows, ldk)
+            src = feats.detach()
+            if not src.is_contiguous() or src.data_ptr() % 16 != 0:
+                src = src.contiguous().clone()
+            k_local = src.view(rows, ldk)
         else:
             k_local = torch.empty((rows, ldk), dtype=plan.k_torch, device=dev)
             ops.prep(lib, feats, plan, normalize, k_local, None, inv_norm)

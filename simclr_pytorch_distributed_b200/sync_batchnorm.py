@@ -191,6 +191,7 @@ class _PeerStats:
             self.ptrs.append((ctypes.c_void_p * world)(*[int(p) for p in h.buffer_ptrs]))
         self.seg = (ctypes.c_int64 * 3)(0, rank * n * 4, n * 4)
         self.calls = 0
+        self.capture_id, self.capture_calls = 0, 0
         self.rank = rank
 
     @classmethod
@@ -214,8 +215,23 @@ class _PeerStats:
     def all_gather(self, src, dev):
         """src: n floats of this rank -> [world * n] floats, rank-major (valid until GENERATIONS-1 further calls)."""
         lib = _lib.load()
-        g = self.calls % self.GENERATIONS
+        # Buffer rotation: eager calls walk through the generations.  A CUDA-graph capture bakes the choice in, so the
+        # rotation restarts at every capture and the first exchange of a graph (and the first eager one after replays)
+        # is preceded by a barrier: no replay seam can hand a rank a buffer that a peer is still reading.
+        cap = lib.scb_stream_capture_id(_Kernels.stream(dev))
+        pre_barrier = False
+        if cap > 0:
+            if cap != self.capture_id:
+                self.capture_id, self.capture_calls, pre_barrier = cap, 0, True
+            g = self.capture_calls % self.GENERATIONS
+            self.capture_calls += 1
+        else:
+            if self.capture_id != 0:
+                self.capture_id, pre_barrier = 0, True
+            g = self.calls % self.GENERATIONS
         self.calls += 1
+        if pre_barrier:
+            self.handles[g].barrier(channel=0)
         _lib.check(lib.scb_peer_bcast(src.data_ptr(), self.seg, 1, self.ptrs[g], self.world,
                                       _Kernels.stream(dev)), 'scb_peer_bcast')
         self.handles[g].barrier(channel=0)

@@ -118,6 +118,69 @@ def _worker(rank, world, port, q):
                    np.linalg.norm(g_hat[sl].ravel()))
             notes.append('loss bf16 in place, p2p=%s: rel loss %.2e rel grad %.2e' % (p2p, e_l, e_g))
             ok = ok and e_l <= 2e-3 and e_g <= 2 * (2e-3 + 2 ** -8)
+        # ---------------- a ONE-step CUDA graph of the sharded loss and of SyncBatchNorm, replayed 8 times on fresh
+        # data: the buffer rotation of the peer-memory exchanges is baked into the graph, every replay re-uses the
+        # same generation, and must still never overwrite rows / statistics a peer is reading
+        os.environ['SCB_P2P'] = '1'
+        zs = torch.zeros(bsz, V, D, dtype=torch.bfloat16, device=dev).requires_grad_(True)
+        xs = torch.zeros(32, 64, 8, 8, dtype=torch.bfloat16, device=dev).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+        dys = torch.zeros(32, 64, 8, 8, dtype=torch.bfloat16, device=dev).contiguous(memory_format=torch.channels_last)
+        crit = DistributedSupConLoss(temperature=0.5, engine='bf16', normalize=False)
+        bn = SyncBatchNorm(64).to(dev)
+        ref_bn = torch.nn.SyncBatchNorm(64).to(dev)
+        ref_bn.load_state_dict(bn.state_dict())
+
+        def fill(step):
+            rng = np.random.default_rng(1000 + step)
+            zh = torch.from_numpy(normalize_rows(rng.standard_normal((world * bsz, V, D)))).to(torch.bfloat16)
+            gx = torch.Generator().manual_seed(5000 + 10 * step + rank)
+            with torch.no_grad():
+                zs.copy_(zh[rank * bsz:(rank + 1) * bsz])
+                xs.copy_((torch.randn(32, 64, 8, 8, generator=gx) * 1.5 + rank).to(torch.bfloat16))
+                dys.copy_(torch.randn(32, 64, 8, 8, generator=gx).to(torch.bfloat16))
+            return zh
+
+        def one_step():
+            zs.grad = None
+            xs.grad = None
+            loss = crit(zs)
+            loss.backward()
+            y = bn(xs)
+            y.backward(dys)
+            return loss, y
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for w in range(3):                      # eager warm-up (sets up the peer buffers); keep the reference in step
+                fill(w)
+                one_step()
+                xr = xs.detach().clone().requires_grad_(True)
+                ref_bn(xr).backward(dys)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        fill(3)
+        with torch.cuda.graph(graph):
+            g_loss, g_y = one_step()
+        e_l = e_g = e_y = e_x = 0.0
+        for step in range(4, 12):
+            zh = fill(step)
+            graph.replay()
+            torch.cuda.synchronize()
+            ref_loss, g_hat, _ = supcon_forward_backward(zh.double().numpy(), temperature=0.5)
+            sl = slice(rank * bsz, (rank + 1) * bsz)
+            e_l = max(e_l, abs(float(g_loss) - ref_loss) / abs(ref_loss))
+            e_g = max(e_g, np.linalg.norm((zs.grad.double().cpu().numpy() - g_hat[sl]).ravel()) / np.linalg.norm(g_hat[sl].ravel()))
+            xr = xs.detach().clone().requires_grad_(True)
+            yr = ref_bn(xr)
+            yr.backward(dys)
+            e_y = max(e_y, ((g_y.float() - yr.float()).abs() / (yr.float().abs() + 1)).max().item())
+            e_x = max(e_x, ((xs.grad.float() - xr.grad.float()).abs() / (xr.grad.float().abs() + 1)).max().item())
+        notes.append('one-step graph x8: loss %.2e grad %.2e bn y %.2e dx %.2e rv %.2e' % (
+            e_l, e_g, e_y, e_x, (bn.running_var - ref_bn.running_var).abs().max().item()))
+        ok = ok and e_l <= 2e-3 and e_g <= 2 * (2e-3 + 2 ** -8) and e_y <= 2.0 ** -7 and e_x <= 2.0 ** -7
+        ok = ok and (bn.running_var - ref_bn.running_var).abs().max().item() <= 1e-4
     except Exception as e:     # report instead of hanging the other ranks
         ok = False
         notes.append('EXC %r' % (e,))
