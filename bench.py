@@ -546,6 +546,113 @@ def gpu_bn_baseline(world, steps=20, pool=12):
     return {'ms_per_step': ms, 'value': 8.0 * S / (ms * 1e-3) / 1e9, 'unit': 'GB/s per GPU', 'what': what}
 
 
+# ----------------------------------------------------------------------------- configs[2]: the model-level step
+def run_model(args, world, rank):
+    """BASELINE configs[2]: SimCLR ResNet-50 + MLP head (tests/carrier_resnet.py restates networks/resnet_big.py),
+    CIFAR-shape synthetic crops, per-GPU batch 256 (two crops -> 512 images), bf16 channels_last, DDP when N > 1.
+    One step = forward, loss, backward, SGD update -- /root/reference/main_supcon.py:266-325.  Three arms on the same
+    data: this library swapped in as the reference does it (`convert_sync_batchnorm` + the loss module), the same with
+    ReLU / add+ReLU folded into the batch-norm kernels, and the stock path (torch.nn.SyncBatchNorm / BatchNorm2d +
+    all-gather + the dense loss on every rank)."""
+    import copy
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, 'tests'))
+    from carrier_resnet import SupConResNet50
+    from oracle.dense_port import dense_supcon_loss
+    from simclr_pytorch_distributed_b200 import SupConLoss, SyncBatchNorm
+    from simclr_pytorch_distributed_b200.gather import DistributedSupConLoss
+    bsz = 256
+    dev = torch.device('cuda')
+    torch.manual_seed(0)
+    base = SupConResNet50().to(dev).to(memory_format=torch.channels_last).to(torch.bfloat16)
+    g = torch.Generator().manual_seed(2024 + rank)
+    pool = [torch.randn(2 * bsz, 3, 32, 32, generator=g).to(torch.bfloat16).cuda().contiguous(
+        memory_format=torch.channels_last) for _ in range(4)]
+
+    def wrap(m):
+        return torch.nn.parallel.DistributedDataParallel(m, device_ids=[dev.index]) if world > 1 else m
+
+    def make(arm):
+        if arm == 'stock':
+            m = copy.deepcopy(base)
+            if world > 1:
+                m = torch.nn.SyncBatchNorm.convert_sync_batchnorm(m)
+
+            def crit(feats):                       # main_supcon.py:268-290: gather, re-insert the local slice, dense loss
+                if world > 1:
+                    parts = [torch.empty_like(feats) for _ in range(world)]
+                    dist.all_gather(parts, feats.detach())
+                    parts[rank] = feats
+                    f1 = torch.cat([p[:bsz] for p in parts])
+                    f2 = torch.cat([p[bsz:] for p in parts])
+                else:
+                    f1, f2 = feats[:bsz], feats[bsz:]
+                return dense_supcon_loss(torch.cat([f1.unsqueeze(1), f2.unsqueeze(1)], 1).float(), temperature=TEMP)
+            normalize_in_model = True
+        else:
+            if arm == 'ours_fused':
+                m = SupConResNet50(bn=SyncBatchNorm, fuse=True).to(dev).to(memory_format=torch.channels_last).to(torch.bfloat16)
+                m.load_state_dict(base.state_dict())
+            else:
+                m = SyncBatchNorm.convert_sync_batchnorm(copy.deepcopy(base))
+            loss_mod = (DistributedSupConLoss(temperature=TEMP, normalize=True) if world > 1
+                        else SupConLoss(temperature=TEMP, normalize=True))
+
+            def crit(feats):                       # the fused normalise replaces main_supcon.py:283
+                return loss_mod(torch.stack([feats[:bsz], feats[bsz:]], 1))
+            normalize_in_model = False
+        m = wrap(m)
+        opt = torch.optim.SGD(m.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+
+        def step(i):
+            feats = m(pool[i % len(pool)], normalize=normalize_in_model)
+            loss = crit(feats)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+            return loss
+        return step
+
+    def bn_share(step):
+        try:
+            from torch.profiler import profile, ProfilerActivity
+            with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                for i in range(2):
+                    step(i)
+                torch.cuda.synchronize()
+            tot = bn = 0.0
+            for ev in prof.key_averages():
+                t = getattr(ev, 'device_time_total', None) or getattr(ev, 'cuda_time_total', 0.0)
+                tot += t
+                if 'bn_' in ev.key or 'batch_norm' in ev.key:
+                    bn += t
+            return bn / tot if tot > 0 else None
+        except Exception as e:      # say so
+            return 'profiler unavailable: %s' % type(e).__name__
+
+    res = {}
+    for arm in ('stock', 'ours_swap', 'ours_fused'):
+        step = make(arm)
+        ms, _ = time_steps(step, min(args.steps, 20), max(3, min(args.warmup, 5)), world)
+        per = ms / min(args.steps, 20)
+        res[arm] = {'ms_per_step': per, 'images_per_s': 2 * bsz * world / (per * 1e-3),
+                    'batch_norm_share_of_gpu_time': bn_share(step), 'loss_after': float(step(0))}
+        del step
+        torch.cuda.empty_cache()
+    if rank == 0:
+        print(json.dumps({
+            'metric': 'SimCLR ResNet-50 training step, images/s', 'unit': 'images/s', 'n_gpus': world,
+            'value': res['ours_fused']['images_per_s'], 'ms_per_step': res['ours_fused']['ms_per_step'],
+            'higher_is_better': True, 'scaling': 'weak', 'data': 'synthetic', 'dtype': 'bf16', 'vs_baseline': None,
+            'config': {'workload': 'SimCLR ResNet-50 + MLP head, 32x32 crops, per-GPU batch 256 (512 images), bf16 '
+                                   'channels_last, fwd + loss + bwd + SGD' + (', DDP' if world > 1 else ''),
+                       'launch': 'eager'},
+            'arms': res,
+            'speedup_over_stock': {k: res['stock']['ms_per_step'] / res[k]['ms_per_step'] for k in ('ours_swap', 'ours_fused')},
+        }), flush=True)
+
+
 # ----------------------------------------------------------------------------- CPU baselines
 def cpu_loss_baseline(budget_s=15.0, max_steps=20):
     """The reference's dense CPU algorithm (oracle/dense_port.py, a port: /root/reference does not
@@ -643,7 +750,7 @@ def main():
     ap.add_argument('--steps', type=int, default=200)
     ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--workload', default='both', choices=['both', 'ntxent', 'syncbn', 'syncbn-census'])
+    ap.add_argument('--workload', default='both', choices=['both', 'ntxent', 'syncbn', 'syncbn-census', 'model'])
     ap.add_argument('--engine', default=os.environ.get('SIMCLR_B200_BENCH_ENGINE', 'bf16'))
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-gpu-baseline', action='store_true')
@@ -671,6 +778,12 @@ def main():
     t_load0 = time.time()
     out = {}
 
+    if args.workload == 'model':
+        run_model(args, world, rank)
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+        return
     # ------------------------------------------------ SyncBN over the layer shapes of the reference ResNet-50
     if args.workload == 'syncbn-census':
         import importlib.util
