@@ -343,6 +343,255 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
     }
 }
 
+// =================================================================== streaming cluster kernels
+// Same ownership (a cluster owns a channel slab end to end, sums meet over distributed shared memory), but the rows
+// are STREAMED twice instead of being held in registers: pass 1 accumulates the sums, pass 2 walks the same rows
+// back to front (what pass 1 touched last is what the L2 still holds) and writes the result.  No capacity limit, so
+// the geometry is free: the slabs may be uneven (C / 8 columns split over 7 clusters of 16 CTAs on a B200, the most
+// it holds at once), which keeps the pieces of a row wide (64..80 bytes at C = 256) and one wave resident.
+// Used for tensors that fit the L2 (the second pass then costs no DRAM traffic).
+struct ClStream {
+    int S;               // slabs = clusters
+    int CS;              // CTAs per cluster
+    int TX;              // threads across a slab row (power of two, >= widest slab in 16-byte vectors, <= 32)
+    int cv;              // 16-byte vectors per row (C / VEC)
+    int64_t rows_per_cta;
+};
+constexpr int kStreamU = 4;      // rows in flight per thread and tensor
+
+template <typename T, bool kAdd>
+__global__ void __launch_bounds__(kClThreads, 1)
+bn_fwd_stream_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __restrict__ y, int64_t M, int C,
+                     const ClStream g, const float* __restrict__ weight, const float* __restrict__ bias,
+                     float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                     float* save_invstd, float* save_count, int flags) {
+    constexpr int VEC = Vec16<T>::N;
+    extern __shared__ float smf[];
+    const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
+    float* sm = smf;
+    float* gath = sm + (kClThreads / 32) * 2 * CW;
+    float* ab = gath + kClMaxCS * 2 * CW;
+    const uint32_t rank = (CS > 1) ? cl_ctarank() : 0u;
+    const int slab = blockIdx.x / CS;
+    const int v_lo = (int)(((int64_t)slab * g.cv) / g.S), v_hi = (int)(((int64_t)(slab + 1) * g.cv) / g.S);
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const bool active = tx < v_hi - v_lo;
+    const int c0 = (v_lo + (active ? tx : 0)) * VEC;
+    const int64_t r_begin = (int64_t)rank * g.rows_per_cta;
+    const int64_t r_end = min(M, r_begin + g.rows_per_cta);
+    float s1[VEC], s2[VEC], k0[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
+    load_row_vec_cached<T, VEC>(x + c0, k0);                    // common shift K_c = x[0, c]
+    if (active) {
+        for (int64_t rk = r_begin + ty; rk < r_end; rk += (int64_t)kStreamU * TY) {
+            uint4 raw[kStreamU];
+#pragma unroll
+            for (int u = 0; u < kStreamU; ++u)
+                if (rk + (int64_t)u * TY < r_end) raw[u] = ldg_stream16(x + (rk + (int64_t)u * TY) * C + c0);
+#pragma unroll
+            for (int u = 0; u < kStreamU; ++u) {
+                if (rk + (int64_t)u * TY < r_end) {
+                    const T* e = reinterpret_cast<const T*>(&raw[u]);
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) {
+                        const float d = to_f32(e[i]) - k0[i];
+                        s1[i] += d;
+                        s2[i] = fmaf(d, d, s2[i]);
+                    }
+                }
+            }
+        }
+    }
+    const float tot = cluster_channel_sums<VEC>(s1, s2, sm, gath, TX, CS, rank);
+    if ((int)threadIdx.x < 2 * CW) ab[threadIdx.x] = tot;
+    __syncthreads();
+    const float n = (float)M;
+    float av = 0.f, bv = 0.f;
+    if ((int)threadIdx.x < CW && (int)threadIdx.x < (v_hi - v_lo) * VEC) {
+        const int c = v_lo * VEC + threadIdx.x;
+        const float S1 = ab[threadIdx.x], S2 = ab[CW + threadIdx.x];
+        const float mean = to_f32(x[c]) + S1 / n;
+        const float m2 = fmaxf(S2 - S1 * S1 / n, 0.f);
+        const float invstd = rsqrtf(m2 / n + eps);
+        av = (weight ? weight[c] : 1.f) * invstd;
+        bv = (bias ? bias[c] : 0.f) - mean * av;
+        if (rank == 0) {
+            if (save_mean) save_mean[c] = mean;
+            if (save_invstd) save_invstd[c] = invstd;
+            if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+            if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+            if (c == 0 && save_count) save_count[0] = n;
+        }
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < CW) { ab[threadIdx.x] = av; ab[CW + threadIdx.x] = bv; }
+    __syncthreads();
+    if (!active) return;
+    float a[VEC], b[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { a[i] = ab[tx * VEC + i]; b[i] = ab[CW + tx * VEC + i]; }
+    const bool relu = (flags & SCB_BN_RELU) != 0;
+    const int64_t chunk = (int64_t)kStreamU * TY;
+    for (int64_t k = (r_end - r_begin + chunk - 1) / chunk - 1; k >= 0; --k) {
+        const int64_t rk = r_begin + k * chunk + ty;
+        uint4 raw[kStreamU], rz[kStreamU];
+#pragma unroll
+        for (int u = 0; u < kStreamU; ++u) {
+            const int64_t r = rk + (int64_t)u * TY;
+            if (r < r_end) {
+                raw[u] = ldg_stream16(x + r * C + c0);
+                if (kAdd) rz[u] = ldg_stream16(z + r * C + c0);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kStreamU; ++u) {
+            const int64_t r = rk + (int64_t)u * TY;
+            if (r < r_end) {
+                const T* e = reinterpret_cast<const T*>(&raw[u]);
+                const T* ez = reinterpret_cast<const T*>(&rz[u]);
+                uint4 o;
+                T* oe = reinterpret_cast<T*>(&o);
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    float v = fmaf(to_f32(e[i]), a[i], b[i]);
+                    if (kAdd) v += to_f32(ez[i]);
+                    oe[i] = from_f32<T>(relu ? fmaxf(v, 0.f) : v);
+                }
+                stg_stream16(y + r * C + c0, o);
+            }
+        }
+    }
+}
+
+template <typename T, int kGate>
+__global__ void __launch_bounds__(kClThreads, 1)
+bn_bwd_stream_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yout,
+                     T* __restrict__ dx, T* __restrict__ dz, int64_t M, int C, const ClStream g,
+                     const float* __restrict__ mean, const float* __restrict__ invstd,
+                     const float* __restrict__ weight, const float* __restrict__ bias,
+                     const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias) {
+    constexpr int VEC = Vec16<T>::N;
+    extern __shared__ float smf[];
+    const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
+    float* sm = smf;
+    float* gath = sm + (kClThreads / 32) * 2 * CW;
+    float* ab = gath + kClMaxCS * 2 * CW;
+    const uint32_t rank = (CS > 1) ? cl_ctarank() : 0u;
+    const int slab = blockIdx.x / CS;
+    const int v_lo = (int)(((int64_t)slab * g.cv) / g.S), v_hi = (int)(((int64_t)(slab + 1) * g.cv) / g.S);
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const bool active = tx < v_hi - v_lo;
+    const int c0 = (v_lo + (active ? tx : 0)) * VEC;
+    const int64_t r_begin = (int64_t)rank * g.rows_per_cta;
+    const int64_t r_end = min(M, r_begin + g.rows_per_cta);
+    float s1[VEC], s2[VEC], mu[VEC], k1[VEC], bb[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        s1[i] = 0.f; s2[i] = 0.f;
+        mu[i] = mean[c0 + i];
+        k1[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
+        bb[i] = (kGate == 1 && bias) ? bias[c0 + i] : 0.f;
+    }
+    if (active) {
+        for (int64_t rk = r_begin + ty; rk < r_end; rk += (int64_t)kStreamU * TY) {
+            uint4 rx[kStreamU], rd[kStreamU], ry[kStreamU];
+#pragma unroll
+            for (int u = 0; u < kStreamU; ++u) {
+                const int64_t r = rk + (int64_t)u * TY;
+                if (r < r_end) {
+                    rx[u] = ldg_stream16(x + r * C + c0);
+                    rd[u] = ldg_stream16(dy + r * C + c0);
+                    if (kGate == 2) ry[u] = ldg_stream16(yout + r * C + c0);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kStreamU; ++u) {
+                if (rk + (int64_t)u * TY < r_end) {
+                    const T* ex = reinterpret_cast<const T*>(&rx[u]);
+                    const T* ed = reinterpret_cast<const T*>(&rd[u]);
+                    const T* ey = reinterpret_cast<const T*>(&ry[u]);
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) {
+                        const float xm = to_f32(ex[i]) - mu[i];
+                        float gv = to_f32(ed[i]);
+                        if (kGate == 1 && !(fmaf(xm, k1[i], bb[i]) > 0.f)) gv = 0.f;
+                        if (kGate == 2 && !(to_f32(ey[i]) > 0.f)) gv = 0.f;
+                        s1[i] += gv;
+                        s2[i] = fmaf(gv, xm, s2[i]);
+                    }
+                }
+            }
+        }
+    }
+    const float tot = cluster_channel_sums<VEC>(s1, s2, sm, gath, TX, CS, rank);
+    if ((int)threadIdx.x < 2 * CW) ab[threadIdx.x] = tot;
+    __syncthreads();
+    float v2 = 0.f, v3 = 0.f;
+    if ((int)threadIdx.x < CW && (int)threadIdx.x < (v_hi - v_lo) * VEC) {
+        const int c = v_lo * VEC + threadIdx.x;
+        const float sd = ab[threadIdx.x], sx = ab[CW + threadIdx.x];
+        const float is = invstd[c];
+        const float inv_n = 1.f / n_total[0];
+        v2 = sd * inv_n;
+        v3 = is * is * sx * inv_n;
+        if (rank == 0) {
+            if (out_sums) { out_sums[c] = sd; out_sums[C + c] = sx; }
+            if (grad_weight) grad_weight[c] = sx * is;
+            if (grad_bias) grad_bias[c] = sd;
+        }
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < CW) { ab[threadIdx.x] = v2; ab[CW + threadIdx.x] = v3; }
+    __syncthreads();
+    if (!active) return;
+    float cB[VEC], cD[VEC];                                    // dx = g k1 + x B + D  (see bn_bwd_cluster_kernel)
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        const float k2 = ab[tx * VEC + i], k3 = ab[CW + tx * VEC + i];
+        cB[i] = -k3 * k1[i];
+        cD[i] = (mu[i] * k3 - k2) * k1[i];
+    }
+    const int64_t chunk = (int64_t)kStreamU * TY;
+    for (int64_t k = (r_end - r_begin + chunk - 1) / chunk - 1; k >= 0; --k) {
+        const int64_t rk = r_begin + k * chunk + ty;
+        uint4 rx[kStreamU], rd[kStreamU], ry[kStreamU];
+#pragma unroll
+        for (int u = 0; u < kStreamU; ++u) {
+            const int64_t r = rk + (int64_t)u * TY;
+            if (r < r_end) {
+                rx[u] = ldg_stream16(x + r * C + c0);
+                rd[u] = ldg_stream16(dy + r * C + c0);
+                if (kGate == 2) ry[u] = ldg_stream16(yout + r * C + c0);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kStreamU; ++u) {
+            const int64_t r = rk + (int64_t)u * TY;
+            if (r < r_end) {
+                const T* ex = reinterpret_cast<const T*>(&rx[u]);
+                const T* ed = reinterpret_cast<const T*>(&rd[u]);
+                const T* ey = reinterpret_cast<const T*>(&ry[u]);
+                uint4 o, oz;
+                T* oe = reinterpret_cast<T*>(&o);
+                T* oze = reinterpret_cast<T*>(&oz);
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float xv = to_f32(ex[i]);
+                    bool off = false;
+                    if (kGate == 1) off = !(fmaf(xv - mu[i], k1[i], bb[i]) > 0.f);
+                    if (kGate == 2) off = !(to_f32(ey[i]) > 0.f);
+                    const float gv = off ? 0.f : to_f32(ed[i]);
+                    oe[i] = from_f32<T>(fmaf(xv, cB[i], fmaf(gv, k1[i], cD[i])));
+                    if (kGate == 2) oze[i] = off ? from_f32<T>(0.f) : ed[i];
+                }
+                stg_stream16(dx + r * C + c0, o);
+                if (kGate == 2 && dz != nullptr) stg_stream16(dz + r * C + c0, oz);
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------ host side: geometry
 static bool cl_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
