@@ -17,6 +17,7 @@
 #include "common.cuh"
 
 #include <stdlib.h>
+#include <utility>
 
 namespace scb {
 
@@ -702,6 +703,57 @@ static bool cl_geom(int64_t M, int C, int es, int rows, ClGeom* out) {
     return found;
 }
 
+// Streaming kernels: as many clusters as the device holds at once, each owning an (uneven) slab of 16-byte columns.
+// Returns false when the row is too wide for 32 threads per slab row with the clusters available.
+static bool cl_stream_geom(int64_t M, int C, int es, ClStream* out) {
+    const int vec = 16 / es;
+    if (C % vec != 0 || M < 2) return false;
+    const int cv = C / vec;
+    bool found = false;
+    double best = 0.0;
+    for (int cs = cl_max_cs(); cs >= 1; cs >>= 1) {
+        int S = cl_max_active(cs);
+        if (S > cv) S = cv;
+        if (S < 1) continue;
+        const int wmax = (int)ceil_div(cv, S);
+        if (wmax > 32) continue;
+        int tx = 1;
+        while (tx < wmax) tx <<= 1;
+        const int64_t rpc = ceil_div(M, cs);
+        const int piece = (cv / S) * 16;                                    // bytes of a row one slab reads
+        const double cost = (double)rpc * tx * (piece >= 64 ? 1.0 : (piece >= 32 ? 1.25 : 2.0));
+        if (!found || cost < best) {
+            found = true; best = cost;
+            out->S = S; out->CS = cs; out->TX = tx; out->cv = cv; out->rows_per_cta = rpc;
+        }
+    }
+    return found;
+}
+
+// which single-launch implementation a tensor takes: 1 = rows held in registers, 2 = rows streamed twice (second
+// pass out of the L2), 0 = neither (too large: the multi-kernel path).  SCB_BN_FUSED_MODE=reg|stream forces one.
+static int cl_pick(int64_t M, int C, int es, int which, int flags) {
+    static const int forced = [] {
+        const char* e = getenv("SCB_BN_FUSED_MODE");
+        if (e == nullptr) return 0;
+        return e[0] == 'r' ? 1 : (e[0] == 's' ? 2 : 0);
+    }();
+    ClGeom g;
+    ClStream gs;
+    const bool add = (flags & SCB_BN_ADD) != 0;
+    const int rows = (which == 0 && !add) ? 2 * kClRows : kClRows;
+    const bool reg_ok = cl_geom(M, C, es, rows, &g);
+    const double bytes = (double)M * C * es;
+    // the second pass must come out of the L2: x (+ z) and y forward, x, dy (+ y) and dx backward
+    const double l2_budget = 96e6;
+    const double resident = which == 0 ? bytes * (add ? 3 : 2) : bytes * (((flags & SCB_BN_RELU) && add) ? 4 : 3);
+    const bool stream_ok = resident <= l2_budget && cl_stream_geom(M, C, es, &gs);
+    if (forced == 1) return reg_ok ? 1 : 0;
+    if (forced == 2) return stream_ok ? 2 : 0;
+    if (stream_ok) return 2;
+    return reg_ok ? 1 : 0;
+}
+
 template <typename... KArgs, typename... Args>
 static cudaError_t cl_launch(void (*kernel)(KArgs...), const ClGeom& g, size_t smem, cudaStream_t stream, Args&&... args) {
     cudaError_t e = set_max_dynamic_smem(kernel, (int)smem);
@@ -721,6 +773,14 @@ static cudaError_t cl_launch(void (*kernel)(KArgs...), const ClGeom& g, size_t s
     cfg.attrs = attr;
     cfg.numAttrs = g.CS > 1 ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+template <typename... KArgs, typename... Args>
+static cudaError_t cl_launch_stream(void (*kernel)(KArgs...), const ClStream& g, size_t smem, cudaStream_t stream,
+                                    Args&&... args) {
+    ClGeom gg;
+    gg.TX = g.TX; gg.CS = g.CS; gg.n_slabs = g.S; gg.rows_per_cta = g.rows_per_cta;
+    return cl_launch(kernel, gg, smem, stream, std::forward<Args>(args)...);
 }
 
 static int cl_check(const void* x, int dtype, int64_t rows, int channels) {
@@ -754,9 +814,7 @@ extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t oute
     if (!channels_last || channels <= 0) return 0;
     if (dtype != SCB_F32 && dtype != SCB_BF16 && dtype != SCB_F16) return 0;
     const int es = (dtype == SCB_F32) ? 4 : 2;
-    ClGeom g;
-    const int rows = (which == 0 && !(flags & SCB_BN_ADD)) ? 2 * kClRows : kClRows;
-    return cl_geom(outer * inner, channels, es, rows, &g) ? 1 : 0;
+    return cl_pick(outer * inner, channels, es, which, flags) != 0 ? 1 : 0;
 }
 
 #define SCB_CL_UNSUPPORTED(what)                                                             \
@@ -775,6 +833,25 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
     const int64_t M = rows;
     const int C = channels;
     if (!cl_aligned16(x) || !cl_aligned16(y) || (add && !cl_aligned16(z))) SCB_CL_UNSUPPORTED("bn_forward_fused");
+    const int pick = cl_pick(M, C, dtype == SCB_F32 ? 4 : 2, 0, flags);
+    if (pick == 0) SCB_CL_UNSUPPORTED("bn_forward_fused");
+    if (pick == 2) {
+        SCB_DISPATCH_FLOAT(dtype, T, {
+            constexpr int VEC = Vec16<T>::N;
+            ClStream g;
+            if (!cl_stream_geom(M, C, sizeof(T), &g)) SCB_CL_UNSUPPORTED("bn_forward_fused");
+            const size_t smem = cl_smem_bytes(g.TX, VEC);
+            const T* xp = (const T*)x; const T* zp = (const T*)z; T* yp = (T*)y;
+            if (add)
+                SCB_CUDA_OK(cl_launch_stream(bn_fwd_stream_kernel<T, true>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
+                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags));
+            else
+                SCB_CUDA_OK(cl_launch_stream(bn_fwd_stream_kernel<T, false>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
+                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags));
+        });
+        count_launch();
+        return SCB_OK;
+    }
     SCB_DISPATCH_FLOAT(dtype, T, {
         constexpr int VEC = Vec16<T>::N;
         ClGeom g;
@@ -838,6 +915,27 @@ static int bn_backward_cluster(const void* dy, const void* x, const void* y, voi
     if (!cl_aligned16(x) || !cl_aligned16(dy) || (dx && !cl_aligned16(dx)) || (gate == 2 && !cl_aligned16(y)) ||
         (dz && !cl_aligned16(dz)))
         SCB_CL_UNSUPPORTED("bn_backward_fused");
+    if (!reduce_only) {
+        const int pick = cl_pick(M, C, dtype == SCB_F32 ? 4 : 2, 1, flags);
+        if (pick == 0) SCB_CL_UNSUPPORTED("bn_backward_fused");
+        if (pick == 2) {
+            SCB_DISPATCH_FLOAT(dtype, T, {
+                constexpr int VEC = Vec16<T>::N;
+                ClStream g;
+                if (!cl_stream_geom(M, C, sizeof(T), &g)) SCB_CL_UNSUPPORTED("bn_backward_fused");
+                const size_t smem = cl_smem_bytes(g.TX, VEC);
+                const T* dyp = (const T*)dy; const T* xp = (const T*)x; const T* yp = (const T*)y;
+                T* dxp = (T*)dx; T* dzp = (T*)dz;
+                cudaError_t err;
+                if (gate == 2) err = cl_launch_stream(bn_bwd_stream_kernel<T, 2>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+                else if (gate == 1) err = cl_launch_stream(bn_bwd_stream_kernel<T, 1>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+                else err = cl_launch_stream(bn_bwd_stream_kernel<T, 0>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+                SCB_CUDA_OK(err);
+            });
+            count_launch();
+            return SCB_OK;
+        }
+    }
     SCB_DISPATCH_FLOAT(dtype, T, {
         ClGeom g;
         if (!cl_geom(M, C, sizeof(T), kClRows, &g)) SCB_CL_UNSUPPORTED("bn_backward_fused");

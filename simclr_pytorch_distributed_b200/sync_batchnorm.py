@@ -57,9 +57,12 @@ class _Kernels:
         lib = _lib.load()
         cl, outer, C, inner = geom
         if cls.fused_supported(x, geom, 0) and x.data_ptr() % 16 == 0:      # cluster reduction, no scratch
-            _lib.check(lib.scb_bn_stats_fused(x.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
-                                              out_stats.data_ptr(), cls.stream(x.device)), 'scb_bn_stats_fused')
-            return
+            rc = lib.scb_bn_stats_fused(x.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
+                                        out_stats.data_ptr(), cls.stream(x.device))
+            if rc == 0:
+                return
+            if rc != -3:
+                _lib.check(rc, 'scb_bn_stats_fused')
         ws = cls.workspace(lib, x.device, C)
         _lib.check(lib.scb_bn_stats(x.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C, inner,
                                     out_stats.data_ptr(), ws.data_ptr(), ws.numel(),
@@ -86,12 +89,14 @@ class _Kernels:
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
         if (cls.fused_supported(x, geom, 1, flags) and x.data_ptr() % 16 == 0 and dy.data_ptr() % 16 == 0 and
                 (yout is None or yout.data_ptr() % 16 == 0)):
-            _lib.check(lib.scb_bn_backward_reduce_fused(
+            rc = lib.scb_bn_backward_reduce_fused(
                 dy.data_ptr(), x.data_ptr(), p(yout), _lib.dtype_code(x.dtype), outer * inner, C,
                 saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), saved[2 * C:].data_ptr(),
-                sums.data_ptr(), p(grad_weight), p(grad_bias), flags, cls.stream(x.device)),
-                'scb_bn_backward_reduce_fused')
-            return
+                sums.data_ptr(), p(grad_weight), p(grad_bias), flags, cls.stream(x.device))
+            if rc == 0:
+                return
+            if rc != -3:
+                _lib.check(rc, 'scb_bn_backward_reduce_fused')
         ws = cls.workspace(lib, x.device, C)
         _lib.check(lib.scb_bn_backward_reduce(
             dy.data_ptr(), x.data_ptr(), p(yout), _lib.dtype_code(x.dtype), cl, outer, C, inner,
