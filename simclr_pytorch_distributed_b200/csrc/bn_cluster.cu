@@ -750,8 +750,11 @@ static int cl_pick(int64_t M, int C, int es, int which, int flags) {
     const bool stream_ok = resident <= l2_budget && cl_stream_geom(M, C, es, &gs);
     if (forced == 1) return reg_ok ? 1 : 0;
     if (forced == 2) return stream_ok ? 2 : 0;
-    if (stream_ok) return 2;
-    return reg_ok ? 1 : 0;
+    // measured on B200 (tools/time_bn.py, fwd+bwd in a CUDA graph): [256,256,8,8] bf16 registers 23.6 us / streamed
+    // 26.5 us, [512,512,4,4] 17.3 / 26.5 (the streamed passes issue their rows in four dependent batches), while
+    // [512,256,8,8], which only the streamed kernels take, gains over the multi-kernel path (43.4 us against 47.3)
+    if (reg_ok) return 1;
+    return stream_ok ? 2 : 0;
 }
 
 template <typename... KArgs, typename... Args>
