@@ -77,6 +77,7 @@ struct FinishParams {
 
 struct TcParams {
     const __nv_bfloat16* k;
+    const __nv_bfloat16* k_lo;          // SCB_ENGINE_BF16X3: low-order halves (k ~= k + k_lo), else nullptr
     int ldk, n_k, dim;
     int row_begin, n_rows, a_count;     // local rows; rows the forward treats as anchors
     int CT, RB, T, q;                   // column tiles, row blocks, tiles, tiles per CTA
@@ -285,16 +286,25 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
 }
 
 // =================================================================================== forward
-// smem: A[2][2*KCH*kSub] | B[2][KCH*kSub] | barriers | tmem slot | merge scratch
-template <int KCH, bool kLabels>
+// smem: A[NSA][A_BYTES] | B[NSB][B_BYTES] | barriers | tmem slot | merge scratch
+//
+// kX3 (SCB_ENGINE_BF16X3): every operand is a pair of bf16 matrices, k ~= hi + lo with lo = bf16(k - hi), and a tile
+// is three MMA groups into the same fp32 accumulator, S = hi hi^T + hi lo^T + lo hi^T (the lo lo^T term is below
+// 2^-16 of the result): fp32-class logits on the bf16 tensor-core path.  The staged tiles are twice as large, so A
+// and B are single-buffered (the tile's MMA time triples anyway).
+template <int KCH, bool kLabels, bool kX3>
 __global__ void __launch_bounds__(kTcThreads, 1)
-supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TcParams p) {
+supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_lo,
+                     const __grid_constant__ TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    constexpr int A_BYTES = 2 * KCH * kSub;
-    constexpr int B_BYTES = KCH * kSub;
-    constexpr int NSB = 2;
+    constexpr int A_PART = 2 * KCH * kSub;           // 256 rows of one bf16 matrix
+    constexpr int B_PART = KCH * kSub;
+    constexpr int A_BYTES = (kX3 ? 2 : 1) * A_PART;  // hi | lo
+    constexpr int B_BYTES = (kX3 ? 2 : 1) * B_PART;
+    constexpr int NSA = kX3 ? 1 : 2;
+    constexpr int NSB = kX3 ? 1 : 2;
     uint8_t* a_smem = smem;
-    uint8_t* b_smem = smem + 2 * A_BYTES;
+    uint8_t* b_smem = smem + NSA * A_BYTES;
     uint64_t* bars = reinterpret_cast<uint64_t*>(b_smem + NSB * B_BYTES);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
     double* s_red = reinterpret_cast<double*>(bars + 18);                  // [16] merge scratch
@@ -343,16 +353,20 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             const int rb = tau / p.CT, ct = tau - rb * p.CT;
             if (rb != cur_rb) {
                 cur_rb = rb;
-                const int buf = n_a & 1;
-                mbar_wait(a_empty(buf), ((n_a >> 1) & 1) ^ 1);
+                const int buf = n_a % NSA;
+                mbar_wait(a_empty(buf), ((n_a / NSA) & 1) ^ 1);
                 if (elect_one()) {
                     mbar_arrive_expect_tx(a_full(buf), A_BYTES);
 #pragma unroll
                     for (int h = 0; h < 2; ++h)
 #pragma unroll
-                        for (int kc = 0; kc < KCH; ++kc)
+                        for (int kc = 0; kc < KCH; ++kc) {
                             tma_load_2d(smem_u32(a_smem + buf * A_BYTES + (h * KCH + kc) * kSub), &tmap, kc * 64,
                                         p.row_begin + rb * kBM + h * kBMH, a_full(buf));
+                            if (kX3)
+                                tma_load_2d(smem_u32(a_smem + buf * A_BYTES + A_PART + (h * KCH + kc) * kSub), &tmap_lo,
+                                            kc * 64, p.row_begin + rb * kBM + h * kBMH, a_full(buf));
+                        }
                 }
                 __syncwarp();
                 ++n_a;
@@ -362,8 +376,12 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             if (elect_one()) {
                 mbar_arrive_expect_tx(b_full(st), B_BYTES);
 #pragma unroll
-                for (int kc = 0; kc < KCH; ++kc)
+                for (int kc = 0; kc < KCH; ++kc) {
                     tma_load_2d(smem_u32(b_smem + st * B_BYTES + kc * kSub), &tmap, kc * 64, ct * kBN, b_full(st));
+                    if (kX3)
+                        tma_load_2d(smem_u32(b_smem + st * B_BYTES + B_PART + kc * kSub), &tmap_lo, kc * 64, ct * kBN,
+                                    b_full(st));
+                }
             }
             __syncwarp();
             ++n_b;
@@ -380,8 +398,8 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                     __syncwarp();
                 }
                 cur_rb = rb;
-                abuf = n_a & 1;
-                mbar_wait(a_full(abuf), (n_a >> 1) & 1);
+                abuf = n_a % NSA;
+                mbar_wait(a_full(abuf), (n_a / NSA) & 1);
                 if (n_a == 0 && lane == 0) stamp(2);
                 ++n_a;
             }
@@ -400,10 +418,15 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                 const uint32_t a_lo = desc_lo(smem_u32(a_smem + abuf * A_BYTES + h * KCH * kSub), 16);
                 if (elect_one()) {
 #pragma unroll
-                    for (int k16 = 0; k16 < KCH * 4; ++k16) {
-                        const uint32_t off = ((k16 >> 2) * kSub + (k16 & 3) * 32) >> 4;
-                        if (k16 == 0) umma_bf16_lo<false>(d, a_lo + off, b_lo + off, idesc);
-                        else umma_bf16_lo<true>(d, a_lo + off, b_lo + off, idesc);
+                    for (int grp = 0; grp < (kX3 ? 3 : 1); ++grp) {       // hi hi^T, hi lo^T, lo hi^T
+                        const uint32_t ag = a_lo + ((grp == 2 ? A_PART : 0) >> 4);
+                        const uint32_t bg = b_lo + ((grp == 1 ? B_PART : 0) >> 4);
+#pragma unroll
+                        for (int k16 = 0; k16 < KCH * 4; ++k16) {
+                            const uint32_t off = ((k16 >> 2) * kSub + (k16 & 3) * 32) >> 4;
+                            if (grp == 0 && k16 == 0) umma_bf16_lo<false>(d, ag + off, bg + off, idesc);
+                            else umma_bf16_lo<true>(d, ag + off, bg + off, idesc);
+                        }
                     }
                     umma_commit(s_full(h, sbuf));
                     if (h == 1) umma_commit(b_empty(st));
@@ -445,8 +468,11 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                     const int v = p.map.view_of(gi);
                     for (int vv = 0; vv < p.n_views; ++vv)
                         if (vv != v)
-                            ps += bf16_dot_rows(p.k + (int64_t)gi * p.ldk,
-                                                p.k + (int64_t)p.map.sibling(gi, vv) * p.ldk, p.ldk);
+                        {
+                            const int64_t oi = (int64_t)gi * p.ldk, oj = (int64_t)p.map.sibling(gi, vv) * p.ldk;
+                            ps += bf16_dot_rows(p.k + oi, p.k + oj, p.ldk);
+                            if (kX3) ps += bf16_dot_rows(p.k + oi, p.k_lo + oj, p.ldk) + bf16_dot_rows(p.k_lo + oi, p.k + oj, p.ldk);
+                        }
                     ps *= p.inv_T;
                     np = (float)(p.n_views - 1);
                 }
@@ -666,6 +692,12 @@ __device__ __forceinline__ void positive_term(const TcParams& p, int gi, int d, 
             const float wgt = cpos * (ai + (p.map.is_anchor(j, p.mode) ? 1.f : 0.f));
             float kj[4];
             load_k4(p.k + (int64_t)j * p.ldk, d, kj);
+            if (p.k_lo != nullptr) {
+                float kl[4];
+                load_k4(p.k_lo + (int64_t)j * p.ldk, d, kl);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) kj[i] += kl[i];
+            }
 #pragma unroll
             for (int i = 0; i < 4; ++i) pos[i] = fmaf(wgt, kj[i], pos[i]);
         }
@@ -678,6 +710,12 @@ __device__ __forceinline__ void positive_term(const TcParams& p, int gi, int d, 
         const float4 sn = *reinterpret_cast<const float4*>(p.fin.cls_anc + (int64_t)rep * p.ldk + d);
         float ki[4];
         load_k4(p.k + (int64_t)gi * p.ldk, d, ki);
+        if (p.k_lo != nullptr) {
+            float kl[4];
+            load_k4(p.k_lo + (int64_t)gi * p.ldk, d, kl);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ki[i] += kl[i];
+        }
         pos[0] = -(nia_i * (sa.x - ki[0]) + c * (sn.x - ai * ki[0]));
         pos[1] = -(nia_i * (sa.y - ki[1]) + c * (sn.y - ai * ki[1]));
         pos[2] = -(nia_i * (sa.z - ki[2]) + c * (sn.z - ai * ki[2]));
@@ -868,6 +906,11 @@ __device__ __noinline__ void finish_staged(const TcParams& p, const float* own, 
                     load_k8(p.k + (int64_t)j * p.ldk, d, kj);
 #pragma unroll
                     for (int i = 0; i < 8; ++i) a[q][i] = fmaf(wgt, kj[i], a[q][i]);
+                    if (p.k_lo != nullptr) {                    // bf16x3: k = hi + lo
+                        load_k8(p.k_lo + (int64_t)j * p.ldk, d, kj);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) a[q][i] = fmaf(wgt, kj[i], a[q][i]);
+                    }
                 }
             } else if (p.mask_kind == SCB_MASK_LABELS) {
                 const int rep = p.rep_row[gi];
@@ -876,6 +919,12 @@ __device__ __noinline__ void finish_staged(const TcParams& p, const float* own, 
                 const float ai = (all || v_l == 0) ? 1.f : 0.f;
                 float ki[8], sa[8], sn[8];
                 load_k8(p.k + (int64_t)gi * p.ldk, d, ki);
+                if (p.k_lo != nullptr) {
+                    float kl[8];
+                    load_k8(p.k_lo + (int64_t)gi * p.ldk, d, kl);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) ki[i] += kl[i];
+                }
                 load8_typed(f.cls_all, SCB_F32, (int64_t)rep * p.ldk + d, sa);
                 load8_typed(f.cls_anc, SCB_F32, (int64_t)rep * p.ldk + d, sn);
 #pragma unroll
@@ -922,6 +971,23 @@ __device__ __forceinline__ void cluster_sync_all() {     // every thread of ever
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+// bf16x3: pv[off .. off+15] as bf16 hi (8 words at taddr) and bf16 lo = bf16(pv - hi) (8 words at taddr + 8)
+template <int N>
+__device__ __forceinline__ void store_p16_split(uint32_t taddr, const float (&pv)[N], int off) {
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float a = pv[off + 2 * i], b = pv[off + 2 * i + 1];
+        const __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
+        const float2 hf = __bfloat1622float2(h2);
+        const __nv_bfloat162 l2 = __floats2bfloat162_rn(a - hf.x, b - hf.y);
+        hi[i] = *reinterpret_cast<const uint32_t*>(&h2);
+        lo[i] = *reinterpret_cast<const uint32_t*>(&l2);
+    }
+    tmem_st8(taddr, hi);
+    tmem_st8(taddr + 8, lo);
+}
+
 // =================================================================================== backward
 // 18 warps: warp 0 = TMA producer + per-tile column factors, warp 1 = MMA issuer + TMEM owner,
 // warps 2..17 = four epilogue warpgroups.
@@ -950,13 +1016,19 @@ constexpr int kBMB = 128;       // rows per row block of the backward
 constexpr int kBwdThreads = 608;     // the forward's 18 warps + one more issuing warp
 constexpr int kBwdMma1Warp = 18;
 
-template <int KCH, bool kDirect>
+// kX3 (SCB_ENGINE_BF16X3): operands split into bf16 hi + lo (see the forward kernel).  S takes three MMA groups; P is
+// split the same way -- of every 16 columns a thread has read, the first 8 TMEM words get bf16(P), the next 8 get
+// bf16(P - bf16(P)) -- and dK += P_hi K_hi + P_hi K_lo + P_lo K_hi.  Tiles are twice as large: two B stages.
+template <int KCH, bool kDirect, bool kX3>
 __global__ void __launch_bounds__(kBwdThreads, 1)
-supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TcParams p) {
+supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_lo,
+                     const __grid_constant__ TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    constexpr int A_BYTES = KCH * kSub;
-    constexpr int B_BYTES = KCH * kSub;
-    constexpr int NSB = 5;
+    constexpr int A_PART = KCH * kSub;
+    constexpr int B_PART = KCH * kSub;
+    constexpr int A_BYTES = (kX3 ? 2 : 1) * A_PART;
+    constexpr int B_BYTES = (kX3 ? 2 : 1) * B_PART;
+    constexpr int NSB = kX3 ? 2 : 5;
     constexpr int NS = 3;                          // S buffers
     constexpr int ND = KCH * 64;                   // dK columns
     constexpr uint32_t kDkCol = 384;
@@ -1041,8 +1113,12 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                 if (elect_one()) {
                     mbar_arrive_expect_tx(a_full, A_BYTES);
 #pragma unroll
-                    for (int kc = 0; kc < KCH; ++kc)
+                    for (int kc = 0; kc < KCH; ++kc) {
                         tma_load_2d(smem_u32(a_smem + kc * kSub), &tmap, kc * 64, p.row_begin + rb * kBMB, a_full);
+                        if (kX3)
+                            tma_load_2d(smem_u32(a_smem + A_PART + kc * kSub), &tmap_lo, kc * 64, p.row_begin + rb * kBMB,
+                                        a_full);
+                    }
                 }
                 __syncwarp();
                 ++n_a;
@@ -1051,8 +1127,12 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             if (elect_one()) {
                 mbar_arrive_expect_tx(b_full(st), B_BYTES);
 #pragma unroll
-                for (int kc = 0; kc < KCH; ++kc)
+                for (int kc = 0; kc < KCH; ++kc) {
                     tma_load_2d(smem_u32(b_smem + st * B_BYTES + kc * kSub), &tmap, kc * 64, ct * kBN, b_full(st));
+                    if (kX3)
+                        tma_load_2d(smem_u32(b_smem + st * B_BYTES + B_PART + kc * kSub), &tmap_lo, kc * 64, ct * kBN,
+                                    b_full(st));
+                }
             }
             __syncwarp();
             // cj[c] = [anchor_j] 2^(m0 - l_j)  (1-exp path),  lj[c] = l_j or +inf  (2-exp path)
@@ -1106,10 +1186,15 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             const uint32_t b_lo = desc_lo(smem_u32(b_smem + st * B_BYTES), 16);
             if (elect_one()) {
 #pragma unroll
-                for (int k16 = 0; k16 < KCH * 4; ++k16) {
-                    const uint32_t off = ((k16 >> 2) * kSub + (k16 & 3) * 32) >> 4;
-                    if (k16 == 0) umma_bf16_lo<false>(d, a_lo + off, b_lo + off, idesc1);
-                    else umma_bf16_lo<true>(d, a_lo + off, b_lo + off, idesc1);
+                for (int grp = 0; grp < (kX3 ? 3 : 1); ++grp) {           // hi hi^T, hi lo^T, lo hi^T
+                    const uint32_t ag = a_lo + ((grp == 2 ? A_PART : 0) >> 4);
+                    const uint32_t bg = b_lo + ((grp == 1 ? B_PART : 0) >> 4);
+#pragma unroll
+                    for (int k16 = 0; k16 < KCH * 4; ++k16) {
+                        const uint32_t off = ((k16 >> 2) * kSub + (k16 & 3) * 32) >> 4;
+                        if (grp == 0 && k16 == 0) umma_bf16_lo<false>(d, ag + off, bg + off, idesc1);
+                        else umma_bf16_lo<true>(d, ag + off, bg + off, idesc1);
+                    }
                 }
                 umma_commit(s_full(buf));
                 if (last_of_rb) umma_commit(a_empty);
@@ -1136,10 +1221,23 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             if (elect_one()) {
                 // 16 columns of P = 8 TMEM words; the warpgroup of column half h keeps its 64 columns in words
                 // h*64 .. h*64+31
-                umma_bf16_ts_dyn(d, pa, b_lo, idesc2, first_of_rb ? 0u : 1u);
+                if (!kX3) {
+                    umma_bf16_ts_dyn(d, pa, b_lo, idesc2, first_of_rb ? 0u : 1u);
 #pragma unroll
-                for (int j16 = 1; j16 < 8; ++j16)
-                    umma_bf16_ts<true>(d, pa + (j16 >> 2) * 64 + (j16 & 3) * 8, b_lo + ((j16 * 2048) >> 4), idesc2);
+                    for (int j16 = 1; j16 < 8; ++j16)
+                        umma_bf16_ts<true>(d, pa + (j16 >> 2) * 64 + (j16 & 3) * 8, b_lo + ((j16 * 2048) >> 4), idesc2);
+                } else {
+                    // P_hi K_hi, P_hi K_lo, P_lo K_hi: of the 16 words of a 16-column group, hi = first 8, lo = next 8
+                    umma_bf16_ts_dyn(d, pa, b_lo, idesc2, first_of_rb ? 0u : 1u);
+#pragma unroll
+                    for (int grp = 0; grp < 3; ++grp) {
+                        const uint32_t bg = b_lo + ((grp == 1 ? B_PART : 0) >> 4);
+                        const uint32_t pg = pa + (grp == 2 ? 8u : 0u);
+#pragma unroll
+                        for (int j16 = (grp == 0 ? 1 : 0); j16 < 8; ++j16)
+                            umma_bf16_ts<true>(d, pg + (j16 >> 2) * 64 + (j16 & 3) * 16, bg + ((j16 * 2048) >> 4), idesc2);
+                    }
+                }
                 umma_commit(s_free(buf));
                 umma_commit(b_empty(st));
                 if (last_of_rb) umma_commit(dz_full);
@@ -1258,8 +1356,13 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
 #pragma unroll
                             for (int c = 0; c < 32; ++c) pv[c] = (c == c_self) ? 0.f : pv[c];
                         }
-                        store_p16(taddr + cc * 16, pv, 0);
-                        store_p16(taddr + cc * 16 + 8, pv, 16);
+                        if (!kX3) {
+                            store_p16(taddr + cc * 16, pv, 0);
+                            store_p16(taddr + cc * 16 + 8, pv, 16);
+                        } else {
+                            store_p16_split(taddr + cc * 32, pv, 0);
+                            store_p16_split(taddr + cc * 32 + 16, pv, 16);
+                        }
                     }
                 } else {
                     // ---------------- rare case (ragged tiles, non-anchor rows, wild LSE ranges): two exps,
@@ -1280,7 +1383,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                             const float e = ex2(fmaf(x, p.c2, -lse2_i)) + ex2(fmaf(x, p.c2, -lj[c]));   // +inf -> 0
                             pv[u] = (j >= p.n_k || j == gi) ? 0.f : e;
                         }
-                        store_p16(taddr + g16 * 8, pv, 0);     // words [8g, 8g+8) lie inside columns already read
+                        if (!kX3) store_p16(taddr + g16 * 8, pv, 0);     // words [8g, 8g+8) lie inside columns already read
+                        else store_p16_split(taddr + g16 * 16, pv, 0); // hi | lo words over the 16 columns just read
                     }
                 }
                 tr(6);
@@ -1360,7 +1464,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
 // -- the fp32 closed form of the positive-pair part of the gradient (positive_term above).
 __global__ void __launch_bounds__(256)
 label_rows_kernel(const int64_t* __restrict__ labels, int n_samples, RowMap map, int n_views, int mode,
-                  const __nv_bfloat16* __restrict__ k, int ldk, int* __restrict__ rep_row,
+                  const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ k_lo, int ldk,
+                  int* __restrict__ rep_row,
                   float* __restrict__ npos_row, float* __restrict__ nia_row, float* __restrict__ cls_all,
                   float* __restrict__ cls_anc) {
     const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -1399,6 +1504,12 @@ label_rows_kernel(const int64_t* __restrict__ labels, int n_samples, RowMap map,
                 if (on) {
                     float kj[4];
                     load_k4(k + (int64_t)j * ldk, d, kj);
+                    if (k_lo != nullptr) {
+                        float kl[4];
+                        load_k4(k_lo + (int64_t)j * ldk, d, kl);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) kj[i] += kl[i];
+                    }
                     const bool anc = map.is_anchor(j, mode);
 #pragma unroll
                     for (int i = 0; i < 4; ++i) { sa[i] += kj[i]; sn[i] += anc ? kj[i] : 0.f; }
@@ -1498,31 +1609,33 @@ static bool thread_has_context() {
     return fn(&ctx) == CUDA_SUCCESS && ctx != nullptr;
 }
 
-static int make_tmap(const scb_supcon_problem* p, CUtensorMap* out) {
+static int make_tmap_ptr(const scb_supcon_problem* p, const void* kptr, CUtensorMap* out);
+static int make_tmap(const scb_supcon_problem* p, CUtensorMap* out) { return make_tmap_ptr(p, p->k, out); }
+static int make_tmap_ptr(const scb_supcon_problem* p, const void* kptr, CUtensorMap* out) {
     // The encoder is a driver-API entry point and needs a context current on THIS thread; autograd calls
     // the backward from its own thread, where nothing may have touched the runtime yet.
     if (!thread_has_context()) SCB_CUDA_OK(cudaFree(nullptr));     // binds the primary context (never during capture:
                                                                     // a thread that captures has used the runtime before)
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return SCB_ERR_CUDA; }
-    SCB_REQUIRE((reinterpret_cast<uintptr_t>(p->k) & 15u) == 0, "supcon: k must be 16-byte aligned");
+    SCB_REQUIRE((reinterpret_cast<uintptr_t>(kptr) & 15u) == 0, "supcon: k must be 16-byte aligned");
     // the descriptor depends on (address, rows, row stride) only: forward and backward of a step, and every
     // step of a training loop that re-uses its buffers, hit this small per-thread cache instead of the driver
     struct Entry { const void* k; int n_k, ldk; CUtensorMap map; };
-    static thread_local Entry cache[4] = {};
+    static thread_local Entry cache[8] = {};
     static thread_local int next = 0;
     for (const Entry& e : cache)
-        if (e.k == p->k && e.n_k == p->n_k && e.ldk == p->ldk) { *out = e.map; return SCB_OK; }
+        if (e.k == kptr && e.n_k == p->n_k && e.ldk == p->ldk) { *out = e.map; return SCB_OK; }
     cuuint64_t gdim[2] = {(cuuint64_t)p->ldk, (cuuint64_t)p->n_k};
     cuuint64_t gstride[1] = {(cuuint64_t)p->ldk * 2};
     cuuint32_t box[2] = {64, 128};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p->k), gdim, gstride, box, estr,
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(kptr), gdim, gstride, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with code %d", (int)r); return SCB_ERR_CUDA; }
-    cache[next] = Entry{p->k, p->n_k, p->ldk, *out};
-    next = (next + 1) & 3;
+    cache[next] = Entry{kptr, p->n_k, p->ldk, *out};
+    next = (next + 1) & 7;
     return SCB_OK;
 }
 
@@ -1614,7 +1727,7 @@ int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows) {
 }
 
 static int tc_supported(const scb_supcon_problem* p) {
-    if (p->engine == SCB_ENGINE_BF16X3) { set_error("the bf16x3 engine is not built yet"); return SCB_ERR_UNSUPPORTED; }
+    if (p->engine == SCB_ENGINE_BF16X3 && p->k_lo == nullptr) { set_error("the bf16x3 engine needs k_lo"); return SCB_ERR_ARG; }
     if (p->mask_kind == SCB_MASK_EXPLICIT) { set_error("tensor-core engine: explicit masks run on ENGINE_FP32"); return SCB_ERR_UNSUPPORTED; }
     if ((int64_t)p->n_k > (int64_t)kMaxFwdRowBlocks * kBM) { set_error("tensor-core engine: more than %d rows", kMaxFwdRowBlocks * kBM); return SCB_ERR_UNSUPPORTED; }
     if (p->ldk != 64 && p->ldk != 128) { set_error("tensor-core engine: ldk must be 64 or 128 (dim <= 128), got %d", p->ldk); return SCB_ERR_UNSUPPORTED; }
@@ -1625,6 +1738,7 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
                         void* workspace, TcParams* t) {
     memset(t, 0, sizeof(*t));
     t->k = (const __nv_bfloat16*)p->k;
+    t->k_lo = (p->engine == SCB_ENGINE_BF16X3) ? (const __nv_bfloat16*)p->k_lo : nullptr;
     t->ldk = p->ldk; t->n_k = p->n_k; t->dim = p->dim;
     t->row_begin = row_begin; t->n_rows = n_rows; t->a_count = a_count;
     t->CT = g.CT; t->RB = g.RB; t->T = g.T; t->q = g.q;
@@ -1656,7 +1770,7 @@ static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, boo
     prefer_max_smem_carveout(label_rows_kernel);
     const int n_samples = p->n_seg * p->seg;
     SCB_CUDA_OK(launch_pdl(label_rows_kernel, dim3((unsigned)ceil_div((int64_t)n_samples * 32, 256)), dim3(256), 0, stream,
-                           p->labels, n_samples, t.map, p->n_views, p->mode, t.k, p->ldk, (int*)t.rep_row,
+                           p->labels, n_samples, t.map, p->n_views, p->mode, t.k, t.k_lo, p->ldk, (int*)t.rep_row,
                            (float*)t.npos_row, (float*)t.nia_row, with_sums ? (float*)t.fin.cls_all : (float*)nullptr,
                            with_sums ? (float*)t.fin.cls_anc : (float*)nullptr));
     count_launch();
@@ -1720,15 +1834,25 @@ int tc_forward(const scb_supcon_problem* p, int row_begin, int n_rows, int n_anc
     // with a label cache the class sums of the backward are built here, once per step
     if (int e = launch_label_rows(p, t, p->label_cache != nullptr, stream)) return e;
     const int kch = p->ldk / 64;
+    const bool x3 = p->engine == SCB_ENGINE_BF16X3;
+    CUtensorMap tmap_lo = tmap;
+    if (x3) { if (int e = make_tmap_ptr(p, p->k_lo, &tmap_lo)) return e; }
+    // bf16: A[2] + B[2]; bf16x3: (hi | lo) tiles, single-buffered -- the same 192 KiB either way at ldk = 128
     const size_t smem = (size_t)2 * (2 * kch * kSub) + 2 * (kch * kSub) + 40 * 8 + 1024;
     const bool lab = p->mask_kind == SCB_MASK_LABELS;
-#define SCB_LAUNCH_FWD(KCH_, LAB_)                                                                      \
+#define SCB_LAUNCH_FWD(KCH_, LAB_, X3_)                                                                 \
     do {                                                                                                \
-        if (int e = set_smem(supcon_tc_fwd_kernel<KCH_, LAB_>, smem)) return e;                         \
-        SCB_CUDA_OK(launch_pdl(supcon_tc_fwd_kernel<KCH_, LAB_>, dim3(g.grid), dim3(kTcThreads), smem, stream, tmap, t)); \
+        if (int e = set_smem(supcon_tc_fwd_kernel<KCH_, LAB_, X3_>, smem)) return e;                    \
+        SCB_CUDA_OK(launch_pdl(supcon_tc_fwd_kernel<KCH_, LAB_, X3_>, dim3(g.grid), dim3(kTcThreads), smem, stream, tmap, \
+                               tmap_lo, t));                                                            \
     } while (0)
-    if (kch == 2) { if (lab) SCB_LAUNCH_FWD(2, true); else SCB_LAUNCH_FWD(2, false); }
-    else { if (lab) SCB_LAUNCH_FWD(1, true); else SCB_LAUNCH_FWD(1, false); }
+    if (x3) {
+        if (kch == 2) { if (lab) SCB_LAUNCH_FWD(2, true, true); else SCB_LAUNCH_FWD(2, false, true); }
+        else { if (lab) SCB_LAUNCH_FWD(1, true, true); else SCB_LAUNCH_FWD(1, false, true); }
+    } else {
+        if (kch == 2) { if (lab) SCB_LAUNCH_FWD(2, true, false); else SCB_LAUNCH_FWD(2, false, false); }
+        else { if (lab) SCB_LAUNCH_FWD(1, true, false); else SCB_LAUNCH_FWD(1, false, false); }
+    }
 #undef SCB_LAUNCH_FWD
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
@@ -1773,16 +1897,26 @@ static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_ro
     if (p->label_cache == nullptr)
         if (int e = launch_label_rows(p, t, true, stream)) return e;
     const int kch = p->ldk / 64;
-    const size_t smem = (size_t)(kch * kSub) + 5 * (kch * kSub) + 5 * 256 * 4 + (5 * 4 + 4) * 4 + 28 * 8 + 1024;
-#define SCB_LAUNCH_BWD(KCH_, DIR_)                                                                      \
+    const bool x3 = p->engine == SCB_ENGINE_BF16X3;
+    CUtensorMap tmap_lo = tmap;
+    if (x3) { if (int e = make_tmap_ptr(p, p->k_lo, &tmap_lo)) return e; }
+    const int nsb = x3 ? 2 : 5, parts = x3 ? 2 : 1;
+    const size_t smem = (size_t)parts * (kch * kSub) + (size_t)nsb * parts * (kch * kSub) + nsb * 256 * 4 +
+                        (nsb * 4 + 4) * 4 + 28 * 8 + 1024;
+#define SCB_LAUNCH_BWD(KCH_, DIR_, X3_)                                                                 \
     do {                                                                                                \
-        if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, DIR_>, smem)) return e;                         \
-        SCB_CUDA_OK(launch_pdl_cluster(supcon_tc_bwd_kernel<KCH_, DIR_>, dim3(g.grid), dim3(kBwdThreads), smem, stream, \
-                                       DIR_ ? g.direct : 1, tmap, t));                                  \
+        if (int e = set_smem(supcon_tc_bwd_kernel<KCH_, DIR_, X3_>, smem)) return e;                    \
+        SCB_CUDA_OK(launch_pdl_cluster(supcon_tc_bwd_kernel<KCH_, DIR_, X3_>, dim3(g.grid), dim3(kBwdThreads), smem, stream, \
+                                       DIR_ ? g.direct : 1, tmap, tmap_lo, t));                         \
     } while (0)
     if (g_ev_start) SCB_CUDA_OK(cudaEventRecord(g_ev_start, stream));
-    if (kch == 2) { if (g.direct) SCB_LAUNCH_BWD(2, true); else SCB_LAUNCH_BWD(2, false); }
-    else { if (g.direct) SCB_LAUNCH_BWD(1, true); else SCB_LAUNCH_BWD(1, false); }
+    if (x3) {
+        if (kch == 2) { if (g.direct) SCB_LAUNCH_BWD(2, true, true); else SCB_LAUNCH_BWD(2, false, true); }
+        else { if (g.direct) SCB_LAUNCH_BWD(1, true, true); else SCB_LAUNCH_BWD(1, false, true); }
+    } else {
+        if (kch == 2) { if (g.direct) SCB_LAUNCH_BWD(2, true, false); else SCB_LAUNCH_BWD(2, false, false); }
+        else { if (g.direct) SCB_LAUNCH_BWD(1, true, false); else SCB_LAUNCH_BWD(1, false, false); }
+    }
 #undef SCB_LAUNCH_BWD
     if (g_ev_stop) SCB_CUDA_OK(cudaEventRecord(g_ev_stop, stream));
     SCB_CUDA_OK(cudaGetLastError());

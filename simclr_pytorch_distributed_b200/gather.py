@@ -330,7 +330,9 @@ class DistributedSupConLoss(nn.Module):
             labels = L.label_ids(labels, dev)
             labels_all = torch.empty(world * bsz, dtype=torch.int64, device=dev)
             _all_gather_flat(labels_all, labels, group)       # sample id = rank*bsz + b
-        engine = L.select_engine(self.engine, features.dtype, dim, mask_kind, world * n_views * bsz)
+        engine = L.select_engine(self.engine, features.dtype, dim, mask_kind, world * n_views * bsz, allow_x3=False)
+        if engine == _lib.ENGINE_BF16X3:
+            raise ValueError("engine 'bf16x3' is a single-GPU engine of SupConLoss; the row-sharded loss takes 'fp32' or 'bf16'")
         plan = L.LossPlan(bsz, n_views, dim, n_seg=world, seg_index=rank, mode=mode, mask_kind=mask_kind,
                           engine=engine)
         plan.scalar_dtype = _lib.dtype_code(features.dtype)

@@ -45,13 +45,16 @@ def tc_engine_supported(dim, mask_kind, n_k):
     return mask_kind != _lib.MASK_EXPLICIT and dim <= 128 and n_k >= 1
 
 
-def select_engine(requested, feat_dtype, dim, mask_kind, n_k):
+def select_engine(requested, feat_dtype, dim, mask_kind, n_k, allow_x3=True):
     req = os.environ.get('SIMCLR_B200_LOSS_ENGINE', requested)
     if req == 'auto':
         if not tc_engine_supported(dim, mask_kind, n_k):
             return _lib.ENGINE_FP32
-        # fp32 features keep fp32 arithmetic (the reference's); 16-bit features take the tensor cores
-        return _lib.ENGINE_BF16 if feat_dtype in (torch.bfloat16, torch.float16) else _lib.ENGINE_FP32
+        # 16-bit features: bf16 operands.  fp32 features (what main_supcon.py:283-290 passes) keep fp32-class
+        # arithmetic on the tensor cores: operands split into bf16 hi + lo, three MMAs per tile (1e-4 of the reference)
+        if feat_dtype in (torch.bfloat16, torch.float16):
+            return _lib.ENGINE_BF16
+        return _lib.ENGINE_BF16X3 if allow_x3 else _lib.ENGINE_FP32
     if req not in _ENGINES:
         raise ValueError('Unknown engine: {}'.format(req))
     eng = _ENGINES[req]
