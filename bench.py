@@ -387,6 +387,47 @@ def bn_kernel_breakdown(steps, pool=8):
     return {n: t / steps * 1e3 for n, t in zip(names, tot)}
 
 
+def loss_fp32_variant(args, pk):
+    import torch
+    from simclr_pytorch_distributed_b200 import SupConLoss, _lib
+    lib = _lib.load()
+    pool = 32
+    g = torch.Generator().manual_seed(4242)
+    zs = [(torch.randn(B_GLOBAL, N_VIEWS, DIM, generator=g) * 2.0 + 0.3).cuda().requires_grad_(True) for _ in range(pool)]
+    crit = SupConLoss(temperature=TEMP, normalize=True)          # engine 'auto'
+    ones = torch.ones((), device='cuda')
+
+    def step(i):
+        zs[i % pool].grad = None
+        crit(zs[i % pool]).backward(ones)
+    step(0)
+    c0 = lib.scb_launch_count()
+    step(1)
+    launches = lib.scb_launch_count() - c0
+    ms, how = time_steps(step, args.steps, args.warmup, 1, graph_pool=pool)
+    per = ms / args.steps
+    flops = 6.0 * (N_VIEWS * B_GLOBAL) ** 2 * DIM
+    ach = flops / (per * 1e-3) / 1e12
+    # parity of exactly this call against the fp64 dense algorithm on the raw fp32 rows
+    from oracle.dense_port import dense_supcon_loss
+    import torch.nn.functional as F
+    f = zs[0].detach().clone().requires_grad_(True)
+    loss = crit(f)
+    loss.backward()
+    r = zs[0].detach().double().requires_grad_(True)
+    ref = dense_supcon_loss(F.normalize(r, dim=-1), temperature=TEMP)
+    ref.backward()
+    return {'metric': METRIC, 'value': B_GLOBAL / (per * 1e-3), 'unit': 'pairs/s', 'ms_per_step': per,
+            'dtype': 'bf16x3 (bf16 hi+lo operands, fp32 accumulate)', 'gpu_launches': int(launches),
+            'config': {'workload': 'raw fp32 embeddings [4096,2,128], normalize=True (fused F.normalize and its '
+                                   'backward), engine auto', 'launch': how},
+            'roofline': {'bound': 'tensor', 'achieved': ach, 'peak': pk['tf'] / 3.0, 'unit': 'TFLOP/s',
+                         'frac': ach / (pk['tf'] / 3.0), 'peak_source': pk['src'] + ' burst bf16 / 3 (three MMAs per '
+                         'algorithmic product)'},
+            'parity': {'loss_rel_err': abs(float(loss) - float(ref)) / abs(float(ref)),
+                       'grad_rel_fro_err': float((f.grad.double() - r.grad).norm() / r.grad.norm()), 'tolerance': 1e-4}}
+
+
 # ----------------------------------------------------------------------------- parity of what is timed
 def all_gather_cat(t, world):
     import torch
@@ -856,6 +897,10 @@ def main():
         par = loss_parity(world, rank, engine)
         if rank == 0:
             out['parity'] = par
+        if world == 1 and engine == 'bf16':
+            # SURVEY 8(d) Metric 1 as the reference calls it: RAW fp32 embeddings, the fused F.normalize, engine
+            # 'auto' = the split-bf16 tensor-core engine at the reference's precision (1e-4)
+            out['ntxent_fp32'] = loss_fp32_variant(args, pk)
         if rank == 0 and not args.no_gpu_baseline:
             out['gpu_baseline'] = gpu_loss_baseline()
             out['gpu_baseline']['ours_over_gpu_baseline_fp32'] = out['value'] / out['gpu_baseline']['fp32']['value']

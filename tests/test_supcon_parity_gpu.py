@@ -31,7 +31,7 @@ def unit_rows(rng, B, V, D, common=0.5):
     return (z / np.linalg.norm(z, axis=-1, keepdims=True)).astype(np.float32)
 
 
-@pytest.mark.parametrize('engine', ['fp32', 'bf16'])
+@pytest.mark.parametrize('engine', ['fp32', 'bf16x3', 'bf16'])
 @pytest.mark.parametrize('mode', ['all', 'one'])
 def test_cfg5_full_size_labels(mode, engine):
     """B = 1024, V = 2, D = 128, 100 classes, T = base_T = 0.07."""
@@ -40,9 +40,9 @@ def test_cfg5_full_size_labels(mode, engine):
     labels = rng.integers(0, 100, size=1024)
     kw = dict(temperature=0.07, base_temperature=0.07, contrast_mode=mode)
     loss, grad = run(z, labels, engine, **kw)
-    used = z if engine == 'fp32' else torch.from_numpy(z).to(torch.bfloat16).float().numpy()
+    used = z if engine != 'bf16' else torch.from_numpy(z).to(torch.bfloat16).float().numpy()
     ref_loss, ref_grad, _ = supcon_forward_backward(used.astype(np.float64), labels, None, **kw)
-    tol = 1e-4 if engine == 'fp32' else 2e-3
+    tol = 1e-4 if engine != 'bf16' else 2e-3
     assert abs(loss - ref_loss) <= tol * abs(ref_loss), (loss, ref_loss)
     assert rel_f(grad, ref_grad.reshape(grad.shape)) <= tol, rel_f(grad, ref_grad.reshape(grad.shape))
 
@@ -117,3 +117,21 @@ def test_backward_general_geometry_matches_direct(monkeypatch):
         outs.append((float(r.stdout.strip().splitlines()[-1]), np.load(path)))
     assert outs[0][0] == outs[1][0]
     assert rel_f(outs[0][1].astype(np.float64), outs[1][1].astype(np.float64)) <= 2.0 ** -8
+
+
+def test_auto_engine_is_the_split_bf16_engine_for_fp32_features():
+    """The literal two-line change of INTEGRATION.md (fp32 features, engine 'auto', as main_supcon.py:283-290 calls
+    it) lands on the tensor cores at the reference's precision: raw fp32 rows, fused normalisation, 1e-4."""
+    from simclr_pytorch_distributed_b200 import losses as L, _lib
+    assert L.select_engine('auto', torch.float32, 128, _lib.MASK_SIMCLR, 8192) == _lib.ENGINE_BF16X3
+    assert L.select_engine('auto', torch.bfloat16, 128, _lib.MASK_SIMCLR, 8192) == _lib.ENGINE_BF16
+    assert L.select_engine('auto', torch.float32, 300, _lib.MASK_SIMCLR, 8192) == _lib.ENGINE_FP32
+    rng = np.random.default_rng(31)
+    raw = (rng.standard_normal((1024, 2, 128)) * 2.0 + 0.3).astype(np.float32)
+    f = torch.from_numpy(raw).cuda().requires_grad_(True)
+    loss = SupConLoss(temperature=0.5, normalize=True)(f)
+    loss.backward()
+    ref_loss, g_hat, _ = supcon_forward_backward(normalize_rows(raw), temperature=0.5)
+    ref_grad = normalize_rows_backward(raw, g_hat)
+    assert abs(float(loss) - ref_loss) <= 1e-4 * abs(ref_loss)
+    assert rel_f(f.grad.cpu().numpy().astype(np.float64), ref_grad.reshape(raw.shape)) <= 1e-4
