@@ -174,6 +174,22 @@ int scb_supcon_finish(const float* dk, int ld_dk, const void* features, int feat
                       void* out_dfeatures, int64_t out_stride_sample, int64_t out_stride_view,
                       void* stream);
 
+/* Feature-norm side outputs of the training loop, /root/reference/main_supcon.py:298-317: from the
+ * 1 / ||z_i|| vector that scb_supcon_prep leaves behind (n = n_views * n_samples rows of the UN-normalised
+ * embeddings) computes out_terms[0..4] = norm_mean, norm_var (:300-301), loss_sec = mean (||z|| - record)^2 with
+ * the moving average `record[0]` updated first (:304-309; record[1] != 0 once it holds a value), loss_l2reg =
+ * mean ||z||^2 (:314), and sec_weight * loss_sec + l2reg_weight * loss_l2reg (what :311-317 add to the loss).
+ * Everything stays on the device: no pass over the embeddings and none of the five .item() syncs of :327-333. */
+int scb_feature_norm_terms(const float* inv_norm, int n, float* record, float momentum, float sec_weight,
+                           float l2reg_weight, float* out_terms, void* stream);
+/* The autograd backward of those two terms, added into d features [n_samples, n_views, dim]:
+ *   d features += *grad_out * (2/n) * ( sec_weight (||z|| - record[0]) / ||z|| + l2reg_weight ) * z */
+int scb_feature_norm_backward(const void* features, int feat_dtype, int n_samples, int n_views, int dim,
+                              int64_t stride_sample, int64_t stride_view, const float* inv_norm,
+                              const float* record, float sec_weight, float l2reg_weight,
+                              const void* grad_out, int grad_dtype, void* dfeatures,
+                              int64_t out_stride_sample, int64_t out_stride_view, void* stream);
+
 /* scb_supcon_backward followed by scb_supcon_finish in one call for the tensor-core engines (two
  * launches instead of three, no [n_rows, ldk] fp32 round trip): the autograd backward of
  * losses.py:52-91 plus that of main_supcon.py:283, written straight into d features.

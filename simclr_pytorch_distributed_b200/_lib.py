@@ -121,6 +121,8 @@ PROTOTYPES = {
     'scb_supcon_backward_features': (_i, [_pp, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i64, _i64, _i, _vp, _vp, _i64,
                                           _i64, _vp, _i64, _vp]),
     'scb_supcon_finish': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _i64, _i64, _vp]),
+    'scb_feature_norm_terms': (_i, [_vp, _i, _vp, _f, _f, _f, _vp, _vp]),
+    'scb_feature_norm_backward': (_i, [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _vp, _f, _f, _vp, _i, _vp, _i64, _i64, _vp]),
     'scb_peer_bcast': (_i, [_vp, _vp, _i, _vp, _i, _vp]),
     'scb_supcon_prep_peers': (_i, [_vp, _i, _i, _i, _i, _i64, _i64, _i, _f, _vp, _i64, _i, _i, _vp, _vp]),
     'scb_supcon_forward_peers': (_i, [_pp, _i, _i, _i, _vp, _vp, _vp, _i64, _vp]),

@@ -642,3 +642,100 @@ extern "C" int scb_peer_wait(const uint32_t* flags_local, const uint32_t* state,
     count_launch();
     return SCB_OK;
 }
+
+// ================================================================== feature-norm side outputs (main_supcon.py:298-317)
+// The training loop of the reference looks at the norms of the UN-normalised embeddings every step: their mean and
+// variance (logged), an exponential moving average of the mean (`record_norm_mean`), and two optional regularisers,
+//   loss_sec   = mean (||z_i|| - record_norm_mean)^2        (:304-312, the moving average updated first, detached)
+//   loss_l2reg = mean ||z_i||^2                             (:314-317).
+// The fused normalisation already has 1 / ||z_i|| (scb_supcon_prep's out_inv_norm), so one small CTA turns that
+// vector into all of it -- no pass over the embeddings, no host synchronisation.
+namespace scb {
+
+__global__ void __launch_bounds__(1024)
+feature_norm_terms_kernel(const float* __restrict__ inv_norm, int n, float* record, float momentum, float w_sec,
+                          float w_l2, float* __restrict__ out) {
+    __shared__ double red[3][32];
+    pdl_launch_dependents();
+    pdl_wait();
+    double s1 = 0.0, s2 = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const double v = 1.0 / (double)inv_norm[i];
+        s1 += v; s2 += v * v;
+    }
+    auto block_sum = [&](double v, int slot) {
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) red[slot][threadIdx.x >> 5] = v;
+        __syncthreads();
+        double t = (threadIdx.x < 32) ? red[slot][threadIdx.x] : 0.0;
+        if (threadIdx.x < 32)
+            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        return t;            // valid in warp 0
+    };
+    const double t1 = block_sum(s1, 0), t2 = block_sum(s2, 1);
+    if (threadIdx.x == 0) {
+        const double mean = t1 / n, msq = t2 / n;
+        // record[0] = moving average, record[1] = 1 once it holds a value (`record_norm_mean is not None`, :304-307)
+        const double rec = (record[1] != 0.f) ? (1.0 - momentum) * (double)record[0] + momentum * mean : mean;
+        record[0] = (float)rec;
+        record[1] = 1.f;
+        const double var = msq - mean * mean;                       // mean (v - mean)^2
+        const double sec = msq - 2.0 * rec * mean + rec * rec;      // mean (v - rec)^2
+        out[0] = (float)mean;
+        out[1] = (float)(var > 0.0 ? var : 0.0);
+        out[2] = (float)sec;
+        out[3] = (float)msq;
+        out[4] = (float)(w_sec * sec + w_l2 * msq);                 // what the caller adds to the loss
+    }
+}
+
+// d features += upstream * [ w_sec * (2/n) (||z|| - record) / ||z|| + w_l2 * (2/n) ] * z      (one warp per row)
+template <typename TF>
+__global__ void __launch_bounds__(256)
+feature_norm_backward_kernel(const TF* __restrict__ feat, int n_samples, int n_views, int dim, int64_t stride_s,
+                             int64_t stride_v, const float* __restrict__ inv_norm, const float* __restrict__ record,
+                             float w_sec, float w_l2, const void* __restrict__ grad_out, int grad_dtype,
+                             TF* __restrict__ dfeat, int64_t ostride_s, int64_t ostride_v) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    pdl_launch_dependents();
+    pdl_wait();
+    const int n = n_samples * n_views;
+    if (warp >= n) return;
+    const int v = warp / n_samples, b = warp - v * n_samples;          // inv_norm is indexed by stacked row v*n_samples + b
+    const float norm = 1.f / inv_norm[warp];
+    const float g = load_scalar(grad_out, grad_dtype) * (2.f / (float)n);
+    const float c = g * (w_sec * (norm - record[0]) / norm + w_l2);
+    const TF* src = feat + (int64_t)b * stride_s + (int64_t)v * stride_v;
+    TF* dst = dfeat + (int64_t)b * ostride_s + (int64_t)v * ostride_v;
+    for (int d = lane; d < dim; d += 32) dst[d] = from_f32<TF>(to_f32(dst[d]) + c * to_f32(src[d]));
+}
+
+}  // namespace scb
+
+extern "C" int scb_feature_norm_terms(const float* inv_norm, int n, float* record, float momentum, float sec_weight,
+                                      float l2reg_weight, float* out_terms, void* stream_) {
+    SCB_REQUIRE(inv_norm && record && out_terms && n >= 1, "feature_norm_terms: null pointer or empty input");
+    SCB_CUDA_OK(launch_pdl(feature_norm_terms_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream_, inv_norm, n, record,
+                           momentum, sec_weight, l2reg_weight, out_terms));
+    count_launch();
+    return SCB_OK;
+}
+
+extern "C" int scb_feature_norm_backward(const void* features, int feat_dtype, int n_samples, int n_views, int dim,
+                                         int64_t stride_sample, int64_t stride_view, const float* inv_norm,
+                                         const float* record, float sec_weight, float l2reg_weight,
+                                         const void* grad_out, int grad_dtype, void* dfeatures,
+                                         int64_t out_stride_sample, int64_t out_stride_view, void* stream_) {
+    SCB_REQUIRE(features && inv_norm && record && grad_out && dfeatures, "feature_norm_backward: null pointer");
+    SCB_REQUIRE(n_samples > 0 && n_views > 0 && dim > 0, "feature_norm_backward: bad shape");
+    const int64_t rows = (int64_t)n_samples * n_views;
+    const unsigned blocks = (unsigned)ceil_div(rows * 32, 256);
+    SCB_DISPATCH_FLOAT(feat_dtype, TF, {
+        SCB_CUDA_OK(launch_pdl(feature_norm_backward_kernel<TF>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream_,
+                               (const TF*)features, n_samples, n_views, dim, stride_sample, stride_view, inv_norm, record,
+                               sec_weight, l2reg_weight, grad_out, grad_dtype, (TF*)dfeatures, out_stride_sample,
+                               out_stride_view));
+    });
+    count_launch();
+    return SCB_OK;
+}

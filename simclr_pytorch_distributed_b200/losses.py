@@ -227,7 +227,7 @@ class _SupConFunction(torch.autograd.Function):
     """Single-GPU loss: prep -> forward -> (backward -> finish).  losses.py:52-91 + autograd."""
 
     @staticmethod
-    def forward(ctx, feats, labels, mask, plan, temperature, base_temperature, normalize):
+    def forward(ctx, feats, labels, mask, plan, temperature, base_temperature, normalize, norms=None):
         lib = _lib.load()
         dev = feats.device
         with _on_device(dev):
@@ -250,9 +250,19 @@ class _SupConFunction(torch.autograd.Function):
             prob = _problem(plan, k, k_lo, labels, mask, temperature, base_temperature)
             cache = label_cache_for(lib, prob, dev)      # labels are scanned once per step, by the forward
             launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
+            ctx.norms = None
+            out = typed_loss(loss, feats.dtype)
+            if norms is not None:
+                # feature-norm side outputs (main_supcon.py:298-317) from the 1/||z|| vector of the fused normalise
+                record, momentum, w_sec, w_l2, terms = norms
+                _lib.check(lib.scb_feature_norm_terms(stats[3].data_ptr(), n_k, record.data_ptr(), momentum, w_sec,
+                                                      w_l2, terms.data_ptr(), _stream(dev)), 'scb_feature_norm_terms')
+                if w_sec != 0.0 or w_l2 != 0.0:
+                    out = out + terms[4].to(out.dtype)
+                    ctx.norms = (record, w_sec, w_l2)
         ctx.plan, ctx.prob_args, ctx.prob = plan, (temperature, base_temperature, normalize), prob
         ctx.save_for_backward(feats, labels, mask, k, k_lo, stats, cache)
-        return typed_loss(loss, feats.dtype)
+        return out
 
     @staticmethod
     def backward(ctx, grad_out):
@@ -272,7 +282,14 @@ class _SupConFunction(torch.autograd.Function):
                 dk = torch.empty((plan.rows_local, plan.ldk), dtype=torch.float32, device=dev)
                 launch_backward(lib, prob, plan, stats[0], stats[2], g, dk, dev)
                 launch_finish(lib, dk, feats, plan, normalize, inv_norm, dfeats)
-        return dfeats, None, None, None, None, None, None
+            if ctx.norms is not None:
+                record, w_sec, w_l2 = ctx.norms
+                _lib.check(lib.scb_feature_norm_backward(
+                    feats.data_ptr(), _lib.dtype_code(feats.dtype), plan.n_local, plan.n_views, plan.dim,
+                    feats.stride(0), feats.stride(1), stats[3].data_ptr(), record.data_ptr(), w_sec, w_l2,
+                    g.data_ptr(), _lib.dtype_code(g.dtype), dfeats.data_ptr(), dfeats.stride(0), dfeats.stride(1),
+                    _stream(dev)), 'scb_feature_norm_backward')
+        return dfeats, None, None, None, None, None, None, None
 
 
 def validate_inputs(features, labels, mask, contrast_mode):
@@ -303,17 +320,27 @@ class SupConLoss(nn.Module):
     """
 
     def __init__(self, temperature=0.07, contrast_mode='all', base_temperature=0.07,
-                 engine='auto', normalize=False):
+                 engine='auto', normalize=False, track_norms=False, norm_momentum=0.1):
         super(SupConLoss, self).__init__()
         self.temperature = temperature
         self.contrast_mode = contrast_mode
         self.base_temperature = base_temperature
         self.engine = engine
         self.normalize = normalize
+        # feature-norm side outputs of the training loop (main_supcon.py:298-317); need normalize=True (raw features in)
+        self.track_norms = track_norms
+        self.norm_momentum = norm_momentum           # `--norm_momentum` of the reference
+        self.record_norm_mean = None                 # device [value, initialised flag]: `opt.record_norm_mean`
+        self.norm_terms = None                       # device [norm_mean, norm_var, loss_sec, loss_l2reg, added term]
 
-    def forward(self, features, labels=None, mask=None):
+    def forward(self, features, labels=None, mask=None, sec_weight=0.0, l2reg_weight=0.0):
         """features [bsz, n_views, ...]; labels [bsz]; mask [bsz, bsz] (float, may be asymmetric).
-        Returns the 0-dim loss, differentiable with respect to `features`."""
+        Returns the 0-dim loss, differentiable with respect to `features`.
+
+        With `track_norms=True` (and `normalize=True`) the call also leaves the feature-norm statistics of
+        main_supcon.py:298-317 in `self.norm_terms` (a device tensor, no synchronisation), keeps the moving average in
+        `self.record_norm_mean`, and adds `sec_weight * loss_sec + l2reg_weight * loss_l2reg` to the loss (the
+        reference's `opt.sec_wei * now_iter / total` and `opt.l2reg_wei * ...` factors, both 0 by default)."""
         labels, mode = validate_inputs(features, labels, mask, self.contrast_mode)
         if not features.is_cuda:
             raise RuntimeError('simclr_pytorch_distributed_b200.SupConLoss runs on CUDA tensors only '
@@ -337,5 +364,16 @@ class SupConLoss(nn.Module):
         engine = select_engine(self.engine, features.dtype, D, mask_kind, V * B)
         plan = LossPlan(B, V, D, mode=mode, mask_kind=mask_kind, engine=engine)
         plan.scalar_dtype = _lib.dtype_code(features.dtype)
+        norms = None
+        if self.track_norms:
+            if not self.normalize:
+                raise ValueError('track_norms needs normalize=True: the norms are those of the un-normalised features')
+            if self.record_norm_mean is None or self.record_norm_mean.device != dev:
+                self.record_norm_mean = torch.zeros(2, dtype=torch.float32, device=dev)
+            self.norm_terms = torch.empty(5, dtype=torch.float32, device=dev)
+            norms = (self.record_norm_mean, float(self.norm_momentum), float(sec_weight), float(l2reg_weight),
+                     self.norm_terms)
+        elif sec_weight != 0.0 or l2reg_weight != 0.0:
+            raise ValueError('sec_weight / l2reg_weight need track_norms=True')
         return _SupConFunction.apply(features, labels, mask, plan, float(self.temperature),
-                                     float(self.base_temperature), bool(self.normalize))
+                                     float(self.base_temperature), bool(self.normalize), norms)

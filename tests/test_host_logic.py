@@ -39,7 +39,8 @@ def test_cpu_tensor_is_refused_loudly():
 
 
 def test_engine_selection():
-    assert L.select_engine('auto', torch.float32, 128, _lib.MASK_SIMCLR, 512) == _lib.ENGINE_FP32
+    assert L.select_engine('auto', torch.float32, 128, _lib.MASK_SIMCLR, 512) == _lib.ENGINE_BF16X3
+    assert L.select_engine('auto', torch.float32, 128, _lib.MASK_SIMCLR, 512, allow_x3=False) == _lib.ENGINE_FP32
     assert L.select_engine('auto', torch.bfloat16, 128, _lib.MASK_LABELS, 512) == _lib.ENGINE_BF16
     assert L.select_engine('auto', torch.float32, 128, _lib.MASK_EXPLICIT, 512) == _lib.ENGINE_FP32
     assert L.select_engine('auto', torch.float32, 4096, _lib.MASK_SIMCLR, 512) == _lib.ENGINE_FP32

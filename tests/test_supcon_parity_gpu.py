@@ -135,3 +135,39 @@ def test_auto_engine_is_the_split_bf16_engine_for_fp32_features():
     ref_grad = normalize_rows_backward(raw, g_hat)
     assert abs(float(loss) - ref_loss) <= 1e-4 * abs(ref_loss)
     assert rel_f(f.grad.cpu().numpy().astype(np.float64), ref_grad.reshape(raw.shape)) <= 1e-4
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_feature_norm_side_outputs_and_regularisers(dtype):
+    """main_supcon.py:298-317 restated with torch autograd: norm mean / variance, the moving average, loss_sec and
+    loss_l2reg, and the gradient of `loss + w_sec * loss_sec + w_l2 * loss_l2reg` with respect to the raw features."""
+    torch.manual_seed(21)
+    B, V, D = 256, 2, 128
+    momentum, w_sec, w_l2 = 0.1, 0.3, 0.05
+    crit = SupConLoss(temperature=0.5, normalize=True, track_norms=True, norm_momentum=momentum)
+    record = None
+    for step in range(3):
+        raw = (torch.randn(B, V, D, device='cuda') * (2.0 + step) + 0.1).to(dtype)
+        f = raw.clone().requires_grad_(True)
+        loss = crit(f, sec_weight=w_sec, l2reg_weight=w_l2)
+        loss.backward()
+        r = raw.double().requires_grad_(True)
+        norms = torch.norm(r.view(B * V, D), p=2, dim=1)                       # :298
+        norm_mean = norms.mean()
+        norm_var = ((norms - norm_mean) ** 2).mean()
+        record = norm_mean.detach() if record is None else (1 - momentum) * record + momentum * norm_mean.detach()
+        loss_sec = ((norms - record) ** 2).mean()
+        loss_l2 = (norms ** 2).mean()
+        from oracle.dense_port import dense_supcon_loss
+        base = dense_supcon_loss(F.normalize(r, dim=-1), temperature=0.5)
+        ref = base + w_sec * loss_sec + w_l2 * loss_l2
+        ref.backward()
+        t = crit.norm_terms.double()
+        tol = 1e-5 if dtype == torch.float32 else 1e-5        # the terms come from fp32 norms of the given values
+        for got, want in zip(t[:4], (norm_mean, norm_var, loss_sec, loss_l2)):
+            assert abs(float(got) - float(want)) <= tol * max(1.0, abs(float(want))) + 1e-4 * abs(float(want))
+        assert abs(float(crit.record_norm_mean[0]) - float(record)) <= 1e-5 * float(record)
+        ltol = 1e-4 if dtype == torch.float32 else 2e-3 + 2 ** -8
+        assert abs(float(loss) - float(ref)) <= ltol * abs(float(ref))
+        gtol = 1e-4 if dtype == torch.float32 else 2e-3 + 2 ** -7
+        assert rel_f(f.grad.double().cpu().numpy(), r.grad.cpu().numpy()) <= gtol
