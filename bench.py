@@ -192,10 +192,14 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
     if world == 1:
         crit = SupConLoss(temperature=TEMP, engine=engine)
         fwd = lambda f: crit(f)                                                     # noqa: E731
+        # end to end: the module's graph mode (one CUDA-graph launch per step instead of four C-ABI calls + autograd)
+        crit_g = SupConLoss(temperature=TEMP, engine=engine, graph=True)
+        fwd_e2e = lambda f: crit_g(f)                                               # noqa: E731
     else:
         from simclr_pytorch_distributed_b200.gather import DistributedSupConLoss
         crit = DistributedSupConLoss(temperature=TEMP, engine=engine, normalize=False)
         fwd = lambda f: crit(f)                                                     # noqa: E731
+        fwd_e2e = fwd
 
     ones = torch.ones((), dtype=dtype, device='cuda')       # upstream gradient of the scalar loss, allocated once
 
@@ -232,7 +236,7 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
         cur = torch.cuda.current_stream()
         cur.wait_event(ready[i % 2])
         f = slots[i % 2].detach().requires_grad_(True)
-        loss = fwd(f)
+        loss = fwd_e2e(f)
         loss.backward()
         freed[i % 2].record(cur)
         loss_host.copy_(loss.detach().float(), non_blocking=True)
@@ -872,8 +876,8 @@ def main():
             'e2e': {'value': B_GLOBAL / (ms_e2e / args.steps * 1e-3), 'unit': 'pairs/s',
                     'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                     'note': 'each step: H2D of its embeddings from pinned memory (prefetched one step ahead on a '
-                            'copy stream), forward + backward, D2H of the loss, host sync; the gradient stays on '
-                            'the device'},
+                            'copy stream), forward + backward through SupConLoss(graph=True) at N=1 (the module replays '
+                            'a captured forward+backward), D2H of the loss, host sync; the gradient stays on the device'},
             'gpu_launches': int(launches),
         })
         # roofline of the STEP (6*A*C*D algorithmic FLOPs of SURVEY 8(d) over the graph-replayed step time, per GPU);

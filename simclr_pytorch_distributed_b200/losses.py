@@ -292,6 +292,35 @@ class _SupConFunction(torch.autograd.Function):
         return dfeats, None, None, None, None, None, None, None
 
 
+class _GraphEntry:
+    """One captured forward+backward of the loss for a fixed (shape, dtype, options, input address)."""
+    __slots__ = ('graph', 'x', 'labels', 'loss', 'grad', 'serial', 'own_input')
+
+
+class _GraphedSupCon(torch.autograd.Function):
+    """Replays a CUDA graph that holds the forward AND the backward kernels of one loss call (upstream gradient 1);
+    autograd's backward then only scales the stored gradient.  Cuts the host side of a step from four C-ABI calls
+    plus autograd bookkeeping to one graph launch."""
+
+    @staticmethod
+    def forward(ctx, feats, entry):
+        if entry.own_input:
+            entry.x.copy_(feats)
+        entry.graph.replay()
+        entry.serial += 1
+        ctx.entry, ctx.serial = entry, entry.serial
+        return entry.loss.clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        e = ctx.entry
+        if e.serial != ctx.serial:
+            raise RuntimeError('SupConLoss(graph=True): backward of a forward that was followed by another forward of '
+                               'the same shape (the captured gradient buffer was overwritten); call backward first '
+                               'or use graph=False')
+        return e.grad * grad_out.to(e.grad.dtype), None
+
+
 def validate_inputs(features, labels, mask, contrast_mode):
     """The reference's argument checks, in its order, with its messages (losses.py:33-61)."""
     if len(features.shape) < 3:
@@ -320,8 +349,12 @@ class SupConLoss(nn.Module):
     """
 
     def __init__(self, temperature=0.07, contrast_mode='all', base_temperature=0.07,
-                 engine='auto', normalize=False, track_norms=False, norm_momentum=0.1):
+                 engine='auto', normalize=False, track_norms=False, norm_momentum=0.1, graph=False):
         super(SupConLoss, self).__init__()
+        # graph=True: forward + backward of a call are captured once per (shape, dtype, labels?) in a CUDA graph and
+        # replayed afterwards (see _GraphedSupCon); for training loops whose step is bound by host launch overhead
+        self.graph = graph
+        self._graphs = {}
         self.temperature = temperature
         self.contrast_mode = contrast_mode
         self.base_temperature = base_temperature
@@ -364,6 +397,9 @@ class SupConLoss(nn.Module):
         engine = select_engine(self.engine, features.dtype, D, mask_kind, V * B)
         plan = LossPlan(B, V, D, mode=mode, mask_kind=mask_kind, engine=engine)
         plan.scalar_dtype = _lib.dtype_code(features.dtype)
+        if (self.graph and mask is None and not self.track_norms and features.requires_grad and
+                torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
+            return self._graphed(features, labels)
         norms = None
         if self.track_norms:
             if not self.normalize:
@@ -377,3 +413,53 @@ class SupConLoss(nn.Module):
             raise ValueError('sec_weight / l2reg_weight need track_norms=True')
         return _SupConFunction.apply(features, labels, mask, plan, float(self.temperature),
                                      float(self.base_temperature), bool(self.normalize), norms)
+
+    # ------------------------------------------------------------------ graph mode
+    _MAX_ADDRESSES = 4          # captured graphs bound to the caller's own input buffers, per shape
+
+    def _graphed(self, features, labels):
+        """Forward through a captured graph.  A graph is bound to the address of its input: callers that feed the loss
+        from a few recurring buffers (a double-buffered prefetcher, a preallocated projection output) get one graph
+        per buffer and no copy; any other input is copied into a buffer the module owns."""
+        dev = features.device
+        base = (tuple(features.shape), features.dtype, dev.index, tuple(features.stride()), labels is not None)
+        per_shape = self._graphs.setdefault(base, {})
+        addr = features.data_ptr()
+        entry = per_shape.get(addr)
+        if entry is None:
+            bound = [k for k in per_shape if k != 'own']
+            if len(bound) < self._MAX_ADDRESSES and features.is_contiguous():
+                entry = self._capture(features, labels, own_input=False)
+                per_shape[addr] = entry
+            else:
+                entry = per_shape.get('own')
+                if entry is None:
+                    entry = per_shape['own'] = self._capture(features, labels, own_input=True)
+        if labels is not None:
+            entry.labels.copy_(labels)
+        return _GraphedSupCon.apply(features, entry)
+
+    def _capture(self, features, labels, own_input):
+        inner = SupConLoss(self.temperature, self.contrast_mode, self.base_temperature, self.engine, self.normalize)
+        e = _GraphEntry()
+        e.own_input, e.serial = own_input, 0
+        e.x = (torch.empty_like(features) if own_input else features.detach())
+        e.labels = labels.clone() if labels is not None else None
+        leaf = e.x.detach().requires_grad_(True)
+        if own_input:
+            e.x.copy_(features.detach())
+        ones = torch.ones((), dtype=features.dtype, device=features.device)
+        side = torch.cuda.Stream(device=features.device)
+        side.wait_stream(torch.cuda.current_stream(features.device))
+        with torch.cuda.stream(side):                      # warm-up outside the capture: builds, workspaces, descriptors
+            for _ in range(2):
+                leaf.grad = None
+                inner(leaf, labels=e.labels).backward(ones)
+        torch.cuda.current_stream(features.device).wait_stream(side)
+        leaf.grad = None
+        e.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(e.graph):
+            loss = inner(leaf, labels=e.labels)
+            loss.backward(ones)
+        e.loss, e.grad = loss.detach(), leaf.grad
+        return e

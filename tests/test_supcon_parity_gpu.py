@@ -171,3 +171,34 @@ def test_feature_norm_side_outputs_and_regularisers(dtype):
         assert abs(float(loss) - float(ref)) <= ltol * abs(float(ref))
         gtol = 1e-4 if dtype == torch.float32 else 2e-3 + 2 ** -7
         assert rel_f(f.grad.double().cpu().numpy(), r.grad.cpu().numpy()) <= gtol
+
+
+def test_graph_mode_matches_eager():
+    """SupConLoss(graph=True): forward+backward replayed from a CUDA graph -- same loss and gradient as the eager
+    module, for recurring input buffers (no copy) and for fresh tensors (copied into the module's buffer), with and
+    without labels, and an upstream gradient different from 1."""
+    torch.manual_seed(8)
+    eager = SupConLoss(temperature=0.5, engine='bf16')
+    graphed = SupConLoss(temperature=0.5, engine='bf16', graph=True)
+    bufs = [torch.empty(512, 2, 128, dtype=torch.bfloat16, device='cuda') for _ in range(2)]
+    for step in range(7):
+        z = F.normalize(torch.randn(512, 2, 128, device='cuda'), dim=-1).to(torch.bfloat16)
+        if step < 4:
+            bufs[step % 2].copy_(z)
+            src = bufs[step % 2]                 # recurring addresses
+        else:
+            src = z.clone()                      # fresh tensors: more addresses than the module binds graphs to
+        labels = torch.randint(0, 20, (512,), device='cuda') if step % 3 == 2 else None
+        a = src.detach().clone().requires_grad_(True)
+        b = src.detach().requires_grad_(True)
+        la = eager(a, labels=labels)
+        (2.0 * la).backward()
+        lb = graphed(b, labels=labels)
+        (2.0 * lb).backward()
+        assert float(la) == float(lb)
+        assert torch.equal(a.grad, b.grad)
+    with pytest.raises(RuntimeError, match='followed by another forward'):
+        b1 = bufs[0].detach().requires_grad_(True)
+        l1 = graphed(b1)
+        graphed(bufs[0].detach().requires_grad_(True))
+        l1.backward()
