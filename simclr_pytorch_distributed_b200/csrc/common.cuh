@@ -62,7 +62,7 @@ inline cudaError_t set_max_dynamic_smem(Kern kern, int bytes) {
 // its prologue (barrier init, TMEM allocation, descriptor prefetch) and then blocks in pdl_wait() until the
 // previous grid has completed and its memory is visible.  RULE: a kernel launched through launch_pdl()
 // calls pdl_wait() in every thread before its first global-memory access.  Without the launch
-// attribute both instructions are no-ops.  SCB_PDL=0 in the environment turns the attribute off.
+// attribute both instructions are no-ops.  The attribute is only set with SCB_PDL=1 in the environment (api.cu).
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
