@@ -61,8 +61,10 @@ inline cudaError_t set_max_dynamic_smem(Kern kern, int bytes) {
 // programmatic stream serialisation: the next grid is scheduled while the previous one still runs, does
 // its prologue (barrier init, TMEM allocation, descriptor prefetch) and then blocks in pdl_wait() until the
 // previous grid has completed and its memory is visible.  RULE: a kernel launched through launch_pdl()
-// calls pdl_wait() in every thread before its first global-memory access.  Without the launch
-// attribute both instructions are no-ops.  The attribute is only set with SCB_PDL=1 in the environment (api.cu).
+// calls pdl_wait() in every thread before its first global-memory access, and reads what an earlier grid of
+// the chain wrote through coherent loads only (no __ldg, no `const T* __restrict__` parameter: ld.global.nc
+// promises data that does not change during the reading grid's lifetime, and that grid is already alive while
+// its predecessor writes).  Without the launch attribute both instructions are no-ops.  SCB_PDL=0 in the environment leaves the attribute off (api.cu).
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 

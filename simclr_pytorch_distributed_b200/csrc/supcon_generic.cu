@@ -11,12 +11,12 @@ namespace scb {
 
 // ------------------------------------------------------------------ prep (normalise + stack + cast)
 template <typename TI, typename TO>
-__device__ __forceinline__ void prep_row_impl(const TI* __restrict__ feat, int n_samples, int dim, int64_t stride_s,
+__device__ __forceinline__ void prep_row_impl(const TI* feat, int n_samples, int dim, int64_t stride_s,
                                               int64_t stride_v, int normalize, float eps, TO* __restrict__ out_k,
                                               __nv_bfloat16* __restrict__ out_lo, int ldk,
                                               float* __restrict__ out_inv_norm, int warp, int lane);
 template <typename TI, typename TO>
-__device__ __forceinline__ void prep_row(const TI* __restrict__ feat, int n_samples, int dim, int64_t stride_s,
+__device__ __forceinline__ void prep_row(const TI* feat, int n_samples, int dim, int64_t stride_s,
                                          int64_t stride_v, int normalize, float eps, TO* __restrict__ out_k,
                                          __nv_bfloat16* __restrict__ out_lo, int ldk, float* __restrict__ out_inv_norm,
                                          int warp, int lane) {
@@ -26,7 +26,7 @@ __device__ __forceinline__ void prep_row(const TI* __restrict__ feat, int n_samp
 
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256)
-supcon_prep_kernel(const TI* __restrict__ feat, int n_samples, int n_views, int dim,
+supcon_prep_kernel(const TI* feat, int n_samples, int n_views, int dim,
                    int64_t stride_s, int64_t stride_v, int normalize, float eps,
                    TO* __restrict__ out_k, __nv_bfloat16* __restrict__ out_lo, int ldk,
                    float* __restrict__ out_inv_norm, const PeerOut po, int64_t row_offset) {
@@ -51,7 +51,7 @@ supcon_prep_kernel(const TI* __restrict__ feat, int n_samples, int n_views, int 
 }
 
 template <typename TI, typename TO>
-__device__ __forceinline__ void prep_row_impl(const TI* __restrict__ feat, int n_samples, int dim, int64_t stride_s,
+__device__ __forceinline__ void prep_row_impl(const TI* feat, int n_samples, int dim, int64_t stride_s,
                                               int64_t stride_v, int normalize, float eps, TO* __restrict__ out_k,
                                               __nv_bfloat16* __restrict__ out_lo, int ldk,
                                               float* __restrict__ out_inv_norm, int warp, int lane) {
@@ -109,9 +109,9 @@ __device__ __forceinline__ void prep_row_impl(const TI* __restrict__ feat, int n
 // ------------------------------------------------------------------ finish (un-stack + normalise bwd)
 template <typename TF>
 __global__ void __launch_bounds__(256)
-supcon_finish_kernel(const float* __restrict__ dk, int ld_dk, const TF* __restrict__ feat,
+supcon_finish_kernel(const float* dk, int ld_dk, const TF* feat,
                      int n_samples, int n_views, int dim, int64_t stride_s, int64_t stride_v,
-                     int normalize, const float* __restrict__ inv_norm, TF* __restrict__ out,
+                     int normalize, const float* inv_norm, TF* __restrict__ out,
                      int64_t ostride_s, int64_t ostride_v) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const int n_rows = n_samples * n_views;
@@ -183,7 +183,7 @@ constexpr int kFinThreads = 256;
 constexpr int kFinMaxCtas = 480;
 
 __global__ void __launch_bounds__(kFinThreads)
-supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_q, int flat_ct, int n_rows,
+supcon_finalize_kernel(const float* part, int n_split_in, int flat_q, int flat_ct, int n_rows,
                        int row_begin,
                        RowMap map, int mode, float loss_scale, double inv_anchors,
                        float* __restrict__ out_lse,
@@ -297,7 +297,7 @@ supcon_finalize_kernel(const float* __restrict__ part, int n_split_in, int flat_
 // ------------------------------------------------------------------ fp32 engine: forward
 // CTA = 32 local rows x a strided set of 32-column tiles; warp ty owns row ty, lane tx a column.
 __global__ void __launch_bounds__(1024)
-supcon_fwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, RowMap map,
+supcon_fwd_fp32_kernel(const float* K, int ldk, int dim, int n_k, RowMap map,
                        MaskSpec msk, int mode, float inv_T, int row_begin, int n_rows,
                        float* __restrict__ part) {
     __shared__ float xs[32][33], ys[32][33];
@@ -348,10 +348,10 @@ supcon_fwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, R
 // H_ij = [i anchor] G_ij + [j anchor] G_ji, dK_i = (1/T) sum_j H_ij k_j; each CTA owns 32 local
 // rows and a 128-wide slice of the feature axis (blockIdx.z), so there are no atomics.
 __global__ void __launch_bounds__(1024)
-supcon_bwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, RowMap map,
+supcon_bwd_fp32_kernel(const float* K, int ldk, int dim, int n_k, RowMap map,
                        MaskSpec msk, int mode, float inv_T, float coef_scale,
-                       const float* __restrict__ grad_out, int grad_dtype, int row_begin, int n_rows,
-                       const float* __restrict__ lse_all, const float* __restrict__ npos_all,
+                       const float* grad_out, int grad_dtype, int row_begin, int n_rows,
+                       const float* lse_all, const float* npos_all,
                        float* __restrict__ out_dk, int ld_dk) {
     __shared__ float xs[32][33], ys[32][33], hs[32][33];
     const int tx = threadIdx.x, ty = threadIdx.y;
@@ -411,8 +411,8 @@ supcon_bwd_fp32_kernel(const float* __restrict__ K, int ldk, int dim, int n_k, R
 
 // ------------------------------------------------------------------ consumer side of a peer exchange
 __global__ void __launch_bounds__(32)
-peer_wait_kernel(const unsigned* __restrict__ flags, const unsigned* __restrict__ state, int n,
-                 const float* __restrict__ loss_shares, float* __restrict__ out_loss, int scalar_dtype) {
+peer_wait_kernel(const unsigned* flags, const unsigned* state, int n,
+                 const float* loss_shares, float* __restrict__ out_loss, int scalar_dtype) {
     pdl_launch_dependents();
     pdl_wait();
     const unsigned want = state[1];               // bumped by this rank's own producer, earlier in the stream
@@ -451,7 +451,7 @@ struct PeerBcastArgs {
 
 template <typename W>      // uint4 when every offset and size is a multiple of 16 bytes, else 32-bit words
 __global__ void __launch_bounds__(256)
-peer_bcast_kernel(const char* __restrict__ src, const PeerBcastArgs a) {
+peer_bcast_kernel(const char* src, const PeerBcastArgs a) {
     pdl_launch_dependents();
     pdl_wait();
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -653,7 +653,7 @@ extern "C" int scb_peer_wait(const uint32_t* flags_local, const uint32_t* state,
 namespace scb {
 
 __global__ void __launch_bounds__(1024)
-feature_norm_terms_kernel(const float* __restrict__ inv_norm, int n, float* record, float momentum, float w_sec,
+feature_norm_terms_kernel(const float* inv_norm, int n, float* record, float momentum, float w_sec,
                           float w_l2, float* __restrict__ out) {
     __shared__ double red[3][32];
     pdl_launch_dependents();
@@ -692,9 +692,9 @@ feature_norm_terms_kernel(const float* __restrict__ inv_norm, int n, float* reco
 // d features += upstream * [ w_sec * (2/n) (||z|| - record) / ||z|| + w_l2 * (2/n) ] * z      (one warp per row)
 template <typename TF>
 __global__ void __launch_bounds__(256)
-feature_norm_backward_kernel(const TF* __restrict__ feat, int n_samples, int n_views, int dim, int64_t stride_s,
-                             int64_t stride_v, const float* __restrict__ inv_norm, const float* __restrict__ record,
-                             float w_sec, float w_l2, const void* __restrict__ grad_out, int grad_dtype,
+feature_norm_backward_kernel(const TF* feat, int n_samples, int n_views, int dim, int64_t stride_s,
+                             int64_t stride_v, const float* inv_norm, const float* record,
+                             float w_sec, float w_l2, const void* grad_out, int grad_dtype,
                              TF* __restrict__ dfeat, int64_t ostride_s, int64_t ostride_v) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     pdl_launch_dependents();

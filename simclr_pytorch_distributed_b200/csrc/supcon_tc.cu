@@ -95,7 +95,6 @@ struct TcParams {
     int ld_dk;
     float* dk_part;                     // backward partials [slot][RB*128][ldk] (one slot per CTA sharing a row block)
     int pair;                           // backward, direct finish: CTAs per row block (1, or 2 = a cluster pair)
-    int dbg;                            // timing experiments only (SCB_DBG): skip parts of the tails, results are wrong
     FwdOut fo;
     FinishParams fin;
     long long* trace;                   // optional (debug): per-role timestamps of CTA 0
@@ -484,14 +483,13 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             }
             // row-block ticket: the CTA that delivers the last partials of the block merges them (fwd_merge_rows)
             const int n_cta = ((rb + 1) * p.CT - 1) / p.q - first_cta + 1;
-            if (p.dbg & 16) return;
             named_bar_sync(1, 512);                       // all partial stores of this CTA are issued ...
             if (threadIdx.x == 64) {
                 __threadfence();                          // ... and made visible before the ticket (cumulative)
                 *s_ticket = atomicAdd(p.fo.rb_count + rb, 1u);
             }
             named_bar_sync(1, 512);
-            if (*s_ticket == (unsigned)n_cta - 1u && !(p.dbg & 8)) fwd_merge_rows(*sp, rb, n_cta, s_red);
+            if (*s_ticket == (unsigned)n_cta - 1u) fwd_merge_rows(*sp, rb, n_cta, s_red);
         };
 
         // incremental tile bookkeeping (no division per tile); one copy of the flush and of the chunk code:
@@ -557,7 +555,7 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                         float pacc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                         for (int c4 = 0; c4 < 8; ++c4) {
-                            const int4 rj = __ldg(reinterpret_cast<const int4*>(p.rep_row + jc) + c4);
+                            const int4 rj = __ldcg(reinterpret_cast<const int4*>(p.rep_row + jc) + c4);
                             pacc[0] += (rj.x == rep_i) ? __uint_as_float(v[c4 * 4 + 0]) : 0.f;
                             pacc[1] += (rj.y == rep_i) ? __uint_as_float(v[c4 * 4 + 1]) : 0.f;
                             pacc[2] += (rj.z == rep_i) ? __uint_as_float(v[c4 * 4 + 2]) : 0.f;
@@ -1083,17 +1081,17 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
     const int rb0 = t0 / p.CT, ct0 = t0 - rb0 * p.CT;
     // reference point of the 1-exp path: P_ij = 2^(s - l_i) (1 + R_i C_j), R_i = 2^(l_i - m0), C_j = 2^(m0 - l_j);
     // any m0 works as long as every |l - m0| stays below kSafeSpread, so one global value does
-    const float m0 = __ldg(p.lse_all) * kLog2e;
+    const float m0 = __ldcg(p.lse_all) * kLog2e;     // coherent loads: see pdl_wait() in common.cuh
 
     if (warp == 0) {
         // ---------------------------------------------------- TMA producer + column factors
         auto load_lse4 = [&](int ct_) {
             const int j = ct_ * kBN + lane * 4;
             float4 l;
-            l.x = (j + 0 < p.n_k) ? __ldg(p.lse_all + j + 0) : 0.f;
-            l.y = (j + 1 < p.n_k) ? __ldg(p.lse_all + j + 1) : 0.f;
-            l.z = (j + 2 < p.n_k) ? __ldg(p.lse_all + j + 2) : 0.f;
-            l.w = (j + 3 < p.n_k) ? __ldg(p.lse_all + j + 3) : 0.f;
+            l.x = (j + 0 < p.n_k) ? __ldcg(p.lse_all + j + 0) : 0.f;
+            l.y = (j + 1 < p.n_k) ? __ldcg(p.lse_all + j + 1) : 0.f;
+            l.z = (j + 2 < p.n_k) ? __ldcg(p.lse_all + j + 2) : 0.f;
+            l.w = (j + 3 < p.n_k) ? __ldcg(p.lse_all + j + 3) : 0.f;
             return l;
         };
         // the log-sum-exps of a tile's columns are fetched three tiles ahead: a load issued and consumed in
@@ -1423,8 +1421,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
         float* recv = own + 128 * pitch;
         const int rb_d = rb0;
         const uint32_t crank = (p.pair == 2) ? cluster_ctarank() : 0u;
-        if (p.pair == 2 && !(p.dbg & 4)) cluster_sync_all();               // the partner, too, is done with its B stages
-        if (warp >= 2 && warp < 18 && !(p.dbg & 2)) {
+        if (p.pair == 2) cluster_sync_all();               // the partner, too, is done with its B stages
+        if (warp >= 2 && warp < 18) {
             const int g = (warp - 2) >> 2, q4 = warp & 3;
             tc_fence_after();
             if (g * 32 < ND) {
@@ -1439,8 +1437,8 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                 }
             }
         }
-        if (p.pair == 2 && !(p.dbg & 4)) cluster_sync_all(); else __syncthreads();
-        if (warp >= 2 && warp < 18 && !(p.dbg & 1)) {
+        if (p.pair == 2) cluster_sync_all(); else __syncthreads();
+        if (warp >= 2 && warp < 18) {
             if (p.pair == 2) finish_staged(*sp, own, recv, pitch, rb_d * kBMB + (int)crank * 64, 64, warp - 2, lane);
             else finish_staged(*sp, own, nullptr, pitch, rb_d * kBMB, 128, warp - 2, lane);
         }
@@ -1464,7 +1462,7 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
 // -- the fp32 closed form of the positive-pair part of the gradient (positive_term above).
 __global__ void __launch_bounds__(256)
 label_rows_kernel(const int64_t* __restrict__ labels, int n_samples, RowMap map, int n_views, int mode,
-                  const __nv_bfloat16* __restrict__ k, const __nv_bfloat16* __restrict__ k_lo, int ldk,
+                  const __nv_bfloat16* k, const __nv_bfloat16* k_lo, int ldk,
                   int* __restrict__ rep_row,
                   float* __restrict__ npos_row, float* __restrict__ nia_row, float* __restrict__ cls_all,
                   float* __restrict__ cls_anc) {
@@ -1761,7 +1759,6 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
     t->fo.po = PeerOut::none();
     t->dk_part = w.dk_part;
     t->pair = 0;
-    { const char* e = getenv("SCB_DBG"); t->dbg = e ? atoi(e) : 0; }
     t->trace = g_trace;
 }
 

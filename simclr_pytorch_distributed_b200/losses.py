@@ -294,7 +294,7 @@ class _SupConFunction(torch.autograd.Function):
 
 class _GraphEntry:
     """One captured forward+backward of the loss for a fixed (shape, dtype, options, input address)."""
-    __slots__ = ('graph', 'x', 'labels', 'loss', 'grad', 'serial', 'own_input')
+    __slots__ = ('graph', 'x', 'labels', 'ones', 'loss', 'grad', 'serial', 'own_input')
 
 
 class _GraphedSupCon(torch.autograd.Function):
@@ -448,7 +448,8 @@ class SupConLoss(nn.Module):
         leaf = e.x.detach().requires_grad_(True)
         if own_input:
             e.x.copy_(features.detach())
-        ones = torch.ones((), dtype=features.dtype, device=features.device)
+        # every tensor the graph reads by address lives as long as the entry: input, labels, the upstream-gradient scalar
+        ones = e.ones = torch.ones((), dtype=features.dtype, device=features.device)
         side = torch.cuda.Stream(device=features.device)
         side.wait_stream(torch.cuda.current_stream(features.device))
         with torch.cuda.stream(side):                      # warm-up outside the capture: builds, workspaces, descriptors

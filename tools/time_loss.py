@@ -58,6 +58,14 @@ for it in range(10):
     torch.cuda.synchronize()
     if it >= 2:
         tf += ef[0].elapsed_time(ef[1]); tb += ef[1].elapsed_time(ef[2])
-print('SCB_DBG=%s SCB_BWD_DIRECT=%s B=%d launches=%d graph step %.2f us  (eager apart: fwd %.1f us, bwd %.1f us)  loss %.4f' % (
-    os.environ.get('SCB_DBG', '0'), os.environ.get('SCB_BWD_DIRECT', '1'), B, launches, per, tf / 8 * 1e3, tb / 8 * 1e3,
-    float(crit(zs[0]))))
+# eager steps back to back (host-bound: what a training loop without graphs pays per step)
+import time
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for i in range(100):
+    step(i)
+torch.cuda.synchronize()
+eager_us = (time.perf_counter() - t0) / 100 * 1e6
+print('SCB_PDL=%s SCB_BWD_DIRECT=%s B=%d launches=%d graph step %.2f us  eager step %.1f us (apart: fwd %.1f us, bwd %.1f us)  loss %.4f' % (
+    os.environ.get('SCB_PDL', '1'), os.environ.get('SCB_BWD_DIRECT', '1'), B, launches, per, eager_us, tf / 8 * 1e3, tb / 8 * 1e3,
+    float(crit(zs[0].detach()))))
