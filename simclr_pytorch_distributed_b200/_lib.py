@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, 'csrc')
 ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(CSRC, 'libsimclr_b200.so')
-SOURCES = ['api.cu', 'bn.cu', 'bn_cluster.cu', 'supcon_generic.cu', 'supcon_tc.cu']
+SOURCES = ['api.cu', 'bn.cu', 'bn_cluster.cu', 'bn_ring.cu', 'supcon_generic.cu', 'supcon_tc.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
 

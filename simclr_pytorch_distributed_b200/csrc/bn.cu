@@ -20,6 +20,8 @@
 #include <mutex>
 #include <utility>
 
+#include "bn_ring.cuh"
+
 namespace scb {
 
 constexpr int kBnThreads = 256;
@@ -673,9 +675,14 @@ static int check_bn_common(const void* x, int dtype, int64_t outer, int channels
 
 using namespace scb;
 
+// scratch of the tiled / NCHW kernels: [2C] float accumulators + tickets
+static int64_t legacy_ws_bytes(int channels) { return bn_ws_counter_offset(channels) + 16; }
+
+// [scratch of the tiled kernels][scratch of the ring kernels (bn_ring.cu)]; a caller that passes only the first part
+// (scb_bn_stats_noalloc does) gets the tiled kernels
 extern "C" int64_t scb_bn_workspace_bytes(int channels) {
     if (channels <= 0) return 0;
-    return bn_ws_counter_offset(channels) + 16;
+    return legacy_ws_bytes(channels) + ring_ws_bytes(channels);
 }
 
 #define SCB_VEC_SWITCH(vecv, VEC_, ...)                                   \
@@ -687,12 +694,17 @@ extern "C" int scb_bn_stats(const void* x, int dtype, int channels_last, int64_t
                             void* stream_) {
     if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
     SCB_REQUIRE(out_stats && workspace, "bn_stats: null output/workspace");
-    SCB_REQUIRE(workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_stats: workspace too small");
+    SCB_REQUIRE(workspace_bytes >= legacy_ws_bytes(channels), "bn_stats: workspace too small");
     cudaStream_t stream = (cudaStream_t)stream_;
     const int C = channels;
     if (outer * inner == 0) {   // empty slice still sends a zero message (_functions.py:50-57)
         SCB_CUDA_OK(cudaMemsetAsync(out_stats, 0, (2 * C + 1) * sizeof(float), stream));
         return SCB_OK;
+    }
+    if (channels_last) {
+        const int r = ring_stats(x, dtype, outer * inner, C, out_stats, (char*)workspace + legacy_ws_bytes(C),
+                                 workspace_bytes - legacy_ws_bytes(C), stream);
+        if (r != kRingUnsupported) return r;
     }
     float* acc = (float*)workspace;
     unsigned* counter = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
@@ -735,6 +747,11 @@ extern "C" int scb_bn_apply(const void* x, const void* z, void* y, int dtype, in
     cudaStream_t stream = (cudaStream_t)stream_;
     const int C = channels;
     if (outer * inner == 0) return SCB_OK;
+    if (channels_last) {
+        const int r = ring_apply(x, z, y, dtype, outer * inner, C, stats_all, n_ranks, weight, bias, running_mean,
+                                 running_var, momentum, eps, save_mean, save_invstd, save_count, flags, stream);
+        if (r != kRingUnsupported) return r;
+    }
     const int target = 4 * sm_count();
     const bool al = aligned16(x) && aligned16(y) && (!add || aligned16(z));
     SCB_DISPATCH_FLOAT(dtype, T, {
@@ -789,7 +806,7 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, const void*
                                       void* workspace, int64_t workspace_bytes, void* stream_) {
     if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
     SCB_REQUIRE(dy && mean && invstd && out_sums && workspace, "bn_backward_reduce: null pointer");
-    SCB_REQUIRE(workspace_bytes >= scb_bn_workspace_bytes(channels), "bn_backward_reduce: workspace too small");
+    SCB_REQUIRE(workspace_bytes >= legacy_ws_bytes(channels), "bn_backward_reduce: workspace too small");
     const int gate = gate_mode(flags);
     SCB_REQUIRE(gate != 2 || y != nullptr, "bn_backward_reduce: SCB_BN_RELU|SCB_BN_ADD needs the saved output y");
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -799,6 +816,12 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, const void*
         if (grad_weight) SCB_CUDA_OK(cudaMemsetAsync(grad_weight, 0, C * sizeof(float), stream));
         if (grad_bias) SCB_CUDA_OK(cudaMemsetAsync(grad_bias, 0, C * sizeof(float), stream));
         return SCB_OK;
+    }
+    if (channels_last) {
+        const int r = ring_backward_reduce(dy, x, y, dtype, outer * inner, C, mean, invstd, weight, bias, out_sums,
+                                           grad_weight, grad_bias, gate, (char*)workspace + legacy_ws_bytes(C),
+                                           workspace_bytes - legacy_ws_bytes(C), stream);
+        if (r != kRingUnsupported) return r;
     }
     float* acc = (float*)workspace;
     unsigned* counter = (unsigned*)((char*)workspace + bn_ws_counter_offset(C));
@@ -843,6 +866,11 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* 
     cudaStream_t stream = (cudaStream_t)stream_;
     const int C = channels;
     if (outer * inner == 0) return SCB_OK;
+    if (channels_last) {
+        const int r = ring_backward_apply(dy, x, y, dx, dz, dtype, outer * inner, C, mean, invstd, weight, bias, sums,
+                                          n_total, gate, stream);
+        if (r != kRingUnsupported) return r;
+    }
     const int target = 4 * sm_count();
     const bool al = aligned16(x) && aligned16(dy) && aligned16(dx) && (gate != 2 || aligned16(y)) &&
                     (dz == nullptr || aligned16(dz));
@@ -884,7 +912,7 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* 
 // host-side stand-in only: the device address is looked up once per device with
 // cudaGetSymbolAddress while that device is current, and that address is what the kernel receives.
 constexpr int kNoAllocMaxChannels = SCB_BN_NOALLOC_MAX_CHANNELS;
-constexpr size_t kNoAllocScratchBytes = (size_t)2 * kNoAllocMaxChannels * sizeof(float) + 256;   // >= scb_bn_workspace_bytes(c) for c <= max
+constexpr size_t kNoAllocScratchBytes = (size_t)2 * kNoAllocMaxChannels * sizeof(float) + 256;   // >= legacy_ws_bytes(c) for c <= max
 static __device__ __align__(256) unsigned char g_bn_noalloc_scratch[kNoAllocScratchBytes];
 
 #include <mutex>
@@ -915,7 +943,7 @@ extern "C" int scb_bn_stats_noalloc(const void* x, int dtype, int channels_last,
     cudaStream_t stream = (cudaStream_t)stream_;
     // The array is shared by every call and keeps whatever the last one left behind; the kernel needs
     // its accumulators and ticket to start at zero, so clear the part this call uses.
-    const int64_t need = scb_bn_workspace_bytes(channels);
+    const int64_t need = legacy_ws_bytes(channels);      // the built-in array holds the tiled kernels' scratch only
     SCB_CUDA_OK(cudaMemsetAsync(scratch, 0, (size_t)need, stream));
     return scb_bn_stats(x, dtype, channels_last, outer, channels, inner, out_stats, scratch, need, stream_);
 }

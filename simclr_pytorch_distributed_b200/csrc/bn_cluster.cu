@@ -25,6 +25,26 @@ constexpr int kClThreads = 512;    // one CTA per SM; 128 registers per thread: 
 constexpr int kClRows = 8;         // rows a thread keeps in registers (per tensor); 16 in the large forward variant
 constexpr int kClMaxCS = 16;
 
+// Timeline instrumentation (tools/trace_bn.py): compiled in only with -DSCB_TRACE=1 (tools/build_trace_lib.sh).
+#ifndef SCB_TRACE
+#define SCB_TRACE 0
+#endif
+#if SCB_TRACE
+__device__ long long* g_bn_trace = nullptr;            // [CTA][8] globaltimer stamps
+__device__ __forceinline__ void bn_stamp(int slot, float dep = 0.f) {
+    if (g_bn_trace != nullptr && threadIdx.x == 0) {
+        long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "f"(dep) : "memory");     // `dep`: not before this value exists
+        g_bn_trace[blockIdx.x * 8 + slot] = t;
+    }
+}
+extern "C" int scb_debug_set_bn_trace(long long* p) {
+    return cudaMemcpyToSymbol(g_bn_trace, &p, sizeof(p)) == cudaSuccess ? 0 : -1;
+}
+#else
+#define bn_stamp(...) ((void)0)
+#endif
+
 __device__ __forceinline__ uint32_t cl_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ uint32_t cl_ctarank() {
     uint32_t r;
@@ -117,6 +137,7 @@ bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __res
     const int64_t r_end = min(M, r_begin + g.rows_per_cta);
     const int64_t r0 = r_begin + ty;
     const int64_t step = (int64_t)TY * C;
+    bn_stamp(0);
     uint4 raw[ROWS], rz[ROWS];
     float s1[VEC], s2[VEC], k0[VEC];
 #pragma unroll
@@ -134,6 +155,7 @@ bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __res
                 if (u < nrow) rz[u] = ldg_stream16(pz + u * step);
         }
         load_row_vec_cached<T, VEC>(x + c0, k0);       // common shift K_c = x[0, c]: no E[x^2] - E[x]^2 cancellation
+        bn_stamp(1);
 #pragma unroll
         for (int u = 0; u < ROWS; ++u) {
             if (u < nrow) {
@@ -147,7 +169,9 @@ bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __res
             }
         }
     }
+    bn_stamp(2, s1[0] + s2[0]);
     const float tot = cluster_channel_sums<VEC>(s1, s2, sm, gath, TX, CS, rank);
+    bn_stamp(3, tot);
     // threads j < CW own channel slab*CW + j: tot = S1 there, S2 sits in thread j + CW -> through shared memory
     if ((int)threadIdx.x < 2 * CW) ab[threadIdx.x] = tot;
     __syncthreads();
@@ -204,6 +228,7 @@ bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __res
             stg_stream16(q + u * step, o);
         }
     }
+    bn_stamp(4);
 }
 
 // ------------------------------------------------------------------ backward
@@ -231,6 +256,7 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
     const int64_t r_end = min(M, r_begin + g.rows_per_cta);
     const int64_t r0 = r_begin + ty;
     const int64_t step = (int64_t)TY * C;
+    bn_stamp(0);
     uint4 rx[kClRows], rd[kClRows];
     unsigned gated[kClRows];               // bit i set: element i of the row is gated off (dy dropped)
     float s1[VEC], s2[VEC];
@@ -247,6 +273,7 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
                 rd[u] = ldg_stream16(pd + u * step);
                 nrow = u + 1;
             }
+        bn_stamp(1);
 #pragma unroll
         for (int u = 0; u < kClRows; ++u) gated[u] = 0u;
         if (kGate == 2) {
@@ -287,7 +314,9 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
             }
         }
     }
+    bn_stamp(2, s1[0] + s2[0]);
     const float tot = cluster_channel_sums<VEC>(s1, s2, sm, gath, TX, CS, rank);
+    bn_stamp(3, tot);
     if ((int)threadIdx.x < 2 * CW) ab[threadIdx.x] = tot;
     __syncthreads();
     float v2 = 0.f, v3 = 0.f;
@@ -342,6 +371,7 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
             if (kGate == 2 && pz != nullptr) stg_stream16(pz + u * step, oz);
         }
     }
+    bn_stamp(4);
 }
 
 // =================================================================== streaming cluster kernels
@@ -744,8 +774,11 @@ static int cl_pick(int64_t M, int C, int es, int which, int flags) {
     const int rows = (which == 0 && !add) ? 2 * kClRows : kClRows;
     const bool reg_ok = cl_geom(M, C, es, rows, &g);
     const double bytes = (double)M * C * es;
-    // the second pass must come out of the L2: x (+ z) and y forward, x, dy (+ y) and dx backward
-    const double l2_budget = 96e6;
+    // the second pass must come out of the L2: x (+ z) and y forward, x, dy (+ y) and dx backward.  Beyond ~56 MB of
+    // resident tensors the two-launch ring kernels (bn_ring.cu) are faster: measured on B200, fwd+bwd in a CUDA graph,
+    // [512,512,8,8] bf16 (32 MiB) streamed 79.5 us / ring 61.0 us; [512,256,8,8] (16 MiB) 41.8 / 41.7;
+    // [512,1024,4,4] (16 MiB, wide slabs) 31.3 / 42.9
+    const double l2_budget = 56e6;
     const double resident = which == 0 ? bytes * (add ? 3 : 2) : bytes * (((flags & SCB_BN_RELU) && add) ? 4 : 3);
     const bool stream_ok = resident <= l2_budget && cl_stream_geom(M, C, es, &gs);
     if (forced == 1) return reg_ok ? 1 : 0;

@@ -1,0 +1,27 @@
+// SyncBatchNorm, channels-last streaming passes fed by bulk copies (bn_ring.cu).  Host entry points used by the
+// C-ABI functions of bn.cu; each returns SCB_OK, an error, or kRingUnsupported (the caller then takes its own kernels).
+#pragma once
+#include "common.cuh"
+
+namespace scb {
+
+constexpr int kRingUnsupported = 1;
+constexpr int kRingReplicas = 4;          // copies of the per-channel accumulators (spreads the L2 atomics)
+
+// bytes of the ring kernels' scratch (accumulator replicas + ticket); zero on entry, zero again on exit
+__host__ __device__ inline int64_t ring_ws_bytes(int C) { return (int64_t)kRingReplicas * 2 * C * 4 + 16; }
+
+int ring_stats(const void* x, int dtype, int64_t M, int C, float* out_stats, void* ws, int64_t ws_bytes,
+               cudaStream_t stream);
+int ring_apply(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* stats_all, int n_ranks,
+               const float* weight, const float* bias, float* running_mean, float* running_var, float momentum,
+               float eps, float* save_mean, float* save_invstd, float* save_count, int flags, cudaStream_t stream);
+int ring_backward_reduce(const void* dy, const void* x, const void* y, int dtype, int64_t M, int C, const float* mean,
+                         const float* invstd, const float* weight, const float* bias, float* out_sums,
+                         float* grad_weight, float* grad_bias, int gate, void* ws, int64_t ws_bytes,
+                         cudaStream_t stream);
+int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
+                        const float* mean, const float* invstd, const float* weight, const float* bias,
+                        const float* sums, const float* n_total, int gate, cudaStream_t stream);
+
+}  // namespace scb

@@ -56,7 +56,7 @@ __device__ __forceinline__ unsigned long long wall_ns() {
 // sub-partition counters fall behind while its warps are parked.)
 // The slow path is kept out of line: the kernels wait in dozens of places and their code must stay inside
 // the instruction cache (a taken branch into cold code costs an L2 round trip).
-__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
+static __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
     unsigned long long t0 = 0;
     for (uint32_t spins = 1;; ++spins) {
         if (mbar_try_wait_park(bar, parity, 100000u)) return;

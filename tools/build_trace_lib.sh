@@ -8,6 +8,9 @@ mkdir -p tools/bin
 cd simclr_pytorch_distributed_b200/csrc
 nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr \
      -DSCB_TRACE=1 -c supcon_tc.cu -o ../../tools/bin/tc_trace.o
+nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr \
+     -DSCB_TRACE=1 -c bn_cluster.cu -o ../../tools/bin/bn_cluster_trace.o
 nvcc -shared -o ../../tools/bin/libtrace.so api.o bn.o supcon_generic.o ../../tools/bin/tc_trace.o \
+     ../../tools/bin/bn_cluster_trace.o \
      -gencode arch=compute_100a,code=sm_100a
 echo "built tools/bin/libtrace.so"
