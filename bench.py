@@ -212,7 +212,7 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
     # copy of step i+1 is issued on a side stream before step i computes (what a training loop's prefetcher
     # does), so it overlaps the kernels; the gradient stays on the device, where the encoder's backward
     # consumes it (reading the 2 MiB gradient back every step would only measure PCIe).
-    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+    loss_host = torch.empty((), dtype=dtype).pin_memory()     # the loss has the features' dtype (losses.py:91)
     copy_stream = torch.cuda.Stream()
     slots = [torch.empty(b_local, N_VIEWS, DIM, dtype=dtype, device='cuda') for _ in range(2)]
     ready = [torch.cuda.Event() for _ in range(2)]          # H2D of the slot has landed
@@ -239,11 +239,11 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
         loss = fwd_e2e(f)
         loss.backward()
         freed[i % 2].record(cur)
-        loss_host.copy_(loss.detach().float(), non_blocking=True)
+        loss_host.copy_(loss.detach(), non_blocking=True)
         cur.synchronize()                                     # the caller reads the loss every step
 
     nbytes = b_local * N_VIEWS * DIM * host[0].element_size()
-    return step_resident, step_e2e, nbytes, 4, b_local
+    return step_resident, step_e2e, nbytes, loss_host.element_size(), b_local
 
 
 def loss_kernel_breakdown(engine, steps):

@@ -309,7 +309,9 @@ class _GraphedSupCon(torch.autograd.Function):
         entry.graph.replay()
         entry.serial += 1
         ctx.entry, ctx.serial = entry, entry.serial
-        return entry.loss.clone()
+        # the graph's own output buffer (as torch.cuda.make_graphed_callables does): no copy kernel; the next call of
+        # the same shape overwrites it
+        return entry.loss.detach()
 
     @staticmethod
     def backward(ctx, grad_out):
@@ -352,7 +354,9 @@ class SupConLoss(nn.Module):
                  engine='auto', normalize=False, track_norms=False, norm_momentum=0.1, graph=False):
         super(SupConLoss, self).__init__()
         # graph=True: forward + backward of a call are captured once per (shape, dtype, labels?) in a CUDA graph and
-        # replayed afterwards (see _GraphedSupCon); for training loops whose step is bound by host launch overhead
+        # replayed afterwards (see _GraphedSupCon); for training loops whose step is bound by host launch overhead.
+        # As with torch.cuda.make_graphed_callables the returned loss is the graph's own output buffer: read it
+        # (.item(), a copy) before the next call with the same shape overwrites it.
         self.graph = graph
         self._graphs = {}
         self.temperature = temperature

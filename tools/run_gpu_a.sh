@@ -1,6 +1,3 @@
 #!/bin/bash
-timeout 900 python -m pytest tests/test_syncbn_gpu.py tests/test_zz_no_alloc.py -x -q -m gpu 2>&1 | tail -3 > gpurun_out/r2p_t.log
-for s in "512 1024 8 8" "512 2048 4 4" "512 256 8 8" "512 512 8 8" "512 128 16 16" "512 1024 4 4"; do
-  SCB_BN_FUSED_MODE=reg timeout 200 python tools/time_bn.py $s 2>&1 | grep shape | sed 's/^/ring: /'
-  timeout 200 python tools/time_bn.py $s 2>&1 | grep shape | sed 's/^/dflt: /'
-done > gpurun_out/r2p_tb.log 2>&1
+timeout 900 python bench.py --workload syncbn-census --steps 20 --warmup 3 > gpurun_out/r2r_census.log 2> gpurun_out/r2r_census.err
+timeout 900 python -m pytest tests/test_syncbn_gpu.py tests/test_model_gpu.py tests/test_peer_gpu.py -x -q -m gpu 2>&1 | tail -3 > gpurun_out/r2r_t.log
