@@ -15,9 +15,13 @@
 //
 // Reference being replaced: /root/reference/losses.py:64-91 and its autograd backward.
 // Work split: the RB x CT tile grid is flattened row-block-major and cut into equal spans, one
-// per CTA (persistent, one CTA per SM); partial row results of CTAs that share a row block are
-// merged by the finalize kernel (forward) or summed from per-CTA partial dK blocks by the reduce
-// kernels (backward): no float atomics anywhere.
+// per CTA (persistent, one CTA per SM).  Forward: CTAs that share a row block leave (max, sum, possum, npos)
+// partials; the last of them (ticket per row block) merges them in the same kernel and the last row block
+// writes the scalar loss (fwd_merge_rows) -- no finalize kernel.  Backward: a row block is shared by at most two
+// CTAs, launched as a cluster pair; the two dK halves meet over distributed shared memory and each CTA turns
+// half of the rows into d features (finish_staged) -- no reduce kernel, no partial dK in global memory (spans
+// that do not line up with row blocks fall back to per-CTA partial blocks + supcon_tc_reduce_finish).
+// No float atomics anywhere: results are bitwise reproducible.
 #include "supcon_tc.cuh"
 #include "supcon_common.cuh"
 #include "tc_ptx.cuh"
