@@ -591,6 +591,53 @@ def gpu_bn_baseline(world, steps=20, pool=12):
     return {'ms_per_step': ms, 'value': 8.0 * S / (ms * 1e-3) / 1e9, 'unit': 'GB/s per GPU', 'what': what}
 
 
+def head_tail_bench(iters=20):
+    """the projection-head tail at the cfg-3 size (512 samples x 2 views per GPU, 2048 -> 128, bf16),
+    this library's one kernel against the torch ops it replaces (Linear, normalize, view stacking), both as CUDA
+    graphs of `iters` forward calls; the step that follows (loss on the tail's output, used in place) is not part of
+    it."""
+    import torch
+    import torch.nn.functional as F
+    from simclr_pytorch_distributed_b200 import ProjectionTail
+    M, K, N = 1024, 2048, 128
+    hs = [torch.relu(torch.randn(M, K, device='cuda')).to(torch.bfloat16) for _ in range(8)]
+    lin = torch.nn.Linear(K, N).cuda().to(torch.bfloat16)
+    tail = ProjectionTail.from_linear(lin, n_views=2)
+
+    def ours(i):
+        return tail(hs[i % 8])
+
+    def stock(i):
+        y = F.normalize(lin(hs[i % 8]), dim=1)
+        return torch.cat([y[:M // 2].unsqueeze(1), y[M // 2:].unsqueeze(1)], dim=1)      # main_supcon.py:285-286
+
+    out = {}
+    with torch.no_grad():
+        for name, fn in (('ours_us', ours), ('torch_us', stock)):
+            for i in range(3):
+                fn(i)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for i in range(iters):
+                    fn(i)
+            g.replay()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(5):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            out[name] = e0.elapsed_time(e1) / (5 * iters) * 1e3
+        err = float((ours(0).float() - stock(0).float()).abs().max())
+    out['max_abs_diff_vs_torch_bf16'] = err
+    out['what'] = ('normalize(Linear(h)) + view stacking, h [1024, 2048] bf16 -> [512, 2, 128] bf16: one tcgen05 kernel '
+                   '(split-K over a cluster of 8, DSMEM reduction, norm in the epilogue) vs cuBLAS + 4 torch kernels')
+    return out
+
+
+
 # ----------------------------------------------------------------------------- configs[2]: the model-level step
 def run_model(args, world, rank):
     """BASELINE configs[2]: SimCLR ResNet-50 + MLP head (tests/carrier_resnet.py restates networks/resnet_big.py),
@@ -905,6 +952,8 @@ def main():
             # SURVEY 8(d) Metric 1 as the reference calls it: RAW fp32 embeddings, the fused F.normalize, engine
             # 'auto' = the split-bf16 tensor-core engine at the reference's precision (1e-4)
             out['ntxent_fp32'] = loss_fp32_variant(args, pk)
+        if rank == 0 and world == 1:
+            out['projection_tail'] = head_tail_bench()
         if rank == 0 and not args.no_gpu_baseline:
             out['gpu_baseline'] = gpu_loss_baseline()
             out['gpu_baseline']['ours_over_gpu_baseline_fp32'] = out['value'] / out['gpu_baseline']['fp32']['value']

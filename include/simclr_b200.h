@@ -241,6 +241,28 @@ int scb_supcon_forward_peers(const scb_supcon_problem* p, int row_begin, int n_r
 int scb_peer_wait(const uint32_t* flags_local, const uint32_t* state, int n, const float* loss_shares,
                   float* out_loss, int scalar_dtype, void* stream);
 
+/* Projection-head tail: out = normalise(h W^T + bias) in one tcgen05 kernel.
+ * Replaces `F.normalize(self.head[2](feat), dim=1)`, /root/reference/networks/resnet_big.py:168-172,177-181 (the
+ * second F.normalize of main_supcon.py:283 is then the identity).  h [m, k] and w [n, k] are bf16, row strides
+ * ld_h / ld_w in elements (multiples of 8); n <= 128, a multiple of 4; bias [n] fp32 or NULL.  out [m, n] in
+ * out_dtype with row stride ld_out; bf16 rows with n in {64, 128} are what the loss takes in place
+ * (SCB_ROWS_SAMPLE_MAJOR).  inv_norm [m] (may be NULL) receives 1 / max(||row||, eps) for the backward.
+ * normalize == 0: plain Linear.  Products are bf16 x bf16 accumulated in fp32 (what autocast runs).
+ * n_views > 1: the m input rows are view-major ([n_views][m / n_views], the encoder ran on cat([view0, view1]),
+ * main_supcon.py:259-262) and output row b * n_views + v receives input row v * (m / n_views) + b -- the stacking of
+ * main_supcon.py:285-286 done by the store, so `out` is the loss's [bsz, n_views, n] tensor.  inv_norm stays in input
+ * row order. */
+int scb_head_forward(const void* h, int64_t ld_h, const void* w, int64_t ld_w, const float* bias, int64_t m, int k,
+                     int n, int n_views, void* out, int out_dtype, int64_t ld_out, float* inv_norm, int normalize,
+                     float eps, void* stream);
+/* Backward of the row normalisation: out = (g - y (g . y)) * inv_norm per row; g is the gradient with respect to the
+ * normalised rows y (what scb_supcon_backward_features returns); with n_views > 1 g and y are in the sample-major
+ * row order scb_head_forward wrote and `out` is back in input row order.  The two weight / input GEMMs of the Linear's
+ * backward are plain library GEMMs on `out` (cuBLAS through torch.matmul in head.py). */
+int scb_head_normalize_backward(const void* g, int g_dtype, int64_t ld_g, const void* y, int y_dtype, int64_t ld_y,
+                                const float* inv_norm, int64_t m, int n, void* out, int out_dtype, int64_t ld_out,
+                                int n_views, void* stream);
+
 /* Peer-memory exchange of the row-sharded loss (replaces the `gather_from_all` / all_gather calls of
  * main_supcon.py:268-279 on one NVLink/NVSwitch box).  Copies up to 4 byte ranges of `src` into EVERY
  * destination buffer (the caller's own and its peers', mapped into this process with symmetric / IPC
@@ -259,7 +281,10 @@ int scb_peer_bcast(const void* src, const int64_t* seg, int n_seg, const void* c
  *                  0 -> memory is [N, C, HW] contiguous (NCHW; inner = HW).
  */
 
-/* bytes of zero-initialised scratch for the two reduction kernels below */
+/* bytes of zero-initialised scratch for the two reduction kernels below (every kernel leaves it zeroed).  It has
+ * two parts, [2C floats + tickets][4 x 2C floats + ticket]: channels-last tensors take the bulk-copy ring kernels
+ * (csrc/bn_ring.cu), which use the second part; a caller that passes only the first (8 * C rounded up to 16, plus 16
+ * bytes) gets the tiled kernels, same results.  The base must be 16-byte aligned. */
 int64_t scb_bn_workspace_bytes(int channels);
 
 /* Replaces torch.batch_norm_stats (_functions.py:39): per-channel statistics of this rank's

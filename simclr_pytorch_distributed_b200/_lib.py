@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, 'csrc')
 ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(CSRC, 'libsimclr_b200.so')
-SOURCES = ['api.cu', 'bn.cu', 'bn_cluster.cu', 'bn_ring.cu', 'supcon_generic.cu', 'supcon_tc.cu']
+SOURCES = ['api.cu', 'bn.cu', 'bn_cluster.cu', 'bn_ring.cu', 'head_tc.cu', 'supcon_generic.cu', 'supcon_tc.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
 
@@ -123,6 +123,8 @@ PROTOTYPES = {
     'scb_supcon_finish': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _i64, _i64, _vp]),
     'scb_feature_norm_terms': (_i, [_vp, _i, _vp, _f, _f, _f, _vp, _vp]),
     'scb_feature_norm_backward': (_i, [_vp, _i, _i, _i, _i, _i64, _i64, _vp, _vp, _f, _f, _vp, _i, _vp, _i64, _i64, _vp]),
+    'scb_head_forward': (_i, [_vp, _i64, _vp, _i64, _vp, _i64, _i, _i, _i, _vp, _i, _i64, _vp, _i, _f, _vp]),
+    'scb_head_normalize_backward': (_i, [_vp, _i, _i64, _vp, _i, _i64, _vp, _i64, _i, _vp, _i, _i64, _i, _vp]),
     'scb_peer_bcast': (_i, [_vp, _vp, _i, _vp, _i, _vp]),
     'scb_supcon_prep_peers': (_i, [_vp, _i, _i, _i, _i, _i64, _i64, _i, _f, _vp, _i64, _i, _i, _vp, _vp]),
     'scb_supcon_forward_peers': (_i, [_pp, _i, _i, _i, _vp, _vp, _vp, _i64, _vp]),

@@ -1641,6 +1641,25 @@ static int make_tmap_ptr(const scb_supcon_problem* p, const void* kptr, CUtensor
     return SCB_OK;
 }
 
+// Generic [rows, cols] bf16 matrix with row stride `ld` (elements), box [128 rows x 64 columns], 128-byte swizzle: the
+// operand layout of every tcgen05 kernel in this library (used by head_tc.cu).  Out-of-range rows / columns read zero.
+int tc_make_tmap_2d(const void* ptr, int64_t rows, int64_t cols, int64_t ld, CUtensorMap* out) {
+    if (!thread_has_context()) SCB_CUDA_OK(cudaFree(nullptr));
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return SCB_ERR_CUDA; }
+    SCB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15u) == 0 && (ld * 2) % 16 == 0,
+                "tensor map: base and row stride must be 16-byte aligned");
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {64, 128};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with code %d", (int)r); return SCB_ERR_CUDA; }
+    return SCB_OK;
+}
+
 static constexpr int kMaxSlots = 32;
 static long long* g_trace = nullptr;   // set through scb_debug_set_trace (diagnostics only)
 void tc_set_trace(long long* p) { g_trace = p; }

@@ -2,6 +2,8 @@
 #pragma once
 #include "common.cuh"
 
+#include <cuda.h>
+
 namespace scb {
 
 int64_t tc_workspace_bytes(const scb_supcon_problem* p, int n_rows);
@@ -25,6 +27,9 @@ int tc_backward_features(const scb_supcon_problem* p, int row_begin, int n_rows,
                          const float* grad_out, int n_anchor_total, const void* features, int feat_dtype,
                          int n_samples, int64_t stride_s, int64_t stride_v, int normalize, const float* inv_norm,
                          void* out, int64_t ostride_s, int64_t ostride_v, void* workspace, cudaStream_t stream);
+
+// TMA descriptor of a [rows, cols] bf16 matrix (row stride ld elements), [128 x 64] boxes, 128-byte swizzle
+int tc_make_tmap_2d(const void* ptr, int64_t rows, int64_t cols, int64_t ld, CUtensorMap* out);
 
 // diagnostics (-DSCB_TRACE=1 builds): device buffer of 6 x 1024 int64 for (event id, %globaltimer) pairs of
 // CTA 0's roles and the entry / exit time of every CTA; nullptr switches tracing off
