@@ -684,15 +684,23 @@ def run_model(args, world, rank):
             normalize_in_model = True
         else:
             if arm == 'ours_fused':
-                m = SupConResNet50(bn=SyncBatchNorm, fuse=True).to(dev).to(memory_format=torch.channels_last).to(torch.bfloat16)
+                # ReLU / add+ReLU inside the batch-norm kernels, and the end of the head (Linear, normalise, view
+                # stacking) as one kernel whose bf16 output the loss uses in place
+                m = SupConResNet50(bn=SyncBatchNorm, fuse=True, tail=True).to(dev).to(
+                    memory_format=torch.channels_last).to(torch.bfloat16)
                 m.load_state_dict(base.state_dict())
+                loss_mod = (DistributedSupConLoss(temperature=TEMP, normalize=False) if world > 1
+                            else SupConLoss(temperature=TEMP))
+
+                def crit(feats):
+                    return loss_mod(feats)
             else:
                 m = SyncBatchNorm.convert_sync_batchnorm(copy.deepcopy(base))
-            loss_mod = (DistributedSupConLoss(temperature=TEMP, normalize=True) if world > 1
-                        else SupConLoss(temperature=TEMP, normalize=True))
+                loss_mod = (DistributedSupConLoss(temperature=TEMP, normalize=True) if world > 1
+                            else SupConLoss(temperature=TEMP, normalize=True))
 
-            def crit(feats):                       # the fused normalise replaces main_supcon.py:283
-                return loss_mod(torch.stack([feats[:bsz], feats[bsz:]], 1))
+                def crit(feats):                       # the fused normalise replaces main_supcon.py:283
+                    return loss_mod(torch.stack([feats[:bsz], feats[bsz:]], 1))
             normalize_in_model = False
         m = wrap(m)
         opt = torch.optim.SGD(m.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)

@@ -11,7 +11,11 @@ L2-normalised, `F.normalize(self.head(feat), dim=1)`).
 `fuse=True` builds the same network on this library's SyncBatchNorm with the activation folded into the batch-norm
 kernels: `relu(bn(x))` becomes one pass (fuse_relu=True) and the block tail
 `relu(bn3(conv3) + shortcut)` becomes `bn3(conv3, shortcut)` with the residual operand.  Parameter and buffer names
-are identical either way, so state dicts are interchangeable."""
+are identical either way, so state dicts are interchangeable.
+
+`tail=True` additionally runs the end of the head through this library's ProjectionTail:
+the last Linear, F.normalize and the stacking of the two views become one kernel and `forward` returns the
+`[bsz, 2, feat_dim]` tensor the loss takes (the parameters stay `head.2.weight / head.2.bias`)."""
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -49,8 +53,9 @@ class Bottleneck(nn.Module):
 
 
 class SupConResNet50(nn.Module):
-    def __init__(self, feat_dim=128, bn=nn.BatchNorm2d, fuse=False, width=64, blocks=(3, 4, 6, 3)):
+    def __init__(self, feat_dim=128, bn=nn.BatchNorm2d, fuse=False, width=64, blocks=(3, 4, 6, 3), tail=False):
         super().__init__()
+        self.use_tail = tail
         kw = {'fuse_relu': True} if fuse else {}
         self.fuse = fuse
         self.in_planes = width
@@ -84,6 +89,10 @@ class SupConResNet50(nn.Module):
         return torch.flatten(F.adaptive_avg_pool2d(out, 1), 1)
 
     def forward(self, x, normalize=True):
+        if self.use_tail:
+            from simclr_pytorch_distributed_b200 import ProjectionTail
+            tail = ProjectionTail.from_linear(self.head[2], n_views=2)      # shares head.2's parameters
+            return tail(self.head[1](self.head[0](self.encode(x))))
         feat = self.head(self.encode(x))
         return F.normalize(feat, dim=1) if normalize else feat
 

@@ -102,3 +102,29 @@ def test_resnet50_step_with_both_drop_ins(dtype, cl):
         worst = max(rel(sd[k].float(), rd[k].float()) for k in rd if k.endswith('running_var'))
         assert worst <= (1e-3 if dtype == torch.float32 else 5e-2), (name, worst)
     assert list(stock.state_dict().keys()) == list(swapped.state_dict().keys()) == list(fused.state_dict().keys())
+
+
+def test_small_carrier_with_projection_tail():
+    """The fused arm of `bench.py --workload model`: ReLU / add+ReLU inside the batch-norm kernels and the end of the
+    head (Linear, normalise, view stacking) through ProjectionTail, whose bf16 output the loss uses in place."""
+    dtype, kw = torch.bfloat16, dict(width=16, blocks=(1, 1, 1, 1))
+    stock, _, _ = build(dtype, True, **kw)
+    tailed = SupConResNet50(bn=SyncBatchNorm, fuse=True, tail=True, **kw).to('cuda').to(
+        memory_format=torch.channels_last).to(dtype)
+    tailed.load_state_dict(stock.state_dict())
+    images = torch.randn(128, 3, 32, 32, device='cuda').to(dtype).contiguous(memory_format=torch.channels_last)
+    truth = copy.deepcopy(stock).double()
+    t_loss, t_grads = one_step(truth, images.double(), lambda f: dense_supcon_loss(f, temperature=0.5))
+    s_loss, s_grads = one_step(stock, images, dense)
+    noise = total_rel(s_grads, t_grads)
+    crit = SupConLoss(temperature=0.5)
+    z = tailed(images)
+    assert z.shape == (64, 2, 128) and z.is_contiguous()
+    loss = crit(z)
+    tailed.zero_grad(set_to_none=True)
+    loss.backward()
+    grads = {n: p.grad.detach().float().clone() for n, p in tailed.named_parameters()}
+    assert abs(float(loss) - float(s_loss)) <= (2e-3 + 2 ** -7) * abs(float(s_loss))
+    err = total_rel(grads, t_grads)
+    assert err <= 1.5 * noise + 1e-2, (err, noise)
+    assert list(tailed.state_dict().keys()) == list(stock.state_dict().keys())
