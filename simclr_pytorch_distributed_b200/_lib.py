@@ -59,6 +59,20 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if nvcc is None:
         raise RuntimeError('libsimclr_b200.so is missing or stale and nvcc was not found; '
                            'build it with `python -c "import __graft_entry__ as g; g.build()"`')
+    # One builder at a time: the ranks of a torchrun job import this module together, and two compilers writing the
+    # same object files would corrupt them.  Whoever gets the lock second finds the library fresh and returns.
+    import fcntl
+    with open(os.path.join(CSRC, '.build.lock'), 'w') as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not _stale():
+                return LIB_PATH
+            return _build_locked(nvcc, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(nvcc, verbose):
     objs = []
 
     def compile_one(src):
