@@ -355,7 +355,11 @@ int scb_bn_backward_apply(const void* dy, const void* x, const void* y, void* dx
  * distributed shared memory and a cluster barrier -- no scratch, no global atomics, no grid-wide barrier, no
  * assumption that the whole grid is resident.  Channels-last [rows, channels] only, and only when the tensor
  * fits the register file of one resident wave: scb_bn_fused_supported(which = 0 forward / 1 backward, flags)
- * says so beforehand, otherwise they return SCB_ERR_UNSUPPORTED and the caller runs the two-kernel path. */
+ * says so beforehand, otherwise they return SCB_ERR_UNSUPPORTED and the caller runs the two-kernel path.
+ * With a workspace (the scb_bn_workspace_bytes scratch; may be NULL) tensors whose share per SM fits shared memory
+ * take the resident passes of csrc/bn_ring.cu instead: one CTA per SM bulk-copies its contiguous rows into shared
+ * memory, the per-channel sums meet in the workspace behind a grid barrier, and the rows are normalised out of shared
+ * memory.  That kernel is launched cooperatively (all CTAs resident at once), which is what makes its barrier legal. */
 int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner, int which,
                            int flags);
 /* diagnostics: how many clusters of `cluster_size` CTAs of these kernels the current device holds at once */
@@ -363,11 +367,11 @@ int scb_bn_cluster_occupancy(int cluster_size);
 int scb_bn_forward_fused(const void* x, const void* z, void* y, int dtype, int64_t rows, int channels,
                          const float* weight, const float* bias, float* running_mean, float* running_var,
                          float momentum, float eps, float* save_mean, float* save_invstd, float* save_count,
-                         int flags, void* stream);
+                         int flags, void* workspace, int64_t workspace_bytes, void* stream);
 int scb_bn_backward_fused(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t rows,
                           int channels, const float* mean, const float* invstd, const float* weight,
                           const float* bias, const float* n_total, float* out_sums, float* grad_weight,
-                          float* grad_bias, int flags, void* stream);
+                          float* grad_bias, int flags, void* workspace, int64_t workspace_bytes, void* stream);
 /* The reductions alone through the same cluster scheme, for several ranks (the exchange of
  * _functions.py:41-79 / :155-165 sits between them and scb_bn_apply / scb_bn_backward_apply):
  * scb_bn_stats_fused writes the (2C+1)-float message of scb_bn_stats, scb_bn_backward_reduce_fused the

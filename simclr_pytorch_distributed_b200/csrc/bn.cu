@@ -676,7 +676,7 @@ static int check_bn_common(const void* x, int dtype, int64_t outer, int channels
 using namespace scb;
 
 // scratch of the tiled / NCHW kernels: [2C] float accumulators + tickets
-static int64_t legacy_ws_bytes(int channels) { return bn_ws_counter_offset(channels) + 16; }
+static int64_t legacy_ws_bytes(int channels) { return legacy_bn_ws_bytes(channels); }   // bn_replicas() == 1
 
 // [scratch of the tiled kernels][scratch of the ring kernels (bn_ring.cu)]; a caller that passes only the first part
 // (scb_bn_stats_noalloc does) gets the tiled kernels

@@ -15,6 +15,7 @@
 // No global atomics, no grid-wide barrier and no co-residency assumption between clusters: a cluster that
 // cannot be scheduled yet (MPS / MIG limits, a concurrent NCCL kernel holding SMs) simply runs later.
 #include "common.cuh"
+#include "bn_ring.cuh"
 
 #include <stdlib.h>
 #include <utility>
@@ -766,7 +767,7 @@ static int cl_pick(int64_t M, int C, int es, int which, int flags) {
     static const int forced = [] {
         const char* e = getenv("SCB_BN_FUSED_MODE");
         if (e == nullptr) return 0;
-        return e[0] == 'r' ? 1 : (e[0] == 's' ? 2 : 0);
+        return e[0] == 'r' ? 1 : (e[0] == 's' ? 2 : (e[0] == 'c' ? 3 : 0));
     }();
     ClGeom g;
     ClStream gs;
@@ -783,6 +784,7 @@ static int cl_pick(int64_t M, int C, int es, int which, int flags) {
     const bool stream_ok = resident <= l2_budget && cl_stream_geom(M, C, es, &gs);
     if (forced == 1) return reg_ok ? 1 : 0;
     if (forced == 2) return stream_ok ? 2 : 0;
+    if (forced == 3) return 0;
     // measured on B200 (tools/time_bn.py, fwd+bwd in a CUDA graph): [256,256,8,8] bf16 registers 23.6 us / streamed
     // 26.5 us, [512,512,4,4] 17.3 / 26.5 (the streamed passes issue their rows in four dependent batches), while
     // [512,256,8,8], which only the streamed kernels take, gains over the multi-kernel path (43.4 us against 47.3)
@@ -845,11 +847,32 @@ using namespace scb;
 extern "C" int scb_bn_cluster_occupancy(int cluster_size) { return cl_max_active(cluster_size); }
 
 // which = 0: forward (with or without a residual operand, see `flags`), 1: backward
+// The shared-memory-resident pass with a grid barrier (bn_ring.cu, cooperative launch) against the cluster passes of
+// this file: SCB_BN_FUSED_MODE=coop|reg|stream forces one family; by default the resident pass is taken whenever the
+// tensor fits (measurements in DESIGN.md section 4).
+static bool cl_use_resident(int dtype, int64_t M, int C, int which, int flags) {
+    static const int forced = [] {
+        const char* e = getenv("SCB_BN_FUSED_MODE");
+        if (e == nullptr) return 0;
+        return e[0] == 'r' ? 1 : (e[0] == 's' ? 2 : (e[0] == 'c' ? 3 : 0));
+    }();
+    if (forced == 1 || forced == 2) return false;
+    // register-resident cluster passes first where the tensor fits them: measured on B200 (fwd+bwd, CUDA graph)
+    // [256,256,8,8] bf16 23.9 us against 24.9 us resident, [512,512,4,4] 17.6 against 25.1; the resident pass wins
+    // where only the streamed cluster pass or the ring passes are left ([512,256,8,8] forward 15.9 against 18.3 / 19.5)
+    // (the 16-rows-per-thread forward variant of the register pass, which [512,256,8,8] would take, is slower than the
+    // resident pass: 19.5 us)
+    ClGeom g8;
+    if (forced == 0 && cl_geom(M, C, dtype == SCB_F32 ? 4 : 2, kClRows, &g8)) return false;
+    return ring_resident_supported(dtype, M, C, which, flags);
+}
+
 extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t outer, int channels, int64_t inner,
                                       int which, int flags) {
     if (!channels_last || channels <= 0) return 0;
     if (dtype != SCB_F32 && dtype != SCB_BF16 && dtype != SCB_F16) return 0;
     const int es = (dtype == SCB_F32) ? 4 : 2;
+    if (cl_use_resident(dtype, outer * inner, channels, which, flags)) return 1;
     return cl_pick(outer * inner, channels, es, which, flags) != 0 ? 1 : 0;
 }
 
@@ -860,7 +883,8 @@ extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t oute
 extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int dtype, int64_t rows, int channels,
                                     const float* weight, const float* bias, float* running_mean,
                                     float* running_var, float momentum, float eps, float* save_mean,
-                                    float* save_invstd, float* save_count, int flags, void* stream_) {
+                                    float* save_invstd, float* save_count, int flags, void* workspace,
+                                    int64_t workspace_bytes, void* stream_) {
     if (int e = cl_check(x, dtype, rows, channels)) return e;
     SCB_REQUIRE(y != nullptr, "bn_forward_fused: null output");
     const bool add = (flags & SCB_BN_ADD) != 0;
@@ -869,6 +893,13 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
     const int64_t M = rows;
     const int C = channels;
     if (!cl_aligned16(x) || !cl_aligned16(y) || (add && !cl_aligned16(z))) SCB_CL_UNSUPPORTED("bn_forward_fused");
+    if (cl_use_resident(dtype, M, C, 0, flags) && workspace != nullptr) {
+        const int r = ring_forward_resident(x, add ? z : nullptr, y, dtype, M, C, weight, bias, running_mean, running_var,
+                                            momentum, eps, save_mean, save_invstd, save_count, flags,
+                                            (char*)workspace + legacy_bn_ws_bytes(C),
+                                            workspace_bytes - legacy_bn_ws_bytes(C), stream);
+        if (r != kRingUnsupported) return r;
+    }
     const int pick = cl_pick(M, C, dtype == SCB_F32 ? 4 : 2, 0, flags);
     if (pick == 0) SCB_CL_UNSUPPORTED("bn_forward_fused");
     if (pick == 2) {
@@ -938,7 +969,8 @@ extern "C" int scb_bn_stats_fused(const void* x, int dtype, int64_t rows, int ch
 static int bn_backward_cluster(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype,
                                int64_t rows, int channels, const float* mean, const float* invstd,
                                const float* weight, const float* bias, const float* n_total, float* out_sums,
-                               float* grad_weight, float* grad_bias, int flags, int reduce_only, void* stream_) {
+                               float* grad_weight, float* grad_bias, int flags, int reduce_only, void* workspace,
+                               int64_t workspace_bytes, void* stream_) {
     if (int e = cl_check(x, dtype, rows, channels)) return e;
     SCB_REQUIRE(dy && mean && invstd && n_total, "bn_backward_fused: null pointer");
     SCB_REQUIRE(reduce_only || dx != nullptr, "bn_backward_fused: null dx");
@@ -951,6 +983,12 @@ static int bn_backward_cluster(const void* dy, const void* x, const void* y, voi
     if (!cl_aligned16(x) || !cl_aligned16(dy) || (dx && !cl_aligned16(dx)) || (gate == 2 && !cl_aligned16(y)) ||
         (dz && !cl_aligned16(dz)))
         SCB_CL_UNSUPPORTED("bn_backward_fused");
+    if (!reduce_only && workspace != nullptr && cl_use_resident(dtype, M, C, 1, flags)) {
+        const int r = ring_backward_resident(dy, x, y, dx, dz, dtype, M, C, mean, invstd, weight, bias, n_total, out_sums,
+                                             grad_weight, grad_bias, gate, (char*)workspace + legacy_bn_ws_bytes(C),
+                                             workspace_bytes - legacy_bn_ws_bytes(C), stream);
+        if (r != kRingUnsupported) return r;
+    }
     if (!reduce_only) {
         const int pick = cl_pick(M, C, dtype == SCB_F32 ? 4 : 2, 1, flags);
         if (pick == 0) SCB_CL_UNSUPPORTED("bn_backward_fused");
@@ -994,9 +1032,10 @@ static int bn_backward_cluster(const void* dy, const void* x, const void* y, voi
 extern "C" int scb_bn_backward_fused(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype,
                                      int64_t rows, int channels, const float* mean, const float* invstd,
                                      const float* weight, const float* bias, const float* n_total, float* out_sums,
-                                     float* grad_weight, float* grad_bias, int flags, void* stream_) {
+                                     float* grad_weight, float* grad_bias, int flags, void* workspace,
+                                     int64_t workspace_bytes, void* stream_) {
     return bn_backward_cluster(dy, x, y, dx, dz, dtype, rows, channels, mean, invstd, weight, bias, n_total, out_sums,
-                               grad_weight, grad_bias, flags, 0, stream_);
+                               grad_weight, grad_bias, flags, 0, workspace, workspace_bytes, stream_);
 }
 
 extern "C" int scb_bn_backward_reduce_fused(const void* dy, const void* x, const void* y, int dtype, int64_t rows,
@@ -1006,5 +1045,5 @@ extern "C" int scb_bn_backward_reduce_fused(const void* dy, const void* x, const
                                             void* stream_) {
     SCB_REQUIRE(out_sums != nullptr, "bn_backward_reduce_fused: null out_sums");
     return bn_backward_cluster(dy, x, y, nullptr, nullptr, dtype, rows, channels, mean, invstd, weight, bias, n_total,
-                               out_sums, grad_weight, grad_bias, flags, 1, stream_);
+                               out_sums, grad_weight, grad_bias, flags, 1, nullptr, 0, stream_);
 }

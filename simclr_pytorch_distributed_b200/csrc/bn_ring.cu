@@ -41,6 +41,26 @@ constexpr int kRingTileVecs = 512;
 
 enum { kOpStats = 0, kOpApply = 1, kOpBwdReduce = 2, kOpBwdApply = 3 };
 
+// Timeline instrumentation of the resident passes (tools/trace_bn.py): only with -DSCB_TRACE=1 (tools/build_trace_lib.sh)
+#ifndef SCB_TRACE
+#define SCB_TRACE 0
+#endif
+#if SCB_TRACE
+__device__ long long* g_ring_trace = nullptr;          // [CTA][8] globaltimer stamps
+__device__ __forceinline__ void ring_stamp(int slot, float dep = 0.f) {
+    if (g_ring_trace != nullptr && threadIdx.x == 0) {
+        long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "f"(dep) : "memory");
+        g_ring_trace[blockIdx.x * 8 + slot] = t;
+    }
+}
+extern "C" int scb_debug_set_ring_trace(long long* p) {
+    return cudaMemcpyToSymbol(g_ring_trace, &p, sizeof(p)) == cudaSuccess ? 0 : -1;
+}
+#else
+#define ring_stamp(...) ((void)0)
+#endif
+
 struct RingArgs {
     const void* in[3];        // stats / apply: x (, z);   backward: x, dy (, saved y)
     void* out[2];             // apply: y;   backward apply: dx (, dz)
@@ -54,6 +74,7 @@ struct RingArgs {
     float *running_mean, *running_var, *save_mean, *save_invstd, *save_count;
     float* acc;               // [kRingReplicas][2C]
     unsigned* counter;
+    unsigned* gbar;           // resident kernels: [arrived, left] of the grid barrier
     float *out0, *grad_weight, *grad_bias;      // out0: out_stats (statistics) / out_sums (backward reduce)
 };
 
@@ -349,6 +370,270 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
     }
 }
 
+// =================================================================== resident single-launch passes
+// For tensors whose share per SM fits shared memory (x alone: up to ~24 MB; x and dy: ~12 MB -- BASELINE cfg 2 is
+// 8 MiB), statistics and normalisation are ONE launch that reads x (and dy) exactly once:
+//   * one CTA per SM owns a contiguous range of rows; the producer issues the bulk copies of the WHOLE range at once
+//     (57 KiB per SM forward, 114 KiB backward at cfg 2: every byte of the pass is in flight from the first
+//     microsecond, fully coalesced, no registers);
+//   * the consumers accumulate per-channel sums as the chunks land, reduce them inside the CTA and add them to the
+//     accumulator copies with 16-byte reductions;
+//   * the grid meets at a barrier in global memory; then every CTA reads the 2C totals, builds its coefficient table
+//     and normalises the rows still sitting in its shared memory, storing coalesced.
+// The barrier is legal because the kernel is launched COOPERATIVELY (cudaLaunchAttributeCooperative): the driver
+// starts the grid only when all of its CTAs are resident at once, so no CTA can wait for one that has not been
+// scheduled (round 1 spun in a plain launch; that hazard is what this attribute removes).  The wait is bounded all
+// the same: a protocol bug must surface as a launch failure, never as a hung GPU.
+// Against the cluster kernels of bn_cluster.cu (which need no barrier): those are forced by the cluster-size limits of
+// the chip to 16-byte-wide channel slabs at C = 256, i.e. every lane of a load in a different 128-byte line.
+constexpr int kResMaxChunks = 16;
+constexpr int kResSmemMax = 227 * 1024;
+
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+template <typename T, bool kBwd, int kGate, bool kAdd>
+__global__ void __launch_bounds__(kRingThreads, 1)
+bn_resident_kernel(const __grid_constant__ RingArgs a) {
+    constexpr int VEC = Vec16<T>::N;
+    constexpr int NL = kBwd ? (kGate == 2 ? 3 : 2) : (kAdd ? 2 : 1);
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int C = a.C, vpr = a.vpr, rpp = a.rpp;
+    const int row_bytes = vpr * 16;
+    const int chunk_bytes = a.chunk_rows * row_bytes;
+    uint8_t* data = smem;                                                          // [n_stage][NL][chunk_bytes]
+    float* red = reinterpret_cast<float*>(data + (size_t)a.n_stage * NL * chunk_bytes);   // [rpp][2][C]
+    float* table = red + (size_t)rpp * 2 * C;                                      // [2][C]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(table + 2 * C);                   // full[kResMaxChunks]
+    unsigned* s_flag = reinterpret_cast<unsigned*>(bars + kResMaxChunks);
+    const uint32_t bar0 = smem_u32(bars);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t r_beg = (int64_t)blockIdx.x * a.rows_per_cta;
+    const int64_t r_end = min(a.M, r_beg + a.rows_per_cta);
+    const int n_chunks = r_end > r_beg ? (int)((r_end - r_beg + a.chunk_rows - 1) / a.chunk_rows) : 0;
+
+    ring_stamp(0);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < n_chunks; ++s) mbar_init(bar0 + 8u * (uint32_t)s, 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == kRingConsumers / 32) {
+        if (lane == 0) {
+            for (int k = 0; k < n_chunks; ++k) {
+                const int64_t row0 = r_beg + (int64_t)k * a.chunk_rows;
+                const uint32_t bytes = (uint32_t)(min((int64_t)a.chunk_rows, r_end - row0) * row_bytes);
+                mbar_arrive_expect_tx(bar0 + 8u * (uint32_t)k, bytes * NL);
+#pragma unroll
+                for (int q = 0; q < NL; ++q)
+                    bulk_g2s(smem_u32(data + ((size_t)k * NL + q) * chunk_bytes),
+                             reinterpret_cast<const uint8_t*>(a.in[q]) + row0 * row_bytes, bytes, bar0 + 8u * (uint32_t)k);
+            }
+        }
+        return;                                      // the data stay in shared memory: the CTA lives on in its consumers
+    }
+
+    const int t = threadIdx.x;
+    const int col = t % vpr, rip = t / vpr;
+    const bool act = t < rpp * vpr;
+    const int c0 = col * VEC;
+    float s1[VEC], s2[VEC], k0[VEC], k1[VEC], bb[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; k0[i] = 0.f; k1[i] = 0.f; bb[i] = 0.f; }
+    if (act) {
+        if (!kBwd) {
+            load_row_vec_cached<T, VEC>(reinterpret_cast<const T*>(a.in[0]) + c0, k0);      // common shift K_c = x[0, c]
+        } else {
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                const int c = c0 + i;
+                k0[i] = a.mean[c];
+                k1[i] = (a.weight ? a.weight[c] : 1.f) * a.invstd[c];
+                if (kGate == 1) bb[i] = a.bias ? a.bias[c] : 0.f;
+            }
+        }
+    }
+    // ---- phase 1: sums, as the chunks land
+    for (int k = 0; k < n_chunks; ++k) {
+        const int64_t row0 = r_beg + (int64_t)k * a.chunk_rows;
+        const int rows = (int)min((int64_t)a.chunk_rows, r_end - row0);
+        mbar_wait(bar0 + 8u * (uint32_t)k, 0);
+        const uint8_t* st0 = data + (size_t)k * NL * chunk_bytes;
+        if (act) {
+#pragma unroll 2
+            for (int p = rip; p < rows; p += rpp) {
+                const int off = (p * vpr + col) * 16;
+                const uint4 r0 = *reinterpret_cast<const uint4*>(st0 + off);
+                const T* e0 = reinterpret_cast<const T*>(&r0);
+                if (!kBwd) {
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) {
+                        const float d = to_f32(e0[i]) - k0[i];
+                        s1[i] += d;
+                        s2[i] = fmaf(d, d, s2[i]);
+                    }
+                } else {
+                    const uint4 r1 = *reinterpret_cast<const uint4*>(st0 + chunk_bytes + off);
+                    const T* e1 = reinterpret_cast<const T*>(&r1);
+                    uint4 r2 = make_uint4(0u, 0u, 0u, 0u);
+                    if (kGate == 2) r2 = *reinterpret_cast<const uint4*>(st0 + 2 * chunk_bytes + off);
+                    const T* e2 = reinterpret_cast<const T*>(&r2);
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) {
+                        const float xm = to_f32(e0[i]) - k0[i];
+                        float g = to_f32(e1[i]);
+                        if (kGate == 1 && !(fmaf(xm, k1[i], bb[i]) > 0.f)) g = 0.f;
+                        if (kGate == 2 && !(to_f32(e2[i]) > 0.f)) g = 0.f;
+                        s1[i] += g;
+                        s2[i] = fmaf(g, xm, s2[i]);
+                    }
+                }
+            }
+        }
+    }
+    ring_stamp(1, s1[0] + s2[0]);                    // all chunks landed, local sums done
+    // ---- CTA sums -> accumulator copies
+    if (act) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            red[(rip * 2 + 0) * C + c0 + i] = s1[i];
+            red[(rip * 2 + 1) * C + c0 + i] = s2[i];
+        }
+    }
+    named_bar_sync(1, kRingConsumers);
+    {
+        float* my_acc = a.acc + (size_t)(blockIdx.x % kRingReplicas) * 2 * C;
+        for (int j = 4 * t; j < 2 * C; j += 4 * kRingConsumers) {
+            const int which = j >= C ? 1 : 0, c = j - which * C;
+            float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int r = 0; r < rpp; ++r) {
+                const float4 v = *reinterpret_cast<const float4*>(red + (r * 2 + which) * C + c);
+                tot.x += v.x; tot.y += v.y; tot.z += v.z; tot.w += v.w;
+            }
+            red_add_v4(my_acc + j, tot);
+        }
+    }
+    ring_stamp(2);                                   // reductions issued
+    // ---- grid barrier (cooperative launch: every CTA is resident)
+    __threadfence();
+    named_bar_sync(1, kRingConsumers);
+    if (t == 0) {
+        atomicAdd(a.gbar, 1u);
+        unsigned long long t0 = 0;
+        for (unsigned spins = 1; ld_acquire_gpu(a.gbar) < gridDim.x; ++spins) {
+            if ((spins & 1023u) == 0u) {
+                const unsigned long long now = wall_ns();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 2000000000ull) __trap();      // 2 s
+            }
+        }
+    }
+    named_bar_sync(1, kRingConsumers);
+    ring_stamp(3);                                   // through the grid barrier
+    // ---- totals -> coefficient table; CTA 0 also writes the per-channel outputs
+    {
+        const float n = kBwd ? a.n_total[0] : (float)a.M;
+        for (int c = t; c < C; c += kRingConsumers) {
+            float u = 0.f, v = 0.f;
+#pragma unroll
+            for (int r = 0; r < kRingReplicas; ++r) {
+                u += __ldcg(a.acc + (size_t)r * 2 * C + c);
+                v += __ldcg(a.acc + (size_t)r * 2 * C + C + c);
+            }
+            if (!kBwd) {
+                const float mean = to_f32(reinterpret_cast<const T*>(a.in[0])[c]) + u / n;
+                const float m2 = fmaxf(v - u * u / n, 0.f);
+                const float invstd = rsqrtf(m2 / n + a.eps);
+                const float sc = (a.weight ? a.weight[c] : 1.f) * invstd;
+                table[c] = sc;
+                table[C + c] = (a.bias ? a.bias[c] : 0.f) - mean * sc;
+                if (blockIdx.x == 0) {
+                    if (a.save_mean) a.save_mean[c] = mean;
+                    if (a.save_invstd) a.save_invstd[c] = invstd;
+                    if (a.running_mean) a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
+                    if (a.running_var)
+                        a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (m2 / (n - 1.f));
+                    if (c == 0 && a.save_count) a.save_count[0] = n;
+                }
+            } else {
+                const float is = a.invstd[c];
+                table[c] = u / n;
+                table[C + c] = is * is * v / n;
+                if (blockIdx.x == 0) {
+                    if (a.out0) { a.out0[c] = u; a.out0[C + c] = v; }
+                    if (a.grad_weight) a.grad_weight[c] = v * is;
+                    if (a.grad_bias) a.grad_bias[c] = u;
+                }
+            }
+        }
+    }
+    named_bar_sync(1, kRingConsumers);
+    ring_stamp(4);                                   // table built
+    // ---- phase 2: normalise the resident rows
+    float q2[VEC], q3[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { q2[i] = act ? table[c0 + i] : 0.f; q3[i] = act ? table[C + c0 + i] : 0.f; }
+    const bool relu = (a.flags & SCB_BN_RELU) != 0;
+    for (int k = 0; k < n_chunks; ++k) {
+        const int64_t row0 = r_beg + (int64_t)k * a.chunk_rows;
+        const int rows = act ? (int)min((int64_t)a.chunk_rows, r_end - row0) : 0;
+        const uint8_t* st0 = data + (size_t)k * NL * chunk_bytes;
+#pragma unroll 2
+        for (int p = rip; p < rows; p += rpp) {
+            const int off = (p * vpr + col) * 16;
+            const int64_t goff = (row0 + p) * row_bytes + col * 16;
+            const uint4 r0 = *reinterpret_cast<const uint4*>(st0 + off);
+            const T* e0 = reinterpret_cast<const T*>(&r0);
+            uint4 o, oz;
+            T* oe = reinterpret_cast<T*>(&o);
+            T* oze = reinterpret_cast<T*>(&oz);
+            if (!kBwd) {
+                uint4 rz = make_uint4(0u, 0u, 0u, 0u);
+                if (kAdd) rz = *reinterpret_cast<const uint4*>(st0 + chunk_bytes + off);
+                const T* ez = reinterpret_cast<const T*>(&rz);
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    float v = fmaf(to_f32(e0[i]), q2[i], q3[i]);
+                    if (kAdd) v += to_f32(ez[i]);
+                    oe[i] = from_f32<T>(relu ? fmaxf(v, 0.f) : v);
+                }
+                stg_stream16(reinterpret_cast<uint8_t*>(a.out[0]) + goff, o);
+            } else {
+                const uint4 r1 = *reinterpret_cast<const uint4*>(st0 + chunk_bytes + off);
+                const T* e1 = reinterpret_cast<const T*>(&r1);
+                uint4 r2 = make_uint4(0u, 0u, 0u, 0u);
+                if (kGate == 2) r2 = *reinterpret_cast<const uint4*>(st0 + 2 * chunk_bytes + off);
+                const T* e2 = reinterpret_cast<const T*>(&r2);
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) {
+                    const float xm = to_f32(e0[i]) - k0[i];
+                    float g = to_f32(e1[i]);
+                    bool off_gate = false;
+                    if (kGate == 1) off_gate = !(fmaf(xm, k1[i], bb[i]) > 0.f);
+                    if (kGate == 2) off_gate = !(to_f32(e2[i]) > 0.f);
+                    if (off_gate) g = 0.f;
+                    oe[i] = from_f32<T>((g - q2[i] - xm * q3[i]) * k1[i]);
+                    if (kGate == 2) oze[i] = off_gate ? from_f32<T>(0.f) : e1[i];
+                }
+                stg_stream16(reinterpret_cast<uint8_t*>(a.out[0]) + goff, o);
+                if (kGate == 2 && a.out[1] != nullptr) stg_stream16(reinterpret_cast<uint8_t*>(a.out[1]) + goff, oz);
+            }
+        }
+    }
+    ring_stamp(5);
+    // ---- leave (off the critical path): the last CTA through re-arms the scratch; everybody read the totals long ago
+    if (t == 0) *s_flag = (atomicAdd(a.gbar + 1, 1u) == gridDim.x - 1u) ? 1u : 0u;
+    named_bar_sync(1, kRingConsumers);
+    if (*s_flag != 0u) {
+        for (int j = t; j < kRingReplicas * 2 * C; j += kRingConsumers) a.acc[j] = 0.f;
+        if (t == 0) { a.gbar[0] = 0u; a.gbar[1] = 0u; }
+    }
+}
+
 // ------------------------------------------------------------------ host side
 static bool ring_enabled() {
     static const bool on = [] { const char* e = getenv("SCB_BN_RING"); return e == nullptr || e[0] != '0'; }();
@@ -470,6 +755,111 @@ int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, 
         if (gate == 2) return ring_launch(bn_ring_kernel<T, kOpBwdApply, 2, false>, a, grid, smem, stream);
         if (gate == 1) return ring_launch(bn_ring_kernel<T, kOpBwdApply, 1, false>, a, grid, smem, stream);
         return ring_launch(bn_ring_kernel<T, kOpBwdApply, 0, false>, a, grid, smem, stream);
+    });
+    return SCB_OK;
+}
+
+// ------------------------------------------------------------------ resident passes: host side
+static bool resident_geom(int64_t M, int C, int es, int n_loads, RingArgs* a, int* grid, size_t* smem) {
+    if (!ring_enabled()) return false;
+    const int64_t row_bytes = (int64_t)C * es;
+    if (C > kRingMaxC || row_bytes % 16 != 0 || row_bytes / 16 > kRingConsumers || M < 2) return false;
+    const int vpr = (int)(row_bytes / 16);
+    const int rpp = kRingConsumers / vpr;
+    const int sms = sm_count();
+    int64_t g = ceil_div(M, (int64_t)rpp);
+    if (g > sms) g = sms;
+    const int64_t rpc = ceil_div(ceil_div(M, g), (int64_t)rpp) * rpp;
+    g = ceil_div(M, rpc);
+    int chunk_rows = (int)(kRingChunkBytes / row_bytes) / rpp * rpp;
+    if (chunk_rows < rpp) chunk_rows = rpp;
+    while (ceil_div(rpc, (int64_t)chunk_rows) > kResMaxChunks) chunk_rows *= 2;
+    const int n_chunks = (int)ceil_div(rpc, (int64_t)chunk_rows);
+    const size_t bytes = (size_t)n_chunks * n_loads * chunk_rows * row_bytes + (size_t)rpp * 2 * C * sizeof(float) +
+                         (size_t)2 * C * sizeof(float) + (kResMaxChunks + 2) * sizeof(uint64_t);
+    if (bytes > (size_t)kResSmemMax) return false;
+    int coop = 0, dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) != cudaSuccess ||
+        !coop)
+        return false;
+    a->M = M; a->C = C; a->vpr = vpr; a->rpp = rpp; a->chunk_rows = chunk_rows; a->n_stage = n_chunks; a->ncol = 1;
+    a->rows_per_cta = rpc;
+    *grid = (int)g;
+    *smem = bytes;
+    return true;
+}
+
+bool ring_resident_supported(int dtype, int64_t M, int C, int which, int flags) {
+    RingArgs a = {};
+    int grid; size_t smem;
+    const bool add = (flags & SCB_BN_ADD) != 0, relu = (flags & SCB_BN_RELU) != 0;
+    const int n_loads = which == 0 ? (add ? 2 : 1) : ((relu && add) ? 3 : 2);
+    return resident_geom(M, C, dtype == SCB_F32 ? 4 : 2, n_loads, &a, &grid, &smem);
+}
+
+template <typename Kern>
+static int resident_launch(Kern kern, const RingArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    SCB_CUDA_OK(set_max_dynamic_smem(kern, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kRingThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;        // all CTAs resident at once: the in-kernel grid barrier is legal
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    SCB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, a));
+    count_launch();
+    return SCB_OK;
+}
+
+static void resident_ws(RingArgs* a, void* ws, int C) {
+    a->acc = (float*)ws;
+    a->counter = (unsigned*)((char*)ws + (size_t)kRingReplicas * 2 * C * 4);
+    a->gbar = a->counter + 1;
+}
+
+int ring_forward_resident(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* weight,
+                          const float* bias, float* running_mean, float* running_var, float momentum, float eps,
+                          float* save_mean, float* save_invstd, float* save_count, int flags, void* ws, int64_t ws_bytes,
+                          cudaStream_t stream) {
+    const bool add = (flags & SCB_BN_ADD) != 0;
+    if (ws == nullptr || ws_bytes < ring_ws_bytes(C) || !al16(x) || !al16(y) || (add && !al16(z))) return kRingUnsupported;
+    RingArgs a = {};
+    int grid; size_t smem;
+    if (!resident_geom(M, C, dtype == SCB_F32 ? 4 : 2, add ? 2 : 1, &a, &grid, &smem)) return kRingUnsupported;
+    a.in[0] = x; a.in[1] = z; a.out[0] = y;
+    a.weight = weight; a.bias = bias; a.running_mean = running_mean; a.running_var = running_var;
+    a.momentum = momentum; a.eps = eps; a.save_mean = save_mean; a.save_invstd = save_invstd; a.save_count = save_count;
+    a.flags = flags;
+    resident_ws(&a, ws, C);
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        if (add) return resident_launch(bn_resident_kernel<T, false, 0, true>, a, grid, smem, stream);
+        return resident_launch(bn_resident_kernel<T, false, 0, false>, a, grid, smem, stream);
+    });
+    return SCB_OK;
+}
+
+int ring_backward_resident(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
+                           const float* mean, const float* invstd, const float* weight, const float* bias,
+                           const float* n_total, float* out_sums, float* grad_weight, float* grad_bias, int gate, void* ws,
+                           int64_t ws_bytes, cudaStream_t stream) {
+    if (ws == nullptr || ws_bytes < ring_ws_bytes(C) || !al16(x) || !al16(dy) || !al16(dx) || (gate == 2 && !al16(y)) ||
+        (dz != nullptr && !al16(dz)))
+        return kRingUnsupported;
+    RingArgs a = {};
+    int grid; size_t smem;
+    if (!resident_geom(M, C, dtype == SCB_F32 ? 4 : 2, gate == 2 ? 3 : 2, &a, &grid, &smem)) return kRingUnsupported;
+    a.in[0] = x; a.in[1] = dy; a.in[2] = y; a.out[0] = dx; a.out[1] = dz;
+    a.mean = mean; a.invstd = invstd; a.weight = weight; a.bias = bias; a.n_total = n_total;
+    a.out0 = out_sums; a.grad_weight = grad_weight; a.grad_bias = grad_bias;
+    resident_ws(&a, ws, C);
+    SCB_DISPATCH_FLOAT(dtype, T, {
+        if (gate == 2) return resident_launch(bn_resident_kernel<T, true, 2, false>, a, grid, smem, stream);
+        if (gate == 1) return resident_launch(bn_resident_kernel<T, true, 1, false>, a, grid, smem, stream);
+        return resident_launch(bn_resident_kernel<T, true, 0, false>, a, grid, smem, stream);
     });
     return SCB_OK;
 }

@@ -8,6 +8,10 @@ namespace scb {
 constexpr int kRingUnsupported = 1;
 constexpr int kRingReplicas = 4;          // copies of the per-channel accumulators (spreads the L2 atomics)
 
+// scratch of the tiled / NCHW kernels of bn.cu: [2C] float accumulators (16-byte rounded) + tickets; the ring kernels'
+// scratch follows it in the caller's workspace (scb_bn_workspace_bytes)
+__host__ __device__ inline int64_t legacy_bn_ws_bytes(int C) { return ((int64_t)2 * C * 4 + 15) / 16 * 16 + 16; }
+
 // bytes of the ring kernels' scratch (accumulator replicas + ticket); zero on entry, zero again on exit
 __host__ __device__ inline int64_t ring_ws_bytes(int C) { return (int64_t)kRingReplicas * 2 * C * 4 + 16; }
 
@@ -23,5 +27,17 @@ int ring_backward_reduce(const void* dy, const void* x, const void* y, int dtype
 int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
                         const float* mean, const float* invstd, const float* weight, const float* bias,
                         const float* sums, const float* n_total, int gate, cudaStream_t stream);
+
+// Single-launch passes with the tensor resident in shared memory and a grid barrier (cooperative launch); the scratch
+// is the ring kernels' (ring_ws_bytes).  `which`: 0 forward, 1 backward.
+bool ring_resident_supported(int dtype, int64_t M, int C, int which, int flags);
+int ring_forward_resident(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* weight,
+                          const float* bias, float* running_mean, float* running_var, float momentum, float eps,
+                          float* save_mean, float* save_invstd, float* save_count, int flags, void* ws, int64_t ws_bytes,
+                          cudaStream_t stream);
+int ring_backward_resident(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
+                           const float* mean, const float* invstd, const float* weight, const float* bias,
+                           const float* n_total, float* out_sums, float* grad_weight, float* grad_bias, int gate, void* ws,
+                           int64_t ws_bytes, cudaStream_t stream);
 
 }  // namespace scb

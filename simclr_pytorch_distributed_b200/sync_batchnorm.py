@@ -109,10 +109,11 @@ class _Kernels:
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        ws = cls.workspace(lib, x.device, C)
         return lib.scb_bn_forward_fused(x.data_ptr(), p(z), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
                                         p(weight), p(bias), p(running_mean), p(running_var), momentum, eps,
                                         saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), saved[2 * C:].data_ptr(),
-                                        flags, cls.stream(x.device))
+                                        flags, ws.data_ptr(), ws.numel(), cls.stream(x.device))
 
     @classmethod
     def backward_fused(cls, dy, x, dx, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags,
@@ -120,10 +121,12 @@ class _Kernels:
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
+        ws = cls.workspace(lib, x.device, C)
         return lib.scb_bn_backward_fused(dy.data_ptr(), x.data_ptr(), p(yout), dx.data_ptr(), p(dz),
                                          _lib.dtype_code(x.dtype), outer * inner, C, saved[0:C].data_ptr(),
                                          saved[C:2 * C].data_ptr(), p(weight), p(bias), saved[2 * C:].data_ptr(),
-                                         sums.data_ptr(), p(grad_weight), p(grad_bias), flags, cls.stream(x.device))
+                                         sums.data_ptr(), p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(),
+                                         cls.stream(x.device))
 
     @classmethod
     def backward_apply(cls, dy, x, dx, geom, saved, weight, bias, sums, flags, yout=None, dz=None):

@@ -10,7 +10,9 @@ nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler
      -DSCB_TRACE=1 -c supcon_tc.cu -o ../../tools/bin/tc_trace.o
 nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr \
      -DSCB_TRACE=1 -c bn_cluster.cu -o ../../tools/bin/bn_cluster_trace.o
-nvcc -shared -o ../../tools/bin/libtrace.so api.o bn.o supcon_generic.o ../../tools/bin/tc_trace.o \
-     ../../tools/bin/bn_cluster_trace.o \
+nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr \
+     -DSCB_TRACE=1 -c bn_ring.cu -o ../../tools/bin/bn_ring_trace.o
+nvcc -shared -o ../../tools/bin/libtrace.so api.o bn.o supcon_generic.o head_tc.o ../../tools/bin/tc_trace.o \
+     ../../tools/bin/bn_cluster_trace.o ../../tools/bin/bn_ring_trace.o \
      -gencode arch=compute_100a,code=sm_100a
 echo "built tools/bin/libtrace.so"

@@ -16,7 +16,7 @@ __global__ void body(int mode, float* sink) {
     if (sink != nullptr && threadIdx.x == 9999) *sink = 1.f;
 }
 
-static float run(int grid, int block, int cluster, size_t smem, int mode, int nodes, int reps) {
+static float run(int grid, int block, int cluster, size_t smem, int mode, int nodes, int reps, int coop = 0) {
     cudaStream_t s;
     cudaStreamCreate(&s);
     cudaFuncSetAttribute(body, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -27,6 +27,7 @@ static float run(int grid, int block, int cluster, size_t smem, int mode, int no
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = cluster > 1 ? 1 : 0;
+    if (coop) { attr[0].id = cudaLaunchAttributeCooperative; attr[0].val.cooperative = 1; cfg.numAttrs = 1; }
     float* sink = nullptr;
     cudaGraph_t g; cudaGraphExec_t ge;
     cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
@@ -63,5 +64,9 @@ int main() {
                 printf("block %4d smem %6zu cluster %2d grid %3d: empty %.2f  +1 cluster barrier %.2f  +2 %.2f\n", block, smem,
                        cl, grid, t0, t1, t2);
             }
+    for (int block : {256, 544})
+        for (size_t smem : smems)
+            printf("cooperative launch: block %4d smem %6zu grid 148: empty %.2f us per node (plain launch %.2f)\n", block, smem,
+                   run(148, block, 1, smem, 0, 100, 20, 1), run(148, block, 1, smem, 0, 100, 20, 0));
     return 0;
 }

@@ -16,6 +16,10 @@ from simclr_pytorch_distributed_b200 import SyncBatchNorm   # noqa: E402
 
 raw = ctypes.CDLL(_lib.LIB_PATH)
 raw.scb_debug_set_bn_trace.argtypes = [ctypes.c_void_p]
+raw.scb_debug_set_ring_trace.argtypes = [ctypes.c_void_p]
+RING = os.environ.get('SCB_BN_FUSED_MODE', 'coop')[0] == 'c'       # which kernels run (and whose stamps to read)
+if RING:
+    raw.scb_debug_set_bn_trace = raw.scb_debug_set_ring_trace
 shape = tuple(int(a) for a in sys.argv[1:5]) if len(sys.argv) >= 5 else (256, 256, 8, 8)
 dev = torch.device('cuda')
 pool = 8
@@ -26,12 +30,13 @@ bn = SyncBatchNorm(shape[1]).to(dev)
 for i in range(pool):
     bn(xs[i]).backward(dys[i])
 torch.cuda.synchronize()
-NAMES = ['entry', 'loads issued', 'local sums', 'cluster sums', 'stores issued']
+NAMES = (['entry', 'local sums', 'reductions', 'grid barrier', 'table built', 'stores issued'] if RING else
+         ['entry', 'loads issued', 'local sums', 'cluster sums', 'stores issued'])
 
 
 def show(tag, tr):
     t = tr.cpu().view(-1, 8)
-    t = t[t[:, 0] > 0][:, :5]
+    t = t[t[:, 0] > 0][:, :len(NAMES)]
     b = int(t[:, 0].min())
     t = (t - b).float() / 1e3
     print('%s: %d CTAs' % (tag, t.shape[0]))
