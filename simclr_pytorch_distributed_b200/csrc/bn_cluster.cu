@@ -860,10 +860,14 @@ static bool cl_use_resident(int dtype, int64_t M, int C, int which, int flags) {
     // register-resident cluster passes first where the tensor fits them: measured on B200 (fwd+bwd, CUDA graph)
     // [256,256,8,8] bf16 23.9 us against 24.9 us resident, [512,512,4,4] 17.6 against 25.1; the resident pass wins
     // where only the streamed cluster pass or the ring passes are left ([512,256,8,8] forward 15.9 against 18.3 / 19.5)
-    // (the 16-rows-per-thread forward variant of the register pass, which [512,256,8,8] would take, is slower than the
-    // resident pass: 19.5 us)
-    ClGeom g8;
-    if (forced == 0 && cl_geom(M, C, dtype == SCB_F32 ? 4 : 2, kClRows, &g8)) return false;
+    // (the 16-rows-per-thread forward variant of the register pass is only kept where its slabs are at least 32 bytes
+    // wide: [512,1024,4,4] 11.3 us against 17.4 us resident, but [512,256,8,8] with 16-byte slabs 19.5 against 15.9)
+    if (forced == 0) {
+        const int es = dtype == SCB_F32 ? 4 : 2;
+        ClGeom g;
+        if (cl_geom(M, C, es, kClRows, &g)) return false;
+        if (which == 0 && !(flags & SCB_BN_ADD) && cl_geom(M, C, es, 2 * kClRows, &g) && g.TX >= 2) return false;
+    }
     return ring_resident_supported(dtype, M, C, which, flags);
 }
 
