@@ -326,6 +326,8 @@ def make_bn_runner(world, rank, pool):
     def step_resident(i):
         x = dev_x[i % pool]
         x.grad = None
+        bn.weight.grad = None                   # optimizer.zero_grad() of the training loop (main_supcon.py:322):
+        bn.bias.grad = None                     # without it autograd adds two accumulation kernels per step
         bn(x).backward(dev_dy[i % pool])
 
     y_host = torch.empty_like(host_x[0]).pin_memory()
@@ -334,6 +336,8 @@ def make_bn_runner(world, rank, pool):
     def step_e2e(i):
         x = host_x[i % pool].cuda(non_blocking=True).requires_grad_(True)
         dy = host_dy[i % pool].cuda(non_blocking=True)
+        bn.weight.grad = None
+        bn.bias.grad = None
         y = bn(x)
         y.backward(dy)
         y_host.copy_(y.detach(), non_blocking=True)

@@ -318,12 +318,15 @@ int scb_bn_stats_noalloc(const void* x, int dtype, int channels_last, int64_t ou
  *   y = (x - mean) * invstd * weight + bias  (+ z with SCB_BN_ADD)  (then ReLU with SCB_BN_RELU).
  * z is the residual operand of resnet_big.py:27-30,60-63 (same shape and layout as x; NULL without SCB_BN_ADD).
  * With stats_all == NULL (eval mode, batchnorm.py:791-828) running_mean / running_var are used
- * as the statistics and are not modified.  weight/bias may be NULL (affine=False). */
+ * as the statistics and are not modified.  weight/bias may be NULL (affine=False). 
+ * num_batches_tracked (may be NULL): the module's int64 step counter (batchnorm.py:763-764), incremented by one in
+ * training mode (stats_all != NULL) by the same kernel, so that the module launches nothing else per call. */
 int scb_bn_apply(const void* x, const void* z, void* y, int dtype, int channels_last, int64_t outer, int channels,
                  int64_t inner, const float* stats_all, int n_ranks,
                  const float* weight, const float* bias,
                  float* running_mean, float* running_var, float momentum, float eps,
-                 float* save_mean, float* save_invstd, float* save_count, int flags, void* stream);
+                 float* save_mean, float* save_invstd, float* save_count, long long* num_batches_tracked,
+                 int flags, void* stream);
 
 /* Replaces torch.batch_norm_backward_reduce (_functions.py:139-153):
  *   out_sums[0:C] = sum dy, out_sums[C:2C] = sum dy (x - mean)   (the 2C floats all-reduced),
@@ -367,7 +370,8 @@ int scb_bn_cluster_occupancy(int cluster_size);
 int scb_bn_forward_fused(const void* x, const void* z, void* y, int dtype, int64_t rows, int channels,
                          const float* weight, const float* bias, float* running_mean, float* running_var,
                          float momentum, float eps, float* save_mean, float* save_invstd, float* save_count,
-                         int flags, void* workspace, int64_t workspace_bytes, void* stream);
+                         long long* num_batches_tracked, int flags, void* workspace, int64_t workspace_bytes,
+                         void* stream);
 int scb_bn_backward_fused(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t rows,
                           int channels, const float* mean, const float* invstd, const float* weight,
                           const float* bias, const float* n_total, float* out_sums, float* grad_weight,

@@ -232,7 +232,7 @@ bn_apply_nhwc_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
                      int64_t rows_per_cta, const float* __restrict__ stats_all, int n_ranks,
                      const float* __restrict__ weight, const float* __restrict__ bias,
                      float* running_mean, float* running_var, float momentum, float eps,
-                     float* save_mean, float* save_invstd, float* save_count, int flags) {
+                     float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags) {
     extern __shared__ float sm[];           // [2][TX*VEC]: scale a, offset b
     const int TY = kBnThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
@@ -256,6 +256,7 @@ bn_apply_nhwc_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
                     if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
                 }
                 if (c == 0 && save_count) save_count[0] = n;
+                if (c == 0 && nbt && stats_all != nullptr) nbt[0] += 1;
             }
         }
         sm[t] = a;
@@ -507,7 +508,7 @@ bn_apply_nchw_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
                      int64_t n_per_cta, const float* __restrict__ stats_all, int n_ranks,
                      const float* __restrict__ weight, const float* __restrict__ bias,
                      float* running_mean, float* running_var, float momentum, float eps,
-                     float* save_mean, float* save_invstd, float* save_count, int flags) {
+                     float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags) {
     const int c = blockIdx.x;
     float mean, invstd, m2, n;
     merged_stats(stats_all, n_ranks, C, c, running_mean, running_var, eps, mean, invstd, m2, n);
@@ -522,6 +523,7 @@ bn_apply_nchw_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
             if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
         }
         if (c == 0 && save_count) save_count[0] = n;
+        if (c == 0 && nbt && stats_all != nullptr) nbt[0] += 1;
     }
     const bool relu = (flags & SCB_BN_RELU) != 0;
     const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
@@ -735,7 +737,8 @@ extern "C" int scb_bn_apply(const void* x, const void* z, void* y, int dtype, in
                             int channels, int64_t inner, const float* stats_all, int n_ranks,
                             const float* weight, const float* bias, float* running_mean,
                             float* running_var, float momentum, float eps, float* save_mean,
-                            float* save_invstd, float* save_count, int flags, void* stream_) {
+                            float* save_invstd, float* save_count, long long* num_batches_tracked, int flags,
+                            void* stream_) {
     if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
     SCB_REQUIRE(y != nullptr, "bn_apply: null output");
     SCB_REQUIRE(stats_all != nullptr || (running_mean && running_var),
@@ -749,7 +752,7 @@ extern "C" int scb_bn_apply(const void* x, const void* z, void* y, int dtype, in
     if (outer * inner == 0) return SCB_OK;
     if (channels_last) {
         const int r = ring_apply(x, z, y, dtype, outer * inner, C, stats_all, n_ranks, weight, bias, running_mean,
-                                 running_var, momentum, eps, save_mean, save_invstd, save_count, flags, stream);
+                                 running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags, stream);
         if (r != kRingUnsupported) return r;
     }
     const int target = 4 * sm_count();
@@ -765,7 +768,7 @@ if (add) {
                     dim3 grid(g.grid_x, (unsigned)g.grid_y);
                     kern<<<grid, kBnThreads, smem, stream>>>((const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta,
                         stats_all, n_ranks, weight, bias, running_mean, running_var, momentum, eps, save_mean,
-                        save_invstd, save_count, flags);
+                        save_invstd, save_count, num_batches_tracked, flags);
                 });
             } else {
                 SCB_VEC_SWITCH(nhwc_vec(C, sizeof(T), al), VEC, {
@@ -775,7 +778,7 @@ if (add) {
                     dim3 grid(g.grid_x, (unsigned)g.grid_y);
                     kern<<<grid, kBnThreads, smem, stream>>>((const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta,
                         stats_all, n_ranks, weight, bias, running_mean, running_var, momentum, eps, save_mean,
-                        save_invstd, save_count, flags);
+                        save_invstd, save_count, num_batches_tracked, flags);
                 });
             }
         } else {
@@ -783,7 +786,7 @@ if (add) {
             dim3 grid(C, (unsigned)g.grid_y);
             SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
                 (const T*)x, (const T*)z, (T*)y, outer, C, inner, g.n_per_cta, stats_all, n_ranks, weight, bias,
-                running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags)));
+                running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags)));
         }
     });
     SCB_CUDA_OK(cudaGetLastError());

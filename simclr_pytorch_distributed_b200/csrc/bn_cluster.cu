@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kClThreads, 1)
 bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __restrict__ y, int64_t M, int C,
                       const ClGeom g, const float* __restrict__ weight, const float* __restrict__ bias,
                       float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
-                      float* save_invstd, float* save_count, float* out_stats, int flags) {
+                      float* save_invstd, float* save_count, long long* nbt, float* out_stats, int flags) {
     constexpr int VEC = Vec16<T>::N;
     extern __shared__ float smf[];
     const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
@@ -199,6 +199,7 @@ bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __res
                 if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
                 if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
                 if (c == 0 && save_count) save_count[0] = n;
+                if (c == 0 && nbt) nbt[0] += 1;              // num_batches_tracked (batchnorm.py:763-764)
             }
         }
     }
@@ -396,7 +397,7 @@ __global__ void __launch_bounds__(kClThreads, 1)
 bn_fwd_stream_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __restrict__ y, int64_t M, int C,
                      const ClStream g, const float* __restrict__ weight, const float* __restrict__ bias,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
-                     float* save_invstd, float* save_count, int flags) {
+                     float* save_invstd, float* save_count, long long* nbt, int flags) {
     constexpr int VEC = Vec16<T>::N;
     extern __shared__ float smf[];
     const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
@@ -454,6 +455,7 @@ bn_fwd_stream_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
             if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
             if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
             if (c == 0 && save_count) save_count[0] = n;
+            if (c == 0 && nbt) nbt[0] += 1;
         }
     }
     __syncthreads();
@@ -887,7 +889,8 @@ extern "C" int scb_bn_fused_supported(int dtype, int channels_last, int64_t oute
 extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int dtype, int64_t rows, int channels,
                                     const float* weight, const float* bias, float* running_mean,
                                     float* running_var, float momentum, float eps, float* save_mean,
-                                    float* save_invstd, float* save_count, int flags, void* workspace,
+                                    float* save_invstd, float* save_count, long long* num_batches_tracked, int flags,
+                                    void* workspace,
                                     int64_t workspace_bytes, void* stream_) {
     if (int e = cl_check(x, dtype, rows, channels)) return e;
     SCB_REQUIRE(y != nullptr, "bn_forward_fused: null output");
@@ -899,7 +902,7 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
     if (!cl_aligned16(x) || !cl_aligned16(y) || (add && !cl_aligned16(z))) SCB_CL_UNSUPPORTED("bn_forward_fused");
     if (cl_use_resident(dtype, M, C, 0, flags) && workspace != nullptr) {
         const int r = ring_forward_resident(x, add ? z : nullptr, y, dtype, M, C, weight, bias, running_mean, running_var,
-                                            momentum, eps, save_mean, save_invstd, save_count, flags,
+                                            momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags,
                                             (char*)workspace + legacy_bn_ws_bytes(C),
                                             workspace_bytes - legacy_bn_ws_bytes(C), stream);
         if (r != kRingUnsupported) return r;
@@ -915,10 +918,10 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
             const T* xp = (const T*)x; const T* zp = (const T*)z; T* yp = (T*)y;
             if (add)
                 SCB_CUDA_OK(cl_launch_stream(bn_fwd_stream_kernel<T, true>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags));
+                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags));
             else
                 SCB_CUDA_OK(cl_launch_stream(bn_fwd_stream_kernel<T, false>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, flags));
+                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags));
         });
         count_launch();
         return SCB_OK;
@@ -935,13 +938,13 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
         float* none = nullptr;
         if (add)
             SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, true, kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, none, flags));
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags));
         else if (nrows == kClRows)
             SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, false, kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, none, flags));
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags));
         else
             SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, false, 2 * kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, none, flags));
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags));
     });
     count_launch();
     return SCB_OK;
@@ -964,7 +967,7 @@ extern "C" int scb_bn_stats_fused(const void* x, int dtype, int64_t rows, int ch
         const T* xp = (const T*)x; const T* zp = nullptr; T* yp = nullptr;
         float* none = nullptr; const float* cnone = nullptr;
         SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 1, false, 2 * kClRows>, g, smem, stream, xp, zp, yp, M, C, g, cnone, cnone,
-                              none, none, 0.f, 0.f, none, none, none, out_stats, 0));
+                              none, none, 0.f, 0.f, none, none, none, (long long*)nullptr, out_stats, 0));
     });
     count_launch();
     return SCB_OK;

@@ -72,6 +72,7 @@ struct RingArgs {
     float momentum, eps;
     const float *stats_all, *weight, *bias, *mean, *invstd, *sums, *n_total;
     float *running_mean, *running_var, *save_mean, *save_invstd, *save_count;
+    long long* nbt;           // num_batches_tracked, incremented by the apply / resident forward pass (may be NULL)
     float* acc;               // [kRingReplicas][2C]
     unsigned* counter;
     unsigned* gbar;           // resident kernels: [arrived, left] of the grid barrier
@@ -163,6 +164,7 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
                         a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (m2 / (n - 1.f));
                 }
                 if (c == 0 && a.save_count) a.save_count[0] = n;
+                if (c == 0 && a.nbt && a.stats_all != nullptr) a.nbt[0] += 1;
             }
         }
     }
@@ -558,6 +560,7 @@ bn_resident_kernel(const __grid_constant__ RingArgs a) {
                     if (a.running_var)
                         a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (m2 / (n - 1.f));
                     if (c == 0 && a.save_count) a.save_count[0] = n;
+                    if (c == 0 && a.nbt) a.nbt[0] += 1;
                 }
             } else {
                 const float is = a.invstd[c];
@@ -700,7 +703,8 @@ int ring_stats(const void* x, int dtype, int64_t M, int C, float* out_stats, voi
 
 int ring_apply(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* stats_all, int n_ranks,
                const float* weight, const float* bias, float* running_mean, float* running_var, float momentum,
-               float eps, float* save_mean, float* save_invstd, float* save_count, int flags, cudaStream_t stream) {
+               float eps, float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags,
+               cudaStream_t stream) {
     const bool add = z != nullptr;
     if (!al16(x) || !al16(y) || (add && !al16(z))) return kRingUnsupported;
     RingArgs a = {};
@@ -710,7 +714,7 @@ int ring_apply(const void* x, const void* z, void* y, int dtype, int64_t M, int 
     a.in[0] = x; a.in[1] = z; a.out[0] = y;
     a.stats_all = stats_all; a.n_ranks = n_ranks; a.weight = weight; a.bias = bias;
     a.running_mean = running_mean; a.running_var = running_var; a.momentum = momentum; a.eps = eps;
-    a.save_mean = save_mean; a.save_invstd = save_invstd; a.save_count = save_count; a.flags = flags;
+    a.save_mean = save_mean; a.save_invstd = save_invstd; a.save_count = save_count; a.nbt = nbt; a.flags = flags;
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (add) return ring_launch(bn_ring_kernel<T, kOpApply, 0, true>, a, grid, smem, stream);
         return ring_launch(bn_ring_kernel<T, kOpApply, 0, false>, a, grid, smem, stream);
@@ -823,7 +827,8 @@ static void resident_ws(RingArgs* a, void* ws, int C) {
 
 int ring_forward_resident(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* weight,
                           const float* bias, float* running_mean, float* running_var, float momentum, float eps,
-                          float* save_mean, float* save_invstd, float* save_count, int flags, void* ws, int64_t ws_bytes,
+                          float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags, void* ws,
+                          int64_t ws_bytes,
                           cudaStream_t stream) {
     const bool add = (flags & SCB_BN_ADD) != 0;
     if (ws == nullptr || ws_bytes < ring_ws_bytes(C) || !al16(x) || !al16(y) || (add && !al16(z))) return kRingUnsupported;
@@ -833,6 +838,7 @@ int ring_forward_resident(const void* x, const void* z, void* y, int dtype, int6
     a.in[0] = x; a.in[1] = z; a.out[0] = y;
     a.weight = weight; a.bias = bias; a.running_mean = running_mean; a.running_var = running_var;
     a.momentum = momentum; a.eps = eps; a.save_mean = save_mean; a.save_invstd = save_invstd; a.save_count = save_count;
+    a.nbt = nbt;
     a.flags = flags;
     resident_ws(&a, ws, C);
     SCB_DISPATCH_FLOAT(dtype, T, {

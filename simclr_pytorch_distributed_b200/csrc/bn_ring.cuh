@@ -19,7 +19,8 @@ int ring_stats(const void* x, int dtype, int64_t M, int C, float* out_stats, voi
                cudaStream_t stream);
 int ring_apply(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* stats_all, int n_ranks,
                const float* weight, const float* bias, float* running_mean, float* running_var, float momentum,
-               float eps, float* save_mean, float* save_invstd, float* save_count, int flags, cudaStream_t stream);
+               float eps, float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags,
+               cudaStream_t stream);
 int ring_backward_reduce(const void* dy, const void* x, const void* y, int dtype, int64_t M, int C, const float* mean,
                          const float* invstd, const float* weight, const float* bias, float* out_sums,
                          float* grad_weight, float* grad_bias, int gate, void* ws, int64_t ws_bytes,
@@ -33,8 +34,8 @@ int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, 
 bool ring_resident_supported(int dtype, int64_t M, int C, int which, int flags);
 int ring_forward_resident(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* weight,
                           const float* bias, float* running_mean, float* running_var, float momentum, float eps,
-                          float* save_mean, float* save_invstd, float* save_count, int flags, void* ws, int64_t ws_bytes,
-                          cudaStream_t stream);
+                          float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags, void* ws,
+                          int64_t ws_bytes, cudaStream_t stream);
 int ring_backward_resident(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
                            const float* mean, const float* invstd, const float* weight, const float* bias,
                            const float* n_total, float* out_sums, float* grad_weight, float* grad_bias, int gate, void* ws,

@@ -70,7 +70,7 @@ class _Kernels:
 
     @classmethod
     def apply(cls, x, y, geom, stats_all, n_ranks, weight, bias, running_mean, running_var,
-              momentum, eps, saved, flags, z=None):
+              momentum, eps, saved, flags, z=None, nbt=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
@@ -79,7 +79,7 @@ class _Kernels:
         sc = saved[2 * C:] if saved is not None else None
         _lib.check(lib.scb_bn_apply(x.data_ptr(), p(z), y.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C,
                                     inner, p(stats_all), n_ranks, p(weight), p(bias), p(running_mean),
-                                    p(running_var), momentum, eps, p(sm), p(si), p(sc), flags,
+                                    p(running_var), momentum, eps, p(sm), p(si), p(sc), p(nbt), flags,
                                     cls.stream(x.device)), 'scb_bn_apply')
 
     @classmethod
@@ -105,7 +105,8 @@ class _Kernels:
             'scb_bn_backward_reduce')
 
     @classmethod
-    def forward_fused(cls, x, y, geom, weight, bias, running_mean, running_var, momentum, eps, saved, flags, z=None):
+    def forward_fused(cls, x, y, geom, weight, bias, running_mean, running_var, momentum, eps, saved, flags, z=None,
+                      nbt=None):
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
@@ -113,7 +114,7 @@ class _Kernels:
         return lib.scb_bn_forward_fused(x.data_ptr(), p(z), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
                                         p(weight), p(bias), p(running_mean), p(running_var), momentum, eps,
                                         saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), saved[2 * C:].data_ptr(),
-                                        flags, ws.data_ptr(), ws.numel(), cls.stream(x.device))
+                                        p(nbt), flags, ws.data_ptr(), ws.numel(), cls.stream(x.device))
 
     @classmethod
     def backward_fused(cls, dy, x, dx, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags,
@@ -272,7 +273,9 @@ class _SyncBNFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, input, z, weight, bias, running_mean, running_var, eps, momentum, process_group,
-                world_size, fuse_relu, use_batch_stats):
+                world_size, fuse_relu, use_batch_stats, nbt=None):
+        # nbt: the module's num_batches_tracked buffer when the kernels are to count the step (training, momentum given)
+        nbt_kw = {'nbt': nbt} if nbt is not None else {}
         kern = _SyncBNFunction.kernels
         x, geom = _layout(input)
         C = geom[2]
@@ -295,7 +298,7 @@ class _SyncBNFunction(torch.autograd.Function):
         if (use_batch_stats and world_size == 1 and hasattr(kern, 'forward_fused') and
                 kern.fused_supported(x, geom, 0, flags)):
             # one rank, tensor fits one resident wave: statistics + normalisation in a single launch
-            rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags, z=z)
+            rc = kern.forward_fused(x, y, geom, w32, b32, rm, rv, momentum, eps, saved, flags, z=z, **nbt_kw)
             if rc == 0:
                 done = True
             elif rc != -3:
@@ -310,9 +313,9 @@ class _SyncBNFunction(torch.autograd.Function):
                 if world_size > 1:
                     stats_all = _exchange(kern, stats_all, 2 * C + 1, process_group, world_size, dev)
             if z is not None:
-                kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags, z=z)
+                kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags, z=z, **nbt_kw)
             else:
-                kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags)
+                kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags, **nbt_kw)
         if rm is not running_mean and running_mean is not None:
             running_mean.copy_(rm)
         if rv is not running_var and running_var is not None:
@@ -375,7 +378,7 @@ class _SyncBNFunction(torch.autograd.Function):
         # dgamma / dbeta stay un-synced: DDP averages them (_functions.py:180-181)
         grad_weight = gw.to(wd) if (w32 is not None and ctx.needs_input_grad[2]) else None
         grad_bias = gb.to(bd) if (b32 is not None and ctx.needs_input_grad[3]) else None
-        return grad_input, grad_z, grad_weight, grad_bias, None, None, None, None, None, None, None, None
+        return grad_input, grad_z, grad_weight, grad_bias, None, None, None, None, None, None, None, None, None
 
 
 class SyncBatchNorm(_BatchNorm):
@@ -416,12 +419,14 @@ class SyncBatchNorm(_BatchNorm):
             exponential_average_factor = 0.0
         else:
             exponential_average_factor = self.momentum
+        nbt = None
         if self.training and self.track_running_stats:
-            self.num_batches_tracked.add_(1)
-            if self.momentum is None:                     # cumulative moving average
+            if self.momentum is None:                     # cumulative moving average: the host needs the count
+                self.num_batches_tracked.add_(1)
                 exponential_average_factor = 1.0 / self.num_batches_tracked.item()
             else:
                 exponential_average_factor = self.momentum
+                nbt = self.num_batches_tracked            # counted by the normalising kernel: no launch of its own
 
         if self.training:
             bn_training = True
@@ -437,7 +442,7 @@ class SyncBatchNorm(_BatchNorm):
             world_size = dist.get_world_size(process_group)
         return _SyncBNFunction.apply(input, z, self.weight, self.bias, running_mean, running_var, self.eps,
                                      float(exponential_average_factor), process_group, world_size,
-                                     self.fuse_relu, bn_training)
+                                     self.fuse_relu, bn_training, nbt)
 
     @classmethod
     def convert_sync_batchnorm(cls, module, process_group=None):

@@ -203,8 +203,11 @@ class OracleBNKernels:
         out_stats[2 * C] = float(xd.numel() // C)
 
     @staticmethod
-    def apply(x, y, geom, stats_all, n_ranks, weight, bias, running_mean, running_var, momentum, eps, saved, flags):
+    def apply(x, y, geom, stats_all, n_ranks, weight, bias, running_mean, running_var, momentum, eps, saved, flags,
+              nbt=None):
         C = geom[2]
+        if nbt is not None:
+            nbt.add_(1)                                # the kernel counts the step (batchnorm.py:763-764)
         st = stats_all.double().view(n_ranks, 2 * C + 1)
         n, mean, m2 = 0.0, torch.zeros(C, dtype=torch.float64), torch.zeros(C, dtype=torch.float64)
         for r in range(n_ranks):                       # Chan merge with counts, rank order

@@ -387,3 +387,28 @@ def test_fused_supported_reports_capacity():
     x_, geom = _layout(x)
     assert _Kernels.fused_supported(x_, geom, 0) and _Kernels.fused_supported(x_, geom, 1)
     assert not _Kernels.fused_supported(x_, (1, 512 * 32 * 32, 256, 1), 1)
+
+
+@pytest.mark.parametrize('shape,cl,dtype', [
+    ((256, 256, 8, 8), True, torch.bfloat16),      # register-resident cluster pass
+    ((512, 256, 8, 8), True, torch.bfloat16),      # shared-memory-resident pass (cooperative grid barrier)
+    ((512, 128, 16, 16), True, torch.bfloat16),    # ring passes
+    ((8, 12, 5, 5), True, torch.float32),          # tiled passes (rows are not a whole number of 16-byte vectors)
+    ((8, 16, 6, 6), False, torch.float32),         # NCHW
+])
+def test_step_counter_is_kept_by_the_kernels(shape, cl, dtype):
+    """num_batches_tracked (batchnorm.py:763-764) is incremented by the normalising kernel itself: once per training
+    forward on every kernel family, never in eval mode."""
+    bn = make_bn(shape[1])
+    x = torch.randn(shape, device=DEV).to(dtype)
+    if cl:
+        x = x.contiguous(memory_format=torch.channels_last)
+    for i in range(3):
+        bn(x)
+        assert int(bn.num_batches_tracked) == i + 1
+    bn.eval()
+    bn(x)
+    assert int(bn.num_batches_tracked) == 3
+    bn.train()
+    bn(x, torch.zeros_like(x))                      # the residual-add variants count too
+    assert int(bn.num_batches_tracked) == 4
