@@ -232,11 +232,11 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
     def step_e2e(i):
         if state['primed'] != i:
             prefetch(i)                                       # first step of a run: nothing was prefetched
-        prefetch(i + 1)
         cur = torch.cuda.current_stream()
         cur.wait_event(ready[i % 2])
         f = slots[i % 2].detach().requires_grad_(True)
         loss = fwd_e2e(f)
+        prefetch(i + 1)                                       # issued while the GPU works on step i
         loss.backward()
         freed[i % 2].record(cur)
         loss_host.copy_(loss.detach(), non_blocking=True)

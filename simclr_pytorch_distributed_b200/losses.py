@@ -388,6 +388,10 @@ class SupConLoss(nn.Module):
             features = features.contiguous()
         B, V, D = features.shape
         dev = features.device
+        if (self.graph and mask is None and not self.track_norms and features.requires_grad and
+                torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
+            # graph mode: nothing below is needed per call (the captured step was planned once)
+            return self._graphed(features, label_ids(labels, dev) if labels is not None else None)
         if labels is not None:
             mask_kind = _lib.MASK_LABELS
             labels = label_ids(labels, dev)
@@ -401,9 +405,6 @@ class SupConLoss(nn.Module):
         engine = select_engine(self.engine, features.dtype, D, mask_kind, V * B)
         plan = LossPlan(B, V, D, mode=mode, mask_kind=mask_kind, engine=engine)
         plan.scalar_dtype = _lib.dtype_code(features.dtype)
-        if (self.graph and mask is None and not self.track_norms and features.requires_grad and
-                torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
-            return self._graphed(features, labels)
         norms = None
         if self.track_norms:
             if not self.normalize:
