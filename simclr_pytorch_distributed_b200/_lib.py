@@ -17,6 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, 'csrc')
 ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(CSRC, 'libsimclr_b200.so')
+_DEFAULT_LIB_PATH = LIB_PATH
 SOURCES = ['api.cu', 'bn.cu', 'bn_cluster.cu', 'bn_ring.cu', 'head_tc.cu', 'supcon_generic.cu', 'supcon_tc.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
@@ -172,7 +173,9 @@ def load():
     with _lock:
         if _lib is not None:
             return _lib
-        if _stale():
+        # a library put in place by hand (tools/build_trace_lib.sh points LIB_PATH at its instrumented build) is
+        # loaded as it is: rebuilding it here would silently replace it by the plain one
+        if LIB_PATH == _DEFAULT_LIB_PATH and _stale():
             build()
         try:
             lib = ctypes.CDLL(LIB_PATH)
