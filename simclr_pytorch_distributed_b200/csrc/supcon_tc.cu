@@ -548,13 +548,34 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                     const float nm = fmaxf(m, cmax * p.c2);
                     sum *= ex2(m - nm);
                     m = nm;
-                    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                    if (kPolyLane >= 0) {
+                        float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const float a = fmaf(__uint_as_float(v[c]), p.c2, -m);
-                        acc[c & 3] += ((c & 3) == kPolyLane) ? ex2_fma(a) : ex2(a);     // one in four on the FMA pipe
+                        for (int c = 0; c < 32; ++c) {
+                            const float a = fmaf(__uint_as_float(v[c]), p.c2, -m);
+                            acc[c & 3] += ((c & 3) == kPolyLane) ? ex2_fma(a) : ex2(a);     // one in four on the FMA pipe
+                        }
+                        sum += (acc[0] + acc[1]) + (acc[2] + acc[3]);
+                    } else {
+                        // two elements per FFMA2 / FADD2: the scale-and-shift and the accumulation take half the issue
+                        // slots, the exponentials stay one MUFU each
+                        const uint64_t c2p = pack2(p.c2, p.c2), mneg = pack2(-m, -m);
+                        uint64_t acc01 = pack2(0.f, 0.f), acc23 = acc01;
+#pragma unroll
+                        for (int c = 0; c < 32; c += 4) {
+                            const uint64_t x01 = ffma2(pack2(__uint_as_float(v[c]), __uint_as_float(v[c + 1])), c2p, mneg);
+                            const uint64_t x23 = ffma2(pack2(__uint_as_float(v[c + 2]), __uint_as_float(v[c + 3])), c2p, mneg);
+                            float x0, x1, x2, x3;
+                            unpack2(x01, x0, x1);
+                            unpack2(x23, x2, x3);
+                            acc01 = fadd2(acc01, pack2(ex2(x0), ex2(x1)));
+                            acc23 = fadd2(acc23, pack2(ex2(x2), ex2(x3)));
+                        }
+                        float s0, s1, s2, s3;
+                        unpack2(acc01, s0, s1);
+                        unpack2(acc23, s2, s3);
+                        sum += (s0 + s1) + (s2 + s3);
                     }
-                    sum += (acc[0] + acc[1]) + (acc[2] + acc[3]);
                     if (kLabels) {
                         float pacc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll

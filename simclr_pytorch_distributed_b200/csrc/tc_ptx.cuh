@@ -223,6 +223,27 @@ __device__ __forceinline__ float ex2(float x) {
     return y;
 }
 
+// Packed fp32 pairs (sm_100: FFMA2 / FADD2 -- one issue slot for two lanes of arithmetic).  A pair lives in a 64-bit
+// register; packing and unpacking adjacent 32-bit registers costs nothing.
+__device__ __forceinline__ uint64_t pack2(float a, float b) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& a, float& b) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
 // 2^x on the FMA pipe, for the share of the exponentials the MUFU pipe (16 ex2/clk/SM) has no room for
 // (tools/mufu_bench.cu: 3 MUFU : 1 of these = 18.8 exp/clk/SM against 15.6 for MUFU alone).  No conversion
 // instruction (F2I / FRND sit on the same XU pipe as MUFU): round to nearest through the 1.5*2^23 magic number,

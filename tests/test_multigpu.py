@@ -117,7 +117,7 @@ def _worker(rank, world, port, q):
             e_g = (np.linalg.norm((f.grad.double().cpu().numpy() - g_hat[sl]).ravel()) /
                    np.linalg.norm(g_hat[sl].ravel()))
             notes.append('loss bf16 in place, p2p=%s: rel loss %.2e rel grad %.2e' % (p2p, e_l, e_g))
-            ok = ok and e_l <= 2e-3 and e_g <= 2 * (2e-3 + 2 ** -8)
+            ok = ok and e_l <= 2e-3 + 2 ** -8 and e_g <= 2 * (2e-3 + 2 ** -8)     # the loss is returned rounded to bf16
         # ---------------- a ONE-step CUDA graph of the sharded loss and of SyncBatchNorm, replayed 8 times on fresh
         # data: the buffer rotation of the peer-memory exchanges is baked into the graph, every replay re-uses the
         # same generation, and must still never overwrite rows / statistics a peer is reading
