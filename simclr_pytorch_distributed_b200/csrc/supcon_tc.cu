@@ -179,7 +179,8 @@ __device__ __forceinline__ void store_loss_scalar(float* out, float loss, int sc
 __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta, double* s_red) {
     const int e = (int)threadIdx.x - 64;          // 0..511
     const FwdOut& o = p.fo;
-    __threadfence();                              // acquire side of the row-block ticket
+    // (the acquire side of the row-block ticket is the ticket's own acq_rel atomic + the barrier behind it; the
+    // partials are read with ld.global.cg, i.e. from the L2 where the other CTAs' released stores are)
     double contrib = 0.0;
     const int li = rb * kBM + e;
     if (e < kBM && li < p.a_count) {
@@ -262,7 +263,9 @@ __device__ __noinline__ void fwd_merge_rows(const TcParams& p, int rb, int n_cta
             const bool finite = fabs(t) < 1e12;
             const long long fx = finite ? __double2ll_rn(t * 1048576.0) : (1ll << 50);
             const unsigned long long add = ((unsigned long long)fx << 12) + 1ull;
-            if (o.po.n_dst > 0) __threadfence_system(); else __threadfence();
+            // peers read lse / npos after this rank's flag: order them at system scope; on one GPU nothing in this
+            // kernel reads them, the kernel boundary publishes them
+            if (o.po.n_dst > 0) __threadfence_system();
             const unsigned long long now = atomicAdd(o.acc, add) + add;
             if ((int)(now & 4095ull) == p.RB) {
                 *o.acc = 0ull;
@@ -327,7 +330,9 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
     auto s_empty = [&](int h, int b) { return bar0 + 8u * (12 + h * 2 + b); };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    auto stamp = [&](int slot) { if (kTrace && p.trace != nullptr && blockIdx.x == 0) { p.trace[slot] = clock64(); p.trace[slot + 16] = global_ns(); } };
+    // trace builds: p.trace[4094] selects the CTA whose phases are stamped (0 by default)
+    const unsigned trace_cta = (kTrace && p.trace != nullptr) ? (unsigned)p.trace[4094] : 0u;
+    auto stamp = [&](int slot) { if (kTrace && p.trace != nullptr && blockIdx.x == trace_cta) { p.trace[slot] = clock64(); p.trace[slot + 16] = global_ns(); } };
     if (threadIdx.x == 0) stamp(0);
     stamp_cta(p.trace, 0);
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
@@ -455,6 +460,7 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
         int pj = -1, pj_lo = 0, pj_hi = -1;
 
         auto flush = [&](int rb) {
+            if (threadIdx.x == 64) stamp(5);              // (trace) tiles of the row block done
             const int first_cta = (rb * p.CT) / p.q;      // CTAs [first_cta, last_cta] overlap this row block
             if (li < p.a_count) {
                 // one slot per (CTA overlapping the row block, column half)
@@ -489,11 +495,19 @@ supcon_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             const int n_cta = ((rb + 1) * p.CT - 1) / p.q - first_cta + 1;
             named_bar_sync(1, 512);                       // all partial stores of this CTA are issued ...
             if (threadIdx.x == 64) {
-                __threadfence();                          // ... and made visible before the ticket (cumulative)
-                *s_ticket = atomicAdd(p.fo.rb_count + rb, 1u);
+                // ... and released by the ticket itself (acq_rel at gpu scope: the barrier above makes the release
+                // cumulative over the whole CTA's stores, the acquire side covers the merge below) -- one L2 round
+                // trip instead of a full fence plus the atomic
+                unsigned tk;
+                asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], %2;" : "=r"(tk) : "l"(p.fo.rb_count + rb), "r"(1u) : "memory");
+                *s_ticket = tk;
             }
             named_bar_sync(1, 512);
-            if (*s_ticket == (unsigned)n_cta - 1u) fwd_merge_rows(*sp, rb, n_cta, s_red);
+            if (threadIdx.x == 64) stamp(6);              // (trace) partials out, ticket taken
+            if (*s_ticket == (unsigned)n_cta - 1u) {
+                fwd_merge_rows(*sp, rb, n_cta, s_red);
+                if (threadIdx.x == 64) stamp(8);          // (trace) row block merged
+            }
         };
 
         // incremental tile bookkeeping (no division per tile); one copy of the flush and of the chunk code:

@@ -31,14 +31,18 @@ torch.cuda.synchronize()
 trace = torch.zeros(5 * 1024, dtype=torch.int64, device=dev)
 if os.environ.get('QUIET'):
     trace[4095] = 1          # per-CTA entry / exit stamps only
+CTA = int(os.environ.get('TRACE_CTA', '0'))
+trace[4094] = CTA            # the CTA whose phases are stamped
 lib.scb_debug_set_trace(trace.data_ptr())
 L.launch_forward(lib, prob, plan, stats[0], stats[1], stats[2], loss, dev)
 torch.cuda.synchronize()
 lib.scb_debug_set_trace(None)
-t = trace.cpu()[:8].tolist()
-tn = trace.cpu()[16:24].tolist()
+t = trace.cpu()[:9].tolist()
+tn = trace.cpu()[16:25].tolist()
+print('CTA %d' % CTA)
 names = ['entry', 'setup done (barriers, TMEM alloc)', 'first A tile landed', 'first B tile landed',
-         'first S tile ready', 'last tile done', 'flush done', 'exit']
+         'first S tile ready', 'tiles of the (last) row block done', 'partials out, ticket taken', 'exit',
+         'row block merged (0 = this CTA did not merge)']
 for n, v, w in zip(names, t, tn):
     print('%-36s %8d cycles %8d ns' % (n, v - t[0], w - tn[0]))
 
@@ -50,6 +54,6 @@ st, en = (w[:, 0] - b).float() / 1e3, (w[:, 1] - b).float() / 1e3
 life = en - st
 print('CTAs %d: start %.2f..%.2f us, end %.2f..%.2f us, lifetime min %.2f / median %.2f / max %.2f us' % (
     len(w), st.min(), st.max(), en.min(), en.max(), life.min(), life.median(), life.max()))
-print('CTA 0 lifetime %.2f us' % float(life[0]))
+print('CTA %d lifetime %.2f us' % (CTA, float(life[CTA])))
 order = torch.argsort(life, descending=True)[:6].tolist()
 print('longest CTAs:', [(int(i), round(float(life[i]), 2)) for i in order])
