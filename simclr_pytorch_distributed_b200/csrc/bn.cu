@@ -112,7 +112,10 @@ __device__ __forceinline__ bool last_cta_done(unsigned* counter, unsigned total)
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
-        unsigned t = atomicAdd(counter, 1u);
+        // acq_rel: a release cumulative over the whole CTA's atomics (ordered before it by the barrier) and the
+        // acquire the finalising CTA needs -- a relaxed atomicAdd behind per-thread fences is neither
+        unsigned t;
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], %2;" : "=r"(t) : "l"(counter), "r"(1u) : "memory");
         s_last = (t == total - 1) ? 1u : 0u;
     }
     __syncthreads();

@@ -89,14 +89,21 @@ __device__ __forceinline__ void red_add_v4(float* p, const float4& v) {
                  : "memory");
 }
 
+// Ticket of the "last CTA finalises" protocol.  The CTA's reductions were issued by many threads: each fences its own,
+// the barrier orders them before thread 0, and thread 0's ticket is an acq_rel atomic -- a release that is cumulative
+// over everything ordered before it through the barrier (a relaxed atomicAdd behind per-thread fences is not a
+// release pattern for the OTHER threads' writes), and the acquire the finalising CTA needs.
+__device__ __forceinline__ unsigned ticket_acq_rel(unsigned* counter) {
+    unsigned t;
+    asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], %2;" : "=r"(t) : "l"(counter), "r"(1u) : "memory");
+    return t;
+}
 __device__ __forceinline__ bool ring_last_cta(unsigned* counter, unsigned total, unsigned* s_flag) {
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) *s_flag = (atomicAdd(counter, 1u) == total - 1u) ? 1u : 0u;
+    if (threadIdx.x == 0) *s_flag = (ticket_acq_rel(counter) == total - 1u) ? 1u : 0u;
     __syncthreads();
-    const bool last = *s_flag != 0u;
-    if (last) __threadfence();
-    return last;
+    return *s_flag != 0u;
 }
 
 // Merge of the ranks' (mean, M2, n) messages for channel c, or the running statistics in eval mode
@@ -524,7 +531,7 @@ bn_resident_kernel(const __grid_constant__ RingArgs a) {
     __threadfence();
     named_bar_sync(1, kRingConsumers);
     if (t == 0) {
-        atomicAdd(a.gbar, 1u);
+        ticket_acq_rel(a.gbar);                      // release, cumulative over the CTA's reductions (see ring_last_cta)
         unsigned long long t0 = 0;
         for (unsigned spins = 1; ld_acquire_gpu(a.gbar) < gridDim.x; ++spins) {
             if ((spins & 1023u) == 0u) {

@@ -314,7 +314,9 @@ def test_large_layer_shapes_property():
 # ----------------------------------------------------------------------------- residual add + ReLU (resnet_big.py:27-30,60-63)
 @pytest.mark.parametrize('shape,cl,dtype', [((32, 64, 16, 16), True, torch.float32), ((256, 256, 8, 8), True, torch.bfloat16),
                                             ((512, 64, 32, 32), True, torch.bfloat16), ((16, 24, 5, 7), False, torch.float32),
-                                            ((64, 128), False, torch.float32)])
+                                            ((64, 128), False, torch.float32),
+                                            ((640, 128, 8, 8), True, torch.bfloat16),      # forward: shared-memory-resident pass
+                                            ((320, 128, 8, 8), True, torch.bfloat16)])     # both directions resident
 @pytest.mark.parametrize('relu', [True, False])
 def test_residual_add_relu_matches_unfused_expression(shape, cl, dtype, relu):
     """y = relu(bn(x) + z) in one pass vs torch autograd on the unfused expression (fp64 reference)."""
@@ -356,9 +358,12 @@ def test_residual_add_relu_matches_unfused_expression(shape, cl, dtype, relu):
 
 
 @pytest.mark.parametrize('shape,dtype', [((256, 256, 8, 8), torch.bfloat16), ((64, 128, 8, 8), torch.float32),
-                                         ((512, 512, 4, 4), torch.bfloat16), ((128, 256, 16, 16), torch.bfloat16)])
+                                         ((512, 512, 4, 4), torch.bfloat16), ((128, 256, 16, 16), torch.bfloat16),
+                                         ((384, 256, 8, 8), torch.bfloat16), ((512, 256, 8, 8), torch.bfloat16),
+                                         ((200, 96, 8, 8), torch.float32)])
 def test_cluster_kernels_match_multi_kernel_path(shape, dtype, monkeypatch):
-    """Single-launch cluster kernels vs stats -> apply / reduce -> apply on the same tensors."""
+    """Single-launch kernels (register-resident cluster passes; for the 12-16 MB shapes the shared-memory-resident
+    passes behind the cooperative grid barrier) vs stats -> apply / reduce -> apply on the same tensors."""
     torch.manual_seed(5)
     C = shape[1]
     x = (torch.randn(shape, device=DEV) * 1.7 + 0.4).to(dtype).contiguous(memory_format=torch.channels_last)
@@ -376,7 +381,12 @@ def test_cluster_kernels_match_multi_kernel_path(shape, dtype, monkeypatch):
     # the ReLU gate may flip for outputs within rounding of zero: compare away from it
     far = outs[1][0].abs() > 1e-2
     assert torch.all(((outs[0][0] - outs[1][0]).abs() <= tol * outs[1][0].abs() + 1e-5) | ~far)
-    assert torch.all(((outs[0][1] - outs[1][1]).abs() <= tol * outs[1][1].abs() + 1e-4) | ~far)
+    # ... and a flipped gate moves sum(dy) and sum(dy (x - mean)) of its channel by that one element, i.e. every dx
+    # of the channel by O(|dy| (1 + xhat^2) / n).  The ring / resident / tiled passes sum through float atomics, so
+    # their statistics differ in the last bit from run to run and such flips do occur (seen: one element of channel
+    # 52 of [384,256,8,8], 3e-4 on that channel's dx, on either side of the comparison).
+    n = x.numel() // C
+    assert torch.all(((outs[0][1] - outs[1][1]).abs() <= tol * outs[1][1].abs() + 1e-4 + 40.0 / n) | ~far)
     for a, b in zip(outs[0][2:], outs[1][2:]):
         assert torch.allclose(a, b, rtol=1e-4, atol=1e-3 * max(1.0, float(b.abs().max())))
 

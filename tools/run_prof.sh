@@ -17,6 +17,14 @@ case "$1" in
     timeout 300 python tools/time_bn.py 512 256 16 16 > gpurun_out/prof_bn_ring_plain.log 2>&1 || exit 1
     timeout 900 ncu --set full --clock-control none --import-source on -k regex:bn_ring -s 8 -c 4 -f -o gpurun_out/r2_bn_ring \
         python tools/time_bn.py 512 256 16 16 > gpurun_out/prof_bn_ring_ncu.log 2>&1 ;;
+  bn_ring_large)
+    timeout 300 python tools/time_bn.py 512 256 32 32 > gpurun_out/prof_bn_ring_large_plain.log 2>&1 || exit 1
+    timeout 900 ncu --set full --clock-control none --import-source on -k regex:bn_ring -s 8 -c 4 -f -o gpurun_out/r2_bn_ring_large \
+        python tools/time_bn.py 512 256 32 32 > gpurun_out/prof_bn_ring_large_ncu.log 2>&1 ;;
+  bn_small_bwd)
+    timeout 300 python tools/time_bn.py > gpurun_out/prof_bn_small_plain.log 2>&1 || exit 1
+    timeout 900 ncu --set full --clock-control none --import-source on -k regex:bn_bwd_cluster -s 4 -c 2 -f -o gpurun_out/r2_bn_cluster_bwd \
+        python tools/time_bn.py > gpurun_out/prof_bn_small_bwd_ncu.log 2>&1 ;;
   head)
     timeout 300 python -m pytest tests/test_head_gpu.py -q -m gpu -k "1024-2048-128-2" > gpurun_out/prof_head_plain.log 2>&1 || exit 1
     timeout 900 ncu --set full --clock-control none --import-source on -k regex:head_tc -c 1 -f -o gpurun_out/r2_head \
