@@ -368,6 +368,13 @@ def test_cluster_kernels_match_multi_kernel_path(shape, dtype, monkeypatch):
     C = shape[1]
     x = (torch.randn(shape, device=DEV) * 1.7 + 0.4).to(dtype).contiguous(memory_format=torch.channels_last)
     dy = torch.randn(shape, device=DEV).to(dtype).contiguous(memory_format=torch.channels_last)
+    # Keep every pre-activation away from the ReLU threshold.  The passes that sum through float atomics are not
+    # bitwise reproducible, so an element within rounding of zero may be gated differently from run to run, and ONE
+    # flipped element moves sum(dy), dgamma and dbeta of its channel by O(1) (seen on channel 52 of [384,256,8,8]).
+    ax = [0, 2, 3]
+    xd64 = x.double()
+    pre = (xd64 - xd64.mean(ax, keepdim=True)) / torch.sqrt(xd64.var(ax, unbiased=False, keepdim=True) + 1e-5) * 1.25 + 0.1
+    x = torch.where(pre.abs() < 4e-3, x + 0.25, x).contiguous(memory_format=torch.channels_last)
     outs = []
     for fused in ('1', '0'):
         monkeypatch.setenv('SCB_BN_FUSED', fused)
@@ -381,12 +388,7 @@ def test_cluster_kernels_match_multi_kernel_path(shape, dtype, monkeypatch):
     # the ReLU gate may flip for outputs within rounding of zero: compare away from it
     far = outs[1][0].abs() > 1e-2
     assert torch.all(((outs[0][0] - outs[1][0]).abs() <= tol * outs[1][0].abs() + 1e-5) | ~far)
-    # ... and a flipped gate moves sum(dy) and sum(dy (x - mean)) of its channel by that one element, i.e. every dx
-    # of the channel by O(|dy| (1 + xhat^2) / n).  The ring / resident / tiled passes sum through float atomics, so
-    # their statistics differ in the last bit from run to run and such flips do occur (seen: one element of channel
-    # 52 of [384,256,8,8], 3e-4 on that channel's dx, on either side of the comparison).
-    n = x.numel() // C
-    assert torch.all(((outs[0][1] - outs[1][1]).abs() <= tol * outs[1][1].abs() + 1e-4 + 40.0 / n) | ~far)
+    assert torch.all(((outs[0][1] - outs[1][1]).abs() <= tol * outs[1][1].abs() + 1e-4) | ~far)
     for a, b in zip(outs[0][2:], outs[1][2:]):
         assert torch.allclose(a, b, rtol=1e-4, atol=1e-3 * max(1.0, float(b.abs().max())))
 
