@@ -199,7 +199,8 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
         from simclr_pytorch_distributed_b200.gather import DistributedSupConLoss
         crit = DistributedSupConLoss(temperature=TEMP, engine=engine, normalize=False)
         fwd = lambda f: crit(f)                                                     # noqa: E731
-        fwd_e2e = fwd
+        crit_g = DistributedSupConLoss(temperature=TEMP, engine=engine, normalize=False, graph=True)
+        fwd_e2e = lambda f: crit_g(f)                                               # noqa: E731
 
     ones = torch.ones((), dtype=dtype, device='cuda')       # upstream gradient of the scalar loss, allocated once
 
@@ -935,8 +936,9 @@ def main():
             'e2e': {'value': B_GLOBAL / (ms_e2e / args.steps * 1e-3), 'unit': 'pairs/s',
                     'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                     'note': 'each step: H2D of its embeddings from pinned memory (prefetched one step ahead on a '
-                            'copy stream), forward + backward through SupConLoss(graph=True) at N=1 (the module replays '
-                            'a captured forward+backward), D2H of the loss, host sync; the gradient stays on the device'},
+                            'copy stream), forward + backward through the module in graph mode (SupConLoss / '
+                            'DistributedSupConLoss with graph=True: one captured forward+backward, exchanges '
+                            'included, replayed per step), D2H of the loss, host sync; the gradient stays on the device'},
             'gpu_launches': int(launches),
         })
         # roofline of the STEP (6*A*C*D algorithmic FLOPs of SURVEY 8(d) over the graph-replayed step time, per GPU);

@@ -298,8 +298,13 @@ class DistributedSupConLoss(nn.Module):
     """
 
     def __init__(self, temperature=0.07, contrast_mode='all', base_temperature=0.07, engine='auto',
-                 normalize=True, process_group=None):
+                 normalize=True, process_group=None, graph=False):
         super().__init__()
+        # graph=True: as SupConLoss(graph=True) -- forward + backward (both exchanges included) captured once per shape
+        # and replayed; the input is always copied into a buffer the module owns, so that "capture or replay" depends
+        # on the shape alone and every rank decides alike.  SimCLR mode only (labels take the eager path).
+        self.graph = graph
+        self._graph_cache = None
         self.temperature = temperature
         self.contrast_mode = contrast_mode
         self.base_temperature = base_temperature
@@ -323,6 +328,14 @@ class DistributedSupConLoss(nn.Module):
             features = features.contiguous()
         bsz, n_views, dim = features.shape
         dev = features.device
+        if (self.graph and labels is None and OPS.requires_cuda and features.requires_grad and torch.is_grad_enabled()
+                and not torch.cuda.is_current_stream_capturing()):
+            if self._graph_cache is None:
+                self._graph_cache = L.GraphCache(
+                    lambda: DistributedSupConLoss(self.temperature, self.contrast_mode, self.base_temperature,
+                                                  self.engine, self.normalize, self.process_group),
+                    bind_addresses=False)
+            return self._graph_cache.run(features, None)
         labels_all = None
         mask_kind = _lib.MASK_SIMCLR
         if labels is not None:

@@ -358,7 +358,7 @@ class SupConLoss(nn.Module):
         # As with torch.cuda.make_graphed_callables the returned loss is the graph's own output buffer: read it
         # (.item(), a copy) before the next call with the same shape overwrites it.
         self.graph = graph
-        self._graphs = {}
+        self._graph_cache = None
         self.temperature = temperature
         self.contrast_mode = contrast_mode
         self.base_temperature = base_temperature
@@ -420,20 +420,36 @@ class SupConLoss(nn.Module):
                                      float(self.base_temperature), bool(self.normalize), norms)
 
     # ------------------------------------------------------------------ graph mode
-    _MAX_ADDRESSES = 4          # captured graphs bound to the caller's own input buffers, per shape
-
     def _graphed(self, features, labels):
-        """Forward through a captured graph.  A graph is bound to the address of its input: callers that feed the loss
-        from a few recurring buffers (a double-buffered prefetcher, a preallocated projection output) get one graph
-        per buffer and no copy; any other input is copied into a buffer the module owns."""
+        if self._graph_cache is None:
+            self._graph_cache = GraphCache(lambda: SupConLoss(self.temperature, self.contrast_mode, self.base_temperature,
+                                                              self.engine, self.normalize))
+        return self._graph_cache.run(features, labels)
+
+
+class GraphCache:
+    """Captured forward+backward graphs of a loss module, per (shape, dtype, strides, labels?) and input address.
+
+    A graph is bound to the address of its input: callers that feed the loss from a few recurring buffers (a
+    double-buffered prefetcher, a preallocated projection output) get one graph per buffer and no copy; any other
+    input is copied into a buffer the cache owns.  `bind_addresses=False` (the row-sharded loss): always the owned
+    buffer, so that whether a call captures or replays depends on the shape alone and every rank decides alike."""
+    MAX_ADDRESSES = 4           # captured graphs bound to the caller's own input buffers, per shape
+
+    def __init__(self, make_inner, bind_addresses=True):
+        self.make_inner = make_inner
+        self.bind_addresses = bind_addresses
+        self.graphs = {}
+
+    def run(self, features, labels):
         dev = features.device
         base = (tuple(features.shape), features.dtype, dev.index, tuple(features.stride()), labels is not None)
-        per_shape = self._graphs.setdefault(base, {})
+        per_shape = self.graphs.setdefault(base, {})
         addr = features.data_ptr()
-        entry = per_shape.get(addr)
+        entry = per_shape.get(addr) if self.bind_addresses else None
         if entry is None:
             bound = [k for k in per_shape if k != 'own']
-            if len(bound) < self._MAX_ADDRESSES and features.is_contiguous():
+            if self.bind_addresses and len(bound) < self.MAX_ADDRESSES and features.is_contiguous():
                 entry = self._capture(features, labels, own_input=False)
                 per_shape[addr] = entry
             else:
@@ -445,7 +461,7 @@ class SupConLoss(nn.Module):
         return _GraphedSupCon.apply(features, entry)
 
     def _capture(self, features, labels, own_input):
-        inner = SupConLoss(self.temperature, self.contrast_mode, self.base_temperature, self.engine, self.normalize)
+        inner = self.make_inner()
         e = _GraphEntry()
         e.own_input, e.serial = own_input, 0
         e.x = (torch.empty_like(features) if own_input else features.detach())

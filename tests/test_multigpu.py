@@ -181,6 +181,23 @@ def _worker(rank, world, port, q):
             e_l, e_g, e_y, e_x, (bn.running_var - ref_bn.running_var).abs().max().item()))
         ok = ok and e_l <= 2e-3 + 2 ** -8 and e_g <= 2 * (2e-3 + 2 ** -8) and e_y <= 2.0 ** -7 and e_x <= 2.0 ** -7
         ok = ok and (bn.running_var - ref_bn.running_var).abs().max().item() <= 1e-4
+        # ---------------- the module's own graph mode: fresh tensors every step (always copied into the module's
+        # buffer, so every rank captures at the same call), against the eager module bit for bit
+        eager_m = DistributedSupConLoss(temperature=0.5, engine='bf16', normalize=False)
+        graph_m = DistributedSupConLoss(temperature=0.5, engine='bf16', normalize=False, graph=True)
+        same = True
+        for step in range(20, 25):
+            rng = np.random.default_rng(2000 + step)
+            zh = torch.from_numpy(normalize_rows(rng.standard_normal((world * bsz, V, D)))).to(torch.bfloat16)
+            fa = zh[rank * bsz:(rank + 1) * bsz].to(dev).requires_grad_(True)
+            fb = fa.detach().clone().requires_grad_(True)
+            la = eager_m(fa)
+            (2.0 * la).backward()
+            lb = graph_m(fb)
+            (2.0 * lb).backward()
+            same = same and bool(torch.equal(la.detach(), lb.detach())) and bool(torch.equal(fa.grad, fb.grad))
+        notes.append('graph mode of the module == eager: %s' % same)
+        ok = ok and same
     except Exception as e:     # report instead of hanging the other ranks
         ok = False
         notes.append('EXC %r' % (e,))
