@@ -29,6 +29,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
+
 namespace scb {
 using namespace ptx;
 
@@ -1696,11 +1698,15 @@ int tc_make_tmap_2d(const void* ptr, int64_t rows, int64_t cols, int64_t ld, CUt
 }
 
 static constexpr int kMaxSlots = 32;
-static long long* g_trace = nullptr;   // set through scb_debug_set_trace (diagnostics only)
-void tc_set_trace(long long* p) { g_trace = p; }
+// diagnostics hooks: set from the caller's thread, read by whichever thread launches (autograd's, for the backward)
+static std::atomic<long long*> g_trace{nullptr};   // set through scb_debug_set_trace
+void tc_set_trace(long long* p) { g_trace.store(p, std::memory_order_release); }
 // measurement aid (scb_debug_set_events): events recorded right before / after the backward main kernel
-static cudaEvent_t g_ev_start = nullptr, g_ev_stop = nullptr;
-void tc_set_events(void* a, void* b) { g_ev_start = (cudaEvent_t)a; g_ev_stop = (cudaEvent_t)b; }
+static std::atomic<cudaEvent_t> g_ev_start{nullptr}, g_ev_stop{nullptr};
+void tc_set_events(void* a, void* b) {
+    g_ev_start.store((cudaEvent_t)a, std::memory_order_release);
+    g_ev_stop.store((cudaEvent_t)b, std::memory_order_release);
+}
 
 static_assert(sizeof(TcParams) % 4 == 0 && sizeof(TcParams) <= 1024, "TcParams copy in shared memory");
 struct TcGeom { int CT, RB, T, q, grid, n_split, direct; };
@@ -1817,7 +1823,7 @@ static void fill_params(const scb_supcon_problem* p, int row_begin, int n_rows, 
     t->fo.po = PeerOut::none();
     t->dk_part = w.dk_part;
     t->pair = 0;
-    t->trace = g_trace;
+    t->trace = g_trace.load(std::memory_order_acquire);
 }
 
 static int launch_label_rows(const scb_supcon_problem* p, const TcParams& t, bool with_sums, cudaStream_t stream) {
@@ -1964,7 +1970,7 @@ static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_ro
         SCB_CUDA_OK(launch_pdl_cluster(supcon_tc_bwd_kernel<KCH_, DIR_, X3_>, dim3(g.grid), dim3(kBwdThreads), smem, stream, \
                                        DIR_ ? g.direct : 1, tmap, tmap_lo, t));                         \
     } while (0)
-    if (g_ev_start) SCB_CUDA_OK(cudaEventRecord(g_ev_start, stream));
+    if (cudaEvent_t ev = g_ev_start.load(std::memory_order_acquire)) SCB_CUDA_OK(cudaEventRecord(ev, stream));
     if (x3) {
         if (kch == 2) { if (g.direct) SCB_LAUNCH_BWD(2, true, true); else SCB_LAUNCH_BWD(2, false, true); }
         else { if (g.direct) SCB_LAUNCH_BWD(1, true, true); else SCB_LAUNCH_BWD(1, false, true); }
@@ -1973,7 +1979,7 @@ static int tc_backward_main(const scb_supcon_problem* p, int row_begin, int n_ro
         else { if (g.direct) SCB_LAUNCH_BWD(1, true, false); else SCB_LAUNCH_BWD(1, false, false); }
     }
 #undef SCB_LAUNCH_BWD
-    if (g_ev_stop) SCB_CUDA_OK(cudaEventRecord(g_ev_stop, stream));
+    if (cudaEvent_t ev = g_ev_stop.load(std::memory_order_acquire)) SCB_CUDA_OK(cudaEventRecord(ev, stream));
     SCB_CUDA_OK(cudaGetLastError());
     count_launch();
     *g_out = g;
