@@ -821,7 +821,14 @@ static int resident_launch(Kern kern, const RingArgs& a, int grid, size_t smem, 
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    SCB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, a));
+    const cudaError_t err = cudaLaunchKernelEx(&cfg, kern, a);
+    if (err == cudaErrorCooperativeLaunchTooLarge || err == cudaErrorLaunchOutOfResources) {
+        // fewer CTAs can be resident at once than the grid needs (MPS / MIG limits, a smaller part): the barrier
+        // would not be legal, the caller takes the cluster or ring passes instead
+        cudaGetLastError();
+        return kRingUnsupported;
+    }
+    SCB_CUDA_OK(err);
     count_launch();
     return SCB_OK;
 }
