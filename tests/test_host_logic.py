@@ -89,3 +89,27 @@ def test_convert_sync_batchnorm_shares_parameters():
     # converting the stock torch.nn.SyncBatchNorm works too (it is a _BatchNorm)
     out2 = SyncBatchNorm.convert_sync_batchnorm(torch.nn.Sequential(torch.nn.SyncBatchNorm(4)))
     assert isinstance(out2[0], SyncBatchNorm)
+
+
+def test_projection_tail_host_checks_and_state():
+    from simclr_pytorch_distributed_b200 import ProjectionTail
+    with pytest.raises(ValueError, match='out_features'):
+        ProjectionTail(64, 256)
+    with pytest.raises(ValueError, match='in_features'):
+        ProjectionTail(60, 32)
+    tail = ProjectionTail(64, 32, n_views=2)
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        tail(torch.zeros(4, 64))
+    with pytest.raises(ValueError, match=r'expected input \[rows, 64\]'):
+        tail(torch.zeros(4, 32))
+    lin = torch.nn.Linear(64, 32)
+    shared = ProjectionTail.from_linear(lin, n_views=2)
+    assert shared.weight is lin.weight and shared.bias is lin.bias
+    assert list(tail.state_dict().keys()) == list(lin.state_dict().keys())
+    tail.load_state_dict(lin.state_dict())
+
+
+def test_graph_mode_is_off_the_cpu_path():
+    # graph=True changes nothing about argument checking: CPU tensors are still refused before any capture
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        SupConLoss(graph=True)(torch.zeros(4, 2, 8, requires_grad=True))
