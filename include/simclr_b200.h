@@ -57,6 +57,12 @@ extern "C" {
 #define SCB_BN_ADD 2        /* y = bn(x) + z: the residual add of resnet_big.py:27-30,60-63;
                                with SCB_BN_RELU the ReLU comes after the add and the backward
                                gates dy by the SAVED output (y > 0) and also returns dz          */
+#define SCB_BN_PDL 4        /* scb_bn_apply (training mode, no residual) and scb_bn_backward_apply only: the
+                               caller vouches that the tensors the pass READS (x; x, dy, y) were complete
+                               before the PREVIOUS kernel of the stream started -- true when that kernel is
+                               scb_bn_stats / scb_bn_backward_reduce on the same tensors.  The pass is then
+                               launched with programmatic stream serialisation and starts filling its
+                               shared-memory ring while its predecessor is still in its reduction tail. */
 
 const char* scb_last_error(void);
 int scb_version(void);

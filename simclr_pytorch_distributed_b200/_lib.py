@@ -30,6 +30,7 @@ ENGINE_FP32, ENGINE_BF16, ENGINE_BF16X3 = 0, 1, 2
 ROWS_VIEW_MAJOR, ROWS_SAMPLE_MAJOR = 0, 1
 BN_RELU = 1
 BN_ADD = 2
+BN_PDL = 4
 BN_NOALLOC_MAX_CHANNELS = 4096      # SCB_BN_NOALLOC_MAX_CHANNELS
 
 _lock = threading.Lock()

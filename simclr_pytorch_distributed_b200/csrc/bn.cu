@@ -874,7 +874,7 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* 
     if (outer * inner == 0) return SCB_OK;
     if (channels_last) {
         const int r = ring_backward_apply(dy, x, y, dx, dz, dtype, outer * inner, C, mean, invstd, weight, bias, sums,
-                                          n_total, gate, stream);
+                                          n_total, gate, flags, stream);
         if (r != kRingUnsupported) return r;
     }
     const int target = 4 * sm_count();

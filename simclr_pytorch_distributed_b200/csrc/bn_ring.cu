@@ -68,6 +68,9 @@ struct RingArgs {
     int64_t rows_per_cta;
     int C, vpr, rpp, chunk_rows, n_stage;
     int ncol;                 // column tiles: a CTA owns vpr 16-byte vectors of every row (vpr * ncol = whole row)
+    int pdl;                  // apply passes: launched with programmatic stream serialisation, the ring is filled
+                              // BEFORE griddepcontrol.wait (the caller vouches that the inputs were complete before
+                              // the previous kernel of the stream started: SCB_BN_PDL)
     int n_ranks, flags;
     float momentum, eps;
     const float *stats_all, *weight, *bias, *mean, *invstd, *sums, *n_total;
@@ -154,28 +157,7 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
         for (int s = 0; s < n_stage; ++s) { mbar_init(full(s), 1); mbar_init(empty(s), kRingConsumers / 32); }
         fence_barrier_init();
     }
-    if (kOp == kOpApply) {
-        for (int j = threadIdx.x; j < CW; j += kRingThreads) {
-            const int c = c_base + j;
-            float mean, invstd, m2, n;
-            ring_merged_stats(a.stats_all, a.n_ranks, C, c, a.running_mean, a.running_var, a.eps, mean, invstd, m2, n);
-            const float sc = (a.weight ? a.weight[c] : 1.f) * invstd;
-            table[j] = sc;
-            table[CW + j] = (a.bias ? a.bias[c] : 0.f) - mean * sc;
-            if (group == 0) {
-                if (a.save_mean) a.save_mean[c] = mean;
-                if (a.save_invstd) a.save_invstd[c] = invstd;
-                if (a.stats_all != nullptr) {
-                    if (a.running_mean) a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
-                    if (a.running_var)
-                        a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (m2 / (n - 1.f));
-                }
-                if (c == 0 && a.save_count) a.save_count[0] = n;
-                if (c == 0 && a.nbt && a.stats_all != nullptr) a.nbt[0] += 1;
-            }
-        }
-    }
-    __syncthreads();
+    __syncthreads();                                   // barriers initialised: the producer may start
 
     const int64_t r_beg = (int64_t)group * a.rows_per_cta;
     const int64_t r_end = min(a.M, r_beg + a.rows_per_cta);
@@ -191,7 +173,9 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
     if (warp == kRingConsumers / 32) {
         // ------------------------------------------------------------ producer
         // whole rows (ncol == 1): a stage is one contiguous copy per tensor, issued by lane 0; column tiles: one copy
-        // per row piece, the lanes share them
+        // per row piece, the lanes share them.  With a.pdl the copies start while the previous kernel of the stream
+        // (the reduce pass over the same tensors) is still in its tail: nothing the producer reads is written by it.
+        if (!a.pdl) pdl_wait();
         for (int k = 0; k < n_chunks; ++k) {
             const int s = k % n_stage;
             const int kk = kReverse ? n_chunks - 1 - k : k;
@@ -223,6 +207,29 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
         __syncwarp();
     } else {
         // ------------------------------------------------------------ consumers
+        pdl_wait();                                       // the previous kernel's results (statistics / sums) are final
+        if (kOp == kOpApply) {
+            for (int j = t; j < CW; j += kRingConsumers) {
+                const int c = c_base + j;
+                float mean, invstd, m2, n;
+                ring_merged_stats(a.stats_all, a.n_ranks, C, c, a.running_mean, a.running_var, a.eps, mean, invstd, m2, n);
+                const float sc = (a.weight ? a.weight[c] : 1.f) * invstd;
+                table[j] = sc;
+                table[CW + j] = (a.bias ? a.bias[c] : 0.f) - mean * sc;
+                if (group == 0) {
+                    if (a.save_mean) a.save_mean[c] = mean;
+                    if (a.save_invstd) a.save_invstd[c] = invstd;
+                    if (a.stats_all != nullptr) {
+                        if (a.running_mean) a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
+                        if (a.running_var)
+                            a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (m2 / (n - 1.f));
+                    }
+                    if (c == 0 && a.save_count) a.save_count[0] = n;
+                    if (c == 0 && a.nbt && a.stats_all != nullptr) a.nbt[0] += 1;
+                }
+            }
+            named_bar_sync(1, kRingConsumers);
+        }
         const int c0 = c_base + col * VEC;               // first of this thread's channels
         // per-thread channel constants
         float k0[VEC], k1[VEC], k2[VEC], k3[VEC], bb[VEC];
@@ -325,6 +332,7 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
             if (lane == 0) mbar_arrive(empty(s));
         }
         if (kReduces) {
+            pdl_launch_dependents();                      // rows done: the apply pass behind may take this SM as we leave
             // CTA sums: the rpp threads that share a column meet in shared memory (the ring is idle now)
             named_bar_sync(1, kRingConsumers);
             float* red = reinterpret_cast<float*>(ring);          // [rpp][2][CW]
@@ -685,10 +693,15 @@ static bool ring_geom(int64_t M, int C, int es, int n_loads, size_t table_bytes,
 }
 
 template <typename Kern>
-static int ring_launch(Kern kern, const RingArgs& a, int grid, size_t smem, cudaStream_t stream) {
+static int ring_launch(Kern kern, RingArgs a, int grid, size_t smem, cudaStream_t stream) {
     SCB_CUDA_OK(set_max_dynamic_smem(kern, (int)smem));
-    kern<<<grid, kRingThreads, smem, stream>>>(a);
-    SCB_CUDA_OK(cudaGetLastError());
+    a.pdl = (a.pdl && pdl_enabled()) ? 1 : 0;
+    if (a.pdl) {
+        SCB_CUDA_OK(launch_pdl(kern, dim3((unsigned)grid), dim3(kRingThreads), smem, stream, a));
+    } else {
+        kern<<<grid, kRingThreads, smem, stream>>>(a);
+        SCB_CUDA_OK(cudaGetLastError());
+    }
     count_launch();
     return SCB_OK;
 }
@@ -722,6 +735,9 @@ int ring_apply(const void* x, const void* z, void* y, int dtype, int64_t M, int 
     a.stats_all = stats_all; a.n_ranks = n_ranks; a.weight = weight; a.bias = bias;
     a.running_mean = running_mean; a.running_var = running_var; a.momentum = momentum; a.eps = eps;
     a.save_mean = save_mean; a.save_invstd = save_invstd; a.save_count = save_count; a.nbt = nbt; a.flags = flags;
+    // the ring may fill before the statistics pass has fully retired only if that pass came before this launch in the
+    // stream (training mode) and the caller vouches for the inputs; the residual operand is not covered by that
+    a.pdl = ((flags & SCB_BN_PDL) && stats_all != nullptr && !add) ? 1 : 0;
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (add) return ring_launch(bn_ring_kernel<T, kOpApply, 0, true>, a, grid, smem, stream);
         return ring_launch(bn_ring_kernel<T, kOpApply, 0, false>, a, grid, smem, stream);
@@ -753,7 +769,7 @@ int ring_backward_reduce(const void* dy, const void* x, const void* y, int dtype
 
 int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
                         const float* mean, const float* invstd, const float* weight, const float* bias,
-                        const float* sums, const float* n_total, int gate, cudaStream_t stream) {
+                        const float* sums, const float* n_total, int gate, int flags, cudaStream_t stream) {
     if (!al16(x) || !al16(dy) || !al16(dx) || (gate == 2 && !al16(y)) || (dz != nullptr && !al16(dz)))
         return kRingUnsupported;
     RingArgs a = {};
@@ -762,6 +778,7 @@ int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, 
     if (!ring_geom(M, C, es, gate == 2 ? 3 : 2, 0, &a, &grid, &smem)) return kRingUnsupported;
     a.in[0] = x; a.in[1] = dy; a.in[2] = y; a.out[0] = dx; a.out[1] = dz;
     a.mean = mean; a.invstd = invstd; a.weight = weight; a.bias = bias; a.sums = sums; a.n_total = n_total;
+    a.pdl = (flags & SCB_BN_PDL) ? 1 : 0;
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (gate == 2) return ring_launch(bn_ring_kernel<T, kOpBwdApply, 2, false>, a, grid, smem, stream);
         if (gate == 1) return ring_launch(bn_ring_kernel<T, kOpBwdApply, 1, false>, a, grid, smem, stream);

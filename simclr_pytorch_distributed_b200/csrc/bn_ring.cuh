@@ -27,7 +27,7 @@ int ring_backward_reduce(const void* dy, const void* x, const void* y, int dtype
                          cudaStream_t stream);
 int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
                         const float* mean, const float* invstd, const float* weight, const float* bias,
-                        const float* sums, const float* n_total, int gate, cudaStream_t stream);
+                        const float* sums, const float* n_total, int gate, int flags, cudaStream_t stream);
 
 // Single-launch passes with the tensor resident in shared memory and a grid barrier (cooperative launch); the scratch
 // is the ring kernels' (ring_ws_bytes).  `which`: 0 forward, 1 backward.

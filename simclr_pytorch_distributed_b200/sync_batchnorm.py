@@ -312,10 +312,13 @@ class _SyncBNFunction(torch.autograd.Function):
                 kern.stats(x, geom, stats_all)
                 if world_size > 1:
                     stats_all = _exchange(kern, stats_all, 2 * C + 1, process_group, world_size, dev)
+            # BN_PDL: x was complete before the statistics pass started, so the apply pass may start filling its ring
+            # while that pass (or the exchange behind it) is still retiring
             if z is not None:
                 kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags, z=z, **nbt_kw)
             else:
-                kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved, flags, **nbt_kw)
+                kern.apply(x, y, geom, stats_all, world_size, w32, b32, rm, rv, momentum, eps, saved,
+                           flags | (_lib.BN_PDL if use_batch_stats else 0), **nbt_kw)
         if rm is not running_mean and running_mean is not None:
             running_mean.copy_(rm)
         if rv is not running_var and running_var is not None:
@@ -369,7 +372,7 @@ class _SyncBNFunction(torch.autograd.Function):
                     grad_input = torch.empty_like(x)
                 if gated:
                     kw['dz'] = grad_z
-                kern.backward_apply(dy, x, grad_input, geom, saved, w32, b32, sums, flags, **kw)
+                kern.backward_apply(dy, x, grad_input, geom, saved, w32, b32, sums, flags | _lib.BN_PDL, **kw)
         if need_dz and not gated:
             grad_z = dy                                          # plain add: the gradient passes through
         if not need_dx:
