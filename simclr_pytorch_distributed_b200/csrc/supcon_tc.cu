@@ -1377,15 +1377,37 @@ supcon_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                         if (cc == 0) tr(4);
                         // exp, weight, (label term), (self column), bf16 pack, 16 words back into TMEM
                         float pv[32];
+                        if (kPolyLane >= 0) {
 #pragma unroll
-                        for (int c4 = 0; c4 < 8; ++c4) {
-                            const float4 c4v = *reinterpret_cast<const float4*>(cj + cc * 32 + c4 * 4);
-                            const float cvv[4] = {c4v.x, c4v.y, c4v.z, c4v.w};
+                            for (int c4 = 0; c4 < 8; ++c4) {
+                                const float4 c4v = *reinterpret_cast<const float4*>(cj + cc * 32 + c4 * 4);
+                                const float cvv[4] = {c4v.x, c4v.y, c4v.z, c4v.w};
 #pragma unroll
-                            for (int u = 0; u < 4; ++u) {
-                                const float a = fmaf(__uint_as_float(v[c4 * 4 + u]), p.c2, -lse2_i);
-                                const float e = (u == kPolyLane) ? ex2_fma(a) : ex2(a);   // one in four on the FMA pipe
-                                pv[c4 * 4 + u] = e * fmaf(R_i, cvv[u], 1.f);
+                                for (int u = 0; u < 4; ++u) {
+                                    const float a = fmaf(__uint_as_float(v[c4 * 4 + u]), p.c2, -lse2_i);
+                                    const float e = (u == kPolyLane) ? ex2_fma(a) : ex2(a);   // one in four on the FMA pipe
+                                    pv[c4 * 4 + u] = e * fmaf(R_i, cvv[u], 1.f);
+                                }
+                            }
+                        } else {
+                            // the same arithmetic on packed pairs (FFMA2 / FMUL2): 2.5 instead of 4 issue slots per
+                            // element around the MUFU, bitwise identical results
+                            const uint64_t c2p = pack2(p.c2, p.c2), lneg = pack2(-lse2_i, -lse2_i);
+                            const uint64_t Rp = pack2(R_i, R_i), onep = pack2(1.f, 1.f);
+#pragma unroll
+                            for (int c4 = 0; c4 < 8; ++c4) {
+                                const float4 c4v = *reinterpret_cast<const float4*>(cj + cc * 32 + c4 * 4);
+                                const uint64_t a01 = ffma2(pack2(__uint_as_float(v[c4 * 4]), __uint_as_float(v[c4 * 4 + 1])), c2p, lneg);
+                                const uint64_t a23 = ffma2(pack2(__uint_as_float(v[c4 * 4 + 2]), __uint_as_float(v[c4 * 4 + 3])), c2p, lneg);
+                                float a0, a1, a2, a3;
+                                unpack2(a01, a0, a1);
+                                unpack2(a23, a2, a3);
+                                const uint64_t w01 = ffma2(Rp, pack2(c4v.x, c4v.y), onep);
+                                const uint64_t w23 = ffma2(Rp, pack2(c4v.z, c4v.w), onep);
+                                const uint64_t p01 = fmul2(pack2(ex2(a0), ex2(a1)), w01);
+                                const uint64_t p23 = fmul2(pack2(ex2(a2), ex2(a3)), w23);
+                                unpack2(p01, pv[c4 * 4], pv[c4 * 4 + 1]);
+                                unpack2(p23, pv[c4 * 4 + 2], pv[c4 * 4 + 3]);
                             }
                         }
                         const int jc = j0 + cc * 32;
