@@ -32,7 +32,7 @@ class _Workspace:
 
     @classmethod
     def get(cls, device, nbytes, stream=None):
-        key = (device.index, stream if stream is not None else torch.cuda.current_stream(device).cuda_stream)
+        key = (device.index, stream if stream is not None else _stream(device))
         buf = cls._cache.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = torch.zeros(_round_up(max(nbytes, 1 << 16), 256), dtype=torch.uint8, device=device)
@@ -123,7 +123,8 @@ def _problem(plan, k, k_lo, labels, mask, temperature, base_temperature):
 
 
 def _stream(device):
-    return torch.cuda.current_stream(device).cuda_stream
+    # raw handle of torch's current stream (torch.cuda.current_stream(...).cuda_stream builds a Stream object: ~9 us)
+    return torch._C._cuda_getCurrentRawStream(device.index if device.index is not None else torch.cuda.current_device())
 
 
 class _on_device:

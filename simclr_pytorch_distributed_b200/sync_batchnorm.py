@@ -27,11 +27,15 @@ class _Kernels:
     """Thin typed wrappers over the C ABI (one per entry point of include/simclr_b200.h)."""
 
     _ws = {}
+    _ws_need = {}
+    _fused_cache = {}
 
     @classmethod
     def workspace(cls, lib, device, channels):
-        key = (device.index, torch.cuda.current_stream(device).cuda_stream)
-        need = lib.scb_bn_workspace_bytes(channels)
+        need = cls._ws_need.get(channels)
+        if need is None:
+            need = cls._ws_need[channels] = lib.scb_bn_workspace_bytes(channels)
+        key = (device.index, cls.stream(device))
         buf = cls._ws.get(key)
         if buf is None or buf.numel() < need:
             buf = torch.zeros(max(need, 1 << 16), dtype=torch.uint8, device=device)
@@ -40,17 +44,25 @@ class _Kernels:
 
     @staticmethod
     def stream(device):
-        return torch.cuda.current_stream(device).cuda_stream
+        # the raw handle of torch's current stream: torch.cuda.current_stream(device).cuda_stream costs ~9 us a call
+        # (it builds a Stream object), and a forward+backward asks five times
+        return torch._C._cuda_getCurrentRawStream(device.index if device.index is not None else torch.cuda.current_device())
 
     @classmethod
     def fused_supported(cls, x, geom, which, flags=0):
-        """True when this tensor fits the single-launch cluster kernels (which: 0 forward, 1 backward)."""
+        """True when this tensor fits the single-launch kernels (which: 0 forward, 1 backward)."""
         import os
         if os.environ.get('SCB_BN_FUSED', '1') == '0':          # tests / measurements: force the multi-kernel path
             return False
-        lib = _lib.load()
-        cl, outer, C, inner = geom
-        return bool(lib.scb_bn_fused_supported(_lib.dtype_code(x.dtype), cl, outer, C, inner, which, flags))
+        key = (x.dtype, geom, which, flags, x.device.index)
+        hit = cls._fused_cache.get(key)
+        if hit is None:
+            lib = _lib.load()
+            cl, outer, C, inner = geom
+            with torch.cuda.device(x.device):
+                hit = bool(lib.scb_bn_fused_supported(_lib.dtype_code(x.dtype), cl, outer, C, inner, which, flags))
+            cls._fused_cache[key] = hit
+        return hit
 
     @classmethod
     def stats(cls, x, geom, out_stats):
