@@ -287,6 +287,12 @@ int scb_peer_bcast(const void* src, const int64_t* seg, int n_seg, const void* c
  *                  0 -> memory is [N, C, HW] contiguous (NCHW; inner = HW).
  */
 
+/* param_dtype (SCB_F32 / SCB_BF16 / SCB_F16) in the entry points below is the element type of weight, bias,
+ * running_mean, running_var, grad_weight and grad_bias -- they are declared float* for the common case and read /
+ * written in the module's own dtype, so that a model converted with `.to(torch.bfloat16)` needs no conversion kernels
+ * around the passes (torch's own batch norm takes mixed dtypes the same way).  Statistics, saved mean / invstd and the
+ * exchanged messages are always fp32. */
+
 /* bytes of zero-initialised scratch for the two reduction kernels below (every kernel leaves it zeroed).  It has
  * two parts, [2C floats + tickets][4 x 2C floats + ticket]: channels-last tensors take the bulk-copy ring kernels
  * (csrc/bn_ring.cu), which use the second part; a caller that passes only the first (8 * C rounded up to 16, plus 16
@@ -332,7 +338,7 @@ int scb_bn_apply(const void* x, const void* z, void* y, int dtype, int channels_
                  const float* weight, const float* bias,
                  float* running_mean, float* running_var, float momentum, float eps,
                  float* save_mean, float* save_invstd, float* save_count, long long* num_batches_tracked,
-                 int flags, void* stream);
+                 int flags, int param_dtype, void* stream);
 
 /* Replaces torch.batch_norm_backward_reduce (_functions.py:139-153):
  *   out_sums[0:C] = sum dy, out_sums[C:2C] = sum dy (x - mean)   (the 2C floats all-reduced),
@@ -343,7 +349,7 @@ int scb_bn_backward_reduce(const void* dy, const void* x, const void* y, int dty
                            int64_t outer, int channels, int64_t inner,
                            const float* mean, const float* invstd,
                            const float* weight, const float* bias,
-                           float* out_sums, float* grad_weight, float* grad_bias, int flags,
+                           float* out_sums, float* grad_weight, float* grad_bias, int flags, int param_dtype,
                            void* workspace, int64_t workspace_bytes, void* stream);
 
 /* Replaces torch.batch_norm_backward_elemt (_functions.py:170-179):
@@ -355,7 +361,7 @@ int scb_bn_backward_apply(const void* dy, const void* x, const void* y, void* dx
                           int channels_last, int64_t outer, int channels, int64_t inner,
                           const float* mean, const float* invstd,
                           const float* weight, const float* bias,
-                          const float* sums, const float* n_total, int flags, void* stream);
+                          const float* sums, const float* n_total, int flags, int param_dtype, void* stream);
 
 /* Single-launch variants (csrc/bn_cluster.cu): the same arithmetic as scb_bn_stats + scb_bn_apply, resp.
  * scb_bn_backward_reduce + scb_bn_backward_apply (torch/nn/modules/_functions.py:39-122 and :139-179 at world
@@ -376,12 +382,13 @@ int scb_bn_cluster_occupancy(int cluster_size);
 int scb_bn_forward_fused(const void* x, const void* z, void* y, int dtype, int64_t rows, int channels,
                          const float* weight, const float* bias, float* running_mean, float* running_var,
                          float momentum, float eps, float* save_mean, float* save_invstd, float* save_count,
-                         long long* num_batches_tracked, int flags, void* workspace, int64_t workspace_bytes,
-                         void* stream);
+                         long long* num_batches_tracked, int flags, int param_dtype, void* workspace,
+                         int64_t workspace_bytes, void* stream);
 int scb_bn_backward_fused(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t rows,
                           int channels, const float* mean, const float* invstd, const float* weight,
                           const float* bias, const float* n_total, float* out_sums, float* grad_weight,
-                          float* grad_bias, int flags, void* workspace, int64_t workspace_bytes, void* stream);
+                          float* grad_bias, int flags, int param_dtype, void* workspace, int64_t workspace_bytes,
+                          void* stream);
 /* The reductions alone through the same cluster scheme, for several ranks (the exchange of
  * _functions.py:41-79 / :155-165 sits between them and scb_bn_apply / scb_bn_backward_apply):
  * scb_bn_stats_fused writes the (2C+1)-float message of scb_bn_stats, scb_bn_backward_reduce_fused the
@@ -390,7 +397,7 @@ int scb_bn_stats_fused(const void* x, int dtype, int64_t rows, int channels, flo
 int scb_bn_backward_reduce_fused(const void* dy, const void* x, const void* y, int dtype, int64_t rows, int channels,
                                  const float* mean, const float* invstd, const float* weight, const float* bias,
                                  const float* n_total, float* out_sums, float* grad_weight, float* grad_bias,
-                                 int flags, void* stream);
+                                 int flags, int param_dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -149,20 +149,20 @@ PROTOTYPES = {
     'scb_bn_stats': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp, _i64, _vp]),
     'scb_bn_stats_noalloc': (_i, [_vp, _i, _i, _i64, _i, _i64, _vp, _vp]),
     'scb_bn_apply': (_i, [_vp, _vp, _vp, _i, _i, _i64, _i, _i64, _vp, _i, _vp, _vp, _vp, _vp, _f, _f,
-                          _vp, _vp, _vp, _vp, _i, _vp]),
+                          _vp, _vp, _vp, _vp, _i, _i, _vp]),
     'scb_bn_backward_reduce': (_i, [_vp, _vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp,
-                                    _vp, _i, _vp, _i64, _vp]),
+                                    _vp, _i, _i, _vp, _i64, _vp]),
     'scb_bn_backward_apply': (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i64, _i, _i64, _vp, _vp, _vp, _vp, _vp,
-                                   _vp, _i, _vp]),
+                                   _vp, _i, _i, _vp]),
     'scb_bn_fused_supported': (_i, [_i, _i, _i64, _i, _i64, _i, _i]),
     'scb_bn_cluster_occupancy': (_i, [_i]),
-    'scb_bn_forward_fused': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _i, _vp,
-                                  _i64, _vp]),
+    'scb_bn_forward_fused': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _i, _i,
+                                  _vp, _i64, _vp]),
     'scb_bn_backward_fused': (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
-                                   _i, _vp, _i64, _vp]),
+                                   _i, _i, _vp, _i64, _vp]),
     'scb_bn_stats_fused': (_i, [_vp, _i, _i64, _i, _vp, _vp]),
     'scb_bn_backward_reduce_fused': (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i,
-                                          _vp]),
+                                          _i, _vp]),
 }
 
 

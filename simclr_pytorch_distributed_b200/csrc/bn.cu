@@ -210,10 +210,10 @@ bn_stats_nhwc_kernel(const T* __restrict__ x, int64_t M, int C, int TX, int64_t 
 __device__ __forceinline__ void merged_stats(const float* __restrict__ stats_all, int n_ranks, int C,
                                              int c, const float* running_mean,
                                              const float* running_var, float eps,
-                                             float& mean, float& invstd, float& m2, float& n) {
+                                             float& mean, float& invstd, float& m2, float& n, int pdt) {
     if (stats_all == nullptr) {
-        mean = running_mean[c];
-        invstd = rsqrtf(running_var[c] + eps);
+        mean = ldp(running_mean, pdt, c, 0.f);
+        invstd = rsqrtf(ldp(running_var, pdt, c, 1.f) + eps);
         m2 = 0.f; n = 1.f;      // eval: statistics are constants, the backward's 1/n terms vanish
         return;
     }
@@ -235,7 +235,7 @@ bn_apply_nhwc_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
                      int64_t rows_per_cta, const float* __restrict__ stats_all, int n_ranks,
                      const float* __restrict__ weight, const float* __restrict__ bias,
                      float* running_mean, float* running_var, float momentum, float eps,
-                     float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags) {
+                     float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags, int pdt) {
     extern __shared__ float sm[];           // [2][TX*VEC]: scale a, offset b
     const int TY = kBnThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
@@ -247,16 +247,16 @@ bn_apply_nhwc_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
         float a = 0.f, b = 0.f;
         if (c < C) {
             float mean, invstd, m2, n;
-            merged_stats(stats_all, n_ranks, C, c, running_mean, running_var, eps, mean, invstd, m2, n);
-            const float g = weight ? weight[c] : 1.f;
+            merged_stats(stats_all, n_ranks, C, c, running_mean, running_var, eps, mean, invstd, m2, n, pdt);
+            const float g = ldp(weight, pdt, c, 1.f);
             a = g * invstd;
-            b = (bias ? bias[c] : 0.f) - mean * a;
+            b = ldp(bias, pdt, c, 0.f) - mean * a;
             if (blockIdx.y == 0) {
                 if (save_mean) save_mean[c] = mean;
                 if (save_invstd) save_invstd[c] = invstd;
                 if (stats_all != nullptr) {
-                    if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-                    if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+                    if (running_mean) stp(running_mean, pdt, c, (1.f - momentum) * ldp(running_mean, pdt, c, 0.f) + momentum * mean);
+                    if (running_var) stp(running_var, pdt, c, (1.f - momentum) * ldp(running_var, pdt, c, 0.f) + momentum * (m2 / (n - 1.f)));
                 }
                 if (c == 0 && save_count) save_count[0] = n;
                 if (c == 0 && nbt && stats_all != nullptr) nbt[0] += 1;
@@ -318,7 +318,7 @@ bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, con
                           int C, int TX, int64_t rows_per_cta, const float* __restrict__ mean,
                           const float* __restrict__ invstd, const float* __restrict__ weight,
                           const float* __restrict__ bias, float* __restrict__ acc, unsigned* counter,
-                          float* __restrict__ out_sums, float* grad_weight, float* grad_bias) {
+                          float* __restrict__ out_sums, float* grad_weight, float* grad_bias, int pdt) {
     extern __shared__ float sm[];
     const int TY = kBnThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
@@ -332,8 +332,8 @@ bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, con
         for (int i = 0; i < VEC; ++i) {
             mu[i] = mean[c0 + i];
             if (kGate == 1) {   // y = (x - mu) * a + b, gate dy by y > 0
-                a[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
-                b[i] = bias ? bias[c0 + i] : 0.f;
+                a[i] = ldp(weight, pdt, c0 + i, 1.f) * invstd[c0 + i];
+                b[i] = ldp(bias, pdt, c0 + i, 0.f);
             }
         }
         const int64_t r_end = min(M, (int64_t)(blockIdx.y + 1) * rows_per_cta);
@@ -378,8 +378,8 @@ bn_bwd_reduce_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, con
             }
             out_sums[c] = sd;
             out_sums[C + c] = sx;
-            if (grad_weight) grad_weight[c] = sx * invstd[c];
-            if (grad_bias) grad_bias[c] = sd;
+            if (grad_weight) stp(grad_weight, pdt, c, sx * invstd[c]);
+            if (grad_bias) stp(grad_bias, pdt, c, sd);
         }
         if (threadIdx.x == 0) *counter = 0u;
     }
@@ -394,7 +394,7 @@ bn_bwd_apply_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, cons
                          T* __restrict__ dx, T* __restrict__ dz, int64_t M, int C, int TX, int64_t rows_per_cta,
                          const float* __restrict__ mean, const float* __restrict__ invstd,
                          const float* __restrict__ weight, const float* __restrict__ bias,
-                         const float* __restrict__ sums, const float* __restrict__ n_total) {
+                         const float* __restrict__ sums, const float* __restrict__ n_total, int pdt) {
     const int TY = kBnThreads / TX;
     const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = (blockIdx.x * TX + tx) * VEC;
@@ -407,10 +407,10 @@ bn_bwd_apply_nhwc_kernel(const T* __restrict__ dy, const T* __restrict__ x, cons
         const int c = c0 + i;
         const float is = invstd[c];
         mu[i] = mean[c];
-        k1[i] = (weight ? weight[c] : 1.f) * is;
+        k1[i] = ldp(weight, pdt, c, 1.f) * is;
         k2[i] = sums[c] * inv_n;
         k3[i] = is * is * sums[C + c] * inv_n;
-        bb[i] = bias ? bias[c] : 0.f;
+        bb[i] = ldp(bias, pdt, c, 0.f);
     }
     const int64_t r_beg = (int64_t)blockIdx.y * rows_per_cta;
     const int64_t r_end = min(M, r_beg + rows_per_cta);
@@ -511,19 +511,19 @@ bn_apply_nchw_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
                      int64_t n_per_cta, const float* __restrict__ stats_all, int n_ranks,
                      const float* __restrict__ weight, const float* __restrict__ bias,
                      float* running_mean, float* running_var, float momentum, float eps,
-                     float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags) {
+                     float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags, int pdt) {
     const int c = blockIdx.x;
     float mean, invstd, m2, n;
-    merged_stats(stats_all, n_ranks, C, c, running_mean, running_var, eps, mean, invstd, m2, n);
-    const float a = (weight ? weight[c] : 1.f) * invstd;
-    const float b = (bias ? bias[c] : 0.f) - mean * a;
+    merged_stats(stats_all, n_ranks, C, c, running_mean, running_var, eps, mean, invstd, m2, n, pdt);
+    const float a = ldp(weight, pdt, c, 1.f) * invstd;
+    const float b = ldp(bias, pdt, c, 0.f) - mean * a;
     __syncthreads();   // every thread has read the running stats before thread 0 rewrites them
     if (blockIdx.y == 0 && threadIdx.x == 0) {
         if (save_mean) save_mean[c] = mean;
         if (save_invstd) save_invstd[c] = invstd;
         if (stats_all != nullptr) {
-            if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-            if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+            if (running_mean) stp(running_mean, pdt, c, (1.f - momentum) * ldp(running_mean, pdt, c, 0.f) + momentum * mean);
+            if (running_var) stp(running_var, pdt, c, (1.f - momentum) * ldp(running_var, pdt, c, 0.f) + momentum * (m2 / (n - 1.f)));
         }
         if (c == 0 && save_count) save_count[0] = n;
         if (c == 0 && nbt && stats_all != nullptr) nbt[0] += 1;
@@ -550,14 +550,14 @@ bn_bwd_reduce_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, con
                           int64_t inner, int64_t n_per_cta, const float* __restrict__ mean,
                           const float* __restrict__ invstd, const float* __restrict__ weight,
                           const float* __restrict__ bias, float* __restrict__ acc, unsigned* counter,
-                          float* __restrict__ out_sums, float* grad_weight, float* grad_bias, int flags) {
+                          float* __restrict__ out_sums, float* grad_weight, float* grad_bias, int flags, int pdt) {
     __shared__ float sm[32];
     const int c = blockIdx.x;
     const float mu = mean[c];
     const bool relu = (flags & SCB_BN_RELU) != 0;
     const bool by_y = relu && (flags & SCB_BN_ADD) != 0;          // gate read from the saved output
-    const float a = relu ? (weight ? weight[c] : 1.f) * invstd[c] : 0.f;
-    const float b = (relu && bias) ? bias[c] : 0.f;
+    const float a = relu ? ldp(weight, pdt, c, 1.f) * invstd[c] : 0.f;
+    const float b = (relu) ? ldp(bias, pdt, c, 0.f) : 0.f;
     const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
     float s1 = 0.f, s2 = 0.f;
     nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
@@ -581,8 +581,8 @@ bn_bwd_reduce_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, con
         for (int cc = threadIdx.x; cc < C; cc += kBnThreads) {
             const float sd = __ldcg(acc + cc), sx = __ldcg(acc + C + cc);
             out_sums[cc] = sd; out_sums[C + cc] = sx;
-            if (grad_weight) grad_weight[cc] = sx * invstd[cc];
-            if (grad_bias) grad_bias[cc] = sd;
+            if (grad_weight) stp(grad_weight, pdt, cc, sx * invstd[cc]);
+            if (grad_bias) stp(grad_bias, pdt, cc, sd);
             acc[cc] = 0.f; acc[C + cc] = 0.f;
         }
         if (threadIdx.x == 0) *counter = 0u;
@@ -595,15 +595,15 @@ bn_bwd_apply_nchw_kernel(const T* __restrict__ dy, const T* __restrict__ x, cons
                          T* __restrict__ dx, T* __restrict__ dz, int64_t N, int C, int64_t inner, int64_t n_per_cta,
                          const float* __restrict__ mean, const float* __restrict__ invstd,
                          const float* __restrict__ weight, const float* __restrict__ bias,
-                         const float* __restrict__ sums, const float* __restrict__ n_total, int flags) {
+                         const float* __restrict__ sums, const float* __restrict__ n_total, int flags, int pdt) {
     const int c = blockIdx.x;
     const bool relu = (flags & SCB_BN_RELU) != 0;
     const float inv_n = 1.f / n_total[0];
     const float is = invstd[c], mu = mean[c];
-    const float k1 = (weight ? weight[c] : 1.f) * is;
+    const float k1 = ldp(weight, pdt, c, 1.f) * is;
     const float k2 = sums[c] * inv_n;
     const float k3 = is * is * sums[C + c] * inv_n;
-    const float bb = bias ? bias[c] : 0.f;
+    const float bb = ldp(bias, pdt, c, 0.f);
     const int64_t n0 = (int64_t)blockIdx.y * n_per_cta, n1 = min(N, n0 + n_per_cta);
     const bool by_y = relu && (flags & SCB_BN_ADD) != 0;
     nchw_foreach<T, VEC>(n0, n1, C, inner, c, [&](int64_t off) {
@@ -741,7 +741,7 @@ extern "C" int scb_bn_apply(const void* x, const void* z, void* y, int dtype, in
                             const float* weight, const float* bias, float* running_mean,
                             float* running_var, float momentum, float eps, float* save_mean,
                             float* save_invstd, float* save_count, long long* num_batches_tracked, int flags,
-                            void* stream_) {
+                            int param_dtype, void* stream_) {
     if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
     SCB_REQUIRE(y != nullptr, "bn_apply: null output");
     SCB_REQUIRE(stats_all != nullptr || (running_mean && running_var),
@@ -755,7 +755,8 @@ extern "C" int scb_bn_apply(const void* x, const void* z, void* y, int dtype, in
     if (outer * inner == 0) return SCB_OK;
     if (channels_last) {
         const int r = ring_apply(x, z, y, dtype, outer * inner, C, stats_all, n_ranks, weight, bias, running_mean,
-                                 running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags, stream);
+                                 running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags, param_dtype,
+                                 stream);
         if (r != kRingUnsupported) return r;
     }
     const int target = 4 * sm_count();
@@ -771,7 +772,7 @@ if (add) {
                     dim3 grid(g.grid_x, (unsigned)g.grid_y);
                     kern<<<grid, kBnThreads, smem, stream>>>((const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta,
                         stats_all, n_ranks, weight, bias, running_mean, running_var, momentum, eps, save_mean,
-                        save_invstd, save_count, num_batches_tracked, flags);
+                        save_invstd, save_count, num_batches_tracked, flags, param_dtype);
                 });
             } else {
                 SCB_VEC_SWITCH(nhwc_vec(C, sizeof(T), al), VEC, {
@@ -781,7 +782,7 @@ if (add) {
                     dim3 grid(g.grid_x, (unsigned)g.grid_y);
                     kern<<<grid, kBnThreads, smem, stream>>>((const T*)x, (const T*)z, (T*)y, M, C, g.tx, g.rows_per_cta,
                         stats_all, n_ranks, weight, bias, running_mean, running_var, momentum, eps, save_mean,
-                        save_invstd, save_count, num_batches_tracked, flags);
+                        save_invstd, save_count, num_batches_tracked, flags, param_dtype);
                 });
             }
         } else {
@@ -789,7 +790,8 @@ if (add) {
             dim3 grid(C, (unsigned)g.grid_y);
             SCB_VEC_SWITCH(g.vec, VEC, (bn_apply_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
                 (const T*)x, (const T*)z, (T*)y, outer, C, inner, g.n_per_cta, stats_all, n_ranks, weight, bias,
-                running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags)));
+                running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags,
+                param_dtype)));
         }
     });
     SCB_CUDA_OK(cudaGetLastError());
@@ -809,7 +811,7 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, const void*
                                       int64_t outer, int channels, int64_t inner, const float* mean,
                                       const float* invstd, const float* weight, const float* bias,
                                       float* out_sums, float* grad_weight, float* grad_bias, int flags,
-                                      void* workspace, int64_t workspace_bytes, void* stream_) {
+                                      int param_dtype, void* workspace, int64_t workspace_bytes, void* stream_) {
     if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
     SCB_REQUIRE(dy && mean && invstd && out_sums && workspace, "bn_backward_reduce: null pointer");
     SCB_REQUIRE(workspace_bytes >= legacy_ws_bytes(channels), "bn_backward_reduce: workspace too small");
@@ -825,7 +827,7 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, const void*
     }
     if (channels_last) {
         const int r = ring_backward_reduce(dy, x, y, dtype, outer * inner, C, mean, invstd, weight, bias, out_sums,
-                                           grad_weight, grad_bias, gate, (char*)workspace + legacy_ws_bytes(C),
+                                           grad_weight, grad_bias, gate, param_dtype, (char*)workspace + legacy_ws_bytes(C),
                                            workspace_bytes - legacy_ws_bytes(C), stream);
         if (r != kRingUnsupported) return r;
     }
@@ -843,7 +845,7 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, const void*
                     NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, resident_ctas(kern, smem));
                     dim3 grid(g.grid_x, (unsigned)g.grid_y);
                     kern<<<grid, kBnThreads, smem, stream>>>((const T*)dy, (const T*)x, (const T*)y, M, C, g.tx,
-                        g.rows_per_cta, mean, invstd, weight, bias, acc, counter, out_sums, grad_weight, grad_bias);
+                        g.rows_per_cta, mean, invstd, weight, bias, acc, counter, out_sums, grad_weight, grad_bias, param_dtype);
                 });
             });
         } else {
@@ -851,7 +853,7 @@ extern "C" int scb_bn_backward_reduce(const void* dy, const void* x, const void*
             dim3 grid(C, (unsigned)g.grid_y);
             SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_reduce_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
                 (const T*)dy, (const T*)x, (const T*)y, outer, C, inner, g.n_per_cta, mean, invstd, weight, bias, acc,
-                counter, out_sums, grad_weight, grad_bias, flags)));
+                counter, out_sums, grad_weight, grad_bias, flags, param_dtype)));
         }
     });
     SCB_CUDA_OK(cudaGetLastError());
@@ -863,7 +865,7 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* 
                                      int channels_last, int64_t outer, int channels, int64_t inner,
                                      const float* mean, const float* invstd, const float* weight,
                                      const float* bias, const float* sums, const float* n_total,
-                                     int flags, void* stream_) {
+                                     int flags, int param_dtype, void* stream_) {
     if (int e = check_bn_common(x, dtype, outer, channels, inner)) return e;
     SCB_REQUIRE(dy && dx && mean && invstd && sums && n_total, "bn_backward_apply: null pointer");
     const int gate = gate_mode(flags);
@@ -874,7 +876,7 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* 
     if (outer * inner == 0) return SCB_OK;
     if (channels_last) {
         const int r = ring_backward_apply(dy, x, y, dx, dz, dtype, outer * inner, C, mean, invstd, weight, bias, sums,
-                                          n_total, gate, flags, stream);
+                                          n_total, gate, flags, param_dtype, stream);
         if (r != kRingUnsupported) return r;
     }
     const int target = 4 * sm_count();
@@ -889,7 +891,7 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* 
                     NhwcGeom g = nhwc_geom(M, C, sizeof(T), al, resident_ctas(kern, 0));
                     dim3 grid(g.grid_x, (unsigned)g.grid_y);
                     kern<<<grid, kBnThreads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)y, (T*)dx, (T*)dz, M, C,
-                        g.tx, g.rows_per_cta, mean, invstd, weight, bias, sums, n_total);
+                        g.tx, g.rows_per_cta, mean, invstd, weight, bias, sums, n_total, param_dtype);
                 });
             });
         } else {
@@ -897,7 +899,7 @@ extern "C" int scb_bn_backward_apply(const void* dy, const void* x, const void* 
             dim3 grid(C, (unsigned)g.grid_y);
             SCB_VEC_SWITCH(g.vec, VEC, (bn_bwd_apply_nchw_kernel<T, VEC><<<grid, kBnThreads, 0, stream>>>(
                 (const T*)dy, (const T*)x, (const T*)y, (T*)dx, (T*)dz, outer, C, inner, g.n_per_cta, mean, invstd, weight,
-                bias, sums, n_total, flags)));
+                bias, sums, n_total, flags, param_dtype)));
         }
     });
     SCB_CUDA_OK(cudaGetLastError());

@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kClThreads, 1)
 bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __restrict__ y, int64_t M, int C,
                       const ClGeom g, const float* __restrict__ weight, const float* __restrict__ bias,
                       float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
-                      float* save_invstd, float* save_count, long long* nbt, float* out_stats, int flags) {
+                      float* save_invstd, float* save_count, long long* nbt, float* out_stats, int flags, int pdt) {
     constexpr int VEC = Vec16<T>::N;
     extern __shared__ float smf[];
     const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
@@ -191,13 +191,13 @@ bn_fwd_cluster_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __res
             }
         } else {
             const float invstd = rsqrtf(m2 / n + eps);
-            av = (weight ? weight[c] : 1.f) * invstd;
-            bv = (bias ? bias[c] : 0.f) - mean * av;
+            av = ldp(weight, pdt, c, 1.f) * invstd;
+            bv = ldp(bias, pdt, c, 0.f) - mean * av;
             if (rank == 0) {
                 if (save_mean) save_mean[c] = mean;
                 if (save_invstd) save_invstd[c] = invstd;
-                if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-                if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+                if (running_mean) stp(running_mean, pdt, c, (1.f - momentum) * ldp(running_mean, pdt, c, 0.f) + momentum * mean);
+                if (running_var) stp(running_var, pdt, c, (1.f - momentum) * ldp(running_var, pdt, c, 0.f) + momentum * (m2 / (n - 1.f)));
                 if (c == 0 && save_count) save_count[0] = n;
                 if (c == 0 && nbt) nbt[0] += 1;              // num_batches_tracked (batchnorm.py:763-764)
             }
@@ -243,7 +243,7 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
                       T* __restrict__ dx, T* __restrict__ dz, int64_t M, int C, const ClGeom g,
                       const float* __restrict__ mean, const float* __restrict__ invstd,
                       const float* __restrict__ weight, const float* __restrict__ bias,
-                      const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias) {
+                      const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias, int pdt) {
     constexpr int VEC = Vec16<T>::N;
     extern __shared__ float smf[];
     const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
@@ -296,8 +296,8 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
         for (int i = 0; i < VEC; ++i) {
             mu[i] = mean[c0 + i];
             // the scale is only needed before the reduction when the gate is recomputed from x
-            k1[i] = (kGate == 1) ? (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i] : 0.f;
-            bb[i] = (kGate == 1 && bias) ? bias[c0 + i] : 0.f;
+            k1[i] = (kGate == 1) ? ldp(weight, pdt, c0 + i, 1.f) * invstd[c0 + i] : 0.f;
+            bb[i] = (kGate == 1) ? ldp(bias, pdt, c0 + i, 0.f) : 0.f;
         }
 #pragma unroll
         for (int u = 0; u < kClRows; ++u) {
@@ -331,8 +331,8 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
         v3 = is * is * sx * inv_n;
         if (rank == 0) {
             if (out_sums) { out_sums[c] = sd; out_sums[C + c] = sx; }
-            if (grad_weight) grad_weight[c] = sx * is;
-            if (grad_bias) grad_bias[c] = sd;
+            if (grad_weight) stp(grad_weight, pdt, c, sx * is);
+            if (grad_bias) stp(grad_bias, pdt, c, sd);
         }
     }
     if (kMode == 1) return;
@@ -347,7 +347,7 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
 #pragma unroll
     for (int i = 0; i < VEC; ++i) {
         const float k2 = ab[tx * VEC + i], k3 = ab[CW + tx * VEC + i];
-        const float kk = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
+        const float kk = ldp(weight, pdt, c0 + i, 1.f) * invstd[c0 + i];
         cA[i] = kk;
         cB[i] = -k3 * kk;
         cD[i] = (mean[c0 + i] * k3 - k2) * kk;
@@ -397,7 +397,7 @@ __global__ void __launch_bounds__(kClThreads, 1)
 bn_fwd_stream_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __restrict__ y, int64_t M, int C,
                      const ClStream g, const float* __restrict__ weight, const float* __restrict__ bias,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
-                     float* save_invstd, float* save_count, long long* nbt, int flags) {
+                     float* save_invstd, float* save_count, long long* nbt, int flags, int pdt) {
     constexpr int VEC = Vec16<T>::N;
     extern __shared__ float smf[];
     const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
@@ -447,13 +447,13 @@ bn_fwd_stream_kernel(const T* __restrict__ x, const T* __restrict__ z, T* __rest
         const float mean = to_f32(x[c]) + S1 / n;
         const float m2 = fmaxf(S2 - S1 * S1 / n, 0.f);
         const float invstd = rsqrtf(m2 / n + eps);
-        av = (weight ? weight[c] : 1.f) * invstd;
-        bv = (bias ? bias[c] : 0.f) - mean * av;
+        av = ldp(weight, pdt, c, 1.f) * invstd;
+        bv = ldp(bias, pdt, c, 0.f) - mean * av;
         if (rank == 0) {
             if (save_mean) save_mean[c] = mean;
             if (save_invstd) save_invstd[c] = invstd;
-            if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-            if (running_var) running_var[c] = (1.f - momentum) * running_var[c] + momentum * (m2 / (n - 1.f));
+            if (running_mean) stp(running_mean, pdt, c, (1.f - momentum) * ldp(running_mean, pdt, c, 0.f) + momentum * mean);
+            if (running_var) stp(running_var, pdt, c, (1.f - momentum) * ldp(running_var, pdt, c, 0.f) + momentum * (m2 / (n - 1.f)));
             if (c == 0 && save_count) save_count[0] = n;
             if (c == 0 && nbt) nbt[0] += 1;
         }
@@ -504,7 +504,7 @@ bn_bwd_stream_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
                      T* __restrict__ dx, T* __restrict__ dz, int64_t M, int C, const ClStream g,
                      const float* __restrict__ mean, const float* __restrict__ invstd,
                      const float* __restrict__ weight, const float* __restrict__ bias,
-                     const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias) {
+                     const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias, int pdt) {
     constexpr int VEC = Vec16<T>::N;
     extern __shared__ float smf[];
     const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
@@ -524,8 +524,8 @@ bn_bwd_stream_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
     for (int i = 0; i < VEC; ++i) {
         s1[i] = 0.f; s2[i] = 0.f;
         mu[i] = mean[c0 + i];
-        k1[i] = (weight ? weight[c0 + i] : 1.f) * invstd[c0 + i];
-        bb[i] = (kGate == 1 && bias) ? bias[c0 + i] : 0.f;
+        k1[i] = ldp(weight, pdt, c0 + i, 1.f) * invstd[c0 + i];
+        bb[i] = (kGate == 1) ? ldp(bias, pdt, c0 + i, 0.f) : 0.f;
     }
     if (active) {
         for (int64_t rk = r_begin + ty; rk < r_end; rk += (int64_t)kStreamU * TY) {
@@ -571,8 +571,8 @@ bn_bwd_stream_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
         v3 = is * is * sx * inv_n;
         if (rank == 0) {
             if (out_sums) { out_sums[c] = sd; out_sums[C + c] = sx; }
-            if (grad_weight) grad_weight[c] = sx * is;
-            if (grad_bias) grad_bias[c] = sd;
+            if (grad_weight) stp(grad_weight, pdt, c, sx * is);
+            if (grad_bias) stp(grad_bias, pdt, c, sd);
         }
     }
     __syncthreads();
@@ -835,10 +835,10 @@ template <typename T, int kMode, int kGate>
 static cudaError_t cl_launch_bwd(const ClGeom& g, cudaStream_t stream, const void* dy, const void* x, const void* y,
                                  void* dx, void* dz, int64_t M, int C, const float* mean, const float* invstd,
                                  const float* weight, const float* bias, const float* n_total, float* out_sums,
-                                 float* grad_weight, float* grad_bias) {
+                                 float* grad_weight, float* grad_bias, int pdt) {
     return cl_launch(bn_bwd_cluster_kernel<T, kMode, kGate>, g, cl_smem_bytes(g.TX, Vec16<T>::N), stream, (const T*)dy,
                      (const T*)x, (const T*)y, (T*)dx, (T*)dz, M, C, g, mean, invstd, weight, bias, n_total, out_sums,
-                     grad_weight, grad_bias);
+                     grad_weight, grad_bias, pdt);
 }
 
 }  // namespace scb
@@ -890,7 +890,7 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
                                     const float* weight, const float* bias, float* running_mean,
                                     float* running_var, float momentum, float eps, float* save_mean,
                                     float* save_invstd, float* save_count, long long* num_batches_tracked, int flags,
-                                    void* workspace,
+                                    int param_dtype, void* workspace,
                                     int64_t workspace_bytes, void* stream_) {
     if (int e = cl_check(x, dtype, rows, channels)) return e;
     SCB_REQUIRE(y != nullptr, "bn_forward_fused: null output");
@@ -902,7 +902,7 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
     if (!cl_aligned16(x) || !cl_aligned16(y) || (add && !cl_aligned16(z))) SCB_CL_UNSUPPORTED("bn_forward_fused");
     if (cl_use_resident(dtype, M, C, 0, flags) && workspace != nullptr) {
         const int r = ring_forward_resident(x, add ? z : nullptr, y, dtype, M, C, weight, bias, running_mean, running_var,
-                                            momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags,
+                                            momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags, param_dtype,
                                             (char*)workspace + legacy_bn_ws_bytes(C),
                                             workspace_bytes - legacy_bn_ws_bytes(C), stream);
         if (r != kRingUnsupported) return r;
@@ -918,10 +918,10 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
             const T* xp = (const T*)x; const T* zp = (const T*)z; T* yp = (T*)y;
             if (add)
                 SCB_CUDA_OK(cl_launch_stream(bn_fwd_stream_kernel<T, true>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags));
+                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags, param_dtype));
             else
                 SCB_CUDA_OK(cl_launch_stream(bn_fwd_stream_kernel<T, false>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags));
+                                             running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, flags, param_dtype));
         });
         count_launch();
         return SCB_OK;
@@ -938,13 +938,13 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
         float* none = nullptr;
         if (add)
             SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, true, kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags));
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags, param_dtype));
         else if (nrows == kClRows)
             SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, false, kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags));
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags, param_dtype));
         else
             SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 0, false, 2 * kClRows>, g, smem, stream, xp, zp, yp, M, C, g, weight, bias,
-                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags));
+                                  running_mean, running_var, momentum, eps, save_mean, save_invstd, save_count, num_batches_tracked, none, flags, param_dtype));
     });
     count_launch();
     return SCB_OK;
@@ -967,7 +967,7 @@ extern "C" int scb_bn_stats_fused(const void* x, int dtype, int64_t rows, int ch
         const T* xp = (const T*)x; const T* zp = nullptr; T* yp = nullptr;
         float* none = nullptr; const float* cnone = nullptr;
         SCB_CUDA_OK(cl_launch(bn_fwd_cluster_kernel<T, 1, false, 2 * kClRows>, g, smem, stream, xp, zp, yp, M, C, g, cnone, cnone,
-                              none, none, 0.f, 0.f, none, none, none, (long long*)nullptr, out_stats, 0));
+                              none, none, 0.f, 0.f, none, none, none, (long long*)nullptr, out_stats, 0, SCB_F32));
     });
     count_launch();
     return SCB_OK;
@@ -976,8 +976,8 @@ extern "C" int scb_bn_stats_fused(const void* x, int dtype, int64_t rows, int ch
 static int bn_backward_cluster(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype,
                                int64_t rows, int channels, const float* mean, const float* invstd,
                                const float* weight, const float* bias, const float* n_total, float* out_sums,
-                               float* grad_weight, float* grad_bias, int flags, int reduce_only, void* workspace,
-                               int64_t workspace_bytes, void* stream_) {
+                               float* grad_weight, float* grad_bias, int flags, int param_dtype, int reduce_only,
+                               void* workspace, int64_t workspace_bytes, void* stream_) {
     if (int e = cl_check(x, dtype, rows, channels)) return e;
     SCB_REQUIRE(dy && mean && invstd && n_total, "bn_backward_fused: null pointer");
     SCB_REQUIRE(reduce_only || dx != nullptr, "bn_backward_fused: null dx");
@@ -992,7 +992,7 @@ static int bn_backward_cluster(const void* dy, const void* x, const void* y, voi
         SCB_CL_UNSUPPORTED("bn_backward_fused");
     if (!reduce_only && workspace != nullptr && cl_use_resident(dtype, M, C, 1, flags)) {
         const int r = ring_backward_resident(dy, x, y, dx, dz, dtype, M, C, mean, invstd, weight, bias, n_total, out_sums,
-                                             grad_weight, grad_bias, gate, (char*)workspace + legacy_bn_ws_bytes(C),
+                                             grad_weight, grad_bias, gate, param_dtype, (char*)workspace + legacy_bn_ws_bytes(C),
                                              workspace_bytes - legacy_bn_ws_bytes(C), stream);
         if (r != kRingUnsupported) return r;
     }
@@ -1008,9 +1008,9 @@ static int bn_backward_cluster(const void* dy, const void* x, const void* y, voi
                 const T* dyp = (const T*)dy; const T* xp = (const T*)x; const T* yp = (const T*)y;
                 T* dxp = (T*)dx; T* dzp = (T*)dz;
                 cudaError_t err;
-                if (gate == 2) err = cl_launch_stream(bn_bwd_stream_kernel<T, 2>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
-                else if (gate == 1) err = cl_launch_stream(bn_bwd_stream_kernel<T, 1>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
-                else err = cl_launch_stream(bn_bwd_stream_kernel<T, 0>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+                if (gate == 2) err = cl_launch_stream(bn_bwd_stream_kernel<T, 2>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
+                else if (gate == 1) err = cl_launch_stream(bn_bwd_stream_kernel<T, 1>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
+                else err = cl_launch_stream(bn_bwd_stream_kernel<T, 0>, g, smem, stream, dyp, xp, yp, dxp, dzp, M, C, g, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
                 SCB_CUDA_OK(err);
             });
             count_launch();
@@ -1022,13 +1022,13 @@ static int bn_backward_cluster(const void* dy, const void* x, const void* y, voi
         if (!cl_geom(M, C, sizeof(T), kClRows, &g)) SCB_CL_UNSUPPORTED("bn_backward_fused");
         cudaError_t err;
         if (reduce_only) {
-            if (gate == 2) err = cl_launch_bwd<T, 1, 2>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
-            else if (gate == 1) err = cl_launch_bwd<T, 1, 1>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
-            else err = cl_launch_bwd<T, 1, 0>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+            if (gate == 2) err = cl_launch_bwd<T, 1, 2>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
+            else if (gate == 1) err = cl_launch_bwd<T, 1, 1>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
+            else err = cl_launch_bwd<T, 1, 0>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
         } else {
-            if (gate == 2) err = cl_launch_bwd<T, 0, 2>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
-            else if (gate == 1) err = cl_launch_bwd<T, 0, 1>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
-            else err = cl_launch_bwd<T, 0, 0>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias);
+            if (gate == 2) err = cl_launch_bwd<T, 0, 2>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
+            else if (gate == 1) err = cl_launch_bwd<T, 0, 1>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
+            else err = cl_launch_bwd<T, 0, 0>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
         }
         SCB_CUDA_OK(err);
     });
@@ -1039,18 +1039,18 @@ static int bn_backward_cluster(const void* dy, const void* x, const void* y, voi
 extern "C" int scb_bn_backward_fused(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype,
                                      int64_t rows, int channels, const float* mean, const float* invstd,
                                      const float* weight, const float* bias, const float* n_total, float* out_sums,
-                                     float* grad_weight, float* grad_bias, int flags, void* workspace,
+                                     float* grad_weight, float* grad_bias, int flags, int param_dtype, void* workspace,
                                      int64_t workspace_bytes, void* stream_) {
     return bn_backward_cluster(dy, x, y, dx, dz, dtype, rows, channels, mean, invstd, weight, bias, n_total, out_sums,
-                               grad_weight, grad_bias, flags, 0, workspace, workspace_bytes, stream_);
+                               grad_weight, grad_bias, flags, param_dtype, 0, workspace, workspace_bytes, stream_);
 }
 
 extern "C" int scb_bn_backward_reduce_fused(const void* dy, const void* x, const void* y, int dtype, int64_t rows,
                                             int channels, const float* mean, const float* invstd,
                                             const float* weight, const float* bias, const float* n_total,
                                             float* out_sums, float* grad_weight, float* grad_bias, int flags,
-                                            void* stream_) {
+                                            int param_dtype, void* stream_) {
     SCB_REQUIRE(out_sums != nullptr, "bn_backward_reduce_fused: null out_sums");
     return bn_backward_cluster(dy, x, y, nullptr, nullptr, dtype, rows, channels, mean, invstd, weight, bias, n_total,
-                               out_sums, grad_weight, grad_bias, flags, 1, nullptr, 0, stream_);
+                               out_sums, grad_weight, grad_bias, flags, param_dtype, 1, nullptr, 0, stream_);
 }

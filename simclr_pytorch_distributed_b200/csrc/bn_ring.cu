@@ -68,6 +68,7 @@ struct RingArgs {
     int64_t rows_per_cta;
     int C, vpr, rpp, chunk_rows, n_stage;
     int ncol;                 // column tiles: a CTA owns vpr 16-byte vectors of every row (vpr * ncol = whole row)
+    int pdt;                  // dtype code of weight / bias / running statistics / parameter gradients (ldp / stp)
     int pdl;                  // apply passes: launched with programmatic stream serialisation, the ring is filled
                               // BEFORE griddepcontrol.wait (the caller vouches that the inputs were complete before
                               // the previous kernel of the stream started: SCB_BN_PDL)
@@ -113,10 +114,10 @@ __device__ __forceinline__ bool ring_last_cta(unsigned* counter, unsigned total,
 // (Normalization.cuh:458-502 restated on M2; same arithmetic as merged_stats of bn.cu).
 __device__ __forceinline__ void ring_merged_stats(const float* stats_all, int n_ranks, int C, int c,
                                                   const float* running_mean, const float* running_var, float eps,
-                                                  float& mean, float& invstd, float& m2, float& n) {
+                                                  float& mean, float& invstd, float& m2, float& n, int pdt) {
     if (stats_all == nullptr) {
-        mean = running_mean[c];
-        invstd = rsqrtf(running_var[c] + eps);
+        mean = ldp(running_mean, pdt, c, 0.f);
+        invstd = rsqrtf(ldp(running_var, pdt, c, 1.f) + eps);
         m2 = 0.f; n = 1.f;
         return;
     }
@@ -212,17 +213,16 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
             for (int j = t; j < CW; j += kRingConsumers) {
                 const int c = c_base + j;
                 float mean, invstd, m2, n;
-                ring_merged_stats(a.stats_all, a.n_ranks, C, c, a.running_mean, a.running_var, a.eps, mean, invstd, m2, n);
-                const float sc = (a.weight ? a.weight[c] : 1.f) * invstd;
+                ring_merged_stats(a.stats_all, a.n_ranks, C, c, a.running_mean, a.running_var, a.eps, mean, invstd, m2, n, a.pdt);
+                const float sc = ldp(a.weight, a.pdt, c, 1.f) * invstd;
                 table[j] = sc;
-                table[CW + j] = (a.bias ? a.bias[c] : 0.f) - mean * sc;
+                table[CW + j] = ldp(a.bias, a.pdt, c, 0.f) - mean * sc;
                 if (group == 0) {
                     if (a.save_mean) a.save_mean[c] = mean;
                     if (a.save_invstd) a.save_invstd[c] = invstd;
                     if (a.stats_all != nullptr) {
-                        if (a.running_mean) a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
-                        if (a.running_var)
-                            a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (m2 / (n - 1.f));
+                        if (a.running_mean) stp(a.running_mean, a.pdt, c, (1.f - a.momentum) * ldp(a.running_mean, a.pdt, c, 0.f) + a.momentum * mean);
+                        if (a.running_var) stp(a.running_var, a.pdt, c, (1.f - a.momentum) * ldp(a.running_var, a.pdt, c, 0.f) + a.momentum * (m2 / (n - 1.f)));
                     }
                     if (c == 0 && a.save_count) a.save_count[0] = n;
                     if (c == 0 && a.nbt && a.stats_all != nullptr) a.nbt[0] += 1;
@@ -250,8 +250,8 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
                     const int c = c0 + i;
                     const float is = a.invstd[c];
                     k0[i] = a.mean[c];
-                    if (kGate == 1 || kOp == kOpBwdApply) k1[i] = (a.weight ? a.weight[c] : 1.f) * is;
-                    if (kGate == 1) bb[i] = a.bias ? a.bias[c] : 0.f;
+                    if (kGate == 1 || kOp == kOpBwdApply) k1[i] = ldp(a.weight, a.pdt, c, 1.f) * is;
+                    if (kGate == 1) bb[i] = ldp(a.bias, a.pdt, c, 0.f);
                     if (kOp == kOpBwdApply) {
                         k2[i] = a.sums[c] * inv_n;
                         k3[i] = is * is * a.sums[C + c] * inv_n;
@@ -376,8 +376,8 @@ bn_ring_kernel(const __grid_constant__ RingArgs a) {
             } else {
                 a.out0[c] = u;
                 a.out0[C + c] = v;
-                if (a.grad_weight) a.grad_weight[c] = v * a.invstd[c];
-                if (a.grad_bias) a.grad_bias[c] = u;
+                if (a.grad_weight) stp(a.grad_weight, a.pdt, c, v * a.invstd[c]);
+                if (a.grad_bias) stp(a.grad_bias, a.pdt, c, u);
             }
         }
         if (threadIdx.x == 0) {
@@ -469,8 +469,8 @@ bn_resident_kernel(const __grid_constant__ RingArgs a) {
             for (int i = 0; i < VEC; ++i) {
                 const int c = c0 + i;
                 k0[i] = a.mean[c];
-                k1[i] = (a.weight ? a.weight[c] : 1.f) * a.invstd[c];
-                if (kGate == 1) bb[i] = a.bias ? a.bias[c] : 0.f;
+                k1[i] = ldp(a.weight, a.pdt, c, 1.f) * a.invstd[c];
+                if (kGate == 1) bb[i] = ldp(a.bias, a.pdt, c, 0.f);
             }
         }
     }
@@ -565,15 +565,14 @@ bn_resident_kernel(const __grid_constant__ RingArgs a) {
                 const float mean = to_f32(reinterpret_cast<const T*>(a.in[0])[c]) + u / n;
                 const float m2 = fmaxf(v - u * u / n, 0.f);
                 const float invstd = rsqrtf(m2 / n + a.eps);
-                const float sc = (a.weight ? a.weight[c] : 1.f) * invstd;
+                const float sc = ldp(a.weight, a.pdt, c, 1.f) * invstd;
                 table[c] = sc;
-                table[C + c] = (a.bias ? a.bias[c] : 0.f) - mean * sc;
+                table[C + c] = ldp(a.bias, a.pdt, c, 0.f) - mean * sc;
                 if (blockIdx.x == 0) {
                     if (a.save_mean) a.save_mean[c] = mean;
                     if (a.save_invstd) a.save_invstd[c] = invstd;
-                    if (a.running_mean) a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
-                    if (a.running_var)
-                        a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (m2 / (n - 1.f));
+                    if (a.running_mean) stp(a.running_mean, a.pdt, c, (1.f - a.momentum) * ldp(a.running_mean, a.pdt, c, 0.f) + a.momentum * mean);
+                    if (a.running_var) stp(a.running_var, a.pdt, c, (1.f - a.momentum) * ldp(a.running_var, a.pdt, c, 0.f) + a.momentum * (m2 / (n - 1.f)));
                     if (c == 0 && a.save_count) a.save_count[0] = n;
                     if (c == 0 && a.nbt) a.nbt[0] += 1;
                 }
@@ -583,8 +582,8 @@ bn_resident_kernel(const __grid_constant__ RingArgs a) {
                 table[C + c] = is * is * v / n;
                 if (blockIdx.x == 0) {
                     if (a.out0) { a.out0[c] = u; a.out0[C + c] = v; }
-                    if (a.grad_weight) a.grad_weight[c] = v * is;
-                    if (a.grad_bias) a.grad_bias[c] = u;
+                    if (a.grad_weight) stp(a.grad_weight, a.pdt, c, v * is);
+                    if (a.grad_bias) stp(a.grad_bias, a.pdt, c, u);
                 }
             }
         }
@@ -724,7 +723,7 @@ int ring_stats(const void* x, int dtype, int64_t M, int C, float* out_stats, voi
 int ring_apply(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* stats_all, int n_ranks,
                const float* weight, const float* bias, float* running_mean, float* running_var, float momentum,
                float eps, float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags,
-               cudaStream_t stream) {
+               int param_dtype, cudaStream_t stream) {
     const bool add = z != nullptr;
     if (!al16(x) || !al16(y) || (add && !al16(z))) return kRingUnsupported;
     RingArgs a = {};
@@ -735,6 +734,7 @@ int ring_apply(const void* x, const void* z, void* y, int dtype, int64_t M, int 
     a.stats_all = stats_all; a.n_ranks = n_ranks; a.weight = weight; a.bias = bias;
     a.running_mean = running_mean; a.running_var = running_var; a.momentum = momentum; a.eps = eps;
     a.save_mean = save_mean; a.save_invstd = save_invstd; a.save_count = save_count; a.nbt = nbt; a.flags = flags;
+    a.pdt = param_dtype;
     // the ring may fill before the statistics pass has fully retired only if that pass came before this launch in the
     // stream (training mode) and the caller vouches for the inputs; the residual operand is not covered by that
     a.pdl = ((flags & SCB_BN_PDL) && stats_all != nullptr && !add) ? 1 : 0;
@@ -747,7 +747,7 @@ int ring_apply(const void* x, const void* z, void* y, int dtype, int64_t M, int 
 
 int ring_backward_reduce(const void* dy, const void* x, const void* y, int dtype, int64_t M, int C, const float* mean,
                          const float* invstd, const float* weight, const float* bias, float* out_sums,
-                         float* grad_weight, float* grad_bias, int gate, void* ws, int64_t ws_bytes,
+                         float* grad_weight, float* grad_bias, int gate, int param_dtype, void* ws, int64_t ws_bytes,
                          cudaStream_t stream) {
     if (ws_bytes < ring_ws_bytes(C) || !al16(x) || !al16(dy) || (gate == 2 && !al16(y))) return kRingUnsupported;
     RingArgs a = {};
@@ -758,7 +758,7 @@ int ring_backward_reduce(const void* dy, const void* x, const void* y, int dtype
     a.mean = mean; a.invstd = invstd; a.weight = weight; a.bias = bias;
     a.acc = (float*)ws;
     a.counter = (unsigned*)((char*)ws + (size_t)kRingReplicas * 2 * C * 4);
-    a.out0 = out_sums; a.grad_weight = grad_weight; a.grad_bias = grad_bias;
+    a.out0 = out_sums; a.grad_weight = grad_weight; a.grad_bias = grad_bias; a.pdt = param_dtype;
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (gate == 2) return ring_launch(bn_ring_kernel<T, kOpBwdReduce, 2, false>, a, grid, smem, stream);
         if (gate == 1) return ring_launch(bn_ring_kernel<T, kOpBwdReduce, 1, false>, a, grid, smem, stream);
@@ -769,7 +769,8 @@ int ring_backward_reduce(const void* dy, const void* x, const void* y, int dtype
 
 int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
                         const float* mean, const float* invstd, const float* weight, const float* bias,
-                        const float* sums, const float* n_total, int gate, int flags, cudaStream_t stream) {
+                        const float* sums, const float* n_total, int gate, int flags, int param_dtype,
+                        cudaStream_t stream) {
     if (!al16(x) || !al16(dy) || !al16(dx) || (gate == 2 && !al16(y)) || (dz != nullptr && !al16(dz)))
         return kRingUnsupported;
     RingArgs a = {};
@@ -779,6 +780,7 @@ int ring_backward_apply(const void* dy, const void* x, const void* y, void* dx, 
     a.in[0] = x; a.in[1] = dy; a.in[2] = y; a.out[0] = dx; a.out[1] = dz;
     a.mean = mean; a.invstd = invstd; a.weight = weight; a.bias = bias; a.sums = sums; a.n_total = n_total;
     a.pdl = (flags & SCB_BN_PDL) ? 1 : 0;
+    a.pdt = param_dtype;
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (gate == 2) return ring_launch(bn_ring_kernel<T, kOpBwdApply, 2, false>, a, grid, smem, stream);
         if (gate == 1) return ring_launch(bn_ring_kernel<T, kOpBwdApply, 1, false>, a, grid, smem, stream);
@@ -858,9 +860,8 @@ static void resident_ws(RingArgs* a, void* ws, int C) {
 
 int ring_forward_resident(const void* x, const void* z, void* y, int dtype, int64_t M, int C, const float* weight,
                           const float* bias, float* running_mean, float* running_var, float momentum, float eps,
-                          float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags, void* ws,
-                          int64_t ws_bytes,
-                          cudaStream_t stream) {
+                          float* save_mean, float* save_invstd, float* save_count, long long* nbt, int flags,
+                          int param_dtype, void* ws, int64_t ws_bytes, cudaStream_t stream) {
     const bool add = (flags & SCB_BN_ADD) != 0;
     if (ws == nullptr || ws_bytes < ring_ws_bytes(C) || !al16(x) || !al16(y) || (add && !al16(z))) return kRingUnsupported;
     RingArgs a = {};
@@ -870,6 +871,7 @@ int ring_forward_resident(const void* x, const void* z, void* y, int dtype, int6
     a.weight = weight; a.bias = bias; a.running_mean = running_mean; a.running_var = running_var;
     a.momentum = momentum; a.eps = eps; a.save_mean = save_mean; a.save_invstd = save_invstd; a.save_count = save_count;
     a.nbt = nbt;
+    a.pdt = param_dtype;
     a.flags = flags;
     resident_ws(&a, ws, C);
     SCB_DISPATCH_FLOAT(dtype, T, {
@@ -881,8 +883,8 @@ int ring_forward_resident(const void* x, const void* z, void* y, int dtype, int6
 
 int ring_backward_resident(const void* dy, const void* x, const void* y, void* dx, void* dz, int dtype, int64_t M, int C,
                            const float* mean, const float* invstd, const float* weight, const float* bias,
-                           const float* n_total, float* out_sums, float* grad_weight, float* grad_bias, int gate, void* ws,
-                           int64_t ws_bytes, cudaStream_t stream) {
+                           const float* n_total, float* out_sums, float* grad_weight, float* grad_bias, int gate,
+                           int param_dtype, void* ws, int64_t ws_bytes, cudaStream_t stream) {
     if (ws == nullptr || ws_bytes < ring_ws_bytes(C) || !al16(x) || !al16(dy) || !al16(dx) || (gate == 2 && !al16(y)) ||
         (dz != nullptr && !al16(dz)))
         return kRingUnsupported;
@@ -891,7 +893,7 @@ int ring_backward_resident(const void* dy, const void* x, const void* y, void* d
     if (!resident_geom(M, C, dtype == SCB_F32 ? 4 : 2, gate == 2 ? 3 : 2, &a, &grid, &smem)) return kRingUnsupported;
     a.in[0] = x; a.in[1] = dy; a.in[2] = y; a.out[0] = dx; a.out[1] = dz;
     a.mean = mean; a.invstd = invstd; a.weight = weight; a.bias = bias; a.n_total = n_total;
-    a.out0 = out_sums; a.grad_weight = grad_weight; a.grad_bias = grad_bias;
+    a.out0 = out_sums; a.grad_weight = grad_weight; a.grad_bias = grad_bias; a.pdt = param_dtype;
     resident_ws(&a, ws, C);
     SCB_DISPATCH_FLOAT(dtype, T, {
         if (gate == 2) return resident_launch(bn_resident_kernel<T, true, 2, false>, a, grid, smem, stream);

@@ -149,6 +149,21 @@ __device__ __forceinline__ void store_row_vec(T* p, const float (&v)[VEC]) {
     }
 }
 
+// Per-channel parameters (weight, bias, running statistics, their gradients) in the module's own dtype: the pointers
+// are declared float* for the common fp32 case and read / written through these with the run-time dtype code, so a
+// bf16 model needs no conversion kernels around the batch-norm passes.  A null pointer reads as `dflt`.
+__device__ __forceinline__ float ldp(const float* p, int dt, int i, float dflt) {
+    if (p == nullptr) return dflt;
+    if (dt == SCB_F32) return p[i];
+    if (dt == SCB_BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
+    return __half2float(reinterpret_cast<const __half*>(p)[i]);
+}
+__device__ __forceinline__ void stp(float* p, int dt, int i, float v) {
+    if (dt == SCB_F32) p[i] = v;
+    else if (dt == SCB_BF16) reinterpret_cast<__nv_bfloat16*>(p)[i] = __float2bfloat16_rn(v);
+    else reinterpret_cast<__half*>(p)[i] = __float2half_rn(v);
+}
+
 // a device scalar whose element type is only known at run time (SCB_F32 / SCB_BF16 / SCB_F16)
 __device__ __forceinline__ float load_scalar(const void* p, int dtype) {
     if (dtype == SCB_BF16) return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(p));

@@ -64,6 +64,22 @@ class _Kernels:
             cls._fused_cache[key] = hit
         return hit
 
+    @staticmethod
+    def param_dtype(*tensors):
+        """dtype code of the per-channel parameter tensors of a call (weight, bias, running statistics, parameter
+        gradients): they must agree; fp32 when there are none."""
+        code = None
+        for t in tensors:
+            if t is None:
+                continue
+            c = _lib.dtype_code(t.dtype)
+            if code is None:
+                code = c
+            elif c != code:
+                raise ValueError('SyncBatchNorm kernels need weight, bias, running statistics and their gradients in one '
+                                 'dtype (got %s)' % sorted({str(u.dtype) for u in tensors if u is not None}))
+        return _lib.F32 if code is None else code
+
     @classmethod
     def stats(cls, x, geom, out_stats):
         lib = _lib.load()
@@ -86,12 +102,13 @@ class _Kernels:
         lib = _lib.load()
         cl, outer, C, inner = geom
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
-        sm = saved[0:C] if saved is not None else None
-        si = saved[C:2 * C] if saved is not None else None
-        sc = saved[2 * C:] if saved is not None else None
+        # saved = [mean (C) | invstd (C) | count]: plain pointer arithmetic (a slice is a new tensor object, ~2 us)
+        s0 = saved.data_ptr() if saved is not None else None
+        sm, si, sc = (s0, s0 + 4 * C, s0 + 8 * C) if s0 is not None else (None, None, None)
         _lib.check(lib.scb_bn_apply(x.data_ptr(), p(z), y.data_ptr(), _lib.dtype_code(x.dtype), cl, outer, C,
                                     inner, p(stats_all), n_ranks, p(weight), p(bias), p(running_mean),
-                                    p(running_var), momentum, eps, p(sm), p(si), p(sc), p(nbt), flags,
+                                    p(running_var), momentum, eps, sm, si, sc, p(nbt), flags,
+                                    cls.param_dtype(weight, bias, running_mean, running_var),
                                     cls.stream(x.device)), 'scb_bn_apply')
 
     @classmethod
@@ -103,8 +120,9 @@ class _Kernels:
                 (yout is None or yout.data_ptr() % 16 == 0)):
             rc = lib.scb_bn_backward_reduce_fused(
                 dy.data_ptr(), x.data_ptr(), p(yout), _lib.dtype_code(x.dtype), outer * inner, C,
-                saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), saved[2 * C:].data_ptr(),
-                sums.data_ptr(), p(grad_weight), p(grad_bias), flags, cls.stream(x.device))
+                saved.data_ptr(), saved.data_ptr() + 4 * C, p(weight), p(bias), saved.data_ptr() + 8 * C,
+                sums.data_ptr(), p(grad_weight), p(grad_bias), flags,
+                cls.param_dtype(weight, bias, grad_weight, grad_bias), cls.stream(x.device))
             if rc == 0:
                 return
             if rc != -3:
@@ -112,9 +130,9 @@ class _Kernels:
         ws = cls.workspace(lib, x.device, C)
         _lib.check(lib.scb_bn_backward_reduce(
             dy.data_ptr(), x.data_ptr(), p(yout), _lib.dtype_code(x.dtype), cl, outer, C, inner,
-            saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), sums.data_ptr(),
-            p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(), cls.stream(x.device)),
-            'scb_bn_backward_reduce')
+            saved.data_ptr(), saved.data_ptr() + 4 * C, p(weight), p(bias), sums.data_ptr(),
+            p(grad_weight), p(grad_bias), flags, cls.param_dtype(weight, bias, grad_weight, grad_bias),
+            ws.data_ptr(), ws.numel(), cls.stream(x.device)), 'scb_bn_backward_reduce')
 
     @classmethod
     def forward_fused(cls, x, y, geom, weight, bias, running_mean, running_var, momentum, eps, saved, flags, z=None,
@@ -125,8 +143,9 @@ class _Kernels:
         ws = cls.workspace(lib, x.device, C)
         return lib.scb_bn_forward_fused(x.data_ptr(), p(z), y.data_ptr(), _lib.dtype_code(x.dtype), outer * inner, C,
                                         p(weight), p(bias), p(running_mean), p(running_var), momentum, eps,
-                                        saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), saved[2 * C:].data_ptr(),
-                                        p(nbt), flags, ws.data_ptr(), ws.numel(), cls.stream(x.device))
+                                        saved.data_ptr(), saved.data_ptr() + 4 * C, saved.data_ptr() + 8 * C,
+                                        p(nbt), flags, cls.param_dtype(weight, bias, running_mean, running_var),
+                                        ws.data_ptr(), ws.numel(), cls.stream(x.device))
 
     @classmethod
     def backward_fused(cls, dy, x, dx, geom, saved, weight, bias, sums, grad_weight, grad_bias, flags,
@@ -136,10 +155,11 @@ class _Kernels:
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
         ws = cls.workspace(lib, x.device, C)
         return lib.scb_bn_backward_fused(dy.data_ptr(), x.data_ptr(), p(yout), dx.data_ptr(), p(dz),
-                                         _lib.dtype_code(x.dtype), outer * inner, C, saved[0:C].data_ptr(),
-                                         saved[C:2 * C].data_ptr(), p(weight), p(bias), saved[2 * C:].data_ptr(),
-                                         sums.data_ptr(), p(grad_weight), p(grad_bias), flags, ws.data_ptr(), ws.numel(),
-                                         cls.stream(x.device))
+                                         _lib.dtype_code(x.dtype), outer * inner, C, saved.data_ptr(),
+                                         saved.data_ptr() + 4 * C, p(weight), p(bias), saved.data_ptr() + 8 * C,
+                                         sums.data_ptr(), p(grad_weight), p(grad_bias), flags,
+                                         cls.param_dtype(weight, bias, grad_weight, grad_bias), ws.data_ptr(),
+                                         ws.numel(), cls.stream(x.device))
 
     @classmethod
     def backward_apply(cls, dy, x, dx, geom, saved, weight, bias, sums, flags, yout=None, dz=None):
@@ -148,8 +168,9 @@ class _Kernels:
         p = lambda t: t.data_ptr() if t is not None else None   # noqa: E731
         _lib.check(lib.scb_bn_backward_apply(
             dy.data_ptr(), x.data_ptr(), p(yout), dx.data_ptr(), p(dz), _lib.dtype_code(x.dtype), cl, outer, C, inner,
-            saved[0:C].data_ptr(), saved[C:2 * C].data_ptr(), p(weight), p(bias), sums.data_ptr(),
-            saved[2 * C:].data_ptr(), flags, cls.stream(x.device)), 'scb_bn_backward_apply')
+            saved.data_ptr(), saved.data_ptr() + 4 * C, p(weight), p(bias), sums.data_ptr(),
+            saved.data_ptr() + 8 * C, flags, cls.param_dtype(weight, bias), cls.stream(x.device)),
+            'scb_bn_backward_apply')
 
 
 def _is_channels_last(x):
@@ -294,8 +315,17 @@ class _SyncBNFunction(torch.autograd.Function):
         size = int(x.numel() // C)
         if use_batch_stats and size == 1 and world_size < 2:
             raise ValueError(f"Expected more than 1 value per channel when training, got input size {size}")
-        w32, b32 = _f32(weight), _f32(bias)
-        rm, rv = _f32(running_mean), _f32(running_var)
+        # The kernels take weight, bias and the running statistics in the module's own dtype (fp32, bf16 or fp16) as long
+        # as they agree: a model converted with .to(torch.bfloat16) then needs no conversion kernels around the passes.
+        # Mixed dtypes (rare) go through fp32 copies.  The oracle-backed stand-in of the CPU tests is fp32-only.
+        ptensors = [t for t in (weight, bias, running_mean, running_var) if t is not None]
+        native = (kern is _Kernels and len({t.dtype for t in ptensors}) <= 1 and
+                  all(t.dtype in (torch.float32, torch.bfloat16, torch.float16) and t.is_contiguous() for t in ptensors))
+        if native:
+            w32, b32, rm, rv = weight, bias, running_mean, running_var
+        else:
+            w32, b32 = _f32(weight), _f32(bias)
+            rm, rv = _f32(running_mean), _f32(running_var)
         dev = x.device
         flags = (_lib.BN_RELU if fuse_relu else 0) | (_lib.BN_ADD if z is not None else 0)
         if z is not None:
@@ -353,8 +383,10 @@ class _SyncBNFunction(torch.autograd.Function):
         if dy.dtype != x.dtype:
             dy = dy.to(x.dtype)
         dev = x.device
-        out = torch.empty(4 * C, dtype=torch.float32, device=dev)           # sums(2C), dgamma, dbeta
-        sums, gw, gb = out[0:2 * C], out[2 * C:3 * C], out[3 * C:]
+        sums = torch.empty(2 * C, dtype=torch.float32, device=dev)          # sum dy, sum dy (x - mean)
+        pdt = w32.dtype if w32 is not None else (b32.dtype if b32 is not None else torch.float32)
+        gwb = torch.empty(2 * C, dtype=pdt, device=dev)                      # dgamma, dbeta in the parameters' dtype
+        gw, gb = gwb[0:C], gwb[C:]
         need_dx = ctx.needs_input_grad[0]
         need_dz = ctx.has_z and ctx.needs_input_grad[1]
         gated = yout is not None                                             # ReLU after the residual add

@@ -424,3 +424,37 @@ def test_step_counter_is_kept_by_the_kernels(shape, cl, dtype):
     bn.train()
     bn(x, torch.zeros_like(x))                      # the residual-add variants count too
     assert int(bn.num_batches_tracked) == 4
+
+
+@pytest.mark.parametrize('shape,cl', [((256, 256, 8, 8), True), ((512, 256, 8, 8), True), ((512, 128, 16, 16), True),
+                                      ((8, 12, 5, 5), True), ((16, 64, 16, 16), False)])
+@pytest.mark.parametrize('pdtype', [torch.bfloat16, torch.float16])
+def test_low_precision_parameters_are_taken_natively(shape, cl, pdtype):
+    """A module converted with .to(bf16 / fp16) -- weight, bias and running statistics in that dtype, as
+    `model.to(torch.bfloat16)` leaves them -- against the same module with fp32 copies of the same parameter values:
+    same y and dx, running statistics and parameter gradients equal up to the rounding of their own dtype, and no
+    change of dtype anywhere (torch's batch norm takes mixed dtypes the same way)."""
+    torch.manual_seed(11)
+    C = shape[1]
+    x = (torch.randn(shape, device=DEV) * 1.3 + 0.2).to(torch.bfloat16)
+    dy = torch.randn(shape, device=DEV).to(torch.bfloat16)
+    if cl:
+        x = x.contiguous(memory_format=torch.channels_last)
+        dy = dy.contiguous(memory_format=torch.channels_last)
+    low = make_bn(C).to(pdtype)
+    ref = make_bn(C)
+    ref.load_state_dict({k: v.float() if v.is_floating_point() else v for k, v in low.state_dict().items()})
+    outs = []
+    for bn in (low, ref):
+        xd = x.clone().requires_grad_(True)
+        y = bn(xd)
+        y.backward(dy)
+        outs.append((y.detach().float(), xd.grad.float(), bn.weight.grad, bn.bias.grad, bn.running_mean, bn.running_var))
+    assert low.weight.dtype == pdtype and low.running_mean.dtype == pdtype
+    assert outs[0][2].dtype == pdtype and outs[0][3].dtype == pdtype
+    ulp = 2.0 ** -7 if pdtype == torch.bfloat16 else 2.0 ** -10
+    assert float((outs[0][0] - outs[1][0]).abs().max()) <= 2.0 ** -7 * float(outs[1][0].abs().max())
+    assert float((outs[0][1] - outs[1][1]).abs().max()) <= 2.0 ** -7 * float(outs[1][1].abs().max()) + 1e-4
+    for a, b in zip(outs[0][2:], outs[1][2:]):
+        assert torch.all((a.float() - b.float()).abs() <= ulp * b.float().abs() + 1e-3 * float(b.float().abs().max()) + 1e-6)
+    assert int(low.num_batches_tracked) == 1
