@@ -732,17 +732,19 @@ def run_model(args, world, rank):
                 tot += t
                 if 'bn_' in ev.key or 'batch_norm' in ev.key:
                     bn += t
-            return bn / tot if tot > 0 else None
+            return (bn / tot if tot > 0 else None), tot / 2 / 1e3        # share, GPU-busy ms per step (sum of kernel times)
         except Exception as e:      # say so
-            return 'profiler unavailable: %s' % type(e).__name__
+            return 'profiler unavailable: %s' % type(e).__name__, None
 
     res = {}
     for arm in ('stock', 'ours_swap', 'ours_fused'):
         step = make(arm)
         ms, _ = time_steps(step, min(args.steps, 20), max(3, min(args.warmup, 5)), world)
         per = ms / min(args.steps, 20)
+        share, busy = bn_share(step)
         res[arm] = {'ms_per_step': per, 'images_per_s': 2 * bsz * world / (per * 1e-3),
-                    'batch_norm_share_of_gpu_time': bn_share(step), 'loss_after': float(step(0))}
+                    'batch_norm_share_of_gpu_time': share, 'gpu_busy_ms_per_step': busy,
+                    'loss_after': float(step(0).detach())}
         del step
         torch.cuda.empty_cache()
     if rank == 0:
