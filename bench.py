@@ -194,13 +194,13 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
         fwd = lambda f: crit(f)                                                     # noqa: E731
         # end to end: the module's graph mode (one CUDA-graph launch per step instead of four C-ABI calls + autograd)
         crit_g = SupConLoss(temperature=TEMP, engine=engine, graph=True)
-        fwd_e2e = lambda f: crit_g(f)                                               # noqa: E731
+        fwd_e2e = crit_g
     else:
         from simclr_pytorch_distributed_b200.gather import DistributedSupConLoss
         crit = DistributedSupConLoss(temperature=TEMP, engine=engine, normalize=False)
         fwd = lambda f: crit(f)                                                     # noqa: E731
         crit_g = DistributedSupConLoss(temperature=TEMP, engine=engine, normalize=False, graph=True)
-        fwd_e2e = lambda f: crit_g(f)                                               # noqa: E731
+        fwd_e2e = crit_g
 
     ones = torch.ones((), dtype=dtype, device='cuda')       # upstream gradient of the scalar loss, allocated once
 
@@ -212,38 +212,76 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
     # End to end: every step copies ITS embeddings from pinned host memory and the host reads the loss.  The
     # copy of step i+1 is issued on a side stream before step i computes (what a training loop's prefetcher
     # does), so it overlaps the kernels; the gradient stays on the device, where the encoder's backward
-    # consumes it (reading the 2 MiB gradient back every step would only measure PCIe).
+    # consumes it (reading the 2 MiB gradient back every step would only measure PCIe).  The loss is copied to
+    # the host as soon as the forward has been issued and the step ends when that copy has landed AND the
+    # backward has been issued (tools/prof_host_loss.py: where the host time of this step goes).
     loss_host = torch.empty((), dtype=dtype).pin_memory()     # the loss has the features' dtype (losses.py:91)
     copy_stream = torch.cuda.Stream()
     slots = [torch.empty(b_local, N_VIEWS, DIM, dtype=dtype, device='cuda') for _ in range(2)]
+    leaves = [s.detach().requires_grad_(True) for s in slots]
     ready = [torch.cuda.Event() for _ in range(2)]          # H2D of the slot has landed
     freed = [torch.cuda.Event() for _ in range(2)]          # the step that used the slot is done with it
+    loss_read = torch.cuda.Event()                          # the loss of the step is on the host
     state = {'primed': -1}
+    for e in freed + ready + [loss_read]:
+        e.record()
+    nbytes = b_local * N_VIEWS * DIM * host[0].element_size()
+    # The copies and event calls of the prefetcher go through cudart directly where cuda-python is importable:
+    # torch's stream context manager + copy_ cost ~20 us of host time per step, these ~4 us.
+    try:
+        if os.environ.get('SIMCLR_B200_BENCH_TORCH_COPIES') == '1':
+            raise ImportError
+        from cuda.bindings import runtime as rt
+        h2d, d2h_kind = rt.cudaMemcpyKind.cudaMemcpyHostToDevice, rt.cudaMemcpyKind.cudaMemcpyDeviceToHost
+        cs = copy_stream.cuda_stream
+        ready_h, freed_h = [e.cuda_event for e in ready], [e.cuda_event for e in freed]
+        host_ptr, slot_ptr, loss_host_ptr = [h.data_ptr() for h in host], [t.data_ptr() for t in slots], loss_host.data_ptr()
+    except ImportError:
+        rt = None
 
     def prefetch(j):
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(freed[j % 2])
-            slots[j % 2].copy_(host[j % pool], non_blocking=True)
-            ready[j % 2].record(copy_stream)
+        s = j % 2
+        if rt is not None:
+            rt.cudaStreamWaitEvent(cs, freed_h[s], 0)
+            err, = rt.cudaMemcpyAsync(slot_ptr[s], host_ptr[j % pool], nbytes, h2d, cs)
+            rt.cudaEventRecord(ready_h[s], cs)
+            if int(err) != 0:
+                raise RuntimeError('cudaMemcpyAsync (prefetch): %s' % err)
+        else:
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(freed[s])
+                slots[s].copy_(host[j % pool], non_blocking=True)
+                ready[s].record(copy_stream)
         state['primed'] = j
 
-    for e in freed:
-        e.record()
+    cur = torch.cuda.current_stream()                         # the bench never changes its stream
+    cur_h, loss_bytes = cur.cuda_stream, loss_host.element_size()
 
     def step_e2e(i):
         if state['primed'] != i:
             prefetch(i)                                       # first step of a run: nothing was prefetched
-        cur = torch.cuda.current_stream()
-        cur.wait_event(ready[i % 2])
-        f = slots[i % 2].detach().requires_grad_(True)
-        loss = fwd_e2e(f)
+        s = i % 2
+        f = leaves[s]
+        f.grad = None
+        if rt is not None:
+            rt.cudaStreamWaitEvent(cur_h, ready_h[s], 0)
+            loss = fwd_e2e(f)
+            err, = rt.cudaMemcpyAsync(loss_host_ptr, loss.data_ptr(), loss_bytes, d2h_kind, cur_h)
+            if int(err) != 0:
+                raise RuntimeError('cudaMemcpyAsync (loss): %s' % err)
+        else:
+            cur.wait_event(ready[s])
+            loss = fwd_e2e(f)
+            loss_host.copy_(loss.detach(), non_blocking=True)
+        loss_read.record(cur)
         prefetch(i + 1)                                       # issued while the GPU works on step i
         loss.backward()
-        freed[i % 2].record(cur)
-        loss_host.copy_(loss.detach(), non_blocking=True)
-        cur.synchronize()                                     # the caller reads the loss every step
+        if rt is not None:
+            rt.cudaEventRecord(freed_h[s], cur_h)
+        else:
+            freed[s].record(cur)
+        loss_read.synchronize()                               # the caller reads the loss every step
 
-    nbytes = b_local * N_VIEWS * DIM * host[0].element_size()
     return step_resident, step_e2e, nbytes, loss_host.element_size(), b_local
 
 

@@ -304,7 +304,7 @@ class DistributedSupConLoss(nn.Module):
         # and replayed; the input is always copied into a buffer the module owns, so that "capture or replay" depends
         # on the shape alone and every rank decides alike.  SimCLR mode only (labels take the eager path).
         self.graph = graph
-        self._graph_cache = None
+        self._graph_cache, self._graph_cache_settings, self._graph_hot = None, None, None
         self.temperature = temperature
         self.contrast_mode = contrast_mode
         self.base_temperature = base_temperature
@@ -312,7 +312,16 @@ class DistributedSupConLoss(nn.Module):
         self.normalize = normalize
         self.process_group = process_group
 
+    def _graph_settings(self):
+        return (self.temperature, self.contrast_mode, self.base_temperature, self.engine, self.normalize,
+                self.process_group)
+
     def forward(self, features, labels=None):
+        hot = self._graph_hot
+        if (hot is not None and labels is None and self.graph and features.shape == hot[0] and
+                features.stride() == hot[1] and features.dtype is hot[2] and self._graph_settings() == hot[3] and
+                features.requires_grad and torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
+            return L._GraphedSupCon.apply(features, hot[4])       # same shape as the last graphed call: replay
         labels, mode = L.validate_inputs(features, labels, None, self.contrast_mode)
         if OPS.requires_cuda and not features.is_cuda:
             raise RuntimeError('DistributedSupConLoss runs on CUDA tensors only (there is no CPU fallback); '
@@ -330,12 +339,16 @@ class DistributedSupConLoss(nn.Module):
         dev = features.device
         if (self.graph and labels is None and OPS.requires_cuda and features.requires_grad and torch.is_grad_enabled()
                 and not torch.cuda.is_current_stream_capturing()):
-            if self._graph_cache is None:
+            settings = self._graph_settings()
+            if self._graph_cache is None or self._graph_cache_settings != settings:   # baked into the captured graphs
                 self._graph_cache = L.GraphCache(
                     lambda: DistributedSupConLoss(self.temperature, self.contrast_mode, self.base_temperature,
                                                   self.engine, self.normalize, self.process_group),
                     bind_addresses=False)
-            return self._graph_cache.run(features, None)
+                self._graph_cache_settings = settings
+            out = self._graph_cache.run(features, None)
+            self._graph_hot = (features.shape, features.stride(), features.dtype, settings, self._graph_cache.last_entry)
+            return out
         labels_all = None
         mask_kind = _lib.MASK_SIMCLR
         if labels is not None:

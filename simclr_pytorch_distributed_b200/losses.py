@@ -359,7 +359,7 @@ class SupConLoss(nn.Module):
         # As with torch.cuda.make_graphed_callables the returned loss is the graph's own output buffer: read it
         # (.item(), a copy) before the next call with the same shape overwrites it.
         self.graph = graph
-        self._graph_cache = None
+        self._graph_cache, self._graph_cache_settings, self._graph_hot = None, None, {}
         self.temperature = temperature
         self.contrast_mode = contrast_mode
         self.base_temperature = base_temperature
@@ -379,20 +379,29 @@ class SupConLoss(nn.Module):
         main_supcon.py:298-317 in `self.norm_terms` (a device tensor, no synchronisation), keeps the moving average in
         `self.record_norm_mean`, and adds `sec_weight * loss_sec + l2reg_weight * loss_l2reg` to the loss (the
         reference's `opt.sec_wei * now_iter / total` and `opt.l2reg_wei * ...` factors, both 0 by default)."""
+        if self.graph and labels is None and mask is None:
+            # graph mode, recurring input buffer: one dictionary probe, then the replay (everything below ran when the
+            # graph for this buffer was captured; the probe compares all it depends on)
+            hot = self._graph_hot.get(features.data_ptr())
+            if (hot is not None and features.shape == hot[0] and features.stride() == hot[1] and
+                    features.dtype is hot[2] and self._graph_settings() == hot[3] and features.requires_grad and
+                    torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
+                return _GraphedSupCon.apply(features, hot[4])
         labels, mode = validate_inputs(features, labels, mask, self.contrast_mode)
         if not features.is_cuda:
             raise RuntimeError('simclr_pytorch_distributed_b200.SupConLoss runs on CUDA tensors only '
                                '(there is no CPU fallback); got a %s tensor' % features.device.type)
         if len(features.shape) > 3:
             features = features.view(features.shape[0], features.shape[1], -1)     # losses.py:36-37
+        own_buffer = True
         if features.stride(2) != 1 and features.shape[2] > 1:
-            features = features.contiguous()
+            features, own_buffer = features.contiguous(), False
         B, V, D = features.shape
         dev = features.device
         if (self.graph and mask is None and not self.track_norms and features.requires_grad and
                 torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
             # graph mode: nothing below is needed per call (the captured step was planned once)
-            return self._graphed(features, label_ids(labels, dev) if labels is not None else None)
+            return self._graphed(features, label_ids(labels, dev) if labels is not None else None, own_buffer)
         if labels is not None:
             mask_kind = _lib.MASK_LABELS
             labels = label_ids(labels, dev)
@@ -421,11 +430,22 @@ class SupConLoss(nn.Module):
                                      float(self.base_temperature), bool(self.normalize), norms)
 
     # ------------------------------------------------------------------ graph mode
-    def _graphed(self, features, labels):
-        if self._graph_cache is None:
+    def _graph_settings(self):
+        """What a captured graph has baked in besides the input's shape: changing any of it drops the graphs."""
+        return (self.temperature, self.contrast_mode, self.base_temperature, self.engine, self.normalize, self.track_norms)
+
+    def _graphed(self, features, labels, bind=True):
+        settings = self._graph_settings()
+        if self._graph_cache is None or self._graph_cache_settings != settings:
             self._graph_cache = GraphCache(lambda: SupConLoss(self.temperature, self.contrast_mode, self.base_temperature,
                                                               self.engine, self.normalize))
-        return self._graph_cache.run(features, labels)
+            self._graph_cache_settings = settings
+            self._graph_hot = {}
+        out = self._graph_cache.run(features, labels, bind)
+        entry = self._graph_cache.last_entry
+        if labels is None and not entry.own_input:          # bound to this buffer: later calls take the probe in forward
+            self._graph_hot[features.data_ptr()] = (features.shape, features.stride(), features.dtype, settings, entry)
+        return out
 
 
 class GraphCache:
@@ -441,16 +461,19 @@ class GraphCache:
         self.make_inner = make_inner
         self.bind_addresses = bind_addresses
         self.graphs = {}
+        self.last_entry = None      # the entry the last run() used
 
-    def run(self, features, labels):
+    def run(self, features, labels, bind=True):
+        """`bind=False`: this input is a temporary of the caller (its address will not recur): use the owned buffer."""
         dev = features.device
         base = (tuple(features.shape), features.dtype, dev.index, tuple(features.stride()), labels is not None)
         per_shape = self.graphs.setdefault(base, {})
         addr = features.data_ptr()
-        entry = per_shape.get(addr) if self.bind_addresses else None
+        bind = bind and self.bind_addresses
+        entry = per_shape.get(addr) if bind else None
         if entry is None:
             bound = [k for k in per_shape if k != 'own']
-            if self.bind_addresses and len(bound) < self.MAX_ADDRESSES and features.is_contiguous():
+            if bind and len(bound) < self.MAX_ADDRESSES and features.is_contiguous():
                 entry = self._capture(features, labels, own_input=False)
                 per_shape[addr] = entry
             else:
@@ -459,6 +482,7 @@ class GraphCache:
                     entry = per_shape['own'] = self._capture(features, labels, own_input=True)
         if labels is not None:
             entry.labels.copy_(labels)
+        self.last_entry = entry
         return _GraphedSupCon.apply(features, entry)
 
     def _capture(self, features, labels, own_input):

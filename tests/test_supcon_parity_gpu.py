@@ -202,3 +202,14 @@ def test_graph_mode_matches_eager():
         l1 = graphed(b1)
         graphed(bufs[0].detach().requires_grad_(True))
         l1.backward()
+    # the module's settings are baked into its graphs: changing one re-captures
+    for crit in (eager, graphed):
+        crit.temperature, crit.contrast_mode = 0.2, 'one'
+    for step in range(3):
+        a = bufs[step % 2].detach().clone().requires_grad_(True)
+        b = bufs[step % 2].detach().requires_grad_(True)
+        la, lb = eager(a), graphed(b)
+        la.backward()
+        lb.backward()
+        assert float(la) == float(lb)
+        assert torch.equal(a.grad, b.grad)
