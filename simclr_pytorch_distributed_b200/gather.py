@@ -321,7 +321,8 @@ class DistributedSupConLoss(nn.Module):
         if (hot is not None and labels is None and self.graph and features.shape == hot[0] and
                 features.stride() == hot[1] and features.dtype is hot[2] and self._graph_settings() == hot[3] and
                 features.requires_grad and torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
-            return L._GraphedSupCon.apply(features, hot[4])       # same shape as the last graphed call: replay
+            hot[4].launch(features)        # same shape as the last graphed call: replay; the GPU starts before
+            return L._GraphedSupCon.apply(features, hot[4], True)      # autograd's bookkeeping for the call
         labels, mode = L.validate_inputs(features, labels, None, self.contrast_mode)
         if OPS.requires_cuda and not features.is_cuda:
             raise RuntimeError('DistributedSupConLoss runs on CUDA tensors only (there is no CPU fallback); '

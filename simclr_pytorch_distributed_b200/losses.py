@@ -297,6 +297,13 @@ class _GraphEntry:
     """One captured forward+backward of the loss for a fixed (shape, dtype, options, input address)."""
     __slots__ = ('graph', 'x', 'labels', 'ones', 'loss', 'grad', 'serial', 'own_input')
 
+    def launch(self, feats):
+        """Issues the captured step for `feats` (copied into the owned buffer unless the graph is bound to its address)."""
+        if self.own_input:
+            self.x.copy_(feats.detach())
+        self.graph.replay()
+        self.serial += 1
+
 
 class _GraphedSupCon(torch.autograd.Function):
     """Replays a CUDA graph that holds the forward AND the backward kernels of one loss call (upstream gradient 1);
@@ -304,11 +311,9 @@ class _GraphedSupCon(torch.autograd.Function):
     plus autograd bookkeeping to one graph launch."""
 
     @staticmethod
-    def forward(ctx, feats, entry):
-        if entry.own_input:
-            entry.x.copy_(feats)
-        entry.graph.replay()
-        entry.serial += 1
+    def forward(ctx, feats, entry, launched=False):
+        if not launched:
+            entry.launch(feats)
         ctx.entry, ctx.serial = entry, entry.serial
         # the graph's own output buffer (as torch.cuda.make_graphed_callables does): no copy kernel; the next call of
         # the same shape overwrites it
@@ -321,7 +326,7 @@ class _GraphedSupCon(torch.autograd.Function):
             raise RuntimeError('SupConLoss(graph=True): backward of a forward that was followed by another forward of '
                                'the same shape (the captured gradient buffer was overwritten); call backward first '
                                'or use graph=False')
-        return e.grad * grad_out.to(e.grad.dtype), None
+        return e.grad * grad_out.to(e.grad.dtype), None, None
 
 
 def validate_inputs(features, labels, mask, contrast_mode):
@@ -386,7 +391,8 @@ class SupConLoss(nn.Module):
             if (hot is not None and features.shape == hot[0] and features.stride() == hot[1] and
                     features.dtype is hot[2] and self._graph_settings() == hot[3] and features.requires_grad and
                     torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
-                return _GraphedSupCon.apply(features, hot[4])
+                hot[4].launch(features)         # the GPU starts now; autograd's bookkeeping for the call runs beside it
+                return _GraphedSupCon.apply(features, hot[4], True)
         labels, mode = validate_inputs(features, labels, mask, self.contrast_mode)
         if not features.is_cuda:
             raise RuntimeError('simclr_pytorch_distributed_b200.SupConLoss runs on CUDA tensors only '
