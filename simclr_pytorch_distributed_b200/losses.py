@@ -384,7 +384,7 @@ class SupConLoss(nn.Module):
         main_supcon.py:298-317 in `self.norm_terms` (a device tensor, no synchronisation), keeps the moving average in
         `self.record_norm_mean`, and adds `sec_weight * loss_sec + l2reg_weight * loss_l2reg` to the loss (the
         reference's `opt.sec_wei * now_iter / total` and `opt.l2reg_wei * ...` factors, both 0 by default)."""
-        if self.graph and labels is None and mask is None:
+        if self.graph and labels is None and mask is None and sec_weight == 0.0 and l2reg_weight == 0.0:
             # graph mode, recurring input buffer: one dictionary probe, then the replay (everything below ran when the
             # graph for this buffer was captured; the probe compares all it depends on)
             hot = self._graph_hot.get(features.data_ptr())
@@ -404,6 +404,8 @@ class SupConLoss(nn.Module):
             features, own_buffer = features.contiguous(), False
         B, V, D = features.shape
         dev = features.device
+        if not self.track_norms and (sec_weight != 0.0 or l2reg_weight != 0.0):
+            raise ValueError('sec_weight / l2reg_weight need track_norms=True')
         if (self.graph and mask is None and not self.track_norms and features.requires_grad and
                 torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing()):
             # graph mode: nothing below is needed per call (the captured step was planned once)
@@ -430,8 +432,6 @@ class SupConLoss(nn.Module):
             self.norm_terms = torch.empty(5, dtype=torch.float32, device=dev)
             norms = (self.record_norm_mean, float(self.norm_momentum), float(sec_weight), float(l2reg_weight),
                      self.norm_terms)
-        elif sec_weight != 0.0 or l2reg_weight != 0.0:
-            raise ValueError('sec_weight / l2reg_weight need track_norms=True')
         return _SupConFunction.apply(features, labels, mask, plan, float(self.temperature),
                                      float(self.base_temperature), bool(self.normalize), norms)
 
