@@ -709,14 +709,17 @@ static int cl_max_active(int cs) {
 static int cl_wave_cap(int cs) { return cl_max_active(cs) * cs; }
 
 // picks (TX, CS) so that the tensor fits the registers of ONE resident wave; false if it does not
-static bool cl_geom(int64_t M, int C, int es, int rows, ClGeom* out) {
+static bool cl_geom(int64_t M, int C, int es, int rows, ClGeom* out, int64_t* out_cost = nullptr) {
     const int vec = 16 / es;
     if (C % vec != 0 || M < 2) return false;
     const int cv = C / vec;
     const int max_cs = cl_max_cs();
     bool found = false;
     int64_t best_cost = 0;
-    for (int cs = max_cs; cs >= 1; cs >>= 1) {
+    // cluster sizes need not be powers of two: 7 CTAs x 16 slabs fit one wave where 8 x 16 do not (SCB_BN_ANY_CLUSTER=0:
+    // powers of two only)
+    static const bool any_cs = [] { const char* e = getenv("SCB_BN_ANY_CLUSTER"); return e == nullptr || e[0] != '0'; }();
+    for (int cs = max_cs; cs >= 1; cs = (any_cs && cs <= 8) ? cs - 1 : cs >> 1) {
         for (int tx = 32; tx >= 1; tx >>= 1) {
             if (cv % tx != 0) continue;
             const int ty = kClThreads / tx;
@@ -733,6 +736,7 @@ static bool cl_geom(int64_t M, int C, int es, int rows, ClGeom* out) {
             }
         }
     }
+    if (found && out_cost != nullptr) *out_cost = best_cost;
     return found;
 }
 
@@ -929,9 +933,15 @@ extern "C" int scb_bn_forward_fused(const void* x, const void* z, void* y, int d
     SCB_DISPATCH_FLOAT(dtype, T, {
         constexpr int VEC = Vec16<T>::N;
         ClGeom g;
-        bool ok = cl_geom(M, C, sizeof(T), kClRows, &g);
+        int64_t cost = 0, cost2 = 0;
+        bool ok = cl_geom(M, C, sizeof(T), kClRows, &g, &cost);
         int nrows = kClRows;
-        if (!ok && !add) { ok = cl_geom(M, C, sizeof(T), 2 * kClRows, &g); nrows = 2 * kClRows; }
+        if (!add) {          // twice the rows per thread: wider slabs may fit one wave (cfg 2: 16 slabs of 32 bytes x 7 CTAs)
+            ClGeom g2;
+            if (cl_geom(M, C, sizeof(T), 2 * kClRows, &g2, &cost2) && (!ok || cost2 < cost)) {
+                g = g2; ok = true; nrows = 2 * kClRows;
+            }
+        }
         if (!ok) SCB_CL_UNSUPPORTED("bn_forward_fused");
         const size_t smem = cl_smem_bytes(g.TX, VEC);
         const T* xp = (const T*)x; const T* zp = (const T*)z; T* yp = (T*)y;
