@@ -376,6 +376,135 @@ bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T
     bn_stamp(4);
 }
 
+// ------------------------------------------------------------------ backward, rows parked in shared memory
+// Same ownership and reduction as bn_bwd_cluster_kernel, but a thread's rows of x and dy sit in shared memory (16-byte
+// asynchronous copies, all in flight at once, no registers tied up), so a CTA holds 12 rows per thread instead of 8:
+// cfg 2 then fits 16 slabs of 32 bytes x clusters of 6 in one wave instead of 32 slabs of 16 bytes x 4, i.e. every
+// load and store moves whole 32-byte sectors.  kGate 0 / 1 (the gate is recomputed from x in both passes).
+constexpr int kClSmemRows = 12;
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(cl_smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+
+template <typename T, int kGate>
+__global__ void __launch_bounds__(kClThreads, 1)
+bn_bwd_cluster_smem_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t M, int C,
+                           const ClGeom g, const float* __restrict__ mean, const float* __restrict__ invstd,
+                           const float* __restrict__ weight, const float* __restrict__ bias,
+                           const float* __restrict__ n_total, float* out_sums, float* grad_weight, float* grad_bias,
+                           int pdt) {
+    constexpr int VEC = Vec16<T>::N;
+    extern __shared__ float smf[];
+    const int TX = g.TX, CS = g.CS, CW = TX * VEC, TY = kClThreads / TX;
+    float* sm = smf;
+    float* gath = sm + (kClThreads / 32) * 2 * CW;
+    float* ab = gath + kClMaxCS * 2 * CW;
+    uint4* park = reinterpret_cast<uint4*>(smf + ((kClThreads / 32 + kClMaxCS + 1) * 2 * CW + 3) / 4 * 4);
+    uint4* sx = park + threadIdx.x;                              // row u of this thread: sx[u * kClThreads]
+    uint4* sd = park + kClSmemRows * kClThreads + threadIdx.x;
+    const uint32_t rank = (CS > 1) ? cl_ctarank() : 0u;
+    const int slab = blockIdx.x / CS;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = slab * CW + tx * VEC;
+    const int64_t r_begin = (int64_t)rank * g.rows_per_cta;
+    const int64_t r_end = min(M, r_begin + g.rows_per_cta);
+    const int64_t r0 = r_begin + ty;
+    const int64_t step = (int64_t)TY * C;
+    bn_stamp(0);
+    int nrow = 0;
+    {
+        const T* px = x + r0 * C + c0;
+        const T* pd = dy + r0 * C + c0;
+#pragma unroll
+        for (int u = 0; u < kClSmemRows; ++u)
+            if (r0 + (int64_t)u * TY < r_end) {
+                cp_async16(sx + u * kClThreads, px + u * step);
+                cp_async16(sd + u * kClThreads, pd + u * step);
+                nrow = u + 1;
+            }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    bn_stamp(1);
+    float s1[VEC], s2[VEC], mu[VEC], k1[VEC], bb[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        s1[i] = 0.f; s2[i] = 0.f;
+        mu[i] = mean[c0 + i];
+        k1[i] = ldp(weight, pdt, c0 + i, 1.f) * invstd[c0 + i];
+        bb[i] = (kGate == 1) ? ldp(bias, pdt, c0 + i, 0.f) : 0.f;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");         // a thread reads only what it copied itself
+#pragma unroll 4
+    for (int u = 0; u < nrow; ++u) {
+        const uint4 vx = sx[u * kClThreads], vd = sd[u * kClThreads];
+        const T* ex = reinterpret_cast<const T*>(&vx);
+        const T* ed = reinterpret_cast<const T*>(&vd);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            const float xm = to_f32(ex[i]) - mu[i];
+            float gv = to_f32(ed[i]);
+            if (kGate == 1 && !(fmaf(xm, k1[i], bb[i]) > 0.f)) gv = 0.f;
+            s1[i] += gv;
+            s2[i] = fmaf(gv, xm, s2[i]);
+        }
+    }
+    bn_stamp(2, s1[0] + s2[0]);
+    const float tot = cluster_channel_sums<VEC>(s1, s2, sm, gath, TX, CS, rank);
+    bn_stamp(3, tot);
+    if ((int)threadIdx.x < 2 * CW) ab[threadIdx.x] = tot;
+    __syncthreads();
+    float v2 = 0.f, v3 = 0.f;
+    if ((int)threadIdx.x < CW) {
+        const int c = slab * CW + threadIdx.x;
+        const float sdy = ab[threadIdx.x], sxy = ab[CW + threadIdx.x];
+        const float is = invstd[c];
+        const float inv_n = 1.f / n_total[0];
+        v2 = sdy * inv_n;
+        v3 = is * is * sxy * inv_n;
+        if (rank == 0) {
+            if (out_sums) { out_sums[c] = sdy; out_sums[C + c] = sxy; }
+            if (grad_weight) stp(grad_weight, pdt, c, sxy * is);
+            if (grad_bias) stp(grad_bias, pdt, c, sdy);
+        }
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < CW) { ab[threadIdx.x] = v2; ab[CW + threadIdx.x] = v3; }
+    __syncthreads();
+    // dx = g A + x B + D with A = k1, B = -k3 k1, D = (mu k3 - k2) k1 (see bn_bwd_cluster_kernel); the gate test
+    // y > 0 is (x - mu) k1 + beta > 0, recomputed exactly as in the first pass
+    float cB[VEC], cD[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        const float k2 = ab[tx * VEC + i], k3 = ab[CW + tx * VEC + i];
+        cB[i] = -k3 * k1[i];
+        cD[i] = (mu[i] * k3 - k2) * k1[i];
+    }
+    T* po = dx + r0 * C + c0;
+#pragma unroll 4
+    for (int u = 0; u < nrow; ++u) {
+        const uint4 vx = sx[u * kClThreads], vd = sd[u * kClThreads];
+        const T* ex = reinterpret_cast<const T*>(&vx);
+        const T* ed = reinterpret_cast<const T*>(&vd);
+        uint4 o;
+        T* oe = reinterpret_cast<T*>(&o);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            const float xv = to_f32(ex[i]);
+            float gv = to_f32(ed[i]);
+            if (kGate == 1 && !(fmaf(xv - mu[i], k1[i], bb[i]) > 0.f)) gv = 0.f;
+            oe[i] = from_f32<T>(fmaf(xv, cB[i], fmaf(gv, k1[i], cD[i])));
+        }
+        stg_stream16(po + u * step, o);
+    }
+    bn_stamp(4);
+}
+
+static size_t cl_smem_park_bytes(int TX, int vec) {
+    return ((size_t)(kClThreads / 32 + kClMaxCS + 1) * 2 * TX * vec + 3) / 4 * 4 * sizeof(float) +
+           (size_t)2 * kClSmemRows * kClThreads * sizeof(uint4);
+}
+
 // =================================================================== streaming cluster kernels
 // Same ownership (a cluster owns a channel slab end to end, sums meet over distributed shared memory), but the rows
 // are STREAMED twice instead of being held in registers: pass 1 accumulates the sums, pass 2 walks the same rows
@@ -802,6 +931,8 @@ template <typename... KArgs, typename... Args>
 static cudaError_t cl_launch(void (*kernel)(KArgs...), const ClGeom& g, size_t smem, cudaStream_t stream, Args&&... args) {
     cudaError_t e = set_max_dynamic_smem(kernel, (int)smem);
     if (e != cudaSuccess) return e;
+    // (no shared-memory carve-out preference here: with the maximum carve-out the register-resident passes, whose loads
+    // are tracked by the L1, slow down by 30-60 %: cfg 2 forward 10.1 -> 13.5 us, backward 14.0 -> 22.1 us)
     if (g.CS > 8 && !attr_done((const void*)kernel, (int)cudaFuncAttributeNonPortableClusterSizeAllowed, 1)) {
         e = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         if (e != cudaSuccess) return e;
@@ -1031,6 +1162,19 @@ static int bn_backward_cluster(const void* dy, const void* x, const void* y, voi
         ClGeom g;
         if (!cl_geom(M, C, sizeof(T), kClRows, &g)) SCB_CL_UNSUPPORTED("bn_backward_fused");
         cudaError_t err;
+        // 16-byte slabs in registers, but 32 bytes or more with 12 rows per thread parked in shared memory: take those
+        ClGeom gp;
+        static const bool park_on = [] { const char* e = getenv("SCB_BN_PARK"); return e == nullptr || e[0] != '0'; }();
+        if (park_on && !reduce_only && gate != 2 && g.TX == 1 && cl_geom(M, C, sizeof(T), kClSmemRows, &gp) && gp.TX >= 2 &&
+            cl_smem_park_bytes(gp.TX, Vec16<T>::N) <= 220 * 1024) {
+            const size_t smem = cl_smem_park_bytes(gp.TX, Vec16<T>::N);
+            if (gate == 1)
+                err = cl_launch(bn_bwd_cluster_smem_kernel<T, 1>, gp, smem, stream, (const T*)dy, (const T*)x, (T*)dx, M, C, gp,
+                                mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
+            else
+                err = cl_launch(bn_bwd_cluster_smem_kernel<T, 0>, gp, smem, stream, (const T*)dy, (const T*)x, (T*)dx, M, C, gp,
+                                mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
+        } else
         if (reduce_only) {
             if (gate == 2) err = cl_launch_bwd<T, 1, 2>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
             else if (gate == 1) err = cl_launch_bwd<T, 1, 1>(g, stream, dy, x, y, dx, dz, M, C, mean, invstd, weight, bias, n_total, out_sums, grad_weight, grad_bias, param_dtype);
