@@ -360,7 +360,9 @@ def test_residual_add_relu_matches_unfused_expression(shape, cl, dtype, relu):
 @pytest.mark.parametrize('shape,dtype', [((256, 256, 8, 8), torch.bfloat16), ((64, 128, 8, 8), torch.float32),
                                          ((512, 512, 4, 4), torch.bfloat16), ((128, 256, 16, 16), torch.bfloat16),
                                          ((384, 256, 8, 8), torch.bfloat16), ((512, 256, 8, 8), torch.bfloat16),
-                                         ((200, 96, 8, 8), torch.float32)])
+                                         ((200, 96, 8, 8), torch.float32),
+                                         # ragged row counts through the shared-memory-parked backward (32-byte slabs x clusters of 6)
+                                         ((250, 256, 8, 8), torch.bfloat16), ((255, 256, 7, 9), torch.float16)])
 def test_cluster_kernels_match_multi_kernel_path(shape, dtype, monkeypatch):
     """Single-launch kernels (register-resident cluster passes; for the 12-16 MB shapes the shared-memory-resident
     passes behind the cooperative grid barrier) vs stats -> apply / reduce -> apply on the same tensors."""
@@ -384,7 +386,7 @@ def test_cluster_kernels_match_multi_kernel_path(shape, dtype, monkeypatch):
             bn.weight.fill_(1.25); bn.bias.fill_(0.1)
         y, dx, gw, gb = ours_fwd_bwd(x, dy, bn)
         outs.append((y.float(), dx.float(), gw, gb, bn.running_mean.clone(), bn.running_var.clone()))
-    tol = 2.0 ** -7 if dtype == torch.bfloat16 else 1e-5
+    tol = 2.0 ** -7 if dtype == torch.bfloat16 else (2.0 ** -10 if dtype == torch.float16 else 1e-5)
     # the ReLU gate may flip for outputs within rounding of zero: compare away from it
     far = outs[1][0].abs() > 1e-2
     assert torch.all(((outs[0][0] - outs[1][0]).abs() <= tol * outs[1][0].abs() + 1e-5) | ~far)
