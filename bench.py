@@ -957,7 +957,10 @@ def main():
         step_res(1)
         launches = lib.scb_launch_count() - c0
         ms, how = time_steps(step_res, args.steps, args.warmup, world, graph_pool=pool)
-        ms_e2e, _ = time_steps(step_e2e, args.steps, args.warmup, world)
+        # one device per process: autograd may run the backward in the calling thread instead of handing it to its
+        # device thread (a PyTorch switch any training script can set; 55 -> 39 us of host time per backward)
+        with torch.autograd.set_multithreading_enabled(False):
+            ms_e2e, _ = time_steps(step_e2e, args.steps, args.warmup, world)
         per = ms / args.steps
         A = C = N_VIEWS * B_GLOBAL
         flops_step = 6.0 * A * C * DIM
@@ -978,7 +981,8 @@ def main():
                     'note': 'each step: H2D of its embeddings from pinned memory (prefetched one step ahead on a '
                             'copy stream), forward + backward through the module in graph mode (SupConLoss / '
                             'DistributedSupConLoss with graph=True: one captured forward+backward, exchanges '
-                            'included, replayed per step), D2H of the loss, host sync; the gradient stays on the device'},
+                            'included, replayed per step), D2H of the loss, host sync; the gradient stays on the device; '
+                            'torch.autograd.set_multithreading_enabled(False) (one device per process)'},
             'gpu_launches': int(launches),
         })
         # roofline of the STEP (6*A*C*D algorithmic FLOPs of SURVEY 8(d) over the graph-replayed step time, per GPU);
@@ -1028,7 +1032,10 @@ def main():
         step_res(1)
         launches = lib.scb_launch_count() - c0
         ms, how = time_steps(step_res, args.steps, args.warmup, world, graph_pool=pool)
-        ms_e2e, _ = time_steps(step_e2e, args.steps, args.warmup, world)
+        # one device per process: autograd may run the backward in the calling thread instead of handing it to its
+        # device thread (a PyTorch switch any training script can set; 55 -> 39 us of host time per backward)
+        with torch.autograd.set_multithreading_enabled(False):
+            ms_e2e, _ = time_steps(step_e2e, args.steps, args.warmup, world)
         per = ms / args.steps
         gbs = 8.0 * S / (per * 1e-3) / 1e9           # per GPU; algorithmic bytes of SURVEY 8(d)
         sb = {'metric': 'SyncBN fwd+bwd HBM GB/s', 'value': gbs * world, 'per_gpu': gbs, 'unit': 'GB/s',

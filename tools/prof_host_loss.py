@@ -161,6 +161,9 @@ variant('+ raw cudart copies/events', True, True, True)
 variant('raw copies, D2H last', False, True, True)
 variant('bench.py now: persistent leaves, event wait', True, False, True, lean=True)
 variant('same with backward(ones)', True, True, True, lean=True)
+with torch.autograd.set_multithreading_enabled(False):      # backward runs in the calling thread: no hand-over
+    variant('bench.py now + single-threaded autograd', True, False, True, lean=True)
+    variant('same with backward(ones)', True, True, True, lean=True)
 variant('floor: graph replay + raw copies, no autograd', True, True, True, no_autograd=True)
 
 # bench.py's own end-to-end step function, timed the same way (wall clock) in this process
