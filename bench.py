@@ -1048,9 +1048,10 @@ def main():
               'gpu_launches': int(launches)}
         # roofline of the STEP: 8*S algorithmic bytes over the graph-replayed fwd+bwd, per GPU
         sb['roofline'] = {'bound': 'hbm', 'achieved': gbs, 'peak': pk['hbm'], 'unit': 'GB/s', 'frac': gbs / pk['hbm'],
-                          'traffic': profiled_traffic('bn_bwd_cluster') or profiled_traffic('bn_fwd_cluster'),
+                          'traffic': (profiled_traffic('bn_bwd_cluster_smem') or profiled_traffic('bn_bwd_cluster')
+                                      or profiled_traffic('bn_fwd_cluster')),
                           'kernel': 'whole step (%d launches): '
-                          'bn_fwd_cluster_kernel + bn_bwd_cluster_kernel' % launches,
+                          'bn_fwd_cluster_kernel + bn_bwd_cluster_smem_kernel; traffic = the backward kernel' % launches,
                           'peak_source': pk['src'], 'algorithmic_bytes_per_step': 8 * S,
                           'note': 'the single-launch passes move 5*S (x once forward; x, dy once backward; y, dx written)'}
         if rank == 0 and world == 1:
