@@ -457,9 +457,10 @@ class SupConLoss(nn.Module):
 class GraphCache:
     """Captured forward+backward graphs of a loss module, per (shape, dtype, strides, labels?) and input address.
 
-    A graph is bound to the address of its input: callers that feed the loss from a few recurring buffers (a
-    double-buffered prefetcher, a preallocated projection output) get one graph per buffer and no copy; any other
-    input is copied into a buffer the cache owns.  `bind_addresses=False` (the row-sharded loss): always the owned
+    A graph is bound to the address of its input: callers that feed the loss from a few recurring addresses (a
+    double-buffered prefetcher, a preallocated projection output, or simply a training loop whose features land at the
+    same allocator address every step) get one graph per address and no copy; any other input is copied into a buffer
+    the cache owns.  `bind_addresses=False` (the row-sharded loss): always the owned
     buffer, so that whether a call captures or replays depends on the shape alone and every rank decides alike."""
     MAX_ADDRESSES = 4           # captured graphs bound to the caller's own input buffers, per shape
 
@@ -515,4 +516,10 @@ class GraphCache:
             loss = inner(leaf, labels=e.labels)
             loss.backward(ones)
         e.loss, e.grad = loss.detach(), leaf.grad
+        if not own_input:
+            # Do not keep the caller's buffer alive: a training loop's features are a fresh allocation every step that
+            # the caching allocator places at the same address once the previous step's tensor is gone -- holding on to
+            # it would force a new address (and a new capture) every step.  The graph is only ever replayed for an
+            # incoming tensor that IS at this address (same shape, strides, dtype), so the memory is live when it runs.
+            e.x = None
         return e

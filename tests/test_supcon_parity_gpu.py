@@ -9,6 +9,7 @@ import torch.nn.functional as F
 
 from oracle import supcon_forward_backward, normalize_rows, normalize_rows_backward
 from simclr_pytorch_distributed_b200 import SupConLoss
+from simclr_pytorch_distributed_b200.losses import GraphCache
 
 pytestmark = pytest.mark.gpu
 
@@ -202,6 +203,22 @@ def test_graph_mode_matches_eager():
         l1 = graphed(b1)
         graphed(bufs[0].detach().requires_grad_(True))
         l1.backward()
+    # a training loop's features are a fresh allocation every step; the allocator tends to hand out the same address
+    # again, and the graph bound to it must then see the NEW contents (the entry does not keep the old tensor alive)
+    loop = SupConLoss(temperature=0.5, engine='bf16', graph=True)
+    addresses = set()
+    for step in range(6):
+        z = F.normalize(torch.randn(512, 2, 128, device='cuda'), dim=-1).to(torch.bfloat16).requires_grad_(True)
+        addresses.add(z.data_ptr())
+        a = z.detach().clone().requires_grad_(True)
+        la, lb = eager(a), loop(z)
+        la.backward()
+        lb.backward()
+        assert float(la) == float(lb)
+        assert torch.equal(a.grad, z.grad)
+        del z, a, la, lb
+    bound = [k for per_shape in loop._graph_cache.graphs.values() for k in per_shape if k != 'own']
+    assert set(bound) <= addresses and len(bound) <= GraphCache.MAX_ADDRESSES
     # the module's settings are baked into its graphs: changing one re-captures
     for crit in (eager, graphed):
         crit.temperature, crit.contrast_mode = 0.2, 'one'
