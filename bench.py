@@ -1044,7 +1044,9 @@ def main():
                          'l2': 'x/dy/y/dx rotate through %d buffer sets (> L2)' % pool,
                          'launch': 'public module API (SyncBatchNorm.forward + autograd backward); ' + how},
               'e2e': {'value': 8.0 * S * world / (ms_e2e / args.steps * 1e-3) / 1e9, 'unit': 'GB/s',
-                      'h2d_bytes_per_step': 2 * S, 'd2h_bytes_per_step': 2 * S},
+                      'h2d_bytes_per_step': 2 * S, 'd2h_bytes_per_step': 2 * S,
+                      'note': 'bound by the host link: x and dy go in, y and dx come back, 4*S = 33.6 MB per step '
+                              'over PCIe against 23 us of kernels -- a PCIe figure, not a kernel one'},
               'gpu_launches': int(launches)}
         # roofline of the STEP: 8*S algorithmic bytes over the graph-replayed fwd+bwd, per GPU
         sb['roofline'] = {'bound': 'hbm', 'achieved': gbs, 'peak': pk['hbm'], 'unit': 'GB/s', 'frac': gbs / pk['hbm'],
