@@ -236,7 +236,7 @@ def make_loss_runner(world, rank, engine, pool, b_local=None):
         cs = copy_stream.cuda_stream
         ready_h, freed_h = [e.cuda_event for e in ready], [e.cuda_event for e in freed]
         host_ptr, slot_ptr, loss_host_ptr = [h.data_ptr() for h in host], [t.data_ptr() for t in slots], loss_host.data_ptr()
-    except ImportError:
+    except (ImportError, AttributeError):       # no cuda-python (or another layout of it): torch's own calls
         rt = None
 
     def prefetch(j):
